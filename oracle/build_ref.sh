@@ -79,9 +79,12 @@ cc tinyblas_cpu_mixmul_amd_avx "$AVX"
 # pristine upstream ggml (haswell ISA so the AVX2 quantize_row_q8_0 body, ggml-quants.c:940-990, is
 # the one compiled and the .so also runs on hosts without AVX-512).
 GG="$REF/llama.cpp/ggml"
+# llamafile's own (patched) AVX2 build of ggml-quants: runtime quantizers + vec_dots, block_q8_K = {d,bsums,qs}
+( cd "$S" && gcc -O2 -fPIC -fvisibility=hidden -mavx -mavx2 -mfma -mf16c -ffp-contract=off -DNDEBUG -w \
+      -I. -Ishim -c llama.cpp/ggml-quants-amd-avx2.c -o obj/lf_quants_avx2.o ) & pids+=($!)
 for f in ggml ggml-quants ggml-aarch64 ggml-alloc ggml-backend; do
   ( gcc -O2 -fPIC -fvisibility=hidden -mavx -mavx2 -mfma -mf16c -ffp-contract=off -D_GNU_SOURCE \
-        -DNDEBUG -w -I"$GG/include" -I"$GG/src" -c "$GG/src/$f.c" -o "$S/obj/up_$f.o" ) & pids+=($!)
+        -DNDEBUG -w -Dquantize_row_q8_0=upstream_quantize_row_q8_0 -I"$GG/include" -I"$GG/src" -c "$GG/src/$f.c" -o "$S/obj/up_$f.o" ) & pids+=($!)
 done
 ( g++ $CXXF $AVX2 -fopenmp -c "$HERE/ref_wrap.cpp" -o "$S/obj/ref_wrap.o" ) & pids+=($!)
 for p in "${pids[@]}"; do wait "$p"; done

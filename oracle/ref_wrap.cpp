@@ -25,18 +25,25 @@ __attribute__((visibility("default"))) bool FLAG_log_disable = true;
 void ggml_barrier(const struct ggml_compute_params *) {
 #pragma omp barrier
 }
-// pristine upstream (ggml/src/ggml-quants.c, ggml.c)
-void quantize_row_q8_0(const float *x, void *y, int64_t k);
-void quantize_row_q8_0_ref(const float *x, void *y, int64_t k);
-void quantize_row_q8_K(const float *x, void *y, int64_t k);
-void quantize_row_q4_0_ref(const float *x, void *y, int64_t k);
-void quantize_row_q4_K_ref(const float *x, void *y, int64_t k);
-void dequantize_row_q4_0(const void *x, float *y, int64_t k);
-void dequantize_row_q8_0(const void *x, float *y, int64_t k);
-void dequantize_row_q4_K(const void *x, float *y, int64_t k);
-void ggml_vec_dot_q4_0_q8_0(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
-void ggml_vec_dot_q8_0_q8_0(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
-void ggml_vec_dot_q4_K_q8_K(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
+// llamafile's runtime-dispatched ggml-quants (llama.cpp.patches/llamafile-files/ggml-quants.cpp:782-1597
+// picks a per-ISA build of the PATCHED ggml-quants.inc; we link the AVX2 build,
+// llamafile-files/ggml-quants-amd-avx2.c — the quantize_row_q8_0 body is the same for every x86 ISA
+// level >= AVX, ggml-quants.c:940-990). The patched build matters: llamafile reorders block_q8_K to
+// {d, bsums, qs} (llama.cpp.patches/patches/ggml-common.h.patch:25-35).
+#define Q(name) name##_amd_avx2
+void Q(quantize_row_q8_0)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q8_0_ref)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q8_K)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q4_0_ref)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q4_K_ref)(const float *x, void *y, int64_t k);
+void Q(dequantize_row_q4_0)(const void *x, float *y, int64_t k);
+void Q(dequantize_row_q8_0)(const void *x, float *y, int64_t k);
+void Q(dequantize_row_q4_K)(const void *x, float *y, int64_t k);
+void Q(ggml_vec_dot_q4_0_q8_0)(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
+void Q(ggml_vec_dot_q8_0_q8_0)(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
+void Q(ggml_vec_dot_q4_K_q8_K)(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
+// what llamafile's dispatcher resolves `quantize_row_q8_0` to (imported by tinyblas_cpu_mixmul.inc:343)
+void quantize_row_q8_0(const float *x, void *y, int64_t k) { Q(quantize_row_q8_0)(x, y, k); }
 }
 
 namespace {
@@ -160,40 +167,40 @@ EXPORT int ref_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, cons
 EXPORT void ref_quantize_q8_0(const float *x, void *y, long rows, long k, int nth) {
     funcs();
 #pragma omp parallel for num_threads(clamp_threads(nth))
-    for (long r = 0; r < rows; ++r) quantize_row_q8_0(x + r * k, (char *)y + r * (k / 32) * 34, k);
+    for (long r = 0; r < rows; ++r) Q(quantize_row_q8_0)(x + r * k, (char *)y + r * (k / 32) * 34, k);
 }
 EXPORT void ref_quantize_q8_0_ref(const float *x, void *y, long rows, long k) {
     funcs();
-    for (long r = 0; r < rows; ++r) quantize_row_q8_0_ref(x + r * k, (char *)y + r * (k / 32) * 34, k);
+    for (long r = 0; r < rows; ++r) Q(quantize_row_q8_0_ref)(x + r * k, (char *)y + r * (k / 32) * 34, k);
 }
 EXPORT void ref_quantize_q8_K(const float *x, void *y, long rows, long k, int nth) {
     funcs();
 #pragma omp parallel for num_threads(clamp_threads(nth))
-    for (long r = 0; r < rows; ++r) quantize_row_q8_K(x + r * k, (char *)y + r * (k / 256) * 292, k);
+    for (long r = 0; r < rows; ++r) Q(quantize_row_q8_K)(x + r * k, (char *)y + r * (k / 256) * 292, k);
 }
 EXPORT void ref_quantize_q4_0_ref(const float *x, void *y, long rows, long k) {
     funcs();
 #pragma omp parallel for
-    for (long r = 0; r < rows; ++r) quantize_row_q4_0_ref(x + r * k, (char *)y + r * (k / 32) * 18, k);
+    for (long r = 0; r < rows; ++r) Q(quantize_row_q4_0_ref)(x + r * k, (char *)y + r * (k / 32) * 18, k);
 }
 EXPORT void ref_quantize_q4_K_ref(const float *x, void *y, long rows, long k) {
     funcs();
 #pragma omp parallel for
-    for (long r = 0; r < rows; ++r) quantize_row_q4_K_ref(x + r * k, (char *)y + r * (k / 256) * 144, k);
+    for (long r = 0; r < rows; ++r) Q(quantize_row_q4_K_ref)(x + r * k, (char *)y + r * (k / 256) * 144, k);
 }
 EXPORT void ref_fp32_to_fp16_row(const float *x, uint16_t *y, long n) { funcs(); ggml_fp32_to_fp16_row(x, y, n); }
 EXPORT void ref_fp16_to_fp32_row(const uint16_t *x, float *y, long n) { funcs(); ggml_fp16_to_fp32_row(x, y, n); }
-EXPORT void ref_dequantize_q4_0(const void *x, float *y, long n) { funcs(); dequantize_row_q4_0(x, y, n); }
-EXPORT void ref_dequantize_q8_0(const void *x, float *y, long n) { funcs(); dequantize_row_q8_0(x, y, n); }
-EXPORT void ref_dequantize_q4_K(const void *x, float *y, long n) { funcs(); dequantize_row_q4_K(x, y, n); }
+EXPORT void ref_dequantize_q4_0(const void *x, float *y, long n) { funcs(); Q(dequantize_row_q4_0)(x, y, n); }
+EXPORT void ref_dequantize_q8_0(const void *x, float *y, long n) { funcs(); Q(dequantize_row_q8_0)(x, y, n); }
+EXPORT void ref_dequantize_q4_K(const void *x, float *y, long n) { funcs(); Q(dequantize_row_q4_K)(x, y, n); }
 
 // the semantic definitions north_star cites (ggml-quants.c:3729, :5227, :6832)
 EXPORT float ref_vec_dot_q4_0_q8_0(long n, const void *x, const void *y) {
-    funcs(); float s = 0; ggml_vec_dot_q4_0_q8_0((int)n, &s, 0, x, 0, y, 0, 1); return s;
+    funcs(); float s = 0; Q(ggml_vec_dot_q4_0_q8_0)((int)n, &s, 0, x, 0, y, 0, 1); return s;
 }
 EXPORT float ref_vec_dot_q8_0_q8_0(long n, const void *x, const void *y) {
-    funcs(); float s = 0; ggml_vec_dot_q8_0_q8_0((int)n, &s, 0, x, 0, y, 0, 1); return s;
+    funcs(); float s = 0; Q(ggml_vec_dot_q8_0_q8_0)((int)n, &s, 0, x, 0, y, 0, 1); return s;
 }
 EXPORT float ref_vec_dot_q4_K_q8_K(long n, const void *x, const void *y) {
-    funcs(); float s = 0; ggml_vec_dot_q4_K_q8_K((int)n, &s, 0, x, 0, y, 0, 1); return s;
+    funcs(); float s = 0; Q(ggml_vec_dot_q4_K_q8_K)((int)n, &s, 0, x, 0, y, 0, 1); return s;
 }
