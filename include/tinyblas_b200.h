@@ -1,0 +1,205 @@
+/* tinyBLAS-B200 — C ABI of the B200-native quantized-matmul module.
+ *
+ * The module is one shared object, libtinyblas_b200.so (sm_100a CUDA + a C++ host layer), loaded
+ * the way llamafile loads its GPU DSO (llamafile/cuda.c:701-753: dlopen -> dlsym table -> link()
+ * handshake that answers "is there a usable device"). Nothing in these signatures is a torch or
+ * C++ type: plain pointers, sizes and ggml type codes only.
+ *
+ * Part 1 are the reference's own entry points for the hot path (llamafile/sgemm.h:23-28, 76-77),
+ * same names, argument meaning and error behaviour, taking HOST pointers exactly like the CPU
+ * implementation they replace. Part 2 is the additive device-level API a GPU backend needs
+ * (last row): resident weights, device-pointer matmuls, activation quantizers.
+ *
+ * There is no CPU fallback anywhere in the module: when no sm_100 device is present
+ * tb200_link() returns false and every compute entry point returns false / TB200_ERR_NO_DEVICE.
+ */
+#ifndef TINYBLAS_B200_H
+#define TINYBLAS_B200_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* llamafile is a Cosmopolitan binary and marks every cross-module pointer ms_abi
+ * (llama.cpp/ggml/include/ggml.h:190-198). Our host is glibc; keep the hook. */
+#ifndef TB200_CALL
+#define TB200_CALL
+#endif
+#define TB200_API __attribute__((visibility("default")))
+
+/* ggml type codes (llama.cpp/ggml/include/ggml.h:361-397) */
+enum tb200_type {
+    TB200_TYPE_F32 = 0,
+    TB200_TYPE_F16 = 1,
+    TB200_TYPE_Q4_0 = 2,
+    TB200_TYPE_Q8_0 = 8,
+    TB200_TYPE_Q4_K = 12,
+    TB200_TYPE_Q8_K = 15,
+    TB200_TYPE_I32 = 26,
+};
+
+/* GGUF block layouts, unchanged (llama.cpp/ggml/src/ggml-common.h:144-149, 186-191, 266-277;
+ * block_q8_K in llamafile's field order {d, bsums, qs}: llama.cpp.patches/patches/ggml-common.h.patch:25-35) */
+#pragma pack(push, 1)
+typedef struct { uint16_t d; uint8_t qs[16]; } tb200_block_q4_0;
+typedef struct { uint16_t d; int8_t qs[32]; } tb200_block_q8_0;
+typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qs[128]; } tb200_block_q4_K;
+typedef struct { float d; int16_t bsums[16]; int8_t qs[256]; } tb200_block_q8_K;
+#pragma pack(pop)
+
+/* Layout-compatible prefix views of the two ggml structs llamafile_mixmul reads
+ * (struct ggml_tensor: llama.cpp/ggml/include/ggml.h:583-618, fields type/ne/nb/data;
+ *  struct ggml_compute_params: llama.cpp.patches/patches/ggml.h.patch:48-57). */
+struct ggml_tensor;
+struct ggml_compute_params;
+typedef struct {
+    int32_t type;
+    int32_t backend_;
+    void *buffer_;
+    int64_t ne[4];
+    size_t nb[4];
+    int32_t op_;
+    int32_t op_params_[16];
+    int32_t flags_;
+    void *grad_;
+    void *src_[10];
+    void *view_src_;
+    size_t view_offs_;
+    void *data;
+    /* char name[128]; void *extra;  (not read) */
+} tb200_ggml_tensor_view;
+typedef struct {
+    int ith, nth;
+    size_t wsize;
+    void *wdata;
+    void *shared_;
+} tb200_ggml_compute_params_view;
+
+/* ------------------------------------------------------------------------------------------
+ * Part 1 — the reference's entry points (host pointers)
+ * ------------------------------------------------------------------------------------------ */
+
+/* llamafile/sgemm.h:23-24, llamafile/sgemm.cpp:128-131. C[ldc*j + i] = sum_l A[lda*i + l] * B[ldb*j + l],
+ * m = weight rows, n = tokens, k/lda/ldb counted in BLOCKS of Atype/Btype, ldc in floats.
+ * Serviced (returns true, C written) for the combinations the reference's x86 build services:
+ *   Q4_0 x Q8_0, Q8_0 x Q8_0, Q4_K x Q8_K, F16 x F16, F16 x F32 (n <= 2), F32 x F32; Ctype F32.
+ * Anything else returns false before touching C ("not handled, caller falls back"), never an error.
+ * Threading contract: ggml calls this from all nth worker threads. Thread 0 does the whole job
+ * on the GPU and returns after C is complete; threads ith != 0 return true immediately and rely on
+ * the caller's barrier after the op (ggml.c.patch:2316), as the CPU kernels do for their own tiles.
+ * A (the mmap'd weights) is uploaded once and cached by (A, m, k, lda, Atype). */
+TB200_API bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void *B, long ldb,
+                               void *C, long ldc, int ith, int nth, int Atype, int Btype, int Ctype);
+
+/* llamafile/sgemm.h:25-28, llamafile/tinyblas_cpu_mixmul.inc:390-398. weights [cols, rows, experts],
+ * thought [cols, tasks, tokens] (F32 or the vec_dot type), plan [thinkers, tokens] I32,
+ * result [rows, thinkers, tokens] F32. Weight types F16, Q8_0, Q4_0 as in the reference; false otherwise. */
+TB200_API bool llamafile_mixmul(const struct ggml_compute_params *params, const struct ggml_tensor *weights,
+                                const struct ggml_tensor *thought, const struct ggml_tensor *plan,
+                                struct ggml_tensor *result);
+
+/* llamafile/tinyblas_cpu_mixmul_amd_avx.cpp:8-18: host scratch bytes llamafile_mixmul would carve from
+ * params->wdata. The GPU module keeps its scratch in HBM, but reports the reference's figure so that
+ * ggml_graph_plan (ggml.c.patch:2279-2285) sizes wdata identically. */
+TB200_API size_t llamafile_mixmul_needs(const struct ggml_tensor *weights, const struct ggml_tensor *thought,
+                                        const struct ggml_tensor *plan);
+
+/* llamafile/sgemm.h:76-77, llamafile/iqk_mul_mat.inc:204-221: one expert's rows with an
+ * mmid_row_mapping {int32 i1, int32 i2}[Ny]; typeA Q4_K (B rows Q8_K) or Q4_0 (B rows Q8_0). */
+TB200_API bool llamafile_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, const void *A,
+                                    const void *B, float *C, long nb1, long nb2, const void *vrow_mapping,
+                                    int ith, int nth);
+
+/* from_float of the vec_dot types (ggml.c type_traits: quantize_row_q8_0 ggml-quants.c:866/940-990,
+ * quantize_row_q8_K :3593-3645, ggml_fp32_to_fp16_row). Host in, host out, bit-exact. */
+TB200_API bool tb200_quantize_row_q8_0(const float *x, void *y, int64_t k);
+TB200_API bool tb200_quantize_row_q8_K(const float *x, void *y, int64_t k);
+TB200_API bool tb200_fp32_to_fp16_row(const float *x, uint16_t *y, int64_t k);
+
+/* ------------------------------------------------------------------------------------------
+ * Part 2 — module handshake and device-level API (additive)
+ * ------------------------------------------------------------------------------------------ */
+
+enum tb200_status {
+    TB200_OK = 0,
+    TB200_ERR_NO_DEVICE = 1,
+    TB200_ERR_UNSUPPORTED = 2,   /* the reference would return false for this request */
+    TB200_ERR_INVALID = 3,
+    TB200_ERR_CUDA = 4,
+};
+
+/* Host services handed to the module at link time, the way llamafile passes libc + ggml helpers
+ * through struct ggml_backend_api (llama.cpp.patches/patches/ggml-backend-impl.h.patch:20-58).
+ * Every member may be NULL (the module then uses its own libc). */
+struct tb200_host_api {
+    void *(TB200_CALL *malloc)(size_t);
+    void (TB200_CALL *free)(void *);
+    long (TB200_CALL *write)(int fd, const void *buf, size_t n);   /* log sink, as g_backend->write */
+    const char *(TB200_CALL *getenv)(const char *);
+};
+
+/* Handshake, mirrors ggml_cuda_link (ggml-cuda.cu.patch:468-520): stores the table, initialises the
+ * current device, returns true iff an sm_100 device is usable. */
+TB200_API bool tb200_link(const struct tb200_host_api *api);
+TB200_API int tb200_device_count(void);
+TB200_API int tb200_set_device(int device);
+TB200_API const char *tb200_last_error(void);
+TB200_API int tb200_sm_count(void);
+/* Stream used by all device-level calls of the calling thread's device (cudaStream_t as void*). */
+TB200_API int tb200_set_stream(void *cuda_stream);
+TB200_API int tb200_synchronize(void);
+
+/* Resident weights. `rows` weight rows of `k` ELEMENTS each in GGUF layout (F16, Q8_0, Q4_0, Q4_K),
+ * `row_stride` bytes apart. Upload = copy + one-time device repack into aligned planes (quants plane,
+ * scales plane) of identical total size; the GGUF bytes themselves are not modified. */
+typedef struct tb200_weights tb200_weights;
+TB200_API tb200_weights *tb200_weights_upload(const void *host_rows, int type, long rows, long k, size_t row_stride);
+TB200_API tb200_weights *tb200_weights_from_device(const void *dev_rows, int type, long rows, long k, size_t row_stride);
+TB200_API void tb200_weights_free(tb200_weights *w);
+TB200_API size_t tb200_weights_bytes(const tb200_weights *w);
+
+/* Device-pointer activation quantizers: x [rows][k] f32 (row stride ldx floats) -> GGUF blocks,
+ * rows contiguous. Bit-exact to the reference. */
+TB200_API int tb200_quantize_q8_0_dev(const float *x, long ldx, void *y, long rows, long k);
+TB200_API int tb200_quantize_q8_K_dev(const float *x, long ldx, void *y, long rows, long k);
+
+/* ggml_compute_forward_mul_mat for one weight matrix (ggml.c:12277-12403): out[t*ldo + i] =
+ * W[i] . vec_dot_type(x[t]); x f32 [tokens][k] on the device, quantized on the device exactly as the
+ * reference does (Q8_0 / Q8_K / F16, or kept F32 for F16 weights when tokens <= 2). Decode kernels for
+ * tokens <= TB200_GEMV_MAX_TOKENS, tcgen05 GEMM above. */
+#define TB200_GEMV_MAX_TOKENS 8
+TB200_API int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens, float *out, long ldo);
+
+/* llamafile_sgemm on device pointers with pre-quantized activations B (GGUF blocks of Btype, ldb in
+ * blocks). Same service matrix as llamafile_sgemm. */
+TB200_API int tb200_sgemm_dev(const tb200_weights *w, long n, const void *B, long ldb, int Btype, float *C, long ldc);
+
+/* Integer block dot products of one weight row set against one activation row, for parity checks:
+ * out[i*nb + b] (Q4_0/Q8_0: int32 per 32-block; Q4_K: two int32 per super-block, as the oracle). */
+TB200_API int tb200_blockdot_dev(const tb200_weights *w, const void *B, int Btype, int32_t *out);
+
+/* llamafile_mixmul on device pointers. weights: `experts` consecutive resident matrices (one upload of
+ * experts*rows rows). thought f32 [tokens][tasks][k] contiguous, plan i32 [tokens][thinkers],
+ * result f32 [tokens][thinkers][rows]. Rows whose plan entry is outside [0, experts) are left untouched. */
+TB200_API int tb200_mixmul_dev(const tb200_weights *w, int experts, const float *thought, int tasks,
+                               const int32_t *plan, int thinkers, long tokens, float *result);
+
+/* raw device memory helpers for hosts without a CUDA runtime of their own */
+TB200_API void *tb200_malloc(size_t bytes);
+TB200_API void tb200_free(void *p);
+TB200_API int tb200_memcpy_h2d(void *dst, const void *src, size_t bytes);
+TB200_API int tb200_memcpy_d2h(void *dst, const void *src, size_t bytes);
+TB200_API void *tb200_host_alloc(size_t bytes);   /* pinned */
+TB200_API void tb200_host_free(void *p);
+
+/* counters: kernels launched by this module since load (bench.py's gpu_launches) */
+TB200_API uint64_t tb200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TINYBLAS_B200_H */

@@ -1,0 +1,130 @@
+// tinyBLAS-B200 internal definitions shared by all translation units (sm_100a only).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/tinyblas_b200.h"
+
+#ifndef __CUDA_ARCH__
+#define TB200_HOST_ONLY 1
+#endif
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "tinyBLAS-B200 is written for sm_100a only"
+#endif
+
+#define QK 32
+#define QK_K 256
+
+static_assert(sizeof(tb200_block_q4_0) == 18, "block_q4_0");
+static_assert(sizeof(tb200_block_q8_0) == 34, "block_q8_0");
+static_assert(sizeof(tb200_block_q4_K) == 144, "block_q4_K");
+static_assert(sizeof(tb200_block_q8_K) == 292, "block_q8_K");
+
+// ---------------------------------------------------------------------------------------------
+// Resident weight matrix: the GGUF rows split into 16-byte-aligned planes (one-time repack at
+// upload, tb200_repack.cu). Total bytes are identical to the GGUF encoding.
+//   Q4_0: qs  [rows][k/32] x 16 B  (byte j: low nibble = elem j, high nibble = elem j+16)
+//         sc  [rows][k/32] fp16 d
+//   Q8_0: qs  [rows][k] int8 ;  sc [rows][k/32] fp16 d
+//   Q4_K: qs  [rows][k/256] x 128 B ; sc [rows][k/256] x 16 B = {fp16 d, fp16 dmin, u8 scales[12]}
+//   F16 : qs  [rows][k] fp16 ; sc = nullptr
+// ---------------------------------------------------------------------------------------------
+struct tb200_weights {
+    int type;
+    long rows, k;
+    void *qs;
+    void *sc;
+    size_t qs_row_bytes, sc_row_bytes;
+    size_t bytes;
+    int device;
+    void *tmap_cache;   // prefill GEMM tensor maps (tb200_gemm.cu), lazily built
+};
+
+// Quantized activations in the module's internal planar form (one per call, lives in scratch):
+//   q   int8  [tokens][k]
+//   ds  {float d, int32 sum} per 32-block [tokens][k/32]   (Q8_0: d = fp16 scale widened; sum = sum of q)
+//   Q8_K: d is the per-256 float scale replicated on its 8 sub-blocks, sum = bsums[2s]+bsums[2s+1]
+struct tb200_acts {
+    const int8_t *q;
+    const int2 *ds;
+    long k;
+    long tokens;
+};
+
+// per-device context (tb200_api.cu)
+struct tb200_ctx {
+    int device;
+    int sm_count;
+    cudaStream_t stream;
+    void *scratch;          // device scratch arena (activations, gathered rows, ...)
+    size_t scratch_bytes;
+    void *pinned;           // host staging for the host-pointer entry points
+    size_t pinned_bytes;
+};
+
+tb200_ctx *tb200_get_ctx();                       // nullptr when no device
+void *tb200_scratch(tb200_ctx *c, size_t bytes);  // grows on demand (stream-ordered)
+void tb200_set_error(const char *fmt, ...);
+void tb200_count_launch(int n = 1);
+
+#define TB_CUDA(expr)                                                                              \
+    do {                                                                                           \
+        cudaError_t e_ = (expr);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            tb200_set_error("%s:%d %s: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_));    \
+            return TB200_ERR_CUDA;                                                                 \
+        }                                                                                          \
+    } while (0)
+
+// ---- kernels' launchers (each defined in its own .cu) ------------------------------------------
+// quantizers: raw GGUF blocks and/or planar activations
+int tb200_launch_quantize_q8_0(tb200_ctx *c, const float *x, long ldx, long rows, long k, void *raw, int8_t *q, int2 *ds);
+int tb200_launch_quantize_q8_K(tb200_ctx *c, const float *x, long ldx, long rows, long k, void *raw, int8_t *q, int2 *ds);
+int tb200_launch_f32_to_f16(tb200_ctx *c, const float *x, long ldx, long rows, long k, __half *y);
+// raw GGUF activation blocks -> planar
+int tb200_launch_unpack_q8_0(tb200_ctx *c, const void *raw, long ldb_blocks, long rows, long k, int8_t *q, int2 *ds);
+int tb200_launch_unpack_q8_K(tb200_ctx *c, const void *raw, long ldb_blocks, long rows, long k, int8_t *q, int2 *ds);
+// repack
+int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long k, size_t row_stride, void *qs, void *sc);
+// decode path. out[t*ldo + i]. rowmap: optional per-token (weight-row offset, output pointer) for mixmul.
+// grouped decode (mixmul): one item = rows [row0, row0+nrows) of one expert against ntok gathered tokens
+struct tb200_gemv_item {
+    long row0;
+    int ntok;
+    int a_row[TB200_GEMV_MAX_TOKENS];     // activation row index per gathered token
+    int out_row[TB200_GEMV_MAX_TOKENS];   // output row index (out + out_row*ldo)
+};
+struct tb200_gemv_args {
+    const tb200_weights *w;
+    long row0, nrows;              // weight rows [row0, row0+nrows)
+    const int8_t *aq; const int2 *ads;    // planar activations (quantized types)
+    const void *af;                // F16 weights: activations as fp16 (tokens>2) or f32 (tokens<=2)
+    int af_is_f32;
+    long a_stride;                 // activation row stride in elements
+    long tokens;
+    float *out; long ldo;
+    const tb200_gemv_item *items; long n_items;   // optional grouped mode (device array); tokens = template T
+};
+int tb200_launch_gemv(tb200_ctx *c, const tb200_gemv_args &a);
+int tb200_launch_blockdot(tb200_ctx *c, const tb200_weights *w, const int8_t *aq, const int2 *ads, int32_t *out);
+
+#ifdef __CUDACC__
+// ---- device helpers ----------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
+    uint4 r;   // weights are read exactly once: bypass L1 allocation
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ int dp4a_ss(int a, int b, int c) { return __dp4a(a, b, c); }
+__device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {   // unsigned bytes x signed bytes
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+#endif

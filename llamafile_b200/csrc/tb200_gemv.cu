@@ -1,0 +1,549 @@
+// Decode path (SURVEY.md §8 rows a9, a10, a11, a12 at n <= 8): skinny GEMV / GEMM that streams the
+// resident quant planes from HBM with 128-bit coalesced loads and does int8 dp4a block dot products.
+//
+// Semantics follow the reference's block dot products:
+//   Q4_0 x Q8_0 : sum_b d_x[b]*d_y[b] * sum_j (q4[j]-8)*q8[j]       ggml-quants.c:4192-4206 (ggml_vec_dot_q4_0_q8_0),
+//                 served by iqk mul_mat_qX_0_q8_0_T<Q4_0_Unpacker>    llamafile/iqk_mul_mat.inc:1129-1201
+//   Q8_0 x Q8_0 : sum_b d_x[b]*d_y[b] * sum_j q8x[j]*q8y[j]          tinyBLAS_Q0_AVX2, llamafile/tinyblas_cpu.h:934-993
+//   Q4_K x Q8_K : sum_sb d*dy * sum_s sc_s*sum_j q4*q8 - dmin*dy * sum_s m_s*bsum_s   ggml-quants.c:7341-7397,
+//                 served by iqk mul_mat_qX_K_q8_K_T<DequantizerQ4K>   llamafile/iqk_mul_mat.inc:601-643
+//   F16         : fp32 FMA of widened fp16 (B fp32 when n<=2 else fp16)  llamafile/tinyblas_cpu_sgemm.inc:121-136
+// The int32 block sums are exact; only the fp32 accumulation order differs from the AVX lanes.
+//
+// Mapping: one warp owns R weight rows and walks K; lane l takes 16-byte pieces l, l+32, ... of each
+// row so every warp load is one contiguous 512-byte segment. Activations (quantized once per call by
+// tb200_quantize.cu) are staged in shared memory, split so that lane-consecutive reads are
+// bank-conflict free. Weights are read exactly once -> ld.global.nc.L1::no_allocate.
+#include "tb200_common.cuh"
+
+namespace {
+
+constexpr int kWarps = 4;   // warps per CTA
+
+// ---- shared-memory activation staging ----------------------------------------------------------
+// Q4_0: a 32-block's low-nibble elements are 0..15 and high-nibble elements 16..31, so the block's two
+// 16-byte activation halves go to two planes: lo[t][b], hi[t][b]; lane b reads lo[b] and hi[b].
+// Q8_0/F16: natural order. Q4_K: see gemv_q4_K.
+// ---- Q4_0 ---------------------------------------------------------------------------------------
+template <int T, int R>
+__global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__restrict__ qs, const __half *__restrict__ sc,
+                                                                long nb, long nbc, long row0, long nrows,
+                                                                const int8_t *__restrict__ aq, const int2 *__restrict__ ads,
+                                                                long a_stride, float *__restrict__ out, long ldo,
+                                                                const tb200_gemv_item *__restrict__ items) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint4 *s_lo = reinterpret_cast<uint4 *>(smem);
+    uint4 *s_hi = s_lo + T * nbc;
+    int2 *s_ds = reinterpret_cast<int2 *>(s_hi + T * nbc);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long r_base = ((long)blockIdx.x * kWarps + warp) * R;   // first row of this warp (relative to row0)
+    const bool active = r_base < nrows;
+    // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
+    __shared__ int s_arow[T];
+    long my_row0 = row0;
+    int ntok = T, orow[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) orow[t] = t;
+    if (items) {
+        const tb200_gemv_item &it = items[blockIdx.y];
+        ntok = it.ntok;
+        if (ntok == 0) return;   // CTA-uniform
+        my_row0 = it.row0;
+#pragma unroll
+        for (int t = 0; t < T; ++t) orow[t] = it.out_row[min(t, ntok - 1)];
+        if (threadIdx.x < T) s_arow[threadIdx.x] = it.a_row[min((int)threadIdx.x, ntok - 1)];
+    } else if (threadIdx.x < T) s_arow[threadIdx.x] = threadIdx.x;
+    __syncthreads();
+
+    float acc[R][T];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+
+    const uint4 *wrow[R];
+    const __half *srow[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const long row = my_row0 + min(r_base + r, nrows - 1);   // clamp: tail rows recompute the last row, never stored
+        wrow[r] = qs + row * nb;
+        srow[r] = sc + row * nb;
+    }
+
+    for (long b0 = 0; b0 < nb; b0 += nbc) {   // K chunks of nbc blocks (one chunk unless T*K is huge)
+        const long cnt = min(nbc, nb - b0);
+        if (b0) __syncthreads();
+        // stage activations: 16-byte piece g of token t -> plane (g&1), index g>>1
+        for (long i = threadIdx.x; i < T * cnt * 2; i += blockDim.x) {
+            const long t = i / (cnt * 2), g = i % (cnt * 2);
+            const uint4 v = *reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + (b0 * 2 + g) * 16);
+            ((g & 1) ? s_hi : s_lo)[t * nbc + (g >> 1)] = v;
+        }
+        for (long i = threadIdx.x; i < T * cnt; i += blockDim.x) s_ds[(i / cnt) * nbc + (i % cnt)] = ads[(long)s_arow[i / cnt] * (a_stride / QK) + b0 + (i % cnt)];
+        __syncthreads();
+        if (!active) continue;
+        for (long b = lane; b < cnt; b += 32) {
+            uint4 w[R];
+            float d[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) w[r] = ldg_stream(wrow[r] + b0 + b);
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = __half2float(srow[r][b0 + b]);
+            // nibble planes: lo = elements 0..15, hi = elements 16..31 (values 0..15; the -8 is folded in below)
+            unsigned wl[R][4], wh[R][4];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                wl[r][0] = w[r].x & 0x0f0f0f0fu, wh[r][0] = (w[r].x >> 4) & 0x0f0f0f0fu;
+                wl[r][1] = w[r].y & 0x0f0f0f0fu, wh[r][1] = (w[r].y >> 4) & 0x0f0f0f0fu;
+                wl[r][2] = w[r].z & 0x0f0f0f0fu, wh[r][2] = (w[r].z >> 4) & 0x0f0f0f0fu;
+                wl[r][3] = w[r].w & 0x0f0f0f0fu, wh[r][3] = (w[r].w >> 4) & 0x0f0f0f0fu;
+            }
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const uint4 al = s_lo[t * nbc + b], ah = s_hi[t * nbc + b];
+                const int2 ds = s_ds[t * nbc + b];
+                const float dy = __int_as_float(ds.x);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    int s = dp4a_us(wl[r][0], (int)al.x, 0);
+                    s = dp4a_us(wl[r][1], (int)al.y, s);
+                    s = dp4a_us(wl[r][2], (int)al.z, s);
+                    s = dp4a_us(wl[r][3], (int)al.w, s);
+                    s = dp4a_us(wh[r][0], (int)ah.x, s);
+                    s = dp4a_us(wh[r][1], (int)ah.y, s);
+                    s = dp4a_us(wh[r][2], (int)ah.z, s);
+                    s = dp4a_us(wh[r][3], (int)ah.w, s);
+                    // sum (q-8)*y = sum q*y - 8*sum y  (exact in int32)
+                    acc[r][t] = fmaf(d[r] * dy, (float)(s - 8 * ds.y), acc[r][t]);
+                }
+            }
+        }
+    }
+    if (!active) return;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const float v = warp_sum(acc[r][t]);
+            if (lane == 0 && r_base + r < nrows && t < ntok) out[(long)orow[t] * ldo + r_base + r] = v;
+        }
+}
+
+// ---- Q8_0 ---------------------------------------------------------------------------------------
+// Unit of work = 16-byte half block (16 int8): lane-consecutive pieces are contiguous in HBM and in smem.
+template <int T, int R>
+__global__ void __launch_bounds__(kWarps * 32) gemv_q8_0_kernel(const uint4 *__restrict__ qs, const __half *__restrict__ sc,
+                                                                long nb, long nbc, long row0, long nrows,
+                                                                const int8_t *__restrict__ aq, const int2 *__restrict__ ads,
+                                                                long a_stride, float *__restrict__ out, long ldo,
+                                                                const tb200_gemv_item *__restrict__ items) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint4 *s_q = reinterpret_cast<uint4 *>(smem);             // [T][2*nbc]
+    int2 *s_ds = reinterpret_cast<int2 *>(s_q + T * nbc * 2);  // [T][nbc]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long r_base = ((long)blockIdx.x * kWarps + warp) * R;
+    const bool active = r_base < nrows;
+    // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
+    __shared__ int s_arow[T];
+    long my_row0 = row0;
+    int ntok = T, orow[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) orow[t] = t;
+    if (items) {
+        const tb200_gemv_item &it = items[blockIdx.y];
+        ntok = it.ntok;
+        if (ntok == 0) return;   // CTA-uniform
+        my_row0 = it.row0;
+#pragma unroll
+        for (int t = 0; t < T; ++t) orow[t] = it.out_row[min(t, ntok - 1)];
+        if (threadIdx.x < T) s_arow[threadIdx.x] = it.a_row[min((int)threadIdx.x, ntok - 1)];
+    } else if (threadIdx.x < T) s_arow[threadIdx.x] = threadIdx.x;
+    __syncthreads();
+    float acc[R][T];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+    const uint4 *wrow[R];
+    const __half *srow[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const long row = my_row0 + min(r_base + r, nrows - 1);
+        wrow[r] = qs + row * nb * 2;
+        srow[r] = sc + row * nb;
+    }
+    for (long b0 = 0; b0 < nb; b0 += nbc) {
+        const long cnt = min(nbc, nb - b0);
+        if (b0) __syncthreads();
+        for (long i = threadIdx.x; i < T * cnt * 2; i += blockDim.x) {
+            const long t = i / (cnt * 2), g = i % (cnt * 2);
+            s_q[t * nbc * 2 + g] = *reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + (b0 * 2 + g) * 16);
+        }
+        for (long i = threadIdx.x; i < T * cnt; i += blockDim.x) s_ds[(i / cnt) * nbc + (i % cnt)] = ads[(long)s_arow[i / cnt] * (a_stride / QK) + b0 + (i % cnt)];
+        __syncthreads();
+        if (!active) continue;
+        for (long g = lane; g < cnt * 2; g += 32) {
+            uint4 w[R];
+            float d[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) w[r] = ldg_stream(wrow[r] + b0 * 2 + g);
+#pragma unroll
+            for (int r = 0; r < R; ++r) d[r] = __half2float(srow[r][b0 + (g >> 1)]);
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const uint4 a = s_q[t * nbc * 2 + g];
+                const float dy = __int_as_float(s_ds[t * nbc + (g >> 1)].x);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    int s = dp4a_ss((int)w[r].x, (int)a.x, 0);
+                    s = dp4a_ss((int)w[r].y, (int)a.y, s);
+                    s = dp4a_ss((int)w[r].z, (int)a.z, s);
+                    s = dp4a_ss((int)w[r].w, (int)a.w, s);
+                    acc[r][t] = fmaf(d[r] * dy, (float)s, acc[r][t]);
+                }
+            }
+        }
+    }
+    if (!active) return;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const float v = warp_sum(acc[r][t]);
+            if (lane == 0 && r_base + r < nrows && t < ntok) out[(long)orow[t] * ldo + r_base + r] = v;
+        }
+}
+
+// ---- Q4_K ---------------------------------------------------------------------------------------
+// Super-block = 128 B of nibbles = 8 pieces of 16 B; piece p = 2c+h holds, for 64-element chunk c,
+// low nibbles = elements 64c+16h+[0,16) (sub-block 2c) and high nibbles = 64c+32+16h+[0,16) (sub-block 2c+1)
+// (dequantize_row_q4_K, ggml-quants.c:2548-2570). 8 lanes share a super-block; activations are staged
+// as lo[sb][p], hi[sb][p] so that a lane reads exactly the 2 x 16 int8 its piece multiplies.
+__device__ __forceinline__ void q4k_scale_min(const uint4 hdr, int j, int &sc, int &m) {   // get_scale_min_k4, :1891-1899
+    // hdr.x = {d, dmin}; scales[12] = bytes 0..11 of (hdr.y, hdr.z, hdr.w)
+    const uint32_t s0 = hdr.y, s1 = hdr.z, s2 = hdr.w;
+    auto byte = [&](int i) -> uint32_t { const uint32_t wv = i < 4 ? s0 : (i < 8 ? s1 : s2); return (wv >> (8 * (i & 3))) & 0xff; };
+    if (j < 4) { sc = byte(j) & 63; m = byte(j + 4) & 63; }
+    else { sc = (byte(j + 4) & 0xF) | ((byte(j - 4) >> 6) << 4); m = (byte(j + 4) >> 4) | ((byte(j) >> 6) << 4); }
+}
+
+template <int T, int R>
+__global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const uint4 *__restrict__ qs, const uint4 *__restrict__ sc,
+                                                                long nsb, long nsbc, long row0, long nrows,
+                                                                const int8_t *__restrict__ aq, const int2 *__restrict__ ads,
+                                                                long a_stride, float *__restrict__ out, long ldo,
+                                                                const tb200_gemv_item *__restrict__ items) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint4 *s_lo = reinterpret_cast<uint4 *>(smem);   // [T][nsbc*8]
+    uint4 *s_hi = s_lo + T * nsbc * 8;
+    int2 *s_ds = reinterpret_cast<int2 *>(s_hi + T * nsbc * 8);   // [T][nsbc*8]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long r_base = ((long)blockIdx.x * kWarps + warp) * R;
+    const bool active = r_base < nrows;
+    // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
+    __shared__ int s_arow[T];
+    long my_row0 = row0;
+    int ntok = T, orow[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) orow[t] = t;
+    if (items) {
+        const tb200_gemv_item &it = items[blockIdx.y];
+        ntok = it.ntok;
+        if (ntok == 0) return;   // CTA-uniform
+        my_row0 = it.row0;
+#pragma unroll
+        for (int t = 0; t < T; ++t) orow[t] = it.out_row[min(t, ntok - 1)];
+        if (threadIdx.x < T) s_arow[threadIdx.x] = it.a_row[min((int)threadIdx.x, ntok - 1)];
+    } else if (threadIdx.x < T) s_arow[threadIdx.x] = threadIdx.x;
+    __syncthreads();
+    float acc[R][T];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+    const int p = lane & 7, c = p >> 1, h = p & 1;
+    for (long sb0 = 0; sb0 < nsb; sb0 += nsbc) {
+        const long cnt = min(nsbc, nsb - sb0);
+        if (sb0) __syncthreads();
+        for (long i = threadIdx.x; i < T * cnt * 16; i += blockDim.x) {
+            const long t = i / (cnt * 16), g = i % (cnt * 16);   // g = 16-byte piece of this chunk of the activation row
+            const long sb = g >> 4;
+            const int gi = (int)(g & 15), cc = gi >> 2, hl = (gi >> 1) & 1, hh = gi & 1;
+            const uint4 v = *reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + (sb0 * 16 + g) * 16);
+            (hl ? s_hi : s_lo)[(t * nsbc + sb) * 8 + 2 * cc + hh] = v;
+        }
+        for (long i = threadIdx.x; i < T * cnt * 8; i += blockDim.x)
+            s_ds[(i / (cnt * 8)) * nsbc * 8 + (i % (cnt * 8))] = ads[(long)s_arow[i / (cnt * 8)] * (a_stride / QK) + sb0 * 8 + (i % (cnt * 8))];
+        __syncthreads();
+        if (!active) continue;
+        for (long sb = lane >> 3; sb < cnt; sb += 4) {
+            uint4 w[R], hdr[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const long row = my_row0 + min(r_base + r, nrows - 1);
+                w[r] = ldg_stream(qs + (row * nsb + sb0 + sb) * 8 + p);
+                hdr[r] = __ldg(sc + row * nsb + sb0 + sb);
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr[r].x);
+                const float d = __low2float(dd), dmin = __high2float(dd);
+                int sc_lo, m_lo, sc_hi, m_hi;
+                q4k_scale_min(hdr[r], 2 * c, sc_lo, m_lo);
+                q4k_scale_min(hdr[r], 2 * c + 1, sc_hi, m_hi);
+                const unsigned wl0 = w[r].x & 0x0f0f0f0fu, wl1 = w[r].y & 0x0f0f0f0fu, wl2 = w[r].z & 0x0f0f0f0fu, wl3 = w[r].w & 0x0f0f0f0fu;
+                const unsigned wh0 = (w[r].x >> 4) & 0x0f0f0f0fu, wh1 = (w[r].y >> 4) & 0x0f0f0f0fu,
+                               wh2 = (w[r].z >> 4) & 0x0f0f0f0fu, wh3 = (w[r].w >> 4) & 0x0f0f0f0fu;
+#pragma unroll
+                for (int t = 0; t < T; ++t) {
+                    const long base = (t * nsbc + sb) * 8;
+                    const uint4 al = s_lo[base + p], ah = s_hi[base + p];
+                    int sl = dp4a_us(wl0, (int)al.x, 0);
+                    sl = dp4a_us(wl1, (int)al.y, sl), sl = dp4a_us(wl2, (int)al.z, sl), sl = dp4a_us(wl3, (int)al.w, sl);
+                    int sh = dp4a_us(wh0, (int)ah.x, 0);
+                    sh = dp4a_us(wh1, (int)ah.y, sh), sh = dp4a_us(wh2, (int)ah.z, sh), sh = dp4a_us(wh3, (int)ah.w, sh);
+                    const int2 ds_lo = s_ds[base + 2 * c], ds_hi = s_ds[base + 2 * c + 1];
+                    const float dy = __int_as_float(ds_lo.x);
+                    const int isum = sc_lo * sl + sc_hi * sh;
+                    const int msum = h == 0 ? m_lo * ds_lo.y + m_hi * ds_hi.y : 0;   // each sub-block's mins counted once
+                    acc[r][t] = fmaf(d * dy, (float)isum, acc[r][t]);
+                    acc[r][t] = fmaf(-(dmin * dy), (float)msum, acc[r][t]);
+                }
+            }
+        }
+    }
+    if (!active) return;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const float v = warp_sum(acc[r][t]);
+            if (lane == 0 && r_base + r < nrows && t < ntok) out[(long)orow[t] * ldo + r_base + r] = v;
+        }
+}
+
+// ---- F16 ----------------------------------------------------------------------------------------
+template <int T, int R, bool kActF32>
+__global__ void __launch_bounds__(kWarps * 32) gemv_f16_kernel(const __half *__restrict__ wt, long k, long kc, long row0, long nrows,
+                                                               const void *__restrict__ act, long a_stride,
+                                                               float *__restrict__ out, long ldo,
+                                                                const tb200_gemv_item *__restrict__ items) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    float *s_a = reinterpret_cast<float *>(smem);   // [T][kc] widened to fp32 once per chunk
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long r_base = ((long)blockIdx.x * kWarps + warp) * R;
+    const bool active = r_base < nrows;
+    // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
+    __shared__ int s_arow[T];
+    long my_row0 = row0;
+    int ntok = T, orow[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) orow[t] = t;
+    if (items) {
+        const tb200_gemv_item &it = items[blockIdx.y];
+        ntok = it.ntok;
+        if (ntok == 0) return;   // CTA-uniform
+        my_row0 = it.row0;
+#pragma unroll
+        for (int t = 0; t < T; ++t) orow[t] = it.out_row[min(t, ntok - 1)];
+        if (threadIdx.x < T) s_arow[threadIdx.x] = it.a_row[min((int)threadIdx.x, ntok - 1)];
+    } else if (threadIdx.x < T) s_arow[threadIdx.x] = threadIdx.x;
+    __syncthreads();
+    float acc[R][T];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+    const bool vec = (k & 7) == 0 && (kc & 7) == 0 && ((uintptr_t)wt & 15) == 0;
+    for (long k0 = 0; k0 < k; k0 += kc) {
+        const long cnt = min(kc, k - k0);
+        if (k0) __syncthreads();
+        for (long i = threadIdx.x; i < T * cnt; i += blockDim.x) {
+            const long t = i / cnt, j = i % cnt;
+            s_a[t * kc + j] = kActF32 ? reinterpret_cast<const float *>(act)[(long)s_arow[t] * a_stride + k0 + j]
+                                      : __half2float(reinterpret_cast<const __half *>(act)[(long)s_arow[t] * a_stride + k0 + j]);
+        }
+        __syncthreads();
+        if (!active) continue;
+        if (vec) {
+            for (long g = lane; g < cnt / 8; g += 32) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const long row = my_row0 + min(r_base + r, nrows - 1);
+                    const uint4 w = ldg_stream(reinterpret_cast<const uint4 *>(wt + row * k + k0) + g);
+                    const __half2 *hp = reinterpret_cast<const __half2 *>(&w);
+                    float wf[8];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(hp[i]); wf[2 * i] = f.x, wf[2 * i + 1] = f.y; }
+#pragma unroll
+                    for (int t = 0; t < T; ++t) {
+                        const float4 a0 = *reinterpret_cast<const float4 *>(s_a + t * kc + g * 8), a1 = *reinterpret_cast<const float4 *>(s_a + t * kc + g * 8 + 4);
+                        float s = acc[r][t];
+                        s = fmaf(wf[0], a0.x, s), s = fmaf(wf[1], a0.y, s), s = fmaf(wf[2], a0.z, s), s = fmaf(wf[3], a0.w, s);
+                        s = fmaf(wf[4], a1.x, s), s = fmaf(wf[5], a1.y, s), s = fmaf(wf[6], a1.z, s), s = fmaf(wf[7], a1.w, s);
+                        acc[r][t] = s;
+                    }
+                }
+            }
+        } else {
+            for (long j = lane; j < cnt; j += 32)
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const long row = my_row0 + min(r_base + r, nrows - 1);
+                    const float wv = __half2float(wt[row * k + k0 + j]);
+#pragma unroll
+                    for (int t = 0; t < T; ++t) acc[r][t] = fmaf(wv, s_a[t * kc + j], acc[r][t]);
+                }
+        }
+    }
+    if (!active) return;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const float v = warp_sum(acc[r][t]);
+            if (lane == 0 && r_base + r < nrows && t < ntok) out[(long)orow[t] * ldo + r_base + r] = v;
+        }
+}
+
+// ---- exact integer block dots (parity instrument; not a hot path) -------------------------------
+__global__ void blockdot_kernel(int type, const uint8_t *__restrict__ qs, const uint8_t *__restrict__ sc, long rows, long k,
+                                const int8_t *__restrict__ aq, const int2 *__restrict__ ads, int32_t *__restrict__ out) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (type == TB200_TYPE_Q4_K) {
+        const long nsb = k / QK_K;
+        if (i >= rows * nsb) return;
+        const long sb = i % nsb;
+        const uint8_t *q4 = qs + i * 128;
+        const uint4 hdr = *reinterpret_cast<const uint4 *>(sc + i * 16);
+        int sum_q = 0, sum_m = 0;
+        for (int s = 0; s < 8; ++s) {
+            int scs, ms;
+            q4k_scale_min(hdr, s, scs, ms);
+            int dot = 0;
+            for (int l = 0; l < 32; ++l) {
+                const int q = (s & 1) ? (q4[(s / 2) * 32 + l] >> 4) : (q4[(s / 2) * 32 + l] & 0xF);
+                dot += q * aq[sb * 256 + s * 32 + l];
+            }
+            sum_q += scs * dot;
+            sum_m += ms * ads[sb * 8 + s].y;
+        }
+        out[2 * i] = sum_q, out[2 * i + 1] = sum_m;
+        return;
+    }
+    const long nb = k / QK;
+    if (i >= rows * nb) return;
+    const long b = i % nb;
+    int s = 0;
+    if (type == TB200_TYPE_Q4_0) {
+        const uint8_t *q4 = qs + i * 16;
+        for (int j = 0; j < 16; ++j) s += ((q4[j] & 0xF) - 8) * aq[b * 32 + j] + ((q4[j] >> 4) - 8) * aq[b * 32 + 16 + j];
+    } else {
+        const int8_t *q8 = reinterpret_cast<const int8_t *>(qs) + i * 32;
+        for (int j = 0; j < 32; ++j) s += q8[j] * aq[b * 32 + j];
+    }
+    out[i] = s;
+}
+
+template <typename K>
+int set_smem(K kernel, size_t bytes) {
+    if (bytes > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        if (e != cudaSuccess) { tb200_set_error("gemv: %zu bytes of shared memory: %s", bytes, cudaGetErrorString(e)); return TB200_ERR_CUDA; }
+    }
+    return TB200_OK;
+}
+
+constexpr size_t kSmemBudget = 96 * 1024;   // activation staging per CTA; larger T*K is walked in K chunks
+
+template <int T, int R>
+int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
+    const tb200_weights *w = a.w;
+    const dim3 grid((unsigned)((a.nrows + kWarps * R - 1) / (kWarps * R)), a.items ? (unsigned)a.n_items : 1u);
+    int rc;
+    switch (w->type) {
+    case TB200_TYPE_Q4_0:
+    case TB200_TYPE_Q8_0: {
+        const long nb = w->k / QK;
+        long nbc = (long)(kSmemBudget / ((size_t)T * 40)) / 32 * 32;
+        if (nbc >= nb) nbc = nb;
+        const size_t smem = (size_t)T * nbc * 40;
+        if (w->type == TB200_TYPE_Q4_0) {
+            if ((rc = set_smem(gemv_q4_0_kernel<T, R>, smem))) return rc;
+            gemv_q4_0_kernel<T, R><<<grid, kWarps * 32, smem, c->stream>>>((const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,
+                                                                          a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items);
+        } else {
+            if ((rc = set_smem(gemv_q8_0_kernel<T, R>, smem))) return rc;
+            gemv_q8_0_kernel<T, R><<<grid, kWarps * 32, smem, c->stream>>>((const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,
+                                                                          a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items);
+        }
+        break;
+    }
+    case TB200_TYPE_Q4_K: {
+        const long nsb = w->k / QK_K;
+        long nsbc = (long)(kSmemBudget / ((size_t)T * 320)) / 4 * 4;
+        if (nsbc >= nsb) nsbc = nsb;
+        const size_t smem = (size_t)T * nsbc * 320;
+        if ((rc = set_smem(gemv_q4_K_kernel<T, R>, smem))) return rc;
+        gemv_q4_K_kernel<T, R><<<grid, kWarps * 32, smem, c->stream>>>((const uint4 *)w->qs, (const uint4 *)w->sc, nsb, nsbc, a.row0, a.nrows,
+                                                                      a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items);
+        break;
+    }
+    case TB200_TYPE_F16: {
+        long kc = (long)(kSmemBudget / ((size_t)T * 4)) / 256 * 256;
+        if (kc >= w->k) kc = w->k;
+        const size_t smem = (size_t)T * kc * 4;
+        if (a.af_is_f32) {
+            if ((rc = set_smem(gemv_f16_kernel<T, R, true>, smem))) return rc;
+            gemv_f16_kernel<T, R, true><<<grid, kWarps * 32, smem, c->stream>>>((const __half *)w->qs, w->k, kc, a.row0, a.nrows, a.af, a.a_stride, a.out, a.ldo, a.items);
+        } else {
+            if ((rc = set_smem(gemv_f16_kernel<T, R, false>, smem))) return rc;
+            gemv_f16_kernel<T, R, false><<<grid, kWarps * 32, smem, c->stream>>>((const __half *)w->qs, w->k, kc, a.row0, a.nrows, a.af, a.a_stride, a.out, a.ldo, a.items);
+        }
+        break;
+    }
+    default:
+        tb200_set_error("gemv: unsupported weight type %d", w->type);
+        return TB200_ERR_UNSUPPORTED;
+    }
+    tb200_count_launch();
+    TB_CUDA(cudaGetLastError());
+    return TB200_OK;
+}
+
+template <int T>
+int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
+    // rows per warp: 2 keeps >= 8 x 16-byte weight loads in flight per lane at K = 4096 while leaving
+    // enough CTAs (N/8) to cover 148 SMs; small matrices fall back to 1 row per warp.
+    if (a.nrows < (long)c->sm_count * kWarps * 4) return launch_TR<T, 1>(c, a);
+    return launch_TR<T, 2>(c, a);
+}
+
+}  // namespace
+
+int tb200_launch_gemv(tb200_ctx *c, const tb200_gemv_args &a) {
+    if (a.nrows == 0 || a.tokens == 0) return TB200_OK;
+    switch (a.tokens) {
+    case 1: return launch_T<1>(c, a);
+    case 2: return launch_T<2>(c, a);
+    case 3: return launch_T<3>(c, a);
+    case 4: return launch_T<4>(c, a);
+    case 5: return launch_T<5>(c, a);
+    case 6: return launch_T<6>(c, a);
+    case 7: return launch_T<7>(c, a);
+    case 8: return launch_T<8>(c, a);
+    default:
+        tb200_set_error("gemv: tokens=%ld exceeds TB200_GEMV_MAX_TOKENS", a.tokens);
+        return TB200_ERR_INVALID;
+    }
+}
+
+int tb200_launch_blockdot(tb200_ctx *c, const tb200_weights *w, const int8_t *aq, const int2 *ads, int32_t *out) {
+    const long units = w->rows * (w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK);
+    if (units == 0) return TB200_OK;
+    blockdot_kernel<<<(unsigned)((units + 127) / 128), 128, 0, c->stream>>>(w->type, (const uint8_t *)w->qs, (const uint8_t *)w->sc, w->rows, w->k, aq, ads, out);
+    tb200_count_launch();
+    TB_CUDA(cudaGetLastError());
+    return TB200_OK;
+}

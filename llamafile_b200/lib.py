@@ -1,0 +1,157 @@
+"""ctypes binding of libtinyblas_b200.so — device-level API (include/tinyblas_b200.h part 2).
+
+Device buffers are passed as integer addresses (e.g. torch.Tensor.data_ptr()); torch is only the
+allocator/stream provider, never on the compute path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "libtinyblas_b200.so"
+
+F32, F16, Q4_0, Q8_0, Q4_K, Q8_K, I32 = 0, 1, 2, 8, 12, 15, 26
+TYPE_SIZE = {F32: 4, F16: 2, Q4_0: 18, Q8_0: 34, Q4_K: 144, Q8_K: 292, I32: 4}
+BLCK = {F32: 1, F16: 1, Q4_0: 32, Q8_0: 32, Q4_K: 256, Q8_K: 256, I32: 1}
+OK, ERR_NO_DEVICE, ERR_UNSUPPORTED, ERR_INVALID, ERR_CUDA = range(5)
+
+
+class TB200Error(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads the CUDA module. Raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise TB200Error(f"{LIB_PATH} not built: run `python -m llamafile_b200.build` (there is no CPU fallback)")
+    L = C.CDLL(str(LIB_PATH))
+    vp, l, i, sz = C.c_void_p, C.c_long, C.c_int, C.c_size_t
+    sig = {
+        "tb200_link": (C.c_bool, [vp]), "tb200_device_count": (i, []), "tb200_set_device": (i, [i]),
+        "tb200_last_error": (C.c_char_p, []), "tb200_sm_count": (i, []), "tb200_set_stream": (i, [vp]),
+        "tb200_synchronize": (i, []), "tb200_launch_count": (C.c_uint64, []),
+        "tb200_weights_upload": (vp, [vp, i, l, l, sz]), "tb200_weights_from_device": (vp, [vp, i, l, l, sz]),
+        "tb200_weights_free": (None, [vp]), "tb200_weights_bytes": (sz, [vp]),
+        "tb200_quantize_q8_0_dev": (i, [vp, l, vp, l, l]), "tb200_quantize_q8_K_dev": (i, [vp, l, vp, l, l]),
+        "tb200_mul_mat": (i, [vp, vp, l, l, vp, l]), "tb200_sgemm_dev": (i, [vp, l, vp, l, i, vp, l]),
+        "tb200_blockdot_dev": (i, [vp, vp, i, vp]), "tb200_mixmul_dev": (i, [vp, i, vp, i, vp, i, l, vp]),
+        "tb200_malloc": (vp, [sz]), "tb200_free": (None, [vp]), "tb200_memcpy_h2d": (i, [vp, vp, sz]),
+        "tb200_memcpy_d2h": (i, [vp, vp, sz]), "tb200_host_alloc": (vp, [sz]), "tb200_host_free": (None, [vp]),
+        "llamafile_sgemm": (C.c_bool, [l, l, l, vp, l, vp, l, vp, l, i, i, i, i, i]),
+        "llamafile_mixmul": (C.c_bool, [vp, vp, vp, vp, vp]), "llamafile_mixmul_needs": (sz, [vp, vp, vp]),
+        "llamafile_mixmul_iqk": (C.c_bool, [l, l, l, i, i, vp, vp, vp, l, l, vp, i, i]),
+        "tb200_quantize_row_q8_0": (C.c_bool, [vp, vp, C.c_int64]), "tb200_quantize_row_q8_K": (C.c_bool, [vp, vp, C.c_int64]),
+        "tb200_fp32_to_fp16_row": (C.c_bool, [vp, vp, C.c_int64]), "tb200_weights_cache_clear": (None, []),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+EXPORTS = None   # filled by tests from include/tinyblas_b200.h
+
+
+def _check(rc: int, what: str):
+    if rc != OK:
+        raise TB200Error(f"{what}: status {rc}: {lib().tb200_last_error().decode(errors='replace')}")
+
+
+def link() -> bool:
+    """tb200_link handshake: True iff an sm_100 device is usable."""
+    return bool(lib().tb200_link(None))
+
+
+def _require_device():
+    if not link():
+        raise TB200Error("no sm_100 (B200) device: tinyBLAS-B200 has no CPU fallback")
+
+
+def device_count() -> int: return int(lib().tb200_device_count())
+def sm_count() -> int: return int(lib().tb200_sm_count())
+def launch_count() -> int: return int(lib().tb200_launch_count())
+def synchronize(): _check(lib().tb200_synchronize(), "synchronize")
+def set_stream(cuda_stream: int): _check(lib().tb200_set_stream(cuda_stream), "set_stream")
+
+
+def _ptr(x) -> int:
+    if x is None:
+        return 0
+    if isinstance(x, int):
+        return x
+    if hasattr(x, "data_ptr"):
+        return x.data_ptr()
+    if hasattr(x, "ctypes"):
+        return x.ctypes.data
+    raise TypeError(type(x))
+
+
+class Weights:
+    """Resident weight matrix (tb200_weights). `data`: GGUF rows as a numpy uint8 array (host) or a
+    torch CUDA uint8 tensor (device); `rows` rows of `k` elements."""
+
+    def __init__(self, data, type_: int, rows: int, k: int, row_stride: int = 0):
+        _require_device()
+        self.type, self.rows, self.k = type_, rows, k
+        on_device = hasattr(data, "is_cuda") and data.is_cuda
+        fn = lib().tb200_weights_from_device if on_device else lib().tb200_weights_upload
+        self.handle = fn(_ptr(data), type_, rows, k, row_stride)
+        if not self.handle:
+            raise TB200Error("weights: " + lib().tb200_last_error().decode(errors="replace"))
+        if on_device:
+            synchronize()
+
+    @property
+    def nbytes(self) -> int: return int(lib().tb200_weights_bytes(self.handle))
+
+    def free(self):
+        if getattr(self, "handle", None):
+            lib().tb200_weights_free(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def mul_mat(w: Weights, x, tokens: int, out, ldx: int | None = None, ldo: int | None = None):
+    """out[t, :] = W . vec_dot_type(x[t]) — ggml_compute_forward_mul_mat on device buffers (f32 in/out)."""
+    _check(lib().tb200_mul_mat(w.handle, _ptr(x), ldx or w.k, tokens, _ptr(out), ldo or w.rows), "mul_mat")
+
+
+def sgemm_dev(w: Weights, n: int, B, ldb: int, Btype: int, Cout, ldc: int) -> bool:
+    rc = lib().tb200_sgemm_dev(w.handle, n, _ptr(B), ldb, Btype, _ptr(Cout), ldc)
+    if rc == ERR_UNSUPPORTED:
+        return False
+    _check(rc, "sgemm_dev")
+    return True
+
+
+def blockdot(w: Weights, B, Btype: int, out):
+    _check(lib().tb200_blockdot_dev(w.handle, _ptr(B), Btype, _ptr(out)), "blockdot")
+
+
+def quantize_q8_0(x, rows: int, k: int, y, ldx: int | None = None):
+    _check(lib().tb200_quantize_q8_0_dev(_ptr(x), ldx or k, _ptr(y), rows, k), "quantize_q8_0")
+
+
+def quantize_q8_K(x, rows: int, k: int, y, ldx: int | None = None):
+    _check(lib().tb200_quantize_q8_K_dev(_ptr(x), ldx or k, _ptr(y), rows, k), "quantize_q8_K")
+
+
+def mixmul(w: Weights, experts: int, thought, tasks: int, plan, thinkers: int, tokens: int, result) -> bool:
+    rc = lib().tb200_mixmul_dev(w.handle, experts, _ptr(thought), tasks, _ptr(plan), thinkers, tokens, _ptr(result))
+    if rc == ERR_UNSUPPORTED:
+        return False
+    _check(rc, "mixmul")
+    return True
