@@ -86,7 +86,8 @@ typedef struct {
 /* llamafile/sgemm.h:23-24, llamafile/sgemm.cpp:128-131. C[ldc*j + i] = sum_l A[lda*i + l] * B[ldb*j + l],
  * m = weight rows, n = tokens, k/lda/ldb counted in BLOCKS of Atype/Btype, ldc in floats.
  * Serviced (returns true, C written) for the combinations the reference's x86 build services:
- *   Q4_0 x Q8_0, Q8_0 x Q8_0, Q4_K x Q8_K, F16 x F16, F16 x F32 (n <= 2), F32 x F32; Ctype F32.
+ *   Q4_0 x Q8_0, Q8_0 x Q8_0, Q4_K x Q8_K, F16 x F16, F16 x F32 (n <= 2); Ctype F32. (F32 and BF16
+ *   weights, which the reference also serves, are outside north_star's list and are handed back.)
  * Anything else returns false before touching C ("not handled, caller falls back"), never an error.
  * Threading contract: ggml calls this from all nth worker threads. Thread 0 does the whole job
  * on the GPU and returns after C is complete; threads ith != 0 return true immediately and rely on
@@ -173,6 +174,14 @@ TB200_API int tb200_quantize_q8_K_dev(const float *x, long ldx, void *y, long ro
  * tokens <= TB200_GEMV_MAX_TOKENS, tcgen05 GEMM above. */
 #define TB200_GEMV_MAX_TOKENS 8
 TB200_API int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens, float *out, long ldo);
+
+/* The same in two steps, for callers that feed one activation tensor to several weight matrices (wq/wk/wv,
+ * gate/up): quantize once into a resident activation object, then run any number of matmuls against it. */
+typedef struct tb200_acts tb200_acts;
+TB200_API tb200_acts *tb200_acts_create(int weight_type, long k, long max_tokens);
+TB200_API int tb200_acts_quantize(tb200_acts *a, const float *x, long ldx, long tokens);
+TB200_API int tb200_mul_mat_acts(const tb200_weights *w, const tb200_acts *a, float *out, long ldo);
+TB200_API void tb200_acts_free(tb200_acts *a);
 
 /* llamafile_sgemm on device pointers with pre-quantized activations B (GGUF blocks of Btype, ldb in
  * blocks). Same service matrix as llamafile_sgemm. */

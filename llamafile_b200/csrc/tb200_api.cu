@@ -266,6 +266,69 @@ int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens,
     return run_matmul(c, w, 0, w->rows, p.q, p.ds, nullptr, 0, w->k, tokens, out, ldo);
 }
 
+// ---- resident activations ---------------------------------------------------------------------------
+struct tb200_acts {
+    int wtype;          // weight type this was prepared for (decides Q8_0 / Q8_K / F16 / F32 form)
+    long k, max_tokens, tokens;
+    int8_t *q; int2 *ds; __half *h; const float *f32; long ldx;
+    void *base;
+};
+
+tb200_acts *tb200_acts_create(int weight_type, long k, long max_tokens) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!c) return nullptr;
+    if (k <= 0 || max_tokens <= 0 || (weight_type != TB200_TYPE_F16 && k % (weight_type == TB200_TYPE_Q4_K ? QK_K : QK))) {
+        tb200_set_error("acts_create: bad arguments");
+        return nullptr;
+    }
+    tb200_acts *a = new tb200_acts();
+    memset(a, 0, sizeof(*a));
+    a->wtype = weight_type, a->k = k, a->max_tokens = max_tokens;
+    const size_t qb = round_up((size_t)max_tokens * k, 256), dsb = round_up((size_t)max_tokens * (k / QK + 1) * 8, 256),
+                 hb = round_up((size_t)max_tokens * k * 2, 256);
+    const size_t total = weight_type == TB200_TYPE_F16 ? hb : qb + dsb;
+    if (cudaMalloc(&a->base, total) != cudaSuccess) { cudaGetLastError(); tb200_set_error("acts_create: cudaMalloc(%zu) failed", total); delete a; return nullptr; }
+    if (weight_type == TB200_TYPE_F16) a->h = (__half *)a->base;
+    else a->q = (int8_t *)a->base, a->ds = (int2 *)((uint8_t *)a->base + qb);
+    return a;
+}
+
+int tb200_acts_quantize(tb200_acts *a, const float *x, long ldx, long tokens) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!c) return TB200_ERR_NO_DEVICE;
+    if (!a || tokens < 0 || tokens > a->max_tokens || ldx < a->k) { tb200_set_error("acts_quantize: bad arguments"); return TB200_ERR_INVALID; }
+    a->tokens = tokens, a->f32 = nullptr, a->ldx = ldx;
+    if (a->wtype == TB200_TYPE_F16) {
+        if (tokens <= 2) { a->f32 = x; return TB200_OK; }   // B stays F32 for n <= 2 (tinyblas_cpu_sgemm.inc:121-136); caller keeps x alive
+        return tb200_launch_f32_to_f16(c, x, ldx, tokens, a->k, a->h);
+    }
+    if (a->wtype == TB200_TYPE_Q4_K) return tb200_launch_quantize_q8_K(c, x, ldx, tokens, a->k, nullptr, a->q, a->ds);
+    return tb200_launch_quantize_q8_0(c, x, ldx, tokens, a->k, nullptr, a->q, a->ds);
+}
+
+int tb200_mul_mat_acts(const tb200_weights *w, const tb200_acts *a, float *out, long ldo) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!c) return TB200_ERR_NO_DEVICE;
+    if (!w || !a || a->k != w->k || ldo < w->rows) { tb200_set_error("mul_mat_acts: bad arguments"); return TB200_ERR_INVALID; }
+    const bool wq = w->type != TB200_TYPE_F16, aq = a->wtype != TB200_TYPE_F16;
+    if (wq != aq || (wq && (w->type == TB200_TYPE_Q4_K) != (a->wtype == TB200_TYPE_Q4_K))) {
+        tb200_set_error("mul_mat_acts: activations were prepared for weight type %d, not %d", a->wtype, w->type);
+        return TB200_ERR_INVALID;
+    }
+    if (a->tokens == 0 || w->rows == 0) return TB200_OK;
+    if (!wq) {
+        if (a->f32) return run_matmul(c, w, 0, w->rows, nullptr, nullptr, a->f32, 1, a->ldx, a->tokens, out, ldo);
+        return run_matmul(c, w, 0, w->rows, nullptr, nullptr, a->h, 0, a->k, a->tokens, out, ldo);
+    }
+    return run_matmul(c, w, 0, w->rows, a->q, a->ds, nullptr, 0, a->k, a->tokens, out, ldo);
+}
+
+void tb200_acts_free(tb200_acts *a) {
+    if (!a) return;
+    if (a->base) cudaFree(a->base);
+    delete a;
+}
+
 // which (Atype, Btype, n) the reference's x86 build services (tinyblas_cpu_sgemm.inc:46-240, 274-331),
 // restricted to the weight types this module holds (F16, Q8_0, Q4_0, Q4_K)
 static bool serviced(int Atype, int Btype, int Ctype, long n) {

@@ -45,12 +45,6 @@ struct tb200_weights {
 //   q   int8  [tokens][k]
 //   ds  {float d, int32 sum} per 32-block [tokens][k/32]   (Q8_0: d = fp16 scale widened; sum = sum of q)
 //   Q8_K: d is the per-256 float scale replicated on its 8 sub-blocks, sum = bsums[2s]+bsums[2s+1]
-struct tb200_acts {
-    const int8_t *q;
-    const int2 *ds;
-    long k;
-    long tokens;
-};
 
 // per-device context (tb200_api.cu)
 struct tb200_ctx {

@@ -15,6 +15,13 @@
 
 namespace {
 
+// _mm256_cvtps_epi32 + packs (ggml-quants.c:962-977): RNE; NaN / out of int32 range -> INT_MIN; saturate to int8.
+// Only differs from a plain round when id = 127/amax overflowed (amax < ~3.7e-37): the reference then stores -128.
+__device__ __forceinline__ int cvt_rne_sat8(float v) {
+    if (!(v >= -2147483648.f && v < 2147483648.f)) return -128;
+    return max(-128, min(127, __float2int_rn(v)));
+}
+
 // One 8-lane group per 32-element block: lane g8 holds elements 4*g8 .. 4*g8+3 (one float4).
 template <bool kVec>
 __global__ void __launch_bounds__(256) quantize_q8_0_kernel(const float *__restrict__ x, long ldx, long rows, long nb,
@@ -35,8 +42,8 @@ __global__ void __launch_bounds__(256) quantize_q8_0_kernel(const float *__restr
     for (int o = 4; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
     const float d = __fdiv_rn(amax, 127.f);
     const float id = (amax != 0.0f) ? __fdiv_rn(127.f, amax) : 0.0f;
-    const int q0 = __float2int_rn(__fmul_rn(v.x, id)), q1 = __float2int_rn(__fmul_rn(v.y, id));
-    const int q2 = __float2int_rn(__fmul_rn(v.z, id)), q3 = __float2int_rn(__fmul_rn(v.w, id));
+    const int q0 = cvt_rne_sat8(__fmul_rn(v.x, id)), q1 = cvt_rne_sat8(__fmul_rn(v.y, id));
+    const int q2 = cvt_rne_sat8(__fmul_rn(v.z, id)), q3 = cvt_rne_sat8(__fmul_rn(v.w, id));
     const uint32_t packed = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
     const __half dh = __float2half_rn(d);
     int sum = q0 + q1 + q2 + q3;
@@ -57,6 +64,9 @@ __global__ void __launch_bounds__(256) quantize_q8_0_kernel(const float *__restr
 }
 
 __device__ __forceinline__ int nearest_int_magic(float fval) {   // ggml-quants.c:1632-1637
+    // iscale = -127/max overflows to inf for |max| < ~3.7e-37; the x86 bit pattern of inf/NaN + magic then
+    // yields a value whose low byte is 0 (x86 NaN = 0xFFC00000, CUDA NaN = 0x7FFFFFFF would give 127)
+    if (!(fabsf(fval) <= 3.4028234664e38f)) return 0;
     const float val = __fadd_rn(fval, 12582912.f);
     return (__float_as_int(val) & 0x007fffff) - 0x00400000;
 }

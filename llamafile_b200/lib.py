@@ -41,6 +41,8 @@ def lib() -> C.CDLL:
         "tb200_weights_free": (None, [vp]), "tb200_weights_bytes": (sz, [vp]),
         "tb200_quantize_q8_0_dev": (i, [vp, l, vp, l, l]), "tb200_quantize_q8_K_dev": (i, [vp, l, vp, l, l]),
         "tb200_mul_mat": (i, [vp, vp, l, l, vp, l]), "tb200_sgemm_dev": (i, [vp, l, vp, l, i, vp, l]),
+        "tb200_acts_create": (vp, [i, l, l]), "tb200_acts_quantize": (i, [vp, vp, l, l]),
+        "tb200_mul_mat_acts": (i, [vp, vp, vp, l]), "tb200_acts_free": (None, [vp]),
         "tb200_blockdot_dev": (i, [vp, vp, i, vp]), "tb200_mixmul_dev": (i, [vp, i, vp, i, vp, i, l, vp]),
         "tb200_malloc": (vp, [sz]), "tb200_free": (None, [vp]), "tb200_memcpy_h2d": (i, [vp, vp, sz]),
         "tb200_memcpy_d2h": (i, [vp, vp, sz]), "tb200_host_alloc": (vp, [sz]), "tb200_host_free": (None, [vp]),
@@ -127,6 +129,35 @@ class Weights:
 def mul_mat(w: Weights, x, tokens: int, out, ldx: int | None = None, ldo: int | None = None):
     """out[t, :] = W . vec_dot_type(x[t]) — ggml_compute_forward_mul_mat on device buffers (f32 in/out)."""
     _check(lib().tb200_mul_mat(w.handle, _ptr(x), ldx or w.k, tokens, _ptr(out), ldo or w.rows), "mul_mat")
+
+
+class Acts:
+    """Resident quantized activations (tb200_acts): quantize once, multiply by several weight matrices."""
+
+    def __init__(self, weight_type: int, k: int, max_tokens: int):
+        _require_device()
+        self.k = k
+        self.handle = lib().tb200_acts_create(weight_type, k, max_tokens)
+        if not self.handle:
+            raise TB200Error("acts: " + lib().tb200_last_error().decode(errors="replace"))
+
+    def quantize(self, x, tokens: int, ldx: int | None = None):
+        _check(lib().tb200_acts_quantize(self.handle, _ptr(x), ldx or self.k, tokens), "acts_quantize")
+
+    def free(self):
+        if getattr(self, "handle", None):
+            lib().tb200_acts_free(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def mul_mat_acts(w: Weights, a: Acts, out, ldo: int | None = None):
+    _check(lib().tb200_mul_mat_acts(w.handle, a.handle, _ptr(out), ldo or w.rows), "mul_mat_acts")
 
 
 def sgemm_dev(w: Weights, n: int, B, ldb: int, Btype: int, Cout, ldc: int) -> bool:

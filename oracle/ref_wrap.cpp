@@ -204,3 +204,16 @@ EXPORT float ref_vec_dot_q8_0_q8_0(long n, const void *x, const void *y) {
 EXPORT float ref_vec_dot_q4_K_q8_K(long n, const void *x, const void *y) {
     funcs(); float s = 0; Q(ggml_vec_dot_q4_K_q8_K)((int)n, &s, 0, x, 0, y, 0, 1); return s;
 }
+
+// layout of the two ggml structs llamafile_mixmul reads, as the reference's patched ggml.h defines them
+EXPORT void ref_struct_layout(size_t *out) {
+    out[0] = offsetof(struct ggml_tensor, type);
+    out[1] = offsetof(struct ggml_tensor, ne);
+    out[2] = offsetof(struct ggml_tensor, nb);
+    out[3] = offsetof(struct ggml_tensor, data);
+    out[4] = sizeof(struct ggml_tensor);
+    out[5] = offsetof(struct ggml_compute_params, ith);
+    out[6] = offsetof(struct ggml_compute_params, nth);
+    out[7] = offsetof(struct ggml_compute_params, wsize);
+    out[8] = offsetof(struct ggml_compute_params, wdata);
+}

@@ -42,8 +42,17 @@ int oracle_blck_size(int type) {
 
 /* ---------------------------------------------------------------- quantizers */
 
+/* _mm256_round_ps(NEAREST) + _mm256_cvtps_epi32 + packs_epi32 + packs_epi16 (ggml-quants.c:962-977):
+ * RNE, NaN or out-of-int32-range -> 0x80000000 ("integer indefinite"), then signed saturation to int8. */
+static inline int8_t cvt_rne_sat8(float v) {
+    if (!(v >= -2147483648.f && v < 2147483648.f)) return -128;
+    long r = lrintf(v);
+    return (int8_t)(r < -128 ? -128 : r > 127 ? 127 : r);
+}
+
 /* ggml-quants.c:940-990 (the x86 AVX/AVX2 body that runs at llamafile run time):
- * d = amax/127 stored as fp16; id = 127/amax (IEEE divide); q = rne(x*id). */
+ * d = amax/127 stored as fp16; id = 127/amax (IEEE divide; overflows to inf for amax < ~3.7e-37);
+ * q = sat8(rne(x*id)). */
 void oracle_quantize_row_q8_0(const float *x, void *vy, int64_t k) {
     blk_q8_0 *y = (blk_q8_0 *)vy;
     for (int64_t i = 0; i < k / QK; ++i, x += QK) {
@@ -52,7 +61,7 @@ void oracle_quantize_row_q8_0(const float *x, void *vy, int64_t k) {
         const float d = amax / 127.f;
         const float id = (amax != 0.0f) ? 127.f / amax : 0.0f;
         y[i].d = f2h(d);
-        for (int j = 0; j < QK; ++j) y[i].qs[j] = (int8_t)(int)nearbyintf(x[j] * id);
+        for (int j = 0; j < QK; ++j) y[i].qs[j] = cvt_rne_sat8(x[j] * id);
     }
 }
 
