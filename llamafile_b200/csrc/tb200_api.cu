@@ -4,6 +4,7 @@
 // point fails.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -56,6 +57,10 @@ void tb200_set_error(const char *fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+bool tb200_pdl_enabled() {
+    static const int on = [] { const char *v = getenv("TB200_PDL"); return (v && *v == '0') ? 0 : 1; }();
+    return on != 0;
 }
 void tb200_count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 

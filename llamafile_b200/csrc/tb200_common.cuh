@@ -103,7 +103,27 @@ struct tb200_gemv_args {
 int tb200_launch_gemv(tb200_ctx *c, const tb200_gemv_args &a);
 int tb200_launch_blockdot(tb200_ctx *c, const tb200_weights *w, const int8_t *aq, const int2 *ads, int32_t *out);
 
+bool tb200_pdl_enabled();   // TB200_PDL=0 disables programmatic dependent launch
+
 #ifdef __CUDACC__
+// Every kernel of the module is launched with programmatic stream serialization (PDL): it may start while its
+// predecessor in the stream is still draining. Contract inside the kernels: pdl_launch_dependents() first (lets
+// the successor be scheduled early), immutable data (resident weights) may be read at once, and pdl_wait() must
+// precede the first access to anything a predecessor may have written or may still be reading.
+template <typename... KArgs, typename... Args>
+inline cudaError_t tb200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = tb200_pdl_enabled() ? 1 : 0;
+    tb200_count_launch();
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- device helpers ----------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -25,34 +25,71 @@ constexpr int kWarps = 4;   // warps per CTA
 // 16-byte activation halves go to two planes: lo[t][b], hi[t][b]; lane b reads lo[b] and hi[b].
 // Q8_0/F16: natural order. Q4_K: see gemv_q4_K.
 // ---- Q4_0 ---------------------------------------------------------------------------------------
+// U x R independent 16-byte weight loads are issued per lane before anything is consumed; the first batch is
+// issued before the activations are even staged (weights are immutable, so it also precedes pdl_wait()), which
+// folds the weight-fetch latency and the activation-fetch latency of these short kernels into one.
 template <int T, int R>
 __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__restrict__ qs, const __half *__restrict__ sc,
                                                                 long nb, long nbc, long row0, long nrows,
                                                                 const int8_t *__restrict__ aq, const int2 *__restrict__ ads,
                                                                 long a_stride, float *__restrict__ out, long ldo,
                                                                 const tb200_gemv_item *__restrict__ items) {
+    constexpr int U = (T * R <= 4) ? 4 : 2;   // batch depth: blocks per lane per row in flight
     extern __shared__ __align__(16) uint8_t smem[];
     uint4 *s_lo = reinterpret_cast<uint4 *>(smem);
     uint4 *s_hi = s_lo + T * nbc;
     int2 *s_ds = reinterpret_cast<int2 *>(s_hi + T * nbc);
+    __shared__ int s_arow[T];
 
+    pdl_launch_dependents();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long r_base = ((long)blockIdx.x * kWarps + warp) * R;   // first row of this warp (relative to row0)
     const bool active = r_base < nrows;
-    // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
-    __shared__ int s_arow[T];
-    long my_row0 = row0;
+
+    uint4 w[U][R];
+    __half dh[U][R];
+    const uint4 *wrow[R];
+    const __half *srow[R];
+    auto set_rows = [&](long my_row0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const long row = my_row0 + min(r_base + r, nrows - 1);   // clamp: tail rows recompute the last row, never stored
+            wrow[r] = qs + row * nb;
+            srow[r] = sc + row * nb;
+        }
+    };
+    auto load_batch = [&](long bbase, long cnt_end) {   // blocks bbase + lane + 32u, u < U, limited to < cnt_end (row-relative)
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long b = bbase + lane + 32 * u;
+            if (b < cnt_end) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) w[u][r] = ldg_stream(wrow[r] + b);
+#pragma unroll
+                for (int r = 0; r < R; ++r) dh[u][r] = srow[r][b];
+            }
+        }
+    };
+
+    // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens.
+    // The item table is written by a predecessor kernel, so it is only read after pdl_wait().
     int ntok = T, orow[T];
 #pragma unroll
     for (int t = 0; t < T; ++t) orow[t] = t;
+    if (!items) {
+        set_rows(row0);
+        if (active) load_batch(0, min(nbc, nb));   // first batch in flight before the activations are touched
+    }
+    pdl_wait();
     if (items) {
         const tb200_gemv_item &it = items[blockIdx.y];
         ntok = it.ntok;
         if (ntok == 0) return;   // CTA-uniform
-        my_row0 = it.row0;
+        set_rows(it.row0);
 #pragma unroll
         for (int t = 0; t < T; ++t) orow[t] = it.out_row[min(t, ntok - 1)];
         if (threadIdx.x < T) s_arow[threadIdx.x] = it.a_row[min((int)threadIdx.x, ntok - 1)];
+        if (active) load_batch(0, min(nbc, nb));
     } else if (threadIdx.x < T) s_arow[threadIdx.x] = threadIdx.x;
     __syncthreads();
 
@@ -61,15 +98,6 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
     for (int r = 0; r < R; ++r)
 #pragma unroll
         for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
-
-    const uint4 *wrow[R];
-    const __half *srow[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-        const long row = my_row0 + min(r_base + r, nrows - 1);   // clamp: tail rows recompute the last row, never stored
-        wrow[r] = qs + row * nb;
-        srow[r] = sc + row * nb;
-    }
 
     for (long b0 = 0; b0 < nb; b0 += nbc) {   // K chunks of nbc blocks (one chunk unless T*K is huge)
         const long cnt = min(nbc, nb - b0);
@@ -83,39 +111,42 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
         for (long i = threadIdx.x; i < T * cnt; i += blockDim.x) s_ds[(i / cnt) * nbc + (i % cnt)] = ads[(long)s_arow[i / cnt] * (a_stride / QK) + b0 + (i % cnt)];
         __syncthreads();
         if (!active) continue;
-        for (long b = lane; b < cnt; b += 32) {
-            uint4 w[R];
-            float d[R];
+        for (long bb = 0; bb < cnt; bb += 32 * U) {
+            if (b0 | bb) load_batch(b0 + bb, b0 + cnt);
 #pragma unroll
-            for (int r = 0; r < R; ++r) w[r] = ldg_stream(wrow[r] + b0 + b);
+            for (int u = 0; u < U; ++u) {
+                const long b = bb + lane + 32 * u;   // chunk-relative
+                if (b < cnt) {
+                    // nibble planes: lo = elements 0..15, hi = elements 16..31 (values 0..15; the -8 is folded in below)
+                    unsigned wl[R][4], wh[R][4];
+                    float d[R];
 #pragma unroll
-            for (int r = 0; r < R; ++r) d[r] = __half2float(srow[r][b0 + b]);
-            // nibble planes: lo = elements 0..15, hi = elements 16..31 (values 0..15; the -8 is folded in below)
-            unsigned wl[R][4], wh[R][4];
+                    for (int r = 0; r < R; ++r) {
+                        d[r] = __half2float(dh[u][r]);
+                        wl[r][0] = w[u][r].x & 0x0f0f0f0fu, wh[r][0] = (w[u][r].x >> 4) & 0x0f0f0f0fu;
+                        wl[r][1] = w[u][r].y & 0x0f0f0f0fu, wh[r][1] = (w[u][r].y >> 4) & 0x0f0f0f0fu;
+                        wl[r][2] = w[u][r].z & 0x0f0f0f0fu, wh[r][2] = (w[u][r].z >> 4) & 0x0f0f0f0fu;
+                        wl[r][3] = w[u][r].w & 0x0f0f0f0fu, wh[r][3] = (w[u][r].w >> 4) & 0x0f0f0f0fu;
+                    }
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                wl[r][0] = w[r].x & 0x0f0f0f0fu, wh[r][0] = (w[r].x >> 4) & 0x0f0f0f0fu;
-                wl[r][1] = w[r].y & 0x0f0f0f0fu, wh[r][1] = (w[r].y >> 4) & 0x0f0f0f0fu;
-                wl[r][2] = w[r].z & 0x0f0f0f0fu, wh[r][2] = (w[r].z >> 4) & 0x0f0f0f0fu;
-                wl[r][3] = w[r].w & 0x0f0f0f0fu, wh[r][3] = (w[r].w >> 4) & 0x0f0f0f0fu;
-            }
+                    for (int t = 0; t < T; ++t) {
+                        const uint4 al = s_lo[t * nbc + b], ah = s_hi[t * nbc + b];
+                        const int2 ds = s_ds[t * nbc + b];
+                        const float dy = __int_as_float(ds.x);
 #pragma unroll
-            for (int t = 0; t < T; ++t) {
-                const uint4 al = s_lo[t * nbc + b], ah = s_hi[t * nbc + b];
-                const int2 ds = s_ds[t * nbc + b];
-                const float dy = __int_as_float(ds.x);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    int s = dp4a_us(wl[r][0], (int)al.x, 0);
-                    s = dp4a_us(wl[r][1], (int)al.y, s);
-                    s = dp4a_us(wl[r][2], (int)al.z, s);
-                    s = dp4a_us(wl[r][3], (int)al.w, s);
-                    s = dp4a_us(wh[r][0], (int)ah.x, s);
-                    s = dp4a_us(wh[r][1], (int)ah.y, s);
-                    s = dp4a_us(wh[r][2], (int)ah.z, s);
-                    s = dp4a_us(wh[r][3], (int)ah.w, s);
-                    // sum (q-8)*y = sum q*y - 8*sum y  (exact in int32)
-                    acc[r][t] = fmaf(d[r] * dy, (float)(s - 8 * ds.y), acc[r][t]);
+                        for (int r = 0; r < R; ++r) {
+                            int s = dp4a_us(wl[r][0], (int)al.x, 0);
+                            s = dp4a_us(wl[r][1], (int)al.y, s);
+                            s = dp4a_us(wl[r][2], (int)al.z, s);
+                            s = dp4a_us(wl[r][3], (int)al.w, s);
+                            s = dp4a_us(wh[r][0], (int)ah.x, s);
+                            s = dp4a_us(wh[r][1], (int)ah.y, s);
+                            s = dp4a_us(wh[r][2], (int)ah.z, s);
+                            s = dp4a_us(wh[r][3], (int)ah.w, s);
+                            // sum (q-8)*y = sum q*y - 8*sum y  (exact in int32)
+                            acc[r][t] = fmaf(d[r] * dy, (float)(s - 8 * ds.y), acc[r][t]);
+                        }
+                    }
                 }
             }
         }
@@ -144,6 +175,8 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q8_0_kernel(const uint4 *__r
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long r_base = ((long)blockIdx.x * kWarps + warp) * R;
     const bool active = r_base < nrows;
+    pdl_launch_dependents();
+    pdl_wait();
     // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
     __shared__ int s_arow[T];
     long my_row0 = row0;
@@ -241,6 +274,8 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const uint4 *__r
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long r_base = ((long)blockIdx.x * kWarps + warp) * R;
     const bool active = r_base < nrows;
+    pdl_launch_dependents();
+    pdl_wait();
     // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
     __shared__ int s_arow[T];
     long my_row0 = row0;
@@ -334,6 +369,8 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_f16_kernel(const __half *__r
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long r_base = ((long)blockIdx.x * kWarps + warp) * R;
     const bool active = r_base < nrows;
+    pdl_launch_dependents();
+    pdl_wait();
     // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
     __shared__ int s_arow[T];
     long my_row0 = row0;
@@ -448,7 +485,7 @@ __global__ void blockdot_kernel(int type, const uint8_t *__restrict__ qs, const 
 
 template <typename K>
 int set_smem(K kernel, size_t bytes) {
-    if (bytes > 48 * 1024) {
+    if (bytes > 47 * 1024) {   // static shared memory counts against the 48 KB default too
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
         if (e != cudaSuccess) { tb200_set_error("gemv: %zu bytes of shared memory: %s", bytes, cudaGetErrorString(e)); return TB200_ERR_CUDA; }
     }
@@ -471,12 +508,12 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         const size_t smem = (size_t)T * nbc * 40;
         if (w->type == TB200_TYPE_Q4_0) {
             if ((rc = set_smem(gemv_q4_0_kernel<T, R>, smem))) return rc;
-            gemv_q4_0_kernel<T, R><<<grid, kWarps * 32, smem, c->stream>>>((const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,
-                                                                          a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items);
+            TB_CUDA(tb200_launch(gemv_q4_0_kernel<T, R>, grid, dim3(kWarps * 32), smem, c->stream, (const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,
+                                                                          a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items));
         } else {
             if ((rc = set_smem(gemv_q8_0_kernel<T, R>, smem))) return rc;
-            gemv_q8_0_kernel<T, R><<<grid, kWarps * 32, smem, c->stream>>>((const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,
-                                                                          a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items);
+            TB_CUDA(tb200_launch(gemv_q8_0_kernel<T, R>, grid, dim3(kWarps * 32), smem, c->stream, (const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,
+                                                                          a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items));
         }
         break;
     }
@@ -486,8 +523,8 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         if (nsbc >= nsb) nsbc = nsb;
         const size_t smem = (size_t)T * nsbc * 320;
         if ((rc = set_smem(gemv_q4_K_kernel<T, R>, smem))) return rc;
-        gemv_q4_K_kernel<T, R><<<grid, kWarps * 32, smem, c->stream>>>((const uint4 *)w->qs, (const uint4 *)w->sc, nsb, nsbc, a.row0, a.nrows,
-                                                                      a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items);
+        TB_CUDA(tb200_launch(gemv_q4_K_kernel<T, R>, grid, dim3(kWarps * 32), smem, c->stream, (const uint4 *)w->qs, (const uint4 *)w->sc, nsb, nsbc, a.row0, a.nrows,
+                                                                      a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items));
         break;
     }
     case TB200_TYPE_F16: {
@@ -496,10 +533,10 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         const size_t smem = (size_t)T * kc * 4;
         if (a.af_is_f32) {
             if ((rc = set_smem(gemv_f16_kernel<T, R, true>, smem))) return rc;
-            gemv_f16_kernel<T, R, true><<<grid, kWarps * 32, smem, c->stream>>>((const __half *)w->qs, w->k, kc, a.row0, a.nrows, a.af, a.a_stride, a.out, a.ldo, a.items);
+            TB_CUDA(tb200_launch(gemv_f16_kernel<T, R, true>, grid, dim3(kWarps * 32), smem, c->stream, (const __half *)w->qs, w->k, kc, a.row0, a.nrows, a.af, a.a_stride, a.out, a.ldo, a.items));
         } else {
             if ((rc = set_smem(gemv_f16_kernel<T, R, false>, smem))) return rc;
-            gemv_f16_kernel<T, R, false><<<grid, kWarps * 32, smem, c->stream>>>((const __half *)w->qs, w->k, kc, a.row0, a.nrows, a.af, a.a_stride, a.out, a.ldo, a.items);
+            TB_CUDA(tb200_launch(gemv_f16_kernel<T, R, false>, grid, dim3(kWarps * 32), smem, c->stream, (const __half *)w->qs, w->k, kc, a.row0, a.nrows, a.af, a.a_stride, a.out, a.ldo, a.items));
         }
         break;
     }
@@ -507,8 +544,6 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         tb200_set_error("gemv: unsupported weight type %d", w->type);
         return TB200_ERR_UNSUPPORTED;
     }
-    tb200_count_launch();
-    TB_CUDA(cudaGetLastError());
     return TB200_OK;
 }
 

@@ -27,6 +27,8 @@ template <bool kVec>
 __global__ void __launch_bounds__(256) quantize_q8_0_kernel(const float *__restrict__ x, long ldx, long rows, long nb,
                                                             uint8_t *__restrict__ raw, int8_t *__restrict__ q,
                                                             int2 *__restrict__ ds) {
+    pdl_launch_dependents();
+    pdl_wait();   // x comes from a predecessor; the outputs may still be read by one
     const long group = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 3;
     const int g8 = threadIdx.x & 7;
     const bool live = group < rows * nb;   // whole 8-lane groups go idle together; shuffles stay in-group
@@ -76,6 +78,8 @@ template <bool kVec>
 __global__ void __launch_bounds__(256) quantize_q8_K_kernel(const float *__restrict__ x, long ldx, long rows, long nb,
                                                             uint8_t *__restrict__ raw, int8_t *__restrict__ q,
                                                             int2 *__restrict__ ds) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long sb = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (sb >= rows * nb) return;   // warp-uniform
@@ -144,6 +148,8 @@ __global__ void __launch_bounds__(256) quantize_q8_K_kernel(const float *__restr
 }
 
 __global__ void f32_to_f16_kernel(const float *__restrict__ x, long ldx, long rows, long k, __half *__restrict__ y) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
     if (i >= rows * k) return;
     y[i] = __float2half_rn(x[(i / k) * ldx + (i % k)]);
@@ -190,10 +196,8 @@ int tb200_launch_quantize_q8_0(tb200_ctx *c, const float *x, long ldx, long rows
     const long nb = k / QK, threads = rows * nb * 8;
     if (threads == 0) return TB200_OK;
     const unsigned grid = (unsigned)((threads + 255) / 256);
-    if (aligned16(x, ldx)) quantize_q8_0_kernel<true><<<grid, 256, 0, c->stream>>>(x, ldx, rows, nb, (uint8_t *)raw, q, ds);
-    else quantize_q8_0_kernel<false><<<grid, 256, 0, c->stream>>>(x, ldx, rows, nb, (uint8_t *)raw, q, ds);
-    tb200_count_launch();
-    TB_CUDA(cudaGetLastError());
+    if (aligned16(x, ldx)) TB_CUDA(tb200_launch(quantize_q8_0_kernel<true>, dim3(grid), dim3(256), 0, c->stream, x, ldx, rows, nb, (uint8_t *)raw, q, ds));
+    else TB_CUDA(tb200_launch(quantize_q8_0_kernel<false>, dim3(grid), dim3(256), 0, c->stream, x, ldx, rows, nb, (uint8_t *)raw, q, ds));
     return TB200_OK;
 }
 
@@ -202,19 +206,15 @@ int tb200_launch_quantize_q8_K(tb200_ctx *c, const float *x, long ldx, long rows
     const long nb = k / QK_K, threads = rows * nb * 32;
     if (threads == 0) return TB200_OK;
     const unsigned grid = (unsigned)((threads + 255) / 256);
-    if (aligned16(x, ldx)) quantize_q8_K_kernel<true><<<grid, 256, 0, c->stream>>>(x, ldx, rows, nb, (uint8_t *)raw, q, ds);
-    else quantize_q8_K_kernel<false><<<grid, 256, 0, c->stream>>>(x, ldx, rows, nb, (uint8_t *)raw, q, ds);
-    tb200_count_launch();
-    TB_CUDA(cudaGetLastError());
+    if (aligned16(x, ldx)) TB_CUDA(tb200_launch(quantize_q8_K_kernel<true>, dim3(grid), dim3(256), 0, c->stream, x, ldx, rows, nb, (uint8_t *)raw, q, ds));
+    else TB_CUDA(tb200_launch(quantize_q8_K_kernel<false>, dim3(grid), dim3(256), 0, c->stream, x, ldx, rows, nb, (uint8_t *)raw, q, ds));
     return TB200_OK;
 }
 
 int tb200_launch_f32_to_f16(tb200_ctx *c, const float *x, long ldx, long rows, long k, __half *y) {
     const long n = rows * k;
     if (n == 0) return TB200_OK;
-    f32_to_f16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(x, ldx, rows, k, y);
-    tb200_count_launch();
-    TB_CUDA(cudaGetLastError());
+    TB_CUDA(tb200_launch(f32_to_f16_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, c->stream, x, ldx, rows, k, y));
     return TB200_OK;
 }
 
