@@ -1,7 +1,502 @@
-// Prefill path placeholder — replaced by the tcgen05 GEMM.
+// Prefill path (SURVEY.md §8 rows a9-a12 at n > 8): quant tiles staged by TMA, dequantised to fp16 in shared
+// memory, fed to tcgen05.mma (cta_group::1, M=128, N<=256, K=16 per instruction) with fp32 accumulators in TMEM.
+//
+// Arithmetic contract (DESIGN.md "prefill numerics"): the reference computes sum_b d_x[b]*d_y[b]*sum_j q_x*q_y with
+// exact int32 block sums (llamafile/iqk_mul_mat.inc:1129-1201, tinyblas_cpu.h:934-993). Here both operands are
+// turned into 16-bit floats once, A' = fp16(d_x*(q_x-8)) and B' = fp16(d_y*q_y*2^-e_t), and multiplied with fp32
+// accumulation; each operand carries one rounding of 2^-12 relative (fp16 keeps 11 significand bits; bf16 would
+// keep 8 and break the 1e-3 bound, which is why the 16-bit type is fp16 — same tensor-pipe rate). The activations
+// are first quantized to Q8_0 / Q8_K bit-exactly like the reference, so quantization noise is identical and only
+// the two operand roundings and the accumulation order differ. e_t is a per-token power of two that keeps every
+// B' value inside fp16 range; it is undone exactly in the epilogue.
+//
+// K order: a dot product does not care about the order of k as long as A' and B' agree. A Q4_0 / Q4_K word holds
+// nibbles of elements (j, j+16) / (l, l+32) interleaved, so unpacking it yields 8 halves in a fixed permuted order;
+// the activation prep kernel writes B' in that same order, which saves all byte permutes in the dequant loop.
+//
+// Warp roles (384 threads, 1 CTA / SM): warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator,
+// warps 4-11 dequantisers (and, after the main loop, TMEM->register->global epilogue).
+#include <cuda.h>
+
 #include "tb200_common.cuh"
-bool tb200_gemm_available() { return false; }
-int tb200_launch_gemm(tb200_ctx *, const tb200_weights *, long, long, const int8_t *, const int2 *, const void *, long, long, float *, long) {
-    return TB200_ERR_UNSUPPORTED;
+
+namespace {
+
+constexpr int BM = 128;        // weight rows per CTA tile = UMMA M
+constexpr int BK = 64;         // K elements per stage = one 128-byte swizzle atom of fp16
+constexpr int kDequantWarps = 8;
+constexpr int kThreads = (4 + kDequantWarps) * 32;
+
+// ------------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
-void tb200_gemm_release(tb200_weights *) {}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+                 "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) { asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t *dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]),
+          "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+          "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]),
+          "=r"(v[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// shared-memory matrix descriptor, K-major, SWIZZLE_128B (cute::UMMA::SmemDescriptor bit layout): start>>4 [0,14),
+// LBO>>4 [16,30) (ignored for swizzled K-major, canonical value 1), SBO>>4 [32,46) = 8 rows x 128 B = 1024 B,
+// version=1 [46,48), layout_type=2 (SWIZZLE_128B) [61,64)
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32=1 [4,6), a/b_format F16=0 [7,10)/[10,13),
+// a/b K-major = 0 [15]/[16], N>>3 [17,23), M>>4 [24,29)
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) { return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24); }
+
+// ------------------------------------------------------------------------------------------------ dequantisers
+// Each dequant thread owns (row = tid>>1, half = tid&1) of the 128 x 64 stage tile and writes 4 16-byte chunks of
+// fp16 into the SWIZZLE_128B A tile: chunk c of row r lives at r*128 + ((c ^ (r & 7)) << 4).
+__device__ __forceinline__ void store_chunk(uint8_t *a_tile, int row, int c, uint4 v) {
+    *reinterpret_cast<uint4 *>(a_tile + row * 128 + ((c ^ (row & 7)) << 4)) = v;
+}
+__device__ __forceinline__ uint32_t h2_sub_mul(uint32_t x, __half2 sub, __half2 mul) {
+    const __half2 r = __hmul2(__hsub2(*reinterpret_cast<const __half2 *>(&x), sub), mul);
+    return *reinterpret_cast<const uint32_t *>(&r);
+}
+__device__ __forceinline__ uint32_t h2_fma(uint32_t x, __half2 mul, __half2 add) {
+    const __half2 r = __hfma2(*reinterpret_cast<const __half2 *>(&x), mul, add);
+    return *reinterpret_cast<const uint32_t *>(&r);
+}
+
+// Q4_0 word (bytes 4w..4w+3 of a block): halves come out as elements (4w, 4w+2, 4w+1, 4w+3, 4w+16, 4w+18, 4w+17, 4w+19).
+// (nibble | 0x6400) is the fp16 1024+q; minus 1032 gives q-8 exactly; one rounding in the multiply by d.
+__device__ __forceinline__ uint4 dequant_q4_word(uint32_t w, __half2 d2) {
+    const __half2 k1032 = __floats2half2_rn(1032.f, 1032.f);
+    uint4 o;
+    o.x = h2_sub_mul((w & 0x000F000Fu) | 0x64006400u, k1032, d2);
+    o.y = h2_sub_mul(((w >> 8) & 0x000F000Fu) | 0x64006400u, k1032, d2);
+    o.z = h2_sub_mul(((w >> 4) & 0x000F000Fu) | 0x64006400u, k1032, d2);
+    o.w = h2_sub_mul(((w >> 12) & 0x000F000Fu) | 0x64006400u, k1032, d2);
+    return o;
+}
+// Q4_K word (bytes 4w..4w+3 of a 32-byte chunk): (l, l+2, l+1, l+3) of the low sub-block then of the high sub-block;
+// value = (d*sc)*q - (dmin*m): fp16 fma of the exact small integer q with the two fp16-rounded sub-block constants.
+__device__ __forceinline__ uint4 dequant_q4K_word(uint32_t w, __half2 a_lo, __half2 b_lo, __half2 a_hi, __half2 b_hi) {
+    const __half2 k1024 = __floats2half2_rn(1024.f, 1024.f);
+    auto q = [&](uint32_t x) { const __half2 r = __hsub2(*reinterpret_cast<const __half2 *>(&x), k1024); return *reinterpret_cast<const uint32_t *>(&r); };
+    uint4 o;
+    o.x = h2_fma(q((w & 0x000F000Fu) | 0x64006400u), a_lo, b_lo);
+    o.y = h2_fma(q(((w >> 8) & 0x000F000Fu) | 0x64006400u), a_lo, b_lo);
+    o.z = h2_fma(q(((w >> 4) & 0x000F000Fu) | 0x64006400u), a_hi, b_hi);
+    o.w = h2_fma(q(((w >> 12) & 0x000F000Fu) | 0x64006400u), a_hi, b_hi);
+    return o;
+}
+// Q8_0 word (4 int8): natural order. (byte ^ 0x80) | 0x6400 is 1024 + (q + 128); minus 1152 gives q exactly.
+__device__ __forceinline__ uint2 dequant_q8_word(uint32_t w, __half2 d2) {
+    const __half2 k1152 = __floats2half2_rn(1152.f, 1152.f);
+    const uint32_t x = w ^ 0x80808080u;
+    uint2 o;
+    o.x = h2_sub_mul(__byte_perm(x, 0x64646464u, 0x4140), k1152, d2);
+    o.y = h2_sub_mul(__byte_perm(x, 0x64646464u, 0x4342), k1152, d2);
+    return o;
+}
+
+__device__ __forceinline__ void q4k_scale_min(const uint4 hdr, int j, int &sc, int &m) {   // get_scale_min_k4, ggml-quants.c:1891-1899
+    const uint32_t s0 = hdr.y, s1 = hdr.z, s2 = hdr.w;
+    auto byte = [&](int i) -> uint32_t { const uint32_t wv = i < 4 ? s0 : (i < 8 ? s1 : s2); return (wv >> (8 * (i & 3))) & 0xff; };
+    if (j < 4) { sc = byte(j) & 63; m = byte(j + 4) & 63; }
+    else { sc = (byte(j + 4) & 0xF) | ((byte(j - 4) >> 6) << 4); m = (byte(j + 4) >> 4) | ((byte(j) >> 6) << 4); }
+}
+
+struct GemmParams {
+    const void *sc;        // scales plane of the weights
+    long sc_row_stride;    // in elements of the plane (fp16 for Q4_0/Q8_0, uint4 for Q4_K)
+    long row0, nrows;      // weight rows [row0, row0 + nrows)
+    long k, tokens;
+    const float *colscale; // [tokens] 2^e_t
+    float *out; long ldo;
+};
+
+// ------------------------------------------------------------------------------------------------ the kernel
+// kType: weight type. BN: token tile (UMMA N). kStages: pipeline depth.
+template <int kType, int BN, int kStages>
+__global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
+                                                                   const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+    constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 0 : BM * BK / 2);
+    constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2;
+    constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;   // power of two >= 32 (BN is 32/64/128/256)
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *sA = smem;                                   // [kStages][BM x 128 B]  swizzled fp16 A'
+    uint8_t *sB = sA + kStages * kABytes;                 // [kStages][BN x 128 B]  swizzled fp16 B' (TMA)
+    uint8_t *sP = sB + kStages * kBBytes;                 // [kStages][packed quant tile] (TMA)
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sP + kStages * (kPackedBytes ? kPackedBytes : 16));
+    uint64_t *full_p = bars, *full_a = bars + kStages, *full_b = bars + 2 * kStages, *empty = bars + 3 * kStages, *accum_full = bars + 4 * kStages;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(accum_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long tile_row = (long)blockIdx.x * BM, tile_tok = (long)blockIdx.y * BN;
+    const int kt = (int)(p.k / BK);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_w);
+        tma_prefetch_desc(&map_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_p[s], 1);
+            mbar_init(&full_a[s], kType == TB200_TYPE_F16 ? 1 : kDequantWarps);   // one elected arrive per dequant warp (F16: the TMA's expect_tx)
+            mbar_init(&full_b[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(accum_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();   // B' and colscale come from the activation prep kernel
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            for (int i = 0; i < kt; ++i) {
+                const int s = i % kStages;
+                if (i >= kStages) mbar_wait(&empty[s], ((i / kStages) - 1) & 1);
+                if (kType == TB200_TYPE_F16) {
+                    mbar_expect_tx(&full_a[s], kABytes);   // F16 weights: TMA writes the swizzled A tile directly
+                    tma_load_2d(sA + s * kABytes, &map_w, &full_a[s], i * BK, (int)(p.row0 + tile_row));
+                } else {
+                    mbar_expect_tx(&full_p[s], kPackedBytes);
+                    tma_load_2d(sP + s * kPackedBytes, &map_w, &full_p[s], i * (kType == TB200_TYPE_Q8_0 ? BK : BK / 2), (int)(p.row0 + tile_row));
+                }
+                mbar_expect_tx(&full_b[s], kBBytes);
+                tma_load_2d(sB + s * kBBytes, &map_b, &full_b[s], i * BK, (int)tile_tok);
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_f16(BM, BN);
+            for (int i = 0; i < kt; ++i) {
+                const int s = i % kStages;
+                const uint32_t ph = (i / kStages) & 1;
+                mbar_wait(&full_a[s], ph);
+                mbar_wait(&full_b[s], ph);
+                tc_fence_after();
+                const uint64_t da = make_desc_sw128(smem_u32(sA + s * kABytes)), db = make_desc_sw128(smem_u32(sB + s * kBBytes));
+#pragma unroll
+                for (int kk = 0; kk < BK / 16; ++kk)   // advance 16 elements = 32 bytes inside the swizzle atom
+                    umma_f16(tmem_base, da + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), idesc, (i | kk) ? 1u : 0u);
+                umma_commit(&empty[s]);                 // frees the stage when these MMAs have read it
+            }
+            umma_commit(accum_full);
+        }
+    } else if (warp >= 4) {
+        // ===== dequantisers =====
+        const int tid = threadIdx.x - 128;            // 0..255
+        const int row = tid >> 1, half = tid & 1;
+        const long grow = p.row0 + min(tile_row + row, p.nrows - 1);   // clamp rows past the matrix end (their outputs are masked)
+        if (kType != TB200_TYPE_F16) {
+            for (int i = 0; i < kt; ++i) {
+                const int s = i % kStages;
+                const uint32_t ph = (i / kStages) & 1;
+                uint8_t *a_tile = sA + s * kABytes;
+                if (kType == TB200_TYPE_Q4_0) {
+                    const __half d = reinterpret_cast<const __half *>(p.sc)[grow * p.sc_row_stride + i * 2 + half];
+                    const __half2 d2 = __half2half2(d);
+                    mbar_wait(&full_p[s], ph);
+                    const uint4 w = *reinterpret_cast<const uint4 *>(sP + s * kPackedBytes + row * 32 + half * 16);
+                    store_chunk(a_tile, row, half * 4 + 0, dequant_q4_word(w.x, d2));
+                    store_chunk(a_tile, row, half * 4 + 1, dequant_q4_word(w.y, d2));
+                    store_chunk(a_tile, row, half * 4 + 2, dequant_q4_word(w.z, d2));
+                    store_chunk(a_tile, row, half * 4 + 3, dequant_q4_word(w.w, d2));
+                } else if (kType == TB200_TYPE_Q8_0) {
+                    const __half d = reinterpret_cast<const __half *>(p.sc)[grow * p.sc_row_stride + i * 2 + half];
+                    const __half2 d2 = __half2half2(d);
+                    mbar_wait(&full_p[s], ph);
+                    const uint4 w0 = *reinterpret_cast<const uint4 *>(sP + s * kPackedBytes + row * 64 + half * 32);
+                    const uint4 w1 = *reinterpret_cast<const uint4 *>(sP + s * kPackedBytes + row * 64 + half * 32 + 16);
+                    uint2 a, b;
+                    a = dequant_q8_word(w0.x, d2), b = dequant_q8_word(w0.y, d2);
+                    store_chunk(a_tile, row, half * 4 + 0, make_uint4(a.x, a.y, b.x, b.y));
+                    a = dequant_q8_word(w0.z, d2), b = dequant_q8_word(w0.w, d2);
+                    store_chunk(a_tile, row, half * 4 + 1, make_uint4(a.x, a.y, b.x, b.y));
+                    a = dequant_q8_word(w1.x, d2), b = dequant_q8_word(w1.y, d2);
+                    store_chunk(a_tile, row, half * 4 + 2, make_uint4(a.x, a.y, b.x, b.y));
+                    a = dequant_q8_word(w1.z, d2), b = dequant_q8_word(w1.w, d2);
+                    store_chunk(a_tile, row, half * 4 + 3, make_uint4(a.x, a.y, b.x, b.y));
+                } else {   // Q4_K: stage i is 64-element chunk c = i & 3 of super-block i >> 2
+                    const uint4 hdr = __ldg(reinterpret_cast<const uint4 *>(p.sc) + grow * p.sc_row_stride + (i >> 2));
+                    const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr.x);
+                    const float d = __low2float(dd), dmin = __high2float(dd);
+                    int sc_lo, m_lo, sc_hi, m_hi;
+                    q4k_scale_min(hdr, 2 * (i & 3), sc_lo, m_lo);
+                    q4k_scale_min(hdr, 2 * (i & 3) + 1, sc_hi, m_hi);
+                    const __half2 a_lo = __float2half2_rn(d * sc_lo), b_lo = __float2half2_rn(-(dmin * m_lo));
+                    const __half2 a_hi = __float2half2_rn(d * sc_hi), b_hi = __float2half2_rn(-(dmin * m_hi));
+                    mbar_wait(&full_p[s], ph);
+                    const uint4 w = *reinterpret_cast<const uint4 *>(sP + s * kPackedBytes + row * 32 + half * 16);
+                    store_chunk(a_tile, row, half * 4 + 0, dequant_q4K_word(w.x, a_lo, b_lo, a_hi, b_hi));
+                    store_chunk(a_tile, row, half * 4 + 1, dequant_q4K_word(w.y, a_lo, b_lo, a_hi, b_hi));
+                    store_chunk(a_tile, row, half * 4 + 2, dequant_q4K_word(w.z, a_lo, b_lo, a_hi, b_hi));
+                    store_chunk(a_tile, row, half * 4 + 3, dequant_q4K_word(w.w, a_lo, b_lo, a_hi, b_hi));
+                }
+                fence_proxy_async();   // generic-proxy stores -> visible to the tensor core (async proxy)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full_a[s]);
+            }
+        }
+        // ===== epilogue: TMEM -> registers -> global. Warp w may touch TMEM lanes 32*(w%4).. ; warps 4-7 take the
+        // first half of the columns, warps 8-11 the second half.
+        mbar_wait(accum_full, 0);
+        tc_fence_after();
+        const int quad = warp & 3, chalf = (warp - 4) >> 2;
+        const long out_row = tile_row + quad * 32 + lane;
+        constexpr int kChunks = BN / 32 > 0 ? BN / 32 : 1;
+        for (int ch = chalf; ch < kChunks; ch += 2) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32), v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const long t = tile_tok + ch * 32 + j;
+                if (t < p.tokens && out_row < p.nrows) p.out[t * p.ldo + out_row] = __uint_as_float(v[j]) * p.colscale[t];
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------------ activation prep
+// planar Q8 activations -> B' fp16 [tokens][k] in the weight type's K order, scaled by 2^-e_t; colscale[t] = 2^e_t.
+// perm: 0 natural (Q8_0), 1 Q4_0 order per 32-block, 2 Q4_K order per 64-chunk.
+__device__ __forceinline__ int perm_pos(int perm, int kk) {   // position of element kk inside its 64-element group
+    if (perm == 0) return kk;
+    if (perm == 1) {   // within a 32-block: element e -> word w = (e & 15) >> 2, slot: low nibble elems (4w,4w+2,4w+1,4w+3), high +16
+        const int blk = kk >> 5, e = kk & 31, hi = e >> 4, x = e & 15, w = x >> 2, r = x & 3;
+        const int slot = (r == 0 ? 0 : r == 2 ? 1 : r == 1 ? 2 : 3) + 4 * hi;
+        return blk * 32 + w * 8 + slot;
+    }
+    const int hi = kk >> 5, x = kk & 31, w = x >> 2, r = x & 3;   // 64-chunk: low sub-block elems 0..31, high 32..63
+    const int slot = (r == 0 ? 0 : r == 2 ? 1 : r == 1 ? 2 : 3) + 4 * hi;
+    return w * 8 + slot;
+}
+
+__global__ void __launch_bounds__(256) prep_acts_kernel(const int8_t *__restrict__ aq, const int2 *__restrict__ ads, long a_stride, long k,
+                                                        int perm, __half *__restrict__ bp, float *__restrict__ colscale) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const long t = blockIdx.x;
+    const int2 *ds = ads + t * (a_stride / QK);
+    const int8_t *q = aq + t * a_stride;
+    __shared__ float s_max[8];
+    float bound = 0.f;
+    for (long b = threadIdx.x; b < k / QK; b += blockDim.x) bound = fmaxf(bound, fabsf(__int_as_float(ds[b].x)) * 127.f);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) bound = fmaxf(bound, __shfl_xor_sync(0xffffffffu, bound, o));
+    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = bound;
+    __syncthreads();
+    bound = s_max[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) bound = fmaxf(bound, s_max[i]);
+    // e_t: bound * 2^-e in [2^14, 2^15) -> every |B'| < 65504; zero or non-finite rows keep e = 0
+    int e = 0;
+    if (bound > 0.f && bound < 3.0e38f) e = ilogbf(bound) - 14;
+    const float inv = ldexpf(1.f, -e);
+    if (threadIdx.x == 0) colscale[t] = ldexpf(1.f, e);
+    for (long i = threadIdx.x; i < k; i += blockDim.x) {
+        const float d = __int_as_float(ds[i >> 5].x);
+        const float v = __fmul_rn(__fmul_rn(d, (float)q[i]), inv);
+        bp[t * k + (i & ~63L) + perm_pos(perm, (int)(i & 63))] = __float2half_rn(v);
+    }
+}
+
+__global__ void fill_ones_kernel(float *p, long n) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i < n) p[i] = 1.f;
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) f = nullptr;
+        return (EncodeTiledFn)f;
+    }();
+    return fn;
+}
+
+bool make_map_2d(CUtensorMap *m, CUtensorMapDataType dt, size_t esize, void *base, uint64_t inner, uint64_t outer, uint64_t row_bytes,
+                 uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle sw) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) { tb200_set_error("gemm: cuTensorMapEncodeTiled unavailable"); return false; }
+    const cuuint64_t dims[2] = {inner, outer};
+    const cuuint64_t strides[1] = {row_bytes};
+    const cuuint32_t box[2] = {box_inner, box_outer};
+    const cuuint32_t estr[2] = {1, 1};
+    (void)esize;
+    const CUresult r = fn(m, dt, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { tb200_set_error("gemm: cuTensorMapEncodeTiled failed (%d)", (int)r); return false; }
+    return true;
+}
+
+struct GemmScratch { void *p = nullptr; size_t cap = 0; };
+GemmScratch g_scratch[16];
+
+void *gemm_scratch(tb200_ctx *c, size_t bytes) {
+    GemmScratch &s = g_scratch[c->device];
+    if (bytes <= s.cap) return s.p;
+    cudaStreamSynchronize(c->stream);
+    if (s.p) cudaFree(s.p);
+    s.p = nullptr, s.cap = 0;
+    const size_t want = (bytes + bytes / 4 + (1 << 20) - 1) >> 20 << 20;
+    if (cudaMalloc(&s.p, want) != cudaSuccess) { cudaGetLastError(); tb200_set_error("gemm: scratch cudaMalloc(%zu) failed", want); return nullptr; }
+    s.cap = want;
+    return s.p;
+}
+
+template <int kType, int BN, int kStages>
+int launch_cfg(tb200_ctx *c, const CUtensorMap &mw, const CUtensorMap &mb, const GemmParams &p) {
+    constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 16 : BM * BK / 2);
+    constexpr size_t smem = 1024 + (size_t)kStages * (BM * BK * 2 + BN * BK * 2 + kPackedBytes) + (4 * kStages + 1) * 8 + 16;
+    static_assert(smem <= 227 * 1024, "stage configuration exceeds shared memory");
+    auto kern = gemm_tcgen05_kernel<kType, BN, kStages>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    const dim3 grid((unsigned)((p.nrows + BM - 1) / BM), (unsigned)((p.tokens + BN - 1) / BN));
+    TB_CUDA(tb200_launch(kern, grid, dim3(kThreads), smem, c->stream, mw, mb, p));
+    return TB200_OK;
+}
+
+template <int kType>
+int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long tokens, void *bp, GemmParams &p) {
+    // token tile: as wide as the batch allows (fewer re-dequantisations of the same weight tile), but keep >= ~1 wave of CTAs
+    const long row_tiles = (p.nrows + BM - 1) / BM;
+    int bn = 256;
+    while (bn > 32 && (tokens <= bn / 2 || row_tiles * ((tokens + bn - 1) / bn) < c->sm_count)) bn >>= 1;
+    if (tokens > 128 && bn < 128) bn = 128;
+    CUtensorMap mb;
+    if (!make_map_2d(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, bp, (uint64_t)w->k, (uint64_t)tokens, (uint64_t)w->k * 2, BK, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B))
+        return TB200_ERR_CUDA;
+    switch (bn) {
+    case 256: return launch_cfg<kType, 256, kType == TB200_TYPE_Q8_0 ? 3 : 4>(c, mw, mb, p);
+    case 128: return launch_cfg<kType, 128, 5>(c, mw, mb, p);
+    case 64: return launch_cfg<kType, 64, 6>(c, mw, mb, p);
+    default: return launch_cfg<kType, 32, 6>(c, mw, mb, p);
+    }
+}
+
+}  // namespace
+
+bool tb200_gemm_available() {
+    static const int on = [] { const char *v = getenv("TB200_GEMM"); return (v && *v == '0') ? 0 : 1; }();
+    return on != 0 && encode_fn() != nullptr;
+}
+
+void tb200_gemm_release(tb200_weights *w) {
+    if (w && w->tmap_cache) { delete reinterpret_cast<CUtensorMap *>(w->tmap_cache); w->tmap_cache = nullptr; }
+}
+
+// out[t*ldo + i] for rows [row0, row0+nrows). Quantized types take planar activations (aq, ads); F16 takes af (fp16 [tokens][a_stride]).
+int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrows, const int8_t *aq, const int2 *ads, const void *af,
+                      long a_stride, long tokens, float *out, long ldo) {
+    if (w->k % 256 || ((uintptr_t)w->qs & 15)) { tb200_set_error("gemm: K=%ld must be a multiple of 256", w->k); return TB200_ERR_UNSUPPORTED; }
+    const size_t bp_bytes = ((size_t)tokens * w->k * 2 + 255) & ~(size_t)255;
+    uint8_t *scr = (uint8_t *)gemm_scratch(c, bp_bytes + (size_t)tokens * 4);
+    if (!scr) return TB200_ERR_CUDA;
+    __half *bp = (__half *)scr;
+    float *colscale = (float *)(scr + bp_bytes);
+    const void *b_src = bp;
+    if (w->type == TB200_TYPE_F16) {
+        // ggml already rounded the activations to fp16 (ggml_fp32_to_fp16_row): use them as they are
+        if (a_stride != w->k) { tb200_set_error("gemm: F16 activations must be contiguous"); return TB200_ERR_UNSUPPORTED; }
+        b_src = af;
+        TB_CUDA(tb200_launch(fill_ones_kernel, dim3((unsigned)((tokens + 255) / 256)), dim3(256), 0, c->stream, colscale, tokens));
+    } else {
+        const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : 2);
+        TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)tokens), dim3(256), 0, c->stream, aq, ads, a_stride, w->k, perm, bp, colscale));
+    }
+    // weight tensor map (whole matrix), cached on the weights object
+    if (!w->tmap_cache) {
+        CUtensorMap *m = new CUtensorMap();
+        bool ok;
+        if (w->type == TB200_TYPE_F16) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k * 2, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
+        else if (w->type == TB200_TYPE_Q8_0) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k, BK, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
+        else ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / 2, (uint64_t)w->rows, (uint64_t)w->k / 2, BK / 2, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
+        if (!ok) { delete m; return TB200_ERR_CUDA; }
+        const_cast<tb200_weights *>(w)->tmap_cache = m;
+    }
+    CUtensorMap &mw = *reinterpret_cast<CUtensorMap *>(w->tmap_cache);
+    GemmParams p;
+    p.sc = w->sc;
+    p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
+    p.row0 = row0, p.nrows = nrows, p.k = w->k, p.tokens = tokens, p.colscale = colscale, p.out = out, p.ldo = ldo;
+    switch (w->type) {
+    case TB200_TYPE_Q4_0: return launch_type<TB200_TYPE_Q4_0>(c, w, mw, tokens, (void *)b_src, p);
+    case TB200_TYPE_Q8_0: return launch_type<TB200_TYPE_Q8_0>(c, w, mw, tokens, (void *)b_src, p);
+    case TB200_TYPE_Q4_K: return launch_type<TB200_TYPE_Q4_K>(c, w, mw, tokens, (void *)b_src, p);
+    case TB200_TYPE_F16: return launch_type<TB200_TYPE_F16>(c, w, mw, tokens, (void *)b_src, p);
+    default: return TB200_ERR_UNSUPPORTED;
+    }
+}

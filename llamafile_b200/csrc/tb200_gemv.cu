@@ -18,7 +18,7 @@
 
 namespace {
 
-constexpr int kWarps = 4;   // warps per CTA
+constexpr int kWarps = 8;   // warps per CTA
 
 // ---- shared-memory activation staging ----------------------------------------------------------
 // Q4_0: a 32-block's low-nibble elements are 0..15 and high-nibble elements 16..31, so the block's two
@@ -102,13 +102,17 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
     for (long b0 = 0; b0 < nb; b0 += nbc) {   // K chunks of nbc blocks (one chunk unless T*K is huge)
         const long cnt = min(nbc, nb - b0);
         if (b0) __syncthreads();
-        // stage activations: 16-byte piece g of token t -> plane (g&1), index g>>1
-        for (long i = threadIdx.x; i < T * cnt * 2; i += blockDim.x) {
-            const long t = i / (cnt * 2), g = i % (cnt * 2);
-            const uint4 v = *reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + (b0 * 2 + g) * 16);
-            ((g & 1) ? s_hi : s_lo)[t * nbc + (g >> 1)] = v;
+        // stage activations: 16-byte piece g of token t -> plane (g&1), index g>>1 (no div/mod: T is compile-time)
+        {
+            const int cnt2 = (int)cnt * 2, nbc_i = (int)nbc;
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const uint4 *src = reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + b0 * 32);
+                const int2 *dsrc = ads + (long)s_arow[t] * (a_stride / QK) + b0;
+                for (int g = threadIdx.x; g < cnt2; g += kWarps * 32) ((g & 1) ? s_hi : s_lo)[t * nbc_i + (g >> 1)] = src[g];
+                for (int g = threadIdx.x; g < (int)cnt; g += kWarps * 32) s_ds[t * nbc_i + g] = dsrc[g];
+            }
         }
-        for (long i = threadIdx.x; i < T * cnt; i += blockDim.x) s_ds[(i / cnt) * nbc + (i % cnt)] = ads[(long)s_arow[i / cnt] * (a_stride / QK) + b0 + (i % cnt)];
         __syncthreads();
         if (!active) continue;
         for (long bb = 0; bb < cnt; bb += 32 * U) {
@@ -123,10 +127,11 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
                         d[r] = __half2float(dh[u][r]);
-                        wl[r][0] = w[u][r].x & 0x0f0f0f0fu, wh[r][0] = (w[u][r].x >> 4) & 0x0f0f0f0fu;
-                        wl[r][1] = w[u][r].y & 0x0f0f0f0fu, wh[r][1] = (w[u][r].y >> 4) & 0x0f0f0f0fu;
-                        wl[r][2] = w[u][r].z & 0x0f0f0f0fu, wh[r][2] = (w[u][r].z >> 4) & 0x0f0f0f0fu;
-                        wl[r][3] = w[u][r].w & 0x0f0f0f0fu, wh[r][3] = (w[u][r].w >> 4) & 0x0f0f0f0fu;
+                        // high nibbles stay in place (= 16*q as unsigned bytes); their dp4a sum is shifted back once
+                        wl[r][0] = w[u][r].x & 0x0f0f0f0fu, wh[r][0] = w[u][r].x & 0xf0f0f0f0u;
+                        wl[r][1] = w[u][r].y & 0x0f0f0f0fu, wh[r][1] = w[u][r].y & 0xf0f0f0f0u;
+                        wl[r][2] = w[u][r].z & 0x0f0f0f0fu, wh[r][2] = w[u][r].z & 0xf0f0f0f0u;
+                        wl[r][3] = w[u][r].w & 0x0f0f0f0fu, wh[r][3] = w[u][r].w & 0xf0f0f0f0u;
                     }
 #pragma unroll
                     for (int t = 0; t < T; ++t) {
@@ -135,16 +140,15 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
                         const float dy = __int_as_float(ds.x);
 #pragma unroll
                         for (int r = 0; r < R; ++r) {
-                            int s = dp4a_us(wl[r][0], (int)al.x, 0);
+                            int s = dp4a_us(wl[r][0], (int)al.x, -8 * ds.y);   // sum (q-8)*y = sum q*y - 8*sum y (exact in int32)
                             s = dp4a_us(wl[r][1], (int)al.y, s);
                             s = dp4a_us(wl[r][2], (int)al.z, s);
                             s = dp4a_us(wl[r][3], (int)al.w, s);
-                            s = dp4a_us(wh[r][0], (int)ah.x, s);
-                            s = dp4a_us(wh[r][1], (int)ah.y, s);
-                            s = dp4a_us(wh[r][2], (int)ah.z, s);
-                            s = dp4a_us(wh[r][3], (int)ah.w, s);
-                            // sum (q-8)*y = sum q*y - 8*sum y  (exact in int32)
-                            acc[r][t] = fmaf(d[r] * dy, (float)(s - 8 * ds.y), acc[r][t]);
+                            int sh = dp4a_us(wh[r][0], (int)ah.x, 0);
+                            sh = dp4a_us(wh[r][1], (int)ah.y, sh);
+                            sh = dp4a_us(wh[r][2], (int)ah.z, sh);
+                            sh = dp4a_us(wh[r][3], (int)ah.w, sh);
+                            acc[r][t] = fmaf(d[r] * dy, (float)(s + (sh >> 4)), acc[r][t]);   // sh is an exact multiple of 16
                         }
                     }
                 }
@@ -209,11 +213,13 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q8_0_kernel(const uint4 *__r
     for (long b0 = 0; b0 < nb; b0 += nbc) {
         const long cnt = min(nbc, nb - b0);
         if (b0) __syncthreads();
-        for (long i = threadIdx.x; i < T * cnt * 2; i += blockDim.x) {
-            const long t = i / (cnt * 2), g = i % (cnt * 2);
-            s_q[t * nbc * 2 + g] = *reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + (b0 * 2 + g) * 16);
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const uint4 *src = reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + b0 * 32);
+            const int2 *dsrc = ads + (long)s_arow[t] * (a_stride / QK) + b0;
+            for (int g = threadIdx.x; g < (int)cnt * 2; g += kWarps * 32) s_q[t * (int)nbc * 2 + g] = src[g];
+            for (int g = threadIdx.x; g < (int)cnt; g += kWarps * 32) s_ds[t * (int)nbc + g] = dsrc[g];
         }
-        for (long i = threadIdx.x; i < T * cnt; i += blockDim.x) s_ds[(i / cnt) * nbc + (i % cnt)] = ads[(long)s_arow[i / cnt] * (a_stride / QK) + b0 + (i % cnt)];
         __syncthreads();
         if (!active) continue;
         for (long g = lane; g < cnt * 2; g += 32) {
@@ -301,15 +307,16 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const uint4 *__r
     for (long sb0 = 0; sb0 < nsb; sb0 += nsbc) {
         const long cnt = min(nsbc, nsb - sb0);
         if (sb0) __syncthreads();
-        for (long i = threadIdx.x; i < T * cnt * 16; i += blockDim.x) {
-            const long t = i / (cnt * 16), g = i % (cnt * 16);   // g = 16-byte piece of this chunk of the activation row
-            const long sb = g >> 4;
-            const int gi = (int)(g & 15), cc = gi >> 2, hl = (gi >> 1) & 1, hh = gi & 1;
-            const uint4 v = *reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + (sb0 * 16 + g) * 16);
-            (hl ? s_hi : s_lo)[(t * nsbc + sb) * 8 + 2 * cc + hh] = v;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const uint4 *src = reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + sb0 * QK_K);
+            const int2 *dsrc = ads + (long)s_arow[t] * (a_stride / QK) + sb0 * 8;
+            for (int g = threadIdx.x; g < (int)cnt * 16; g += kWarps * 32) {   // g = 16-byte piece of this chunk of the activation row
+                const int sb = g >> 4, gi = g & 15, cc = gi >> 2, hl = (gi >> 1) & 1, hh = gi & 1;
+                (hl ? s_hi : s_lo)[(t * (int)nsbc + sb) * 8 + 2 * cc + hh] = src[g];
+            }
+            for (int g = threadIdx.x; g < (int)cnt * 8; g += kWarps * 32) s_ds[t * (int)nsbc * 8 + g] = dsrc[g];
         }
-        for (long i = threadIdx.x; i < T * cnt * 8; i += blockDim.x)
-            s_ds[(i / (cnt * 8)) * nsbc * 8 + (i % (cnt * 8))] = ads[(long)s_arow[i / (cnt * 8)] * (a_stride / QK) + sb0 * 8 + (i % (cnt * 8))];
         __syncthreads();
         if (!active) continue;
         for (long sb = lane >> 3; sb < cnt; sb += 4) {
@@ -328,8 +335,7 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const uint4 *__r
                 q4k_scale_min(hdr[r], 2 * c, sc_lo, m_lo);
                 q4k_scale_min(hdr[r], 2 * c + 1, sc_hi, m_hi);
                 const unsigned wl0 = w[r].x & 0x0f0f0f0fu, wl1 = w[r].y & 0x0f0f0f0fu, wl2 = w[r].z & 0x0f0f0f0fu, wl3 = w[r].w & 0x0f0f0f0fu;
-                const unsigned wh0 = (w[r].x >> 4) & 0x0f0f0f0fu, wh1 = (w[r].y >> 4) & 0x0f0f0f0fu,
-                               wh2 = (w[r].z >> 4) & 0x0f0f0f0fu, wh3 = (w[r].w >> 4) & 0x0f0f0f0fu;
+                const unsigned wh0 = w[r].x & 0xf0f0f0f0u, wh1 = w[r].y & 0xf0f0f0f0u, wh2 = w[r].z & 0xf0f0f0f0u, wh3 = w[r].w & 0xf0f0f0f0u;   // 16*q
 #pragma unroll
                 for (int t = 0; t < T; ++t) {
                     const long base = (t * nsbc + sb) * 8;
@@ -340,7 +346,7 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const uint4 *__r
                     sh = dp4a_us(wh1, (int)ah.y, sh), sh = dp4a_us(wh2, (int)ah.z, sh), sh = dp4a_us(wh3, (int)ah.w, sh);
                     const int2 ds_lo = s_ds[base + 2 * c], ds_hi = s_ds[base + 2 * c + 1];
                     const float dy = __int_as_float(ds_lo.x);
-                    const int isum = sc_lo * sl + sc_hi * sh;
+                    const int isum = sc_lo * sl + sc_hi * (sh >> 4);
                     const int msum = h == 0 ? m_lo * ds_lo.y + m_hi * ds_hi.y : 0;   // each sub-block's mins counted once
                     acc[r][t] = fmaf(d * dy, (float)isum, acc[r][t]);
                     acc[r][t] = fmaf(-(dmin * dy), (float)msum, acc[r][t]);
@@ -396,11 +402,11 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_f16_kernel(const __half *__r
     for (long k0 = 0; k0 < k; k0 += kc) {
         const long cnt = min(kc, k - k0);
         if (k0) __syncthreads();
-        for (long i = threadIdx.x; i < T * cnt; i += blockDim.x) {
-            const long t = i / cnt, j = i % cnt;
-            s_a[t * kc + j] = kActF32 ? reinterpret_cast<const float *>(act)[(long)s_arow[t] * a_stride + k0 + j]
-                                      : __half2float(reinterpret_cast<const __half *>(act)[(long)s_arow[t] * a_stride + k0 + j]);
-        }
+#pragma unroll
+        for (int t = 0; t < T; ++t)
+            for (int j = threadIdx.x; j < (int)cnt; j += kWarps * 32)
+                s_a[t * kc + j] = kActF32 ? reinterpret_cast<const float *>(act)[(long)s_arow[t] * a_stride + k0 + j]
+                                          : __half2float(reinterpret_cast<const __half *>(act)[(long)s_arow[t] * a_stride + k0 + j]);
         __syncthreads();
         if (!active) continue;
         if (vec) {

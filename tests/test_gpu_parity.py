@@ -282,3 +282,36 @@ def test_llamafile_mixmul_iqk_host(tb, oracle, golden, typeA):
     m = ~np.isnan(ref)
     H.assert_close(out[m], ref[m])
     tb.weights_cache_clear()
+
+
+# ------------------------------------------------------------------ (c) prefill path (tcgen05) vs oracle
+@pytest.mark.parametrize("wt", H.WEIGHT_TYPES)
+@pytest.mark.parametrize("N,K,T", [(128, 256, 32), (256, 1024, 64), (130, 512, 33), (384, 4096, 512), (1000, 2048, 300), (256, 512, 9)])
+def test_prefill_parity(tb, oracle, wt, N, K, T):
+    W = H.make_weights(wt, N, K, seed=N + T, realistic_q4k=False)
+    X = H.make_acts(T, K, seed=T)
+    H.assert_close(gpu_mul_mat(tb, W, wt, X, N, K), oracle.mul_mat(W, wt, X), f"prefill {H.TYPE_NAME[wt]} N={N} K={K} T={T}")
+
+
+def test_prefill_activation_outliers(tb, oracle):
+    """Token rows with huge / tiny magnitudes: the per-token power-of-two scaling keeps fp16 operands in range."""
+    N, K, T = 256, 1024, 48
+    W = H.make_weights(H.Q4_0, N, K, seed=1)
+    X = H.make_acts(T, K, seed=2)
+    X[3] *= 3.0e5
+    X[7] *= 1.0e-6
+    X[11, 5] = 9.0e4
+    out, ref = gpu_mul_mat(tb, W, H.Q4_0, X, N, K), oracle.mul_mat(W, H.Q4_0, X)
+    for t in range(T):   # per token, since magnitudes differ by 11 orders
+        H.assert_close(out[t], ref[t], f"token {t}")
+
+
+def test_prefill_llama_shape_sampled(tb, oracle):
+    """Llama-3-8B prefill shape at full K and N: every token row, a sample of output columns."""
+    N, K, T = 4096, 4096, 512
+    W = H.make_weights(H.Q4_0, N, K, seed=7)
+    X = H.make_acts(T, K, seed=8)
+    out = gpu_mul_mat(tb, W, H.Q4_0, X, N, K)
+    rb = K // 32 * 18
+    for lo, hi in ((0, 128), (2000, 2100), (N - 64, N)):
+        H.assert_close(out[:, lo:hi], oracle.mul_mat(W[lo * rb:hi * rb], H.Q4_0, X), f"cols {lo}:{hi}")
