@@ -5,7 +5,7 @@ A "step" is one decode token's worth of weight matmuls of Llama-3-8B (BASELINE c
 N=4096/14336/128256 plus the model's other matrices): 32 layers x {wq, wk, wv, wo, gate, up, down} + the
 output projection = 225 GEMVs over 4.22 GB of distinct Q4_0 weights (>> 126 MB L2, so every step streams
 from HBM; no flush needed). Activations are quantized on the device exactly as ggml does before
-llamafile_sgemm (once per distinct input: 129 quantizer launches).
+llamafile_sgemm (inside the GEMV kernels; matrices sharing an input — wq/wk/wv, gate/up — share one launch: 129 launches).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
 
@@ -226,21 +226,29 @@ def run_b200_arm(args):
     gathered = [torch.empty(world, outs[i].numel(), device=dev, dtype=torch.float32) if world > 1 else None for i in range(len(mats))]
     even = all((hi - lo) * world == N for (_, N, lo, hi, K, g, w) in mats)
 
-    def step(with_quant=True, with_gemv=True, with_gather=True):
-        done = set()
-        for i, (name, N, lo, hi, K, grp, w) in enumerate(mats):
-            x, acts = groups[grp]
-            if with_quant and grp not in done:
-                acts.quantize(x, 1)
-                done.add(grp)
-            if with_gemv:
-                tb.mul_mat_acts(w, acts, outs[i])
-            if world > 1 and with_gather and with_gemv:
-                if even:
-                    dist.all_gather_into_tensor(gathered[i], outs[i])
-                else:   # uneven tail shard (vocab 128256 = 1002 tiles): pad to the widest shard
-                    pad = torch.zeros(gathered[i].shape[1], device=dev); pad[: outs[i].numel()] = outs[i].view(-1)
-                    dist.all_gather_into_tensor(gathered[i], pad)
+    # launch schedule of one step: matrices that consume the same activations go out in ONE launch
+    # (tb200_mul_mat_multi: wq/wk/wv, gate/up); every launch quantizes its activations in-kernel.
+    schedule = []
+    for i, m in enumerate(mats):
+        if schedule and schedule[-1][0] == m[5] and len(schedule[-1][1]) < 4 and wtype == Q4_0:
+            schedule[-1][1].append(i)
+        else:
+            schedule.append((m[5], [i]))
+
+    def step(with_gather=True):
+        for grp, idx in schedule:
+            x = groups[grp][0]
+            if len(idx) == 1:
+                tb.mul_mat(mats[idx[0]][6], x, 1, outs[idx[0]])
+            else:
+                tb.mul_mat_multi([mats[i][6] for i in idx], x, 1, [outs[i] for i in idx])
+            if world > 1 and with_gather:
+                for i in idx:
+                    if even:
+                        dist.all_gather_into_tensor(gathered[i], outs[i])
+                    else:   # uneven tail shard (vocab 128256 = 1002 tiles): pad to the widest shard
+                        pad = torch.zeros(gathered[i].shape[1], device=dev); pad[: outs[i].numel()] = outs[i].view(-1)
+                        dist.all_gather_into_tensor(gathered[i], pad)
 
     if world > 1:   # make every shard buffer the same width so all_gather_into_tensor applies
         for i, (name, N, lo, hi, K, grp, w) in enumerate(mats):
@@ -300,9 +308,9 @@ def run_b200_arm(args):
     value = total_step_bytes / (ms_per_step * 1e-3) / 1e9
 
     # ---- roofline: the decode GEMV kernel alone (no quantizers, no collectives)
-    run_gemv, _ = capture(lambda: step(with_quant=False, with_gather=False))
+    run_gemv, _ = capture(lambda: step(with_gather=False))
     ms_gemv = timed(run_gemv, args.steps, args.warmup) / args.steps
-    n_gemv = len(mats)
+    n_gemv = len(schedule)
     peak, peak_src = measured_peak()
     achieved = step_bytes / (ms_gemv * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "gemv_q4_0_kernel" if wtype == Q4_0 else "gemv_q4_K_kernel", "achieved": achieved, "peak": peak,
@@ -316,7 +324,7 @@ def run_b200_arm(args):
 
         def only(idx=idx):
             for i in idx:
-                tb.mul_mat_acts(mats[i][6], groups[mats[i][5]][1], outs[i])
+                tb.mul_mat(mats[i][6], groups[mats[i][5]][0], 1, outs[i])
         run_s, _ = capture(only)
         ms = timed(run_s, max(3, args.steps // 2), 2) / max(3, args.steps // 2)
         b = algorithmic_bytes(wtype, shape[0], shape[1]) * len(idx)
@@ -382,7 +390,7 @@ def run_b200_arm(args):
                 "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int8 dp4a block dots, fp32 accumulate",
                 "data": "synthetic",
-                "config": {"workload": args.workload, "tokens": 1, "layers": layers, "matmuls_per_step": len(mats),
+                "config": {"workload": args.workload, "tokens": 1, "layers": layers, "matmuls_per_step": len(mats), "launches_per_step": len(schedule),
                            "weight_GB_per_step": total_step_bytes / 1e9, "l2": "distinct weights per step exceed L2 (126 MB) 30x; no flush needed",
                            "cuda_graph": graphed, "parallelism": f"row-shard x{world} + NCCL all-gather" if world > 1 else "single GPU",
                            "decode_tokens_per_s": 1e3 / ms_per_step},

@@ -173,7 +173,13 @@ TB200_API int tb200_quantize_q8_K_dev(const float *x, long ldx, void *y, long ro
  * reference does (Q8_0 / Q8_K / F16, or kept F32 for F16 weights when tokens <= 2). Decode kernels for
  * tokens <= TB200_GEMV_MAX_TOKENS, tcgen05 GEMM above. */
 #define TB200_GEMV_MAX_TOKENS 8
+#define TB200_GEMV_MAX_MATS 4
 TB200_API int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens, float *out, long ldo);
+
+/* Decode only (tokens <= TB200_GEMV_MAX_TOKENS): n <= TB200_GEMV_MAX_MATS weight matrices of the same type and K that
+ * consume the SAME activations (wq/wk/wv, gate/up) in one launch; out[m][t*ldo[m] + i]. */
+TB200_API int tb200_mul_mat_multi(int n, const tb200_weights *const *w, const float *x, long ldx, long tokens, float *const *out,
+                                  const long *ldo);
 
 /* The same in two steps, for callers that feed one activation tensor to several weight matrices (wq/wk/wv,
  * gate/up): quantize once into a resident activation object, then run any number of matmuls against it. */

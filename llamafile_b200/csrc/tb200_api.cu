@@ -231,6 +231,8 @@ int run_matmul(tb200_ctx *c, const tb200_weights *w, long row0, long nrows, cons
         return tb200_launch_gemm(c, w, row0, nrows, aq, ads, af, a_stride, tokens, out, ldo);
     for (long t0 = 0; t0 < tokens; t0 += TB200_GEMV_MAX_TOKENS) {
         tb200_gemv_args a;
+        memset(&a, 0, sizeof(a));
+        a.nmat = 1;
         a.w = w, a.row0 = row0, a.nrows = nrows;
         a.aq = aq ? aq + t0 * a_stride : nullptr;
         a.ads = ads ? ads + t0 * (a_stride / QK) : nullptr;
@@ -263,12 +265,45 @@ int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens,
         if ((rc = tb200_launch_f32_to_f16(c, x, ldx, tokens, w->k, p.h))) return rc;
         return run_matmul(c, w, 0, w->rows, nullptr, nullptr, p.h, 0, w->k, tokens, out, ldo);
     }
+    if (w->type == TB200_TYPE_Q4_0 && tokens <= TB200_GEMV_MAX_TOKENS) {
+        // decode: one launch; every CTA quantizes the activations itself (same arithmetic, bit-exact)
+        const tb200_weights *ws[1] = {w};
+        float *outs[1] = {out};
+        const long ldos[1] = {ldo};
+        return tb200_mul_mat_multi(1, ws, x, ldx, tokens, outs, ldos);
+    }
     Planar p = carve(c, w->type, tokens, w->k, 0, nullptr);
     if (!p.q) return TB200_ERR_CUDA;
     if (w->type == TB200_TYPE_Q4_K) rc = tb200_launch_quantize_q8_K(c, x, ldx, tokens, w->k, nullptr, p.q, p.ds);
     else rc = tb200_launch_quantize_q8_0(c, x, ldx, tokens, w->k, nullptr, p.q, p.ds);
     if (rc) return rc;
     return run_matmul(c, w, 0, w->rows, p.q, p.ds, nullptr, 0, w->k, tokens, out, ldo);
+}
+
+int tb200_mul_mat_multi(int n, const tb200_weights *const *w, const float *x, long ldx, long tokens, float *const *out, const long *ldo) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!c) return TB200_ERR_NO_DEVICE;
+    if (n < 1 || n > TB200_GEMV_MAX_MATS || !w || !out || !ldo || tokens < 0) { tb200_set_error("mul_mat_multi: bad arguments"); return TB200_ERR_INVALID; }
+    for (int m = 0; m < n; ++m)
+        if (!w[m] || w[m]->type != w[0]->type || w[m]->k != w[0]->k || ldo[m] < w[m]->rows || ldx < w[m]->k) {
+            tb200_set_error("mul_mat_multi: matrices must share type and K");
+            return TB200_ERR_INVALID;
+        }
+    if (tokens == 0) return TB200_OK;
+    if (w[0]->type != TB200_TYPE_Q4_0 || tokens > TB200_GEMV_MAX_TOKENS) {   // other types / prefill: one matmul each
+        for (int m = 0; m < n; ++m) {
+            const int rc = tb200_mul_mat(w[m], x, ldx, tokens, out[m], ldo[m]);
+            if (rc) return rc;
+        }
+        return TB200_OK;
+    }
+    tb200_gemv_args a;
+    memset(&a, 0, sizeof(a));
+    a.w = w[0], a.row0 = 0, a.nrows = w[0]->rows, a.out = out[0], a.ldo = ldo[0];
+    a.nmat = n;
+    for (int m = 1; m < n; ++m) a.w_more[m - 1] = w[m], a.out_more[m - 1] = out[m], a.ldo_more[m - 1] = ldo[m];
+    a.xf = x, a.ldx = ldx, a.a_stride = w[0]->k, a.tokens = tokens;
+    return tb200_launch_gemv(c, a);
 }
 
 // ---- resident activations ---------------------------------------------------------------------------

@@ -14,6 +14,8 @@
 // row so every warp load is one contiguous 512-byte segment. Activations (quantized once per call by
 // tb200_quantize.cu) are staged in shared memory, split so that lane-consecutive reads are
 // bank-conflict free. Weights are read exactly once -> ld.global.nc.L1::no_allocate.
+#include <string.h>
+
 #include "tb200_common.cuh"
 
 namespace {
@@ -28,14 +30,65 @@ constexpr int kWarps = 8;   // warps per CTA
 // U x R independent 16-byte weight loads are issued per lane before anything is consumed; the first batch is
 // issued before the activations are even staged (weights are immutable, so it also precedes pdl_wait()), which
 // folds the weight-fetch latency and the activation-fetch latency of these short kernels into one.
-template <int T, int R>
-__global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__restrict__ qs, const __half *__restrict__ sc,
-                                                                long nb, long nbc, long row0, long nrows,
-                                                                const int8_t *__restrict__ aq, const int2 *__restrict__ ads,
-                                                                long a_stride, float *__restrict__ out, long ldo,
-                                                                const tb200_gemv_item *__restrict__ items) {
+// One launch can serve up to kMaxMats weight matrices that share K and the activations (wq/wk/wv, gate/up): the
+// grid is the concatenation of their row tiles. With kFused the CTA quantizes the fp32 activations itself
+// (quantize_row_q8_0 arithmetic, bit-exact) instead of reading a pre-quantized planar copy.
+constexpr int kMaxMats = TB200_GEMV_MAX_MATS;
+struct GemvQ4Args {
+    int nmat;
+    int cta_begin[kMaxMats + 1];
+    const uint4 *qs[kMaxMats];
+    const __half *sc[kMaxMats];
+    long row0[kMaxMats], nrows[kMaxMats];
+    float *out[kMaxMats];
+    long ldo[kMaxMats];
+    long nb, nbc;
+    const int8_t *aq; const int2 *ads; long a_stride;   // planar activations
+    const float *xf; long ldx;                          // fused: fp32 activations
+    const tb200_gemv_item *items;
+};
+
+// quantize_row_q8_0 of one 32-block (ggml-quants.c:940-990), same arithmetic as tb200_quantize.cu
+__device__ __forceinline__ void quantize_block_q8_0(const float *__restrict__ x, bool vec, uint4 &lo, uint4 &hi, int2 &ds) {
+    float v[32];
+    if (vec) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float4 f = reinterpret_cast<const float4 *>(x)[i];
+            v[4 * i] = f.x, v[4 * i + 1] = f.y, v[4 * i + 2] = f.z, v[4 * i + 3] = f.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = x[i];
+    }
+    float amax = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) amax = fmaxf(amax, fabsf(v[i]));
+    const float d = __fdiv_rn(amax, 127.f);
+    const float id = (amax != 0.0f) ? __fdiv_rn(127.f, amax) : 0.0f;
+    uint32_t pk[8];
+    int sum = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        int q[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float p = __fmul_rn(v[4 * i + j], id);
+            q[j] = (!(p >= -2147483648.f && p < 2147483648.f)) ? -128 : max(-128, min(127, __float2int_rn(p)));
+            sum += q[j];
+        }
+        pk[i] = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
+    }
+    lo = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    hi = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    ds = make_int2(__float_as_int(__half2float(__float2half_rn(d))), sum);
+}
+
+template <int T, int R, bool kFused>
+__global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_constant__ GemvQ4Args A) {
     constexpr int U = (T * R <= 4) ? 4 : 2;   // batch depth: blocks per lane per row in flight
     extern __shared__ __align__(16) uint8_t smem[];
+    const long nb = A.nb, nbc = A.nbc;
     uint4 *s_lo = reinterpret_cast<uint4 *>(smem);
     uint4 *s_hi = s_lo + T * nbc;
     int2 *s_ds = reinterpret_cast<int2 *>(s_hi + T * nbc);
@@ -43,8 +96,15 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
 
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const long r_base = ((long)blockIdx.x * kWarps + warp) * R;   // first row of this warp (relative to row0)
+    int mat = 0;
+#pragma unroll
+    for (int m = 1; m < kMaxMats; ++m)
+        if (m < A.nmat && (int)blockIdx.x >= A.cta_begin[m]) mat = m;
+    const long nrows = A.nrows[mat];
+    const long r_base = ((long)((int)blockIdx.x - A.cta_begin[mat]) * kWarps + warp) * R;   // first row of this warp (relative to row0)
     const bool active = r_base < nrows;
+    const uint4 *qs = A.qs[mat];
+    const __half *sc = A.sc[mat];
 
     uint4 w[U][R];
     __half dh[U][R];
@@ -76,13 +136,13 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
     int ntok = T, orow[T];
 #pragma unroll
     for (int t = 0; t < T; ++t) orow[t] = t;
-    if (!items) {
-        set_rows(row0);
+    if (!A.items) {
+        set_rows(A.row0[mat]);
         if (active) load_batch(0, min(nbc, nb));   // first batch in flight before the activations are touched
     }
     pdl_wait();
-    if (items) {
-        const tb200_gemv_item &it = items[blockIdx.y];
+    if (A.items) {
+        const tb200_gemv_item &it = A.items[blockIdx.y];
         ntok = it.ntok;
         if (ntok == 0) return;   // CTA-uniform
         set_rows(it.row0);
@@ -102,13 +162,27 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
     for (long b0 = 0; b0 < nb; b0 += nbc) {   // K chunks of nbc blocks (one chunk unless T*K is huge)
         const long cnt = min(nbc, nb - b0);
         if (b0) __syncthreads();
-        // stage activations: 16-byte piece g of token t -> plane (g&1), index g>>1 (no div/mod: T is compile-time)
-        {
-            const int cnt2 = (int)cnt * 2, nbc_i = (int)nbc;
+        const int nbc_i = (int)nbc;
+        if (kFused) {
+            // quantize this chunk of the fp32 activations: one thread per 32-block
+            const bool vec = (((uintptr_t)A.xf) & 15) == 0 && (A.ldx & 3) == 0;
 #pragma unroll
             for (int t = 0; t < T; ++t) {
-                const uint4 *src = reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + b0 * 32);
-                const int2 *dsrc = ads + (long)s_arow[t] * (a_stride / QK) + b0;
+                const float *xr = A.xf + (long)s_arow[t] * A.ldx + b0 * QK;
+                for (int g = threadIdx.x; g < (int)cnt; g += kWarps * 32) {
+                    uint4 lo, hi;
+                    int2 ds;
+                    quantize_block_q8_0(xr + g * QK, vec, lo, hi, ds);
+                    s_lo[t * nbc_i + g] = lo, s_hi[t * nbc_i + g] = hi, s_ds[t * nbc_i + g] = ds;
+                }
+            }
+        } else {
+            // stage activations: 16-byte piece g of token t -> plane (g&1), index g>>1 (no div/mod: T is compile-time)
+            const int cnt2 = (int)cnt * 2;
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const uint4 *src = reinterpret_cast<const uint4 *>(A.aq + (long)s_arow[t] * A.a_stride + b0 * 32);
+                const int2 *dsrc = A.ads + (long)s_arow[t] * (A.a_stride / QK) + b0;
                 for (int g = threadIdx.x; g < cnt2; g += kWarps * 32) ((g & 1) ? s_hi : s_lo)[t * nbc_i + (g >> 1)] = src[g];
                 for (int g = threadIdx.x; g < (int)cnt; g += kWarps * 32) s_ds[t * nbc_i + g] = dsrc[g];
             }
@@ -156,6 +230,8 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const uint4 *__r
         }
     }
     if (!active) return;
+    float *out = A.out[mat];
+    const long ldo = A.ldo[mat];
 #pragma unroll
     for (int r = 0; r < R; ++r)
 #pragma unroll
@@ -513,9 +589,29 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         if (nbc >= nb) nbc = nb;
         const size_t smem = (size_t)T * nbc * 40;
         if (w->type == TB200_TYPE_Q4_0) {
-            if ((rc = set_smem(gemv_q4_0_kernel<T, R>, smem))) return rc;
-            TB_CUDA(tb200_launch(gemv_q4_0_kernel<T, R>, grid, dim3(kWarps * 32), smem, c->stream, (const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,
-                                                                          a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items));
+            GemvQ4Args ka;
+            memset(&ka, 0, sizeof(ka));
+            ka.nmat = a.nmat > 0 ? a.nmat : 1;
+            int ctas = 0;
+            for (int m = 0; m < ka.nmat; ++m) {
+                const tb200_weights *wm = m == 0 ? w : a.w_more[m - 1];
+                const long nr = m == 0 ? a.nrows : wm->rows;
+                ka.cta_begin[m] = ctas;
+                ctas += (int)((nr + kWarps * R - 1) / (kWarps * R));
+                ka.qs[m] = (const uint4 *)wm->qs, ka.sc[m] = (const __half *)wm->sc;
+                ka.row0[m] = m == 0 ? a.row0 : 0, ka.nrows[m] = nr;
+                ka.out[m] = m == 0 ? a.out : a.out_more[m - 1], ka.ldo[m] = m == 0 ? a.ldo : a.ldo_more[m - 1];
+            }
+            ka.cta_begin[ka.nmat] = ctas;
+            ka.nb = nb, ka.nbc = nbc, ka.aq = a.aq, ka.ads = a.ads, ka.a_stride = a.a_stride, ka.xf = a.xf, ka.ldx = a.ldx, ka.items = a.items;
+            const dim3 g2((unsigned)ctas, grid.y);
+            if (a.xf) {
+                if ((rc = set_smem(gemv_q4_0_kernel<T, R, true>, smem))) return rc;
+                TB_CUDA(tb200_launch(gemv_q4_0_kernel<T, R, true>, g2, dim3(kWarps * 32), smem, c->stream, ka));
+            } else {
+                if ((rc = set_smem(gemv_q4_0_kernel<T, R, false>, smem))) return rc;
+                TB_CUDA(tb200_launch(gemv_q4_0_kernel<T, R, false>, g2, dim3(kWarps * 32), smem, c->stream, ka));
+            }
         } else {
             if ((rc = set_smem(gemv_q8_0_kernel<T, R>, smem))) return rc;
             TB_CUDA(tb200_launch(gemv_q8_0_kernel<T, R>, grid, dim3(kWarps * 32), smem, c->stream, (const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,
@@ -557,7 +653,9 @@ template <int T>
 int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
     // rows per warp: 2 keeps >= 8 x 16-byte weight loads in flight per lane at K = 4096 while leaving
     // enough CTAs (N/8) to cover 148 SMs; small matrices fall back to 1 row per warp.
-    if (a.nrows < (long)c->sm_count * kWarps * 4) return launch_TR<T, 1>(c, a);
+    long total = a.nrows;
+    for (int m = 1; m < a.nmat; ++m) total += a.w_more[m - 1]->rows;
+    if (total < (long)c->sm_count * kWarps * 4) return launch_TR<T, 1>(c, a);
     return launch_TR<T, 2>(c, a);
 }
 

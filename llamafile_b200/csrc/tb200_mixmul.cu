@@ -8,6 +8,8 @@
 // launch serves all experts: decode kernels for small routing counts, tcgen05 GEMM for prefill.
 // Plan entries outside [0, experts) match no expert and leave their result row untouched, as in the
 // reference's loop.
+#include <string.h>
+
 #include "tb200_common.cuh"
 
 int tb200_run_matmul(tb200_ctx *c, const tb200_weights *w, long row0, long nrows, const int8_t *aq, const int2 *ads, const void *af,
@@ -66,6 +68,8 @@ template <int G>
 int grouped(tb200_ctx *c, const tb200_weights *w, long rows, const int8_t *aq, const int2 *ads, const void *af, long k,
             const tb200_gemv_item *items, long n_items, float *result) {
     tb200_gemv_args a;
+    memset(&a, 0, sizeof(a));
+    a.nmat = 1;
     a.w = w, a.row0 = 0, a.nrows = rows, a.aq = aq, a.ads = ads, a.af = af, a.af_is_f32 = 0, a.a_stride = k;
     a.tokens = G, a.out = result, a.ldo = rows, a.items = items, a.n_items = n_items;
     return tb200_launch_gemv(c, a);

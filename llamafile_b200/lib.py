@@ -41,6 +41,7 @@ def lib() -> C.CDLL:
         "tb200_weights_free": (None, [vp]), "tb200_weights_bytes": (sz, [vp]),
         "tb200_quantize_q8_0_dev": (i, [vp, l, vp, l, l]), "tb200_quantize_q8_K_dev": (i, [vp, l, vp, l, l]),
         "tb200_mul_mat": (i, [vp, vp, l, l, vp, l]), "tb200_sgemm_dev": (i, [vp, l, vp, l, i, vp, l]),
+        "tb200_mul_mat_multi": (i, [i, vp, vp, l, l, vp, vp]),
         "tb200_acts_create": (vp, [i, l, l]), "tb200_acts_quantize": (i, [vp, vp, l, l]),
         "tb200_mul_mat_acts": (i, [vp, vp, vp, l]), "tb200_acts_free": (None, [vp]),
         "tb200_blockdot_dev": (i, [vp, vp, i, vp]), "tb200_mixmul_dev": (i, [vp, i, vp, i, vp, i, l, vp]),
@@ -158,6 +159,15 @@ class Acts:
 
 def mul_mat_acts(w: Weights, a: Acts, out, ldo: int | None = None):
     _check(lib().tb200_mul_mat_acts(w.handle, a.handle, _ptr(out), ldo or w.rows), "mul_mat_acts")
+
+
+def mul_mat_multi(ws, x, tokens: int, outs, ldx: int | None = None):
+    """Decode: several weight matrices sharing K and the activations in ONE launch (wq/wk/wv, gate/up)."""
+    n = len(ws)
+    W = (C.c_void_p * n)(*[w.handle for w in ws])
+    O = (C.c_void_p * n)(*[_ptr(o) for o in outs])
+    Ld = (C.c_long * n)(*[w.rows for w in ws])
+    _check(lib().tb200_mul_mat_multi(n, W, _ptr(x), ldx or ws[0].k, tokens, O, Ld), "mul_mat_multi")
 
 
 def sgemm_dev(w: Weights, n: int, B, ldb: int, Btype: int, Cout, ldc: int) -> bool:

@@ -315,3 +315,42 @@ def test_prefill_llama_shape_sampled(tb, oracle):
     rb = K // 32 * 18
     for lo, hi in ((0, 128), (2000, 2100), (N - 64, N)):
         H.assert_close(out[:, lo:hi], oracle.mul_mat(W[lo * rb:hi * rb], H.Q4_0, X), f"cols {lo}:{hi}")
+
+
+# ------------------------------------------------------------------ decode API variants
+@pytest.mark.parametrize("wt", H.WEIGHT_TYPES)
+@pytest.mark.parametrize("T", [1, 3, 8])
+def test_resident_activations_api(tb, oracle, wt, T):
+    """tb200_acts_quantize + tb200_mul_mat_acts (planar activations) == one-shot tb200_mul_mat == oracle."""
+    K = 1024
+    X = H.make_acts(T, K, seed=T)
+    acts = tb.Acts(wt, K, 8)
+    xd = dev(X)
+    acts.quantize(xd, T)
+    for N in (96, 320):
+        W = H.make_weights(wt, N, K, seed=N, realistic_q4k=False)
+        w = tb.Weights(W, wt, N, K)
+        out = torch.full((T, N), float("nan"), device="cuda")
+        tb.mul_mat_acts(w, acts, out)
+        tb.synchronize()
+        H.assert_close(out.cpu().numpy(), oracle.mul_mat(W, wt, X))
+        w.free()
+    acts.free()
+
+
+@pytest.mark.parametrize("wt", [H.Q4_0, H.Q4_K])
+@pytest.mark.parametrize("T", [1, 2, 8])
+def test_mul_mat_multi(tb, oracle, wt, T):
+    """Several matrices sharing K and the activations in one launch (QKV / gate-up); uneven row counts."""
+    K = 2048
+    X = H.make_acts(T, K, seed=T + 40)
+    shapes = [520, 128, 130]
+    Ws = [H.make_weights(wt, n, K, seed=n, realistic_q4k=False) for n in shapes]
+    ws = [tb.Weights(W, wt, n, K) for W, n in zip(Ws, shapes)]
+    outs = [torch.full((T, n), float("nan"), device="cuda") for n in shapes]
+    tb.mul_mat_multi(ws, dev(X), T, outs)
+    tb.synchronize()
+    for W, n, o in zip(Ws, shapes, outs):
+        H.assert_close(o.cpu().numpy(), oracle.mul_mat(W, wt, X), f"multi n={n}")
+    for w in ws:
+        w.free()
