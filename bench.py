@@ -5,7 +5,8 @@ A "step" is one decode token's worth of weight matmuls of Llama-3-8B (BASELINE c
 N=4096/14336/128256 plus the model's other matrices): 32 layers x {wq, wk, wv, wo, gate, up, down} + the
 output projection = 225 GEMVs over 4.22 GB of distinct Q4_0 weights (>> 126 MB L2, so every step streams
 from HBM; no flush needed). Activations are quantized on the device exactly as ggml does before
-llamafile_sgemm (inside the GEMV kernels; matrices sharing an input — wq/wk/wv, gate/up — share one launch: 129 launches).
+llamafile_sgemm (one quantizer launch per distinct input; matrices sharing an input — wq/wk/wv, gate/up — share one
+GEMV launch: 129 + 129 launches).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
 
@@ -13,7 +14,7 @@ value   : algorithmic GB/s, inputs resident in HBM, the whole step replayed from
 e2e     : the same step through the reference-facing C-ABI entry point llamafile_sgemm() with HOST buffers
           (pinned): Q8_0 activations H2D and fp32 results D2H inside the timed region, weights resident
           (uploaded once at first use, as the mmap'd GGUF would be).
-roofline: the decode GEMV kernel alone (graph of the 225 GEMV launches, no quantizers), CUDA events.
+roofline: the decode GEMV kernel alone (graph of the step's 129 GEMV launches, no quantizers), CUDA events.
 cpu_baseline / --impl reference: the reference's own CPU tinyBLAS/iqk path (oracle/_ref) on the host cores.
 N > 1   : every weight matrix row-sharded over the ranks, outputs all-gathered with NCCL.
 """
@@ -235,13 +236,12 @@ def run_b200_arm(args):
         else:
             schedule.append((m[5], [i]))
 
-    def step(with_gather=True):
+    def step(with_gather=True, with_quant=True):
         for grp, idx in schedule:
-            x = groups[grp][0]
-            if len(idx) == 1:
-                tb.mul_mat(mats[idx[0]][6], x, 1, outs[idx[0]])
-            else:
-                tb.mul_mat_multi([mats[i][6] for i in idx], x, 1, [outs[i] for i in idx])
+            x, acts = groups[grp]
+            if with_quant:
+                acts.quantize(x, 1)
+            tb.mul_mat_acts_multi([mats[i][6] for i in idx], acts, [outs[i] for i in idx])
             if world > 1 and with_gather:
                 for i in idx:
                     if even:
@@ -308,7 +308,7 @@ def run_b200_arm(args):
     value = total_step_bytes / (ms_per_step * 1e-3) / 1e9
 
     # ---- roofline: the decode GEMV kernel alone (no quantizers, no collectives)
-    run_gemv, _ = capture(lambda: step(with_gather=False))
+    run_gemv, _ = capture(lambda: step(with_gather=False, with_quant=False))
     ms_gemv = timed(run_gemv, args.steps, args.warmup) / args.steps
     n_gemv = len(schedule)
     peak, peak_src = measured_peak()
@@ -324,7 +324,7 @@ def run_b200_arm(args):
 
         def only(idx=idx):
             for i in idx:
-                tb.mul_mat(mats[i][6], groups[mats[i][5]][0], 1, outs[i])
+                tb.mul_mat_acts(mats[i][6], groups[mats[i][5]][1], outs[i])
         run_s, _ = capture(only)
         ms = timed(run_s, max(3, args.steps // 2), 2) / max(3, args.steps // 2)
         b = algorithmic_bytes(wtype, shape[0], shape[1]) * len(idx)

@@ -187,6 +187,7 @@ typedef struct tb200_acts tb200_acts;
 TB200_API tb200_acts *tb200_acts_create(int weight_type, long k, long max_tokens);
 TB200_API int tb200_acts_quantize(tb200_acts *a, const float *x, long ldx, long tokens);
 TB200_API int tb200_mul_mat_acts(const tb200_weights *w, const tb200_acts *a, float *out, long ldo);
+TB200_API int tb200_mul_mat_acts_multi(int n, const tb200_weights *const *w, const tb200_acts *a, float *const *out, const long *ldo);
 TB200_API void tb200_acts_free(tb200_acts *a);
 
 /* llamafile_sgemm on device pointers with pre-quantized activations B (GGUF blocks of Btype, ldb in

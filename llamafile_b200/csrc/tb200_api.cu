@@ -265,13 +265,6 @@ int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens,
         if ((rc = tb200_launch_f32_to_f16(c, x, ldx, tokens, w->k, p.h))) return rc;
         return run_matmul(c, w, 0, w->rows, nullptr, nullptr, p.h, 0, w->k, tokens, out, ldo);
     }
-    if (w->type == TB200_TYPE_Q4_0 && tokens <= TB200_GEMV_MAX_TOKENS) {
-        // decode: one launch; every CTA quantizes the activations itself (same arithmetic, bit-exact)
-        const tb200_weights *ws[1] = {w};
-        float *outs[1] = {out};
-        const long ldos[1] = {ldo};
-        return tb200_mul_mat_multi(1, ws, x, ldx, tokens, outs, ldos);
-    }
     Planar p = carve(c, w->type, tokens, w->k, 0, nullptr);
     if (!p.q) return TB200_ERR_CUDA;
     if (w->type == TB200_TYPE_Q4_K) rc = tb200_launch_quantize_q8_K(c, x, ldx, tokens, w->k, nullptr, p.q, p.ds);
@@ -297,12 +290,17 @@ int tb200_mul_mat_multi(int n, const tb200_weights *const *w, const float *x, lo
         }
         return TB200_OK;
     }
+    // quantize once (one launch), then ONE decode launch over the concatenated row tiles of all n matrices
+    Planar p = carve(c, TB200_TYPE_Q4_0, tokens, w[0]->k, 0, nullptr);
+    if (!p.q) return TB200_ERR_CUDA;
+    int rc = tb200_launch_quantize_q8_0(c, x, ldx, tokens, w[0]->k, nullptr, p.q, p.ds);
+    if (rc) return rc;
     tb200_gemv_args a;
     memset(&a, 0, sizeof(a));
     a.w = w[0], a.row0 = 0, a.nrows = w[0]->rows, a.out = out[0], a.ldo = ldo[0];
     a.nmat = n;
     for (int m = 1; m < n; ++m) a.w_more[m - 1] = w[m], a.out_more[m - 1] = out[m], a.ldo_more[m - 1] = ldo[m];
-    a.xf = x, a.ldx = ldx, a.a_stride = w[0]->k, a.tokens = tokens;
+    a.aq = p.q, a.ads = p.ds, a.a_stride = w[0]->k, a.tokens = tokens;
     return tb200_launch_gemv(c, a);
 }
 
@@ -361,6 +359,28 @@ int tb200_mul_mat_acts(const tb200_weights *w, const tb200_acts *a, float *out, 
         return run_matmul(c, w, 0, w->rows, nullptr, nullptr, a->h, 0, a->k, a->tokens, out, ldo);
     }
     return run_matmul(c, w, 0, w->rows, a->q, a->ds, nullptr, 0, a->k, a->tokens, out, ldo);
+}
+
+int tb200_mul_mat_acts_multi(int n, const tb200_weights *const *w, const tb200_acts *a, float *const *out, const long *ldo) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!c) return TB200_ERR_NO_DEVICE;
+    if (n < 1 || n > TB200_GEMV_MAX_MATS || !w || !a || !out || !ldo) { tb200_set_error("mul_mat_acts_multi: bad arguments"); return TB200_ERR_INVALID; }
+    bool one_launch = w[0] && w[0]->type == TB200_TYPE_Q4_0 && a->tokens <= TB200_GEMV_MAX_TOKENS && a->wtype != TB200_TYPE_F16 && a->wtype != TB200_TYPE_Q4_K;
+    for (int m = 0; m < n && one_launch; ++m) one_launch = w[m] && w[m]->type == TB200_TYPE_Q4_0 && w[m]->k == a->k && ldo[m] >= w[m]->rows;
+    if (!one_launch) {
+        for (int m = 0; m < n; ++m) {
+            const int rc = tb200_mul_mat_acts(w[m], a, out[m], ldo[m]);
+            if (rc) return rc;
+        }
+        return TB200_OK;
+    }
+    if (a->tokens == 0) return TB200_OK;
+    tb200_gemv_args g;
+    memset(&g, 0, sizeof(g));
+    g.w = w[0], g.row0 = 0, g.nrows = w[0]->rows, g.out = out[0], g.ldo = ldo[0], g.nmat = n;
+    for (int m = 1; m < n; ++m) g.w_more[m - 1] = w[m], g.out_more[m - 1] = out[m], g.ldo_more[m - 1] = ldo[m];
+    g.aq = a->q, g.ads = a->ds, g.a_stride = a->k, g.tokens = a->tokens;
+    return tb200_launch_gemv(c, g);
 }
 
 void tb200_acts_free(tb200_acts *a) {

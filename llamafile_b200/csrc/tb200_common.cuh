@@ -99,10 +99,8 @@ struct tb200_gemv_args {
     long tokens;
     float *out; long ldo;
     const tb200_gemv_item *items; long n_items;   // optional grouped mode (device array); tokens = template T
-    // optional (Q4_0): more matrices sharing K and the activations, served by the same launch; fp32 activations to
-    // quantize inside the kernel instead of (aq, ads)
+    // optional (Q4_0): more matrices sharing K and the activations, served by the same launch
     int nmat; const tb200_weights *w_more[TB200_GEMV_MAX_MATS - 1]; float *out_more[TB200_GEMV_MAX_MATS - 1]; long ldo_more[TB200_GEMV_MAX_MATS - 1];
-    const float *xf; long ldx;
 };
 int tb200_launch_gemv(tb200_ctx *c, const tb200_gemv_args &a);
 int tb200_launch_blockdot(tb200_ctx *c, const tb200_weights *w, const int8_t *aq, const int2 *ads, int32_t *out);

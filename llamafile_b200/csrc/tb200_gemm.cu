@@ -160,6 +160,11 @@ struct GemmParams {
     long k, tokens;
     const float *colscale; // [tokens] 2^e_t
     float *out; long ldo;
+    // grouped (mixmul) mode: blockIdx.y indexes a device-built tile table {weight row offset, first B' row, rows in tile, -};
+    // rowmap[t] = output row of B' row t
+    const int4 *tiles;
+    const int *rowmap;
+    long n_tiles;
 };
 
 // ------------------------------------------------------------------------------------------------ the kernel
@@ -180,8 +185,15 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(accum_full + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const long tile_row = (long)blockIdx.x * BM, tile_tok = (long)blockIdx.y * BN;
+    long tile_row = (long)blockIdx.x * BM, tile_tok = (long)blockIdx.y * BN;
+    long w_row0 = p.row0, tok_end = p.tokens;
     const int kt = (int)(p.k / BK);
+    if (p.tiles) {   // CTA-uniform; the table is written by a predecessor kernel
+        pdl_wait();
+        const int4 tl = p.tiles[blockIdx.y];
+        if (tl.z == 0) return;
+        w_row0 = tl.x, tile_tok = tl.y, tok_end = tl.y + tl.z;
+    }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
@@ -213,10 +225,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
                 if (i >= kStages) mbar_wait(&empty[s], ((i / kStages) - 1) & 1);
                 if (kType == TB200_TYPE_F16) {
                     mbar_expect_tx(&full_a[s], kABytes);   // F16 weights: TMA writes the swizzled A tile directly
-                    tma_load_2d(sA + s * kABytes, &map_w, &full_a[s], i * BK, (int)(p.row0 + tile_row));
+                    tma_load_2d(sA + s * kABytes, &map_w, &full_a[s], i * BK, (int)(w_row0 + tile_row));
                 } else {
                     mbar_expect_tx(&full_p[s], kPackedBytes);
-                    tma_load_2d(sP + s * kPackedBytes, &map_w, &full_p[s], i * (kType == TB200_TYPE_Q8_0 ? BK : BK / 2), (int)(p.row0 + tile_row));
+                    tma_load_2d(sP + s * kPackedBytes, &map_w, &full_p[s], i * (kType == TB200_TYPE_Q8_0 ? BK : BK / 2), (int)(w_row0 + tile_row));
                 }
                 mbar_expect_tx(&full_b[s], kBBytes);
                 tma_load_2d(sB + s * kBBytes, &map_b, &full_b[s], i * BK, (int)tile_tok);
@@ -244,7 +256,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
         // ===== dequantisers =====
         const int tid = threadIdx.x - 128;            // 0..255
         const int row = tid >> 1, half = tid & 1;
-        const long grow = p.row0 + min(tile_row + row, p.nrows - 1);   // clamp rows past the matrix end (their outputs are masked)
+        const long grow = w_row0 + min(tile_row + row, p.nrows - 1);   // clamp rows past the matrix end (their outputs are masked)
         if (kType != TB200_TYPE_F16) {
             for (int i = 0; i < kt; ++i) {
                 const int s = i % kStages;
@@ -308,7 +320,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
                 const long t = tile_tok + ch * 32 + j;
-                if (t < p.tokens && out_row < p.nrows) p.out[t * p.ldo + out_row] = __uint_as_float(v[j]) * p.colscale[t];
+                if (t < tok_end && out_row < p.nrows) p.out[(p.rowmap ? (long)p.rowmap[t] : t) * p.ldo + out_row] = __uint_as_float(v[j]) * p.colscale[t];
             }
         }
     }
@@ -332,13 +344,17 @@ __device__ __forceinline__ int perm_pos(int perm, int kk) {   // position of ele
     return w * 8 + slot;
 }
 
+// Grouped mode: B' row t is the activation row of pair order[t] (expert-sorted), i.e. row (pair / thinkers) * tasks + (pair % thinkers) % tasks.
 __global__ void __launch_bounds__(256) prep_acts_kernel(const int8_t *__restrict__ aq, const int2 *__restrict__ ads, long a_stride, long k,
-                                                        int perm, __half *__restrict__ bp, float *__restrict__ colscale) {
+                                                        int perm, __half *__restrict__ bp, float *__restrict__ colscale,
+                                                        const int *__restrict__ order, int thinkers, int tasks) {
     pdl_launch_dependents();
     pdl_wait();
     const long t = blockIdx.x;
-    const int2 *ds = ads + t * (a_stride / QK);
-    const int8_t *q = aq + t * a_stride;
+    long src = t;
+    if (order) { const int pr = order[t]; src = (long)(pr / thinkers) * tasks + (pr % thinkers) % tasks; }
+    const int2 *ds = ads + src * (a_stride / QK);
+    const int8_t *q = aq + src * a_stride;
     __shared__ float s_max[8];
     float bound = 0.f;
     for (long b = threadIdx.x; b < k / QK; b += blockDim.x) bound = fmaxf(bound, fabsf(__int_as_float(ds[b].x)) * 127.f);
@@ -424,18 +440,19 @@ int launch_cfg(tb200_ctx *c, const CUtensorMap &mw, const CUtensorMap &mb, const
         TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
-    const dim3 grid((unsigned)((p.nrows + BM - 1) / BM), (unsigned)((p.tokens + BN - 1) / BN));
+    const dim3 grid((unsigned)((p.nrows + BM - 1) / BM), p.tiles ? (unsigned)p.n_tiles : (unsigned)((p.tokens + BN - 1) / BN));
     TB_CUDA(tb200_launch(kern, grid, dim3(kThreads), smem, c->stream, mw, mb, p));
     return TB200_OK;
 }
 
 template <int kType>
-int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long tokens, void *bp, GemmParams &p) {
+int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long tokens, void *bp, GemmParams &p, int force_bn = 0) {
     // token tile: as wide as the batch allows (fewer re-dequantisations of the same weight tile), but keep >= ~1 wave of CTAs
     const long row_tiles = (p.nrows + BM - 1) / BM;
     int bn = 256;
     while (bn > 32 && (tokens <= bn / 2 || row_tiles * ((tokens + bn - 1) / bn) < c->sm_count)) bn >>= 1;
     if (tokens > 128 && bn < 128) bn = 128;
+    if (force_bn) bn = force_bn;
     CUtensorMap mb;
     if (!make_map_2d(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, bp, (uint64_t)w->k, (uint64_t)tokens, (uint64_t)w->k * 2, BK, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B))
         return TB200_ERR_CUDA;
@@ -447,6 +464,115 @@ int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long toke
     }
 }
 
+
+// ---- grouped (mixmul) support ------------------------------------------------------------------------------------
+// One CTA; warp e scans all (token, thinker) pairs in order (same stable order as the reference's build_row_pointers,
+// tinyblas_cpu_mixmul.inc:297-320): order[] = pairs sorted by expert, tiles[] = {expert row offset, first sorted row, count}.
+__global__ void __launch_bounds__(1024) build_groups_kernel(const int32_t *__restrict__ plan, long pairs, int experts, long rows, int bn,
+                                                            int *__restrict__ order, int4 *__restrict__ tiles, long max_tiles) {
+    extern __shared__ int s_cnt[];   // [experts + 1]
+    pdl_launch_dependents();
+    pdl_wait();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    for (int e = warp; e < experts; e += nwarps) {
+        int count = 0;
+        for (long p0 = 0; p0 < pairs; p0 += 32) {
+            const long pr = p0 + lane;
+            count += __popc(__ballot_sync(0xffffffffu, pr < pairs && plan[pr] == e));
+        }
+        if (lane == 0) s_cnt[e + 1] = count;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_cnt[0] = 0;
+        long nt = 0;
+        for (int e = 0; e < experts; ++e) {
+            const int cnt = s_cnt[e + 1], off = s_cnt[e];
+            for (int t0 = 0; t0 < cnt && nt < max_tiles; t0 += bn) tiles[nt++] = make_int4((int)(e * rows), off + t0, min(bn, cnt - t0), e);
+            s_cnt[e + 1] = off + cnt;
+        }
+        for (; nt < max_tiles; ++nt) tiles[nt] = make_int4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    // sorted slots past the routed pairs (plan entries naming no expert) belong to no tile; point them at pair 0 so the
+    // activation prep reads a valid row
+    for (long i = s_cnt[experts] + threadIdx.x; i < pairs; i += blockDim.x) order[i] = 0;
+    for (int e = warp; e < experts; e += nwarps) {
+        int count = 0;
+        for (long p0 = 0; p0 < pairs; p0 += 32) {
+            const long pr = p0 + lane;
+            const bool hit = pr < pairs && plan[pr] == e;
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (hit) order[s_cnt[e] + count + __popc(m & ((1u << lane) - 1))] = (int)pr;
+            count += __popc(m);
+        }
+    }
+}
+
+__global__ void gather_f16_kernel(const __half *__restrict__ a, long k, const int *__restrict__ order, int thinkers, int tasks,
+                                  __half *__restrict__ bp, float *__restrict__ colscale) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const long t = blockIdx.x;
+    const int pr = order[t];
+    const long src = (long)(pr / thinkers) * tasks + (pr % thinkers) % tasks;
+    for (long i = threadIdx.x; i < k; i += blockDim.x) bp[t * k + i] = a[src * k + i];
+    if (threadIdx.x == 0) colscale[t] = 1.f;
+}
+
+}  // namespace
+
+// mixmul prefill: all experts in one grouped tcgen05 launch. Activations: planar (aq, ads) [tokens*tasks][k] or fp16 (af).
+// result[pair][rows]. Pairs whose plan entry names no expert are in no tile and stay untouched.
+int tb200_launch_gemm_grouped(tb200_ctx *c, const tb200_weights *w, int experts, long rows, const int8_t *aq, const int2 *ads, const void *af,
+                              const int32_t *plan, long pairs, int thinkers, int tasks, float *result) {
+    if (w->k % 256 || ((uintptr_t)w->qs & 15)) { tb200_set_error("gemm: K=%ld must be a multiple of 256", w->k); return TB200_ERR_UNSUPPORTED; }
+    const long avg = pairs / experts;
+    const int bn = avg >= 192 ? 256 : (avg >= 96 ? 128 : (avg >= 40 ? 64 : 32));
+    const long max_tiles = (pairs + bn - 1) / bn + experts;
+    const size_t bp_bytes = ((size_t)(pairs + 256) * w->k * 2 + 255) & ~(size_t)255;   // + one box of slack rows for the last tile's TMA
+    const size_t cs_bytes = ((size_t)pairs * 4 + 255) & ~(size_t)255, ord_bytes = cs_bytes, tl_bytes = ((size_t)max_tiles * 16 + 255) & ~(size_t)255;
+    uint8_t *scr = (uint8_t *)gemm_scratch(c, bp_bytes + cs_bytes + ord_bytes + tl_bytes);
+    if (!scr) return TB200_ERR_CUDA;
+    __half *bp = (__half *)scr;
+    float *colscale = (float *)(scr + bp_bytes);
+    int *order = (int *)(scr + bp_bytes + cs_bytes);
+    int4 *tiles = (int4 *)(scr + bp_bytes + cs_bytes + ord_bytes);
+    const int threads = experts >= 32 ? 1024 : experts * 32;
+    TB_CUDA(tb200_launch(build_groups_kernel, dim3(1), dim3(threads), (experts + 1) * sizeof(int), c->stream, plan, pairs, experts, rows, bn, order, tiles, max_tiles));
+    // rows of B' that belong to no expert (invalid plan entries) are never read by a tile; order[] past the valid count is
+    // not written, so size the prep grid by a device-independent bound: every sorted slot < pairs is either valid or unused.
+    // Unused slots would read garbage order[] -> pre-fill with pair 0.
+    if (w->type == TB200_TYPE_F16) {
+        TB_CUDA(tb200_launch(gather_f16_kernel, dim3((unsigned)pairs), dim3(256), 0, c->stream, (const __half *)af, w->k, (const int *)order, thinkers, tasks, bp, colscale));
+    } else {
+        const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : 2);
+        TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)pairs), dim3(256), 0, c->stream, aq, ads, w->k, w->k, perm, bp, colscale, (const int *)order, thinkers, tasks));
+    }
+    if (!w->tmap_cache) {
+        CUtensorMap *m = new CUtensorMap();
+        bool ok;
+        if (w->type == TB200_TYPE_F16) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k * 2, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
+        else if (w->type == TB200_TYPE_Q8_0) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k, BK, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
+        else ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / 2, (uint64_t)w->rows, (uint64_t)w->k / 2, BK / 2, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
+        if (!ok) { delete m; return TB200_ERR_CUDA; }
+        const_cast<tb200_weights *>(w)->tmap_cache = m;
+    }
+    CUtensorMap &mw = *reinterpret_cast<CUtensorMap *>(w->tmap_cache);
+    GemmParams p;
+    p.sc = w->sc;
+    p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
+    p.row0 = 0, p.nrows = rows, p.k = w->k, p.tokens = pairs, p.colscale = colscale, p.out = result, p.ldo = rows;
+    p.tiles = tiles, p.rowmap = order, p.n_tiles = max_tiles;
+    switch (w->type) {
+    case TB200_TYPE_Q4_0: return launch_type<TB200_TYPE_Q4_0>(c, w, mw, pairs, bp, p, bn);
+    case TB200_TYPE_Q8_0: return launch_type<TB200_TYPE_Q8_0>(c, w, mw, pairs, bp, p, bn);
+    case TB200_TYPE_F16: return launch_type<TB200_TYPE_F16>(c, w, mw, pairs, bp, p, bn);
+    default: return TB200_ERR_UNSUPPORTED;
+    }
+}
+
+namespace {
 }  // namespace
 
 bool tb200_gemm_available() {
@@ -475,7 +601,7 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
         TB_CUDA(tb200_launch(fill_ones_kernel, dim3((unsigned)((tokens + 255) / 256)), dim3(256), 0, c->stream, colscale, tokens));
     } else {
         const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : 2);
-        TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)tokens), dim3(256), 0, c->stream, aq, ads, a_stride, w->k, perm, bp, colscale));
+        TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)tokens), dim3(256), 0, c->stream, aq, ads, a_stride, w->k, perm, bp, colscale, (const int *)nullptr, 1, 1));
     }
     // weight tensor map (whole matrix), cached on the weights object
     if (!w->tmap_cache) {
@@ -492,6 +618,7 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
     p.sc = w->sc;
     p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
     p.row0 = row0, p.nrows = nrows, p.k = w->k, p.tokens = tokens, p.colscale = colscale, p.out = out, p.ldo = ldo;
+    p.tiles = nullptr, p.rowmap = nullptr, p.n_tiles = 0;
     switch (w->type) {
     case TB200_TYPE_Q4_0: return launch_type<TB200_TYPE_Q4_0>(c, w, mw, tokens, (void *)b_src, p);
     case TB200_TYPE_Q8_0: return launch_type<TB200_TYPE_Q8_0>(c, w, mw, tokens, (void *)b_src, p);

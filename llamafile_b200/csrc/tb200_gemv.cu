@@ -31,8 +31,8 @@ constexpr int kWarps = 8;   // warps per CTA
 // issued before the activations are even staged (weights are immutable, so it also precedes pdl_wait()), which
 // folds the weight-fetch latency and the activation-fetch latency of these short kernels into one.
 // One launch can serve up to kMaxMats weight matrices that share K and the activations (wq/wk/wv, gate/up): the
-// grid is the concatenation of their row tiles. With kFused the CTA quantizes the fp32 activations itself
-// (quantize_row_q8_0 arithmetic, bit-exact) instead of reading a pre-quantized planar copy.
+// grid is the concatenation of their row tiles. (Quantizing the fp32 activations inside every CTA was tried and
+// measured slower at every shape — N=128256: 94.7 vs 48.1 us — so activations arrive pre-quantized.)
 constexpr int kMaxMats = TB200_GEMV_MAX_MATS;
 struct GemvQ4Args {
     int nmat;
@@ -44,47 +44,10 @@ struct GemvQ4Args {
     long ldo[kMaxMats];
     long nb, nbc;
     const int8_t *aq; const int2 *ads; long a_stride;   // planar activations
-    const float *xf; long ldx;                          // fused: fp32 activations
     const tb200_gemv_item *items;
 };
 
-// quantize_row_q8_0 of one 32-block (ggml-quants.c:940-990), same arithmetic as tb200_quantize.cu
-__device__ __forceinline__ void quantize_block_q8_0(const float *__restrict__ x, bool vec, uint4 &lo, uint4 &hi, int2 &ds) {
-    float v[32];
-    if (vec) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const float4 f = reinterpret_cast<const float4 *>(x)[i];
-            v[4 * i] = f.x, v[4 * i + 1] = f.y, v[4 * i + 2] = f.z, v[4 * i + 3] = f.w;
-        }
-    } else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = x[i];
-    }
-    float amax = 0.f;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) amax = fmaxf(amax, fabsf(v[i]));
-    const float d = __fdiv_rn(amax, 127.f);
-    const float id = (amax != 0.0f) ? __fdiv_rn(127.f, amax) : 0.0f;
-    uint32_t pk[8];
-    int sum = 0;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        int q[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float p = __fmul_rn(v[4 * i + j], id);
-            q[j] = (!(p >= -2147483648.f && p < 2147483648.f)) ? -128 : max(-128, min(127, __float2int_rn(p)));
-            sum += q[j];
-        }
-        pk[i] = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
-    }
-    lo = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-    hi = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-    ds = make_int2(__float_as_int(__half2float(__float2half_rn(d))), sum);
-}
-
-template <int T, int R, bool kFused>
+template <int T, int R>
 __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_constant__ GemvQ4Args A) {
     constexpr int U = (T * R <= 4) ? 4 : 2;   // batch depth: blocks per lane per row in flight
     extern __shared__ __align__(16) uint8_t smem[];
@@ -163,20 +126,7 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_con
         const long cnt = min(nbc, nb - b0);
         if (b0) __syncthreads();
         const int nbc_i = (int)nbc;
-        if (kFused) {
-            // quantize this chunk of the fp32 activations: one thread per 32-block
-            const bool vec = (((uintptr_t)A.xf) & 15) == 0 && (A.ldx & 3) == 0;
-#pragma unroll
-            for (int t = 0; t < T; ++t) {
-                const float *xr = A.xf + (long)s_arow[t] * A.ldx + b0 * QK;
-                for (int g = threadIdx.x; g < (int)cnt; g += kWarps * 32) {
-                    uint4 lo, hi;
-                    int2 ds;
-                    quantize_block_q8_0(xr + g * QK, vec, lo, hi, ds);
-                    s_lo[t * nbc_i + g] = lo, s_hi[t * nbc_i + g] = hi, s_ds[t * nbc_i + g] = ds;
-                }
-            }
-        } else {
+        {
             // stage activations: 16-byte piece g of token t -> plane (g&1), index g>>1 (no div/mod: T is compile-time)
             const int cnt2 = (int)cnt * 2;
 #pragma unroll
@@ -603,15 +553,10 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
                 ka.out[m] = m == 0 ? a.out : a.out_more[m - 1], ka.ldo[m] = m == 0 ? a.ldo : a.ldo_more[m - 1];
             }
             ka.cta_begin[ka.nmat] = ctas;
-            ka.nb = nb, ka.nbc = nbc, ka.aq = a.aq, ka.ads = a.ads, ka.a_stride = a.a_stride, ka.xf = a.xf, ka.ldx = a.ldx, ka.items = a.items;
+            ka.nb = nb, ka.nbc = nbc, ka.aq = a.aq, ka.ads = a.ads, ka.a_stride = a.a_stride, ka.items = a.items;
             const dim3 g2((unsigned)ctas, grid.y);
-            if (a.xf) {
-                if ((rc = set_smem(gemv_q4_0_kernel<T, R, true>, smem))) return rc;
-                TB_CUDA(tb200_launch(gemv_q4_0_kernel<T, R, true>, g2, dim3(kWarps * 32), smem, c->stream, ka));
-            } else {
-                if ((rc = set_smem(gemv_q4_0_kernel<T, R, false>, smem))) return rc;
-                TB_CUDA(tb200_launch(gemv_q4_0_kernel<T, R, false>, g2, dim3(kWarps * 32), smem, c->stream, ka));
-            }
+            if ((rc = set_smem(gemv_q4_0_kernel<T, R>, smem))) return rc;
+            TB_CUDA(tb200_launch(gemv_q4_0_kernel<T, R>, g2, dim3(kWarps * 32), smem, c->stream, ka));
         } else {
             if ((rc = set_smem(gemv_q8_0_kernel<T, R>, smem))) return rc;
             TB_CUDA(tb200_launch(gemv_q8_0_kernel<T, R>, grid, dim3(kWarps * 32), smem, c->stream, (const uint4 *)w->qs, (const __half *)w->sc, nb, nbc, a.row0, a.nrows,

@@ -15,6 +15,10 @@
 int tb200_run_matmul(tb200_ctx *c, const tb200_weights *w, long row0, long nrows, const int8_t *aq, const int2 *ads, const void *af,
                      int af_is_f32, long a_stride, long tokens, float *out, long ldo);
 
+int tb200_launch_gemm_grouped(tb200_ctx *c, const tb200_weights *w, int experts, long rows, const int8_t *aq, const int2 *ads, const void *af,
+                              const int32_t *plan, long pairs, int thinkers, int tasks, float *result);
+bool tb200_gemm_available();
+
 namespace {
 
 // One CTA; warp e (looping if experts > warps) scans all pairs in order, so every expert's list is
@@ -109,6 +113,10 @@ extern "C" int tb200_mixmul_dev(const tb200_weights *w, int experts, const float
     if (w->type == TB200_TYPE_F16) rc = tb200_launch_f32_to_f16(c, thought, k, arows, k, ah);          // quantize_thought :322-348
     else rc = tb200_launch_quantize_q8_0(c, thought, k, arows, k, nullptr, aq, ads);
     if (rc) return rc;
+    // prefill-sized routing: one grouped tcgen05 launch over all experts
+    if (pairs >= 16L * experts && k % 256 == 0 && tb200_gemm_available())
+        return tb200_launch_gemm_grouped(c, w, experts, rows, w->type == TB200_TYPE_F16 ? nullptr : aq, w->type == TB200_TYPE_F16 ? nullptr : ads,
+                                         w->type == TB200_TYPE_F16 ? (const void *)ah : nullptr, plan, pairs, thinkers, tasks, result);
     const int threads = experts >= 32 ? 1024 : experts * 32;
     build_items_kernel<<<1, threads, (experts + 1) * sizeof(int), c->stream>>>(plan, pairs, thinkers, tasks, experts, rows, group, items,
                                                                               max_items, nullptr);

@@ -43,7 +43,7 @@ def lib() -> C.CDLL:
         "tb200_mul_mat": (i, [vp, vp, l, l, vp, l]), "tb200_sgemm_dev": (i, [vp, l, vp, l, i, vp, l]),
         "tb200_mul_mat_multi": (i, [i, vp, vp, l, l, vp, vp]),
         "tb200_acts_create": (vp, [i, l, l]), "tb200_acts_quantize": (i, [vp, vp, l, l]),
-        "tb200_mul_mat_acts": (i, [vp, vp, vp, l]), "tb200_acts_free": (None, [vp]),
+        "tb200_mul_mat_acts": (i, [vp, vp, vp, l]), "tb200_mul_mat_acts_multi": (i, [i, vp, vp, vp, vp]), "tb200_acts_free": (None, [vp]),
         "tb200_blockdot_dev": (i, [vp, vp, i, vp]), "tb200_mixmul_dev": (i, [vp, i, vp, i, vp, i, l, vp]),
         "tb200_malloc": (vp, [sz]), "tb200_free": (None, [vp]), "tb200_memcpy_h2d": (i, [vp, vp, sz]),
         "tb200_memcpy_d2h": (i, [vp, vp, sz]), "tb200_host_alloc": (vp, [sz]), "tb200_host_free": (None, [vp]),
@@ -159,6 +159,14 @@ class Acts:
 
 def mul_mat_acts(w: Weights, a: Acts, out, ldo: int | None = None):
     _check(lib().tb200_mul_mat_acts(w.handle, a.handle, _ptr(out), ldo or w.rows), "mul_mat_acts")
+
+
+def mul_mat_acts_multi(ws, a: Acts, outs):
+    n = len(ws)
+    W = (C.c_void_p * n)(*[w.handle for w in ws])
+    O = (C.c_void_p * n)(*[_ptr(o) for o in outs])
+    Ld = (C.c_long * n)(*[w.rows for w in ws])
+    _check(lib().tb200_mul_mat_acts_multi(n, W, a.handle, O, Ld), "mul_mat_acts_multi")
 
 
 def mul_mat_multi(ws, x, tokens: int, outs, ldx: int | None = None):

@@ -354,3 +354,35 @@ def test_mul_mat_multi(tb, oracle, wt, T):
         H.assert_close(o.cpu().numpy(), oracle.mul_mat(W, wt, X), f"multi n={n}")
     for w in ws:
         w.free()
+
+
+# ------------------------------------------------------------------ mixmul at prefill sizes (grouped tcgen05 launch)
+@pytest.mark.parametrize("wt", [H.Q4_0, H.Q8_0, H.F16])
+@pytest.mark.parametrize("tokens,tasks,skew", [(100, 1, False), (300, 2, False), (256, 1, True)])
+def test_mixmul_prefill_vs_oracle(tb, oracle, wt, tokens, tasks, skew):
+    rows, cols, experts, thinkers = 200, 1024, 8, 2
+    W = H.make_weights(wt, experts * rows, cols, seed=tokens)
+    X = np.random.default_rng(tokens).standard_normal((tokens, tasks, cols)).astype(np.float32)
+    plan = H.make_plan(tokens, experts, thinkers, skew=skew)
+    ok, out = run_mixmul_host(tb, W, wt, X, plan, rows, cols, experts)
+    assert ok
+    ref = np.full((tokens, thinkers, rows), np.nan, np.float32)
+    assert oracle.mixmul(B.Tensor.of(W, wt, [cols, rows, experts]), B.Tensor.of(X, H.F32, [cols, tasks, tokens]),
+                         B.Tensor.of(plan, H.I32, [thinkers, tokens]), B.Tensor.of(ref, H.F32, [rows, thinkers, tokens]))
+    H.assert_close(out, ref)
+
+
+def test_mixmul_prefill_invalid_experts_untouched(tb, oracle):
+    rows, cols, experts, thinkers, tokens = 128, 512, 4, 2, 200
+    W = H.make_weights(H.Q4_0, experts * rows, cols, seed=2)
+    X = np.random.default_rng(5).standard_normal((tokens, 1, cols)).astype(np.float32)
+    plan = H.make_plan(tokens, experts, thinkers, seed=6)
+    plan[::7, 0] = 11
+    plan[3::9, 1] = -2
+    ok, out = run_mixmul_host(tb, W, H.Q4_0, X, plan, rows, cols, experts, fill=7.5)
+    assert ok
+    ref = np.full((tokens, thinkers, rows), 7.5, np.float32)
+    assert oracle.mixmul(B.Tensor.of(W, H.Q4_0, [cols, rows, experts]), B.Tensor.of(X, H.F32, [cols, 1, tokens]),
+                         B.Tensor.of(plan, H.I32, [thinkers, tokens]), B.Tensor.of(ref, H.F32, [rows, thinkers, tokens]))
+    assert np.array_equal(out == 7.5, ref == 7.5)
+    H.assert_close(out, ref)
