@@ -54,13 +54,7 @@ def algorithmic_bytes(wtype, N, K, T=1):
     return N * K * BPE[wtype] + T * K * 4 + T * N * 4
 
 
-def shard_rows(N, rank, world, tile=128):
-    """Contiguous split of the output rows in tiles of 128 (the reference rounds its row split to the mmq tile,
-    ggml-cuda.cu:646-674)."""
-    tiles = (N + tile - 1) // tile
-    lo = (tiles * rank // world) * tile
-    hi = min(N, (tiles * (rank + 1) // world) * tile)
-    return lo, hi
+from llamafile_b200.shard import shard_rows  # noqa: E402  (row split in 128-row tiles, as ggml-cuda.cu:646-674)
 
 
 class ClockSampler(threading.Thread):
@@ -223,9 +217,12 @@ def run_b200_arm(args):
         if grp not in groups:
             x = torch.randn(1, K, device=dev, dtype=torch.float32)
             groups[grp] = (x, tb.Acts(wtype, K, 1))
-    outs = [torch.empty(1, hi - lo, device=dev, dtype=torch.float32) for (_, N, lo, hi, K, g, w) in mats]
-    gathered = [torch.empty(world, outs[i].numel(), device=dev, dtype=torch.float32) if world > 1 else None for i in range(len(mats))]
-    even = all((hi - lo) * world == N for (_, N, lo, hi, K, g, w) in mats)
+    # outputs: each rank writes its row slice into a staging row as wide as the widest shard (uneven splits, e.g. vocab
+    # 128256 = 1002 tiles, are padded for the collective), which is what gets all-gathered
+    from llamafile_b200.shard import max_shard
+    staging = [torch.zeros(1, max_shard(N, world), device=dev, dtype=torch.float32) for (_, N, lo, hi, K, g, w) in mats]
+    outs = [staging[i][:, : m[3] - m[2]] for i, m in enumerate(mats)]
+    gathered = [torch.empty(world, staging[i].shape[1], device=dev, dtype=torch.float32) if world > 1 else None for i in range(len(mats))]
 
     # launch schedule of one step: matrices that consume the same activations go out in ONE launch
     # (tb200_mul_mat_multi: wq/wk/wv, gate/up); every launch quantizes its activations in-kernel.
@@ -244,16 +241,7 @@ def run_b200_arm(args):
             tb.mul_mat_acts_multi([mats[i][6] for i in idx], acts, [outs[i] for i in idx])
             if world > 1 and with_gather:
                 for i in idx:
-                    if even:
-                        dist.all_gather_into_tensor(gathered[i], outs[i])
-                    else:   # uneven tail shard (vocab 128256 = 1002 tiles): pad to the widest shard
-                        pad = torch.zeros(gathered[i].shape[1], device=dev); pad[: outs[i].numel()] = outs[i].view(-1)
-                        dist.all_gather_into_tensor(gathered[i], pad)
-
-    if world > 1:   # make every shard buffer the same width so all_gather_into_tensor applies
-        for i, (name, N, lo, hi, K, grp, w) in enumerate(mats):
-            width = max(shard_rows(N, r, world)[1] - shard_rows(N, r, world)[0] for r in range(world))
-            gathered[i] = torch.empty(world, width, device=dev, dtype=torch.float32)
+                    dist.all_gather_into_tensor(gathered[i], staging[i])
 
     step_bytes = sum(algorithmic_bytes(wtype, hi - lo, K) for (_, N, lo, hi, K, g, w) in mats)
     total_step_bytes = sum(algorithmic_bytes(wtype, N, K) for (_, N, lo, hi, K, g, w) in mats)
