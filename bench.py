@@ -162,10 +162,17 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
+def log(msg):
+    if os.environ.get("TB200_BENCH_VERBOSE"):
+        sys.stderr.write(f"[bench r{os.environ.get('RANK', '0')} {time.strftime('%H:%M:%S')}] {msg}\n")
+        sys.stderr.flush()
+
+
 def run_b200_arm(args):
     import torch
     import torch.distributed as dist
 
+    log("start")
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -176,6 +183,7 @@ def run_b200_arm(args):
     import llamafile_b200 as tb
     if not tb.link():
         raise SystemExit("bench: no sm_100 device; the CUDA path cannot run and there is no CPU fallback")
+    log("library linked")
     dev = torch.device("cuda", local)
     stream = torch.cuda.Stream(device=dev)
     tb.set_stream(stream.cuda_stream)
@@ -217,31 +225,36 @@ def run_b200_arm(args):
         if grp not in groups:
             x = torch.randn(1, K, device=dev, dtype=torch.float32)
             groups[grp] = (x, tb.Acts(wtype, K, 1))
-    # outputs: each rank writes its row slice into a staging row as wide as the widest shard (uneven splits, e.g. vocab
-    # 128256 = 1002 tiles, are padded for the collective), which is what gets all-gathered
-    from llamafile_b200.shard import max_shard
-    staging = [torch.zeros(1, max_shard(N, world), device=dev, dtype=torch.float32) for (_, N, lo, hi, K, g, w) in mats]
-    outs = [staging[i][:, : m[3] - m[2]] for i, m in enumerate(mats)]
-    gathered = [torch.empty(world, staging[i].shape[1], device=dev, dtype=torch.float32) if world > 1 else None for i in range(len(mats))]
-
     # launch schedule of one step: matrices that consume the same activations go out in ONE launch
-    # (tb200_mul_mat_multi: wq/wk/wv, gate/up); every launch quantizes its activations in-kernel.
+    # (tb200_mul_mat_acts_multi: wq/wk/wv, gate/up).
     schedule = []
     for i, m in enumerate(mats):
         if schedule and schedule[-1][0] == m[5] and len(schedule[-1][1]) < 4 and wtype == Q4_0:
             schedule[-1][1].append(i)
         else:
             schedule.append((m[5], [i]))
+    # outputs: each rank writes its row slices of a launch group into ONE staging row (every slice padded to the widest
+    # shard so uneven splits, e.g. vocab 128256 = 1002 tiles, line up), which is all-gathered with one collective per group
+    from llamafile_b200.shard import max_shard
+    outs, staging, gathered = [None] * len(mats), [], []
+    for grp, idx in schedule:
+        widths = [max_shard(mats[i][1], world) for i in idx]
+        st = torch.zeros(1, sum(widths), device=dev, dtype=torch.float32)
+        off = 0
+        for i, wd in zip(idx, widths):
+            outs[i] = st[:, off: off + (mats[i][3] - mats[i][2])]
+            off += wd
+        staging.append(st)
+        gathered.append(torch.empty(world, st.shape[1], device=dev, dtype=torch.float32) if world > 1 else None)
 
     def step(with_gather=True, with_quant=True):
-        for grp, idx in schedule:
+        for gi, (grp, idx) in enumerate(schedule):
             x, acts = groups[grp]
             if with_quant:
                 acts.quantize(x, 1)
             tb.mul_mat_acts_multi([mats[i][6] for i in idx], acts, [outs[i] for i in idx])
             if world > 1 and with_gather:
-                for i in idx:
-                    dist.all_gather_into_tensor(gathered[i], staging[i])
+                dist.all_gather_into_tensor(gathered[gi], staging[gi])
 
     step_bytes = sum(algorithmic_bytes(wtype, hi - lo, K) for (_, N, lo, hi, K, g, w) in mats)
     total_step_bytes = sum(algorithmic_bytes(wtype, N, K) for (_, N, lo, hi, K, g, w) in mats)
@@ -251,6 +264,8 @@ def run_b200_arm(args):
         with torch.cuda.stream(stream):
             fn()   # grows nothing afterwards; sets kernel attributes
             stream.synchronize()
+            if args.no_graph:
+                return fn, False
             try:
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g, stream=stream):
@@ -283,18 +298,22 @@ def run_b200_arm(args):
             ms = float(t.item())
         return ms
 
+    log('weights resident; first step')
     l0 = tb.launch_count()
     with torch.cuda.stream(stream):
         step()
     launches_per_step = tb.launch_count() - l0
+    log('capturing full step')
     run_full, graphed = capture(step)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    log('timing full step')
     ms_total = timed(run_full, args.steps, args.warmup)
     ms_per_step = ms_total / args.steps
     value = total_step_bytes / (ms_per_step * 1e-3) / 1e9
 
+    log('roofline pass')
     # ---- roofline: the decode GEMV kernel alone (no quantizers, no collectives)
     run_gemv, _ = capture(lambda: step(with_gather=False, with_quant=False))
     ms_gemv = timed(run_gemv, args.steps, args.warmup) / args.steps
@@ -305,6 +324,7 @@ def run_b200_arm(args):
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
                 "launches_timed": n_gemv, "avg_launch_us": ms_gemv * 1e3 / n_gemv, "algorithmic_bytes_per_launch": step_bytes / n_gemv,
                 "frac_of_spec_8TBs": achieved / 8000.0}
+    log('per-shape pass')
     # per-shape view of the same kernel (BASELINE configs[1] names N=4096/14336/128256 at K=4096)
     per_shape = {}
     for shape in sorted({(hi - lo, K) for (_, N, lo, hi, K, g, w) in mats}):
@@ -319,6 +339,7 @@ def run_b200_arm(args):
         per_shape[f"N={shape[0]},K={shape[1]}"] = {"launches": len(idx), "us_per_launch": ms * 1e3 / len(idx), "GBps": b / (ms * 1e-3) / 1e9,
                                                   "distinct_MB": b / 1e6}
 
+    log('e2e pass')
     # ---- e2e: llamafile_sgemm() with HOST buffers (pinned), weights resident after the first call
     e2e = None
     if args.e2e:
@@ -359,6 +380,7 @@ def run_b200_arm(args):
                "api": "llamafile_sgemm(host A cached on device, pinned host B Q8_0, pinned host C), one call + sync per matmul"}
         tb.set_stream(stream.cuda_stream)
 
+    log('done; assembling line')
     clocks = None
     if rank == 0:
         sampler.stop_flag = True
@@ -385,8 +407,12 @@ def run_b200_arm(args):
                 "roofline": roofline, "per_shape": per_shape, "cpu_baseline": cpu_baseline, "e2e": e2e,
                 "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks}
         print(json.dumps(line), flush=True)
+    log("line printed; leaving")
     if world > 1:
-        dist.destroy_process_group()
+        dist.barrier()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)   # skip interpreter teardown: CUDA graphs holding NCCL nodes + process-group destruction can stall at exit
 
 
 def main():
@@ -399,6 +425,7 @@ def main():
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (debug)")
     ap.add_argument("--no-e2e", dest="e2e", action="store_false")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay (debug)")
     args = ap.parse_args()
     args.warmup = max(3, args.warmup) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
