@@ -174,6 +174,7 @@ TB200_API int tb200_quantize_q8_K_dev(const float *x, long ldx, void *y, long ro
  * tokens <= TB200_GEMV_MAX_TOKENS, tcgen05 GEMM above. */
 #define TB200_GEMV_MAX_TOKENS 8
 #define TB200_GEMV_MAX_MATS 4
+#define TB200_MAX_PEERS 8
 TB200_API int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens, float *out, long ldo);
 
 /* Decode only (tokens <= TB200_GEMV_MAX_TOKENS): n <= TB200_GEMV_MAX_MATS weight matrices of the same type and K that
@@ -189,6 +190,21 @@ TB200_API int tb200_acts_quantize(tb200_acts *a, const float *x, long ldx, long 
 TB200_API int tb200_mul_mat_acts(const tb200_weights *w, const tb200_acts *a, float *out, long ldo);
 TB200_API int tb200_mul_mat_acts_multi(int n, const tb200_weights *const *w, const tb200_acts *a, float *const *out, const long *ldo);
 TB200_API void tb200_acts_free(tb200_acts *a);
+
+/* Multi-GPU, one process per GPU: weights row-sharded (each rank uploads its row slice), the all-gather of the output
+ * slices fused into the decode kernel as peer stores over NVLink. The host shares one symmetric output buffer and one flag
+ * buffer ([TB200_MAX_PEERS] uint32, zeroed) per rank through CUDA IPC handles (both from tb200_malloc). */
+typedef struct tb200_peers tb200_peers;
+TB200_API int tb200_ipc_get_handle(const void *dev_ptr, void *handle64);
+TB200_API void *tb200_ipc_open_handle(const void *handle64);
+TB200_API int tb200_ipc_close_handle(void *p);
+TB200_API tb200_peers *tb200_peers_create(int world, int rank, void *const *out_bases, void *const *flag_bases);
+TB200_API void tb200_peers_free(tb200_peers *g);
+TB200_API int tb200_mul_mat_acts_multi_gather(tb200_peers *g, int n, const tb200_weights *const *w, const tb200_acts *a,
+                                              const size_t *out_offset, const long *ldo, const long *row_lo);
+TB200_API int tb200_peers_barrier(tb200_peers *g);   /* enqueue: all ranks' slices of everything launched so far are visible after it */
+TB200_API int tb200_peers_timed_out(tb200_peers *g);
+TB200_API int tb200_memset(void *dst, int value, size_t bytes);
 
 /* llamafile_sgemm on device pointers with pre-quantized activations B (GGUF blocks of Btype, ldb in
  * blocks). Same service matrix as llamafile_sgemm. */

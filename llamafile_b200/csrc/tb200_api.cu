@@ -119,6 +119,7 @@ void *tb200_malloc(size_t bytes) { if (!tb200_get_ctx()) return nullptr; void *p
 void tb200_free(void *p) { if (p) cudaFree(p); }
 int tb200_memcpy_h2d(void *dst, const void *src, size_t bytes) { tb200_ctx *c = tb200_get_ctx(); if (!c) return TB200_ERR_NO_DEVICE; TB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream)); TB_CUDA(cudaStreamSynchronize(c->stream)); return TB200_OK; }
 int tb200_memcpy_d2h(void *dst, const void *src, size_t bytes) { tb200_ctx *c = tb200_get_ctx(); if (!c) return TB200_ERR_NO_DEVICE; TB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream)); TB_CUDA(cudaStreamSynchronize(c->stream)); return TB200_OK; }
+int tb200_memset(void *dst, int value, size_t bytes) { tb200_ctx *c = tb200_get_ctx(); if (!c) return TB200_ERR_NO_DEVICE; TB_CUDA(cudaMemsetAsync(dst, value, bytes, c->stream)); TB_CUDA(cudaStreamSynchronize(c->stream)); return TB200_OK; }
 void *tb200_host_alloc(size_t bytes) { if (!tb200_get_ctx()) return nullptr; void *p = nullptr; if (cudaMallocHost(&p, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; } return p; }
 void tb200_host_free(void *p) { if (p) cudaFreeHost(p); }
 
@@ -283,7 +284,7 @@ int tb200_mul_mat_multi(int n, const tb200_weights *const *w, const float *x, lo
             return TB200_ERR_INVALID;
         }
     if (tokens == 0) return TB200_OK;
-    if (w[0]->type != TB200_TYPE_Q4_0 || tokens > TB200_GEMV_MAX_TOKENS) {   // other types / prefill: one matmul each
+    if ((w[0]->type != TB200_TYPE_Q4_0 && w[0]->type != TB200_TYPE_Q4_K) || tokens > TB200_GEMV_MAX_TOKENS) {   // other types / prefill: one matmul each
         for (int m = 0; m < n; ++m) {
             const int rc = tb200_mul_mat(w[m], x, ldx, tokens, out[m], ldo[m]);
             if (rc) return rc;
@@ -291,9 +292,10 @@ int tb200_mul_mat_multi(int n, const tb200_weights *const *w, const float *x, lo
         return TB200_OK;
     }
     // quantize once (one launch), then ONE decode launch over the concatenated row tiles of all n matrices
-    Planar p = carve(c, TB200_TYPE_Q4_0, tokens, w[0]->k, 0, nullptr);
+    Planar p = carve(c, w[0]->type, tokens, w[0]->k, 0, nullptr);
     if (!p.q) return TB200_ERR_CUDA;
-    int rc = tb200_launch_quantize_q8_0(c, x, ldx, tokens, w[0]->k, nullptr, p.q, p.ds);
+    int rc = w[0]->type == TB200_TYPE_Q4_K ? tb200_launch_quantize_q8_K(c, x, ldx, tokens, w[0]->k, nullptr, p.q, p.ds)
+                                           : tb200_launch_quantize_q8_0(c, x, ldx, tokens, w[0]->k, nullptr, p.q, p.ds);
     if (rc) return rc;
     tb200_gemv_args a;
     memset(&a, 0, sizeof(a));
@@ -365,8 +367,11 @@ int tb200_mul_mat_acts_multi(int n, const tb200_weights *const *w, const tb200_a
     tb200_ctx *c = tb200_get_ctx();
     if (!c) return TB200_ERR_NO_DEVICE;
     if (n < 1 || n > TB200_GEMV_MAX_MATS || !w || !a || !out || !ldo) { tb200_set_error("mul_mat_acts_multi: bad arguments"); return TB200_ERR_INVALID; }
-    bool one_launch = w[0] && w[0]->type == TB200_TYPE_Q4_0 && a->tokens <= TB200_GEMV_MAX_TOKENS && a->wtype != TB200_TYPE_F16 && a->wtype != TB200_TYPE_Q4_K;
-    for (int m = 0; m < n && one_launch; ++m) one_launch = w[m] && w[m]->type == TB200_TYPE_Q4_0 && w[m]->k == a->k && ldo[m] >= w[m]->rows;
+    // one launch when all matrices are Q4_0 (Q8_0 activations) or all Q4_K (Q8_K activations) and share K
+    const int t0 = w[0] ? w[0]->type : -1;
+    bool one_launch = (t0 == TB200_TYPE_Q4_0 || t0 == TB200_TYPE_Q4_K) && a->tokens <= TB200_GEMV_MAX_TOKENS && a->wtype != TB200_TYPE_F16 &&
+                      (t0 == TB200_TYPE_Q4_K) == (a->wtype == TB200_TYPE_Q4_K);
+    for (int m = 0; m < n && one_launch; ++m) one_launch = w[m] && w[m]->type == t0 && w[m]->k == a->k && ldo[m] >= w[m]->rows;
     if (!one_launch) {
         for (int m = 0; m < n; ++m) {
             const int rc = tb200_mul_mat_acts(w[m], a, out[m], ldo[m]);
@@ -381,6 +386,36 @@ int tb200_mul_mat_acts_multi(int n, const tb200_weights *const *w, const tb200_a
     for (int m = 1; m < n; ++m) g.w_more[m - 1] = w[m], g.out_more[m - 1] = out[m], g.ldo_more[m - 1] = ldo[m];
     g.aq = a->q, g.ads = a->ds, g.a_stride = a->k, g.tokens = a->tokens;
     return tb200_launch_gemv(c, g);
+}
+
+// tb200_mul_mat_acts_multi with the all-gather fused into the kernel: matrix m's rows are this rank's slice starting at row
+// row_lo[m] of the full output, which lives at byte offset out_offset[m] of the symmetric buffer with leading dimension
+// ldo[m] (the full N). Every rank holds every slice once tb200_peers_barrier() has passed.
+int tb200_mul_mat_acts_multi_gather(tb200_peers *g, int n, const tb200_weights *const *w, const tb200_acts *a, const size_t *out_offset,
+                                    const long *ldo, const long *row_lo) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!c) return TB200_ERR_NO_DEVICE;
+    if (!g || n < 1 || n > TB200_GEMV_MAX_MATS || !w || !a || !out_offset || !ldo || !row_lo) { tb200_set_error("multi_gather: bad arguments"); return TB200_ERR_INVALID; }
+    const int t0 = w[0] ? w[0]->type : -1;
+    if ((t0 != TB200_TYPE_Q4_0 && t0 != TB200_TYPE_Q4_K) || a->tokens > TB200_GEMV_MAX_TOKENS || (t0 == TB200_TYPE_Q4_K) != (a->wtype == TB200_TYPE_Q4_K) ||
+        a->wtype == TB200_TYPE_F16)
+        return TB200_ERR_UNSUPPORTED;
+    for (int m = 0; m < n; ++m)
+        if (!w[m] || w[m]->type != t0 || w[m]->k != a->k || row_lo[m] < 0 || ldo[m] < row_lo[m] + w[m]->rows || (out_offset[m] & 3)) {
+            tb200_set_error("multi_gather: matrix %d does not fit its slot", m);
+            return TB200_ERR_INVALID;
+        }
+    if (a->tokens == 0) return TB200_OK;
+    char *base = (char *)g->out_base[g->rank];
+    tb200_gemv_args ga;
+    memset(&ga, 0, sizeof(ga));
+    ga.nmat = n;
+    ga.w = w[0], ga.row0 = 0, ga.nrows = w[0]->rows, ga.out = (float *)(base + out_offset[0]) + row_lo[0], ga.ldo = ldo[0];
+    for (int m = 1; m < n; ++m) ga.w_more[m - 1] = w[m], ga.out_more[m - 1] = (float *)(base + out_offset[m]) + row_lo[m], ga.ldo_more[m - 1] = ldo[m];
+    ga.aq = a->q, ga.ads = a->ds, ga.a_stride = a->k, ga.tokens = a->tokens;
+    ga.world = g->world, ga.local_base = base;
+    for (int p = 0; p < g->world; ++p) ga.peer_base[p] = g->out_base[p];
+    return tb200_launch_gemv(c, ga);
 }
 
 void tb200_acts_free(tb200_acts *a) {

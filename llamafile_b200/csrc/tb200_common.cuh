@@ -46,6 +46,15 @@ struct tb200_weights {
 //   ds  {float d, int32 sum} per 32-block [tokens][k/32]   (Q8_0: d = fp16 scale widened; sum = sum of q)
 //   Q8_K: d is the per-256 float scale replicated on its 8 sub-blocks, sum = bsums[2s]+bsums[2s+1]
 
+// peer group for the fused all-gather (tb200_peer.cu)
+struct tb200_peers {
+    int world, rank;
+    void *out_base[TB200_MAX_PEERS];    // symmetric output buffer on every rank (own entry = local pointer)
+    uint32_t *flags[TB200_MAX_PEERS];   // [world] arrival epochs on every rank
+    uint32_t *epoch;                    // local launch counter (device memory, so graph replays advance it)
+    int *timeout_flag;                  // set when a barrier gave up waiting
+};
+
 // per-device context (tb200_api.cu)
 struct tb200_ctx {
     int device;
@@ -99,8 +108,11 @@ struct tb200_gemv_args {
     long tokens;
     float *out; long ldo;
     const tb200_gemv_item *items; long n_items;   // optional grouped mode (device array); tokens = template T
-    // optional (Q4_0): more matrices sharing K and the activations, served by the same launch
+    // optional (Q4_0 / Q4_K): more matrices sharing K and the activations, served by the same launch
     int nmat; const tb200_weights *w_more[TB200_GEMV_MAX_MATS - 1]; float *out_more[TB200_GEMV_MAX_MATS - 1]; long ldo_more[TB200_GEMV_MAX_MATS - 1];
+    // optional (Q4_0 / Q4_K): fused all-gather — `out` pointers lie inside this rank's symmetric buffer `local_base`, and
+    // every result is stored at the same offset of every rank's copy (peer_base[0..world))
+    int world; const void *local_base; void *peer_base[TB200_MAX_PEERS];
 };
 int tb200_launch_gemv(tb200_ctx *c, const tb200_gemv_args &a);
 int tb200_launch_blockdot(tb200_ctx *c, const tb200_weights *w, const int8_t *aq, const int2 *ads, int32_t *out);

@@ -36,9 +36,12 @@ constexpr int kWarps = 8;   // warps per CTA
 constexpr int kMaxMats = TB200_GEMV_MAX_MATS;
 struct GemvQ4Args {
     int nmat;
+    int world;                         // > 1: fused all-gather, lane p stores the row result into peer p's copy of the buffer
+    const char *local_base;            // base of this rank's symmetric output buffer
+    char *peer_base[TB200_MAX_PEERS];  // the same buffer on every rank (own entry included), peer-mapped
     int cta_begin[kMaxMats + 1];
-    const uint4 *qs[kMaxMats];
-    const __half *sc[kMaxMats];
+    const void *qs[kMaxMats];
+    const void *sc[kMaxMats];
     long row0[kMaxMats], nrows[kMaxMats];
     float *out[kMaxMats];
     long ldo[kMaxMats];
@@ -46,6 +49,30 @@ struct GemvQ4Args {
     const int8_t *aq; const int2 *ads; long a_stride;   // planar activations
     const tb200_gemv_item *items;
 };
+
+// Epilogue shared by the quantized decode kernels: warp-reduce each (row, token) and store. With world > 1 the
+// store IS the all-gather: every lane p < world writes the value into rank p's copy of the symmetric output buffer
+// over NVLink (peer-mapped pointers), so no collective follows the kernel — only a flag barrier (tb200_peer.cu).
+template <int T, int R>
+__device__ __forceinline__ void store_rows(const GemvQ4Args &A, int mat, float (&acc)[R][T], const int (&orow)[T], int ntok,
+                                           long r_base, long nrows, int lane) {
+    float *out = A.out[mat];
+    const long ldo = A.ldo[mat];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const float v = warp_sum(acc[r][t]);   // xor-shuffle: every lane holds the sum
+            if (r_base + r < nrows && t < ntok) {
+                float *dst = out + (long)orow[t] * ldo + r_base + r;
+                if (A.world <= 1) {
+                    if (lane == 0) *dst = v;
+                } else if (lane < A.world) {
+                    *reinterpret_cast<float *>(A.peer_base[lane] + (reinterpret_cast<const char *>(dst) - A.local_base)) = v;
+                }
+            }
+        }
+}
 
 template <int T, int R>
 __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_constant__ GemvQ4Args A) {
@@ -66,8 +93,8 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_con
     const long nrows = A.nrows[mat];
     const long r_base = ((long)((int)blockIdx.x - A.cta_begin[mat]) * kWarps + warp) * R;   // first row of this warp (relative to row0)
     const bool active = r_base < nrows;
-    const uint4 *qs = A.qs[mat];
-    const __half *sc = A.sc[mat];
+    const uint4 *qs = (const uint4 *)A.qs[mat];
+    const __half *sc = (const __half *)A.sc[mat];
 
     uint4 w[U][R];
     __half dh[U][R];
@@ -180,15 +207,7 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_con
         }
     }
     if (!active) return;
-    float *out = A.out[mat];
-    const long ldo = A.ldo[mat];
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-#pragma unroll
-        for (int t = 0; t < T; ++t) {
-            const float v = warp_sum(acc[r][t]);
-            if (lane == 0 && r_base + r < nrows && t < ntok) out[(long)orow[t] * ldo + r_base + r] = v;
-        }
+    store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane);
 }
 
 // ---- Q8_0 ---------------------------------------------------------------------------------------
@@ -293,50 +312,84 @@ __device__ __forceinline__ void q4k_scale_min(const uint4 hdr, int j, int &sc, i
     else { sc = (byte(j + 4) & 0xF) | ((byte(j - 4) >> 6) << 4); m = (byte(j + 4) >> 4) | ((byte(j) >> 6) << 4); }
 }
 
+// Same launch structure as the Q4_0 kernel (multi-matrix grid, first weight batch before pdl_wait, fused all-gather
+// stores); A.nb / A.nbc count super-blocks here.
 template <int T, int R>
-__global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const uint4 *__restrict__ qs, const uint4 *__restrict__ sc,
-                                                                long nsb, long nsbc, long row0, long nrows,
-                                                                const int8_t *__restrict__ aq, const int2 *__restrict__ ads,
-                                                                long a_stride, float *__restrict__ out, long ldo,
-                                                                const tb200_gemv_item *__restrict__ items) {
+__global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const __grid_constant__ GemvQ4Args A) {
+    constexpr int U = (T * R <= 2) ? 2 : 1;   // super-blocks per 8-lane group per row in flight
     extern __shared__ __align__(16) uint8_t smem[];
+    const long nsb = A.nb, nsbc = A.nbc;
     uint4 *s_lo = reinterpret_cast<uint4 *>(smem);   // [T][nsbc*8]
     uint4 *s_hi = s_lo + T * nsbc * 8;
     int2 *s_ds = reinterpret_cast<int2 *>(s_hi + T * nsbc * 8);   // [T][nsbc*8]
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const long r_base = ((long)blockIdx.x * kWarps + warp) * R;
-    const bool active = r_base < nrows;
-    pdl_launch_dependents();
-    pdl_wait();
-    // grouped mode (mixmul): this CTA column serves one work item = one expert's rows x up to T gathered tokens
     __shared__ int s_arow[T];
-    long my_row0 = row0;
+
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int mat = 0;
+#pragma unroll
+    for (int m = 1; m < kMaxMats; ++m)
+        if (m < A.nmat && (int)blockIdx.x >= A.cta_begin[m]) mat = m;
+    const long nrows = A.nrows[mat];
+    const long r_base = ((long)((int)blockIdx.x - A.cta_begin[mat]) * kWarps + warp) * R;
+    const bool active = r_base < nrows;
+    const uint4 *qs = (const uint4 *)A.qs[mat];
+    const uint4 *sc = (const uint4 *)A.sc[mat];
+    const int p = lane & 7, c = p >> 1, h = p & 1, grp = lane >> 3;
+
+    uint4 w[U][R], hdr[U][R];
+    long rowv[R];
+    auto set_rows = [&](long my_row0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) rowv[r] = my_row0 + min(r_base + r, nrows - 1);
+    };
+    auto load_batch = [&](long sbase, long end) {   // super-blocks sbase + grp + 4u (row-relative), limited to < end
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long sb = sbase + grp + 4 * u;
+            if (sb < end) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    w[u][r] = ldg_stream(qs + (rowv[r] * nsb + sb) * 8 + p);
+                    hdr[u][r] = __ldg(sc + rowv[r] * nsb + sb);
+                }
+            }
+        }
+    };
+
     int ntok = T, orow[T];
 #pragma unroll
     for (int t = 0; t < T; ++t) orow[t] = t;
-    if (items) {
-        const tb200_gemv_item &it = items[blockIdx.y];
+    if (!A.items) {
+        set_rows(A.row0[mat]);
+        if (active) load_batch(0, min(nsbc, nsb));
+    }
+    pdl_wait();
+    if (A.items) {
+        const tb200_gemv_item &it = A.items[blockIdx.y];
         ntok = it.ntok;
         if (ntok == 0) return;   // CTA-uniform
-        my_row0 = it.row0;
+        set_rows(it.row0);
 #pragma unroll
         for (int t = 0; t < T; ++t) orow[t] = it.out_row[min(t, ntok - 1)];
         if (threadIdx.x < T) s_arow[threadIdx.x] = it.a_row[min((int)threadIdx.x, ntok - 1)];
+        if (active) load_batch(0, min(nsbc, nsb));
     } else if (threadIdx.x < T) s_arow[threadIdx.x] = threadIdx.x;
     __syncthreads();
+
     float acc[R][T];
 #pragma unroll
     for (int r = 0; r < R; ++r)
 #pragma unroll
         for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
-    const int p = lane & 7, c = p >> 1, h = p & 1;
+
     for (long sb0 = 0; sb0 < nsb; sb0 += nsbc) {
         const long cnt = min(nsbc, nsb - sb0);
         if (sb0) __syncthreads();
 #pragma unroll
         for (int t = 0; t < T; ++t) {
-            const uint4 *src = reinterpret_cast<const uint4 *>(aq + (long)s_arow[t] * a_stride + sb0 * QK_K);
-            const int2 *dsrc = ads + (long)s_arow[t] * (a_stride / QK) + sb0 * 8;
+            const uint4 *src = reinterpret_cast<const uint4 *>(A.aq + (long)s_arow[t] * A.a_stride + sb0 * QK_K);
+            const int2 *dsrc = A.ads + (long)s_arow[t] * (A.a_stride / QK) + sb0 * 8;
             for (int g = threadIdx.x; g < (int)cnt * 16; g += kWarps * 32) {   // g = 16-byte piece of this chunk of the activation row
                 const int sb = g >> 4, gi = g & 15, cc = gi >> 2, hl = (gi >> 1) & 1, hh = gi & 1;
                 (hl ? s_hi : s_lo)[(t * (int)nsbc + sb) * 8 + 2 * cc + hh] = src[g];
@@ -345,49 +398,44 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const uint4 *__r
         }
         __syncthreads();
         if (!active) continue;
-        for (long sb = lane >> 3; sb < cnt; sb += 4) {
-            uint4 w[R], hdr[R];
+        for (long sbb = 0; sbb < cnt; sbb += 4 * U) {
+            if (sb0 | sbb) load_batch(sb0 + sbb, sb0 + cnt);
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const long row = my_row0 + min(r_base + r, nrows - 1);
-                w[r] = ldg_stream(qs + (row * nsb + sb0 + sb) * 8 + p);
-                hdr[r] = __ldg(sc + row * nsb + sb0 + sb);
-            }
+            for (int u = 0; u < U; ++u) {
+                const long sb = sbb + grp + 4 * u;   // chunk-relative
+                if (sb < cnt) {
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr[r].x);
-                const float d = __low2float(dd), dmin = __high2float(dd);
-                int sc_lo, m_lo, sc_hi, m_hi;
-                q4k_scale_min(hdr[r], 2 * c, sc_lo, m_lo);
-                q4k_scale_min(hdr[r], 2 * c + 1, sc_hi, m_hi);
-                const unsigned wl0 = w[r].x & 0x0f0f0f0fu, wl1 = w[r].y & 0x0f0f0f0fu, wl2 = w[r].z & 0x0f0f0f0fu, wl3 = w[r].w & 0x0f0f0f0fu;
-                const unsigned wh0 = w[r].x & 0xf0f0f0f0u, wh1 = w[r].y & 0xf0f0f0f0u, wh2 = w[r].z & 0xf0f0f0f0u, wh3 = w[r].w & 0xf0f0f0f0u;   // 16*q
+                    for (int r = 0; r < R; ++r) {
+                        const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr[u][r].x);
+                        const float d = __low2float(dd), dmin = __high2float(dd);
+                        int sc_lo, m_lo, sc_hi, m_hi;
+                        q4k_scale_min(hdr[u][r], 2 * c, sc_lo, m_lo);
+                        q4k_scale_min(hdr[u][r], 2 * c + 1, sc_hi, m_hi);
+                        const uint4 wv = w[u][r];
+                        const unsigned wl0 = wv.x & 0x0f0f0f0fu, wl1 = wv.y & 0x0f0f0f0fu, wl2 = wv.z & 0x0f0f0f0fu, wl3 = wv.w & 0x0f0f0f0fu;
+                        const unsigned wh0 = wv.x & 0xf0f0f0f0u, wh1 = wv.y & 0xf0f0f0f0u, wh2 = wv.z & 0xf0f0f0f0u, wh3 = wv.w & 0xf0f0f0f0u;   // 16*q
 #pragma unroll
-                for (int t = 0; t < T; ++t) {
-                    const long base = (t * nsbc + sb) * 8;
-                    const uint4 al = s_lo[base + p], ah = s_hi[base + p];
-                    int sl = dp4a_us(wl0, (int)al.x, 0);
-                    sl = dp4a_us(wl1, (int)al.y, sl), sl = dp4a_us(wl2, (int)al.z, sl), sl = dp4a_us(wl3, (int)al.w, sl);
-                    int sh = dp4a_us(wh0, (int)ah.x, 0);
-                    sh = dp4a_us(wh1, (int)ah.y, sh), sh = dp4a_us(wh2, (int)ah.z, sh), sh = dp4a_us(wh3, (int)ah.w, sh);
-                    const int2 ds_lo = s_ds[base + 2 * c], ds_hi = s_ds[base + 2 * c + 1];
-                    const float dy = __int_as_float(ds_lo.x);
-                    const int isum = sc_lo * sl + sc_hi * (sh >> 4);
-                    const int msum = h == 0 ? m_lo * ds_lo.y + m_hi * ds_hi.y : 0;   // each sub-block's mins counted once
-                    acc[r][t] = fmaf(d * dy, (float)isum, acc[r][t]);
-                    acc[r][t] = fmaf(-(dmin * dy), (float)msum, acc[r][t]);
+                        for (int t = 0; t < T; ++t) {
+                            const long base = (t * nsbc + sb) * 8;
+                            const uint4 al = s_lo[base + p], ah = s_hi[base + p];
+                            int sl = dp4a_us(wl0, (int)al.x, 0);
+                            sl = dp4a_us(wl1, (int)al.y, sl), sl = dp4a_us(wl2, (int)al.z, sl), sl = dp4a_us(wl3, (int)al.w, sl);
+                            int sh = dp4a_us(wh0, (int)ah.x, 0);
+                            sh = dp4a_us(wh1, (int)ah.y, sh), sh = dp4a_us(wh2, (int)ah.z, sh), sh = dp4a_us(wh3, (int)ah.w, sh);
+                            const int2 ds_lo = s_ds[base + 2 * c], ds_hi = s_ds[base + 2 * c + 1];
+                            const float dy = __int_as_float(ds_lo.x);
+                            const int isum = sc_lo * sl + sc_hi * (sh >> 4);
+                            const int msum = h == 0 ? m_lo * ds_lo.y + m_hi * ds_hi.y : 0;   // each sub-block's mins counted once
+                            acc[r][t] = fmaf(d * dy, (float)isum, acc[r][t]);
+                            acc[r][t] = fmaf(-(dmin * dy), (float)msum, acc[r][t]);
+                        }
+                    }
                 }
             }
         }
     }
     if (!active) return;
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-#pragma unroll
-        for (int t = 0; t < T; ++t) {
-            const float v = warp_sum(acc[r][t]);
-            if (lane == 0 && r_base + r < nrows && t < ntok) out[(long)orow[t] * ldo + r_base + r] = v;
-        }
+    store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane);
 }
 
 // ---- F16 ----------------------------------------------------------------------------------------
@@ -524,6 +572,30 @@ int set_smem(K kernel, size_t bytes) {
     return TB200_OK;
 }
 
+// kernel arguments of the Q4_0 / Q4_K decode kernels from the launcher-level request: concatenated row tiles of up to
+// kMaxMats matrices, optional peer bases for the fused all-gather
+template <int R>
+int fill_args(GemvQ4Args &ka, const tb200_gemv_args &a, long nb, long nbc) {
+    memset(&ka, 0, sizeof(ka));
+    ka.nmat = a.nmat > 0 ? a.nmat : 1;
+    int ctas = 0;
+    for (int m = 0; m < ka.nmat; ++m) {
+        const tb200_weights *wm = m == 0 ? a.w : a.w_more[m - 1];
+        const long nr = m == 0 ? a.nrows : wm->rows;
+        ka.cta_begin[m] = ctas;
+        ctas += (int)((nr + kWarps * R - 1) / (kWarps * R));
+        ka.qs[m] = wm->qs, ka.sc[m] = wm->sc;
+        ka.row0[m] = m == 0 ? a.row0 : 0, ka.nrows[m] = nr;
+        ka.out[m] = m == 0 ? a.out : a.out_more[m - 1], ka.ldo[m] = m == 0 ? a.ldo : a.ldo_more[m - 1];
+    }
+    ka.cta_begin[ka.nmat] = ctas;
+    ka.nb = nb, ka.nbc = nbc, ka.aq = a.aq, ka.ads = a.ads, ka.a_stride = a.a_stride, ka.items = a.items;
+    ka.world = a.world > 1 ? a.world : 1;
+    ka.local_base = (const char *)a.local_base;
+    for (int p = 0; p < TB200_MAX_PEERS; ++p) ka.peer_base[p] = p < ka.world ? (char *)a.peer_base[p] : nullptr;
+    return ctas;
+}
+
 constexpr size_t kSmemBudget = 96 * 1024;   // activation staging per CTA; larger T*K is walked in K chunks
 
 template <int T, int R>
@@ -540,20 +612,7 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         const size_t smem = (size_t)T * nbc * 40;
         if (w->type == TB200_TYPE_Q4_0) {
             GemvQ4Args ka;
-            memset(&ka, 0, sizeof(ka));
-            ka.nmat = a.nmat > 0 ? a.nmat : 1;
-            int ctas = 0;
-            for (int m = 0; m < ka.nmat; ++m) {
-                const tb200_weights *wm = m == 0 ? w : a.w_more[m - 1];
-                const long nr = m == 0 ? a.nrows : wm->rows;
-                ka.cta_begin[m] = ctas;
-                ctas += (int)((nr + kWarps * R - 1) / (kWarps * R));
-                ka.qs[m] = (const uint4 *)wm->qs, ka.sc[m] = (const __half *)wm->sc;
-                ka.row0[m] = m == 0 ? a.row0 : 0, ka.nrows[m] = nr;
-                ka.out[m] = m == 0 ? a.out : a.out_more[m - 1], ka.ldo[m] = m == 0 ? a.ldo : a.ldo_more[m - 1];
-            }
-            ka.cta_begin[ka.nmat] = ctas;
-            ka.nb = nb, ka.nbc = nbc, ka.aq = a.aq, ka.ads = a.ads, ka.a_stride = a.a_stride, ka.items = a.items;
+            const int ctas = fill_args<R>(ka, a, nb, nbc);
             const dim3 g2((unsigned)ctas, grid.y);
             if ((rc = set_smem(gemv_q4_0_kernel<T, R>, smem))) return rc;
             TB_CUDA(tb200_launch(gemv_q4_0_kernel<T, R>, g2, dim3(kWarps * 32), smem, c->stream, ka));
@@ -569,9 +628,11 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         long nsbc = (long)(kSmemBudget / ((size_t)T * 320)) / 4 * 4;
         if (nsbc >= nsb) nsbc = nsb;
         const size_t smem = (size_t)T * nsbc * 320;
+        GemvQ4Args ka;
+        const int ctas = fill_args<R>(ka, a, nsb, nsbc);
+        const dim3 g2((unsigned)ctas, grid.y);
         if ((rc = set_smem(gemv_q4_K_kernel<T, R>, smem))) return rc;
-        TB_CUDA(tb200_launch(gemv_q4_K_kernel<T, R>, grid, dim3(kWarps * 32), smem, c->stream, (const uint4 *)w->qs, (const uint4 *)w->sc, nsb, nsbc, a.row0, a.nrows,
-                                                                      a.aq, a.ads, a.a_stride, a.out, a.ldo, a.items));
+        TB_CUDA(tb200_launch(gemv_q4_K_kernel<T, R>, g2, dim3(kWarps * 32), smem, c->stream, ka));
         break;
     }
     case TB200_TYPE_F16: {

@@ -44,6 +44,10 @@ def lib() -> C.CDLL:
         "tb200_mul_mat_multi": (i, [i, vp, vp, l, l, vp, vp]),
         "tb200_acts_create": (vp, [i, l, l]), "tb200_acts_quantize": (i, [vp, vp, l, l]),
         "tb200_mul_mat_acts": (i, [vp, vp, vp, l]), "tb200_mul_mat_acts_multi": (i, [i, vp, vp, vp, vp]), "tb200_acts_free": (None, [vp]),
+        "tb200_ipc_get_handle": (i, [vp, vp]), "tb200_ipc_open_handle": (vp, [vp]), "tb200_ipc_close_handle": (i, [vp]),
+        "tb200_peers_create": (vp, [i, i, vp, vp]), "tb200_peers_free": (None, [vp]), "tb200_peers_barrier": (i, [vp]),
+        "tb200_peers_timed_out": (i, [vp]), "tb200_memset": (i, [vp, i, sz]),
+        "tb200_mul_mat_acts_multi_gather": (i, [vp, i, vp, vp, vp, vp, vp]),
         "tb200_blockdot_dev": (i, [vp, vp, i, vp]), "tb200_mixmul_dev": (i, [vp, i, vp, i, vp, i, l, vp]),
         "tb200_malloc": (vp, [sz]), "tb200_free": (None, [vp]), "tb200_memcpy_h2d": (i, [vp, vp, sz]),
         "tb200_memcpy_d2h": (i, [vp, vp, sz]), "tb200_host_alloc": (vp, [sz]), "tb200_host_free": (None, [vp]),
