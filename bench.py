@@ -177,6 +177,7 @@ def run_b200_arm(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = os.environ.get("TB200_NCCL_DEBUG", "WARN")   # keep NCCL's version banner off stdout: ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from llamafile_b200.build import build
     build()
@@ -247,11 +248,29 @@ def run_b200_arm(args):
         staging.append(st)
         gathered.append(torch.empty(world, st.shape[1], device=dev, dtype=torch.float32) if world > 1 else None)
 
+    # multi-GPU exchange: "p2p" = the decode kernels store their rows into every rank's symmetric buffer over NVLink
+    # (fused all-gather, one flag barrier per launch group); "nccl" = ncclAllGather of the staging rows per launch group
+    pg, p2p_off = None, None
+    if world > 1 and args.gather == "p2p":
+        from llamafile_b200.peer import PeerGroup
+        p2p_off, off = [], 0
+        for (_, N, lo, hi, K, g, w) in mats:
+            p2p_off.append(off)
+            off += N * 4
+        pg = PeerGroup(world, rank, off)
+
     def step(with_gather=True, with_quant=True):
         for gi, (grp, idx) in enumerate(schedule):
             x, acts = groups[grp]
             if with_quant:
                 acts.quantize(x, 1)
+            if pg is not None and with_gather:
+                live = [i for i in idx if mats[i][3] > mats[i][2]]
+                if live:
+                    pg.mul_mat_gather([mats[i][6] for i in live], acts, [p2p_off[i] for i in live], [mats[i][1] for i in live],
+                                      [mats[i][2] for i in live])
+                pg.barrier()
+                continue
             tb.mul_mat_acts_multi([mats[i][6] for i in idx], acts, [outs[i] for i in idx])
             if world > 1 and with_gather:
                 dist.all_gather_into_tensor(gathered[gi], staging[gi])
@@ -402,11 +421,13 @@ def run_b200_arm(args):
                 "data": "synthetic",
                 "config": {"workload": args.workload, "tokens": 1, "layers": layers, "matmuls_per_step": len(mats), "launches_per_step": len(schedule),
                            "weight_GB_per_step": total_step_bytes / 1e9, "l2": "distinct weights per step exceed L2 (126 MB) 30x; no flush needed",
-                           "cuda_graph": graphed, "parallelism": f"row-shard x{world} + NCCL all-gather" if world > 1 else "single GPU",
+                           "cuda_graph": graphed, "parallelism": (f"row-shard x{world} + " + ("fused all-gather (peer stores over NVLink + flag barrier per launch group)" if pg is not None else "NCCL all-gather per launch group")) if world > 1 else "single GPU",
                            "decode_tokens_per_s": 1e3 / ms_per_step},
                 "roofline": roofline, "per_shape": per_shape, "cpu_baseline": cpu_baseline, "e2e": e2e,
                 "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks}
         print(json.dumps(line), flush=True)
+    if pg is not None and pg.timed_out():
+        sys.stderr.write("bench: WARNING peer barrier timed out\n")
     log("line printed; leaving")
     if world > 1:
         dist.barrier()
@@ -425,6 +446,7 @@ def main():
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (debug)")
     ap.add_argument("--no-e2e", dest="e2e", action="store_false")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="multi-GPU output exchange")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay (debug)")
     args = ap.parse_args()
     args.warmup = max(3, args.warmup) if args.impl == "b200" else args.warmup

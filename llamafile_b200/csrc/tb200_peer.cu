@@ -16,10 +16,13 @@ struct BarrierArgs {
     int world, rank;
 };
 
-// Launched WITHOUT programmatic serialization: it starts only after the preceding GEMV has completed, i.e. after all of
-// this rank's peer stores have been issued and flushed. Thread p publishes this rank's epoch to rank p and waits for
-// rank p's epoch to arrive here. The wait is bounded (~2 s) so a missing peer cannot wedge the GPU.
+// Launched with programmatic serialization like every kernel of the module, so it is already resident when the preceding
+// GEMV drains; pdl_wait() returns once that GEMV has completed, i.e. after all of this rank's peer stores have been
+// issued and flushed. Thread p then publishes this rank's epoch to rank p and waits for rank p's epoch to arrive here.
+// The wait is bounded (~2 s) so a missing peer cannot wedge the GPU.
 __global__ void peer_barrier_kernel(const BarrierArgs a) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ uint32_t e;
     if (threadIdx.x == 0) e = ++(*a.epoch);
     __syncthreads();
@@ -93,9 +96,7 @@ int tb200_peers_barrier(tb200_peers *g) {
     BarrierArgs a;
     for (int p = 0; p < TB200_MAX_PEERS; ++p) a.flags[p] = g->flags[p];
     a.epoch = g->epoch, a.timeout_flag = g->timeout_flag, a.world = g->world, a.rank = g->rank;
-    peer_barrier_kernel<<<1, 32, 0, c->stream>>>(a);
-    tb200_count_launch();
-    TB_CUDA(cudaGetLastError());
+    TB_CUDA(tb200_launch(peer_barrier_kernel, dim3(1), dim3(32), 0, c->stream, a));
     return TB200_OK;
 }
 
