@@ -4,7 +4,10 @@
 // Same argument meaning and true/false behaviour as the CPU implementation; the work itself runs on the
 // GPU: weights are uploaded once and cached by host address, activations go H2D, results come D2H, and the
 // call returns when the result is in the caller's buffer. Nothing here computes on the CPU.
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #include <map>
 #include <mutex>
@@ -38,6 +41,155 @@ void *io_buffer(tb200_ctx *c, size_t bytes) {
     return io.p;
 }
 
+size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+// ---- decode lane: host-mapped staging, completion word, cached launch graphs ---------------------------------------
+// A decode-size call (n <= 8) moves a few KB each way, so its cost is latency, not bandwidth. Measured on the B200
+// box (tools/host_latency.py): every cudaLaunchKernelEx costs ~3.3 us of host time and a kernel starts several us
+// after its launch call, so "H2D copy, two kernels, D2H copy, cudaStreamSynchronize" is ~30 us around ~4 us of GPU
+// work. The lane cuts that down:
+//   * activation blocks are read by the unpack kernel straight from host-MAPPED pinned memory (the caller's own
+//     buffer when it is already pinned, else one memcpy into the lane's staging page): no copy-engine transfer;
+//   * a small C is stored by the decode kernel straight into mapped host memory; a large one (scattered 4-byte
+//     PCIe stores cost ~0.6 us per 1000 rows) goes to HBM and leaves through one copy-engine transfer;
+//   * completion is a sequence number published by a one-thread kernel (st.release.sys after griddepcontrol.wait,
+//     i.e. after every store of its predecessors is performed); the caller spins on that word instead of
+//     cudaStreamSynchronize();
+//   * the launches of one (weights, n, buffers) combination are captured once into a CUDA graph and replayed with a
+//     single cudaGraphLaunch on the lane's own stream (the entry points are synchronous, so nothing else orders on it).
+struct LaneKey {
+    const tb200_weights *w; long n; int btype; const void *dB; void *dC; long ldb, ldo; void *h_dst;
+    bool operator<(const LaneKey &o) const {
+        return std::tie(w, n, btype, dB, dC, ldb, ldo, h_dst) < std::tie(o.w, o.n, o.btype, o.dB, o.dC, o.ldb, o.ldo, o.h_dst);
+    }
+};
+struct HostLane {
+    uint8_t *in = nullptr;  size_t in_cap = 0;     // mapped pinned, host address == device address (UVA)
+    uint8_t *out = nullptr; size_t out_cap = 0;
+    uint8_t *dact = nullptr; size_t dact_cap = 0;  // device: activations in the kernels' planar form
+    uint8_t *dout = nullptr; size_t dout_cap = 0;  // device: large C before its D2H transfer
+    uint32_t *flag = nullptr;                      // mapped pinned completion word
+    uint32_t *dcount = nullptr;                    // device: publish counter (graph replays advance it)
+    uint32_t seq = 0;                              // host mirror of dcount
+    cudaStream_t stream = nullptr;
+    std::map<LaneKey, cudaGraphExec_t> graphs;     // exec == nullptr: seen once, not captured yet
+};
+HostLane g_lane[16];
+constexpr size_t kLaneDirectBytes = 32 * 1024;     // C up to this size is stored straight into host memory
+
+__global__ void publish_kernel(uint32_t *flag, uint32_t *count) {
+    pdl_launch_dependents();
+    pdl_wait();                                    // predecessor grid complete, its stores performed
+    const uint32_t v = *count + 1;
+    *count = v;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(v) : "memory");
+}
+// fp16 / f32 activations of the F16 path: every CTA re-reads them, so they must come from HBM, not over PCIe
+__global__ void stage_copy_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst, long n16, const uint8_t *src_tail, uint8_t *dst_tail, int tail) {
+    pdl_launch_dependents();
+    pdl_wait();
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n16; i += (long)gridDim.x * blockDim.x) dst[i] = src[i];
+    if (blockIdx.x == 0 && (int)threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail[threadIdx.x];
+}
+
+void lane_drop_graphs(HostLane &L) {
+    for (auto &kv : L.graphs)
+        if (kv.second) cudaGraphExecDestroy(kv.second);
+    L.graphs.clear();
+}
+
+bool lane_reserve_host(HostLane &L, uint8_t **p, size_t *cap, size_t bytes) {
+    if (bytes <= *cap) return true;
+    lane_drop_graphs(L);   // captured graphs hold the old address
+    if (*p) { cudaDeviceSynchronize(); cudaFreeHost(*p); *p = nullptr; *cap = 0; }
+    const size_t want = (bytes + bytes / 2 + 65535) & ~(size_t)65535;
+    if (cudaHostAlloc((void **)p, want, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError(); tb200_set_error("lane: cudaHostAlloc(%zu) failed", want); *p = nullptr; return false;
+    }
+    *cap = want;
+    return true;
+}
+bool lane_reserve_dev(HostLane &L, uint8_t **p, size_t *cap, size_t bytes) {
+    if (bytes <= *cap) return true;
+    lane_drop_graphs(L);
+    if (*p) { cudaDeviceSynchronize(); cudaFree(*p); *p = nullptr; *cap = 0; }
+    const size_t want = (bytes + bytes / 2 + 65535) & ~(size_t)65535;
+    if (cudaMalloc((void **)p, want) != cudaSuccess) { cudaGetLastError(); tb200_set_error("lane: cudaMalloc(%zu) failed", want); *p = nullptr; return false; }
+    *cap = want;
+    return true;
+}
+bool lane_init(HostLane &L) {
+    if (L.flag) return true;
+    if (cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (cudaMalloc((void **)&L.dcount, 64) != cudaSuccess || cudaMemset(L.dcount, 0, 64) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (cudaHostAlloc((void **)&L.flag, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return false; }
+    *L.flag = 0;
+    return true;
+}
+
+// device-usable alias of a host pointer that is already pinned (cudaHostAlloc / cudaHostRegister), else nullptr
+void *pinned_alias(const void *h) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, h) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
+}
+
+inline void cpu_relax() {
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#elif defined(__aarch64__)
+    asm volatile("yield" ::: "memory");
+#endif
+}
+
+// spin on the completion word; every ~4k spins look at the stream so a failed launch cannot hang the caller
+bool lane_wait(HostLane &L, uint32_t seq) {
+    volatile uint32_t *f = L.flag;
+    for (unsigned long spins = 1;; ++spins) {
+        if (*f == seq) { __atomic_thread_fence(__ATOMIC_ACQUIRE); return true; }
+        if ((spins & 0xfff) == 0) {
+            const cudaError_t q = cudaStreamQuery(L.stream);
+            if (q == cudaSuccess) { __atomic_thread_fence(__ATOMIC_ACQUIRE); return *f == seq; }
+            if (q != cudaErrorNotReady) { cudaGetLastError(); tb200_set_error("lane: stream error %s", cudaGetErrorString(q)); return false; }
+        }
+        cpu_relax();
+    }
+}
+
+// TB200_LANE_TRACE=1: cumulative wall time of the lane's phases, printed every 1024 calls (debug aid)
+struct LaneTrace { double prep = 0, launch = 0, wait = 0, out = 0; long calls = 0, replays = 0; };
+LaneTrace g_trace;
+bool env_flag(const char *name, int dflt) { const char *v = getenv(name); return v && *v ? *v != '0' : dflt != 0; }
+bool trace_enabled() { static const bool on = env_flag("TB200_LANE_TRACE", 0); return on; }
+bool lane_enabled() { static const bool on = env_flag("TB200_HOST_LANE", 1); return on; }
+bool lane_graphs_enabled() { static const bool on = env_flag("TB200_LANE_GRAPH", 1); return on; }
+double now_us() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; }
+
+// the launches of one decode call, on c->stream (which the caller has pointed at the lane's stream)
+int lane_issue(tb200_ctx *c, HostLane &L, const LaneKey &k, size_t b_bytes) {
+    const tb200_weights *w = k.w;
+    int rc;
+    if (w->type == TB200_TYPE_F16) {
+        const long n16 = (long)(b_bytes / 16);
+        const unsigned grid = (unsigned)((n16 + 255) / 256 > 0 ? (n16 + 255) / 256 : 1);
+        TB_CUDA(tb200_launch(stage_copy_kernel, dim3(grid < 1184u ? grid : 1184u), dim3(256), 0, c->stream, (const uint4 *)k.dB, (uint4 *)L.dact, n16,
+                             (const uint8_t *)k.dB + n16 * 16, L.dact + n16 * 16, (int)(b_bytes & 15)));
+        rc = tb200_run_matmul(c, w, 0, w->rows, nullptr, nullptr, L.dact, k.btype == TB200_TYPE_F32, k.ldb, k.n, (float *)k.dC, k.ldo);
+    } else {
+        int8_t *q = (int8_t *)L.dact;
+        int2 *ds = (int2 *)(L.dact + up256((size_t)k.n * w->k));
+        rc = w->type == TB200_TYPE_Q4_K ? tb200_launch_unpack_q8_K(c, k.dB, k.ldb, k.n, w->k, q, ds) : tb200_launch_unpack_q8_0(c, k.dB, k.ldb, k.n, w->k, q, ds);
+        if (rc) return rc;
+        rc = tb200_run_matmul(c, w, 0, w->rows, q, ds, nullptr, 0, w->k, k.n, (float *)k.dC, k.ldo);
+    }
+    if (rc) return rc;
+    if (k.h_dst)   // large C: HBM -> pinned host through the copy engine (h_dst rows are k.ldo_host apart; here dense)
+        TB_CUDA(cudaMemcpyAsync(k.h_dst, k.dC, (size_t)k.n * w->rows * 4, cudaMemcpyDeviceToHost, c->stream));
+    TB_CUDA(tb200_launch(publish_kernel, dim3(1), dim3(1), 0, c->stream, L.flag, L.dcount));
+    return TB200_OK;
+}
+
 tb200_weights *cached_weights(const void *A, int type, long rows, long k, size_t row_stride) {
     std::lock_guard<std::mutex> lk(g_cache_mu);
     const auto key = std::make_tuple(A, rows, k, row_stride, type);
@@ -50,7 +202,6 @@ tb200_weights *cached_weights(const void *A, int type, long rows, long k, size_t
 
 int blck(int type) { return (type == TB200_TYPE_Q4_K || type == TB200_TYPE_Q8_K) ? QK_K : (type == TB200_TYPE_Q4_0 || type == TB200_TYPE_Q8_0) ? QK : 1; }
 size_t tsize(int type) { return tb200_gguf_row_bytes(type, blck(type)); }
-size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 }  // namespace
 
@@ -58,6 +209,10 @@ extern "C" {
 
 TB200_API void tb200_weights_cache_clear(void) {
     std::lock_guard<std::mutex> lk(g_cache_mu);
+    for (HostLane &L : g_lane) {   // captured graphs hold weight pointers
+        if (L.stream) cudaStreamSynchronize(L.stream);
+        lane_drop_graphs(L);
+    }
     for (auto &kv : g_cache) tb200_weights_free(kv.second);
     g_cache.clear();
 }
@@ -79,6 +234,82 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
     tb200_weights *w = cached_weights(A, Atype, m, ke, a_stride);
     if (!w) return false;
     const size_t b_bytes = ((size_t)(n - 1) * ldb_eff + k) * tsize(Btype), c_bytes = (size_t)n * m * 4;
+    if (n <= TB200_GEMV_MAX_TOKENS && lane_enabled()) {
+        // decode lane (see HostLane)
+        const bool tr = trace_enabled();
+        const double t0 = tr ? now_us() : 0;
+        HostLane &L = g_lane[c->device];
+        if (!lane_init(L)) return false;
+        LaneKey key = {w, n, Btype, pinned_alias(B), nullptr, ldb_eff, ldc, nullptr};
+        if (!key.dB || (Atype == TB200_TYPE_F16 && ((uintptr_t)key.dB & 15))) {   // the fp16/f32 stage copy moves 16-byte words
+            if (!lane_reserve_host(L, &L.in, &L.in_cap, b_bytes)) return false;
+            memcpy(L.in, B, b_bytes);
+            key.dB = L.in;
+        }
+        void *pinC = pinned_alias(C);
+        if (c_bytes <= kLaneDirectBytes) {   // kernels store C over PCIe
+            key.dC = pinC;
+            if (!key.dC) {
+                if (!lane_reserve_host(L, &L.out, &L.out_cap, c_bytes)) return false;
+                key.dC = L.out, key.ldo = m;
+            }
+        } else {                             // HBM, then one D2H transfer into pinned memory
+            if (!lane_reserve_dev(L, &L.dout, &L.dout_cap, c_bytes)) return false;
+            key.dC = L.dout, key.ldo = m;
+            key.h_dst = (pinC && (ldc == m || n == 1)) ? (void *)C : nullptr;
+            if (!key.h_dst) {
+                if (!lane_reserve_host(L, &L.out, &L.out_cap, c_bytes)) return false;
+                key.h_dst = L.out;
+            }
+        }
+        const size_t act_bytes = Atype == TB200_TYPE_F16 ? up256(b_bytes) : up256((size_t)n * ke) + up256((size_t)n * (ke / QK) * 8);
+        if (!lane_reserve_dev(L, &L.dact, &L.dact_cap, act_bytes)) return false;
+        const double t1 = tr ? now_us() : 0;
+
+        const uint32_t seq = ++L.seq;
+        bool ok = true;
+        auto it = lane_graphs_enabled() ? L.graphs.find(key) : L.graphs.end();
+        if (it != L.graphs.end() && it->second) {
+            ok = cudaGraphLaunch(it->second, L.stream) == cudaSuccess;
+            if (tr) ++g_trace.replays;
+        } else {
+            cudaStream_t user = c->stream;
+            c->stream = L.stream;
+            const bool capture = lane_graphs_enabled() && it != L.graphs.end();   // second sighting: kernel attributes are set, buffers sized
+            if (capture) ok = cudaStreamBeginCapture(L.stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+            if (ok) ok = lane_issue(c, L, key, b_bytes) == TB200_OK;
+            if (capture) {
+                cudaGraph_t g = nullptr;
+                const bool ended = cudaStreamEndCapture(L.stream, &g) == cudaSuccess && g;
+                cudaGraphExec_t ex = nullptr;
+                ok = ok && ended && cudaGraphInstantiate(&ex, g, 0) == cudaSuccess;
+                if (g) cudaGraphDestroy(g);
+                if (ok) { it->second = ex; ok = cudaGraphLaunch(ex, L.stream) == cudaSuccess; }
+            } else if (ok && lane_graphs_enabled()) L.graphs[key] = nullptr;
+            c->stream = user;
+        }
+        if (!ok) {
+            cudaGetLastError();
+            cudaStreamSynchronize(L.stream);
+            // resynchronise the host mirror with the device counter so later calls keep working
+            cudaMemcpy(&L.seq, L.dcount, 4, cudaMemcpyDeviceToHost);
+            return false;
+        }
+        const double t2 = tr ? now_us() : 0;
+        if (!lane_wait(L, seq)) return false;
+        const double t3 = tr ? now_us() : 0;
+        const float *src = key.h_dst ? (const float *)key.h_dst : (const float *)key.dC;
+        if ((const void *)src == (const void *)L.out)
+            for (long j = 0; j < n; ++j) memcpy((float *)C + j * ldc, src + j * m, (size_t)m * 4);
+        if (tr) {
+            LaneTrace &T = g_trace;
+            T.prep += t1 - t0, T.launch += t2 - t1, T.wait += t3 - t2, T.out += now_us() - t3;
+            if (++T.calls % 1024 == 0)
+                fprintf(stderr, "tb200 lane: %ld calls (%ld graph replays), per call us: prep %.2f launch %.2f wait %.2f copy-out %.2f\n", T.calls,
+                        T.replays, T.prep / T.calls, T.launch / T.calls, T.wait / T.calls, T.out / T.calls);
+        }
+        return true;
+    }
     uint8_t *io = (uint8_t *)io_buffer(c, up256(b_bytes) + c_bytes);
     if (!io) return false;
     float *dC = (float *)(io + up256(b_bytes));

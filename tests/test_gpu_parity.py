@@ -181,6 +181,30 @@ def test_llamafile_sgemm_host(tb, oracle, wt, n):
     tb.weights_cache_clear()
 
 
+@pytest.mark.parametrize("wt", H.WEIGHT_TYPES)
+def test_llamafile_sgemm_host_pinned_buffers(tb, oracle, wt):
+    """Decode lane with the caller's buffers already pinned: the kernels read B and write C in place (ldc honoured),
+    and repeated calls keep returning complete results (the completion word is a sequence number)."""
+    import torch
+    m, K, n = 328, 2048, 2
+    W = H.make_weights(wt, m, K, seed=3, realistic_q4k=False)
+    kb = K // B.BLCK[wt]
+    vdt = B.VEC_DOT_TYPE[wt]
+    ldc = m + 24
+    for rep in range(4):
+        X = H.make_acts(n, K, seed=40 + rep)
+        Bq = oracle.from_float(X, vdt)
+        hB = torch.from_numpy(Bq.view(np.uint8).reshape(-1).copy()).pin_memory()
+        hC = torch.full((n, ldc), float("nan")).pin_memory()
+        assert tb.llamafile_sgemm(m, n, kb, W, kb, hB.numpy(), kb, hC.numpy(), ldc, 0, 1, wt, vdt, H.F32)
+        ok, Cr = oracle.sgemm(m, n, kb, W, kb, Bq, kb, ldc, wt, vdt)
+        assert ok
+        Cm = hC.numpy()
+        assert np.isnan(Cm[:, m:]).all()
+        H.assert_close(Cm[:, :m], Cr[:, :m], f"pinned rep {rep}")
+    tb.weights_cache_clear()
+
+
 def test_llamafile_sgemm_rejects_like_reference(tb):
     W = np.zeros(18 * 8 * 4, np.uint8); X = np.zeros((1, 256), np.float32); Cm = np.full((1, 4), np.nan, np.float32)
     assert not tb.llamafile_sgemm(4, 1, 8, W, 8, X, 256, Cm, 4, 0, 1, H.Q4_0, H.F32, H.F32)    # WANT_QUANTIZATION
