@@ -1,5 +1,13 @@
-// Prefill path (SURVEY.md §8 rows a9-a12 at n > 8): quant tiles staged by TMA, dequantised to fp16 in shared
-// memory, fed to tcgen05.mma (cta_group::1, M=128, N<=256, K=16 per instruction) with fp32 accumulators in TMEM.
+// Prefill path (SURVEY.md §8 rows a9-a12 at n > 8): quant tiles staged by TMA, dequantised to fp16 and fed to
+// tcgen05.mma (cta_group::1, M=128, N<=256, K=16 per instruction) with fp32 accumulators in TMEM.
+//
+// Where the dequantised weights live: the first version wrote A' to shared memory (SS form of the MMA) and ran at
+// ~980 clk per 64-wide K stage against 512 clk of tensor time: per stage the SM's shared memory had to move 16 KB of
+// A' stores + 16 KB of A' reads + 32 KB of B' TMA fill + 32 KB of B' reads + the packed tile, ~104 KB = 203 B/clk
+// against 128 B/clk. A' therefore goes to TENSOR MEMORY instead (tcgen05.st by the dequant warps, TS form of the
+// MMA: A from TMEM, B from shared memory): a ring of kStages x 32 columns next to the accumulator. Shared memory then
+// only carries B' and the packed tile (72 KB per stage, 140 B/clk). F16 weights need no dequantisation and keep the
+// SS form (TMA writes the swizzled A tile).
 //
 // Arithmetic contract (DESIGN.md "prefill numerics"): the reference computes sum_b d_x[b]*d_y[b]*sum_j q_x*q_y with
 // exact int32 block sums (llamafile/iqk_mul_mat.inc:1129-1201, tinyblas_cpu.h:934-993). Here both operands are
@@ -15,7 +23,8 @@
 // the activation prep kernel writes B' in that same order, which saves all byte permutes in the dequant loop.
 //
 // Warp roles (384 threads, 1 CTA / SM): warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator,
-// warps 4-11 dequantisers (and, after the main loop, TMEM->register->global epilogue).
+// warps 4-11 dequantisers (and, after the main loop, TMEM->register->global epilogue). TMEM lane = weight row, so
+// dequant warp w owns rows 32*(w&3).. and the K half (w-4)>>2 of every stage.
 #include <cuda.h>
 
 #include "tb200_common.cuh"
@@ -50,7 +59,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
                  "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
@@ -73,6 +81,22 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
+// A from tensor memory (lane = row, 2 fp16 per 32-bit column, 8 columns per K=16 slice), B from shared memory
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}" ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]),
+        "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -88,6 +112,53 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// ---- CTA-pair (cta_group::2) forms -------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t smem_addr, uint32_t rank) {   // same offset in CTA `rank` of the cluster
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load into THIS CTA's shared memory whose bytes are counted on the barrier at `bar_cluster_addr` (the pair leader's)
+__device__ __forceinline__ void tma_load_2d_pair(void *dst, const CUtensorMap *map, uint32_t bar_cluster_addr, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+                 "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t *dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_f16_ts_pair(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}" ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives (once all prior MMAs of this thread have retired) on the barrier at the same offset in both CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+                 "h"((uint16_t)3) : "memory");
+}
+
 // shared-memory matrix descriptor, K-major, SWIZZLE_128B (cute::UMMA::SmemDescriptor bit layout): start>>4 [0,14),
 // LBO>>4 [16,30) (ignored for swizzled K-major, canonical value 1), SBO>>4 [32,46) = 8 rows x 128 B = 1024 B,
 // version=1 [46,48), layout_type=2 (SWIZZLE_128B) [61,64)
@@ -99,11 +170,6 @@ __device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr) {
 __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) { return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24); }
 
 // ------------------------------------------------------------------------------------------------ dequantisers
-// Each dequant thread owns (row = tid>>1, half = tid&1) of the 128 x 64 stage tile and writes 4 16-byte chunks of
-// fp16 into the SWIZZLE_128B A tile: chunk c of row r lives at r*128 + ((c ^ (r & 7)) << 4).
-__device__ __forceinline__ void store_chunk(uint8_t *a_tile, int row, int c, uint4 v) {
-    *reinterpret_cast<uint4 *>(a_tile + row * 128 + ((c ^ (row & 7)) << 4)) = v;
-}
 __device__ __forceinline__ uint32_t h2_sub_mul(uint32_t x, __half2 sub, __half2 mul) {
     const __half2 r = __hmul2(__hsub2(*reinterpret_cast<const __half2 *>(&x), sub), mul);
     return *reinterpret_cast<const uint32_t *>(&r);
@@ -153,6 +219,12 @@ __device__ __forceinline__ void q4k_scale_min(const uint4 hdr, int j, int &sc, i
     else { sc = (byte(j + 4) & 0xF) | ((byte(j - 4) >> 6) << 4); m = (byte(j + 4) >> 4) | ((byte(j) >> 6) << 4); }
 }
 
+__host__ __device__ constexpr uint32_t tmem_cols_pow2(uint32_t need) {
+    uint32_t c = 32;
+    while (c < need) c <<= 1;
+    return c;
+}
+
 struct GemmParams {
     const void *sc;        // scales plane of the weights
     long sc_row_stride;    // in elements of the plane (fp16 for Q4_0/Q8_0, uint4 for Q4_K)
@@ -167,19 +239,95 @@ struct GemmParams {
     long n_tiles;
 };
 
+// ------------------------------------------------------------------------------------------------ dequant warps
+// One dequant thread owns weight row `row` of the CTA tile (= its TMEM lane) and the K half `chalf` (32 elements) of
+// every 64-wide stage. RowDequant carries that thread's scale stream: the scale of stage i+1 is fetched from global
+// memory while stage i is being processed. regs() turns the thread's 16 (Q4_0/Q4_K) or 32 (Q8_0) packed bytes of the
+// staged tile into 32 fp16 = 16 registers, ready for one tcgen05.st.32x32b.x16.
+template <int kType>
+struct RowDequant {
+    const __half *scp;    // Q4_0 / Q8_0: fp16 d of this row, element [2*i + chalf] belongs to stage i
+    const uint4 *hdp;     // Q4_K: {d, dmin, scales[12]} of this row, one per 256 elements = 4 stages
+    __half d_next;
+    uint4 hdr_next;
+    int row, chalf;
+
+    __device__ __forceinline__ RowDequant(const GemmParams &p, long grow, int row_, int chalf_) : row(row_), chalf(chalf_) {
+        scp = reinterpret_cast<const __half *>(p.sc) + grow * p.sc_row_stride + chalf_;
+        hdp = reinterpret_cast<const uint4 *>(p.sc) + grow * p.sc_row_stride;
+        d_next = __float2half(0.f);
+        hdr_next = make_uint4(0, 0, 0, 0);
+        if (kType == TB200_TYPE_Q4_K) hdr_next = __ldg(hdp);
+        else d_next = scp[0];
+    }
+    // call before waiting for stage i's packed tile: takes stage i's scale and puts stage i+1's fetch in flight
+    __device__ __forceinline__ void advance(int i, int kt, __half2 &d2, uint4 &hdr) {
+        if (kType == TB200_TYPE_Q4_K) {
+            hdr = hdr_next;
+            if ((i & 3) == 3 && i + 1 < kt) hdr_next = __ldg(hdp + ((i + 1) >> 2));
+        } else {
+            d2 = __half2half2(d_next);
+            if (i + 1 < kt) d_next = scp[(i + 1) * 2];
+        }
+    }
+    // tile: this stage's packed quant tile in shared memory (TMA, 32B swizzle for 32-byte rows, 64B swizzle for 64-byte rows)
+    __device__ __forceinline__ void regs(const uint8_t *tile, int i, __half2 d2, const uint4 &hdr, uint32_t (&r)[16]) const {
+        if (kType == TB200_TYPE_Q4_0) {
+            // SWIZZLE_32B, 32-byte rows: 16-byte chunk c of row r sits at chunk c ^ ((r >> 2) & 1)
+            const uint4 w = *reinterpret_cast<const uint4 *>(tile + row * 32 + ((chalf ^ ((row >> 2) & 1)) << 4));
+            uint4 o;
+            o = dequant_q4_word(w.x, d2), r[0] = o.x, r[1] = o.y, r[2] = o.z, r[3] = o.w;
+            o = dequant_q4_word(w.y, d2), r[4] = o.x, r[5] = o.y, r[6] = o.z, r[7] = o.w;
+            o = dequant_q4_word(w.z, d2), r[8] = o.x, r[9] = o.y, r[10] = o.z, r[11] = o.w;
+            o = dequant_q4_word(w.w, d2), r[12] = o.x, r[13] = o.y, r[14] = o.z, r[15] = o.w;
+        } else if (kType == TB200_TYPE_Q8_0) {
+            // SWIZZLE_64B, 64-byte rows: chunk c of row r sits at chunk c ^ ((r >> 1) & 3)
+            const uint8_t *rp = tile + row * 64;
+            const int sw = (row >> 1) & 3;
+            const uint4 w0 = *reinterpret_cast<const uint4 *>(rp + (((chalf * 2) ^ sw) << 4));
+            const uint4 w1 = *reinterpret_cast<const uint4 *>(rp + (((chalf * 2 + 1) ^ sw) << 4));
+            uint2 a;
+            a = dequant_q8_word(w0.x, d2), r[0] = a.x, r[1] = a.y;
+            a = dequant_q8_word(w0.y, d2), r[2] = a.x, r[3] = a.y;
+            a = dequant_q8_word(w0.z, d2), r[4] = a.x, r[5] = a.y;
+            a = dequant_q8_word(w0.w, d2), r[6] = a.x, r[7] = a.y;
+            a = dequant_q8_word(w1.x, d2), r[8] = a.x, r[9] = a.y;
+            a = dequant_q8_word(w1.y, d2), r[10] = a.x, r[11] = a.y;
+            a = dequant_q8_word(w1.z, d2), r[12] = a.x, r[13] = a.y;
+            a = dequant_q8_word(w1.w, d2), r[14] = a.x, r[15] = a.y;
+        } else {   // Q4_K: stage i is 64-element chunk c = i & 3 of super-block i >> 2
+            const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr.x);
+            const float d = __low2float(dd), dmin = __high2float(dd);
+            int sc_lo, m_lo, sc_hi, m_hi;
+            q4k_scale_min(hdr, 2 * (i & 3), sc_lo, m_lo);
+            q4k_scale_min(hdr, 2 * (i & 3) + 1, sc_hi, m_hi);
+            const __half2 a_lo = __float2half2_rn(d * sc_lo), b_lo = __float2half2_rn(-(dmin * m_lo));
+            const __half2 a_hi = __float2half2_rn(d * sc_hi), b_hi = __float2half2_rn(-(dmin * m_hi));
+            const uint4 w = *reinterpret_cast<const uint4 *>(tile + row * 32 + ((chalf ^ ((row >> 2) & 1)) << 4));
+            uint4 o;
+            o = dequant_q4K_word(w.x, a_lo, b_lo, a_hi, b_hi), r[0] = o.x, r[1] = o.y, r[2] = o.z, r[3] = o.w;
+            o = dequant_q4K_word(w.y, a_lo, b_lo, a_hi, b_hi), r[4] = o.x, r[5] = o.y, r[6] = o.z, r[7] = o.w;
+            o = dequant_q4K_word(w.z, a_lo, b_lo, a_hi, b_hi), r[8] = o.x, r[9] = o.y, r[10] = o.z, r[11] = o.w;
+            o = dequant_q4K_word(w.w, a_lo, b_lo, a_hi, b_hi), r[12] = o.x, r[13] = o.y, r[14] = o.z, r[15] = o.w;
+        }
+    }
+};
+
 // ------------------------------------------------------------------------------------------------ the kernel
 // kType: weight type. BN: token tile (UMMA N). kStages: pipeline depth.
 template <int kType, int BN, int kStages>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                                                                    const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+    constexpr bool kTS = kType != TB200_TYPE_F16;   // A' in tensor memory (dequantised types) or in shared memory (F16, via TMA)
     constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 0 : BM * BK / 2);
-    constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2;
-    constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;   // power of two >= 32 (BN is 32/64/128/256)
+    constexpr int kABytes = kTS ? 0 : BM * BK * 2, kBBytes = BN * BK * 2;
+    constexpr uint32_t kAccCols = BN < 32 ? 32 : BN;                 // accumulator columns [0, kAccCols)
+    constexpr uint32_t kTmemCols = tmem_cols_pow2(kAccCols + (kTS ? kStages * 32 : 0));   // A' ring: 32 columns (64 fp16) per stage
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint8_t *sA = smem;                                   // [kStages][BM x 128 B]  swizzled fp16 A'
+    uint8_t *sA = smem;                                   // [kStages][BM x 128 B]  swizzled fp16 A (F16 weights only)
     uint8_t *sB = sA + kStages * kABytes;                 // [kStages][BN x 128 B]  swizzled fp16 B' (TMA)
-    uint8_t *sP = sB + kStages * kBBytes;                 // [kStages][packed quant tile] (TMA)
+    uint8_t *sP = sB + kStages * kBBytes;                 // [kStages][packed quant tile] (TMA, 32B/64B swizzle)
     uint64_t *bars = reinterpret_cast<uint64_t *>(sP + kStages * (kPackedBytes ? kPackedBytes : 16));
     uint64_t *full_p = bars, *full_a = bars + kStages, *full_b = bars + 2 * kStages, *empty = bars + 3 * kStages, *accum_full = bars + 4 * kStages;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(accum_full + 1);
@@ -244,65 +392,45 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
                 mbar_wait(&full_a[s], ph);
                 mbar_wait(&full_b[s], ph);
                 tc_fence_after();
-                const uint64_t da = make_desc_sw128(smem_u32(sA + s * kABytes)), db = make_desc_sw128(smem_u32(sB + s * kBBytes));
+                const uint64_t db = make_desc_sw128(smem_u32(sB + s * kBBytes));
+                if (kTS) {
+                    const uint32_t ta = tmem_base + kAccCols + (uint32_t)s * 32;
 #pragma unroll
-                for (int kk = 0; kk < BK / 16; ++kk)   // advance 16 elements = 32 bytes inside the swizzle atom
-                    umma_f16(tmem_base, da + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), idesc, (i | kk) ? 1u : 0u);
+                    for (int kk = 0; kk < BK / 16; ++kk)   // K=16 slice: 8 TMEM columns of A', 32 bytes inside B's swizzle atom
+                        umma_f16_ts(tmem_base, ta + (uint32_t)(kk * 8), db + (uint64_t)(kk * 2), idesc, (i | kk) ? 1u : 0u);
+                } else {
+                    const uint64_t da = make_desc_sw128(smem_u32(sA + s * kABytes));
+#pragma unroll
+                    for (int kk = 0; kk < BK / 16; ++kk)
+                        umma_f16(tmem_base, da + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), idesc, (i | kk) ? 1u : 0u);
+                }
                 umma_commit(&empty[s]);                 // frees the stage when these MMAs have read it
             }
             umma_commit(accum_full);
         }
     } else if (warp >= 4) {
-        // ===== dequantisers =====
-        const int tid = threadIdx.x - 128;            // 0..255
-        const int row = tid >> 1, half = tid & 1;
+        // ===== dequantisers: packed tile (smem) -> fp16 -> tensor memory =====
+        const int quad = warp & 3, chalf = (warp - 4) >> 2;
+        const int row = quad * 32 + lane;             // TMEM lane == weight row of the tile
         const long grow = w_row0 + min(tile_row + row, p.nrows - 1);   // clamp rows past the matrix end (their outputs are masked)
-        if (kType != TB200_TYPE_F16) {
+        if (kTS) {
+            const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCols + (uint32_t)(chalf * 16);
+            RowDequant<kType> dq(p, grow, row, chalf);
             for (int i = 0; i < kt; ++i) {
                 const int s = i % kStages;
                 const uint32_t ph = (i / kStages) & 1;
-                uint8_t *a_tile = sA + s * kABytes;
-                if (kType == TB200_TYPE_Q4_0) {
-                    const __half d = reinterpret_cast<const __half *>(p.sc)[grow * p.sc_row_stride + i * 2 + half];
-                    const __half2 d2 = __half2half2(d);
-                    mbar_wait(&full_p[s], ph);
-                    const uint4 w = *reinterpret_cast<const uint4 *>(sP + s * kPackedBytes + row * 32 + half * 16);
-                    store_chunk(a_tile, row, half * 4 + 0, dequant_q4_word(w.x, d2));
-                    store_chunk(a_tile, row, half * 4 + 1, dequant_q4_word(w.y, d2));
-                    store_chunk(a_tile, row, half * 4 + 2, dequant_q4_word(w.z, d2));
-                    store_chunk(a_tile, row, half * 4 + 3, dequant_q4_word(w.w, d2));
-                } else if (kType == TB200_TYPE_Q8_0) {
-                    const __half d = reinterpret_cast<const __half *>(p.sc)[grow * p.sc_row_stride + i * 2 + half];
-                    const __half2 d2 = __half2half2(d);
-                    mbar_wait(&full_p[s], ph);
-                    const uint4 w0 = *reinterpret_cast<const uint4 *>(sP + s * kPackedBytes + row * 64 + half * 32);
-                    const uint4 w1 = *reinterpret_cast<const uint4 *>(sP + s * kPackedBytes + row * 64 + half * 32 + 16);
-                    uint2 a, b;
-                    a = dequant_q8_word(w0.x, d2), b = dequant_q8_word(w0.y, d2);
-                    store_chunk(a_tile, row, half * 4 + 0, make_uint4(a.x, a.y, b.x, b.y));
-                    a = dequant_q8_word(w0.z, d2), b = dequant_q8_word(w0.w, d2);
-                    store_chunk(a_tile, row, half * 4 + 1, make_uint4(a.x, a.y, b.x, b.y));
-                    a = dequant_q8_word(w1.x, d2), b = dequant_q8_word(w1.y, d2);
-                    store_chunk(a_tile, row, half * 4 + 2, make_uint4(a.x, a.y, b.x, b.y));
-                    a = dequant_q8_word(w1.z, d2), b = dequant_q8_word(w1.w, d2);
-                    store_chunk(a_tile, row, half * 4 + 3, make_uint4(a.x, a.y, b.x, b.y));
-                } else {   // Q4_K: stage i is 64-element chunk c = i & 3 of super-block i >> 2
-                    const uint4 hdr = __ldg(reinterpret_cast<const uint4 *>(p.sc) + grow * p.sc_row_stride + (i >> 2));
-                    const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr.x);
-                    const float d = __low2float(dd), dmin = __high2float(dd);
-                    int sc_lo, m_lo, sc_hi, m_hi;
-                    q4k_scale_min(hdr, 2 * (i & 3), sc_lo, m_lo);
-                    q4k_scale_min(hdr, 2 * (i & 3) + 1, sc_hi, m_hi);
-                    const __half2 a_lo = __float2half2_rn(d * sc_lo), b_lo = __float2half2_rn(-(dmin * m_lo));
-                    const __half2 a_hi = __float2half2_rn(d * sc_hi), b_hi = __float2half2_rn(-(dmin * m_hi));
-                    mbar_wait(&full_p[s], ph);
-                    const uint4 w = *reinterpret_cast<const uint4 *>(sP + s * kPackedBytes + row * 32 + half * 16);
-                    store_chunk(a_tile, row, half * 4 + 0, dequant_q4K_word(w.x, a_lo, b_lo, a_hi, b_hi));
-                    store_chunk(a_tile, row, half * 4 + 1, dequant_q4K_word(w.y, a_lo, b_lo, a_hi, b_hi));
-                    store_chunk(a_tile, row, half * 4 + 2, dequant_q4K_word(w.z, a_lo, b_lo, a_hi, b_hi));
-                    store_chunk(a_tile, row, half * 4 + 3, dequant_q4K_word(w.w, a_lo, b_lo, a_hi, b_hi));
-                }
-                fence_proxy_async();   // generic-proxy stores -> visible to the tensor core (async proxy)
+                __half2 d2 = __half2half2(__float2half(0.f));
+                uint4 hdr = make_uint4(0, 0, 0, 0);
+                uint32_t r[16];
+                dq.advance(i, kt, d2, hdr);
+                mbar_wait(&full_p[s], ph);
+                dq.regs(sP + s * kPackedBytes, i, d2, hdr, r);
+                // full_p[s] completing implies (through the producer's wait on empty[s]) that the MMAs which read this A' stage
+                // one ring turn ago have retired
+                tc_fence_after();
+                tmem_st16(ta + (uint32_t)s * 32, r);
+                tmem_wait_st();
+                tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&full_a[s]);
             }
@@ -311,7 +439,6 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
         // first half of the columns, warps 8-11 the second half.
         mbar_wait(accum_full, 0);
         tc_fence_after();
-        const int quad = warp & 3, chalf = (warp - 4) >> 2;
         const long out_row = tile_row + quad * 32 + lane;
         constexpr int kChunks = BN / 32 > 0 ? BN / 32 : 1;
         for (int ch = chalf; ch < kChunks; ch += 2) {
@@ -327,6 +454,159 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
     tc_fence_before();
     __syncthreads();
     if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------------ the CTA-pair kernel
+// Same pipeline on a pair of CTAs (cluster 2x1x1 along the row tiles, one UMMA of M=256): CTA r of the pair owns weight
+// rows [128r, 128r+128) of a 256-row tile (its own packed tiles, its own dequant warps, its own TMEM lanes) and stages
+// only HALF of the B' tile (tokens [r*BN/2, (r+1)*BN/2)); the tensor cores of both SMs read both halves. One SM's L2
+// traffic per 64-wide stage drops from 4 KB + BN*128 B to 4 KB + BN*64 B, which is what the single-CTA kernel is bound
+// by at BN=256 (36 KB per 512 tensor clocks per SM = 70 B/clk/SM against ~43 B/clk/SM of L2->SM fabric).
+// Barrier ownership: full_a / full_b live in the leader (rank 0), where the one MMA thread waits — the peer's TMA
+// counts its bytes there and the peer's dequant warps arrive there remotely; empty / accum_full exist in both CTAs
+// and are arrived on by the leader's multicast tcgen05.commit; full_p is CTA-local.
+template <int kType, int BN, int kStages>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+    gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+    constexpr bool kTS = kType != TB200_TYPE_F16;
+    constexpr int BNH = BN / 2;                      // B' rows staged by each CTA
+    constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 0 : BM * BK / 2);
+    constexpr int kABytes = kTS ? 0 : BM * BK * 2, kBBytes = BNH * BK * 2;
+    constexpr uint32_t kAccCols = BN;
+    constexpr uint32_t kTmemCols = tmem_cols_pow2(kAccCols + (kTS ? kStages * 32 : 0));
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t *sA = smem;
+    uint8_t *sB = sA + kStages * kABytes;
+    uint8_t *sP = sB + kStages * kBBytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sP + kStages * (kPackedBytes ? kPackedBytes : 16));
+    uint64_t *full_p = bars, *full_a = bars + kStages, *full_b = bars + 2 * kStages, *empty = bars + 3 * kStages, *accum_full = bars + 4 * kStages;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(accum_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    long tile_row = (long)blockIdx.x * BM, tile_tok = (long)blockIdx.y * BN;
+    long w_row0 = p.row0, tok_end = p.tokens;
+    const int kt = (int)(p.k / BK);
+    if (p.tiles) {   // uniform over the pair (same blockIdx.y); the table is written by a predecessor kernel
+        pdl_wait();
+        const int4 tl = p.tiles[blockIdx.y];
+        if (tl.z == 0) return;
+        w_row0 = tl.x, tile_tok = tl.y, tok_end = tl.y + tl.z;
+    }
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_w);
+        tma_prefetch_desc(&map_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_p[s], 1);
+            mbar_init(&full_a[s], kTS ? 2 * kDequantWarps : 1);   // dequant warps of both CTAs (F16: the leader's expect_tx for both TMA halves)
+            mbar_init(&full_b[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(accum_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc_pair(tmem_slot, kTmemCols);
+    tc_fence_before();
+    cluster_sync_all();     // barriers of both CTAs initialised, both TMEM allocations done
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();
+
+    if (warp == 0) {
+        // ===== TMA producer (one thread per CTA) =====
+        if (lane == 0) {
+            for (int i = 0; i < kt; ++i) {
+                const int s = i % kStages;
+                if (i >= kStages) mbar_wait(&empty[s], ((i / kStages) - 1) & 1);
+                if (kType == TB200_TYPE_F16) {
+                    if (leader) mbar_expect_tx(&full_a[s], 2 * kABytes);
+                    tma_load_2d_pair(sA + s * kABytes, &map_w, mapa_rank(smem_u32(&full_a[s]), 0), i * BK, (int)(w_row0 + tile_row));
+                } else {
+                    mbar_expect_tx(&full_p[s], kPackedBytes);
+                    tma_load_2d(sP + s * kPackedBytes, &map_w, &full_p[s], i * (kType == TB200_TYPE_Q8_0 ? BK : BK / 2), (int)(w_row0 + tile_row));
+                }
+                if (leader) mbar_expect_tx(&full_b[s], 2 * kBBytes);
+                tma_load_2d_pair(sB + s * kBBytes, &map_b, mapa_rank(smem_u32(&full_b[s]), 0), i * BK, (int)(tile_tok + rank * BNH));
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: one thread of the leader drives the tensor cores of both SMs =====
+        if (leader && lane == 0) {
+            constexpr uint32_t idesc = make_idesc_f16(2 * BM, BN);
+            for (int i = 0; i < kt; ++i) {
+                const int s = i % kStages;
+                const uint32_t ph = (i / kStages) & 1;
+                mbar_wait(&full_a[s], ph);
+                mbar_wait(&full_b[s], ph);
+                tc_fence_after();
+                const uint64_t db = make_desc_sw128(smem_u32(sB + s * kBBytes));
+                if (kTS) {
+                    const uint32_t ta = tmem_base + kAccCols + (uint32_t)s * 32;
+#pragma unroll
+                    for (int kk = 0; kk < BK / 16; ++kk)
+                        umma_f16_ts_pair(tmem_base, ta + (uint32_t)(kk * 8), db + (uint64_t)(kk * 2), idesc, (i | kk) ? 1u : 0u);
+                } else {
+                    const uint64_t da = make_desc_sw128(smem_u32(sA + s * kABytes));
+#pragma unroll
+                    for (int kk = 0; kk < BK / 16; ++kk)
+                        umma_f16_pair(tmem_base, da + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), idesc, (i | kk) ? 1u : 0u);
+                }
+                umma_commit_pair(&empty[s]);
+            }
+            umma_commit_pair(accum_full);
+        }
+    } else if (warp >= 4) {
+        const int quad = warp & 3, chalf = (warp - 4) >> 2;
+        const int row = quad * 32 + lane;
+        const long grow = w_row0 + min(tile_row + row, p.nrows - 1);
+        if (kTS) {
+            // ===== dequantisers: packed tile (smem) -> fp16 -> this CTA's tensor memory; arrive at the leader =====
+            const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCols + (uint32_t)(chalf * 16);
+            RowDequant<kType> dq(p, grow, row, chalf);
+            for (int i = 0; i < kt; ++i) {
+                const int s = i % kStages;
+                const uint32_t ph = (i / kStages) & 1;
+                __half2 d2 = __half2half2(__float2half(0.f));
+                uint4 hdr = make_uint4(0, 0, 0, 0);
+                uint32_t r[16];
+                dq.advance(i, kt, d2, hdr);
+                mbar_wait(&full_p[s], ph);
+                dq.regs(sP + s * kPackedBytes, i, d2, hdr, r);
+                tc_fence_after();
+                tmem_st16(ta + (uint32_t)s * 32, r);
+                tmem_wait_st();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if (leader) mbar_arrive(&full_a[s]);
+                    else mbar_arrive_cluster(mapa_rank(smem_u32(&full_a[s]), 0));
+                }
+            }
+        }
+        // ===== epilogue: this CTA's 128 rows x BN tokens =====
+        mbar_wait(accum_full, 0);
+        tc_fence_after();
+        const long out_row = tile_row + quad * 32 + lane;
+        constexpr int kChunks = BN / 32;
+        for (int ch = chalf; ch < kChunks; ch += 2) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32), v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const long t = tile_tok + ch * 32 + j;
+                if (t < tok_end && out_row < p.nrows) p.out[(p.rowmap ? (long)p.rowmap[t] : t) * p.ldo + out_row] = __uint_as_float(v[j]) * p.colscale[t];
+            }
+        }
+    }
+    tc_fence_before();
+    cluster_sync_all();     // neither CTA leaves (or frees TMEM) while the other can still touch its barriers / memories
+    if (warp == 2) tmem_dealloc_pair(tmem_base, kTmemCols);
 }
 
 // ------------------------------------------------------------------------------------------------ activation prep
@@ -432,8 +712,10 @@ void *gemm_scratch(tb200_ctx *c, size_t bytes) {
 template <int kType, int BN, int kStages>
 int launch_cfg(tb200_ctx *c, const CUtensorMap &mw, const CUtensorMap &mb, const GemmParams &p) {
     constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 16 : BM * BK / 2);
-    constexpr size_t smem = 1024 + (size_t)kStages * (BM * BK * 2 + BN * BK * 2 + kPackedBytes) + (4 * kStages + 1) * 8 + 16;
+    constexpr int kABytes = kType == TB200_TYPE_F16 ? BM * BK * 2 : 0;   // dequantised A' lives in tensor memory
+    constexpr size_t smem = 1024 + (size_t)kStages * (kABytes + BN * BK * 2 + kPackedBytes) + (4 * kStages + 1) * 8 + 16;
     static_assert(smem <= 227 * 1024, "stage configuration exceeds shared memory");
+    static_assert(kType == TB200_TYPE_F16 || (BN < 32 ? 32 : BN) + kStages * 32 <= 512, "accumulator + A' ring exceed tensor memory");
     auto kern = gemm_tcgen05_kernel<kType, BN, kStages>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -445,6 +727,51 @@ int launch_cfg(tb200_ctx *c, const CUtensorMap &mw, const CUtensorMap &mb, const
     return TB200_OK;
 }
 
+// tensor map over the resident quants plane (whole matrix), cached on the weights object. Packed tiles use the 32-byte
+// (Q4_0/Q4_K: 32 bytes per row and stage) or 64-byte (Q8_0) swizzle so that the dequant warps' row-strided 16-byte
+// reads are bank-conflict free.
+CUtensorMap *weight_map(const tb200_weights *w) {
+    if (!w->tmap_cache) {
+        CUtensorMap *m = new CUtensorMap();
+        bool ok;
+        if (w->type == TB200_TYPE_F16) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k * 2, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
+        else if (w->type == TB200_TYPE_Q8_0) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k, BK, BM, CU_TENSOR_MAP_SWIZZLE_64B);
+        else ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / 2, (uint64_t)w->rows, (uint64_t)w->k / 2, BK / 2, BM, CU_TENSOR_MAP_SWIZZLE_32B);
+        if (!ok) { delete m; return nullptr; }
+        const_cast<tb200_weights *>(w)->tmap_cache = m;
+    }
+    return reinterpret_cast<CUtensorMap *>(w->tmap_cache);
+}
+
+template <int kType, int BN, int kStages>
+int launch_cfg_pair(tb200_ctx *c, const CUtensorMap &mw, const CUtensorMap &mb, const GemmParams &p) {
+    constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 16 : BM * BK / 2);
+    constexpr int kABytes = kType == TB200_TYPE_F16 ? BM * BK * 2 : 0;
+    constexpr size_t smem = 1024 + (size_t)kStages * (kABytes + (BN / 2) * BK * 2 + kPackedBytes) + (4 * kStages + 1) * 8 + 16;
+    static_assert(smem <= 227 * 1024, "stage configuration exceeds shared memory");
+    static_assert(kType == TB200_TYPE_F16 || BN + kStages * 32 <= 512, "accumulator + A' ring exceed tensor memory");
+    auto kern = gemm_tcgen05_pair_kernel<kType, BN, kStages>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    const unsigned row_tiles = (unsigned)((p.nrows + BM - 1) / BM);
+    const dim3 grid((row_tiles + 1) & ~1u, p.tiles ? (unsigned)p.n_tiles : (unsigned)((p.tokens + BN - 1) / BN));   // pairs along x
+    TB_CUDA(tb200_launch(kern, grid, dim3(kThreads), smem, c->stream, mw, mb, p));
+    return TB200_OK;
+}
+
+// TB200_GEMM_PAIR: 0 = never, 1 (default) = CTA pairs where measured faster, 2 = CTA pairs for every weight type.
+// Measured on B200 (tools/gemm_probe.py, N=14336 K=4096 T=4096, sustained): F16 weights (SS form) 792 -> 841 TFLOPS with
+// pairs; the dequantised types (TS form) run at 864 TFLOPS single-CTA but only 518 TFLOPS as pairs (not power-limited
+// there: 810 W, full clock — a latency stall in the pair's A'-in-TMEM hand-off that is not understood yet), so they
+// stay on the single-CTA kernel.
+int pair_mode() {
+    static const int mode = [] { const char *v = getenv("TB200_GEMM_PAIR"); return (v && *v >= '0' && *v <= '2') ? *v - '0' : 1; }();
+    return mode;
+}
+
 template <int kType>
 int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long tokens, void *bp, GemmParams &p, int force_bn = 0) {
     // token tile: as wide as the batch allows (fewer re-dequantisations of the same weight tile), but keep >= ~1 wave of CTAs
@@ -453,14 +780,20 @@ int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long toke
     while (bn > 32 && (tokens <= bn / 2 || row_tiles * ((tokens + bn - 1) / bn) < c->sm_count)) bn >>= 1;
     if (tokens > 128 && bn < 128) bn = 128;
     if (force_bn) bn = force_bn;
+    const bool pair = bn >= 128 && (pair_mode() == 2 || (pair_mode() == 1 && kType == TB200_TYPE_F16));   // CTA pairs: each CTA stages half of the B' tile
     CUtensorMap mb;
-    if (!make_map_2d(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, bp, (uint64_t)w->k, (uint64_t)tokens, (uint64_t)w->k * 2, BK, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B))
+    if (!make_map_2d(&mb, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, bp, (uint64_t)w->k, (uint64_t)tokens, (uint64_t)w->k * 2, BK, (uint32_t)(pair ? bn / 2 : bn), CU_TENSOR_MAP_SWIZZLE_128B))
         return TB200_ERR_CUDA;
+    constexpr bool f16 = kType == TB200_TYPE_F16;   // SS form: A and B stages in shared memory; TS form: B + packed tile only
+    if (pair) {
+        if (bn == 256) return launch_cfg_pair<kType, 256, f16 ? 6 : 8>(c, mw, mb, p);
+        return launch_cfg_pair<kType, 128, 8>(c, mw, mb, p);
+    }
     switch (bn) {
-    case 256: return launch_cfg<kType, 256, kType == TB200_TYPE_Q8_0 ? 3 : 4>(c, mw, mb, p);
-    case 128: return launch_cfg<kType, 128, 5>(c, mw, mb, p);
-    case 64: return launch_cfg<kType, 64, 6>(c, mw, mb, p);
-    default: return launch_cfg<kType, 32, 6>(c, mw, mb, p);
+    case 256: return launch_cfg<kType, 256, f16 ? 4 : (kType == TB200_TYPE_Q8_0 ? 5 : 6)>(c, mw, mb, p);
+    case 128: return launch_cfg<kType, 128, f16 ? 5 : 8>(c, mw, mb, p);
+    case 64: return launch_cfg<kType, 64, f16 ? 6 : 8>(c, mw, mb, p);
+    default: return launch_cfg<kType, 32, f16 ? 6 : 8>(c, mw, mb, p);
     }
 }
 
@@ -549,16 +882,9 @@ int tb200_launch_gemm_grouped(tb200_ctx *c, const tb200_weights *w, int experts,
         const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : 2);
         TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)pairs), dim3(256), 0, c->stream, aq, ads, w->k, w->k, perm, bp, colscale, (const int *)order, thinkers, tasks));
     }
-    if (!w->tmap_cache) {
-        CUtensorMap *m = new CUtensorMap();
-        bool ok;
-        if (w->type == TB200_TYPE_F16) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k * 2, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
-        else if (w->type == TB200_TYPE_Q8_0) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k, BK, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
-        else ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / 2, (uint64_t)w->rows, (uint64_t)w->k / 2, BK / 2, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
-        if (!ok) { delete m; return TB200_ERR_CUDA; }
-        const_cast<tb200_weights *>(w)->tmap_cache = m;
-    }
-    CUtensorMap &mw = *reinterpret_cast<CUtensorMap *>(w->tmap_cache);
+    CUtensorMap *mwp = weight_map(w);
+    if (!mwp) return TB200_ERR_CUDA;
+    CUtensorMap &mw = *mwp;
     GemmParams p;
     p.sc = w->sc;
     p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
@@ -604,16 +930,9 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
         TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)tokens), dim3(256), 0, c->stream, aq, ads, a_stride, w->k, perm, bp, colscale, (const int *)nullptr, 1, 1));
     }
     // weight tensor map (whole matrix), cached on the weights object
-    if (!w->tmap_cache) {
-        CUtensorMap *m = new CUtensorMap();
-        bool ok;
-        if (w->type == TB200_TYPE_F16) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k * 2, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
-        else if (w->type == TB200_TYPE_Q8_0) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k, BK, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
-        else ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / 2, (uint64_t)w->rows, (uint64_t)w->k / 2, BK / 2, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
-        if (!ok) { delete m; return TB200_ERR_CUDA; }
-        const_cast<tb200_weights *>(w)->tmap_cache = m;
-    }
-    CUtensorMap &mw = *reinterpret_cast<CUtensorMap *>(w->tmap_cache);
+    CUtensorMap *mwp = weight_map(w);
+    if (!mwp) return TB200_ERR_CUDA;
+    CUtensorMap &mw = *mwp;
     GemmParams p;
     p.sc = w->sc;
     p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
