@@ -230,7 +230,7 @@ def run_b200_arm(args):
     # (tb200_mul_mat_acts_multi: wq/wk/wv, gate/up).
     schedule = []
     for i, m in enumerate(mats):
-        if schedule and schedule[-1][0] == m[5] and len(schedule[-1][1]) < 4 and wtype == Q4_0:
+        if schedule and schedule[-1][0] == m[5] and len(schedule[-1][1]) < 4 and wtype in (Q4_0, Q4_K):
             schedule[-1][1].append(i)
         else:
             schedule.append((m[5], [i]))

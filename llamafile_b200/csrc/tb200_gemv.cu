@@ -302,9 +302,17 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q8_0_kernel(const uint4 *__r
 // ---- Q4_K ---------------------------------------------------------------------------------------
 // Super-block = 128 B of nibbles = 8 pieces of 16 B; piece p = 2c+h holds, for 64-element chunk c,
 // low nibbles = elements 64c+16h+[0,16) (sub-block 2c) and high nibbles = 64c+32+16h+[0,16) (sub-block 2c+1)
-// (dequantize_row_q4_K, ggml-quants.c:2548-2570). 8 lanes share a super-block; activations are staged
-// as lo[sb][p], hi[sb][p] so that a lane reads exactly the 2 x 16 int8 its piece multiplies.
-__device__ __forceinline__ void q4k_scale_min(const uint4 hdr, int j, int &sc, int &m) {   // get_scale_min_k4, :1891-1899
+// (dequantize_row_q4_K, ggml-quants.c:2548-2570).
+// A lane owns one whole 64-element chunk (pieces 2c and 2c+1 = 32 contiguous bytes), so 4 lanes share a super-block and
+// a warp step covers 8 super-blocks = 1 KB of one row: the low nibbles of the two pieces meet activations 64c+[0,32)
+// (sub-block 2c), the high nibbles 64c+[32,64) (sub-block 2c+1) — the activation row in its natural order. All 16
+// six-bit scales/mins of the super-block are decoded with ~10 word-wide logic ops (get_scale_min_k4, :1891-1899, on
+// four bytes at a time) and the lane picks its two pairs by a fixed shift. The first version gave every lane one
+// piece and decoded two scale pairs per 16 bytes with byte-wise code: ~80 instructions per 16 B of weights, which
+// capped the kernel at 3.1 TB/s (issue-bound); this form needs ~37.
+// Shared memory: activations [T][super-block][chunk] as 4 x 16 B + 16 B of padding (80-byte stride: the 64-byte
+// lane stride of the natural layout would be a 4-way bank conflict), then {d, sum} per 32-sub-block.
+__device__ __forceinline__ void q4k_scale_min(const uint4 hdr, int j, int &sc, int &m) {   // get_scale_min_k4, :1891-1899 (blockdot checker kernel)
     // hdr.x = {d, dmin}; scales[12] = bytes 0..11 of (hdr.y, hdr.z, hdr.w)
     const uint32_t s0 = hdr.y, s1 = hdr.z, s2 = hdr.w;
     auto byte = [&](int i) -> uint32_t { const uint32_t wv = i < 4 ? s0 : (i < 8 ? s1 : s2); return (wv >> (8 * (i & 3))) & 0xff; };
@@ -312,16 +320,17 @@ __device__ __forceinline__ void q4k_scale_min(const uint4 hdr, int j, int &sc, i
     else { sc = (byte(j + 4) & 0xF) | ((byte(j - 4) >> 6) << 4); m = (byte(j + 4) >> 4) | ((byte(j) >> 6) << 4); }
 }
 
+constexpr int kQ4KSmemPerSb = 4 * 80 + 64;   // bytes of staged activations per super-block and token
+
 // Same launch structure as the Q4_0 kernel (multi-matrix grid, first weight batch before pdl_wait, fused all-gather
 // stores); A.nb / A.nbc count super-blocks here.
 template <int T, int R>
 __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const __grid_constant__ GemvQ4Args A) {
-    constexpr int U = (T * R <= 2) ? 2 : 1;   // super-blocks per 8-lane group per row in flight
+    constexpr int U = (T * R <= 2) ? 2 : 1;   // super-blocks per 4-lane group per row in flight
     extern __shared__ __align__(16) uint8_t smem[];
     const long nsb = A.nb, nsbc = A.nbc;
-    uint4 *s_lo = reinterpret_cast<uint4 *>(smem);   // [T][nsbc*8]
-    uint4 *s_hi = s_lo + T * nsbc * 8;
-    int2 *s_ds = reinterpret_cast<int2 *>(s_hi + T * nsbc * 8);   // [T][nsbc*8]
+    uint4 *s_q = reinterpret_cast<uint4 *>(smem);                       // [T][nsbc][4 chunks][5]
+    int2 *s_ds = reinterpret_cast<int2 *>(s_q + T * nsbc * 20);         // [T][nsbc*8]
     __shared__ int s_arow[T];
 
     pdl_launch_dependents();
@@ -335,22 +344,25 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const __grid_con
     const bool active = r_base < nrows;
     const uint4 *qs = (const uint4 *)A.qs[mat];
     const uint4 *sc = (const uint4 *)A.sc[mat];
-    const int p = lane & 7, c = p >> 1, h = p & 1, grp = lane >> 3;
+    const int c = lane & 3, grp = lane >> 2;
+    const int shift = 16 * (c & 1);           // this lane's scale pair inside the decoded 4-byte word
 
-    uint4 w[U][R], hdr[U][R];
+    uint4 w0[U][R], w1[U][R], hdr[U][R];
     long rowv[R];
     auto set_rows = [&](long my_row0) {
 #pragma unroll
         for (int r = 0; r < R; ++r) rowv[r] = my_row0 + min(r_base + r, nrows - 1);
     };
-    auto load_batch = [&](long sbase, long end) {   // super-blocks sbase + grp + 4u (row-relative), limited to < end
+    auto load_batch = [&](long sbase, long end) {   // super-blocks sbase + grp + 8u (row-relative), limited to < end
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const long sb = sbase + grp + 4 * u;
+            const long sb = sbase + grp + 8 * u;
             if (sb < end) {
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    w[u][r] = ldg_stream(qs + (rowv[r] * nsb + sb) * 8 + p);
+                    const uint4 *pw = qs + (rowv[r] * nsb + sb) * 8 + 2 * c;
+                    w0[u][r] = ldg_stream(pw);
+                    w1[u][r] = ldg_stream(pw + 1);
                     hdr[u][r] = __ldg(sc + rowv[r] * nsb + sb);
                 }
             }
@@ -386,46 +398,52 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const __grid_con
     for (long sb0 = 0; sb0 < nsb; sb0 += nsbc) {
         const long cnt = min(nsbc, nsb - sb0);
         if (sb0) __syncthreads();
+        const int nsbc_i = (int)nsbc;
 #pragma unroll
         for (int t = 0; t < T; ++t) {
             const uint4 *src = reinterpret_cast<const uint4 *>(A.aq + (long)s_arow[t] * A.a_stride + sb0 * QK_K);
             const int2 *dsrc = A.ads + (long)s_arow[t] * (A.a_stride / QK) + sb0 * 8;
-            for (int g = threadIdx.x; g < (int)cnt * 16; g += kWarps * 32) {   // g = 16-byte piece of this chunk of the activation row
-                const int sb = g >> 4, gi = g & 15, cc = gi >> 2, hl = (gi >> 1) & 1, hh = gi & 1;
-                (hl ? s_hi : s_lo)[(t * (int)nsbc + sb) * 8 + 2 * cc + hh] = src[g];
-            }
-            for (int g = threadIdx.x; g < (int)cnt * 8; g += kWarps * 32) s_ds[t * (int)nsbc * 8 + g] = dsrc[g];
+            for (int g = threadIdx.x; g < (int)cnt * 16; g += kWarps * 32)   // g = 16-byte piece; 4 pieces per chunk, chunk stride 5
+                s_q[t * nsbc_i * 20 + (g >> 2) * 5 + (g & 3)] = src[g];
+            for (int g = threadIdx.x; g < (int)cnt * 8; g += kWarps * 32) s_ds[t * nsbc_i * 8 + g] = dsrc[g];
         }
         __syncthreads();
         if (!active) continue;
-        for (long sbb = 0; sbb < cnt; sbb += 4 * U) {
+        for (long sbb = 0; sbb < cnt; sbb += 8 * U) {
             if (sb0 | sbb) load_batch(sb0 + sbb, sb0 + cnt);
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                const long sb = sbb + grp + 4 * u;   // chunk-relative
-                if (sb < cnt) {
+                const int sb = (int)sbb + grp + 8 * u;   // chunk-relative
+                if (sb < (int)cnt) {
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
-                        const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr[u][r].x);
+                        const uint4 h = hdr[u][r];
+                        const __half2 dd = *reinterpret_cast<const __half2 *>(&h.x);
                         const float d = __low2float(dd), dmin = __high2float(dd);
-                        int sc_lo, m_lo, sc_hi, m_hi;
-                        q4k_scale_min(hdr[u][r], 2 * c, sc_lo, m_lo);
-                        q4k_scale_min(hdr[u][r], 2 * c + 1, sc_hi, m_hi);
-                        const uint4 wv = w[u][r];
-                        const unsigned wl0 = wv.x & 0x0f0f0f0fu, wl1 = wv.y & 0x0f0f0f0fu, wl2 = wv.z & 0x0f0f0f0fu, wl3 = wv.w & 0x0f0f0f0fu;
-                        const unsigned wh0 = wv.x & 0xf0f0f0f0u, wh1 = wv.y & 0xf0f0f0f0u, wh2 = wv.z & 0xf0f0f0f0u, wh3 = wv.w & 0xf0f0f0f0u;   // 16*q
+                        // sub-blocks 0..3: 6 low bits of scales[0..3] / scales[4..7]; 4..7: nibbles of scales[8..11] + the 2 high bits
+                        const uint32_t scw = c < 2 ? (h.y & 0x3f3f3f3fu) : ((h.w & 0x0f0f0f0fu) | ((h.y >> 2) & 0x30303030u));
+                        const uint32_t mw = c < 2 ? (h.z & 0x3f3f3f3fu) : (((h.w >> 4) & 0x0f0f0f0fu) | ((h.z >> 2) & 0x30303030u));
+                        const int sc_lo = (scw >> shift) & 0xff, sc_hi = (scw >> (shift + 8)) & 0xff;
+                        const int m_lo = (mw >> shift) & 0xff, m_hi = (mw >> (shift + 8)) & 0xff;
+                        const uint4 a = w0[u][r], b = w1[u][r];
+                        const unsigned al0 = a.x & 0x0f0f0f0fu, al1 = a.y & 0x0f0f0f0fu, al2 = a.z & 0x0f0f0f0fu, al3 = a.w & 0x0f0f0f0fu;
+                        const unsigned bl0 = b.x & 0x0f0f0f0fu, bl1 = b.y & 0x0f0f0f0fu, bl2 = b.z & 0x0f0f0f0fu, bl3 = b.w & 0x0f0f0f0fu;
+                        const unsigned ah0 = a.x & 0xf0f0f0f0u, ah1 = a.y & 0xf0f0f0f0u, ah2 = a.z & 0xf0f0f0f0u, ah3 = a.w & 0xf0f0f0f0u;   // 16*q
+                        const unsigned bh0 = b.x & 0xf0f0f0f0u, bh1 = b.y & 0xf0f0f0f0u, bh2 = b.z & 0xf0f0f0f0u, bh3 = b.w & 0xf0f0f0f0u;
 #pragma unroll
                         for (int t = 0; t < T; ++t) {
-                            const long base = (t * nsbc + sb) * 8;
-                            const uint4 al = s_lo[base + p], ah = s_hi[base + p];
-                            int sl = dp4a_us(wl0, (int)al.x, 0);
-                            sl = dp4a_us(wl1, (int)al.y, sl), sl = dp4a_us(wl2, (int)al.z, sl), sl = dp4a_us(wl3, (int)al.w, sl);
-                            int sh = dp4a_us(wh0, (int)ah.x, 0);
-                            sh = dp4a_us(wh1, (int)ah.y, sh), sh = dp4a_us(wh2, (int)ah.z, sh), sh = dp4a_us(wh3, (int)ah.w, sh);
-                            const int2 ds_lo = s_ds[base + 2 * c], ds_hi = s_ds[base + 2 * c + 1];
-                            const float dy = __int_as_float(ds_lo.x);
-                            const int isum = sc_lo * sl + sc_hi * (sh >> 4);
-                            const int msum = h == 0 ? m_lo * ds_lo.y + m_hi * ds_hi.y : 0;   // each sub-block's mins counted once
+                            const uint4 *ap = s_q + ((t * nsbc_i + sb) * 4 + c) * 5;
+                            const uint4 y0 = ap[0], y1 = ap[1], y2 = ap[2], y3 = ap[3];
+                            int sl = dp4a_us(al0, (int)y0.x, 0);
+                            sl = dp4a_us(al1, (int)y0.y, sl), sl = dp4a_us(al2, (int)y0.z, sl), sl = dp4a_us(al3, (int)y0.w, sl);
+                            sl = dp4a_us(bl0, (int)y1.x, sl), sl = dp4a_us(bl1, (int)y1.y, sl), sl = dp4a_us(bl2, (int)y1.z, sl), sl = dp4a_us(bl3, (int)y1.w, sl);
+                            int sh = dp4a_us(ah0, (int)y2.x, 0);
+                            sh = dp4a_us(ah1, (int)y2.y, sh), sh = dp4a_us(ah2, (int)y2.z, sh), sh = dp4a_us(ah3, (int)y2.w, sh);
+                            sh = dp4a_us(bh0, (int)y3.x, sh), sh = dp4a_us(bh1, (int)y3.y, sh), sh = dp4a_us(bh2, (int)y3.z, sh), sh = dp4a_us(bh3, (int)y3.w, sh);
+                            const int4 dsv = *reinterpret_cast<const int4 *>(s_ds + (t * nsbc_i + sb) * 8 + 2 * c);   // {d, sum} of sub-blocks 2c, 2c+1
+                            const float dy = __int_as_float(dsv.x);
+                            const int isum = sc_lo * sl + sc_hi * (sh >> 4);   // sh is an exact multiple of 16
+                            const int msum = m_lo * dsv.y + m_hi * dsv.w;
                             acc[r][t] = fmaf(d * dy, (float)isum, acc[r][t]);
                             acc[r][t] = fmaf(-(dmin * dy), (float)msum, acc[r][t]);
                         }
@@ -625,9 +643,9 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
     }
     case TB200_TYPE_Q4_K: {
         const long nsb = w->k / QK_K;
-        long nsbc = (long)(kSmemBudget / ((size_t)T * 320)) / 4 * 4;
+        long nsbc = (long)(kSmemBudget / ((size_t)T * kQ4KSmemPerSb)) / 8 * 8;
         if (nsbc >= nsb) nsbc = nsb;
-        const size_t smem = (size_t)T * nsbc * 320;
+        const size_t smem = (size_t)T * nsbc * kQ4KSmemPerSb;
         GemvQ4Args ka;
         const int ctas = fill_args<R>(ka, a, nsb, nsbc);
         const dim3 g2((unsigned)ctas, grid.y);
