@@ -24,7 +24,7 @@
 //
 // Warp roles (384 threads, 1 CTA / SM): warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator,
 // warps 4-11 dequantisers (and, after the main loop, TMEM->register->global epilogue). TMEM lane = weight row, so
-// dequant warp w owns rows 32*(w&3).. and the K half (w-4)>>2 of every stage.
+// dequant warp w owns rows 32*(w&3).. of the stages i = (w-4)>>2 (mod 2).
 #include <cuda.h>
 
 #include "tb200_common.cuh"
@@ -240,38 +240,44 @@ struct GemmParams {
 };
 
 // ------------------------------------------------------------------------------------------------ dequant warps
-// One dequant thread owns weight row `row` of the CTA tile (= its TMEM lane) and the K half `chalf` (32 elements) of
-// every 64-wide stage. RowDequant carries that thread's scale stream: the scale of stage i+1 is fetched from global
-// memory while stage i is being processed. regs() turns the thread's 16 (Q4_0/Q4_K) or 32 (Q8_0) packed bytes of the
-// staged tile into 32 fp16 = 16 registers, ready for one tcgen05.st.32x32b.x16.
+// One dequant thread owns weight row `row` of the CTA tile (= its TMEM lane) for a whole 64-wide stage: two halves of
+// 32 elements, each turned into 32 fp16 = 16 registers for one tcgen05.st.32x32b.x16. The 8 dequant warps form two
+// groups of four (one warp per 32 TMEM lanes); group g takes the stages i = g (mod 2), so two stages are in flight and
+// the ~400-clock chain wait -> ld.shared -> unpack -> tcgen05.st -> wait::st of one stage no longer bounds the rate
+// (the first TS version had all 8 warps on the same stage and was dequant-latency-bound whenever a stage's MMAs took
+// less than that, i.e. at BN <= 128). RowDequant carries the thread's scale stream: the scales of the group's next
+// stage are fetched from global memory while the current one is being processed.
 template <int kType>
 struct RowDequant {
-    const __half *scp;    // Q4_0 / Q8_0: fp16 d of this row, element [2*i + chalf] belongs to stage i
+    const __half *scp;    // Q4_0 / Q8_0: fp16 d of this row; elements [2i], [2i+1] belong to the halves of stage i
     const uint4 *hdp;     // Q4_K: {d, dmin, scales[12]} of this row, one per 256 elements = 4 stages
-    __half d_next;
+    __half2 d_next;
     uint4 hdr_next;
-    int row, chalf;
+    int row;
 
-    __device__ __forceinline__ RowDequant(const GemmParams &p, long grow, int row_, int chalf_) : row(row_), chalf(chalf_) {
-        scp = reinterpret_cast<const __half *>(p.sc) + grow * p.sc_row_stride + chalf_;
+    __device__ __forceinline__ RowDequant(const GemmParams &p, long grow, int row_, int first_stage, int kt) : row(row_) {
+        scp = reinterpret_cast<const __half *>(p.sc) + grow * p.sc_row_stride;
         hdp = reinterpret_cast<const uint4 *>(p.sc) + grow * p.sc_row_stride;
-        d_next = __float2half(0.f);
+        d_next = __half2half2(__float2half(0.f));
         hdr_next = make_uint4(0, 0, 0, 0);
-        if (kType == TB200_TYPE_Q4_K) hdr_next = __ldg(hdp);
-        else d_next = scp[0];
+        if (first_stage < kt) {
+            if (kType == TB200_TYPE_Q4_K) hdr_next = __ldg(hdp + (first_stage >> 2));
+            else d_next = *reinterpret_cast<const __half2 *>(scp + 2 * first_stage);
+        }
     }
-    // call before waiting for stage i's packed tile: takes stage i's scale and puts stage i+1's fetch in flight
-    __device__ __forceinline__ void advance(int i, int kt, __half2 &d2, uint4 &hdr) {
+    // call before waiting for stage i's packed tile: takes stage i's scales and puts the fetch for stage i+2 in flight
+    __device__ __forceinline__ void advance(int i, int kt, __half2 &dpair, uint4 &hdr) {
         if (kType == TB200_TYPE_Q4_K) {
             hdr = hdr_next;
-            if ((i & 3) == 3 && i + 1 < kt) hdr_next = __ldg(hdp + ((i + 1) >> 2));
+            if (i + 2 < kt) hdr_next = __ldg(hdp + ((i + 2) >> 2));
         } else {
-            d2 = __half2half2(d_next);
-            if (i + 1 < kt) d_next = scp[(i + 1) * 2];
+            dpair = d_next;
+            if (i + 2 < kt) d_next = *reinterpret_cast<const __half2 *>(scp + 2 * (i + 2));
         }
     }
     // tile: this stage's packed quant tile in shared memory (TMA, 32B swizzle for 32-byte rows, 64B swizzle for 64-byte rows)
-    __device__ __forceinline__ void regs(const uint8_t *tile, int i, __half2 d2, const uint4 &hdr, uint32_t (&r)[16]) const {
+    __device__ __forceinline__ void regs(const uint8_t *tile, int i, int chalf, __half2 dpair, const uint4 &hdr, uint32_t (&r)[16]) const {
+        const __half2 d2 = chalf ? __high2half2(dpair) : __low2half2(dpair);
         if (kType == TB200_TYPE_Q4_0) {
             // SWIZZLE_32B, 32-byte rows: 16-byte chunk c of row r sits at chunk c ^ ((r >> 2) & 1)
             const uint4 w = *reinterpret_cast<const uint4 *>(tile + row * 32 + ((chalf ^ ((row >> 2) & 1)) << 4));
@@ -350,7 +356,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full_p[s], 1);
-            mbar_init(&full_a[s], kType == TB200_TYPE_F16 ? 1 : kDequantWarps);   // one elected arrive per dequant warp (F16: the TMA's expect_tx)
+            mbar_init(&full_a[s], kType == TB200_TYPE_F16 ? 1 : kDequantWarps / 2);   // one elected arrive per warp of the stage's dequant group (F16: the TMA's expect_tx)
             mbar_init(&full_b[s], 1);
             mbar_init(&empty[s], 1);
         }
@@ -414,21 +420,23 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
         const int row = quad * 32 + lane;             // TMEM lane == weight row of the tile
         const long grow = w_row0 + min(tile_row + row, p.nrows - 1);   // clamp rows past the matrix end (their outputs are masked)
         if (kTS) {
-            const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCols + (uint32_t)(chalf * 16);
-            RowDequant<kType> dq(p, grow, row, chalf);
-            for (int i = 0; i < kt; ++i) {
+            const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCols;
+            RowDequant<kType> dq(p, grow, row, chalf, kt);
+            for (int i = chalf; i < kt; i += 2) {   // this warp group's stages
                 const int s = i % kStages;
                 const uint32_t ph = (i / kStages) & 1;
-                __half2 d2 = __half2half2(__float2half(0.f));
+                __half2 dpair = __half2half2(__float2half(0.f));
                 uint4 hdr = make_uint4(0, 0, 0, 0);
-                uint32_t r[16];
-                dq.advance(i, kt, d2, hdr);
+                uint32_t r0[16], r1[16];
+                dq.advance(i, kt, dpair, hdr);
                 mbar_wait(&full_p[s], ph);
-                dq.regs(sP + s * kPackedBytes, i, d2, hdr, r);
+                dq.regs(sP + s * kPackedBytes, i, 0, dpair, hdr, r0);
+                dq.regs(sP + s * kPackedBytes, i, 1, dpair, hdr, r1);
                 // full_p[s] completing implies (through the producer's wait on empty[s]) that the MMAs which read this A' stage
                 // one ring turn ago have retired
                 tc_fence_after();
-                tmem_st16(ta + (uint32_t)s * 32, r);
+                tmem_st16(ta + (uint32_t)s * 32, r0);
+                tmem_st16(ta + (uint32_t)s * 32 + 16, r1);
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
@@ -503,7 +511,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full_p[s], 1);
-            mbar_init(&full_a[s], kTS ? 2 * kDequantWarps : 1);   // dequant warps of both CTAs (F16: the leader's expect_tx for both TMA halves)
+            mbar_init(&full_a[s], kTS ? kDequantWarps : 1);   // the stage's dequant group (4 warps) in both CTAs (F16: the leader's expect_tx for both TMA halves)
             mbar_init(&full_b[s], 1);
             mbar_init(&empty[s], 1);
         }
@@ -567,19 +575,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         const long grow = w_row0 + min(tile_row + row, p.nrows - 1);
         if (kTS) {
             // ===== dequantisers: packed tile (smem) -> fp16 -> this CTA's tensor memory; arrive at the leader =====
-            const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCols + (uint32_t)(chalf * 16);
-            RowDequant<kType> dq(p, grow, row, chalf);
-            for (int i = 0; i < kt; ++i) {
+            const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCols;
+            RowDequant<kType> dq(p, grow, row, chalf, kt);
+            for (int i = chalf; i < kt; i += 2) {   // this warp group's stages
                 const int s = i % kStages;
                 const uint32_t ph = (i / kStages) & 1;
-                __half2 d2 = __half2half2(__float2half(0.f));
+                __half2 dpair = __half2half2(__float2half(0.f));
                 uint4 hdr = make_uint4(0, 0, 0, 0);
-                uint32_t r[16];
-                dq.advance(i, kt, d2, hdr);
+                uint32_t r0[16], r1[16];
+                dq.advance(i, kt, dpair, hdr);
                 mbar_wait(&full_p[s], ph);
-                dq.regs(sP + s * kPackedBytes, i, d2, hdr, r);
+                dq.regs(sP + s * kPackedBytes, i, 0, dpair, hdr, r0);
+                dq.regs(sP + s * kPackedBytes, i, 1, dpair, hdr, r1);
+                // full_p[s] completing implies (through the producer's wait on empty[s]) that the MMAs which read this A' stage
+                // one ring turn ago have retired
                 tc_fence_after();
-                tmem_st16(ta + (uint32_t)s * 32, r);
+                tmem_st16(ta + (uint32_t)s * 32, r0);
+                tmem_st16(ta + (uint32_t)s * 32 + 16, r1);
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
