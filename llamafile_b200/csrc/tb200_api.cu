@@ -15,7 +15,7 @@
 #include "tb200_common.cuh"
 
 int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrows, const int8_t *aq, const int2 *ads,
-                      const void *af, long a_stride, long tokens, float *out, long ldo);   // tb200_gemm.cu
+                      const void *af, long a_stride, long tokens, float *out, long ldo, const tb200_peers *peers = nullptr);   // tb200_gemm.cu
 bool tb200_gemm_available();
 void tb200_gemm_release(tb200_weights *);
 
@@ -229,7 +229,7 @@ Planar carve(tb200_ctx *c, int wtype, long tokens, long k, size_t extra, void **
 int run_matmul(tb200_ctx *c, const tb200_weights *w, long row0, long nrows, const int8_t *aq, const int2 *ads, const void *af,
                int af_is_f32, long a_stride, long tokens, float *out, long ldo) {
     if (tokens > TB200_GEMV_MAX_TOKENS && tb200_gemm_available() && !af_is_f32)
-        return tb200_launch_gemm(c, w, row0, nrows, aq, ads, af, a_stride, tokens, out, ldo);
+        return tb200_launch_gemm(c, w, row0, nrows, aq, ads, af, a_stride, tokens, out, ldo, nullptr);
     for (long t0 = 0; t0 < tokens; t0 += TB200_GEMV_MAX_TOKENS) {
         tb200_gemv_args a;
         memset(&a, 0, sizeof(a));
@@ -397,14 +397,27 @@ int tb200_mul_mat_acts_multi_gather(tb200_peers *g, int n, const tb200_weights *
     if (!c) return TB200_ERR_NO_DEVICE;
     if (!g || n < 1 || n > TB200_GEMV_MAX_MATS || !w || !a || !out_offset || !ldo || !row_lo) { tb200_set_error("multi_gather: bad arguments"); return TB200_ERR_INVALID; }
     const int t0 = w[0] ? w[0]->type : -1;
-    if ((t0 != TB200_TYPE_Q4_0 && t0 != TB200_TYPE_Q4_K) || a->tokens > TB200_GEMV_MAX_TOKENS || (t0 == TB200_TYPE_Q4_K) != (a->wtype == TB200_TYPE_Q4_K) ||
-        a->wtype == TB200_TYPE_F16)
-        return TB200_ERR_UNSUPPORTED;
     for (int m = 0; m < n; ++m)
         if (!w[m] || w[m]->type != t0 || w[m]->k != a->k || row_lo[m] < 0 || ldo[m] < row_lo[m] + w[m]->rows || (out_offset[m] & 3)) {
             tb200_set_error("multi_gather: matrix %d does not fit its slot", m);
             return TB200_ERR_INVALID;
         }
+    if (a->tokens > TB200_GEMV_MAX_TOKENS) {
+        // prefill: one tcgen05 launch per matrix, the epilogue stores each 128-byte output segment into every rank's buffer
+        if (!tb200_gemm_available()) return TB200_ERR_UNSUPPORTED;
+        const bool wq = t0 != TB200_TYPE_F16, aq_ok = a->wtype != TB200_TYPE_F16;
+        if (wq != aq_ok || (wq && (t0 == TB200_TYPE_Q4_K) != (a->wtype == TB200_TYPE_Q4_K)) || (!wq && a->f32)) return TB200_ERR_UNSUPPORTED;
+        char *base = (char *)g->out_base[g->rank];
+        for (int m = 0; m < n; ++m) {
+            float *out = (float *)(base + out_offset[m]) + row_lo[m];
+            const int rc = tb200_launch_gemm(c, w[m], 0, w[m]->rows, wq ? a->q : nullptr, wq ? a->ds : nullptr, wq ? nullptr : (const void *)a->h, a->k,
+                                             a->tokens, out, ldo[m], g);
+            if (rc) return rc;
+        }
+        return TB200_OK;
+    }
+    if ((t0 != TB200_TYPE_Q4_0 && t0 != TB200_TYPE_Q4_K) || (t0 == TB200_TYPE_Q4_K) != (a->wtype == TB200_TYPE_Q4_K) || a->wtype == TB200_TYPE_F16)
+        return TB200_ERR_UNSUPPORTED;
     if (a->tokens == 0) return TB200_OK;
     char *base = (char *)g->out_base[g->rank];
     tb200_gemv_args ga;

@@ -237,7 +237,32 @@ struct GemmParams {
     const int4 *tiles;
     const int *rowmap;
     long n_tiles;
+    // fused all-gather (row-sharded prefill): `out` lies inside this rank's symmetric buffer `local_base`; every result is
+    // stored at the same offset of every rank's copy (peer-mapped pointers, own entry included) over NVLink
+    int world;
+    const char *local_base;
+    char *peer_base[TB200_MAX_PEERS];
 };
+
+// Epilogue store of one accumulator chunk: lane = weight row, so each of the 32 store instructions of a warp writes 128
+// contiguous bytes of one token's output row. With world > 1 that segment goes to every rank's copy of the buffer: the
+// NVLink transfers of a tile overlap the main loops of the other CTAs, and no collective follows — only the flag barrier.
+__device__ __forceinline__ void store_chunk_out(const GemmParams &p, const uint32_t (&v)[32], long tile_tok, int ch, long tok_end, long out_row) {
+    if (out_row >= p.nrows) return;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const long t = tile_tok + ch * 32 + j;
+        if (t < tok_end) {
+            float *dst = p.out + (p.rowmap ? (long)p.rowmap[t] : t) * p.ldo + out_row;
+            const float val = __uint_as_float(v[j]) * p.colscale[t];
+            if (p.world <= 1) *dst = val;
+            else {
+                const long off = reinterpret_cast<const char *>(dst) - p.local_base;
+                for (int pr = 0; pr < p.world; ++pr) *reinterpret_cast<float *>(p.peer_base[pr] + off) = val;
+            }
+        }
+    }
+}
 
 // ------------------------------------------------------------------------------------------------ dequant warps
 // One dequant thread owns weight row `row` of the CTA tile (= its TMEM lane) for a whole 64-wide stage: two halves of
@@ -452,11 +477,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
         for (int ch = chalf; ch < kChunks; ch += 2) {
             uint32_t v[32];
             tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32), v);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const long t = tile_tok + ch * 32 + j;
-                if (t < tok_end && out_row < p.nrows) p.out[(p.rowmap ? (long)p.rowmap[t] : t) * p.ldo + out_row] = __uint_as_float(v[j]) * p.colscale[t];
-            }
+            store_chunk_out(p, v, tile_tok, ch, tok_end, out_row);
         }
     }
     tc_fence_before();
@@ -609,11 +630,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         for (int ch = chalf; ch < kChunks; ch += 2) {
             uint32_t v[32];
             tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32), v);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const long t = tile_tok + ch * 32 + j;
-                if (t < tok_end && out_row < p.nrows) p.out[(p.rowmap ? (long)p.rowmap[t] : t) * p.ldo + out_row] = __uint_as_float(v[j]) * p.colscale[t];
-            }
+            store_chunk_out(p, v, tile_tok, ch, tok_end, out_row);
         }
     }
     tc_fence_before();
@@ -902,6 +919,8 @@ int tb200_launch_gemm_grouped(tb200_ctx *c, const tb200_weights *w, int experts,
     p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
     p.row0 = 0, p.nrows = rows, p.k = w->k, p.tokens = pairs, p.colscale = colscale, p.out = result, p.ldo = rows;
     p.tiles = tiles, p.rowmap = order, p.n_tiles = max_tiles;
+    p.world = 1, p.local_base = nullptr;
+    for (int r = 0; r < TB200_MAX_PEERS; ++r) p.peer_base[r] = nullptr;
     switch (w->type) {
     case TB200_TYPE_Q4_0: return launch_type<TB200_TYPE_Q4_0>(c, w, mw, pairs, bp, p, bn);
     case TB200_TYPE_Q8_0: return launch_type<TB200_TYPE_Q8_0>(c, w, mw, pairs, bp, p, bn);
@@ -924,7 +943,7 @@ void tb200_gemm_release(tb200_weights *w) {
 
 // out[t*ldo + i] for rows [row0, row0+nrows). Quantized types take planar activations (aq, ads); F16 takes af (fp16 [tokens][a_stride]).
 int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrows, const int8_t *aq, const int2 *ads, const void *af,
-                      long a_stride, long tokens, float *out, long ldo) {
+                      long a_stride, long tokens, float *out, long ldo, const tb200_peers *peers) {
     if (w->k % 256 || ((uintptr_t)w->qs & 15)) { tb200_set_error("gemm: K=%ld must be a multiple of 256", w->k); return TB200_ERR_UNSUPPORTED; }
     const size_t bp_bytes = ((size_t)tokens * w->k * 2 + 255) & ~(size_t)255;
     uint8_t *scr = (uint8_t *)gemm_scratch(c, bp_bytes + (size_t)tokens * 4);
@@ -950,6 +969,12 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
     p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
     p.row0 = row0, p.nrows = nrows, p.k = w->k, p.tokens = tokens, p.colscale = colscale, p.out = out, p.ldo = ldo;
     p.tiles = nullptr, p.rowmap = nullptr, p.n_tiles = 0;
+    p.world = 1, p.local_base = nullptr;
+    for (int r = 0; r < TB200_MAX_PEERS; ++r) p.peer_base[r] = nullptr;
+    if (peers && peers->world > 1) {
+        p.world = peers->world, p.local_base = (const char *)peers->out_base[peers->rank];
+        for (int r = 0; r < peers->world; ++r) p.peer_base[r] = (char *)peers->out_base[r];
+    }
     switch (w->type) {
     case TB200_TYPE_Q4_0: return launch_type<TB200_TYPE_Q4_0>(c, w, mw, tokens, (void *)b_src, p);
     case TB200_TYPE_Q8_0: return launch_type<TB200_TYPE_Q8_0>(c, w, mw, tokens, (void *)b_src, p);

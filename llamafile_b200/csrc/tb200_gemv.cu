@@ -51,27 +51,49 @@ struct GemvQ4Args {
 };
 
 // Epilogue shared by the quantized decode kernels: warp-reduce each (row, token) and store. With world > 1 the
-// store IS the all-gather: every lane p < world writes the value into rank p's copy of the symmetric output buffer
-// over NVLink (peer-mapped pointers), so no collective follows the kernel — only a flag barrier (tb200_peer.cu).
+// store IS the all-gather: the CTA's kWarps*R row results are first collected in shared memory and then written as ONE
+// contiguous segment (64 B at R = 2) into every rank's copy of the symmetric output buffer over NVLink (peer-mapped
+// pointers), so no collective follows the kernel — only a flag barrier (tb200_peer.cu). (The first version let lane p
+// of every warp store its 4-byte value to peer p: 16x more NVLink packets, and the barrier after the kernel waited
+// for them.) Every warp of the CTA must call this (it contains a block barrier when world > 1).
 template <int T, int R>
 __device__ __forceinline__ void store_rows(const GemvQ4Args &A, int mat, float (&acc)[R][T], const int (&orow)[T], int ntok,
-                                           long r_base, long nrows, int lane) {
+                                           long r_base, long nrows, int lane, bool active) {
     float *out = A.out[mat];
     const long ldo = A.ldo[mat];
+    if (A.world <= 1) {
+        if (!active) return;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const float v = warp_sum(acc[r][t]);
+                if (lane == 0 && r_base + r < nrows && t < ntok) out[(long)orow[t] * ldo + r_base + r] = v;
+            }
+        return;
+    }
+    constexpr int kRowsPerCta = kWarps * R;
+    __shared__ float s_out[T * kRowsPerCta];
+    const int warp = threadIdx.x >> 5;
 #pragma unroll
     for (int r = 0; r < R; ++r)
 #pragma unroll
         for (int t = 0; t < T; ++t) {
-            const float v = warp_sum(acc[r][t]);   // xor-shuffle: every lane holds the sum
-            if (r_base + r < nrows && t < ntok) {
-                float *dst = out + (long)orow[t] * ldo + r_base + r;
-                if (A.world <= 1) {
-                    if (lane == 0) *dst = v;
-                } else if (lane < A.world) {
-                    *reinterpret_cast<float *>(A.peer_base[lane] + (reinterpret_cast<const char *>(dst) - A.local_base)) = v;
-                }
-            }
+            const float v = warp_sum(acc[r][t]);
+            if (lane == 0) s_out[t * kRowsPerCta + warp * R + r] = v;
         }
+    __syncthreads();
+    const long cta_base = r_base - (long)warp * R;   // first row of this CTA (relative to row0)
+    const int j = threadIdx.x;                        // thread j < kRowsPerCta owns row j of the CTA: lanes write consecutive floats
+    if (j < kRowsPerCta && cta_base + j < nrows) {
+#pragma unroll
+        for (int t = 0; t < T; ++t)
+            if (t < ntok) {
+                const float v = s_out[t * kRowsPerCta + j];
+                const long off = reinterpret_cast<const char *>(out + (long)orow[t] * ldo + cta_base + j) - A.local_base;
+                for (int pr = 0; pr < A.world; ++pr) *reinterpret_cast<float *>(A.peer_base[pr] + off) = v;
+            }
+    }
 }
 
 template <int T, int R>
@@ -206,8 +228,7 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_con
             }
         }
     }
-    if (!active) return;
-    store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane);
+    store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane, active);
 }
 
 // ---- Q8_0 ---------------------------------------------------------------------------------------
@@ -452,8 +473,7 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const __grid_con
             }
         }
     }
-    if (!active) return;
-    store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane);
+    store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane, active);
 }
 
 // ---- F16 ----------------------------------------------------------------------------------------

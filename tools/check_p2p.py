@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Multi-GPU parity check of the fused all-gather decode path (run under torchrun, one rank per GPU):
 every rank must end up with the full, unsharded result, equal to the oracle's, for Q4_0 and Q4_K, T = 1 and 4,
-including an uneven split (vocab 128256 over 128-row tiles).
+including an uneven split (vocab 128256 over 128-row tiles), and for prefill-size T (tcgen05 GEMM epilogue) in all four types.
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/check_p2p.py
 """
 import os
@@ -27,8 +27,11 @@ def main():
     assert tb.link()
     o = B.oracle()
     ok_all = True
-    for wt, K, shapes in ((H.Q4_0, 1024, [1000, 384, 130]), (H.Q4_K, 1024, [520, 256]), (H.Q4_0, 512, [128256 // 8])):
-        for T in (1, 4):
+    # (weight type, K, matrix row counts, token counts); T > 8 goes through the tcgen05 GEMM whose epilogue does the peer stores
+    cases = ((H.Q4_0, 1024, [1000, 384, 130], (1, 4)), (H.Q4_K, 1024, [520, 256], (1, 4)), (H.Q4_0, 512, [128256 // 8], (1, 4)),
+             (H.Q4_0, 1024, [1000, 384], (40, 300)), (H.Q8_0, 512, [700], (129,)), (H.Q4_K, 1024, [520], (64,)), (H.F16, 512, [300], (33,)))
+    for wt, K, shapes, toks in cases:
+        for T in toks:
             X = H.make_acts(T, K, seed=T + K)
             Ws = [H.make_weights(wt, n, K, seed=n, realistic_q4k=False) for n in shapes]
             rb = B.row_bytes(wt, K)
@@ -40,7 +43,7 @@ def main():
                 offsets.append(off)
                 off += T * n * 4
             pg = PeerGroup(world, rank, max(off, 256))
-            acts = tb.Acts(wt, K, 8)
+            acts = tb.Acts(wt, K, max(8, T))
             acts.quantize(torch.from_numpy(X).cuda(), T)
             for rep in range(3):   # several epochs through the same flags
                 if live:
