@@ -697,7 +697,7 @@ template <int T>
 int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
     // rows per warp: 2 keeps >= 8 x 16-byte weight loads in flight per lane at K = 4096 while leaving
     // enough CTAs (N/8) to cover 148 SMs; small matrices fall back to 1 row per warp.
-    long total = a.nrows;
+    long total = a.nrows * (a.items ? (a.n_items > 0 ? a.n_items : 1) : 1);   // grouped mode: every item walks nrows rows
     for (int m = 1; m < a.nmat; ++m) total += a.w_more[m - 1]->rows;
     if (total < (long)c->sm_count * kWarps * 4) return launch_TR<T, 1>(c, a);
     return launch_TR<T, 2>(c, a);

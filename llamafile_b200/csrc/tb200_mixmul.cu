@@ -27,6 +27,8 @@ __global__ void __launch_bounds__(1024) build_items_kernel(const int32_t *__rest
                                                            int experts, long rows, int group, tb200_gemv_item *__restrict__ items,
                                                            long max_items, int *__restrict__ expert_counts) {
     extern __shared__ int s_base[];   // [experts + 1] first item of each expert
+    pdl_launch_dependents();
+    pdl_wait();                       // the item table may still be read by the previous call's grouped kernel
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     for (long i = threadIdx.x; i < max_items; i += blockDim.x) items[i].ntok = 0, items[i].row0 = 0;
     for (int e = warp; e < experts; e += nwarps) {
@@ -95,7 +97,7 @@ extern "C" int tb200_mixmul_dev(const tb200_weights *w, int experts, const float
     if (k % (w->type == TB200_TYPE_F16 ? 16 : 32)) return TB200_ERR_UNSUPPORTED;   // mixmat: cols % KN (:273)
     if (pairs == 0 || rows == 0) return TB200_OK;
     const int group = pairs <= experts ? 1 : (pairs <= 4L * experts ? 4 : 8);
-    const long max_items = (pairs + group - 1) / group + experts;
+    const long max_items = group == 1 ? pairs : (pairs + group - 1) / group + (pairs < experts ? pairs : experts);   // sum_e ceil(c_e / group)
 
     // scratch: planar activations | items
     size_t q_bytes = 0, ds_bytes = 0, h_bytes = 0;
@@ -118,10 +120,8 @@ extern "C" int tb200_mixmul_dev(const tb200_weights *w, int experts, const float
         return tb200_launch_gemm_grouped(c, w, experts, rows, w->type == TB200_TYPE_F16 ? nullptr : aq, w->type == TB200_TYPE_F16 ? nullptr : ads,
                                          w->type == TB200_TYPE_F16 ? (const void *)ah : nullptr, plan, pairs, thinkers, tasks, result);
     const int threads = experts >= 32 ? 1024 : experts * 32;
-    build_items_kernel<<<1, threads, (experts + 1) * sizeof(int), c->stream>>>(plan, pairs, thinkers, tasks, experts, rows, group, items,
-                                                                              max_items, nullptr);
-    tb200_count_launch();
-    TB_CUDA(cudaGetLastError());
+    TB_CUDA(tb200_launch(build_items_kernel, dim3(1), dim3(threads), (experts + 1) * sizeof(int), c->stream, plan, pairs, thinkers, tasks, experts, rows,
+                         group, items, max_items, (int *)nullptr));
     const void *af = w->type == TB200_TYPE_F16 ? (const void *)ah : nullptr;
     if (w->type == TB200_TYPE_F16) aq = nullptr, ads = nullptr;
     switch (group) {
