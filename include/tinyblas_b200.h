@@ -192,8 +192,13 @@ TB200_API int tb200_mul_mat_acts_multi(int n, const tb200_weights *const *w, con
 TB200_API void tb200_acts_free(tb200_acts *a);
 
 /* Multi-GPU, one process per GPU: weights row-sharded (each rank uploads its row slice), the all-gather of the output
- * slices fused into the decode kernel as peer stores over NVLink. The host shares one symmetric output buffer and one flag
- * buffer ([TB200_MAX_PEERS] uint32, zeroed) per rank through CUDA IPC handles (both from tb200_malloc). */
+ * slices fused into the kernels as peer stores over NVLink (decode: the GEMV epilogue, one 64-byte segment per CTA and
+ * peer; more than TB200_GEMV_MAX_TOKENS tokens: the tcgen05 GEMM epilogue, 128-byte segments, all four weight types).
+ * The host shares one symmetric output buffer and one flag buffer ([TB200_MAX_PEERS] uint32, zeroed) per rank through CUDA
+ * IPC handles (both from tb200_malloc). Matrix m's rows are this rank's slice starting at row row_lo[m] of a full output
+ * with leading dimension ldo[m] stored at byte offset out_offset[m] of the symmetric buffer; every rank holds every
+ * slice once tb200_peers_barrier() has passed. The reference moves such slices with cudaMemcpyPeerAsync + events per
+ * device (llama.cpp/ggml/src/ggml-cuda.cu:1600-1676). */
 typedef struct tb200_peers tb200_peers;
 TB200_API int tb200_ipc_get_handle(const void *dev_ptr, void *handle64);
 TB200_API void *tb200_ipc_open_handle(const void *handle64);

@@ -317,6 +317,40 @@ def test_prefill_parity(tb, oracle, wt, N, K, T):
     H.assert_close(gpu_mul_mat(tb, W, wt, X, N, K), oracle.mul_mat(W, wt, X), f"prefill {H.TYPE_NAME[wt]} N={N} K={K} T={T}")
 
 
+_PAIR_SNIPPET = r"""
+import sys
+sys.path.insert(0, {root!r}); sys.path.insert(0, {root!r} + "/tests")
+import numpy as np, torch
+import helpers as H
+import llamafile_b200 as tb
+from oracle import binding as B
+assert tb.link()
+o = B.oracle()
+for wt in H.WEIGHT_TYPES:
+    for (N, K, T) in ((384, 1024, 300), (1000, 512, 129)):
+        W = H.make_weights(wt, N, K, seed=N + T, realistic_q4k=False)
+        X = H.make_acts(T, K, seed=T)
+        w = tb.Weights(W, wt, N, K)
+        out = torch.full((T, N), float("nan"), device="cuda")
+        tb.mul_mat(w, torch.from_numpy(X).cuda(), T, out)
+        tb.synchronize()
+        H.assert_close(out.cpu().numpy(), o.mul_mat(W, wt, X), f"pair kernel {{H.TYPE_NAME[wt]}} N={{N}} K={{K}} T={{T}}")
+print("PAIR_OK")
+"""
+
+
+def test_prefill_cta_pair_kernel_all_types():
+    """The cta_group::2 kernel is the default only for F16 weights; TB200_GEMM_PAIR=2 (read once per process) routes every
+    weight type through it, including an odd number of row tiles (the pair's second CTA is all padding)."""
+    import os
+    import subprocess
+    import sys
+    root = str(__import__("pathlib").Path(__file__).resolve().parent.parent)
+    env = dict(os.environ, TB200_GEMM_PAIR="2")
+    r = subprocess.run([sys.executable, "-c", _PAIR_SNIPPET.format(root=root)], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "PAIR_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def test_prefill_activation_outliers(tb, oracle):
     """Token rows with huge / tiny magnitudes: the per-token power-of-two scaling keeps fp16 operands in range."""
     N, K, T = 256, 1024, 48
