@@ -14,6 +14,7 @@
 // row so every warp load is one contiguous 512-byte segment. Activations (quantized once per call by
 // tb200_quantize.cu) are staged in shared memory, split so that lane-consecutive reads are
 // bank-conflict free. Weights are read exactly once -> ld.global.nc.L1::no_allocate.
+#include <stdlib.h>
 #include <string.h>
 
 #include "tb200_common.cuh"
@@ -229,6 +230,133 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_con
         }
     }
     store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane, active);
+}
+
+// ---- Q4_0, resident-grid form ----------------------------------------------------------------------
+// Same arithmetic and per-warp work unit (R = 2 rows x one K batch) as gemv_q4_0_kernel, but the grid is exactly the
+// number of CTAs the GPU can hold (3 per SM) and every warp walks the row pairs of the launch (all matrices
+// concatenated) with a stride. The one-shot grid needs ceil(N/16) CTAs, i.e. 2.02 waves for N = 14336 and 18 for the
+// vocabulary matrix: every wave boundary drains the memory pipe, the last wave is mostly empty, and each CTA stages
+// the activations again (896 x 5 KB of L2 traffic for 33 MB of weights). Here they are staged once per CTA and all
+// warps finish within one step of each other.
+template <int T>
+__global__ void __launch_bounds__(kWarps * 32, 3) gemv_q4_0_resident_kernel(const __grid_constant__ GemvQ4Args A) {
+    constexpr int R = 2;
+    constexpr int U = T <= 2 ? 4 : 2;
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int nb = (int)A.nb;                      // whole K is staged (the launcher guarantees it fits)
+    uint4 *s_lo = reinterpret_cast<uint4 *>(smem);
+    uint4 *s_hi = s_lo + T * nb;
+    int2 *s_ds = reinterpret_cast<int2 *>(s_hi + T * nb);
+
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nkb = (nb + 32 * U - 1) / (32 * U);  // K batches per row pair
+    const long units = A.cta_begin[A.nmat];        // row pairs of all matrices (cta_begin[] holds unit offsets here)
+    const long stride = (long)gridDim.x * kWarps;
+    long unit = (long)blockIdx.x * kWarps + warp;
+
+    int mat = 0;
+    long r_base = 0, nrows = 0;
+    const uint4 *wrow[R];
+    const __half *srow[R];
+    auto locate = [&](long u) {
+        mat = 0;
+#pragma unroll
+        for (int m = 1; m < kMaxMats; ++m)
+            if (m < A.nmat && u >= A.cta_begin[m]) mat = m;
+        nrows = A.nrows[mat];
+        r_base = (u - A.cta_begin[mat]) * R;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const long row = A.row0[mat] + min(r_base + r, nrows - 1);   // odd tail: the last row is recomputed, never stored
+            wrow[r] = (const uint4 *)A.qs[mat] + row * nb;
+            srow[r] = (const __half *)A.sc[mat] + row * nb;
+        }
+    };
+    uint4 w[U][R];
+    __half dh[U][R];
+    auto load_batch = [&](int kbi) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int b = kbi * 32 * U + lane + 32 * u;
+            if (b < nb) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) w[u][r] = ldg_stream(wrow[r] + b);
+#pragma unroll
+                for (int r = 0; r < R; ++r) dh[u][r] = srow[r][b];
+            }
+        }
+    };
+    const bool any = unit < units;
+    if (any) {
+        locate(unit);
+        load_batch(0);                              // immutable weights: in flight before the activations exist
+    }
+    pdl_wait();
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(A.aq + (long)t * A.a_stride);
+        const int2 *dsrc = A.ads + (long)t * (A.a_stride / QK);
+        for (int g = threadIdx.x; g < nb * 2; g += kWarps * 32) ((g & 1) ? s_hi : s_lo)[t * nb + (g >> 1)] = src[g];
+        for (int g = threadIdx.x; g < nb; g += kWarps * 32) s_ds[t * nb + g] = dsrc[g];
+    }
+    __syncthreads();
+
+    int orow[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) orow[t] = t;
+    const bool peers = A.world > 1;                 // the peer-store epilogue contains a block barrier: every warp must reach it
+    const long rounds = (units + stride - 1) / stride;
+    for (long it = 0; it < rounds; ++it, unit += stride) {
+        const bool active = unit < units;
+        float acc[R][T];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+        if (active) {
+            if (it) locate(unit);
+            for (int kb = 0; kb < nkb; ++kb) {
+                if (it | kb) load_batch(kb);
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int b = kb * 32 * U + lane + 32 * u;
+                    if (b < nb) {
+                        unsigned wl[R][4], wh[R][4];
+                        float d[R];
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            d[r] = __half2float(dh[u][r]);
+                            wl[r][0] = w[u][r].x & 0x0f0f0f0fu, wh[r][0] = w[u][r].x & 0xf0f0f0f0u;
+                            wl[r][1] = w[u][r].y & 0x0f0f0f0fu, wh[r][1] = w[u][r].y & 0xf0f0f0f0u;
+                            wl[r][2] = w[u][r].z & 0x0f0f0f0fu, wh[r][2] = w[u][r].z & 0xf0f0f0f0u;
+                            wl[r][3] = w[u][r].w & 0x0f0f0f0fu, wh[r][3] = w[u][r].w & 0xf0f0f0f0u;
+                        }
+#pragma unroll
+                        for (int t = 0; t < T; ++t) {
+                            const uint4 al = s_lo[t * nb + b], ah = s_hi[t * nb + b];
+                            const int2 ds = s_ds[t * nb + b];
+                            const float dy = __int_as_float(ds.x);
+#pragma unroll
+                            for (int r = 0; r < R; ++r) {
+                                int sl = dp4a_us(wl[r][0], (int)al.x, -8 * ds.y);   // sum (q-8)*y = sum q*y - 8*sum y (exact in int32)
+                                sl = dp4a_us(wl[r][1], (int)al.y, sl);
+                                sl = dp4a_us(wl[r][2], (int)al.z, sl);
+                                sl = dp4a_us(wl[r][3], (int)al.w, sl);
+                                int sh = dp4a_us(wh[r][0], (int)ah.x, 0);
+                                sh = dp4a_us(wh[r][1], (int)ah.y, sh);
+                                sh = dp4a_us(wh[r][2], (int)ah.z, sh);
+                                sh = dp4a_us(wh[r][3], (int)ah.w, sh);
+                                acc[r][t] = fmaf(d[r] * dy, (float)(sl + (sh >> 4)), acc[r][t]);   // sh is an exact multiple of 16
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        if (active || peers) store_rows<T, R>(A, mat, acc, orow, T, r_base, nrows, lane, active);
+    }
 }
 
 // ---- Q8_0 ---------------------------------------------------------------------------------------
@@ -693,6 +821,29 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
     return TB200_OK;
 }
 
+bool resident_enabled() {
+    static const int on = [] { const char *v = getenv("TB200_GEMV_RESIDENT"); return (v && *v == '0') ? 0 : 1; }();
+    return on != 0;
+}
+
+// Q4_0 dense launches with more row pairs than resident warps: the resident-grid kernel (3 CTAs per SM)
+template <int T>
+int launch_resident_q4_0(tb200_ctx *c, const tb200_gemv_args &a) {
+    const long nb = a.w->k / QK;
+    GemvQ4Args ka;
+    fill_args<2>(ka, a, nb, nb);
+    long units = 0;   // cta_begin[] carries row-pair offsets for this kernel
+    for (int m = 0; m < ka.nmat; ++m) { ka.cta_begin[m] = (int)units; units += (ka.nrows[m] + 1) / 2; }
+    ka.cta_begin[ka.nmat] = (int)units;
+    const size_t smem = (size_t)T * nb * 40;
+    int rc;
+    if ((rc = set_smem(gemv_q4_0_resident_kernel<T>, smem))) return rc;
+    long ctas = (units + kWarps - 1) / kWarps;
+    if (ctas > 3L * c->sm_count) ctas = 3L * c->sm_count;
+    TB_CUDA(tb200_launch(gemv_q4_0_resident_kernel<T>, dim3((unsigned)ctas), dim3(kWarps * 32), smem, c->stream, ka));
+    return TB200_OK;
+}
+
 template <int T>
 int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
     // rows per warp: 2 keeps >= 8 x 16-byte weight loads in flight per lane at K = 4096 while leaving
@@ -700,6 +851,9 @@ int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
     long total = a.nrows * (a.items ? (a.n_items > 0 ? a.n_items : 1) : 1);   // grouped mode: every item walks nrows rows
     for (int m = 1; m < a.nmat; ++m) total += a.w_more[m - 1]->rows;
     if (total < (long)c->sm_count * kWarps * 4) return launch_TR<T, 1>(c, a);
+    if (a.w->type == TB200_TYPE_Q4_0 && !a.items && T <= 2 && resident_enabled() && total / 2 > 4 * 3L * c->sm_count * kWarps &&   // >= 4 rounds of the resident grid
+        (size_t)T * (a.w->k / QK) * 40 * 3 <= 200 * 1024)
+        return launch_resident_q4_0<T>(c, a);
     return launch_TR<T, 2>(c, a);
 }
 
