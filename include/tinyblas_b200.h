@@ -211,6 +211,20 @@ TB200_API int tb200_peers_barrier(tb200_peers *g);   /* enqueue: all ranks' slic
 TB200_API int tb200_peers_timed_out(tb200_peers *g);
 TB200_API int tb200_memset(void *dst, int value, size_t bytes);
 
+/* GGUF tensor loader: tensors of a GGUF file (v2/v3) straight from an mmap to resident weights.
+ * Mirrors the reader in llama.cpp/ggml/src/ggml.c:20896-21160 (gguf_init_from_file) for the parts this path needs:
+ * header, metadata skipped except general.alignment, tensor infos, aligned data section. `data` pointers returned by
+ * tb200_gguf_find() point into the mapping and stay valid until tb200_gguf_close(). tb200_gguf_upload() accepts F16, Q4_0,
+ * Q8_0 and Q4_K tensors of rank 2 (a weight matrix; rows [row_lo, row_hi) when row_hi > row_lo = a rank's shard) or
+ * rank 3 (ne[2] stacked expert matrices, the form tb200_mixmul_dev takes). */
+typedef struct tb200_gguf tb200_gguf;
+TB200_API tb200_gguf *tb200_gguf_open(const char *path);
+TB200_API void tb200_gguf_close(tb200_gguf *g);
+TB200_API long tb200_gguf_tensor_count(const tb200_gguf *g);
+TB200_API const char *tb200_gguf_tensor_name(const tb200_gguf *g, long i);
+TB200_API int tb200_gguf_find(const tb200_gguf *g, const char *name, int *type, int64_t ne[4], const void **data, size_t *bytes);
+TB200_API tb200_weights *tb200_gguf_upload(const tb200_gguf *g, const char *name, long row_lo, long row_hi);
+
 /* llamafile_sgemm on device pointers with pre-quantized activations B (GGUF blocks of Btype, ldb in
  * blocks). Same service matrix as llamafile_sgemm. */
 TB200_API int tb200_sgemm_dev(const tb200_weights *w, long n, const void *B, long ldb, int Btype, float *C, long ldc);

@@ -56,6 +56,9 @@ def lib() -> C.CDLL:
         "llamafile_mixmul_iqk": (C.c_bool, [l, l, l, i, i, vp, vp, vp, l, l, vp, i, i]),
         "tb200_quantize_row_q8_0": (C.c_bool, [vp, vp, C.c_int64]), "tb200_quantize_row_q8_K": (C.c_bool, [vp, vp, C.c_int64]),
         "tb200_fp32_to_fp16_row": (C.c_bool, [vp, vp, C.c_int64]), "tb200_weights_cache_clear": (None, []),
+        "tb200_gguf_open": (vp, [C.c_char_p]), "tb200_gguf_close": (None, [vp]), "tb200_gguf_tensor_count": (l, [vp]),
+        "tb200_gguf_tensor_name": (C.c_char_p, [vp, l]), "tb200_gguf_find": (i, [vp, C.c_char_p, vp, vp, vp, vp]),
+        "tb200_gguf_upload": (vp, [vp, C.c_char_p, l, l]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -208,3 +211,50 @@ def mixmul(w: Weights, experts: int, thought, tasks: int, plan, thinkers: int, t
         return False
     _check(rc, "mixmul")
     return True
+
+
+class GgufFile:
+    """GGUF tensors straight from an mmap (tb200_gguf_*): metadata of every tensor, raw bytes as numpy views, and
+    resident Weights for the matrix types this module holds."""
+
+    def __init__(self, path):
+        self.handle = lib().tb200_gguf_open(str(path).encode())
+        if not self.handle:
+            raise TB200Error("gguf: " + lib().tb200_last_error().decode(errors="replace"))
+
+    def names(self):
+        L = lib()
+        return [L.tb200_gguf_tensor_name(self.handle, i).decode() for i in range(L.tb200_gguf_tensor_count(self.handle))]
+
+    def info(self, name: str):
+        """-> (ggml type, ne[4], host address, bytes)"""
+        ty, ne, data, nbytes = C.c_int(), (C.c_int64 * 4)(), C.c_void_p(), C.c_size_t()
+        _check(lib().tb200_gguf_find(self.handle, name.encode(), C.byref(ty), ne, C.byref(data), C.byref(nbytes)), "gguf_find")
+        return ty.value, list(ne), data.value, nbytes.value
+
+    def raw(self, name: str):
+        import numpy as np
+        ty, ne, addr, nbytes = self.info(name)
+        return np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(addr)) if nbytes else np.zeros(0, np.uint8)
+
+    def weights(self, name: str, row_lo: int = 0, row_hi: int = 0) -> "Weights":
+        _require_device()
+        ty, ne, _, _ = self.info(name)
+        hnd = lib().tb200_gguf_upload(self.handle, name.encode(), row_lo, row_hi)
+        if not hnd:
+            raise TB200Error("gguf_upload: " + lib().tb200_last_error().decode(errors="replace"))
+        w = Weights.__new__(Weights)
+        w.type, w.k, w.handle = ty, ne[0], hnd
+        w.rows = (row_hi - row_lo) if row_hi > row_lo else ne[1] * ne[2]
+        return w
+
+    def close(self):
+        if getattr(self, "handle", None):
+            lib().tb200_gguf_close(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
