@@ -38,6 +38,7 @@ enum tb200_type {
     TB200_TYPE_Q4_0 = 2,
     TB200_TYPE_Q8_0 = 8,
     TB200_TYPE_Q4_K = 12,
+    TB200_TYPE_Q6_K = 14,   /* the type Q4_K_M files keep output / ffn_down / attn_v in */
     TB200_TYPE_Q8_K = 15,
     TB200_TYPE_I32 = 26,
 };
@@ -49,6 +50,7 @@ typedef struct { uint16_t d; uint8_t qs[16]; } tb200_block_q4_0;
 typedef struct { uint16_t d; int8_t qs[32]; } tb200_block_q8_0;
 typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qs[128]; } tb200_block_q4_K;
 typedef struct { float d; int16_t bsums[16]; int8_t qs[256]; } tb200_block_q8_K;
+typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d; } tb200_block_q6_K;   /* ggml-common.h:299-307 */
 #pragma pack(pop)
 
 /* Layout-compatible prefix views of the two ggml structs llamafile_mixmul reads
@@ -86,7 +88,7 @@ typedef struct {
 /* llamafile/sgemm.h:23-24, llamafile/sgemm.cpp:128-131. C[ldc*j + i] = sum_l A[lda*i + l] * B[ldb*j + l],
  * m = weight rows, n = tokens, k/lda/ldb counted in BLOCKS of Atype/Btype, ldc in floats.
  * Serviced (returns true, C written) for the combinations the reference's x86 build services:
- *   Q4_0 x Q8_0, Q8_0 x Q8_0, Q4_K x Q8_K, F16 x F16, F16 x F32 (n <= 2); Ctype F32. (F32 and BF16
+ *   Q4_0 x Q8_0, Q8_0 x Q8_0, Q4_K x Q8_K, Q6_K x Q8_K, F16 x F16, F16 x F32 (n <= 2); Ctype F32. (F32 and BF16
  *   weights, which the reference also serves, are outside north_star's list and are handed back.)
  * Anything else returns false before touching C ("not handled, caller falls back"), never an error.
  * Threading contract: ggml calls this from all nth worker threads. Thread 0 does the whole job

@@ -130,6 +130,7 @@ static bool weight_geometry(int type, long rows, long k, tb200_weights *w) {
     case TB200_TYPE_Q4_0: if (k % QK) return false; w->qs_row_bytes = (size_t)k / QK * 16, w->sc_row_bytes = (size_t)k / QK * 2; break;
     case TB200_TYPE_Q8_0: if (k % QK) return false; w->qs_row_bytes = (size_t)k, w->sc_row_bytes = (size_t)k / QK * 2; break;
     case TB200_TYPE_Q4_K: if (k % QK_K) return false; w->qs_row_bytes = (size_t)k / 2, w->sc_row_bytes = (size_t)k / QK_K * 16; break;
+    case TB200_TYPE_Q6_K: if (k % QK_K) return false; w->qs_row_bytes = (size_t)k / QK_K * 192, w->sc_row_bytes = (size_t)k / QK_K * 16, w->d_row_bytes = (size_t)k / QK_K * 2; break;
     case TB200_TYPE_F16: w->qs_row_bytes = (size_t)k * 2, w->sc_row_bytes = 0; break;
     default: return false;
     }
@@ -141,6 +142,7 @@ static size_t gguf_row_bytes(int type, long k) {
     case TB200_TYPE_Q4_0: return (size_t)k / QK * 18;
     case TB200_TYPE_Q8_0: return (size_t)k / QK * 34;
     case TB200_TYPE_Q4_K: return (size_t)k / QK_K * 144;
+    case TB200_TYPE_Q6_K: return (size_t)k / QK_K * 210;
     case TB200_TYPE_Q8_K: return (size_t)k / QK_K * 292;
     case TB200_TYPE_F16: return (size_t)k * 2;
     case TB200_TYPE_F32: return (size_t)k * 4;
@@ -156,13 +158,15 @@ tb200_weights *tb200_weights_from_device(const void *dev_rows, int type, long ro
     if (rows < 0 || k <= 0 || !weight_geometry(type, rows, k, w)) { tb200_set_error("weights: unsupported type %d / k %ld", type, k); delete w; return nullptr; }
     if (row_stride == 0) row_stride = gguf_row_bytes(type, k);
     w->device = c->device;
-    const size_t qs_bytes = round_up(w->qs_row_bytes * rows, 256), sc_bytes = round_up(w->sc_row_bytes * rows, 256);
-    w->bytes = qs_bytes + sc_bytes;
+    const size_t qs_bytes = round_up(w->qs_row_bytes * rows, 256), sc_bytes = round_up(w->sc_row_bytes * rows, 256),
+                 d_bytes = round_up(w->d_row_bytes * rows, 256);
+    w->bytes = qs_bytes + sc_bytes + d_bytes;
     void *base = nullptr;
     if (cudaMalloc(&base, w->bytes + 256) != cudaSuccess) { cudaGetLastError(); tb200_set_error("weights: cudaMalloc(%zu) failed", w->bytes); delete w; return nullptr; }
     w->qs = base;
     w->sc = sc_bytes ? (uint8_t *)base + qs_bytes : nullptr;
-    if (tb200_launch_repack(c, dev_rows, type, rows, k, row_stride, w->qs, w->sc) != TB200_OK) { cudaFree(base); delete w; return nullptr; }
+    w->d = d_bytes ? (uint8_t *)base + qs_bytes + sc_bytes : nullptr;
+    if (tb200_launch_repack(c, dev_rows, type, rows, k, row_stride, w->qs, w->sc, w->d) != TB200_OK) { cudaFree(base); delete w; return nullptr; }
     return w;
 }
 
@@ -268,7 +272,7 @@ int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens,
     }
     Planar p = carve(c, w->type, tokens, w->k, 0, nullptr);
     if (!p.q) return TB200_ERR_CUDA;
-    if (w->type == TB200_TYPE_Q4_K) rc = tb200_launch_quantize_q8_K(c, x, ldx, tokens, w->k, nullptr, p.q, p.ds);
+    if (tb200_is_kquant(w->type)) rc = tb200_launch_quantize_q8_K(c, x, ldx, tokens, w->k, nullptr, p.q, p.ds);
     else rc = tb200_launch_quantize_q8_0(c, x, ldx, tokens, w->k, nullptr, p.q, p.ds);
     if (rc) return rc;
     return run_matmul(c, w, 0, w->rows, p.q, p.ds, nullptr, 0, w->k, tokens, out, ldo);
@@ -284,7 +288,7 @@ int tb200_mul_mat_multi(int n, const tb200_weights *const *w, const float *x, lo
             return TB200_ERR_INVALID;
         }
     if (tokens == 0) return TB200_OK;
-    if ((w[0]->type != TB200_TYPE_Q4_0 && w[0]->type != TB200_TYPE_Q4_K) || tokens > TB200_GEMV_MAX_TOKENS) {   // other types / prefill: one matmul each
+    if ((w[0]->type != TB200_TYPE_Q4_0 && !tb200_is_kquant(w[0]->type)) || tokens > TB200_GEMV_MAX_TOKENS) {   // other types / prefill: one matmul each
         for (int m = 0; m < n; ++m) {
             const int rc = tb200_mul_mat(w[m], x, ldx, tokens, out[m], ldo[m]);
             if (rc) return rc;
@@ -294,7 +298,7 @@ int tb200_mul_mat_multi(int n, const tb200_weights *const *w, const float *x, lo
     // quantize once (one launch), then ONE decode launch over the concatenated row tiles of all n matrices
     Planar p = carve(c, w[0]->type, tokens, w[0]->k, 0, nullptr);
     if (!p.q) return TB200_ERR_CUDA;
-    int rc = w[0]->type == TB200_TYPE_Q4_K ? tb200_launch_quantize_q8_K(c, x, ldx, tokens, w[0]->k, nullptr, p.q, p.ds)
+    int rc = tb200_is_kquant(w[0]->type) ? tb200_launch_quantize_q8_K(c, x, ldx, tokens, w[0]->k, nullptr, p.q, p.ds)
                                            : tb200_launch_quantize_q8_0(c, x, ldx, tokens, w[0]->k, nullptr, p.q, p.ds);
     if (rc) return rc;
     tb200_gemv_args a;
@@ -317,7 +321,7 @@ struct tb200_acts {
 tb200_acts *tb200_acts_create(int weight_type, long k, long max_tokens) {
     tb200_ctx *c = tb200_get_ctx();
     if (!c) return nullptr;
-    if (k <= 0 || max_tokens <= 0 || (weight_type != TB200_TYPE_F16 && k % (weight_type == TB200_TYPE_Q4_K ? QK_K : QK))) {
+    if (k <= 0 || max_tokens <= 0 || (weight_type != TB200_TYPE_F16 && k % (tb200_is_kquant(weight_type) ? QK_K : QK))) {
         tb200_set_error("acts_create: bad arguments");
         return nullptr;
     }
@@ -342,7 +346,7 @@ int tb200_acts_quantize(tb200_acts *a, const float *x, long ldx, long tokens) {
         if (tokens <= 2) { a->f32 = x; return TB200_OK; }   // B stays F32 for n <= 2 (tinyblas_cpu_sgemm.inc:121-136); caller keeps x alive
         return tb200_launch_f32_to_f16(c, x, ldx, tokens, a->k, a->h);
     }
-    if (a->wtype == TB200_TYPE_Q4_K) return tb200_launch_quantize_q8_K(c, x, ldx, tokens, a->k, nullptr, a->q, a->ds);
+    if (tb200_is_kquant(a->wtype)) return tb200_launch_quantize_q8_K(c, x, ldx, tokens, a->k, nullptr, a->q, a->ds);
     return tb200_launch_quantize_q8_0(c, x, ldx, tokens, a->k, nullptr, a->q, a->ds);
 }
 
@@ -351,7 +355,7 @@ int tb200_mul_mat_acts(const tb200_weights *w, const tb200_acts *a, float *out, 
     if (!c) return TB200_ERR_NO_DEVICE;
     if (!w || !a || a->k != w->k || ldo < w->rows) { tb200_set_error("mul_mat_acts: bad arguments"); return TB200_ERR_INVALID; }
     const bool wq = w->type != TB200_TYPE_F16, aq = a->wtype != TB200_TYPE_F16;
-    if (wq != aq || (wq && (w->type == TB200_TYPE_Q4_K) != (a->wtype == TB200_TYPE_Q4_K))) {
+    if (wq != aq || (wq && tb200_is_kquant(w->type) != tb200_is_kquant(a->wtype))) {
         tb200_set_error("mul_mat_acts: activations were prepared for weight type %d, not %d", a->wtype, w->type);
         return TB200_ERR_INVALID;
     }
@@ -369,8 +373,8 @@ int tb200_mul_mat_acts_multi(int n, const tb200_weights *const *w, const tb200_a
     if (n < 1 || n > TB200_GEMV_MAX_MATS || !w || !a || !out || !ldo) { tb200_set_error("mul_mat_acts_multi: bad arguments"); return TB200_ERR_INVALID; }
     // one launch when all matrices are Q4_0 (Q8_0 activations) or all Q4_K (Q8_K activations) and share K
     const int t0 = w[0] ? w[0]->type : -1;
-    bool one_launch = (t0 == TB200_TYPE_Q4_0 || t0 == TB200_TYPE_Q4_K) && a->tokens <= TB200_GEMV_MAX_TOKENS && a->wtype != TB200_TYPE_F16 &&
-                      (t0 == TB200_TYPE_Q4_K) == (a->wtype == TB200_TYPE_Q4_K);
+    bool one_launch = (t0 == TB200_TYPE_Q4_0 || tb200_is_kquant(t0)) && a->tokens <= TB200_GEMV_MAX_TOKENS && a->wtype != TB200_TYPE_F16 &&
+                      tb200_is_kquant(t0) == tb200_is_kquant(a->wtype);
     for (int m = 0; m < n && one_launch; ++m) one_launch = w[m] && w[m]->type == t0 && w[m]->k == a->k && ldo[m] >= w[m]->rows;
     if (!one_launch) {
         for (int m = 0; m < n; ++m) {
@@ -406,7 +410,7 @@ int tb200_mul_mat_acts_multi_gather(tb200_peers *g, int n, const tb200_weights *
         // prefill: one tcgen05 launch per matrix, the epilogue stores each 128-byte output segment into every rank's buffer
         if (!tb200_gemm_available()) return TB200_ERR_UNSUPPORTED;
         const bool wq = t0 != TB200_TYPE_F16, aq_ok = a->wtype != TB200_TYPE_F16;
-        if (wq != aq_ok || (wq && (t0 == TB200_TYPE_Q4_K) != (a->wtype == TB200_TYPE_Q4_K)) || (!wq && a->f32)) return TB200_ERR_UNSUPPORTED;
+        if (wq != aq_ok || (wq && tb200_is_kquant(t0) != tb200_is_kquant(a->wtype)) || (!wq && a->f32)) return TB200_ERR_UNSUPPORTED;
         char *base = (char *)g->out_base[g->rank];
         for (int m = 0; m < n; ++m) {
             float *out = (float *)(base + out_offset[m]) + row_lo[m];
@@ -416,7 +420,7 @@ int tb200_mul_mat_acts_multi_gather(tb200_peers *g, int n, const tb200_weights *
         }
         return TB200_OK;
     }
-    if ((t0 != TB200_TYPE_Q4_0 && t0 != TB200_TYPE_Q4_K) || (t0 == TB200_TYPE_Q4_K) != (a->wtype == TB200_TYPE_Q4_K) || a->wtype == TB200_TYPE_F16)
+    if ((t0 != TB200_TYPE_Q4_0 && !tb200_is_kquant(t0)) || tb200_is_kquant(t0) != tb200_is_kquant(a->wtype) || a->wtype == TB200_TYPE_F16)
         return TB200_ERR_UNSUPPORTED;
     if (a->tokens == 0) return TB200_OK;
     char *base = (char *)g->out_base[g->rank];
@@ -443,7 +447,7 @@ static bool serviced(int Atype, int Btype, int Ctype, long n) {
     if (Ctype != TB200_TYPE_F32) return false;
     switch (Atype) {
     case TB200_TYPE_Q4_0: case TB200_TYPE_Q8_0: return Btype == TB200_TYPE_Q8_0;
-    case TB200_TYPE_Q4_K: return Btype == TB200_TYPE_Q8_K;
+    case TB200_TYPE_Q4_K: case TB200_TYPE_Q6_K: return Btype == TB200_TYPE_Q8_K;
     case TB200_TYPE_F16: return Btype == TB200_TYPE_F16 || (Btype == TB200_TYPE_F32 && n <= 2);
     default: return false;
     }
@@ -459,11 +463,11 @@ int tb200_sgemm_dev(const tb200_weights *w, long n, const void *B, long ldb, int
         if (ldb < w->k) { tb200_set_error("sgemm_dev: ldb < k"); return TB200_ERR_INVALID; }
         return run_matmul(c, w, 0, w->rows, nullptr, nullptr, B, Btype == TB200_TYPE_F32, ldb, n, C, ldc);
     }
-    const long blck = w->type == TB200_TYPE_Q4_K ? QK_K : QK;
+    const long blck = tb200_is_kquant(w->type) ? QK_K : QK;
     if (ldb < w->k / blck) { tb200_set_error("sgemm_dev: ldb < k"); return TB200_ERR_INVALID; }
     Planar p = carve(c, w->type, n, w->k, 0, nullptr);
     if (!p.q) return TB200_ERR_CUDA;
-    int rc = w->type == TB200_TYPE_Q4_K ? tb200_launch_unpack_q8_K(c, B, ldb, n, w->k, p.q, p.ds)
+    int rc = tb200_is_kquant(w->type) ? tb200_launch_unpack_q8_K(c, B, ldb, n, w->k, p.q, p.ds)
                                        : tb200_launch_unpack_q8_0(c, B, ldb, n, w->k, p.q, p.ds);
     if (rc) return rc;
     return run_matmul(c, w, 0, w->rows, p.q, p.ds, nullptr, 0, w->k, n, C, ldc);
@@ -475,8 +479,8 @@ int tb200_blockdot_dev(const tb200_weights *w, const void *B, int Btype, int32_t
     if (!w || w->type == TB200_TYPE_F16 || !serviced(w->type, Btype, TB200_TYPE_F32, 1)) return TB200_ERR_UNSUPPORTED;
     Planar p = carve(c, w->type, 1, w->k, 0, nullptr);
     if (!p.q) return TB200_ERR_CUDA;
-    const long blck = w->type == TB200_TYPE_Q4_K ? QK_K : QK;
-    int rc = w->type == TB200_TYPE_Q4_K ? tb200_launch_unpack_q8_K(c, B, w->k / blck, 1, w->k, p.q, p.ds)
+    const long blck = tb200_is_kquant(w->type) ? QK_K : QK;
+    int rc = tb200_is_kquant(w->type) ? tb200_launch_unpack_q8_K(c, B, w->k / blck, 1, w->k, p.q, p.ds)
                                        : tb200_launch_unpack_q8_0(c, B, w->k / blck, 1, w->k, p.q, p.ds);
     if (rc) return rc;
     return tb200_launch_blockdot(c, w, p.q, p.ds, out);

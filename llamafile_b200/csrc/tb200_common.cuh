@@ -20,6 +20,10 @@ static_assert(sizeof(tb200_block_q4_0) == 18, "block_q4_0");
 static_assert(sizeof(tb200_block_q8_0) == 34, "block_q8_0");
 static_assert(sizeof(tb200_block_q4_K) == 144, "block_q4_K");
 static_assert(sizeof(tb200_block_q8_K) == 292, "block_q8_K");
+static_assert(sizeof(tb200_block_q6_K) == 210, "block_q6_K");
+
+// weight types whose activations are Q8_K (256-element super-blocks)
+static inline bool tb200_is_kquant(int type) { return type == TB200_TYPE_Q4_K || type == TB200_TYPE_Q6_K; }
 
 // ---------------------------------------------------------------------------------------------
 // Resident weight matrix: the GGUF rows split into 16-byte-aligned planes (one-time repack at
@@ -28,6 +32,9 @@ static_assert(sizeof(tb200_block_q8_K) == 292, "block_q8_K");
 //         sc  [rows][k/32] fp16 d
 //   Q8_0: qs  [rows][k] int8 ;  sc [rows][k/32] fp16 d
 //   Q4_K: qs  [rows][k/256] x 128 B ; sc [rows][k/256] x 16 B = {fp16 d, fp16 dmin, u8 scales[12]}
+//   Q6_K: qs  [rows][k/256] x 192 B = 4 units x {ql piece, ql piece +32, qh piece} (unit u = 2*half + l/16 covers elements
+//              128*half + 16*(l/16) + 32*j + [0,16), j = 0..3: one 64-wide K stage of the prefill path, one lane of the decode path)
+//         sc  [rows][k/256] x 16 B int8 scales ; d [rows][k/256] fp16
 //   F16 : qs  [rows][k] fp16 ; sc = nullptr
 // ---------------------------------------------------------------------------------------------
 struct tb200_weights {
@@ -35,7 +42,8 @@ struct tb200_weights {
     long rows, k;
     void *qs;
     void *sc;
-    size_t qs_row_bytes, sc_row_bytes;
+    void *d;            // Q6_K only: per-super-block fp16 scale plane
+    size_t qs_row_bytes, sc_row_bytes, d_row_bytes;
     size_t bytes;
     int device;
     void *tmap_cache;   // prefill GEMM tensor maps (tb200_gemm.cu), lazily built
@@ -89,7 +97,7 @@ int tb200_launch_f32_to_f16(tb200_ctx *c, const float *x, long ldx, long rows, l
 int tb200_launch_unpack_q8_0(tb200_ctx *c, const void *raw, long ldb_blocks, long rows, long k, int8_t *q, int2 *ds);
 int tb200_launch_unpack_q8_K(tb200_ctx *c, const void *raw, long ldb_blocks, long rows, long k, int8_t *q, int2 *ds);
 // repack
-int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long k, size_t row_stride, void *qs, void *sc);
+int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long k, size_t row_stride, void *qs, void *sc, void *d);
 // decode path. out[t*ldo + i]. rowmap: optional per-token (weight-row offset, output pointer) for mixmul.
 // grouped decode (mixmul): one item = rows [row0, row0+nrows) of one expert against ntok gathered tokens
 struct tb200_gemv_item {

@@ -34,6 +34,10 @@ namespace {
 constexpr int BM = 128;        // weight rows per CTA tile = UMMA M
 constexpr int BK = 64;         // K elements per stage = one 128-byte swizzle atom of fp16
 constexpr int kDequantWarps = 8;
+// packed quant bytes of one weight row in one 64-wide K stage (0: F16 weights are not dequantised)
+__host__ __device__ constexpr int packed_row_bytes(int type) {
+    return type == TB200_TYPE_Q8_0 ? 64 : (type == TB200_TYPE_Q6_K ? 48 : (type == TB200_TYPE_F16 ? 0 : 32));
+}
 constexpr int kThreads = (4 + kDequantWarps) * 32;
 
 // ------------------------------------------------------------------------------------------------ PTX wrappers
@@ -227,7 +231,8 @@ __host__ __device__ constexpr uint32_t tmem_cols_pow2(uint32_t need) {
 
 struct GemmParams {
     const void *sc;        // scales plane of the weights
-    long sc_row_stride;    // in elements of the plane (fp16 for Q4_0/Q8_0, uint4 for Q4_K)
+    long sc_row_stride;    // in elements of the plane (fp16 for Q4_0/Q8_0, uint4 for Q4_K / Q6_K)
+    const void *d6;        // Q6_K: fp16 super-block scale plane, sc_row_stride elements per row
     long row0, nrows;      // weight rows [row0, row0 + nrows)
     long k, tokens;
     const float *colscale; // [tokens] 2^e_t
@@ -275,7 +280,8 @@ __device__ __forceinline__ void store_chunk_out(const GemmParams &p, const uint3
 template <int kType>
 struct RowDequant {
     const __half *scp;    // Q4_0 / Q8_0: fp16 d of this row; elements [2i], [2i+1] belong to the halves of stage i
-    const uint4 *hdp;     // Q4_K: {d, dmin, scales[12]} of this row, one per 256 elements = 4 stages
+    const uint4 *hdp;     // Q4_K: {d, dmin, scales[12]} of this row, one per 256 elements = 4 stages; Q6_K: int8 scales[16]
+    const __half *d6p;    // Q6_K: fp16 d of this row, one per 256 elements
     __half2 d_next;
     uint4 hdr_next;
     int row;
@@ -283,10 +289,12 @@ struct RowDequant {
     __device__ __forceinline__ RowDequant(const GemmParams &p, long grow, int row_, int first_stage, int kt) : row(row_) {
         scp = reinterpret_cast<const __half *>(p.sc) + grow * p.sc_row_stride;
         hdp = reinterpret_cast<const uint4 *>(p.sc) + grow * p.sc_row_stride;
+        d6p = reinterpret_cast<const __half *>(p.d6) + grow * p.sc_row_stride;
         d_next = __half2half2(__float2half(0.f));
         hdr_next = make_uint4(0, 0, 0, 0);
         if (first_stage < kt) {
             if (kType == TB200_TYPE_Q4_K) hdr_next = __ldg(hdp + (first_stage >> 2));
+            else if (kType == TB200_TYPE_Q6_K) hdr_next = __ldg(hdp + (first_stage >> 2)), d_next = __half2half2(d6p[first_stage >> 2]);
             else d_next = *reinterpret_cast<const __half2 *>(scp + 2 * first_stage);
         }
     }
@@ -295,6 +303,9 @@ struct RowDequant {
         if (kType == TB200_TYPE_Q4_K) {
             hdr = hdr_next;
             if (i + 2 < kt) hdr_next = __ldg(hdp + ((i + 2) >> 2));
+        } else if (kType == TB200_TYPE_Q6_K) {
+            hdr = hdr_next, dpair = d_next;
+            if (i + 2 < kt) hdr_next = __ldg(hdp + ((i + 2) >> 2)), d_next = __half2half2(d6p[(i + 2) >> 2]);
         } else {
             dpair = d_next;
             if (i + 2 < kt) d_next = *reinterpret_cast<const __half2 *>(scp + 2 * (i + 2));
@@ -326,6 +337,28 @@ struct RowDequant {
             a = dequant_q8_word(w1.y, d2), r[10] = a.x, r[11] = a.y;
             a = dequant_q8_word(w1.z, d2), r[12] = a.x, r[13] = a.y;
             a = dequant_q8_word(w1.w, d2), r[14] = a.x, r[15] = a.y;
+        } else if (kType == TB200_TYPE_Q6_K) {
+            // stage i is unit u = i & 3 of super-block i >> 2: 48 bytes {qlA, qlB, qh}; half `chalf` of the stage is j = 2*chalf,
+            // 2*chalf+1 (16 elements each, scale byte 8*(u>>1) + (u&1) + 2j): value = fp16(d*sc_j) * (q6 - 32), q6 - 32 exact in fp16
+            const int u = i & 3, hf = u >> 1, rr = u & 1;
+            const uint8_t *rp = tile + row * 48;     // 48-byte row stride: the 8 lanes of a quarter-warp hit 8 distinct bank groups
+            const uint4 qa = *reinterpret_cast<const uint4 *>(rp), qb = *reinterpret_cast<const uint4 *>(rp + 16),
+                        qh = *reinterpret_cast<const uint4 *>(rp + 32);
+            const uint32_t sw = chalf ? (hf ? hdr.w : hdr.y) : (hf ? hdr.z : hdr.x);   // scales 8*hf + 4*chalf + [0,4)
+            const int sA = (int)(sw << (24 - 8 * rr)) >> 24, sB = (int)(sw << (8 - 8 * rr)) >> 24;   // bytes rr and rr + 2
+            const float d = __low2float(dpair);
+            const __half2 aA = __float2half2_rn(d * (float)sA), aB = __float2half2_rn(d * (float)sB);
+            const __half2 k1056 = __floats2half2_rn(1056.f, 1056.f);
+            const uint32_t a[4] = {qa.x, qa.y, qa.z, qa.w}, b[4] = {qb.x, qb.y, qb.z, qb.w}, h[4] = {qh.x, qh.y, qh.z, qh.w};
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                const uint32_t xa = chalf ? (((a[w] >> 4) & 0x0f0f0f0fu) | (h[w] & 0x30303030u)) : ((a[w] & 0x0f0f0f0fu) | ((h[w] << 4) & 0x30303030u));
+                const uint32_t xb = chalf ? (((b[w] >> 4) & 0x0f0f0f0fu) | ((h[w] >> 2) & 0x30303030u)) : ((b[w] & 0x0f0f0f0fu) | ((h[w] << 2) & 0x30303030u));
+                r[2 * w] = h2_sub_mul(__byte_perm(xa, 0x64646464u, 0x4140), k1056, aA);       // bytes -> fp16 1024 + q, natural order
+                r[2 * w + 1] = h2_sub_mul(__byte_perm(xa, 0x64646464u, 0x4342), k1056, aA);
+                r[8 + 2 * w] = h2_sub_mul(__byte_perm(xb, 0x64646464u, 0x4140), k1056, aB);
+                r[8 + 2 * w + 1] = h2_sub_mul(__byte_perm(xb, 0x64646464u, 0x4342), k1056, aB);
+            }
         } else {   // Q4_K: stage i is 64-element chunk c = i & 3 of super-block i >> 2
             const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr.x);
             const float d = __low2float(dd), dmin = __high2float(dd);
@@ -350,7 +383,7 @@ template <int kType, int BN, int kStages>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                                                                    const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
     constexpr bool kTS = kType != TB200_TYPE_F16;   // A' in tensor memory (dequantised types) or in shared memory (F16, via TMA)
-    constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 0 : BM * BK / 2);
+    constexpr int kPackedBytes = BM * packed_row_bytes(kType);
     constexpr int kABytes = kTS ? 0 : BM * BK * 2, kBBytes = BN * BK * 2;
     constexpr uint32_t kAccCols = BN < 32 ? 32 : BN;                 // accumulator columns [0, kAccCols)
     constexpr uint32_t kTmemCols = tmem_cols_pow2(kAccCols + (kTS ? kStages * 32 : 0));   // A' ring: 32 columns (64 fp16) per stage
@@ -407,7 +440,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
                     tma_load_2d(sA + s * kABytes, &map_w, &full_a[s], i * BK, (int)(w_row0 + tile_row));
                 } else {
                     mbar_expect_tx(&full_p[s], kPackedBytes);
-                    tma_load_2d(sP + s * kPackedBytes, &map_w, &full_p[s], i * (kType == TB200_TYPE_Q8_0 ? BK : BK / 2), (int)(w_row0 + tile_row));
+                    tma_load_2d(sP + s * kPackedBytes, &map_w, &full_p[s], i * packed_row_bytes(kType), (int)(w_row0 + tile_row));
                 }
                 mbar_expect_tx(&full_b[s], kBBytes);
                 tma_load_2d(sB + s * kBBytes, &map_b, &full_b[s], i * BK, (int)tile_tok);
@@ -499,7 +532,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
     constexpr bool kTS = kType != TB200_TYPE_F16;
     constexpr int BNH = BN / 2;                      // B' rows staged by each CTA
-    constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 0 : BM * BK / 2);
+    constexpr int kPackedBytes = BM * packed_row_bytes(kType);
     constexpr int kABytes = kTS ? 0 : BM * BK * 2, kBBytes = BNH * BK * 2;
     constexpr uint32_t kAccCols = BN;
     constexpr uint32_t kTmemCols = tmem_cols_pow2(kAccCols + (kTS ? kStages * 32 : 0));
@@ -558,7 +591,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
                     tma_load_2d_pair(sA + s * kABytes, &map_w, mapa_rank(smem_u32(&full_a[s]), 0), i * BK, (int)(w_row0 + tile_row));
                 } else {
                     mbar_expect_tx(&full_p[s], kPackedBytes);
-                    tma_load_2d(sP + s * kPackedBytes, &map_w, &full_p[s], i * (kType == TB200_TYPE_Q8_0 ? BK : BK / 2), (int)(w_row0 + tile_row));
+                    tma_load_2d(sP + s * kPackedBytes, &map_w, &full_p[s], i * packed_row_bytes(kType), (int)(w_row0 + tile_row));
                 }
                 if (leader) mbar_expect_tx(&full_b[s], 2 * kBBytes);
                 tma_load_2d_pair(sB + s * kBBytes, &map_b, mapa_rank(smem_u32(&full_b[s]), 0), i * BK, (int)(tile_tok + rank * BNH));
@@ -640,7 +673,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 
 // ------------------------------------------------------------------------------------------------ activation prep
 // planar Q8 activations -> B' fp16 [tokens][k] in the weight type's K order, scaled by 2^-e_t; colscale[t] = 2^e_t.
-// perm: 0 natural (Q8_0), 1 Q4_0 order per 32-block, 2 Q4_K order per 64-chunk.
+// perm: 0 natural (Q8_0), 1 Q4_0 order per 32-block, 2 Q4_K order per 64-chunk, 3 Q6_K unit order per super-block.
 __device__ __forceinline__ int perm_pos(int perm, int kk) {   // position of element kk inside its 64-element group
     if (perm == 0) return kk;
     if (perm == 1) {   // within a 32-block: element e -> word w = (e & 15) >> 2, slot: low nibble elems (4w,4w+2,4w+1,4w+3), high +16
@@ -682,7 +715,12 @@ __global__ void __launch_bounds__(256) prep_acts_kernel(const int8_t *__restrict
     for (long i = threadIdx.x; i < k; i += blockDim.x) {
         const float d = __int_as_float(ds[i >> 5].x);
         const float v = __fmul_rn(__fmul_rn(d, (float)q[i]), inv);
-        bp[t * k + (i & ~63L) + perm_pos(perm, (int)(i & 63))] = __float2half_rn(v);
+        long dst;
+        if (perm == 3) {   // Q6_K: element 128*half + 32*j + 16*r + e of a super-block -> stage u = 2*half + r, position 16*j + e
+            const int e256 = (int)(i & 255), hf = e256 >> 7, j = (e256 >> 5) & 3, r = (e256 >> 4) & 1, e = e256 & 15;
+            dst = (i & ~255L) + (hf * 2 + r) * 64 + j * 16 + e;
+        } else dst = (i & ~63L) + perm_pos(perm, (int)(i & 63));
+        bp[t * k + dst] = __float2half_rn(v);
     }
 }
 
@@ -740,7 +778,7 @@ void *gemm_scratch(tb200_ctx *c, size_t bytes) {
 
 template <int kType, int BN, int kStages>
 int launch_cfg(tb200_ctx *c, const CUtensorMap &mw, const CUtensorMap &mb, const GemmParams &p) {
-    constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 16 : BM * BK / 2);
+    constexpr int kPackedBytes = kType == TB200_TYPE_F16 ? 16 : BM * packed_row_bytes(kType);
     constexpr int kABytes = kType == TB200_TYPE_F16 ? BM * BK * 2 : 0;   // dequantised A' lives in tensor memory
     constexpr size_t smem = 1024 + (size_t)kStages * (kABytes + BN * BK * 2 + kPackedBytes) + (4 * kStages + 1) * 8 + 16;
     static_assert(smem <= 227 * 1024, "stage configuration exceeds shared memory");
@@ -765,6 +803,7 @@ CUtensorMap *weight_map(const tb200_weights *w) {
         bool ok;
         if (w->type == TB200_TYPE_F16) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k * 2, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
         else if (w->type == TB200_TYPE_Q8_0) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k, BK, BM, CU_TENSOR_MAP_SWIZZLE_64B);
+        else if (w->type == TB200_TYPE_Q6_K) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / QK_K * 192, (uint64_t)w->rows, (uint64_t)w->k / QK_K * 192, 48, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
         else ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / 2, (uint64_t)w->rows, (uint64_t)w->k / 2, BK / 2, BM, CU_TENSOR_MAP_SWIZZLE_32B);
         if (!ok) { delete m; return nullptr; }
         const_cast<tb200_weights *>(w)->tmap_cache = m;
@@ -774,7 +813,7 @@ CUtensorMap *weight_map(const tb200_weights *w) {
 
 template <int kType, int BN, int kStages>
 int launch_cfg_pair(tb200_ctx *c, const CUtensorMap &mw, const CUtensorMap &mb, const GemmParams &p) {
-    constexpr int kPackedBytes = kType == TB200_TYPE_Q8_0 ? BM * BK : (kType == TB200_TYPE_F16 ? 16 : BM * BK / 2);
+    constexpr int kPackedBytes = kType == TB200_TYPE_F16 ? 16 : BM * packed_row_bytes(kType);
     constexpr int kABytes = kType == TB200_TYPE_F16 ? BM * BK * 2 : 0;
     constexpr size_t smem = 1024 + (size_t)kStages * (kABytes + (BN / 2) * BK * 2 + kPackedBytes) + (4 * kStages + 1) * 8 + 16;
     static_assert(smem <= 227 * 1024, "stage configuration exceeds shared memory");
@@ -819,7 +858,7 @@ int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long toke
         return launch_cfg_pair<kType, 128, 8>(c, mw, mb, p);
     }
     switch (bn) {
-    case 256: return launch_cfg<kType, 256, f16 ? 4 : (kType == TB200_TYPE_Q8_0 ? 5 : 6)>(c, mw, mb, p);
+    case 256: return launch_cfg<kType, 256, f16 ? 4 : ((kType == TB200_TYPE_Q8_0 || kType == TB200_TYPE_Q6_K) ? 5 : 6)>(c, mw, mb, p);
     case 128: return launch_cfg<kType, 128, f16 ? 5 : 8>(c, mw, mb, p);
     case 64: return launch_cfg<kType, 64, f16 ? 6 : 8>(c, mw, mb, p);
     default: return launch_cfg<kType, 32, f16 ? 6 : 8>(c, mw, mb, p);
@@ -908,7 +947,7 @@ int tb200_launch_gemm_grouped(tb200_ctx *c, const tb200_weights *w, int experts,
     if (w->type == TB200_TYPE_F16) {
         TB_CUDA(tb200_launch(gather_f16_kernel, dim3((unsigned)pairs), dim3(256), 0, c->stream, (const __half *)af, w->k, (const int *)order, thinkers, tasks, bp, colscale));
     } else {
-        const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : 2);
+        const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : (w->type == TB200_TYPE_Q6_K ? 3 : 2));
         TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)pairs), dim3(256), 0, c->stream, aq, ads, w->k, w->k, perm, bp, colscale, (const int *)order, thinkers, tasks));
     }
     CUtensorMap *mwp = weight_map(w);
@@ -916,7 +955,8 @@ int tb200_launch_gemm_grouped(tb200_ctx *c, const tb200_weights *w, int experts,
     CUtensorMap &mw = *mwp;
     GemmParams p;
     p.sc = w->sc;
-    p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
+    p.sc_row_stride = tb200_is_kquant(w->type) ? w->k / QK_K : w->k / QK;
+    p.d6 = w->d;
     p.row0 = 0, p.nrows = rows, p.k = w->k, p.tokens = pairs, p.colscale = colscale, p.out = result, p.ldo = rows;
     p.tiles = tiles, p.rowmap = order, p.n_tiles = max_tiles;
     p.world = 1, p.local_base = nullptr;
@@ -957,7 +997,7 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
         b_src = af;
         TB_CUDA(tb200_launch(fill_ones_kernel, dim3((unsigned)((tokens + 255) / 256)), dim3(256), 0, c->stream, colscale, tokens));
     } else {
-        const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : 2);
+        const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : (w->type == TB200_TYPE_Q6_K ? 3 : 2));
         TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)tokens), dim3(256), 0, c->stream, aq, ads, a_stride, w->k, perm, bp, colscale, (const int *)nullptr, 1, 1));
     }
     // weight tensor map (whole matrix), cached on the weights object
@@ -966,7 +1006,8 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
     CUtensorMap &mw = *mwp;
     GemmParams p;
     p.sc = w->sc;
-    p.sc_row_stride = w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK;
+    p.sc_row_stride = tb200_is_kquant(w->type) ? w->k / QK_K : w->k / QK;
+    p.d6 = w->d;
     p.row0 = row0, p.nrows = nrows, p.k = w->k, p.tokens = tokens, p.colscale = colscale, p.out = out, p.ldo = ldo;
     p.tiles = nullptr, p.rowmap = nullptr, p.n_tiles = 0;
     p.world = 1, p.local_base = nullptr;
@@ -979,6 +1020,7 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
     case TB200_TYPE_Q4_0: return launch_type<TB200_TYPE_Q4_0>(c, w, mw, tokens, (void *)b_src, p);
     case TB200_TYPE_Q8_0: return launch_type<TB200_TYPE_Q8_0>(c, w, mw, tokens, (void *)b_src, p);
     case TB200_TYPE_Q4_K: return launch_type<TB200_TYPE_Q4_K>(c, w, mw, tokens, (void *)b_src, p);
+    case TB200_TYPE_Q6_K: return launch_type<TB200_TYPE_Q6_K>(c, w, mw, tokens, (void *)b_src, p);
     case TB200_TYPE_F16: return launch_type<TB200_TYPE_F16>(c, w, mw, tokens, (void *)b_src, p);
     default: return TB200_ERR_UNSUPPORTED;
     }

@@ -43,6 +43,7 @@ struct GemvQ4Args {
     int cta_begin[kMaxMats + 1];
     const void *qs[kMaxMats];
     const void *sc[kMaxMats];
+    const void *d6[kMaxMats];           // Q6_K: fp16 super-block scale plane
     long row0[kMaxMats], nrows[kMaxMats];
     float *out[kMaxMats];
     long ldo[kMaxMats];
@@ -604,6 +605,159 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const __grid_con
     store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane, active);
 }
 
+// ---- Q6_K ---------------------------------------------------------------------------------------
+// Resident layout (tb200_repack.cu): per super-block 4 units of 48 B = {qlA, qlB, qh}; unit u = 2*half + r covers the
+// 64 elements 128*half + 16*r + 32*j + [0,16), j = 0..3, with q = (nibble | 2 high bits << 4) - 32 and one int8 scale
+// per j: scales[8*half + r + 2j] (dequantize_row_q6_K, ggml-quants.c:2970-3000; dot: ggml_vec_dot_q6_K_q8_K scalar
+// branch :8642-8682, served by iqk DequantizerQ6K, llamafile/iqk_mul_mat.inc:570-600). A lane owns one unit (3 x 16-byte
+// loads, 48 contiguous bytes), 4 lanes share a super-block, a warp step covers 8 super-blocks = 1.5 KB of one row.
+// The 6-bit values are assembled four at a time with word-wide logic, re-centred with one per-byte subtract and
+// multiplied with dp4a; the integer sum of a super-block is exact, like the reference's.
+// Shared memory: activations [T][super-block][j][u] as 16-byte pieces, 20 pieces per super-block (4 of padding) so the
+// 8 lanes of a quarter-warp (2 super-blocks x 4 units) hit 8 distinct bank groups; then the Q8_K scale per sub-block.
+constexpr int kQ6KSmemPerSb = 20 * 16 + 64;
+
+template <int T, int R>
+__global__ void __launch_bounds__(kWarps * 32) gemv_q6_K_kernel(const __grid_constant__ GemvQ4Args A) {
+    constexpr int U = (T * R <= 2) ? 2 : 1;   // super-blocks per 4-lane group per row in flight
+    extern __shared__ __align__(16) uint8_t smem[];
+    const long nsb = A.nb, nsbc = A.nbc;
+    uint4 *s_q = reinterpret_cast<uint4 *>(smem);                       // [T][nsbc][20]
+    int2 *s_ds = reinterpret_cast<int2 *>(s_q + T * nsbc * 20);         // [T][nsbc*8]
+    __shared__ int s_arow[T];
+
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int mat = 0;
+#pragma unroll
+    for (int m = 1; m < kMaxMats; ++m)
+        if (m < A.nmat && (int)blockIdx.x >= A.cta_begin[m]) mat = m;
+    const long nrows = A.nrows[mat];
+    const long r_base = ((long)((int)blockIdx.x - A.cta_begin[mat]) * kWarps + warp) * R;
+    const bool active = r_base < nrows;
+    const uint4 *qs = (const uint4 *)A.qs[mat];
+    const uint4 *sc = (const uint4 *)A.sc[mat];
+    const __half *dp = (const __half *)A.d6[mat];
+    const int u = lane & 3, grp = lane >> 2;
+    const int half = u >> 1, rr = u & 1;       // scales of this unit: bytes 8*half + rr + 2j of the 16
+
+    uint4 wa[U][R], wb[U][R], wh[U][R], hdr[U][R];
+    __half dw[U][R];
+    long rowv[R];
+    auto set_rows = [&](long my_row0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) rowv[r] = my_row0 + min(r_base + r, nrows - 1);
+    };
+    auto load_batch = [&](long sbase, long end) {   // super-blocks sbase + grp + 8u' (row-relative), limited to < end
+#pragma unroll
+        for (int uu = 0; uu < U; ++uu) {
+            const long sb = sbase + grp + 8 * uu;
+            if (sb < end) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const uint4 *pw = qs + (rowv[r] * nsb + sb) * 12 + 3 * u;
+                    wa[uu][r] = ldg_stream(pw);
+                    wb[uu][r] = ldg_stream(pw + 1);
+                    wh[uu][r] = ldg_stream(pw + 2);
+                    hdr[uu][r] = __ldg(sc + rowv[r] * nsb + sb);
+                    dw[uu][r] = dp[rowv[r] * nsb + sb];
+                }
+            }
+        }
+    };
+
+    int ntok = T, orow[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) orow[t] = t;
+    if (!A.items) {
+        set_rows(A.row0[mat]);
+        if (active) load_batch(0, min(nsbc, nsb));
+    }
+    pdl_wait();
+    if (A.items) {
+        const tb200_gemv_item &it = A.items[blockIdx.y];
+        ntok = it.ntok;
+        if (ntok == 0) return;   // CTA-uniform
+        set_rows(it.row0);
+#pragma unroll
+        for (int t = 0; t < T; ++t) orow[t] = it.out_row[min(t, ntok - 1)];
+        if (threadIdx.x < T) s_arow[threadIdx.x] = it.a_row[min((int)threadIdx.x, ntok - 1)];
+        if (active) load_batch(0, min(nsbc, nsb));
+    } else if (threadIdx.x < T) s_arow[threadIdx.x] = threadIdx.x;
+    __syncthreads();
+
+    float acc[R][T];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+
+    for (long sb0 = 0; sb0 < nsb; sb0 += nsbc) {
+        const long cnt = min(nsbc, nsb - sb0);
+        if (sb0) __syncthreads();
+        const int nsbc_i = (int)nsbc;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const uint4 *src = reinterpret_cast<const uint4 *>(A.aq + (long)s_arow[t] * A.a_stride + sb0 * QK_K);
+            const int2 *dsrc = A.ads + (long)s_arow[t] * (A.a_stride / QK) + sb0 * 8;
+            for (int g = threadIdx.x; g < (int)cnt * 16; g += kWarps * 32) {
+                // natural piece q = 8*half + 2j + r of its super-block -> slot 4j + (2*half + r)
+                const int q = g & 15, pos = ((q & 7) >> 1) * 4 + ((q >> 3) * 2 + (q & 1));
+                s_q[(t * nsbc_i + (g >> 4)) * 20 + pos] = src[g];
+            }
+            for (int g = threadIdx.x; g < (int)cnt * 8; g += kWarps * 32) s_ds[t * nsbc_i * 8 + g] = dsrc[g];
+        }
+        __syncthreads();
+        if (!active) continue;
+        for (long sbb = 0; sbb < cnt; sbb += 8 * U) {
+            if (sb0 | sbb) load_batch(sb0 + sbb, sb0 + cnt);
+#pragma unroll
+            for (int uu = 0; uu < U; ++uu) {
+                const int sb = (int)sbb + grp + 8 * uu;   // chunk-relative
+                if (sb < (int)cnt) {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const uint4 h = hdr[uu][r];
+                        const float d = __half2float(dw[uu][r]);
+                        // scales 8*half + rr + {0,2,4,6}: words 2*half and 2*half+1, bytes rr and rr+2 (sign-extended)
+                        const uint32_t s01 = half ? h.z : h.x, s23 = half ? h.w : h.y;
+                        const int sc0 = (int)(s01 << (24 - 8 * rr)) >> 24, sc1 = (int)(s01 << (8 - 8 * rr)) >> 24;
+                        const int sc2 = (int)(s23 << (24 - 8 * rr)) >> 24, sc3 = (int)(s23 << (8 - 8 * rr)) >> 24;
+                        const uint32_t a[4] = {wa[uu][r].x, wa[uu][r].y, wa[uu][r].z, wa[uu][r].w};
+                        const uint32_t b[4] = {wb[uu][r].x, wb[uu][r].y, wb[uu][r].z, wb[uu][r].w};
+                        const uint32_t hh[4] = {wh[uu][r].x, wh[uu][r].y, wh[uu][r].z, wh[uu][r].w};
+                        uint32_t q0[4], q1[4], q2[4], q3[4];
+#pragma unroll
+                        for (int w = 0; w < 4; ++w) {   // (nibble | 2 high bits << 4) - 32 per byte; no borrow crosses bytes (0..63 - 32)
+                            q0[w] = __vsub4((a[w] & 0x0f0f0f0fu) | ((hh[w] << 4) & 0x30303030u), 0x20202020u);
+                            q1[w] = __vsub4((b[w] & 0x0f0f0f0fu) | ((hh[w] << 2) & 0x30303030u), 0x20202020u);
+                            q2[w] = __vsub4(((a[w] >> 4) & 0x0f0f0f0fu) | (hh[w] & 0x30303030u), 0x20202020u);
+                            q3[w] = __vsub4(((b[w] >> 4) & 0x0f0f0f0fu) | ((hh[w] >> 2) & 0x30303030u), 0x20202020u);
+                        }
+#pragma unroll
+                        for (int t = 0; t < T; ++t) {
+                            const uint4 *ap = s_q + (t * nsbc_i + sb) * 20 + u;
+                            const uint4 y0 = ap[0], y1 = ap[4], y2 = ap[8], y3 = ap[12];
+                            int d0 = dp4a_ss((int)q0[0], (int)y0.x, 0), d1 = dp4a_ss((int)q1[0], (int)y1.x, 0);
+                            int d2 = dp4a_ss((int)q2[0], (int)y2.x, 0), d3 = dp4a_ss((int)q3[0], (int)y3.x, 0);
+                            d0 = dp4a_ss((int)q0[1], (int)y0.y, d0), d1 = dp4a_ss((int)q1[1], (int)y1.y, d1);
+                            d2 = dp4a_ss((int)q2[1], (int)y2.y, d2), d3 = dp4a_ss((int)q3[1], (int)y3.y, d3);
+                            d0 = dp4a_ss((int)q0[2], (int)y0.z, d0), d1 = dp4a_ss((int)q1[2], (int)y1.z, d1);
+                            d2 = dp4a_ss((int)q2[2], (int)y2.z, d2), d3 = dp4a_ss((int)q3[2], (int)y3.z, d3);
+                            d0 = dp4a_ss((int)q0[3], (int)y0.w, d0), d1 = dp4a_ss((int)q1[3], (int)y1.w, d1);
+                            d2 = dp4a_ss((int)q2[3], (int)y2.w, d2), d3 = dp4a_ss((int)q3[3], (int)y3.w, d3);
+                            const float dy = __int_as_float(s_ds[(t * nsbc_i + sb) * 8].x);   // Q8_K: one d per super-block
+                            const int isum = sc0 * d0 + sc1 * d1 + sc2 * d2 + sc3 * d3;
+                            acc[r][t] = fmaf(d * dy, (float)isum, acc[r][t]);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    store_rows<T, R>(A, mat, acc, orow, ntok, r_base, nrows, lane, active);
+}
+
 // ---- F16 ----------------------------------------------------------------------------------------
 template <int T, int R, bool kActF32>
 __global__ void __launch_bounds__(kWarps * 32) gemv_f16_kernel(const __half *__restrict__ wt, long k, long kc, long row0, long nrows,
@@ -694,6 +848,29 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_f16_kernel(const __half *__r
 __global__ void blockdot_kernel(int type, const uint8_t *__restrict__ qs, const uint8_t *__restrict__ sc, long rows, long k,
                                 const int8_t *__restrict__ aq, const int2 *__restrict__ ads, int32_t *__restrict__ out) {
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (type == TB200_TYPE_Q6_K) {   // one int32 per super-block: sum_j scale_j * sum (q6 - 32) * q8, from the resident unit layout
+        const long nsb = k / QK_K;
+        if (i >= rows * nsb) return;
+        const long sb = i % nsb;
+        const uint8_t *q = qs + i * 192;
+        const int8_t *scl = reinterpret_cast<const int8_t *>(sc) + i * 16;
+        int sum = 0;
+        for (int u = 0; u < 4; ++u) {
+            const int half = u >> 1, r = u & 1;
+            const uint8_t *qa = q + u * 48, *qb = qa + 16, *qh = qa + 32;
+            for (int j = 0; j < 4; ++j) {
+                int dot = 0;
+                for (int l = 0; l < 16; ++l) {
+                    const int nib = j == 0 ? (qa[l] & 0xF) : j == 1 ? (qb[l] & 0xF) : j == 2 ? (qa[l] >> 4) : (qb[l] >> 4);
+                    const int q6 = (nib | (((qh[l] >> (2 * j)) & 3) << 4)) - 32;
+                    dot += q6 * aq[sb * 256 + 128 * half + 16 * r + 32 * j + l];
+                }
+                sum += (int)scl[8 * half + r + 2 * j] * dot;
+            }
+        }
+        out[i] = sum;
+        return;
+    }
     if (type == TB200_TYPE_Q4_K) {
         const long nsb = k / QK_K;
         if (i >= rows * nsb) return;
@@ -750,7 +927,7 @@ int fill_args(GemvQ4Args &ka, const tb200_gemv_args &a, long nb, long nbc) {
         const long nr = m == 0 ? a.nrows : wm->rows;
         ka.cta_begin[m] = ctas;
         ctas += (int)((nr + kWarps * R - 1) / (kWarps * R));
-        ka.qs[m] = wm->qs, ka.sc[m] = wm->sc;
+        ka.qs[m] = wm->qs, ka.sc[m] = wm->sc, ka.d6[m] = wm->d;
         ka.row0[m] = m == 0 ? a.row0 : 0, ka.nrows[m] = nr;
         ka.out[m] = m == 0 ? a.out : a.out_more[m - 1], ka.ldo[m] = m == 0 ? a.ldo : a.ldo_more[m - 1];
     }
@@ -799,6 +976,18 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         const dim3 g2((unsigned)ctas, grid.y);
         if ((rc = set_smem(gemv_q4_K_kernel<T, R>, smem))) return rc;
         TB_CUDA(tb200_launch(gemv_q4_K_kernel<T, R>, g2, dim3(kWarps * 32), smem, c->stream, ka));
+        break;
+    }
+    case TB200_TYPE_Q6_K: {
+        const long nsb = w->k / QK_K;
+        long nsbc = (long)(kSmemBudget / ((size_t)T * kQ6KSmemPerSb)) / 8 * 8;
+        if (nsbc >= nsb) nsbc = nsb;
+        const size_t smem = (size_t)T * nsbc * kQ6KSmemPerSb;
+        GemvQ4Args ka;
+        const int ctas = fill_args<R>(ka, a, nsb, nsbc);
+        const dim3 g2((unsigned)ctas, grid.y);
+        if ((rc = set_smem(gemv_q6_K_kernel<T, R>, smem))) return rc;
+        TB_CUDA(tb200_launch(gemv_q6_K_kernel<T, R>, g2, dim3(kWarps * 32), smem, c->stream, ka));
         break;
     }
     case TB200_TYPE_F16: {
@@ -877,7 +1066,7 @@ int tb200_launch_gemv(tb200_ctx *c, const tb200_gemv_args &a) {
 }
 
 int tb200_launch_blockdot(tb200_ctx *c, const tb200_weights *w, const int8_t *aq, const int2 *ads, int32_t *out) {
-    const long units = w->rows * (w->type == TB200_TYPE_Q4_K ? w->k / QK_K : w->k / QK);
+    const long units = w->rows * (tb200_is_kquant(w->type) ? w->k / QK_K : w->k / QK);
     if (units == 0) return TB200_OK;
     blockdot_kernel<<<(unsigned)((units + 127) / 128), 128, 0, c->stream>>>(w->type, (const uint8_t *)w->qs, (const uint8_t *)w->sc, w->rows, w->k, aq, ads, out);
     tb200_count_launch();

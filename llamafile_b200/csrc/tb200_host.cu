@@ -179,7 +179,7 @@ int lane_issue(tb200_ctx *c, HostLane &L, const LaneKey &k, size_t b_bytes) {
     } else {
         int8_t *q = (int8_t *)L.dact;
         int2 *ds = (int2 *)(L.dact + up256((size_t)k.n * w->k));
-        rc = w->type == TB200_TYPE_Q4_K ? tb200_launch_unpack_q8_K(c, k.dB, k.ldb, k.n, w->k, q, ds) : tb200_launch_unpack_q8_0(c, k.dB, k.ldb, k.n, w->k, q, ds);
+        rc = tb200_is_kquant(w->type) ? tb200_launch_unpack_q8_K(c, k.dB, k.ldb, k.n, w->k, q, ds) : tb200_launch_unpack_q8_0(c, k.dB, k.ldb, k.n, w->k, q, ds);
         if (rc) return rc;
         rc = tb200_run_matmul(c, w, 0, w->rows, q, ds, nullptr, 0, w->k, k.n, (float *)k.dC, k.ldo);
     }
@@ -200,7 +200,7 @@ tb200_weights *cached_weights(const void *A, int type, long rows, long k, size_t
     return w;
 }
 
-int blck(int type) { return (type == TB200_TYPE_Q4_K || type == TB200_TYPE_Q8_K) ? QK_K : (type == TB200_TYPE_Q4_0 || type == TB200_TYPE_Q8_0) ? QK : 1; }
+int blck(int type) { return (tb200_is_kquant(type) || type == TB200_TYPE_Q8_K) ? QK_K : (type == TB200_TYPE_Q4_0 || type == TB200_TYPE_Q8_0) ? QK : 1; }
 size_t tsize(int type) { return tb200_gguf_row_bytes(type, blck(type)); }
 
 }  // namespace
@@ -228,7 +228,7 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
     if (m == 0 || n == 0) return true;
     const long ke = k * blck(Atype);
     // iqk (Q4_0, Q4_K) takes rows ggml_row_size apart and ignores lda/ldb (iqk_mul_mat.inc:191-199); tinyBLAS honours them
-    const bool iqk = Atype == TB200_TYPE_Q4_0 || Atype == TB200_TYPE_Q4_K;
+    const bool iqk = Atype == TB200_TYPE_Q4_0 || tb200_is_kquant(Atype);
     const size_t a_stride = iqk ? tb200_gguf_row_bytes(Atype, ke) : (size_t)lda * tsize(Atype);
     const long ldb_eff = iqk ? k : ldb;
     tb200_weights *w = cached_weights(A, Atype, m, ke, a_stride);
@@ -409,13 +409,13 @@ bool llamafile_mixmul(const struct ggml_compute_params *params_, const struct gg
 // [ne12][ne11], C row for mapping y = C + i1*nb1 + i2*nb2, B row = (i1 % ne11) + i2*ne11.
 bool llamafile_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, const void *A, const void *B, float *C, long nb1, long nb2,
                           const void *vrow_mapping, int ith, int nth) {
-    if (typeA != TB200_TYPE_Q4_K && typeA != TB200_TYPE_Q4_0) return false;   // the other iqk types are outside this module
+    if (!tb200_is_kquant(typeA) && typeA != TB200_TYPE_Q4_0) return false;   // the other iqk types are outside this module
     if (!vrow_mapping || Nx < 0 || Ny < 0 || ne11 <= 0 || nth <= 0 || ith < 0 || ith >= nth || ne00 % blck(typeA)) return false;
     tb200_ctx *c = tb200_get_ctx();
     if (!c) return false;
     if (ith != 0) return true;
     if (Nx == 0 || Ny == 0) return true;
-    const int Btype = typeA == TB200_TYPE_Q4_K ? TB200_TYPE_Q8_K : TB200_TYPE_Q8_0;
+    const int Btype = tb200_is_kquant(typeA) ? TB200_TYPE_Q8_K : TB200_TYPE_Q8_0;
     tb200_weights *w = cached_weights(A, typeA, Nx, ne00, 0);
     if (!w) return false;
     const int32_t *rm = (const int32_t *)vrow_mapping;

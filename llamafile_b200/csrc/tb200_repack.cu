@@ -5,6 +5,7 @@
 //   block_q4_0 {fp16 d; u8 qs[16]}            (ggml-common.h:144-149) -> sc[b] = d, qs[b] = 16 B
 //   block_q8_0 {fp16 d; i8 qs[32]}            (ggml-common.h:186-191) -> sc[b] = d, qs[b] = 32 B
 //   block_q4_K {d, dmin, scales[12]; qs[128]} (ggml-common.h:266-277) -> sc[b] = first 16 B, qs[b] = 128 B
+//   block_q6_K {ql[128]; qh[64]; scales[16]; d} (ggml-common.h:299-307) -> qs[b] = 4 units x 48 B, sc[b] = 16 B, d[b]
 #include "tb200_common.cuh"
 
 namespace {
@@ -55,9 +56,32 @@ __global__ void repack_q4_K_kernel(const uint8_t *__restrict__ raw, size_t row_s
     else qs[blk * 32 + (w - 4)] = v;
 }
 
+// block_q6_K {ql[128], qh[64], scales[16], d} (ggml-common.h:299-307) -> 4 units of 48 B + scales + d. One thread per
+// 16-byte piece of the 192 quant bytes (12 pieces) plus one for the 16 scales and d. Unit u = 2*half + r holds
+// ql[64*half + 16*r ..], ql[64*half + 32 + 16*r ..], qh[32*half + 16*r ..] (the three pieces dequantize_row_q6_K,
+// ggml-quants.c:2970-3000, combines for l in [16r, 16r+16) of that half).
+__global__ void repack_q6_K_kernel(const uint8_t *__restrict__ raw, size_t row_stride, long rows, long nb,
+                                   uint8_t *__restrict__ qs, uint8_t *__restrict__ sc, uint16_t *__restrict__ d) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i >= rows * nb * 13) return;
+    const long blk = i / 13;
+    const int piece = (int)(i % 13);
+    const long row = blk / nb, b = blk % nb;
+    const uint8_t *src = raw + row * row_stride + b * sizeof(tb200_block_q6_K);
+    if (piece == 12) {
+        for (int j = 0; j < 16; ++j) sc[blk * 16 + j] = src[192 + j];
+        d[blk] = (uint16_t)src[208] | ((uint16_t)src[209] << 8);
+        return;
+    }
+    const int u = piece / 3, part = piece % 3, half = u >> 1, r = u & 1;
+    const int off = part == 0 ? 64 * half + 16 * r : (part == 1 ? 64 * half + 32 + 16 * r : 128 + 32 * half + 16 * r);
+    uint8_t *dst = qs + blk * 192 + piece * 16;
+    for (int j = 0; j < 16; ++j) dst[j] = src[off + j];
+}
+
 }  // namespace
 
-int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long k, size_t row_stride, void *qs, void *sc) {
+int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long k, size_t row_stride, void *qs, void *sc, void *d) {
     if (rows == 0 || k == 0) return TB200_OK;
     const uint8_t *r = (const uint8_t *)raw;
     switch (type) {
@@ -74,6 +98,11 @@ int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long
     case TB200_TYPE_Q4_K: {
         const long nb = k / QK_K, n = rows * nb * 36;
         repack_q4_K_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(r, row_stride, rows, nb, (uint32_t *)qs, (uint32_t *)sc);
+        break;
+    }
+    case TB200_TYPE_Q6_K: {
+        const long nb = k / QK_K, n = rows * nb * 13;
+        repack_q6_K_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(r, row_stride, rows, nb, (uint8_t *)qs, (uint8_t *)sc, (uint16_t *)d);
         break;
     }
     case TB200_TYPE_F16:

@@ -17,10 +17,10 @@ HERE = Path(__file__).resolve().parent
 ORACLE_SO = HERE / "_build" / "liboracle.so"
 REF_SO = HERE / "_ref" / "libtb200_ref.so"
 
-F32, F16, Q4_0, Q8_0, Q4_K, Q8_K, I32 = 0, 1, 2, 8, 12, 15, 26
-TYPE_SIZE = {F32: 4, F16: 2, Q4_0: 18, Q8_0: 34, Q4_K: 144, Q8_K: 292, I32: 4}
-BLCK = {F32: 1, F16: 1, Q4_0: 32, Q8_0: 32, Q4_K: 256, Q8_K: 256, I32: 1}
-VEC_DOT_TYPE = {Q4_0: Q8_0, Q8_0: Q8_0, Q4_K: Q8_K, F16: F16}   # ggml.c type_traits.vec_dot_type
+F32, F16, Q4_0, Q8_0, Q4_K, Q6_K, Q8_K, I32 = 0, 1, 2, 8, 12, 14, 15, 26
+TYPE_SIZE = {F32: 4, F16: 2, Q4_0: 18, Q8_0: 34, Q4_K: 144, Q6_K: 210, Q8_K: 292, I32: 4}
+BLCK = {F32: 1, F16: 1, Q4_0: 32, Q8_0: 32, Q4_K: 256, Q6_K: 256, Q8_K: 256, I32: 1}
+VEC_DOT_TYPE = {Q4_0: Q8_0, Q8_0: Q8_0, Q4_K: Q8_K, Q6_K: Q8_K, F16: F16}   # ggml.c type_traits.vec_dot_type
 
 
 def row_bytes(t: int, k: int) -> int:
@@ -119,7 +119,7 @@ class Oracle(_Common):
         L.oracle_fp16_to_fp32_row.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.oracle_dequantize_row.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64]
         L.oracle_vec_dot.argtypes = [C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
-        for f in ("oracle_blockdot_q4_0_q8_0", "oracle_blockdot_q8_0_q8_0", "oracle_blockdot_q4_K_q8_K"):
+        for f in ("oracle_blockdot_q4_0_q8_0", "oracle_blockdot_q8_0_q8_0", "oracle_blockdot_q4_K_q8_K", "oracle_blockdot_q6_K_q8_K"):
             getattr(L, f).argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
 
     name = "oracle"
@@ -147,7 +147,8 @@ class Oracle(_Common):
         return out
 
     def blockdot(self, xtype, x, y, nb):
-        fn = {Q4_0: self.lib.oracle_blockdot_q4_0_q8_0, Q8_0: self.lib.oracle_blockdot_q8_0_q8_0, Q4_K: self.lib.oracle_blockdot_q4_K_q8_K}[xtype]
+        fn = {Q4_0: self.lib.oracle_blockdot_q4_0_q8_0, Q8_0: self.lib.oracle_blockdot_q8_0_q8_0, Q4_K: self.lib.oracle_blockdot_q4_K_q8_K,
+              Q6_K: self.lib.oracle_blockdot_q6_K_q8_K}[xtype]
         out = np.zeros(nb * (2 if xtype == Q4_K else 1), np.int32)
         fn(_p(x), _p(y), nb, _p(out))
         return out
@@ -184,11 +185,11 @@ class Reference(_Common):
         L.ref_mixmul_iqk.argtypes = [C.c_long, C.c_long, C.c_long, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_long, C.c_long, C.c_void_p, C.c_int]
         for f in ("ref_quantize_q8_0", "ref_quantize_q8_K"):
             getattr(L, f).argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_long, C.c_int]
-        for f in ("ref_quantize_q8_0_ref", "ref_quantize_q4_0_ref", "ref_quantize_q4_K_ref"):
+        for f in ("ref_quantize_q8_0_ref", "ref_quantize_q4_0_ref", "ref_quantize_q4_K_ref", "ref_quantize_q6_K_ref"):
             getattr(L, f).argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_long]
-        for f in ("ref_fp32_to_fp16_row", "ref_fp16_to_fp32_row", "ref_dequantize_q4_0", "ref_dequantize_q8_0", "ref_dequantize_q4_K"):
+        for f in ("ref_fp32_to_fp16_row", "ref_fp16_to_fp32_row", "ref_dequantize_q4_0", "ref_dequantize_q8_0", "ref_dequantize_q4_K", "ref_dequantize_q6_K"):
             getattr(L, f).argtypes = [C.c_void_p, C.c_void_p, C.c_long]
-        for f in ("ref_vec_dot_q4_0_q8_0", "ref_vec_dot_q8_0_q8_0", "ref_vec_dot_q4_K_q8_K"):
+        for f in ("ref_vec_dot_q4_0_q8_0", "ref_vec_dot_q8_0_q8_0", "ref_vec_dot_q4_K_q8_K", "ref_vec_dot_q6_K_q8_K"):
             getattr(L, f).argtypes = [C.c_long, C.c_void_p, C.c_void_p]
             getattr(L, f).restype = C.c_float
         self.variant = L.ref_variant_name().decode()
@@ -208,6 +209,7 @@ class Reference(_Common):
     def quantize_q8_K(self, X, nth=1): return self._rows(self.lib.ref_quantize_q8_K, X, Q8_K, nth)
     def quantize_q4_0(self, X): return self._rows(self.lib.ref_quantize_q4_0_ref, X, Q4_0)
     def quantize_q4_K(self, X): return self._rows(self.lib.ref_quantize_q4_K_ref, X, Q4_K)
+    def quantize_q6_K(self, X): return self._rows(self.lib.ref_quantize_q6_K_ref, X, Q6_K)
 
     def fp32_to_fp16(self, X):
         X = _f32(X); out = np.zeros(X.size, np.uint16)
@@ -216,12 +218,13 @@ class Reference(_Common):
 
     def dequantize(self, type_, data, n):
         out = np.zeros(n, np.float32)
-        {Q4_0: self.lib.ref_dequantize_q4_0, Q8_0: self.lib.ref_dequantize_q8_0, Q4_K: self.lib.ref_dequantize_q4_K,
+        {Q4_0: self.lib.ref_dequantize_q4_0, Q8_0: self.lib.ref_dequantize_q8_0, Q4_K: self.lib.ref_dequantize_q4_K, Q6_K: self.lib.ref_dequantize_q6_K,
          F16: self.lib.ref_fp16_to_fp32_row}[type_](_p(data), _p(out), n)
         return out
 
     def vec_dot(self, xtype, n, x, y):
-        fn = {Q4_0: self.lib.ref_vec_dot_q4_0_q8_0, Q8_0: self.lib.ref_vec_dot_q8_0_q8_0, Q4_K: self.lib.ref_vec_dot_q4_K_q8_K}[xtype]
+        fn = {Q4_0: self.lib.ref_vec_dot_q4_0_q8_0, Q8_0: self.lib.ref_vec_dot_q8_0_q8_0, Q4_K: self.lib.ref_vec_dot_q4_K_q8_K,
+              Q6_K: self.lib.ref_vec_dot_q6_K_q8_K}[xtype]
         return float(fn(n, _p(x), _p(y)))
 
     def _sgemm(self, m, n, k, A, lda, B, ldb, Cm, ldc, Atype, Btype, Ctype, nth):

@@ -36,12 +36,15 @@ void Q(quantize_row_q8_0_ref)(const float *x, void *y, int64_t k);
 void Q(quantize_row_q8_K)(const float *x, void *y, int64_t k);
 void Q(quantize_row_q4_0_ref)(const float *x, void *y, int64_t k);
 void Q(quantize_row_q4_K_ref)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q6_K_ref)(const float *x, void *y, int64_t k);
 void Q(dequantize_row_q4_0)(const void *x, float *y, int64_t k);
 void Q(dequantize_row_q8_0)(const void *x, float *y, int64_t k);
 void Q(dequantize_row_q4_K)(const void *x, float *y, int64_t k);
+void Q(dequantize_row_q6_K)(const void *x, float *y, int64_t k);
 void Q(ggml_vec_dot_q4_0_q8_0)(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
 void Q(ggml_vec_dot_q8_0_q8_0)(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
 void Q(ggml_vec_dot_q4_K_q8_K)(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
+void Q(ggml_vec_dot_q6_K_q8_K)(int n, float *s, size_t bs, const void *vx, size_t bx, const void *vy, size_t by, int nrc);
 // what llamafile's dispatcher resolves `quantize_row_q8_0` to (imported by tinyblas_cpu_mixmul.inc:343)
 void quantize_row_q8_0(const float *x, void *y, int64_t k) { Q(quantize_row_q8_0)(x, y, k); }
 }
@@ -188,11 +191,17 @@ EXPORT void ref_quantize_q4_K_ref(const float *x, void *y, long rows, long k) {
 #pragma omp parallel for
     for (long r = 0; r < rows; ++r) Q(quantize_row_q4_K_ref)(x + r * k, (char *)y + r * (k / 256) * 144, k);
 }
+EXPORT void ref_quantize_q6_K_ref(const float *x, void *y, long rows, long k) {
+    funcs();
+#pragma omp parallel for
+    for (long r = 0; r < rows; ++r) Q(quantize_row_q6_K_ref)(x + r * k, (char *)y + r * (k / 256) * 210, k);
+}
 EXPORT void ref_fp32_to_fp16_row(const float *x, uint16_t *y, long n) { funcs(); ggml_fp32_to_fp16_row(x, y, n); }
 EXPORT void ref_fp16_to_fp32_row(const uint16_t *x, float *y, long n) { funcs(); ggml_fp16_to_fp32_row(x, y, n); }
 EXPORT void ref_dequantize_q4_0(const void *x, float *y, long n) { funcs(); Q(dequantize_row_q4_0)(x, y, n); }
 EXPORT void ref_dequantize_q8_0(const void *x, float *y, long n) { funcs(); Q(dequantize_row_q8_0)(x, y, n); }
 EXPORT void ref_dequantize_q4_K(const void *x, float *y, long n) { funcs(); Q(dequantize_row_q4_K)(x, y, n); }
+EXPORT void ref_dequantize_q6_K(const void *x, float *y, long n) { funcs(); Q(dequantize_row_q6_K)(x, y, n); }
 
 // the semantic definitions north_star cites (ggml-quants.c:3729, :5227, :6832)
 EXPORT float ref_vec_dot_q4_0_q8_0(long n, const void *x, const void *y) {
@@ -203,6 +212,10 @@ EXPORT float ref_vec_dot_q8_0_q8_0(long n, const void *x, const void *y) {
 }
 EXPORT float ref_vec_dot_q4_K_q8_K(long n, const void *x, const void *y) {
     funcs(); float s = 0; Q(ggml_vec_dot_q4_K_q8_K)((int)n, &s, 0, x, 0, y, 0, 1); return s;
+}
+
+EXPORT float ref_vec_dot_q6_K_q8_K(long n, const void *x, const void *y) {
+    funcs(); float s = 0; Q(ggml_vec_dot_q6_K_q8_K)((int)n, &s, 0, x, 0, y, 0, 1); return s;
 }
 
 // layout of the two ggml structs llamafile_mixmul reads, as the reference's patched ggml.h defines them

@@ -16,7 +16,10 @@ typedef struct { uint16_t d; int8_t qs[32]; } blk_q8_0;                        /
 typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qs[128]; } blk_q4_K; /* 144 B */
 /* llamafile swaps bsums and qs relative to upstream (llama.cpp.patches/patches/ggml-common.h.patch:25-35) */
 typedef struct { float d; int16_t bsums[16]; int8_t qs[256]; } blk_q8_K;       /* 292 B */
+/* llama.cpp/ggml/src/ggml-common.h:299-307 */
+typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d; } blk_q6_K; /* 210 B */
 #pragma pack(pop)
+_Static_assert(sizeof(blk_q6_K) == 210, "q6_K");
 _Static_assert(sizeof(blk_q4_0) == 18, "q4_0");
 _Static_assert(sizeof(blk_q8_0) == 34, "q8_0");
 _Static_assert(sizeof(blk_q4_K) == 144, "q4_K");
@@ -30,13 +33,13 @@ static inline uint16_t f2h(float f) { _Float16 v = (_Float16)f; uint16_t h; memc
 size_t oracle_type_size(int type) {
     switch (type) {
     case OR_F32: return 4; case OR_F16: return 2; case OR_Q4_0: return 18; case OR_Q8_0: return 34;
-    case OR_Q4_K: return 144; case OR_Q8_K: return 292; case OR_I32: return 4; default: return 0;
+    case OR_Q4_K: return 144; case OR_Q6_K: return 210; case OR_Q8_K: return 292; case OR_I32: return 4; default: return 0;
     }
 }
 int oracle_blck_size(int type) {
     switch (type) {
     case OR_F32: case OR_F16: case OR_I32: return 1; case OR_Q4_0: case OR_Q8_0: return 32;
-    case OR_Q4_K: case OR_Q8_K: return 256; default: return 0;
+    case OR_Q4_K: case OR_Q6_K: case OR_Q8_K: return 256; default: return 0;
     }
 }
 
@@ -160,6 +163,27 @@ void oracle_dequantize_row(int type, const void *vx, float *y, int64_t k) {
                 q += 32; is += 2;
             }
         }
+    } else if (type == OR_Q6_K) {   /* ggml-quants.c:2970-3000 */
+        const blk_q6_K *x = (const blk_q6_K *)vx;
+        for (int64_t i = 0; i < k / QK_K; ++i) {
+            const float d = h2f(x[i].d);
+            const uint8_t *ql = x[i].ql, *qh = x[i].qh;
+            const int8_t *sc = x[i].scales;
+            for (int n = 0; n < QK_K; n += 128) {
+                for (int l = 0; l < 32; ++l) {
+                    const int is = l / 16;
+                    const int8_t q1 = (int8_t)((ql[l + 0] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                    const int8_t q2 = (int8_t)((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                    const int8_t q3 = (int8_t)((ql[l + 0] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                    const int8_t q4 = (int8_t)((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+                    y[l + 0] = d * sc[is + 0] * q1;
+                    y[l + 32] = d * sc[is + 2] * q2;
+                    y[l + 64] = d * sc[is + 4] * q3;
+                    y[l + 96] = d * sc[is + 6] * q4;
+                }
+                y += 128; ql += 64; qh += 32; sc += 8;
+            }
+        }
     } else if (type == OR_F16) {
         oracle_fp16_to_fp32_row((const uint16_t *)vx, y, k);
     } else if (type == OR_F32) {
@@ -211,6 +235,33 @@ void oracle_blockdot_q4_K_q8_K(const void *vx, const void *vy, int64_t nb, int32
     }
 }
 
+/* ggml-quants.c:8642-8682 (scalar branch of ggml_vec_dot_q6_K_q8_K), integer part: one int32 per super-block,
+ * sum over the 16 sub-blocks of 16 of scale_j * sum (q6 - 32) * q8 */
+void oracle_blockdot_q6_K_q8_K(const void *vx, const void *vy, int64_t nb, int32_t *out) {
+    const blk_q6_K *x = (const blk_q6_K *)vx; const blk_q8_K *y = (const blk_q8_K *)vy;
+    for (int64_t i = 0; i < nb; ++i) {
+        int8_t a[QK_K];
+        const uint8_t *q4 = x[i].ql, *qh = x[i].qh;
+        int8_t *ap = a;
+        for (int j = 0; j < QK_K; j += 128) {
+            for (int l = 0; l < 32; ++l) {
+                ap[l + 0] = (int8_t)((q4[l + 0] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                ap[l + 32] = (int8_t)((q4[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                ap[l + 64] = (int8_t)((q4[l + 0] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                ap[l + 96] = (int8_t)((q4[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+            }
+            ap += 128; q4 += 64; qh += 32;
+        }
+        int32_t sum = 0;
+        for (int j = 0; j < QK_K / 16; ++j) {
+            int32_t dot = 0;
+            for (int l = 0; l < 16; ++l) dot += (int32_t)a[16 * j + l] * y[i].qs[16 * j + l];
+            sum += (int32_t)x[i].scales[j] * dot;
+        }
+        out[i] = sum;
+    }
+}
+
 /* ggml_vec_dot_{q4_0_q8_0,q8_0_q8_0,q4_K_q8_K} scalar semantics: per block sumi*d_x*d_y summed in
  * fp32 in block order (ggml-quants.c:4205, :7385-7392). F16: fp32 products, double accumulation
  * (tinyBLAS's ruler-function summation, tinyblas_cpu.h:534-584, keeps fp32 error logarithmic; a
@@ -238,6 +289,15 @@ float oracle_vec_dot(int xtype, int64_t n, const void *vx, const void *vy) {
         }
         return sumf + sumq;
     }
+    if (xtype == OR_Q6_K) {   /* per super-block d_x * d_y * integer sum, fp32 in block order (ggml-quants.c:8677-8681) */
+        const int64_t nb = n / QK_K; float sumf = 0;
+        const blk_q6_K *x = (const blk_q6_K *)vx; const blk_q8_K *y = (const blk_q8_K *)vy;
+        for (int64_t i = 0; i < nb; ++i) {
+            int32_t si; oracle_blockdot_q6_K_q8_K(x + i, y + i, 1, &si);
+            sumf += h2f(x[i].d) * y[i].d * si;
+        }
+        return sumf;
+    }
     return NAN;
 }
 
@@ -263,11 +323,12 @@ int oracle_sgemm(long m, long n, long k, const void *A, long lda, const void *B,
     if (Ctype != OR_F32) return 0;
     float *c = (float *)C;
     if (Btype == OR_Q8_K) {
-        if (Atype != OR_Q4_K) return 0;
+        if (Atype != OR_Q4_K && Atype != OR_Q6_K) return 0;   /* iqk_mul_mat.inc:1408-1463: the k-quants this build holds */
+        const long rowa = Atype == OR_Q4_K ? 144 : 210;
         /* iqk ignores lda/ldb: rows are ggml_row_size apart (iqk_mul_mat.inc:191-199) */
         _Pragma("omp parallel for collapse(2)")
         for (long j = 0; j < n; ++j) for (long i = 0; i < m; ++i)
-            c[ldc * j + i] = oracle_vec_dot(OR_Q4_K, k * QK_K, (const char *)A + i * k * 144, (const char *)B + j * k * 292);
+            c[ldc * j + i] = oracle_vec_dot(Atype, k * QK_K, (const char *)A + i * k * rowa, (const char *)B + j * k * 292);
         return 1;
     }
     if (Atype == OR_Q4_0 && Btype == OR_Q8_0) {
@@ -404,6 +465,7 @@ int oracle_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, const vo
     const int32_t *rm = (const int32_t *)row_mapping;
     int btype; size_t bs_a, bs_b; int blk;
     if (typeA == OR_Q4_K) { btype = OR_Q8_K; bs_a = 144; bs_b = 292; blk = 256; }
+    else if (typeA == OR_Q6_K) { btype = OR_Q8_K; bs_a = 210; bs_b = 292; blk = 256; }
     else if (typeA == OR_Q4_0) { btype = OR_Q8_0; bs_a = 18; bs_b = 34; blk = 32; }
     else return 0;   /* other iqk types (:1408-1463) are outside the build's scope */
     (void)btype;

@@ -31,7 +31,7 @@ def main():
     # --- llamafile_sgemm through ggml's mul_mat flow, every weight type, decode and small-batch shapes
     N, K = 48, 512
     for wt in H.WEIGHT_TYPES:
-        W = {H.Q4_0: r.quantize_q4_0, H.Q8_0: r.quantize_q8_0_ref, H.Q4_K: r.quantize_q4_K, H.F16: r.fp32_to_fp16}[wt](
+        W = {H.Q4_0: r.quantize_q4_0, H.Q8_0: r.quantize_q8_0_ref, H.Q4_K: r.quantize_q4_K, H.Q6_K: r.quantize_q6_K, H.F16: r.fp32_to_fp16}[wt](
             (np.random.default_rng(100 + wt).standard_normal((N, K)) * 0.02).astype(np.float32))
         g[f"w_{wt}"] = W
         for T in (1, 2, 3, 8, 9, 33):

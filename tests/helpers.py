@@ -5,9 +5,9 @@ import numpy as np
 
 from oracle import binding as B
 
-F32, F16, Q4_0, Q8_0, Q4_K, Q8_K, I32 = B.F32, B.F16, B.Q4_0, B.Q8_0, B.Q4_K, B.Q8_K, B.I32
-WEIGHT_TYPES = [Q4_0, Q8_0, Q4_K, F16]
-TYPE_NAME = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q8_K: "q8_K"}
+F32, F16, Q4_0, Q8_0, Q4_K, Q6_K, Q8_K, I32 = B.F32, B.F16, B.Q4_0, B.Q8_0, B.Q4_K, B.Q6_K, B.Q8_K, B.I32
+WEIGHT_TYPES = [Q4_0, Q8_0, Q4_K, Q6_K, F16]
+TYPE_NAME = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K", Q8_K: "q8_K"}
 
 # fp32 output gate (north_star): max|c-r| / max|r| <= 1e-3, plus the reference's own backend gate NMSE <= 5e-4
 # (llama.cpp/tests/test-backend-ops.cpp:966-968)
@@ -46,6 +46,16 @@ def synth_q4_K(rows: int, k: int, seed: int) -> np.ndarray:
     return blk.reshape(-1)
 
 
+def synth_q6_K(rows: int, k: int, seed: int) -> np.ndarray:
+    """Random but well-formed block_q6_K bytes: any ql/qh pattern and any int8 scale is a valid block; d kept small."""
+    rng = np.random.default_rng(seed)
+    nb = rows * k // 256
+    blk = rng.integers(0, 256, (nb, 210), dtype=np.uint8)
+    d = (rng.uniform(0.5, 2.0, nb) * 2e-5).astype(np.float16)
+    blk[:, 208:210] = d.view(np.uint8).reshape(nb, 2)
+    return blk.reshape(-1)
+
+
 def make_weights(wtype: int, rows: int, k: int, seed: int = 1, realistic_q4k: bool = True) -> np.ndarray:
     """fp32 N(0, 0.02^2) quantized with the reference's *_ref quantizers (oracle restatements). Q4_K uses the
     reference library when present (quantize_row_q4_K_ref is weight-prep, outside the hot path), else
@@ -57,6 +67,11 @@ def make_weights(wtype: int, rows: int, k: int, seed: int = 1, realistic_q4k: bo
         if r is None:
             return synth_q4_K(rows, k, seed)
         return r.quantize_q4_K((rng.standard_normal((rows, k)) * 0.02).astype(np.float32))
+    if wtype == Q6_K:
+        r = B.reference() if realistic_q4k else None
+        if r is None:
+            return synth_q6_K(rows, k, seed)
+        return r.quantize_q6_K((rng.standard_normal((rows, k)) * 0.02).astype(np.float32))
     w = (rng.standard_normal((rows, k)) * 0.02).astype(np.float32)
     if wtype == Q4_0:
         return o.quantize_q4_0(w)

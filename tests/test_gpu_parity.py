@@ -78,7 +78,7 @@ def test_host_pointer_quantizers(tb, oracle, golden):
 
 
 # ------------------------------------------------------------------ integer block dots: exact
-@pytest.mark.parametrize("wt", [H.Q4_0, H.Q8_0, H.Q4_K])
+@pytest.mark.parametrize("wt", [H.Q4_0, H.Q8_0, H.Q4_K, H.Q6_K])
 def test_block_dots_exact(tb, oracle, wt):
     rows, k = 37, 2048
     W = H.make_weights(wt, rows, k, seed=5, realistic_q4k=False)
@@ -121,7 +121,7 @@ def test_golden_tinyllama_shapes(tb, golden, wt, shape):
     H.assert_close(gpu_mul_mat(tb, golden[f"tl_w_{wt}_{n}_{k}"], wt, X[:1], n, k), golden[f"tl_mv_{wt}_{n}_{k}"])
 
 
-@pytest.mark.parametrize("wt,K", [(H.Q4_0, 14336), (H.Q8_0, 14336), (H.Q4_K, 28672), (H.F16, 14336)])
+@pytest.mark.parametrize("wt,K", [(H.Q4_0, 14336), (H.Q8_0, 14336), (H.Q4_K, 28672), (H.Q6_K, 28672), (H.F16, 14336)])
 def test_decode_long_k_chunked_staging(tb, oracle, wt, K):
     """T*K large enough that the activation staging walks K in chunks."""
     N, T = 96, 8
@@ -285,7 +285,7 @@ def test_mixmul_device_api_no_host_sync(tb, oracle):
     w.free()
 
 
-@pytest.mark.parametrize("typeA", [H.Q4_K, H.Q4_0])
+@pytest.mark.parametrize("typeA", [H.Q4_K, H.Q4_0, H.Q6_K])
 def test_llamafile_mixmul_iqk_host(tb, oracle, golden, typeA):
     if typeA == H.Q4_K:
         W, X, mapping = golden["iqk_w"], golden["iqk_x"], golden["iqk_map"]
@@ -396,7 +396,7 @@ def test_resident_activations_api(tb, oracle, wt, T):
     acts.free()
 
 
-@pytest.mark.parametrize("wt", [H.Q4_0, H.Q4_K])
+@pytest.mark.parametrize("wt", [H.Q4_0, H.Q4_K, H.Q6_K])
 @pytest.mark.parametrize("T", [1, 2, 8])
 def test_mul_mat_multi(tb, oracle, wt, T):
     """Several matrices sharing K and the activations in one launch (QKV / gate-up); uneven row counts."""

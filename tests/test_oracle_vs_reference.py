@@ -112,7 +112,7 @@ def test_mixmul_q4_K_not_serviced(oracle, reference):
                                B.Tensor.of(plan, H.I32, [1, 1]), B.Tensor.of(out, H.F32, [rows, 1, 1]))
 
 
-@pytest.mark.parametrize("typeA", [H.Q4_K, H.Q4_0])
+@pytest.mark.parametrize("typeA", [H.Q4_K, H.Q4_0, H.Q6_K])
 def test_mixmul_iqk(oracle, reference, typeA):
     Nx, ne00, ne11, ne12 = 24, 512, 2, 9
     W = H.make_weights(typeA, Nx, ne00, seed=3)
