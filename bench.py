@@ -35,12 +35,15 @@ import numpy as np
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
-Q4_0, Q8_0, Q4_K, F16, F32 = 2, 8, 12, 1, 0
-BPE = {Q4_0: 18 / 32, Q8_0: 34 / 32, Q4_K: 144 / 256, F16: 2.0}
+Q4_0, Q8_0, Q4_K, Q6_K, F16, F32 = 2, 8, 12, 14, 1, 0
+BPE = {Q4_0: 18 / 32, Q8_0: 34 / 32, Q4_K: 144 / 256, Q6_K: 210 / 256, F16: 2.0}
 
 WORKLOADS = {
     # name: (weight type, hidden, layers, per-layer [(name, N, K, input-group)], [(name, N, K)] tail)
     "llama3-8b-q4_0-decode": (Q4_0, 32, [("wq", 4096, 4096, "attn"), ("wk", 1024, 4096, "attn"), ("wv", 1024, 4096, "attn"),
+                                         ("wo", 4096, 4096, "o"), ("gate", 14336, 4096, "ffn"), ("up", 14336, 4096, "ffn"),
+                                         ("down", 4096, 14336, "down")], [("output", 128256, 4096, "out")]),
+    "llama3-8b-q6_K-decode": (Q6_K, 32, [("wq", 4096, 4096, "attn"), ("wk", 1024, 4096, "attn"), ("wv", 1024, 4096, "attn"),
                                          ("wo", 4096, 4096, "o"), ("gate", 14336, 4096, "ffn"), ("up", 14336, 4096, "ffn"),
                                          ("down", 4096, 14336, "down")], [("output", 128256, 4096, "out")]),
     "llama3-70b-q4_K-decode": (Q4_K, 80, [("wq", 8192, 8192, "attn"), ("wk", 1024, 8192, "attn"), ("wv", 1024, 8192, "attn"),
@@ -192,7 +195,7 @@ def run_b200_arm(args):
     wtype, layers, layer, tail = WORKLOADS[args.workload]
     if args.layers:
         layers = args.layers
-    ts, blck = {Q4_0: (18, 32), Q4_K: (144, 256)}[wtype]
+    ts, blck = {Q4_0: (18, 32), Q4_K: (144, 256), Q6_K: (210, 256)}[wtype]
 
     # ---- synthetic resident weights: random quant bytes, realistic fp16 scales; each rank builds its row shard
     def synth(N, K, seed):
@@ -203,6 +206,9 @@ def run_b200_arm(args):
         raw[:, 0:2] = d.to(torch.float16).view(torch.uint8).reshape(nb, 2)
         if wtype == Q4_K:
             raw[:, 2:4] = (d * 2).to(torch.float16).view(torch.uint8).reshape(nb, 2)
+        if wtype == Q6_K:   # block_q6_K keeps d in its last two bytes; the first two are quants
+            raw[:, 0:2] = torch.randint(0, 256, (nb, 2), dtype=torch.uint8, device=dev, generator=g)
+            raw[:, 208:210] = (d * 1e-2).to(torch.float16).view(torch.uint8).reshape(nb, 2)
         return raw.reshape(-1)
 
     mats = []   # (name, N_full, lo, hi, K, group, Weights, raw or None)
@@ -230,7 +236,7 @@ def run_b200_arm(args):
     # (tb200_mul_mat_acts_multi: wq/wk/wv, gate/up).
     schedule = []
     for i, m in enumerate(mats):
-        if schedule and schedule[-1][0] == m[5] and len(schedule[-1][1]) < 4 and wtype in (Q4_0, Q4_K):
+        if schedule and schedule[-1][0] == m[5] and len(schedule[-1][1]) < 4 and wtype in (Q4_0, Q4_K, Q6_K):
             schedule[-1][1].append(i)
         else:
             schedule.append((m[5], [i]))
@@ -348,7 +354,7 @@ def run_b200_arm(args):
             traffic, traffic_src = tj["traffic_over_algorithmic"] * step_bytes / n_gemv, tj["source"]
     except Exception:   # noqa: BLE001
         pass
-    roofline = {"bound": "hbm", "kernel": "gemv_q4_0_kernel" if wtype == Q4_0 else "gemv_q4_K_kernel", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": {Q4_0: "gemv_q4_0_kernel", Q4_K: "gemv_q4_K_kernel", Q6_K: "gemv_q6_K_kernel"}[wtype], "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": traffic, "traffic_source": traffic_src,
                 "launches_timed": n_gemv, "avg_launch_us": ms_gemv * 1e3 / n_gemv, "algorithmic_bytes_per_launch": step_bytes / n_gemv,
                 "frac_of_spec_8TBs": achieved / 8000.0}
@@ -375,7 +381,7 @@ def run_b200_arm(args):
             from oracle import binding as OB   # only used to pre-quantize the host activations once (checker-side prep)
         except Exception:
             OB = None
-        vdt, vts = (Q8_0, 34) if wtype == Q4_0 else (15, 292)
+        vdt, vts = (Q8_0, 34) if wtype == Q4_0 else (15, 292)   # Q8_K activations for the k-quants
         hB, hC = [], []
         for i, (name, N, lo, hi, K, grp, w) in enumerate(mats):
             x = groups[grp][0].cpu().numpy()
@@ -429,7 +435,8 @@ def run_b200_arm(args):
             cpu_baseline = {"value": None, "unit": "GB/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
 
     if rank == 0:
-        line = {"metric": "Q4_0 decode GEMV GB/s (Llama-3-8B shapes)" if wtype == Q4_0 else "Q4_K decode GEMV GB/s (Llama-3-70B shapes)",
+        line = {"metric": {Q4_0: "Q4_0 decode GEMV GB/s (Llama-3-8B shapes)", Q4_K: "Q4_K decode GEMV GB/s (Llama-3-70B shapes)",
+                           Q6_K: "Q6_K decode GEMV GB/s (Llama-3-8B shapes)"}[wtype],
                 "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int8 dp4a block dots, fp32 accumulate",
                 "data": "synthetic",

@@ -13,7 +13,7 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
 
-TYPES = {"q4_0": (2, 18, 32), "q8_0": (8, 34, 32), "q4_K": (12, 144, 256), "f16": (1, 2, 1)}
+TYPES = {"q4_0": (2, 18, 32), "q8_0": (8, 34, 32), "q4_K": (12, 144, 256), "q6_K": (14, 210, 256), "f16": (1, 2, 1)}
 SHAPES = [(4096, 4096), (14336, 4096), (4096, 14336)]
 
 
@@ -28,6 +28,9 @@ def synth(torch, dev, name, N, K, seed=0):
     raw[:, 0:2] = d.to(torch.float16).view(torch.uint8).reshape(nb, 2)
     if name == "q4_K":
         raw[:, 2:4] = (d * 2).to(torch.float16).view(torch.uint8).reshape(nb, 2)
+    if name == "q6_K":   # d sits in the last two bytes of block_q6_K
+        raw[:, 0:2] = torch.randint(0, 256, (nb, 2), dtype=torch.uint8, device=dev, generator=g)
+        raw[:, 208:210] = (d * 1e-2).to(torch.float16).view(torch.uint8).reshape(nb, 2)
     return raw.reshape(-1)
 
 
