@@ -32,9 +32,10 @@ static inline bool tb200_is_kquant(int type) { return type == TB200_TYPE_Q4_K ||
 //         sc  [rows][k/32] fp16 d
 //   Q8_0: qs  [rows][k] int8 ;  sc [rows][k/32] fp16 d
 //   Q4_K: qs  [rows][k/256] x 128 B ; sc [rows][k/256] x 16 B = {fp16 d, fp16 dmin, u8 scales[12]}
-//   Q6_K: qs  [rows][k/256] x 192 B = 4 units x {ql piece, ql piece +32, qh piece} (unit u = 2*half + l/16 covers elements
-//              128*half + 16*(l/16) + 32*j + [0,16), j = 0..3: one 64-wide K stage of the prefill path, one lane of the decode path)
-//         sc  [rows][k/256] x 16 B int8 scales ; d [rows][k/256] fp16
+//   Q6_K: qs  [rows][k/256] x 192 B = 4 units x 3 pieces of 16 B (unit u = 2*half + l/16 covers elements
+//              128*half + 16*(l/16) + 32*j + [0,16), j = 0..3: one 64-wide K stage of the prefill path, one lane of the decode
+//              path); piece j < 3, byte e = q_j[e] << 2 | two bits of q_3[e] (bits 5:4, 3:2, 1:0 for j = 0, 1, 2)
+//         sc  [rows][k/256] x 16 B int8 scales, byte 4u + j ; d [rows][k/256] fp16
 //   F16 : qs  [rows][k] fp16 ; sc = nullptr
 // ---------------------------------------------------------------------------------------------
 struct tb200_weights {

@@ -280,7 +280,7 @@ __device__ __forceinline__ void store_chunk_out(const GemmParams &p, const uint3
 template <int kType>
 struct RowDequant {
     const __half *scp;    // Q4_0 / Q8_0: fp16 d of this row; elements [2i], [2i+1] belong to the halves of stage i
-    const uint4 *hdp;     // Q4_K: {d, dmin, scales[12]} of this row, one per 256 elements = 4 stages; Q6_K: int8 scales[16]
+    const uint4 *hdp;     // Q4_K: {d, dmin, scales[12]} of this row, one per 256 elements = 4 stages; Q6_K: int8 scales, word i = stage i's four
     const __half *d6p;    // Q6_K: fp16 d of this row, one per 256 elements
     __half2 d_next;
     uint4 hdr_next;
@@ -294,7 +294,7 @@ struct RowDequant {
         hdr_next = make_uint4(0, 0, 0, 0);
         if (first_stage < kt) {
             if (kType == TB200_TYPE_Q4_K) hdr_next = __ldg(hdp + (first_stage >> 2));
-            else if (kType == TB200_TYPE_Q6_K) hdr_next = __ldg(hdp + (first_stage >> 2)), d_next = __half2half2(d6p[first_stage >> 2]);
+            else if (kType == TB200_TYPE_Q6_K) hdr_next.x = __ldg(reinterpret_cast<const uint32_t *>(hdp) + first_stage), d_next = __half2half2(d6p[first_stage >> 2]);
             else d_next = *reinterpret_cast<const __half2 *>(scp + 2 * first_stage);
         }
     }
@@ -305,7 +305,7 @@ struct RowDequant {
             if (i + 2 < kt) hdr_next = __ldg(hdp + ((i + 2) >> 2));
         } else if (kType == TB200_TYPE_Q6_K) {
             hdr = hdr_next, dpair = d_next;
-            if (i + 2 < kt) hdr_next = __ldg(hdp + ((i + 2) >> 2)), d_next = __half2half2(d6p[(i + 2) >> 2]);
+            if (i + 2 < kt) hdr_next.x = __ldg(reinterpret_cast<const uint32_t *>(hdp) + i + 2), d_next = __half2half2(d6p[(i + 2) >> 2]);
         } else {
             dpair = d_next;
             if (i + 2 < kt) d_next = *reinterpret_cast<const __half2 *>(scp + 2 * (i + 2));
@@ -338,26 +338,26 @@ struct RowDequant {
             a = dequant_q8_word(w1.z, d2), r[12] = a.x, r[13] = a.y;
             a = dequant_q8_word(w1.w, d2), r[14] = a.x, r[15] = a.y;
         } else if (kType == TB200_TYPE_Q6_K) {
-            // stage i is unit u = i & 3 of super-block i >> 2: 48 bytes {qlA, qlB, qh}; half `chalf` of the stage is j = 2*chalf,
-            // 2*chalf+1 (16 elements each, scale byte 8*(u>>1) + (u&1) + 2j): value = fp16(d*sc_j) * (q6 - 32), q6 - 32 exact in fp16
-            const int u = i & 3, hf = u >> 1, rr = u & 1;
+            // stage i is unit u = i & 3 of super-block i >> 2: 48 bytes = pieces j = 0,1,2 (byte = q_j << 2 | two bits of q_3,
+            // tb200_repack.cu); half `chalf` of the stage is j = 2*chalf, 2*chalf+1 (16 elements each, scale byte j of hdr.x):
+            // value = fp16(d*sc_j) * (q - 32). A byte 4q under the fp16 exponent of 256 reads as 256 + q, so no shift is needed.
             const uint8_t *rp = tile + row * 48;     // 48-byte row stride: the 8 lanes of a quarter-warp hit 8 distinct bank groups
-            const uint4 qa = *reinterpret_cast<const uint4 *>(rp), qb = *reinterpret_cast<const uint4 *>(rp + 16),
-                        qh = *reinterpret_cast<const uint4 *>(rp + 32);
-            const uint32_t sw = chalf ? (hf ? hdr.w : hdr.y) : (hf ? hdr.z : hdr.x);   // scales 8*hf + 4*chalf + [0,4)
-            const int sA = (int)(sw << (24 - 8 * rr)) >> 24, sB = (int)(sw << (8 - 8 * rr)) >> 24;   // bytes rr and rr + 2
+            const uint4 p0 = *reinterpret_cast<const uint4 *>(rp), p1 = *reinterpret_cast<const uint4 *>(rp + 16),
+                        p2 = *reinterpret_cast<const uint4 *>(rp + 32);
+            const uint32_t sw = chalf ? (hdr.x >> 16) : hdr.x;
+            const int sA = (int)(int8_t)sw, sB = (int)(int8_t)(sw >> 8);
             const float d = __low2float(dpair);
             const __half2 aA = __float2half2_rn(d * (float)sA), aB = __float2half2_rn(d * (float)sB);
-            const __half2 k1056 = __floats2half2_rn(1056.f, 1056.f);
-            const uint32_t a[4] = {qa.x, qa.y, qa.z, qa.w}, b[4] = {qb.x, qb.y, qb.z, qb.w}, h[4] = {qh.x, qh.y, qh.z, qh.w};
+            const __half2 k288 = __floats2half2_rn(288.f, 288.f);
+            const uint32_t a[4] = {p0.x, p0.y, p0.z, p0.w}, b[4] = {p1.x, p1.y, p1.z, p1.w}, h[4] = {p2.x, p2.y, p2.z, p2.w};
 #pragma unroll
             for (int w = 0; w < 4; ++w) {
-                const uint32_t xa = chalf ? (((a[w] >> 4) & 0x0f0f0f0fu) | (h[w] & 0x30303030u)) : ((a[w] & 0x0f0f0f0fu) | ((h[w] << 4) & 0x30303030u));
-                const uint32_t xb = chalf ? (((b[w] >> 4) & 0x0f0f0f0fu) | ((h[w] >> 2) & 0x30303030u)) : ((b[w] & 0x0f0f0f0fu) | ((h[w] << 2) & 0x30303030u));
-                r[2 * w] = h2_sub_mul(__byte_perm(xa, 0x64646464u, 0x4140), k1056, aA);       // bytes -> fp16 1024 + q, natural order
-                r[2 * w + 1] = h2_sub_mul(__byte_perm(xa, 0x64646464u, 0x4342), k1056, aA);
-                r[8 + 2 * w] = h2_sub_mul(__byte_perm(xb, 0x64646464u, 0x4140), k1056, aB);
-                r[8 + 2 * w + 1] = h2_sub_mul(__byte_perm(xb, 0x64646464u, 0x4342), k1056, aB);
+                const uint32_t xa = chalf ? (h[w] & 0xfcfcfcfcu) : (a[w] & 0xfcfcfcfcu);
+                const uint32_t xb = chalf ? ((((a[w] << 6) & 0xc0c0c0c0u) | ((b[w] << 4) & 0x30303030u)) | ((h[w] << 2) & 0x0c0c0c0cu)) : (b[w] & 0xfcfcfcfcu);
+                r[2 * w] = h2_sub_mul(__byte_perm(xa, 0x5c5c5c5cu, 0x4140), k288, aA);       // bytes -> fp16 256 + q, natural order
+                r[2 * w + 1] = h2_sub_mul(__byte_perm(xa, 0x5c5c5c5cu, 0x4342), k288, aA);
+                r[8 + 2 * w] = h2_sub_mul(__byte_perm(xb, 0x5c5c5c5cu, 0x4140), k288, aB);
+                r[8 + 2 * w + 1] = h2_sub_mul(__byte_perm(xb, 0x5c5c5c5cu, 0x4342), k288, aB);
             }
         } else {   // Q4_K: stage i is 64-element chunk c = i & 3 of super-block i >> 2
             const __half2 dd = *reinterpret_cast<const __half2 *>(&hdr.x);

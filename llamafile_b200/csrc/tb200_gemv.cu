@@ -606,20 +606,24 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const __grid_con
 }
 
 // ---- Q6_K ---------------------------------------------------------------------------------------
-// Resident layout (tb200_repack.cu): per super-block 4 units of 48 B = {qlA, qlB, qh}; unit u = 2*half + r covers the
-// 64 elements 128*half + 16*r + 32*j + [0,16), j = 0..3, with q = (nibble | 2 high bits << 4) - 32 and one int8 scale
-// per j: scales[8*half + r + 2j] (dequantize_row_q6_K, ggml-quants.c:2970-3000; dot: ggml_vec_dot_q6_K_q8_K scalar
-// branch :8642-8682, served by iqk DequantizerQ6K, llamafile/iqk_mul_mat.inc:570-600). A lane owns one unit (3 x 16-byte
-// loads, 48 contiguous bytes), 4 lanes share a super-block, a warp step covers 8 super-blocks = 1.5 KB of one row.
-// The 6-bit values are assembled four at a time with word-wide logic, re-centred with one per-byte subtract and
-// multiplied with dp4a; the integer sum of a super-block is exact, like the reference's.
+// Resident layout (tb200_repack.cu): per super-block 4 units of 48 B = three 16-byte pieces; unit u = 2*half + r covers
+// the 64 elements 128*half + 16*r + 32*j + [0,16), j = 0..3, one int8 scale per j: scales[8*half + r + 2j], stored as
+// byte 4u + j (dequantize_row_q6_K, ggml-quants.c:2970-3000; dot: ggml_vec_dot_q6_K_q8_K scalar branch :8642-8682,
+// served by iqk DequantizerQ6K, llamafile/iqk_mul_mat.inc:570-600). Piece j < 3 holds q_j << 2 with two bits of q_3 in
+// the low end of every byte, so (piece & 0xfc) ^ 0x80 is 4*(q_j - 32) as int8 with no nibble/high-bit merge: 9 logic
+// ops per 16 weights instead of 28 for the file's ql/qh split. A lane owns one unit (3 x 16-byte loads, 48 contiguous
+// bytes), 4 lanes share a super-block, a warp step covers 8 super-blocks = 1.5 KB of one row. dp4a sums are 4x the
+// reference's integers (exact; the 1/4 is folded into d).
 // Shared memory: activations [T][super-block][j][u] as 16-byte pieces, 20 pieces per super-block (4 of padding) so the
 // 8 lanes of a quarter-warp (2 super-blocks x 4 units) hit 8 distinct bank groups; then the Q8_K scale per sub-block.
 constexpr int kQ6KSmemPerSb = 20 * 16 + 64;
 
+// Occupancy over per-thread depth: with <= 64 registers four CTAs fit an SM, which measured 68 us on the 128256-row matrix
+// against 83 us for the two-CTA version that kept two super-blocks per row in flight (and 91 us for five CTAs at 48
+// registers, which spills).
 template <int T, int R>
-__global__ void __launch_bounds__(kWarps * 32) gemv_q6_K_kernel(const __grid_constant__ GemvQ4Args A) {
-    constexpr int U = (T * R <= 2) ? 2 : 1;   // super-blocks per 4-lane group per row in flight
+__global__ void __launch_bounds__(kWarps * 32, T * R <= 2 ? 4 : (T == 3 && R == 1 ? 3 : 2)) gemv_q6_K_kernel(const __grid_constant__ GemvQ4Args A) {
+    constexpr int U = T * R == 1 ? 2 : 1;   // super-blocks per 4-lane group per row in flight
     extern __shared__ __align__(16) uint8_t smem[];
     const long nsb = A.nb, nsbc = A.nbc;
     uint4 *s_q = reinterpret_cast<uint4 *>(smem);                       // [T][nsbc][20]
@@ -636,12 +640,12 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q6_K_kernel(const __grid_con
     const long r_base = ((long)((int)blockIdx.x - A.cta_begin[mat]) * kWarps + warp) * R;
     const bool active = r_base < nrows;
     const uint4 *qs = (const uint4 *)A.qs[mat];
-    const uint4 *sc = (const uint4 *)A.sc[mat];
+    const uint32_t *sc = (const uint32_t *)A.sc[mat];   // word u of a super-block = the 4 int8 scales of unit u
     const __half *dp = (const __half *)A.d6[mat];
     const int u = lane & 3, grp = lane >> 2;
-    const int half = u >> 1, rr = u & 1;       // scales of this unit: bytes 8*half + rr + 2j of the 16
 
-    uint4 wa[U][R], wb[U][R], wh[U][R], hdr[U][R];
+    uint4 wa[U][R], wb[U][R], wh[U][R];   // pieces j = 0, 1, 2: byte = q_j << 2 | two bits of q_3 (tb200_repack.cu)
+    uint32_t hdr[U][R];
     __half dw[U][R];
     long rowv[R];
     auto set_rows = [&](long my_row0) {
@@ -659,7 +663,7 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q6_K_kernel(const __grid_con
                     wa[uu][r] = ldg_stream(pw);
                     wb[uu][r] = ldg_stream(pw + 1);
                     wh[uu][r] = ldg_stream(pw + 2);
-                    hdr[uu][r] = __ldg(sc + rowv[r] * nsb + sb);
+                    hdr[uu][r] = __ldg(sc + (rowv[r] * nsb + sb) * 4 + u);
                     dw[uu][r] = dp[rowv[r] * nsb + sb];
                 }
             }
@@ -717,22 +721,19 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q6_K_kernel(const __grid_con
                 if (sb < (int)cnt) {
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
-                        const uint4 h = hdr[uu][r];
-                        const float d = __half2float(dw[uu][r]);
-                        // scales 8*half + rr + {0,2,4,6}: words 2*half and 2*half+1, bytes rr and rr+2 (sign-extended)
-                        const uint32_t s01 = half ? h.z : h.x, s23 = half ? h.w : h.y;
-                        const int sc0 = (int)(s01 << (24 - 8 * rr)) >> 24, sc1 = (int)(s01 << (8 - 8 * rr)) >> 24;
-                        const int sc2 = (int)(s23 << (24 - 8 * rr)) >> 24, sc3 = (int)(s23 << (8 - 8 * rr)) >> 24;
+                        const uint32_t h = hdr[uu][r];
+                        const float d = 0.25f * __half2float(dw[uu][r]);   // the int8 operands below are 4*(q - 32)
+                        const int sc0 = (int)(int8_t)h, sc1 = (int)(int8_t)(h >> 8), sc2 = (int)(int8_t)(h >> 16), sc3 = (int)h >> 24;
                         const uint32_t a[4] = {wa[uu][r].x, wa[uu][r].y, wa[uu][r].z, wa[uu][r].w};
                         const uint32_t b[4] = {wb[uu][r].x, wb[uu][r].y, wb[uu][r].z, wb[uu][r].w};
                         const uint32_t hh[4] = {wh[uu][r].x, wh[uu][r].y, wh[uu][r].z, wh[uu][r].w};
                         uint32_t q0[4], q1[4], q2[4], q3[4];
 #pragma unroll
-                        for (int w = 0; w < 4; ++w) {   // (nibble | 2 high bits << 4) - 32 per byte; no borrow crosses bytes (0..63 - 32)
-                            q0[w] = __vsub4((a[w] & 0x0f0f0f0fu) | ((hh[w] << 4) & 0x30303030u), 0x20202020u);
-                            q1[w] = __vsub4((b[w] & 0x0f0f0f0fu) | ((hh[w] << 2) & 0x30303030u), 0x20202020u);
-                            q2[w] = __vsub4(((a[w] >> 4) & 0x0f0f0f0fu) | (hh[w] & 0x30303030u), 0x20202020u);
-                            q3[w] = __vsub4(((b[w] >> 4) & 0x0f0f0f0fu) | ((hh[w] >> 2) & 0x30303030u), 0x20202020u);
+                        for (int w = 0; w < 4; ++w) {   // top 6 bits of a byte ^ 0x80 = int8 4*(q - 32); q_3 from the three 2-bit tails
+                            q0[w] = (a[w] & 0xfcfcfcfcu) ^ 0x80808080u;
+                            q1[w] = (b[w] & 0xfcfcfcfcu) ^ 0x80808080u;
+                            q2[w] = (hh[w] & 0xfcfcfcfcu) ^ 0x80808080u;
+                            q3[w] = ((((a[w] << 6) & 0xc0c0c0c0u) ^ 0x80808080u) | ((b[w] << 4) & 0x30303030u)) | ((hh[w] << 2) & 0x0c0c0c0cu);
                         }
 #pragma unroll
                         for (int t = 0; t < T; ++t) {
@@ -853,19 +854,19 @@ __global__ void blockdot_kernel(int type, const uint8_t *__restrict__ qs, const 
         if (i >= rows * nsb) return;
         const long sb = i % nsb;
         const uint8_t *q = qs + i * 192;
-        const int8_t *scl = reinterpret_cast<const int8_t *>(sc) + i * 16;
+        const int8_t *scl = reinterpret_cast<const int8_t *>(sc) + i * 16;   // byte 4u + j
         int sum = 0;
         for (int u = 0; u < 4; ++u) {
             const int half = u >> 1, r = u & 1;
-            const uint8_t *qa = q + u * 48, *qb = qa + 16, *qh = qa + 32;
+            const uint8_t *p0 = q + u * 48, *p1 = p0 + 16, *p2 = p0 + 32;
             for (int j = 0; j < 4; ++j) {
                 int dot = 0;
                 for (int l = 0; l < 16; ++l) {
-                    const int nib = j == 0 ? (qa[l] & 0xF) : j == 1 ? (qb[l] & 0xF) : j == 2 ? (qa[l] >> 4) : (qb[l] >> 4);
-                    const int q6 = (nib | (((qh[l] >> (2 * j)) & 3) << 4)) - 32;
-                    dot += q6 * aq[sb * 256 + 128 * half + 16 * r + 32 * j + l];
+                    const int q6 = j == 0 ? (p0[l] >> 2) : j == 1 ? (p1[l] >> 2) : j == 2 ? (p2[l] >> 2)
+                                                                                 : (((p0[l] & 3) << 4) | ((p1[l] & 3) << 2) | (p2[l] & 3));
+                    dot += (q6 - 32) * aq[sb * 256 + 128 * half + 16 * r + 32 * j + l];
                 }
-                sum += (int)scl[8 * half + r + 2 * j] * dot;
+                sum += (int)scl[4 * u + j] * dot;
             }
         }
         out[i] = sum;

@@ -57,9 +57,11 @@ __global__ void repack_q4_K_kernel(const uint8_t *__restrict__ raw, size_t row_s
 }
 
 // block_q6_K {ql[128], qh[64], scales[16], d} (ggml-common.h:299-307) -> 4 units of 48 B + scales + d. One thread per
-// 16-byte piece of the 192 quant bytes (12 pieces) plus one for the 16 scales and d. Unit u = 2*half + r holds
-// ql[64*half + 16*r ..], ql[64*half + 32 + 16*r ..], qh[32*half + 16*r ..] (the three pieces dequantize_row_q6_K,
-// ggml-quants.c:2970-3000, combines for l in [16r, 16r+16) of that half).
+// 16-byte piece of the 192 quant bytes (12 pieces) plus one for the 16 scales and d. Unit u = 2*half + r covers
+// l in [16r, 16r+16) of that half, i.e. the four 16-element groups j = 0..3 at elements 128*half + 32*j + 16*r
+// (the values dequantize_row_q6_K, ggml-quants.c:2970-3000, calls q1..q4). The 6-bit values are re-cut so that a
+// decode lane needs no nibble/high-bit merge: piece j (j = 0,1,2), byte e = q_j[e] << 2 | bits (5-2j, 4-2j) of q_3[e].
+// (piece & 0xfc) ^ 0x80 is then the int8 4*(q_j - 32), and the three 2-bit tails reassemble 4*q_3.
 __global__ void repack_q6_K_kernel(const uint8_t *__restrict__ raw, size_t row_stride, long rows, long nb,
                                    uint8_t *__restrict__ qs, uint8_t *__restrict__ sc, uint16_t *__restrict__ d) {
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
@@ -68,15 +70,21 @@ __global__ void repack_q6_K_kernel(const uint8_t *__restrict__ raw, size_t row_s
     const int piece = (int)(i % 13);
     const long row = blk / nb, b = blk % nb;
     const uint8_t *src = raw + row * row_stride + b * sizeof(tb200_block_q6_K);
-    if (piece == 12) {
-        for (int j = 0; j < 16; ++j) sc[blk * 16 + j] = src[192 + j];
+    if (piece == 12) {   // scales regrouped per unit: byte 4u + j = scales[8*half + r + 2j]
+        for (int u = 0; u < 4; ++u)
+            for (int j = 0; j < 4; ++j) sc[blk * 16 + 4 * u + j] = src[192 + 8 * (u >> 1) + (u & 1) + 2 * j];
         d[blk] = (uint16_t)src[208] | ((uint16_t)src[209] << 8);
         return;
     }
     const int u = piece / 3, part = piece % 3, half = u >> 1, r = u & 1;
-    const int off = part == 0 ? 64 * half + 16 * r : (part == 1 ? 64 * half + 32 + 16 * r : 128 + 32 * half + 16 * r);
+    const uint8_t *ql = src + 64 * half + 16 * r, *qh = src + 128 + 32 * half + 16 * r;
     uint8_t *dst = qs + blk * 192 + piece * 16;
-    for (int j = 0; j < 16; ++j) dst[j] = src[off + j];
+    for (int e = 0; e < 16; ++e) {
+        const int h = qh[e];
+        const int q3 = (ql[e + 32] >> 4) | (((h >> 6) & 3) << 4);
+        const int qj = part == 0 ? ((ql[e] & 0xF) | ((h & 3) << 4)) : part == 1 ? ((ql[e + 32] & 0xF) | (((h >> 2) & 3) << 4)) : ((ql[e] >> 4) | (((h >> 4) & 3) << 4));
+        dst[e] = (uint8_t)((qj << 2) | ((q3 >> (4 - 2 * part)) & 3));
+    }
 }
 
 }  // namespace
