@@ -98,6 +98,7 @@ __device__ __forceinline__ void store_rows(const GemvQ4Args &A, int mat, float (
     }
 }
 
+// (Unlike the K-quant kernels, this one loses with a shallower batch and four CTAs per SM: 3347 vs 3704 GB/s on the 8B step.)
 template <int T, int R>
 __global__ void __launch_bounds__(kWarps * 32) gemv_q4_0_kernel(const __grid_constant__ GemvQ4Args A) {
     constexpr int U = (T * R <= 4) ? 4 : 2;   // batch depth: blocks per lane per row in flight
@@ -475,8 +476,8 @@ constexpr int kQ4KSmemPerSb = 4 * 80 + 64;   // bytes of staged activations per 
 // Same launch structure as the Q4_0 kernel (multi-matrix grid, first weight batch before pdl_wait, fused all-gather
 // stores); A.nb / A.nbc count super-blocks here.
 template <int T, int R>
-__global__ void __launch_bounds__(kWarps * 32) gemv_q4_K_kernel(const __grid_constant__ GemvQ4Args A) {
-    constexpr int U = (T * R <= 2) ? 2 : 1;   // super-blocks per 4-lane group per row in flight
+__global__ void __launch_bounds__(kWarps * 32, T * R <= 2 ? 4 : ((R == 2 || T <= 4) ? 2 : 1)) gemv_q4_K_kernel(const __grid_constant__ GemvQ4Args A) {
+    constexpr int U = T * R == 1 ? 2 : 1;   // super-blocks per 4-lane group per row in flight
     extern __shared__ __align__(16) uint8_t smem[];
     const long nsb = A.nb, nsbc = A.nbc;
     uint4 *s_q = reinterpret_cast<uint4 *>(smem);                       // [T][nsbc][4 chunks][5]
