@@ -33,7 +33,8 @@ namespace {
 
 constexpr int BM = 128;        // weight rows per CTA tile = UMMA M
 constexpr int BK = 64;         // K elements per stage = one 128-byte swizzle atom of fp16
-constexpr int kDequantWarps = 8;
+constexpr int kDequantWarps = 16;
+constexpr int kGroups = kDequantWarps / 4;   // dequant groups of four warps (one per 32 TMEM lanes); group g takes the stages i = g (mod kGroups)
 // packed quant bytes of one weight row in one 64-wide K stage (0: F16 weights are not dequantised)
 __host__ __device__ constexpr int packed_row_bytes(int type) {
     return type == TB200_TYPE_Q8_0 ? 64 : (type == TB200_TYPE_Q6_K ? 48 : (type == TB200_TYPE_F16 ? 0 : 32));
@@ -282,34 +283,37 @@ struct RowDequant {
     const __half *scp;    // Q4_0 / Q8_0: fp16 d of this row; elements [2i], [2i+1] belong to the halves of stage i
     const uint4 *hdp;     // Q4_K: {d, dmin, scales[12]} of this row, one per 256 elements = 4 stages; Q6_K: int8 scales, word i = stage i's four
     const __half *d6p;    // Q6_K: fp16 d of this row, one per 256 elements
-    __half2 d_next;
-    uint4 hdr_next;
+    // scale ring: entry j holds the scales of the group's stage (current + 2j). kLook group steps = 2*kLook stages of lookahead;
+    // one step was enough while a stage's MMAs take >= 256 clocks (BN = 256) but left the L2/HBM latency of these scattered
+    // 4..16-byte loads exposed at small token tiles, where a stage is ~100 clocks of tensor work (measured ~740 clocks per
+    // stage at BN = 32 before this ring).
+    static constexpr int kLook = 4;
+    __half2 d_ring[kLook];
+    uint4 h_ring[kLook];
     int row;
 
+    __device__ __forceinline__ void fetch(int stage, __half2 &d, uint4 &h) const {
+        if (kType == TB200_TYPE_Q4_K) h = __ldg(hdp + (stage >> 2));
+        else if (kType == TB200_TYPE_Q6_K) h.x = __ldg(reinterpret_cast<const uint32_t *>(hdp) + stage), d = __half2half2(d6p[stage >> 2]);
+        else d = *reinterpret_cast<const __half2 *>(scp + 2 * stage);
+    }
     __device__ __forceinline__ RowDequant(const GemmParams &p, long grow, int row_, int first_stage, int kt) : row(row_) {
         scp = reinterpret_cast<const __half *>(p.sc) + grow * p.sc_row_stride;
         hdp = reinterpret_cast<const uint4 *>(p.sc) + grow * p.sc_row_stride;
         d6p = reinterpret_cast<const __half *>(p.d6) + grow * p.sc_row_stride;
-        d_next = __half2half2(__float2half(0.f));
-        hdr_next = make_uint4(0, 0, 0, 0);
-        if (first_stage < kt) {
-            if (kType == TB200_TYPE_Q4_K) hdr_next = __ldg(hdp + (first_stage >> 2));
-            else if (kType == TB200_TYPE_Q6_K) hdr_next.x = __ldg(reinterpret_cast<const uint32_t *>(hdp) + first_stage), d_next = __half2half2(d6p[first_stage >> 2]);
-            else d_next = *reinterpret_cast<const __half2 *>(scp + 2 * first_stage);
+#pragma unroll
+        for (int j = 0; j < kLook; ++j) {
+            d_ring[j] = __half2half2(__float2half(0.f));
+            h_ring[j] = make_uint4(0, 0, 0, 0);
+            if (first_stage + kGroups * j < kt) fetch(first_stage + kGroups * j, d_ring[j], h_ring[j]);
         }
     }
-    // call before waiting for stage i's packed tile: takes stage i's scales and puts the fetch for stage i+2 in flight
+    // call before waiting for stage i's packed tile: takes stage i's scales and puts the fetch for stage i + 2*kLook in flight
     __device__ __forceinline__ void advance(int i, int kt, __half2 &dpair, uint4 &hdr) {
-        if (kType == TB200_TYPE_Q4_K) {
-            hdr = hdr_next;
-            if (i + 2 < kt) hdr_next = __ldg(hdp + ((i + 2) >> 2));
-        } else if (kType == TB200_TYPE_Q6_K) {
-            hdr = hdr_next, dpair = d_next;
-            if (i + 2 < kt) hdr_next.x = __ldg(reinterpret_cast<const uint32_t *>(hdp) + i + 2), d_next = __half2half2(d6p[(i + 2) >> 2]);
-        } else {
-            dpair = d_next;
-            if (i + 2 < kt) d_next = *reinterpret_cast<const __half2 *>(scp + 2 * (i + 2));
-        }
+        dpair = d_ring[0], hdr = h_ring[0];
+#pragma unroll
+        for (int j = 0; j + 1 < kLook; ++j) d_ring[j] = d_ring[j + 1], h_ring[j] = h_ring[j + 1];
+        if (i + kGroups * kLook < kt) fetch(i + kGroups * kLook, d_ring[kLook - 1], h_ring[kLook - 1]);
     }
     // tile: this stage's packed quant tile in shared memory (TMA, 32B swizzle for 32-byte rows, 64B swizzle for 64-byte rows)
     __device__ __forceinline__ void regs(const uint8_t *tile, int i, int chalf, __half2 dpair, const uint4 &hdr, uint32_t (&r)[16]) const {
@@ -414,7 +418,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full_p[s], 1);
-            mbar_init(&full_a[s], kType == TB200_TYPE_F16 ? 1 : kDequantWarps / 2);   // one elected arrive per warp of the stage's dequant group (F16: the TMA's expect_tx)
+            mbar_init(&full_a[s], kType == TB200_TYPE_F16 ? 1 : 4);   // one elected arrive per warp of the stage's dequant group (F16: the TMA's expect_tx)
             mbar_init(&full_b[s], 1);
             mbar_init(&empty[s], 1);
         }
@@ -474,19 +478,26 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
         }
     } else if (warp >= 4) {
         // ===== dequantisers: packed tile (smem) -> fp16 -> tensor memory =====
-        const int quad = warp & 3, chalf = (warp - 4) >> 2;
+        const int quad = warp & 3, grp = (warp - 4) >> 2;
         const int row = quad * 32 + lane;             // TMEM lane == weight row of the tile
         const long grow = w_row0 + min(tile_row + row, p.nrows - 1);   // clamp rows past the matrix end (their outputs are masked)
         if (kTS) {
             const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCols;
-            RowDequant<kType> dq(p, grow, row, chalf, kt);
-            for (int i = chalf; i < kt; i += 2) {   // this warp group's stages
+            RowDequant<kType> dq(p, grow, row, grp, kt);
+            for (int i = grp; i < kt; i += kGroups) {   // this warp group's stages
                 const int s = i % kStages;
                 const uint32_t ph = (i / kStages) & 1;
                 __half2 dpair = __half2half2(__float2half(0.f));
                 uint4 hdr = make_uint4(0, 0, 0, 0);
                 uint32_t r0[16], r1[16];
                 dq.advance(i, kt, dpair, hdr);
+                // A parity wait is only unambiguous one phase ahead. When the ring depth is not a multiple of the group count a
+                // slot is served by a different group every turn, and this group could get here while the slot's previous
+                // load (stage i - kStages, another group's) is still in flight — bulk copies may land out of order — and take
+                // the phase before that one for its own. full_a[s] of the previous turn (that stage dequantised, hence landed)
+                // is at most one phase behind here, because this group's last stage was only loaded after the in-order MMAs
+                // had consumed everything up to i - kGroups - kStages. (Seen as a hang with 5 stages and 4 groups.)
+                if (kStages % kGroups != 0 && i >= kStages) mbar_wait(&full_a[s], ph ^ 1);
                 mbar_wait(&full_p[s], ph);
                 dq.regs(sP + s * kPackedBytes, i, 0, dpair, hdr, r0);
                 dq.regs(sP + s * kPackedBytes, i, 1, dpair, hdr, r1);
@@ -507,7 +518,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tcgen05_kernel(const __grid_
         tc_fence_after();
         const long out_row = tile_row + quad * 32 + lane;
         constexpr int kChunks = BN / 32 > 0 ? BN / 32 : 1;
-        for (int ch = chalf; ch < kChunks; ch += 2) {
+        for (int ch = grp; ch < kChunks; ch += kGroups) {
             uint32_t v[32];
             tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32), v);
             store_chunk_out(p, v, tile_tok, ch, tok_end, out_row);
@@ -531,6 +542,7 @@ template <int kType, int BN, int kStages>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
     constexpr bool kTS = kType != TB200_TYPE_F16;
+    static_assert(!kTS || kStages % kGroups == 0, "every ring slot must belong to one dequant group (parity waits are one phase deep; full_a is remote for the peer)");
     constexpr int BNH = BN / 2;                      // B' rows staged by each CTA
     constexpr int kPackedBytes = BM * packed_row_bytes(kType);
     constexpr int kABytes = kTS ? 0 : BM * BK * 2, kBBytes = BNH * BK * 2;
@@ -565,7 +577,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full_p[s], 1);
-            mbar_init(&full_a[s], kTS ? kDequantWarps : 1);   // the stage's dequant group (4 warps) in both CTAs (F16: the leader's expect_tx for both TMA halves)
+            mbar_init(&full_a[s], kTS ? 8 : 1);   // the stage's dequant group (4 warps) in both CTAs (F16: the leader's expect_tx for both TMA halves)
             mbar_init(&full_b[s], 1);
             mbar_init(&empty[s], 1);
         }
@@ -624,14 +636,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             umma_commit_pair(accum_full);
         }
     } else if (warp >= 4) {
-        const int quad = warp & 3, chalf = (warp - 4) >> 2;
+        const int quad = warp & 3, grp = (warp - 4) >> 2;
         const int row = quad * 32 + lane;
         const long grow = w_row0 + min(tile_row + row, p.nrows - 1);
         if (kTS) {
             // ===== dequantisers: packed tile (smem) -> fp16 -> this CTA's tensor memory; arrive at the leader =====
             const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + kAccCols;
-            RowDequant<kType> dq(p, grow, row, chalf, kt);
-            for (int i = chalf; i < kt; i += 2) {   // this warp group's stages
+            RowDequant<kType> dq(p, grow, row, grp, kt);
+            for (int i = grp; i < kt; i += kGroups) {   // this warp group's stages
                 const int s = i % kStages;
                 const uint32_t ph = (i / kStages) & 1;
                 __half2 dpair = __half2half2(__float2half(0.f));
@@ -660,7 +672,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         tc_fence_after();
         const long out_row = tile_row + quad * 32 + lane;
         constexpr int kChunks = BN / 32;
-        for (int ch = chalf; ch < kChunks; ch += 2) {
+        for (int ch = grp; ch < kChunks; ch += kGroups) {
             uint32_t v[32];
             tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(ch * 32), v);
             store_chunk_out(p, v, tile_tok, ch, tok_end, out_row);
@@ -712,15 +724,31 @@ __global__ void __launch_bounds__(256) prep_acts_kernel(const int8_t *__restrict
     if (bound > 0.f && bound < 3.0e38f) e = ilogbf(bound) - 14;
     const float inv = ldexpf(1.f, -e);
     if (threadIdx.x == 0) colscale[t] = ldexpf(1.f, e);
-    for (long i = threadIdx.x; i < k; i += blockDim.x) {
+    // four consecutive elements per thread: one 32-bit load, one 8-byte store — every K order keeps a 4-run together
+    // (perm 1/2: positions w*8 + 4*hi + {0,2,1,3}; perm 0/3: natural)
+    const uint32_t *q4 = reinterpret_cast<const uint32_t *>(q);
+    for (long i4 = threadIdx.x; i4 < k / 4; i4 += blockDim.x) {
+        const long i = i4 * 4;
         const float d = __int_as_float(ds[i >> 5].x);
-        const float v = __fmul_rn(__fmul_rn(d, (float)q[i]), inv);
+        const uint32_t qw = q4[i4];
+        const float v0 = __fmul_rn(__fmul_rn(d, (float)(int8_t)(qw & 0xff)), inv), v1 = __fmul_rn(__fmul_rn(d, (float)(int8_t)((qw >> 8) & 0xff)), inv);
+        const float v2 = __fmul_rn(__fmul_rn(d, (float)(int8_t)((qw >> 16) & 0xff)), inv), v3 = __fmul_rn(__fmul_rn(d, (float)(int8_t)(qw >> 24)), inv);
         long dst;
+        __half2 lo, hi;
         if (perm == 3) {   // Q6_K: element 128*half + 32*j + 16*r + e of a super-block -> stage u = 2*half + r, position 16*j + e
             const int e256 = (int)(i & 255), hf = e256 >> 7, j = (e256 >> 5) & 3, r = (e256 >> 4) & 1, e = e256 & 15;
             dst = (i & ~255L) + (hf * 2 + r) * 64 + j * 16 + e;
-        } else dst = (i & ~63L) + perm_pos(perm, (int)(i & 63));
-        bp[t * k + dst] = __float2half_rn(v);
+            lo = __floats2half2_rn(v0, v1), hi = __floats2half2_rn(v2, v3);
+        } else if (perm == 0) {
+            dst = i;
+            lo = __floats2half2_rn(v0, v1), hi = __floats2half2_rn(v2, v3);
+        } else {
+            dst = (i & ~63L) + perm_pos(perm, (int)(i & 63));   // position of the run's first element; the run is stored as (e0, e2, e1, e3)
+            lo = __floats2half2_rn(v0, v2), hi = __floats2half2_rn(v1, v3);
+        }
+        uint2 o;
+        o.x = *reinterpret_cast<const uint32_t *>(&lo), o.y = *reinterpret_cast<const uint32_t *>(&hi);
+        *reinterpret_cast<uint2 *>(bp + t * k + dst) = o;
     }
 }
 
@@ -840,6 +868,14 @@ int pair_mode() {
     return mode;
 }
 
+// deepest ring that fits: shared memory (227 KB minus alignment and barriers) and, for the TS form, tensor memory
+constexpr int deep_stages(int type, int bn) {
+    const int stage = (type == TB200_TYPE_F16 ? BM * BK * 2 : BM * packed_row_bytes(type)) + bn * BK * 2;
+    int s = (227 * 1024 - 2048) / (stage + 32);
+    if (type != TB200_TYPE_F16 && s > (512 - bn) / 32) s = (512 - bn) / 32;
+    return s > 16 ? 16 : s;
+}
+
 template <int kType>
 int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long tokens, void *bp, GemmParams &p, int force_bn = 0) {
     // token tile: as wide as the batch allows (fewer re-dequantisations of the same weight tile), but keep >= ~1 wave of CTAs
@@ -859,9 +895,11 @@ int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long toke
     }
     switch (bn) {
     case 256: return launch_cfg<kType, 256, f16 ? 4 : ((kType == TB200_TYPE_Q8_0 || kType == TB200_TYPE_Q6_K) ? 5 : 6)>(c, mw, mb, p);
-    case 128: return launch_cfg<kType, 128, f16 ? 5 : 8>(c, mw, mb, p);
-    case 64: return launch_cfg<kType, 64, f16 ? 6 : 8>(c, mw, mb, p);
-    default: return launch_cfg<kType, 32, f16 ? 6 : 8>(c, mw, mb, p);
+    // small token tiles are weight-streaming-bound: the ring is as deep as tensor memory (accumulator + 32 columns of A' per
+    // stage <= 512) and shared memory allow, since bytes in flight per SM are what sets the HBM rate there
+    case 128: return launch_cfg<kType, 128, deep_stages(kType, 128)>(c, mw, mb, p);
+    case 64: return launch_cfg<kType, 64, deep_stages(kType, 64)>(c, mw, mb, p);
+    default: return launch_cfg<kType, 32, deep_stages(kType, 32)>(c, mw, mb, p);
     }
 }
 

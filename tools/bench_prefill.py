@@ -115,6 +115,7 @@ def run(types, tokens, shapes=SHAPES, iters=20, warmup=3, cpu=False):
                         res[-1]["cpu_baseline"] = cpu_reference(name, N, K, T)
                     except Exception as e:   # noqa: BLE001
                         res[-1]["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
+                print("#", name, N, K, T, round(med * 1000, 1), "us", file=sys.stderr, flush=True)
             w.free()
     tb.set_stream(0)
     return res
