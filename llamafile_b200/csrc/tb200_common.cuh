@@ -117,6 +117,7 @@ struct tb200_gemv_args {
     long tokens;
     float *out; long ldo;
     const tb200_gemv_item *items; long n_items;   // optional grouped mode (device array); tokens = template T
+    const int *n_live;             // optional with items: device count of live items, which must lead the table (resident grouped kernel)
     // optional (Q4_0 / Q4_K): more matrices sharing K and the activations, served by the same launch
     int nmat; const tb200_weights *w_more[TB200_GEMV_MAX_MATS - 1]; float *out_more[TB200_GEMV_MAX_MATS - 1]; long ldo_more[TB200_GEMV_MAX_MATS - 1];
     // optional (Q4_0 / Q4_K): fused all-gather — `out` pointers lie inside this rank's symmetric buffer `local_base`, and

@@ -50,6 +50,7 @@ struct GemvQ4Args {
     long nb, nbc;
     const int8_t *aq; const int2 *ads; long a_stride;   // planar activations
     const tb200_gemv_item *items;
+    const int *n_live;                 // grouped resident kernel: number of live items (they lead the table)
 };
 
 // Epilogue shared by the quantized decode kernels: warp-reduce each (row, token) and store. With world > 1 the
@@ -358,6 +359,174 @@ __global__ void __launch_bounds__(kWarps * 32, 3) gemv_q4_0_resident_kernel(cons
             }
         }
         if (active || peers) store_rows<T, R>(A, mat, acc, orow, T, r_base, nrows, lane, active);
+    }
+}
+
+// ---- Q4_0, grouped resident form (mixmul decode, more routed pairs than experts) ---------------------------------
+// One item = all rows of one expert against up to T gathered tokens. The one-shot grouped launch gives every CTA 16
+// weight rows (36 KB at K = 4096) and makes it stage the item's T activation rows first (20 KB at T = 4), and its token
+// loop always runs T wide. Here the grid is the CTAs the GPU holds; each CTA serves one of the L live items (L written by
+// the item builder, read after pdl_wait), dealt out by cost, and walks that expert's row pairs with the stride of the CTAs
+// sharing the item, so the activations are staged once per CTA and amortised over ~25 row pairs.
+//
+// Token loops are bounded by the item's real token count (CTA-uniform), so a half-empty group costs half the dp4a work.
+// Activations are staged per K block as one record {T x low halves | T x high halves | T x {d, sum} | 16 B pad}: every
+// token's operands sit at a compile-time offset from ONE address per block, and the pad makes the record stride 4 (mod 8)
+// words, which keeps the 128-bit lane accesses conflict-free. The kernel is compiled for two CTAs per SM (128 registers)
+// so that the nibble masks of a block stay in registers across its tokens: with the 80 registers of three CTAs per SM and
+// planar staging, ptxas re-derived the masks and three staging addresses inside every guarded token block (ncu, batch 32:
+// 44 instructions per 32-element block and token - 19 % LOP3, 18 % LEA/IMAD - against 8 dp4a; issue-bound at 290 us).
+// Compiling the body once per token count inside a switch was tried: each body alone is spill-free, eight together spill 2 KB.
+template <int NT>
+__device__ __forceinline__ void grouped_item_q4_0(const GemvQ4Args &A, const tb200_gemv_item &it, int slot, int sharers, uint8_t *smem) {
+    constexpr int R = 2;
+    constexpr int U = 4;
+    constexpr int kRec = NT * 40 + 16;
+    const int ntok = it.ntok;                      // 1..NT, CTA-uniform
+    const int nb = (int)A.nb;                      // whole K is staged (the launcher guarantees it fits)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long row0 = it.row0, nrows = A.nrows[0];
+    const int nkb = (nb + 32 * U - 1) / (32 * U);  // K batches per row pair
+    const long units = (nrows + 1) / 2;
+    const long stride = (long)sharers * kWarps;
+    long unit = (long)slot * kWarps + warp;
+    const uint4 *qs = (const uint4 *)A.qs[0];
+    const __half *sc = (const __half *)A.sc[0];
+    const uint4 *wrow[R];
+    const __half *srow[R];
+    long r_base = 0;
+    auto locate = [&](long u) {
+        r_base = u * R;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const long row = row0 + min(r_base + r, nrows - 1);   // odd tail: the last row is recomputed, never stored
+            wrow[r] = qs + row * nb;
+            srow[r] = sc + row * nb;
+        }
+    };
+    uint4 w[U][R];
+    __half dh[U][R];
+    auto load_batch = [&](int kbi) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int b = kbi * 32 * U + lane + 32 * u;
+            if (b < nb) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) w[u][r] = ldg_stream(wrow[r] + b);
+#pragma unroll
+                for (int r = 0; r < R; ++r) dh[u][r] = srow[r][b];
+            }
+        }
+    };
+    if (unit < units) {
+        locate(unit);
+        load_batch(0);
+    }
+    for (int t = 0; t < ntok; ++t) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(A.aq + (long)it.a_row[t] * A.a_stride);
+        const int2 *dsrc = A.ads + (long)it.a_row[t] * (A.a_stride / QK);
+        for (int g = threadIdx.x; g < nb * 2; g += kWarps * 32)
+            *reinterpret_cast<uint4 *>(smem + (g >> 1) * kRec + (g & 1) * (NT * 16) + t * 16) = src[g];
+        for (int g = threadIdx.x; g < nb; g += kWarps * 32) *reinterpret_cast<int2 *>(smem + g * kRec + NT * 32 + t * 8) = dsrc[g];
+    }
+    __syncthreads();
+
+    float *out = A.out[0];
+    const long ldo = A.ldo[0];
+    for (bool first = true; unit < units; unit += stride, first = false) {
+        float acc[R][NT];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) acc[r][t] = 0.f;
+        if (!first) locate(unit);
+        for (int kb = 0; kb < nkb; ++kb) {
+            if (!first || kb) load_batch(kb);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int b = kb * 32 * U + lane + 32 * u;
+                if (b < nb) {
+                    const uint8_t *rec = smem + b * kRec;
+                    unsigned wl[R][4], wh[R][4];
+                    float d[R];
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        d[r] = __half2float(dh[u][r]);
+                        wl[r][0] = w[u][r].x & 0x0f0f0f0fu, wh[r][0] = w[u][r].x & 0xf0f0f0f0u;
+                        wl[r][1] = w[u][r].y & 0x0f0f0f0fu, wh[r][1] = w[u][r].y & 0xf0f0f0f0u;
+                        wl[r][2] = w[u][r].z & 0x0f0f0f0fu, wh[r][2] = w[u][r].z & 0xf0f0f0f0u;
+                        wl[r][3] = w[u][r].w & 0x0f0f0f0fu, wh[r][3] = w[u][r].w & 0xf0f0f0f0u;
+                    }
+#pragma unroll
+                    for (int t = 0; t < NT; ++t) {
+                        if (t >= ntok) break;
+                        const uint4 al = *reinterpret_cast<const uint4 *>(rec + t * 16);
+                        const uint4 ah = *reinterpret_cast<const uint4 *>(rec + NT * 16 + t * 16);
+                        const int2 ds = *reinterpret_cast<const int2 *>(rec + NT * 32 + t * 8);
+                        const float dy = __int_as_float(ds.x);
+                        const int bias = -8 * ds.y;
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            int sl = dp4a_us(wl[r][0], (int)al.x, bias);   // sum (q-8)*y = sum q*y - 8*sum y (exact in int32)
+                            sl = dp4a_us(wl[r][1], (int)al.y, sl);
+                            sl = dp4a_us(wl[r][2], (int)al.z, sl);
+                            sl = dp4a_us(wl[r][3], (int)al.w, sl);
+                            int sh = dp4a_us(wh[r][0], (int)ah.x, 0);
+                            sh = dp4a_us(wh[r][1], (int)ah.y, sh);
+                            sh = dp4a_us(wh[r][2], (int)ah.z, sh);
+                            sh = dp4a_us(wh[r][3], (int)ah.w, sh);
+                            acc[r][t] = fmaf(d[r] * dy, (float)(sl + (sh >> 4)), acc[r][t]);   // sh is an exact multiple of 16
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+            if (t >= ntok) break;
+            const long o = (long)it.out_row[t] * ldo + r_base;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float v = warp_sum(acc[r][t]);
+                if (lane == 0 && r_base + r < nrows) out[o + r] = v;
+            }
+        }
+    }
+}
+
+template <int T>
+__global__ void __launch_bounds__(kWarps * 32, 2) gemv_q4_0_grouped_kernel(const __grid_constant__ GemvQ4Args A) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    pdl_launch_dependents();
+    pdl_wait();                                    // item table and live count come from the predecessor
+    const int live = *A.n_live;
+    if (live <= 0) return;
+    // Which item this CTA serves. An item costs about (ntok + 1) units (one pass over the expert's weights + ntok dot products
+    // per block), and the kernel ends with its slowest item, so CTAs are dealt out in proportion to that cost: one per item,
+    // the rest by cumulative cost. With more items than half the grid every CTA walks the items c, c + grid, ... alone.
+    constexpr int kMaxLive = kWarps * 32;
+    __shared__ int s_cum[kMaxLive + 1], s_pick[3];
+    const bool dealt = 2 * live <= (int)gridDim.x && live <= kMaxLive;
+    if (dealt) {
+        if ((int)threadIdx.x < live) s_cum[threadIdx.x + 1] = A.items[threadIdx.x].ntok + 1;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            s_cum[0] = 0;
+            for (int i = 0; i < live; ++i) s_cum[i + 1] += s_cum[i];
+        }
+        __syncthreads();
+        const long spare = (long)gridDim.x - live, total = s_cum[live];
+        if ((int)threadIdx.x < live) {
+            const int lo = (int)threadIdx.x + (int)(s_cum[threadIdx.x] * spare / total), hi = (int)threadIdx.x + 1 + (int)(s_cum[threadIdx.x + 1] * spare / total);
+            if ((int)blockIdx.x >= lo && (int)blockIdx.x < hi) s_pick[0] = threadIdx.x, s_pick[1] = (int)blockIdx.x - lo, s_pick[2] = hi - lo;
+        }
+        __syncthreads();
+    }
+    for (int item = dealt ? s_pick[0] : (int)blockIdx.x; item < live; item += dealt ? live : (int)gridDim.x) {
+        const int slot = dealt ? s_pick[1] : 0, sharers = dealt ? s_pick[2] : 1;
+        const tb200_gemv_item &it = A.items[item];
+        grouped_item_q4_0<T>(A, it, slot, sharers, smem);
+        __syncthreads();   // the staged activations are replaced by the next item's
     }
 }
 
@@ -934,7 +1103,7 @@ int fill_args(GemvQ4Args &ka, const tb200_gemv_args &a, long nb, long nbc) {
         ka.out[m] = m == 0 ? a.out : a.out_more[m - 1], ka.ldo[m] = m == 0 ? a.ldo : a.ldo_more[m - 1];
     }
     ka.cta_begin[ka.nmat] = ctas;
-    ka.nb = nb, ka.nbc = nbc, ka.aq = a.aq, ka.ads = a.ads, ka.a_stride = a.a_stride, ka.items = a.items;
+    ka.nb = nb, ka.nbc = nbc, ka.aq = a.aq, ka.ads = a.ads, ka.a_stride = a.a_stride, ka.items = a.items, ka.n_live = a.n_live;
     ka.world = a.world > 1 ? a.world : 1;
     ka.local_base = (const char *)a.local_base;
     for (int p = 0; p < TB200_MAX_PEERS; ++p) ka.peer_base[p] = p < ka.world ? (char *)a.peer_base[p] : nullptr;
@@ -1035,12 +1204,32 @@ int launch_resident_q4_0(tb200_ctx *c, const tb200_gemv_args &a) {
     return TB200_OK;
 }
 
+// grouped Q4_0 launches whose item table leads with its live items (mixmul decode): resident grid, item chosen per CTA
+size_t grouped_q4_0_smem(int T, long k) { return (size_t)(k / QK) * (T * 40 + 16); }
+
+template <int T>
+int launch_grouped_q4_0(tb200_ctx *c, const tb200_gemv_args &a) {
+    const long nb = a.w->k / QK;
+    GemvQ4Args ka;
+    fill_args<2>(ka, a, nb, nb);
+    const size_t smem = grouped_q4_0_smem(T, a.w->k);
+    int rc;
+    if ((rc = set_smem(gemv_q4_0_grouped_kernel<T>, smem))) return rc;
+    const size_t per_cta = smem + 1040 + 1024;   // + the kernel's static shared memory + the per-CTA reservation
+    const int resident = per_cta * 2 <= 227 * 1024 ? 2 : 1;   // the kernel is compiled for two CTAs per SM (128 registers)
+    TB_CUDA(tb200_launch(gemv_q4_0_grouped_kernel<T>, dim3((unsigned)(resident * c->sm_count)), dim3(kWarps * 32), smem, c->stream, ka));
+    return TB200_OK;
+}
+
 template <int T>
 int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
     // rows per warp: 2 keeps >= 8 x 16-byte weight loads in flight per lane at K = 4096 while leaving
     // enough CTAs (N/8) to cover 148 SMs; small matrices fall back to 1 row per warp.
     long total = a.nrows * (a.items ? (a.n_items > 0 ? a.n_items : 1) : 1);   // grouped mode: every item walks nrows rows
     for (int m = 1; m < a.nmat; ++m) total += a.w_more[m - 1]->rows;
+    if constexpr (T == 4 || T == 8)
+        if (a.w->type == TB200_TYPE_Q4_0 && a.items && a.n_live && a.nmat <= 1 && a.world <= 1 && grouped_q4_0_smem(T, a.w->k) <= 110 * 1024)
+            return launch_grouped_q4_0<T>(c, a);
     if (total < (long)c->sm_count * kWarps * 4) return launch_TR<T, 1>(c, a);
     if (a.w->type == TB200_TYPE_Q4_0 && !a.items && T <= 2 && resident_enabled() && total / 2 > 4 * 3L * c->sm_count * kWarps &&   // >= 4 rounds of the resident grid
         (size_t)T * (a.w->k / QK) * 40 * 3 <= 200 * 1024)

@@ -69,13 +69,17 @@ struct HostLane {
     uint8_t *dact = nullptr; size_t dact_cap = 0;  // device: activations in the kernels' planar form
     uint8_t *dout = nullptr; size_t dout_cap = 0;  // device: large C before its D2H transfer
     uint32_t *flag = nullptr;                      // mapped pinned completion word
-    uint32_t *dcount = nullptr;                    // device: publish counter (graph replays advance it)
+    uint32_t *dcount = nullptr;                    // device: publish counter (graph replays advance it); dcount[1] = CTA arrivals of the copy-out
     uint32_t seq = 0;                              // host mirror of dcount
     cudaStream_t stream = nullptr;
     std::map<LaneKey, cudaGraphExec_t> graphs;     // exec == nullptr: seen once, not captured yet
 };
 HostLane g_lane[16];
-constexpr size_t kLaneDirectBytes = 32 * 1024;     // C up to this size is stored straight into host memory
+// C up to this size is stored straight into host memory by the decode kernel (scattered 4-byte PCIe stores, ~0.6 us per
+// 1000 rows); larger ones go through HBM and are written out by copy_publish_kernel in 512-byte warp stores. Beyond
+// kLaneKernelCopyBytes the copy engine takes over.
+size_t lane_direct_bytes() { static const size_t v = [] { const char *e = getenv("TB200_LANE_DIRECT_BYTES"); return e && *e ? (size_t)atol(e) : (size_t)4096; }(); return v; }
+constexpr size_t kLaneKernelCopyBytes = 4u << 20;
 
 __global__ void publish_kernel(uint32_t *flag, uint32_t *count) {
     pdl_launch_dependents();
@@ -84,6 +88,35 @@ __global__ void publish_kernel(uint32_t *flag, uint32_t *count) {
     *count = v;
     __threadfence_system();
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(v) : "memory");
+}
+// Large C: HBM -> mapped pinned host memory with coalesced stores, then the completion word, in ONE kernel (a
+// cudaMemcpyAsync node between the decode kernel and publish_kernel cost ~15 us of copy-engine latency per call: N=14336
+// took 37 us against 18 us for N=4096). Small results use one CTA (its thread 0 publishes with a release store after the CTA barrier); larger ones
+// use several, thread 0 of each fences the CTA's stores system-wide and counts the CTA in, and the last to arrive publishes.
+__global__ void __launch_bounds__(1024) copy_publish_kernel(const float *__restrict__ src, float *__restrict__ dst, long n, uint32_t *flag, uint32_t *count) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const long tid = blockIdx.x * (long)blockDim.x + threadIdx.x, nthr = (long)gridDim.x * blockDim.x;
+    if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+        const long n4 = n >> 2;
+        const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+        uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+        for (long i = tid; i < n4; i += nthr) d4[i] = s4[i];
+        for (long i = (n4 << 2) + tid; i < n; i += nthr) dst[i] = src[i];
+    } else {
+        for (long i = tid; i < n; i += nthr) dst[i] = src[i];
+    }
+    __syncthreads();                 // the CTA's stores are ordered before thread 0's release (cumulative), so ONE system-scope
+    if (threadIdx.x == 0) {          // fence per CTA is enough: a fence in every thread cost ~9 us per call
+        if (gridDim.x > 1) {
+            __threadfence_system();
+            if (atomicAdd(count + 1, 1u) != gridDim.x - 1) return;
+            count[1] = 0;
+        }
+        const uint32_t v = *count + 1;
+        *count = v;
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(v) : "memory");
+    }
 }
 // fp16 / f32 activations of the F16 path: every CTA re-reads them, so they must come from HBM, not over PCIe
 __global__ void stage_copy_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst, long n16, const uint8_t *src_tail, uint8_t *dst_tail, int tail) {
@@ -184,8 +217,19 @@ int lane_issue(tb200_ctx *c, HostLane &L, const LaneKey &k, size_t b_bytes) {
         rc = tb200_run_matmul(c, w, 0, w->rows, q, ds, nullptr, 0, w->k, k.n, (float *)k.dC, k.ldo);
     }
     if (rc) return rc;
-    if (k.h_dst)   // large C: HBM -> pinned host through the copy engine (h_dst rows are k.ldo_host apart; here dense)
-        TB_CUDA(cudaMemcpyAsync(k.h_dst, k.dC, (size_t)k.n * w->rows * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (k.h_dst) {   // large C: HBM -> pinned host (dense rows)
+        const size_t c_bytes = (size_t)k.n * w->rows * 4;
+        void *h_dev = c_bytes <= kLaneKernelCopyBytes ? pinned_alias(k.h_dst) : nullptr;
+        if (h_dev) {
+            const long n = (long)(c_bytes / 4);
+            // up to 128 KB: ONE CTA, so one fence and no arrival counting (two dependent system fences cost ~4 us)
+            long ctas = c_bytes <= 128 * 1024 ? 1 : (n / 4 + 1023) / 1024;
+            ctas = ctas > c->sm_count ? c->sm_count : ctas;
+            TB_CUDA(tb200_launch(copy_publish_kernel, dim3((unsigned)ctas), dim3(1024), 0, c->stream, (const float *)k.dC, (float *)h_dev, n, L.flag, L.dcount));
+            return TB200_OK;
+        }
+        TB_CUDA(cudaMemcpyAsync(k.h_dst, k.dC, c_bytes, cudaMemcpyDeviceToHost, c->stream));
+    }
     TB_CUDA(tb200_launch(publish_kernel, dim3(1), dim3(1), 0, c->stream, L.flag, L.dcount));
     return TB200_OK;
 }
@@ -247,7 +291,7 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
             key.dB = L.in;
         }
         void *pinC = pinned_alias(C);
-        if (c_bytes <= kLaneDirectBytes) {   // kernels store C over PCIe
+        if (c_bytes <= lane_direct_bytes()) {   // kernels store C over PCIe
             key.dC = pinC;
             if (!key.dC) {
                 if (!lane_reserve_host(L, &L.out, &L.out_cap, c_bytes)) return false;

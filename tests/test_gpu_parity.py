@@ -285,6 +285,25 @@ def test_mixmul_device_api_no_host_sync(tb, oracle):
     w.free()
 
 
+@pytest.mark.parametrize("tokens,skew", [(5, False), (12, False), (24, True), (60, False)])
+def test_mixmul_grouped_resident_odd_rows(tb, oracle, tokens, skew):
+    """Q4_0 decode-size routing through the grouped resident kernel (items of up to 8 tokens, CTAs spread over the live items):
+    odd row count per expert (row-pair tail), experts with more than 8 tokens (several items), experts with none."""
+    rows, cols, experts, thinkers = 97, 2048, 8, 2
+    W = H.make_weights(H.Q4_0, experts * rows, cols, seed=tokens + 1)
+    w = tb.Weights(W, H.Q4_0, experts * rows, cols)
+    X = np.random.default_rng(tokens).standard_normal((tokens, 1, cols)).astype(np.float32)
+    plan = H.make_plan(tokens, experts, thinkers, skew=skew, seed=tokens)
+    out = torch.full((tokens, thinkers, rows), float("nan"), device="cuda")
+    assert tb.mixmul(w, experts, dev(X), 1, dev(plan), thinkers, tokens, out)
+    tb.synchronize()
+    ref = np.full((tokens, thinkers, rows), np.nan, np.float32)
+    assert oracle.mixmul(B.Tensor.of(W, H.Q4_0, [cols, rows, experts]), B.Tensor.of(X, H.F32, [cols, 1, tokens]),
+                         B.Tensor.of(plan, H.I32, [thinkers, tokens]), B.Tensor.of(ref, H.F32, [rows, thinkers, tokens]))
+    H.assert_close(out.cpu().numpy(), ref, f"tokens={tokens}")
+    w.free()
+
+
 @pytest.mark.parametrize("typeA", [H.Q4_K, H.Q4_0, H.Q6_K])
 def test_llamafile_mixmul_iqk_host(tb, oracle, golden, typeA):
     if typeA == H.Q4_K:

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--type", default="q4_0")
     ap.add_argument("--batches", default="1,8,64,512")
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--graph", type=int, default=4, help="also time a CUDA graph of this many calls over as many distinct expert stacks (0 = off)")
     a = ap.parse_args()
     import torch
     from llamafile_b200.build import build
@@ -41,6 +42,9 @@ def main():
     for name in a.type.split(","):
         for (mat, rows, cols) in SHAPES:
             w = tb.Weights(synth(torch, dev, name, rows * EXPERTS, cols), TYPES[name][0], rows * EXPERTS, cols)
+            # graph mode: a decode step calls mul_mat_id once per layer, each on its own expert stack, from one captured graph; the
+            # distinct stacks (a.graph x 2-8 touched experts x 33 MB) exceed L2, and launch overhead of the eager loop is gone
+            more = [tb.Weights(synth(torch, dev, name, rows * EXPERTS, cols), TYPES[name][0], rows * EXPERTS, cols) for _ in range(max(0, a.graph - 1))]
             for tokens in [int(b) for b in a.batches.split(",")]:
                 x = torch.randn(tokens, 1, cols, device=dev, generator=g)
                 # top-2 routing: two distinct experts per token, uniformly random
@@ -59,13 +63,43 @@ def main():
                     stream.synchronize()
                 ms = sorted(e0.elapsed_time(e1) for e0, e1 in ev)
                 med = ms[len(ms) // 2]
+                graph_ms = None
+                if a.graph:
+                    stacks = [w] + more
+                    plans = [torch.stack([torch.randperm(EXPERTS, device=dev, generator=g)[:TOP] for _ in range(tokens)]).to(torch.int32).contiguous()
+                             for _ in stacks]
+                    touched_g = sum(int(torch.unique(p).numel()) for p in plans)
+                    with torch.cuda.stream(stream):
+                        for ws, pl in zip(stacks, plans):
+                            tb.mixmul(ws, EXPERTS, x, 1, pl, TOP, tokens, out)
+                        stream.synchronize()
+                        gr = torch.cuda.CUDAGraph()
+                        with torch.cuda.graph(gr, stream=stream):
+                            for ws, pl in zip(stacks, plans):
+                                tb.mixmul(ws, EXPERTS, x, 1, pl, TOP, tokens, out)
+                        for _ in range(3):
+                            gr.replay()
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        e0.record(stream)
+                        for _ in range(a.iters):
+                            gr.replay()
+                        e1.record(stream)
+                        stream.synchronize()
+                    graph_ms = e0.elapsed_time(e1) / a.iters / len(stacks)
+                    gbytes = (touched_g * rows * cols * BPE[name]) / len(stacks) + tokens * cols * 4 + tokens * TOP * rows * 4
+                    del gr
                 byts = touched * rows * cols * BPE[name] + tokens * cols * 4 + tokens * TOP * rows * 4
                 fl = 2.0 * tokens * TOP * rows * cols
                 print(json.dumps({"op": "mul_mat_id", "type": name, "matrix": mat, "rows": rows, "cols": cols, "experts": EXPERTS, "top": TOP,
                                   "tokens": tokens, "experts_touched": touched, "ms_median": med, "ms_min": ms[0],
                                   "GBps": byts / (med * 1e-3) / 1e9, "TFLOPS": fl / (med * 1e-3) / 1e12,
+                                  "graph_calls": a.graph, "graph_ms_per_call": graph_ms,
+                                  "graph_GBps": gbytes / (graph_ms * 1e-3) / 1e9 if graph_ms else None,
+                                  "graph_TFLOPS": fl / (graph_ms * 1e-3) / 1e12 if graph_ms else None,
                                   "includes": "activation quantize + device-side grouping + grouped kernel", "l2": "256 MiB flush between iterations"}), flush=True)
             w.free()
+            for m in more:
+                m.free()
 
 
 if __name__ == "__main__":
