@@ -530,6 +530,186 @@ __global__ void __launch_bounds__(kWarps * 32, 2) gemv_q4_0_grouped_kernel(const
     }
 }
 
+// ---- Q4_0, skinny GEMM on the integer tensor-core path (2..8 tokens) ---------------------------------------------
+// With T tokens the dp4a kernels spend 8 dp4a + ~12 other instructions per 32-element block, row and token: at T = 8
+// the vocabulary matrix took 209 us (1.4 TB/s) against 46 us at T = 1 - the kernel is issue-bound, not HBM-bound. One
+// warp-level mma.sync.m16n8k32 (u8 x s8 -> s32) does a whole Q4_0 block of 16 rows against 8 tokens exactly as the block dot
+// product defines it: K = 32 is ONE block, so the int32 result is the block's sum_j q[j]*y[j] (ggml-quants.c:4192-4206) and
+// is scaled per block in fp32 like the reference. The -8 of (q - 8) enters as the accumulator's initial value -8*sum(y),
+// so the int32 the scale multiplies is exact.
+//   A fragment: lane (g = lane/4, c = lane%4) needs word c of the packed block of rows g and g+8: its low nibbles are
+//   elements 4c..4c+3 (a0/a1), its high nibbles elements 16+4c..16+4c+3 (a2/a3) - exactly the K slices the fragment wants,
+//   so unpacking is two ANDs and a shift. The weights go from HBM to registers with no staging: lane (g, c) loads the whole
+//   16-byte block b0+c of its rows (a warp load touches 8 rows x 64 contiguous bytes) and the four lanes of a group exchange
+//   words with three shuffles (4x4 transpose). (First version: 4-byte loads of word c straight from HBM - every warp load
+//   touched 8 cache lines for 128 bytes and the L1 tag stage capped the kernel at 2.1 TB/s.)
+//   B fragment: the activations of token g, same K slices, staged once per CTA as [block][token][c]{b0, b1} (one
+//   conflict-free 8-byte read per mma); {d_y, -8*sum y} per block and token sit beside them.
+// A CTA owns one 16-row tile at a time and its 8 warps split K, so even a 4096-row matrix fills the GPU (256 tiles); the
+// eight partial 16x8 tiles meet in shared memory. The grid is resident (CTAs walk the tiles with a stride) and every lane
+// keeps the next batch of blocks in flight while it consumes one.
+__device__ __forceinline__ void mma_u8s8_16832(int (&d)[4], unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned b0, unsigned b1, int c0, int c1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%10,%11};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(c0), "r"(c1));
+}
+// lane c of a 4-lane group holds x = the four words of block c; on return x[j] = word c of block j
+__device__ __forceinline__ void quad_transpose(uint4 &x, int c, int lane) {
+    unsigned z0 = x.x, z1 = x.y, z2 = x.z, z3 = x.w, t;
+    if (c & 1) t = z0, z0 = z1, z1 = z2, z2 = z3, z3 = t;             // z[i] = x[(i + c) & 3]
+    if (c & 2) t = z0, z0 = z2, z2 = t, t = z1, z1 = z3, z3 = t;
+    const int base = lane & ~3;
+    const unsigned w1 = __shfl_sync(0xffffffffu, z1, base | ((c - 1) & 3));   // round r: word c of block (c - r) & 3
+    const unsigned w2 = __shfl_sync(0xffffffffu, z2, base | ((c - 2) & 3));
+    const unsigned w3 = __shfl_sync(0xffffffffu, z3, base | ((c - 3) & 3));
+    unsigned v0 = z0, v1 = w3, v2 = w2, v3 = w1;                        // v[i] = word c of block (c + i) & 3
+    if (c & 1) t = v3, v3 = v2, v2 = v1, v1 = v0, v0 = t;             // y[j] = v[(j - c) & 3]
+    if (c & 2) t = v0, v0 = v2, v2 = t, t = v1, v1 = v3, v3 = t;
+    x = make_uint4(v0, v1, v2, v3);
+}
+
+template <int T, int KS>   // KS = warps sharing a tile's K (8: small matrices, every tile's partials meet in shared memory; 1: a warp owns its tile)
+__global__ void __launch_bounds__(kWarps * 32, 3) gemm_q4_0_mma_kernel(const __grid_constant__ GemvQ4Args A) {
+    constexpr int Q = 2;                           // quads (4 blocks) per lane and row in flight per batch
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int nb = (int)A.nb;                      // nb % 32 == 0 (launcher): every warp's K slice is whole quads
+    uint2 *s_b = reinterpret_cast<uint2 *>(smem);                        // [nb][T][4] {b0, b1}
+    int4 *s_ds = reinterpret_cast<int4 *>(smem + (size_t)nb * T * 32);   // [nb][4] {d_y(2c), bias(2c), d_y(2c+1), bias(2c+1)}
+    __shared__ float4 s_red[KS > 1 ? 2 : 1][KS > 1 ? kWarps : 1][32];
+
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, c = lane & 3;
+    const long nrows = A.nrows[0];
+    const long tiles = (nrows + 15) / 16;
+    const int slice = nb / KS;                     // blocks of K per warp
+    const int b_lo = KS > 1 ? warp * slice : 0;
+    const int nbat = (slice + 4 * Q - 1) / (4 * Q);
+    const long tile0 = KS > 1 ? (long)blockIdx.x : (long)blockIdx.x * kWarps + warp, tstride = KS > 1 ? (long)gridDim.x : (long)gridDim.x * kWarps;
+    const long my_tiles = tile0 < tiles ? (tiles - tile0 + tstride - 1) / tstride : 0;
+    const long steps = my_tiles * nbat;
+    const uint4 *qs = (const uint4 *)A.qs[0];
+    const __half *sc = (const __half *)A.sc[0];
+
+    // prefetch side: step -> (tile, K batch); lane (g, c) loads block (quad base + c) of rows g and g+8. The four row
+    // pointers are rebuilt once per tile and advanced by a constant per batch.
+    long pf_tile = tile0;
+    int pf_bat = 0;
+    const uint4 *pq0 = nullptr, *pq1 = nullptr;
+    const uint2 *ps0 = nullptr, *ps1 = nullptr;
+    auto load_step = [&](uint4 (&w)[Q][2], uint2 (&dq)[Q][2]) {
+        if (pf_bat == 0) {
+            const long r0 = A.row0[0] + min(pf_tile * 16 + g, nrows - 1), r1 = A.row0[0] + min(pf_tile * 16 + g + 8, nrows - 1);
+            pq0 = qs + r0 * nb + b_lo + c, pq1 = qs + r1 * nb + b_lo + c;
+            ps0 = reinterpret_cast<const uint2 *>(sc + r0 * nb + b_lo), ps1 = reinterpret_cast<const uint2 *>(sc + r1 * nb + b_lo);
+        }
+#pragma unroll
+        for (int q = 0; q < Q; ++q)
+            if (pf_bat * 4 * Q + q * 4 < slice) {   // slice-relative, warp-uniform
+                w[q][0] = ldg_stream(pq0 + q * 4), w[q][1] = ldg_stream(pq1 + q * 4);
+                dq[q][0] = __ldg(ps0 + q), dq[q][1] = __ldg(ps1 + q);
+            }
+        pq0 += 4 * Q, pq1 += 4 * Q, ps0 += Q, ps1 += Q;
+        if (++pf_bat == nbat) pf_bat = 0, pf_tile += tstride;
+    };
+    uint4 wA[Q][2], wB[Q][2];
+    uint2 dA[Q][2], dB[Q][2];
+    if (steps > 0) load_step(wA, dA);              // immutable weights: in flight before the activations exist
+
+    pdl_wait();
+    // stage the activations in fragment order: source word w of (token, block) -> [block][token][w & 3] slot (w >> 2)
+    {
+        unsigned *sb = reinterpret_cast<unsigned *>(s_b);
+        const int words = nb * 8;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const unsigned *src = reinterpret_cast<const unsigned *>(A.aq + (long)t * A.a_stride);
+            for (int i = threadIdx.x; i < words; i += kWarps * 32) {
+                const int b = i >> 3, w = i & 7;
+                sb[((b * T + t) * 4 + (w & 3)) * 2 + (w >> 2)] = src[i];
+            }
+        }
+        int *sd = reinterpret_cast<int *>(s_ds);
+        for (int i = threadIdx.x; i < nb * 8; i += kWarps * 32) {
+            const int b = i >> 3, t = i & 7;
+            int2 v = make_int2(0, 0);
+            if (t < T) v = A.ads[(long)t * (A.a_stride / QK) + b];
+            sd[(b * 8 + t) * 2] = v.x, sd[(b * 8 + t) * 2 + 1] = -8 * v.y;
+        }
+    }
+    __syncthreads();
+
+    const int tb = g < T ? g : T - 1;              // B columns beyond T repeat the last token; their results are never stored
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    long cu_tile = tile0;
+    int cu_bat = 0, parity = 0;
+    float *out = A.out[0];
+    const long ldo = A.ldo[0];
+    auto compute_step = [&](uint4 (&w)[Q][2], const uint2 (&dq)[Q][2]) {
+#pragma unroll
+        for (int q = 0; q < Q; ++q) {
+            const int bq = cu_bat * 4 * Q + q * 4;
+            if (bq < slice) {                      // warp-uniform
+                quad_transpose(w[q][0], c, lane);
+                quad_transpose(w[q][1], c, lane);
+                const unsigned w0[4] = {w[q][0].x, w[q][0].y, w[q][0].z, w[q][0].w}, w1[4] = {w[q][1].x, w[q][1].y, w[q][1].z, w[q][1].w};
+                const unsigned h0[2] = {dq[q][0].x, dq[q][0].y}, h1[2] = {dq[q][1].x, dq[q][1].y};
+                const uint2 *pb = s_b + ((b_lo + bq) * T + tb) * 4 + c;   // one address per quad, compile-time offsets per block
+                const int4 *pd = s_ds + (b_lo + bq) * 4 + c;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint2 bf = pb[j * T * 4];
+                    const int4 ds = pd[j * 4];
+                    int d[4];
+                    mma_u8s8_16832(d, w0[j] & 0x0f0f0f0fu, w1[j] & 0x0f0f0f0fu, (w0[j] >> 4) & 0x0f0f0f0fu, (w1[j] >> 4) & 0x0f0f0f0fu, bf.x, bf.y, ds.y, ds.w);
+                    const float dw0 = __half2float(__ushort_as_half((unsigned short)((j & 1) ? (h0[j >> 1] >> 16) : (h0[j >> 1] & 0xffffu))));
+                    const float dw1 = __half2float(__ushort_as_half((unsigned short)((j & 1) ? (h1[j >> 1] >> 16) : (h1[j >> 1] & 0xffffu))));
+                    const float y0 = __int_as_float(ds.x), y1 = __int_as_float(ds.z);
+                    acc[0] = fmaf(dw0 * y0, (float)d[0], acc[0]);
+                    acc[1] = fmaf(dw0 * y1, (float)d[1], acc[1]);
+                    acc[2] = fmaf(dw1 * y0, (float)d[2], acc[2]);
+                    acc[3] = fmaf(dw1 * y1, (float)d[3], acc[3]);
+                }
+            }
+        }
+        if (++cu_bat == nbat) {
+            if constexpr (KS > 1) {   // this warp's K slice of the tile is done: the eight partial tiles meet in shared memory
+                s_red[parity][warp][lane] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                __syncthreads();
+                if (threadIdx.x < 128) {
+                    const float *p = reinterpret_cast<const float *>(&s_red[parity][0][0]) + threadIdx.x;
+                    float v = 0.f;
+#pragma unroll
+                    for (int w8 = 0; w8 < kWarps; ++w8) v += p[w8 * 128];
+                    const int ln = threadIdx.x >> 2, i = threadIdx.x & 3;   // lane (g, c) element i: row g + 8*(i>>1), token 2c + (i&1)
+                    const long r = cu_tile * 16 + (ln >> 2) + 8 * (i >> 1);
+                    const int tok = 2 * (ln & 3) + (i & 1);
+                    if (tok < T && r < nrows) out[(long)tok * ldo + r] = v;
+                }
+                parity ^= 1;   // the next tile's partials go to the other buffer, so one barrier per tile is enough
+            } else {                  // lane (g, c) holds rows g, g+8 x tokens 2c, 2c+1, complete
+                const long r = cu_tile * 16 + g;
+                if (2 * c < T) {
+                    if (r < nrows) out[(long)(2 * c) * ldo + r] = acc[0];
+                    if (r + 8 < nrows) out[(long)(2 * c) * ldo + r + 8] = acc[2];
+                }
+                if (2 * c + 1 < T) {
+                    if (r < nrows) out[(long)(2 * c + 1) * ldo + r] = acc[1];
+                    if (r + 8 < nrows) out[(long)(2 * c + 1) * ldo + r + 8] = acc[3];
+                }
+            }
+            acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+            cu_bat = 0, cu_tile += tstride;
+        }
+    };
+    for (long s = 0; s < steps; s += 2) {
+        if (s + 1 < steps) load_step(wB, dB);
+        compute_step(wA, dA);
+        if (s + 1 >= steps) break;
+        if (s + 2 < steps) load_step(wA, dA);
+        compute_step(wB, dB);
+    }
+}
+
 // ---- Q8_0 ---------------------------------------------------------------------------------------
 // Unit of work = 16-byte half block (16 int8): lane-consecutive pieces are contiguous in HBM and in smem.
 template <int T, int R>
@@ -1205,6 +1385,40 @@ int launch_resident_q4_0(tb200_ctx *c, const tb200_gemv_args &a) {
 }
 
 // grouped Q4_0 launches whose item table leads with its live items (mixmul decode): resident grid, item chosen per CTA
+size_t mma_q4_0_smem(int T, long k) { return (size_t)(k / QK) * (T * 32 + 64); }
+bool mma_enabled() {
+    static const int on = [] { const char *v = getenv("TB200_GEMV_MMA"); return (v && *v == '0') ? 0 : 1; }();
+    return on != 0;
+}
+
+// dense Q4_0 launches with 2..8 tokens: integer tensor-core kernel on a resident grid
+template <int T>
+int launch_mma_q4_0(tb200_ctx *c, const tb200_gemv_args &a) {
+    const long nb = a.w->k / QK;
+    GemvQ4Args ka;
+    fill_args<2>(ka, a, nb, nb);
+    const size_t smem = mma_q4_0_smem(T, a.w->k);
+    const long tiles = (a.nrows + 15) / 16;
+    // a warp per tile needs >= 3 rounds of tiles for the resident warps to balance; smaller matrices split K over the CTA's warps
+    // (a warp per tile, KS = 1, was measured on the vocabulary matrix: 107 us against 100 us split - 8016 tiles are 2.26
+    // rounds of the 3552 resident warps - so every Llama shape takes the split form; KS = 1 is kept for taller matrices)
+    static const int force = [] { const char *v = getenv("TB200_MMA_SPLIT"); return v && *v ? atoi(v) : -1; }();
+    const bool split = force >= 0 ? force != 0 : tiles < 6L * 3 * c->sm_count * kWarps;
+    const size_t per_cta = smem + 1024 + (split ? 2 * kWarps * 32 * 16 : 512);
+    const int resident = per_cta * 3 <= 227 * 1024 ? 3 : (per_cta * 2 <= 227 * 1024 ? 2 : 1);
+    long ctas = split ? tiles : (tiles + kWarps - 1) / kWarps;
+    if (ctas > (long)resident * c->sm_count) ctas = (long)resident * c->sm_count;
+    int rc;
+    if (split) {
+        if ((rc = set_smem(gemm_q4_0_mma_kernel<T, kWarps>, smem))) return rc;
+        TB_CUDA(tb200_launch(gemm_q4_0_mma_kernel<T, kWarps>, dim3((unsigned)ctas), dim3(kWarps * 32), smem, c->stream, ka));
+    } else {
+        if ((rc = set_smem(gemm_q4_0_mma_kernel<T, 1>, smem))) return rc;
+        TB_CUDA(tb200_launch(gemm_q4_0_mma_kernel<T, 1>, dim3((unsigned)ctas), dim3(kWarps * 32), smem, c->stream, ka));
+    }
+    return TB200_OK;
+}
+
 size_t grouped_q4_0_smem(int T, long k) { return (size_t)(k / QK) * (T * 40 + 16); }
 
 template <int T>
@@ -1227,6 +1441,10 @@ int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
     // enough CTAs (N/8) to cover 148 SMs; small matrices fall back to 1 row per warp.
     long total = a.nrows * (a.items ? (a.n_items > 0 ? a.n_items : 1) : 1);   // grouped mode: every item walks nrows rows
     for (int m = 1; m < a.nmat; ++m) total += a.w_more[m - 1]->rows;
+    if constexpr (T >= 4)   // below 4 tokens the dp4a kernels are faster (vocabulary matrix, T = 3: 89 vs 99 us)
+        if (a.w->type == TB200_TYPE_Q4_0 && !a.items && a.nmat <= 1 && a.world <= 1 && mma_enabled() && (a.w->k / QK) % 32 == 0 &&
+            mma_q4_0_smem(T, a.w->k) <= 200 * 1024)
+            return launch_mma_q4_0<T>(c, a);
     if constexpr (T == 4 || T == 8)
         if (a.w->type == TB200_TYPE_Q4_0 && a.items && a.n_live && a.nmat <= 1 && a.world <= 1 && grouped_q4_0_smem(T, a.w->k) <= 110 * 1024)
             return launch_grouped_q4_0<T>(c, a);

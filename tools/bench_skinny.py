@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--types", default="q4_0")
     ap.add_argument("--tokens", default="1,2,3,4,6,8")
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--shape", default="", help="N,K: only this shape")
     a = ap.parse_args()
     import torch
     from llamafile_b200.build import build
@@ -36,7 +37,7 @@ def main():
     tb.set_stream(stream.cuda_stream)
     for name in a.types.split(","):
         wtype = TYPES[name][0]
-        for (N, K) in SHAPES:
+        for (N, K) in ([tuple(int(v) for v in a.shape.split(","))] if a.shape else SHAPES):
             wbytes = N * K * BPE[name]
             copies = max(2, int(2 * 126e6 * 2 // wbytes) + 1) if wbytes < 256e6 else 2
             copies = min(copies, 64)
