@@ -710,6 +710,142 @@ __global__ void __launch_bounds__(kWarps * 32, 3) gemm_q4_0_mma_kernel(const __g
     }
 }
 
+// ---- Q8_0, skinny GEMM on the integer tensor-core path (4..8 tokens) --------------------------------------------
+// Same plan as gemm_q4_0_mma_kernel for tinyBLAS_Q0_AVX2's Q8_0 x Q8_0 block product (llamafile/tinyblas_cpu.h:934-993):
+// one mma.sync.m16n8k32 (s8 x s8 -> s32) per 32-byte block of 16 rows x 8 tokens, fp32 scaling per block. A block is two
+// 16-byte units; lane (g, c) loads unit c of a PAIR of blocks of its rows (a warp load = 8 rows x 64 contiguous bytes), lanes
+// c and c^2 swap eight bytes, and every lane then holds eight bytes of the first and eight of the second block: lane c
+// carries bytes {0,16,8,24}[c]..+7 of either block. The dot product is order-free inside a block, so the B fragment (the
+// token's activations) is simply staged with the same byte order.
+__device__ __forceinline__ void mma_s8s8_16832(int (&d)[4], unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned b0, unsigned b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+
+template <int T>
+__global__ void __launch_bounds__(kWarps * 32, 3) gemm_q8_0_mma_kernel(const uint4 *__restrict__ qs, const __half *__restrict__ sc, long nb, long row0, long nrows,
+                                                                       const int8_t *__restrict__ aq, const int2 *__restrict__ ads, long a_stride,
+                                                                       float *__restrict__ out, long ldo) {
+    constexpr int P = 2;                           // block pairs per lane and row in flight per batch (4 blocks)
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint2 *s_b = reinterpret_cast<uint2 *>(smem);                                  // [nb][T][4] {b0, b1}
+    float2 *s_dy = reinterpret_cast<float2 *>(smem + (size_t)nb * T * 32);         // [nb][4] {d_y(2c), d_y(2c+1)}
+    __shared__ float4 s_red[2][kWarps][32];
+
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, c = lane & 3;
+    const long tiles = (nrows + 15) / 16;
+    const int slice = (int)nb / kWarps;            // blocks of K per warp; nb % 32 == 0 (launcher)
+    const int b_lo = warp * slice;
+    const int nbat = slice / (2 * P);
+    const long my_tiles = (long)blockIdx.x < tiles ? (tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const long steps = my_tiles * nbat;
+
+    long pf_tile = blockIdx.x;
+    int pf_bat = 0;
+    const uint4 *pq0 = nullptr, *pq1 = nullptr;
+    const uint2 *ps0 = nullptr, *ps1 = nullptr;
+    auto load_step = [&](uint4 (&w)[P][2], uint2 (&dq)[2]) {
+        if (pf_bat == 0) {
+            const long r0 = row0 + min(pf_tile * 16 + g, nrows - 1), r1 = row0 + min(pf_tile * 16 + g + 8, nrows - 1);
+            pq0 = qs + (r0 * nb + b_lo) * 2 + c, pq1 = qs + (r1 * nb + b_lo) * 2 + c;
+            ps0 = reinterpret_cast<const uint2 *>(sc + r0 * nb + b_lo), ps1 = reinterpret_cast<const uint2 *>(sc + r1 * nb + b_lo);
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p) w[p][0] = ldg_stream(pq0 + p * 4), w[p][1] = ldg_stream(pq1 + p * 4);
+        dq[0] = __ldg(ps0), dq[1] = __ldg(ps1);
+        pq0 += 4 * P, pq1 += 4 * P, ps0 += 1, ps1 += 1;
+        if (++pf_bat == nbat) pf_bat = 0, pf_tile += gridDim.x;
+    };
+    uint4 wA[P][2], wB[P][2];
+    uint2 dA[2], dB[2];
+    if (steps > 0) load_step(wA, dA);
+
+    pdl_wait();
+    {   // source word w of (token, block): byte offset 4w = {0,16,8,24}[c] + 4*slot  ->  c = {0,2,1,3}[w >> 1], slot = w & 1
+        unsigned *sb = reinterpret_cast<unsigned *>(s_b);
+        const int words = (int)nb * 8;
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const unsigned *src = reinterpret_cast<const unsigned *>(aq + (long)t * a_stride);
+            for (int i = threadIdx.x; i < words; i += kWarps * 32) {
+                const int b = i >> 3, w = i & 7, pr = w >> 1;
+                const int cc = ((pr & 1) << 1) | (pr >> 1);
+                sb[((b * T + t) * 4 + cc) * 2 + (w & 1)] = src[i];
+            }
+        }
+        float *sd = reinterpret_cast<float *>(s_dy);
+        for (int i = threadIdx.x; i < (int)nb * 8; i += kWarps * 32) {
+            const int b = i >> 3, t = i & 7;
+            sd[i] = t < T ? __int_as_float(ads[(long)t * (a_stride / QK) + b].x) : 0.f;
+        }
+    }
+    __syncthreads();
+
+    const int tb = g < T ? g : T - 1;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    long cu_tile = blockIdx.x;
+    int cu_bat = 0, parity = 0;
+    auto compute_step = [&](const uint4 (&w)[P][2], const uint2 (&dq)[2]) {
+        const unsigned h0[2] = {dq[0].x, dq[0].y}, h1[2] = {dq[1].x, dq[1].y};
+        const int bq = b_lo + cu_bat * 2 * P;
+        const uint2 *pb = s_b + ((long)bq * T + tb) * 4 + c;
+        const float2 *pd = s_dy + (long)bq * 4 + c;
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            unsigned f0[2][2], f1[2][2];   // [block of the pair][slot] for rows g and g+8
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                const uint4 x = w[p][r];
+                const unsigned sx = c < 2 ? x.z : x.x, sy = c < 2 ? x.w : x.y;
+                const unsigned rx = __shfl_xor_sync(0xffffffffu, sx, 2), ry = __shfl_xor_sync(0xffffffffu, sy, 2);
+                unsigned (&f)[2][2] = r ? f1 : f0;
+                f[0][0] = c < 2 ? x.x : rx, f[0][1] = c < 2 ? x.y : ry;
+                f[1][0] = c < 2 ? rx : x.z, f[1][1] = c < 2 ? ry : x.w;
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int jb = 2 * p + j;      // block within the batch
+                const uint2 bf = pb[jb * T * 4];
+                const float2 dy = pd[jb * 4];
+                int d[4];
+                mma_s8s8_16832(d, f0[j][0], f1[j][0], f0[j][1], f1[j][1], bf.x, bf.y);
+                const float dw0 = __half2float(__ushort_as_half((unsigned short)((jb & 1) ? (h0[jb >> 1] >> 16) : (h0[jb >> 1] & 0xffffu))));
+                const float dw1 = __half2float(__ushort_as_half((unsigned short)((jb & 1) ? (h1[jb >> 1] >> 16) : (h1[jb >> 1] & 0xffffu))));
+                acc[0] = fmaf(dw0 * dy.x, (float)d[0], acc[0]);
+                acc[1] = fmaf(dw0 * dy.y, (float)d[1], acc[1]);
+                acc[2] = fmaf(dw1 * dy.x, (float)d[2], acc[2]);
+                acc[3] = fmaf(dw1 * dy.y, (float)d[3], acc[3]);
+            }
+        }
+        if (++cu_bat == nbat) {
+            s_red[parity][warp][lane] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            __syncthreads();
+            if (threadIdx.x < 128) {
+                const float *p = reinterpret_cast<const float *>(&s_red[parity][0][0]) + threadIdx.x;
+                float v = 0.f;
+#pragma unroll
+                for (int w8 = 0; w8 < kWarps; ++w8) v += p[w8 * 128];
+                const int ln = threadIdx.x >> 2, i = threadIdx.x & 3;
+                const long r = cu_tile * 16 + (ln >> 2) + 8 * (i >> 1);
+                const int tok = 2 * (ln & 3) + (i & 1);
+                if (tok < T && r < nrows) out[(long)tok * ldo + r] = v;
+            }
+            parity ^= 1;
+            acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+            cu_bat = 0, cu_tile += gridDim.x;
+        }
+    };
+    for (long s = 0; s < steps; s += 2) {
+        if (s + 1 < steps) load_step(wB, dB);
+        compute_step(wA, dA);
+        if (s + 1 >= steps) break;
+        if (s + 2 < steps) load_step(wA, dA);
+        compute_step(wB, dB);
+    }
+}
+
 // ---- Q8_0 ---------------------------------------------------------------------------------------
 // Unit of work = 16-byte half block (16 int8): lane-consecutive pieces are contiguous in HBM and in smem.
 template <int T, int R>
@@ -1419,6 +1555,22 @@ int launch_mma_q4_0(tb200_ctx *c, const tb200_gemv_args &a) {
     return TB200_OK;
 }
 
+template <int T>
+int launch_mma_q8_0(tb200_ctx *c, const tb200_gemv_args &a) {
+    const long nb = a.w->k / QK;
+    const size_t smem = (size_t)nb * (T * 32 + 32);
+    const long tiles = (a.nrows + 15) / 16;
+    const size_t per_cta = smem + 1024 + 2 * kWarps * 32 * 16;
+    const int resident = per_cta * 3 <= 227 * 1024 ? 3 : (per_cta * 2 <= 227 * 1024 ? 2 : 1);
+    long ctas = tiles;
+    if (ctas > (long)resident * c->sm_count) ctas = (long)resident * c->sm_count;
+    int rc;
+    if ((rc = set_smem(gemm_q8_0_mma_kernel<T>, smem))) return rc;
+    TB_CUDA(tb200_launch(gemm_q8_0_mma_kernel<T>, dim3((unsigned)ctas), dim3(kWarps * 32), smem, c->stream, (const uint4 *)a.w->qs, (const __half *)a.w->sc, nb,
+                         a.row0, a.nrows, a.aq, a.ads, a.a_stride, a.out, a.ldo));
+    return TB200_OK;
+}
+
 size_t grouped_q4_0_smem(int T, long k) { return (size_t)(k / QK) * (T * 40 + 16); }
 
 template <int T>
@@ -1445,6 +1597,10 @@ int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
         if (a.w->type == TB200_TYPE_Q4_0 && !a.items && a.nmat <= 1 && a.world <= 1 && mma_enabled() && (a.w->k / QK) % 32 == 0 &&
             mma_q4_0_smem(T, a.w->k) <= 200 * 1024)
             return launch_mma_q4_0<T>(c, a);
+    if constexpr (T >= 4)
+        if (a.w->type == TB200_TYPE_Q8_0 && !a.items && a.nmat <= 1 && a.world <= 1 && mma_enabled() && (a.w->k / QK) % 32 == 0 &&
+            (size_t)(a.w->k / QK) * (T * 32 + 32) <= 200 * 1024)
+            return launch_mma_q8_0<T>(c, a);
     if constexpr (T == 4 || T == 8)
         if (a.w->type == TB200_TYPE_Q4_0 && a.items && a.n_live && a.nmat <= 1 && a.world <= 1 && grouped_q4_0_smem(T, a.w->k) <= 110 * 1024)
             return launch_grouped_q4_0<T>(c, a);

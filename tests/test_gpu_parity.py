@@ -370,6 +370,58 @@ def test_prefill_cta_pair_kernel_all_types():
     assert r.returncode == 0 and "PAIR_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
+_MMA_SNIPPET = r"""
+import sys
+sys.path.insert(0, {root!r}); sys.path.insert(0, {root!r} + "/tests")
+import numpy as np, torch
+import helpers as H
+import llamafile_b200 as tb
+from oracle import binding as B
+assert tb.link()
+o = B.oracle()
+for (N, K) in ((131, 1024), (1024, 4096), (50, 14336)):
+    W = H.make_weights(H.Q4_0, N, K, seed=N)
+    w = tb.Weights(W, H.Q4_0, N, K)
+    for T in (4, 5, 8):
+        X = H.make_acts(T, K, seed=T)
+        out = torch.full((T, N), float("nan"), device="cuda")
+        tb.mul_mat(w, torch.from_numpy(X).cuda(), T, out)
+        tb.synchronize()
+        H.assert_close(out.cpu().numpy(), o.mul_mat(W, H.Q4_0, X), f"mma N={{N}} K={{K}} T={{T}}")
+print("MMA_OK")
+"""
+
+
+@pytest.mark.parametrize("split", ["0", "1"])
+def test_decode_mma_kernel_both_forms(split):
+    """Q4_0 at 4..8 tokens runs on mma.sync m16n8k32: TB200_MMA_SPLIT (read once per process) forces the warp-per-tile form (0,
+    otherwise only used for very tall matrices) or the split-K form (1); ragged row tiles, K slices shorter than a batch."""
+    import os
+    import subprocess
+    import sys
+    root = str(__import__("pathlib").Path(__file__).resolve().parent.parent)
+    env = dict(os.environ, TB200_MMA_SPLIT=split)
+    r = subprocess.run([sys.executable, "-c", _MMA_SNIPPET.format(root=root)], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "MMA_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_decode_mma_exact_integer_path(tb, oracle):
+    """Activations that quantize exactly and power-of-two scales: every fp32 product and sum of the tensor-core path is
+    exact, so the result must EQUAL the oracle's (the int32 block sums and the -8 correction carry no rounding)."""
+    N, K, T = 64, 1024, 8
+    rng = np.random.default_rng(11)
+    blocks = np.zeros((N * K // 32, 18), np.uint8)
+    blocks[:, :2] = np.full(N * K // 32, 2.0 ** -6, np.float16).view(np.uint8).reshape(-1, 2)
+    blocks[:, 2:] = rng.integers(0, 256, (N * K // 32, 16), dtype=np.uint8)
+    W = blocks.reshape(-1)
+    # every 32-block holds +-127 once, so d = amax/127 = 1 and the int8 quants are the values themselves
+    X = rng.integers(-20, 21, (T, K)).astype(np.float32)
+    X[:, ::32] = 127.0
+    out = gpu_mul_mat(tb, W, H.Q4_0, X, N, K)
+    ref = oracle.mul_mat(W, H.Q4_0, X)
+    assert np.array_equal(out, ref), float(np.abs(out - ref).max())
+
+
 def test_prefill_activation_outliers(tb, oracle):
     """Token rows with huge / tiny magnitudes: the per-token power-of-two scaling keeps fp16 operands in range."""
     N, K, T = 256, 1024, 48
