@@ -1597,7 +1597,7 @@ int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
         if (a.w->type == TB200_TYPE_Q4_0 && !a.items && a.nmat <= 1 && a.world <= 1 && mma_enabled() && (a.w->k / QK) % 32 == 0 &&
             mma_q4_0_smem(T, a.w->k) <= 200 * 1024)
             return launch_mma_q4_0<T>(c, a);
-    if constexpr (T >= 4)
+    if constexpr (T >= 2)   // Q8_0 streams twice the bytes per mma, so the tensor kernel already wins at 2 tokens (vocabulary matrix: 89 vs 118 us)
         if (a.w->type == TB200_TYPE_Q8_0 && !a.items && a.nmat <= 1 && a.world <= 1 && mma_enabled() && (a.w->k / QK) % 32 == 0 &&
             (size_t)(a.w->k / QK) * (T * 32 + 32) <= 200 * 1024)
             return launch_mma_q8_0<T>(c, a);
