@@ -176,6 +176,11 @@ def run_b200_arm(args):
     import torch.distributed as dist
 
     log("start")
+    # stdout carries ONE JSON line: native libraries (NCCL's version banner, whatever NCCL_DEBUG says) write to fd 1 directly,
+    # so fd 1 is pointed at stderr for the whole run and the line goes out through a saved copy of the real stdout
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -446,7 +451,8 @@ def run_b200_arm(args):
                            "decode_tokens_per_s": 1e3 / ms_per_step},
                 "roofline": roofline, "per_shape": per_shape, "cpu_baseline": cpu_baseline, "e2e": e2e,
                 "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks}
-        print(json.dumps(line), flush=True)
+        real_stdout.write(json.dumps(line) + "\n")
+        real_stdout.flush()
     if pg is not None and pg.timed_out():
         sys.stderr.write("bench: WARNING peer barrier timed out\n")
     log("line printed; leaving")
