@@ -568,7 +568,14 @@ __device__ __forceinline__ void quad_transpose(uint4 &x, int c, int lane) {
     x = make_uint4(v0, v1, v2, v3);
 }
 
-template <int T, int KS>   // KS = warps sharing a tile's K (8: small matrices, every tile's partials meet in shared memory; 1: a warp owns its tile)
+// PAIR (TB200_MMA_PAIR=1, experimental): 8-byte loads instead - lanes c < 2 hold the halves of one block, lanes c >= 2 those of the
+// next, and one shuffle with lane c^2 + three selects per two mma replace the 4x4 transpose (lane c then carries word {0,2,1,3}[c]).
+__device__ __forceinline__ uint2 ldg_stream64(const uint2 *p) {
+    uint2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+}
+template <int T, int KS, bool PAIR = false>   // KS = warps sharing a tile's K (8: small matrices, every tile's partials meet in shared memory; 1: a warp owns its tile)
 __global__ void __launch_bounds__(kWarps * 32, 3) gemm_q4_0_mma_kernel(const __grid_constant__ GemvQ4Args A) {
     constexpr int Q = 2;                           // quads (4 blocks) per lane and row in flight per batch
     extern __shared__ __align__(16) uint8_t smem[];
@@ -599,13 +606,19 @@ __global__ void __launch_bounds__(kWarps * 32, 3) gemm_q4_0_mma_kernel(const __g
     auto load_step = [&](uint4 (&w)[Q][2], uint2 (&dq)[Q][2]) {
         if (pf_bat == 0) {
             const long r0 = A.row0[0] + min(pf_tile * 16 + g, nrows - 1), r1 = A.row0[0] + min(pf_tile * 16 + g + 8, nrows - 1);
-            pq0 = qs + r0 * nb + b_lo + c, pq1 = qs + r1 * nb + b_lo + c;
+            pq0 = qs + r0 * nb + b_lo + (PAIR ? 0 : c), pq1 = qs + r1 * nb + b_lo + (PAIR ? 0 : c);
             ps0 = reinterpret_cast<const uint2 *>(sc + r0 * nb + b_lo), ps1 = reinterpret_cast<const uint2 *>(sc + r1 * nb + b_lo);
         }
 #pragma unroll
         for (int q = 0; q < Q; ++q)
             if (pf_bat * 4 * Q + q * 4 < slice) {   // slice-relative, warp-uniform
-                w[q][0] = ldg_stream(pq0 + q * 4), w[q][1] = ldg_stream(pq1 + q * 4);
+                if constexpr (PAIR) {
+                    const uint2 *h0p = reinterpret_cast<const uint2 *>(pq0 + q * 4) + c, *h1p = reinterpret_cast<const uint2 *>(pq1 + q * 4) + c;
+                    const uint2 a0 = ldg_stream64(h0p), b0 = ldg_stream64(h0p + 4), a1 = ldg_stream64(h1p), b1 = ldg_stream64(h1p + 4);
+                    w[q][0] = make_uint4(a0.x, a0.y, b0.x, b0.y), w[q][1] = make_uint4(a1.x, a1.y, b1.x, b1.y);
+                } else {
+                    w[q][0] = ldg_stream(pq0 + q * 4), w[q][1] = ldg_stream(pq1 + q * 4);
+                }
                 dq[q][0] = __ldg(ps0 + q), dq[q][1] = __ldg(ps1 + q);
             }
         pq0 += 4 * Q, pq1 += 4 * Q, ps0 += Q, ps1 += Q;
@@ -625,7 +638,8 @@ __global__ void __launch_bounds__(kWarps * 32, 3) gemm_q4_0_mma_kernel(const __g
             const unsigned *src = reinterpret_cast<const unsigned *>(A.aq + (long)t * A.a_stride);
             for (int i = threadIdx.x; i < words; i += kWarps * 32) {
                 const int b = i >> 3, w = i & 7;
-                sb[((b * T + t) * 4 + (w & 3)) * 2 + (w >> 2)] = src[i];
+                const int cc = PAIR ? (((w & 1) << 1) | ((w >> 1) & 1)) : (w & 3);   // PAIR: lane c carries word {0,2,1,3}[c]
+                sb[((b * T + t) * 4 + cc) * 2 + (w >> 2)] = src[i];
             }
         }
         int *sd = reinterpret_cast<int *>(s_ds);
@@ -649,8 +663,17 @@ __global__ void __launch_bounds__(kWarps * 32, 3) gemm_q4_0_mma_kernel(const __g
         for (int q = 0; q < Q; ++q) {
             const int bq = cu_bat * 4 * Q + q * 4;
             if (bq < slice) {                      // warp-uniform
-                quad_transpose(w[q][0], c, lane);
-                quad_transpose(w[q][1], c, lane);
+                if constexpr (PAIR) {
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        const uint4 x = w[q][r];
+                        const unsigned ra = __shfl_xor_sync(0xffffffffu, c < 2 ? x.y : x.x, 2), rb = __shfl_xor_sync(0xffffffffu, c < 2 ? x.w : x.z, 2);
+                        w[q][r] = make_uint4(c < 2 ? x.x : ra, c < 2 ? ra : x.y, c < 2 ? x.z : rb, c < 2 ? rb : x.w);
+                    }
+                } else {
+                    quad_transpose(w[q][0], c, lane);
+                    quad_transpose(w[q][1], c, lane);
+                }
                 const unsigned w0[4] = {w[q][0].x, w[q][0].y, w[q][0].z, w[q][0].w}, w1[4] = {w[q][1].x, w[q][1].y, w[q][1].z, w[q][1].w};
                 const unsigned h0[2] = {dq[q][0].x, dq[q][0].y}, h1[2] = {dq[q][1].x, dq[q][1].y};
                 const uint2 *pb = s_b + ((b_lo + bq) * T + tb) * 4 + c;   // one address per quad, compile-time offsets per block
@@ -1546,6 +1569,12 @@ int launch_mma_q4_0(tb200_ctx *c, const tb200_gemv_args &a) {
     if (ctas > (long)resident * c->sm_count) ctas = (long)resident * c->sm_count;
     int rc;
     if (split) {
+        static const bool pair = [] { const char *v = getenv("TB200_MMA_PAIR"); return v && *v == '1'; }();
+        if (pair) {
+            if ((rc = set_smem(gemm_q4_0_mma_kernel<T, kWarps, true>, smem))) return rc;
+            TB_CUDA(tb200_launch(gemm_q4_0_mma_kernel<T, kWarps, true>, dim3((unsigned)ctas), dim3(kWarps * 32), smem, c->stream, ka));
+            return TB200_OK;
+        }
         if ((rc = set_smem(gemm_q4_0_mma_kernel<T, kWarps>, smem))) return rc;
         TB_CUDA(tb200_launch(gemm_q4_0_mma_kernel<T, kWarps>, dim3((unsigned)ctas), dim3(kWarps * 32), smem, c->stream, ka));
     } else {
