@@ -51,6 +51,7 @@ struct GemvQ4Args {
     const int8_t *aq; const int2 *ads; long a_stride;   // planar activations
     const tb200_gemv_item *items;
     const int *n_live;                 // grouped resident kernel: number of live items (they lead the table)
+    int flags;                         // bit 0: the Q4_0 mma kernel pulls the step after next into L2 (TB200_MMA_PREFETCH=0 turns it off)
 };
 
 // Epilogue shared by the quantized decode kernels: warp-reduce each (row, token) and store. With world > 1 the
@@ -623,6 +624,10 @@ __global__ void __launch_bounds__(kWarps * 32, 3) gemm_q4_0_mma_kernel(const __g
             }
         pq0 += 4 * Q, pq1 += 4 * Q, ps0 += Q, ps1 += Q;
         if (++pf_bat == nbat) pf_bat = 0, pf_tile += tstride;
+        if ((A.flags & 1) && lane < 16 && pf_tile < tiles) {   // the step after this one: one 128-byte line per row into L2
+            const long r = A.row0[0] + min(pf_tile * 16 + lane, nrows - 1);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(qs + r * nb + b_lo + pf_bat * 4 * Q));
+        }
     };
     uint4 wA[Q][2], wB[Q][2];
     uint2 dA[Q][2], dB[Q][2];
@@ -1570,6 +1575,8 @@ int launch_mma_q4_0(tb200_ctx *c, const tb200_gemv_args &a) {
     int rc;
     if (split) {
         static const bool pair = [] { const char *v = getenv("TB200_MMA_PAIR"); return v && *v == '1'; }();
+        static const bool pref = [] { const char *v = getenv("TB200_MMA_PREFETCH"); return !(v && *v == '0'); }();   // N=14336 T=4 15.4 -> 14.3 us, K=14336 T=8 29.2 -> 25.4 us, vocabulary matrix unchanged
+        if (pref) ka.flags |= 1;
         if (pair) {
             if ((rc = set_smem(gemm_q4_0_mma_kernel<T, kWarps, true>, smem))) return rc;
             TB_CUDA(tb200_launch(gemm_q4_0_mma_kernel<T, kWarps, true>, dim3((unsigned)ctas), dim3(kWarps * 32), smem, c->stream, ka));
