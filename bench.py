@@ -1,22 +1,22 @@
 #!/usr/bin/env python
-"""bench.py — BASELINE.json's metric on B200: Q4_0 decode GEMV GB/s at Llama-3-8B shapes.
+"""bench.py — BASELINE.json's metric on B200: Q4_0 decode GEMV GB/s (+ Q8_0/Q4_0 prefill GEMM TFLOPS) at Llama-3-8B shapes.
 
 A "step" is one decode token's worth of weight matmuls of Llama-3-8B (BASELINE configs[1]: M=1, K=4096,
-N=4096/14336/128256 plus the model's other matrices): 32 layers x {wq, wk, wv, wo, gate, up, down} + the
-output projection = 225 GEMVs over 4.22 GB of distinct Q4_0 weights (>> 126 MB L2, so every step streams
-from HBM; no flush needed). Activations are quantized on the device exactly as ggml does before
-llamafile_sgemm (one quantizer launch per distinct input; matrices sharing an input — wq/wk/wv, gate/up — share one
-GEMV launch: 129 + 129 launches).
+N=4096/14336/128256 plus the model's other matrices): 32 layers x {wq, wk, wv, wo, gate, up, down} + the output
+projection = 225 GEMVs in 129 launch groups (matrices sharing an input — wq/wk/wv, gate/up — form one group) over
+4.22 GB of distinct Q4_0 weights (>> 126 MB L2: every step streams from HBM, no flush needed). Each group's fp32 input is
+quantized to Q8_0 exactly as ggml does before llamafile_sgemm, inside the timed region.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME] [--decode plan|oneshot]
 
-value   : algorithmic GB/s, inputs resident in HBM, the whole step replayed from a CUDA graph.
-e2e     : the same step through the reference-facing C-ABI entry point llamafile_sgemm() with HOST buffers
-          (pinned): Q8_0 activations H2D and fp32 results D2H inside the timed region, weights resident
-          (uploaded once at first use, as the mmap'd GGUF would be).
-roofline: the decode GEMV kernel alone (graph of the step's 129 GEMV launches, no quantizers), CUDA events.
-cpu_baseline / --impl reference: the reference's own CPU tinyBLAS/iqk path (oracle/_ref) on the host cores.
-N > 1   : every weight matrix row-sharded over the ranks, outputs all-gathered with NCCL.
+value    : algorithmic GB/s of the whole step, inputs resident in HBM. Default (Q4_0, 1 GPU): the DECODE PLAN, the whole step
+           as ONE persistent kernel (tb200_plan.cu: per-warp TMA rings, in-kernel quantization, group g waits for g-1).
+           `--decode oneshot` (and the other weight types / N > 1): one quantizer + one GEMV launch per group from a CUDA graph.
+roofline : the dominant kernel — the plan kernel (it IS the step), or the GEMV launches alone for oneshot — with CUDA events;
+           plus roofline.prefill[] (tcgen05 GEMM, TFLOPS sustained for >= 1 s per point), roofline.mixmul[], roofline.quantizer.
+e2e      : the same step through the reference-facing C entry point llamafile_sgemm() with HOST buffers.
+cpu_baseline / --impl reference: the reference's own CPU tinyBLAS/iqk path (oracle/_ref) over the SAME full step on the host cores.
+N > 1    : launch groups >= --split-min-mb row-sharded over the ranks, outputs exchanged by peer stores fused into the kernels.
 """
 from __future__ import annotations
 
@@ -37,19 +37,22 @@ sys.path.insert(0, str(ROOT))
 
 Q4_0, Q8_0, Q4_K, Q6_K, F16, F32 = 2, 8, 12, 14, 1, 0
 BPE = {Q4_0: 18 / 32, Q8_0: 34 / 32, Q4_K: 144 / 256, Q6_K: 210 / 256, F16: 2.0}
+TS_BLCK = {Q4_0: (18, 32), Q8_0: (34, 32), Q4_K: (144, 256), Q6_K: (210, 256)}
+SPEC_HBM_GBS, SPEC_BF16_TFLOPS = 8000.0, 2250.0       # the figures north_star names
 
+_LLAMA8B = [("wq", 4096, 4096, "attn"), ("wk", 1024, 4096, "attn"), ("wv", 1024, 4096, "attn"), ("wo", 4096, 4096, "o"),
+            ("gate", 14336, 4096, "ffn"), ("up", 14336, 4096, "ffn"), ("down", 4096, 14336, "down")]
 WORKLOADS = {
-    # name: (weight type, hidden, layers, per-layer [(name, N, K, input-group)], [(name, N, K)] tail)
-    "llama3-8b-q4_0-decode": (Q4_0, 32, [("wq", 4096, 4096, "attn"), ("wk", 1024, 4096, "attn"), ("wv", 1024, 4096, "attn"),
-                                         ("wo", 4096, 4096, "o"), ("gate", 14336, 4096, "ffn"), ("up", 14336, 4096, "ffn"),
-                                         ("down", 4096, 14336, "down")], [("output", 128256, 4096, "out")]),
-    "llama3-8b-q6_K-decode": (Q6_K, 32, [("wq", 4096, 4096, "attn"), ("wk", 1024, 4096, "attn"), ("wv", 1024, 4096, "attn"),
-                                         ("wo", 4096, 4096, "o"), ("gate", 14336, 4096, "ffn"), ("up", 14336, 4096, "ffn"),
-                                         ("down", 4096, 14336, "down")], [("output", 128256, 4096, "out")]),
+    # name: (weight type, layers, per-layer [(name, N, K, input-group)], [(name, N, K, group)] tail)
+    "llama3-8b-q4_0-decode": (Q4_0, 32, _LLAMA8B, [("output", 128256, 4096, "out")]),
+    "llama3-8b-q6_K-decode": (Q6_K, 32, _LLAMA8B, [("output", 128256, 4096, "out")]),
     "llama3-70b-q4_K-decode": (Q4_K, 80, [("wq", 8192, 8192, "attn"), ("wk", 1024, 8192, "attn"), ("wv", 1024, 8192, "attn"),
                                           ("wo", 8192, 8192, "o"), ("gate", 28672, 8192, "ffn"), ("up", 28672, 8192, "ffn"),
                                           ("down", 8192, 28672, "down")], [("output", 128256, 8192, "out")]),
 }
+METRIC = {Q4_0: "Q4_0 decode GEMV GB/s (Llama-3-8B shapes)", Q4_K: "Q4_K decode GEMV GB/s (Llama-3-70B shapes)",
+          Q6_K: "Q6_K decode GEMV GB/s (Llama-3-8B shapes)"}
+PREFILL_SHAPES = [(4096, 4096), (14336, 4096), (4096, 14336)]
 
 
 def algorithmic_bytes(wtype, N, K, T=1):
@@ -57,16 +60,26 @@ def algorithmic_bytes(wtype, N, K, T=1):
     return N * K * BPE[wtype] + T * K * 4 + T * N * 4
 
 
-from llamafile_b200.shard import shard_rows  # noqa: E402  (row split in 128-row tiles, as ggml-cuda.cu:646-674)
+def workload_config(name, layers=0):
+    """The part of `config` both arms print identically."""
+    wtype, L, layer, tail = WORKLOADS[name]
+    L = layers or L
+    mats = [(N, K) for _ in range(L) for (_, N, K, _) in layer] + [(N, K) for (_, N, K, _) in tail]
+    return {"workload": name, "tokens": 1, "layers": L, "matmuls_per_step": len(mats),
+            "weight_GB_per_step": sum(algorithmic_bytes(wtype, N, K) for N, K in mats) / 1e9,
+            "l2": "distinct weights per step exceed L2 (126 MB) 30x; no flush needed"}
+
+
+from llamafile_b200.shard import max_shard, shard_rows  # noqa: E402  (row split in 128-row tiles, as ggml-cuda.cu:646-674)
 
 
 class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.rows, self.stop_flag, self.marks = index, [], False, {}
 
     def run(self):
-        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw"
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
@@ -77,90 +90,117 @@ class ClockSampler(threading.Thread):
                 pass
             time.sleep(0.1)
 
-    def summary(self):
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+    def mark(self, name):
+        self.marks[name] = len(self.rows)
+
+    def summary(self, lo=0, hi=None):
+        rows = self.rows[lo:hi]
+        num = lambda s: s.replace(".", "", 1).isdigit()   # noqa: E731
+        sm = [float(r[0]) for r in rows if r and num(r[0])]
+        mx = [float(r[1]) for r in rows if len(r) > 1 and num(r[1])]
+        pw = [float(r[7]) for r in rows if len(r) > 7 and num(r[7])]
         reasons = set()
-        for r in self.rows:
+        for r in rows:
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
-def measured_peak():
+def measured_peaks():
     p = ROOT / "MEASURED_PEAKS.json"
+    out = {"hbm": (6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"), "tf_sustained": (1377.0, "fallback"), "tf_burst": (1630.9, "fallback")}
     if p.exists():
         try:
-            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+            j = json.loads(p.read_text())
+            out["hbm"] = (float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)")
+            out["tf_sustained"] = (float(j["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained)")
+            out["tf_burst"] = (float(j["bf16_tflops"]), "measured (MEASURED_PEAKS.json bf16_tflops)")
         except Exception:
             pass
-    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+    return out
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
-def reference_sample(workload, threads=None, budget_s=12.0, min_reps=2):
-    """One layer of the workload (its 7 matmuls) through the reference's own CPU path: quantize_row_q8_0 /
-    q8_K + llamafile_sgemm (iqk / tinyBLAS), all host threads. Returns (GB/s, info)."""
-    from oracle import binding as B
-    impl = B.reference()
-    kind = "reference"
-    if impl is None:
-        impl, kind = B.oracle(), "port"
-    wtype, _, layer, _ = WORKLOADS[workload]
-    nth = threads or (os.cpu_count() or 1)
-    rng = np.random.default_rng(0)
-    mats = []
-    for name, N, K, _g in layer:
-        nb = N * K // B.BLCK[wtype]
-        W = rng.integers(0, 256, (nb, B.TYPE_SIZE[wtype]), dtype=np.uint8)
-        W[:, :2] = (rng.uniform(0.5, 1.5, nb) * 2e-3).astype(np.float16).view(np.uint8).reshape(-1, 2)
-        if wtype == Q4_K:
-            W[:, 2:4] = (rng.uniform(0.5, 1.5, nb) * 4e-3).astype(np.float16).view(np.uint8).reshape(-1, 2)
-        mats.append((N, K, W.reshape(-1), rng.standard_normal((1, K)).astype(np.float32)))
-    total_bytes = sum(algorithmic_bytes(wtype, N, K) for N, K, _, _ in mats)
+class ReferenceStep:
+    """The workload's FULL decode step (every matmul, every layer) through the reference's own CPU path: quantize_row_q8_0 /
+    q8_K + llamafile_sgemm (iqk / tinyBLAS), all host threads, driven like llamafile/sgemm_matmul_test.cpp:32-40. One layer's
+    weights are synthesized and copied to every layer's own host buffer (distinct memory, so nothing is cache-resident
+    across layers — the same bytes the GPU arm streams)."""
 
-    def one_pass():
-        for N, K, W, x in mats:
-            impl.mul_mat(W, wtype, x, nth=nth) if kind == "reference" else impl.mul_mat(W, wtype, x)
-    one_pass()   # warm-up
-    reps, t0 = 0, time.perf_counter()
-    while reps < min_reps or time.perf_counter() - t0 < budget_s:
-        one_pass()
-        reps += 1
-        if time.perf_counter() - t0 > 3 * budget_s:
-            break
-    dt = (time.perf_counter() - t0) / reps
-    info = {"kind": kind, "cores": nth if kind == "reference" else (os.cpu_count() or 1),
-            "sample": f"1 of {WORKLOADS[workload][1]} layers ({len(mats)} matmuls, {total_bytes / 1e9:.3f} GB) x {reps} reps, "
-                      f"activation quantization included" + (f", ISA variant {impl.variant}" if kind == "reference" else ", OpenMP scalar port"),
-            "ms_per_sample": dt * 1e3}
-    return total_bytes / dt / 1e9, info
+    def __init__(self, workload, layers=0, threads=None):
+        from oracle import binding as B
+        self.B = B
+        self.impl, self.kind = B.reference(), "reference"
+        if self.impl is None:
+            self.impl, self.kind = B.oracle(), "port"
+        self.wtype, L, layer, tail = WORKLOADS[workload]
+        self.layers = layers or L
+        self.nth = threads or (os.cpu_count() or 1)
+        rng = np.random.default_rng(0)
+
+        def synth(N, K):
+            ts, blck = TS_BLCK[self.wtype]
+            nb = N * K // blck
+            W = rng.integers(0, 256, (nb, ts), dtype=np.uint8)
+            d = (rng.uniform(0.5, 1.5, nb) * 2e-3).astype(np.float16).view(np.uint8).reshape(-1, 2)
+            if self.wtype == Q6_K:
+                W[:, 208:210] = (rng.uniform(0.5, 1.5, nb) * 2e-5).astype(np.float16).view(np.uint8).reshape(-1, 2)
+            else:
+                W[:, :2] = d
+            if self.wtype == Q4_K:
+                W[:, 2:4] = (rng.uniform(0.5, 1.5, nb) * 4e-3).astype(np.float16).view(np.uint8).reshape(-1, 2)
+            return W.reshape(-1)
+        proto = [(N, K, synth(N, K)) for (_, N, K, _) in layer]
+        self.mats = []
+        for li in range(self.layers):
+            for N, K, W in proto:
+                self.mats.append((N, K, W if li == 0 else W.copy(), rng.standard_normal((1, K)).astype(np.float32)))
+        for (_, N, K, _) in tail:
+            self.mats.append((N, K, synth(N, K), rng.standard_normal((1, K)).astype(np.float32)))
+        self.bytes = sum(algorithmic_bytes(self.wtype, N, K) for N, K, _, _ in self.mats)
+
+    def step(self):
+        for N, K, W, x in self.mats:
+            if self.kind == "reference":
+                self.impl.mul_mat(W, self.wtype, x, nth=self.nth)
+            else:
+                self.impl.mul_mat(W, self.wtype, x)
+
+    def describe(self, reps):
+        isa = f", ISA variant {self.impl.variant}" if self.kind == "reference" else ", OpenMP scalar port"
+        return (f"full step: {self.layers} layers, {len(self.mats)} matmuls, {self.bytes / 1e9:.3f} GB of distinct host weights x {reps} reps, "
+                f"activation quantization included{isa}")
+
+    def timed(self, reps):
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            self.step()
+        return (time.perf_counter() - t0) / reps
 
 
 def run_reference_arm(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    wtype, layers, layer, tail = WORKLOADS[args.workload]
-    vals = []
-    for _ in range(max(1, args.warmup) - 1):
-        pass
-    per_step_budget = max(2.0, min(12.0, 150.0 / max(1, args.steps + args.warmup)))
     t0 = time.perf_counter()
-    info = None
-    for s in range(args.steps):
-        v, info = reference_sample(args.workload, budget_s=per_step_budget / 2, min_reps=1)
-        vals.append(v)
-    value = statistics.median(vals)
-    line = {"impl": "reference", "metric": "Q4_0 decode GEMV GB/s (Llama-3-8B shapes)", "value": value, "unit": "GB/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": info["ms_per_sample"], "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "int8 dot products, fp32 accumulate", "data": "synthetic",
-            "config": {"workload": args.workload, "tokens": 1, "note": "each step = bounded sample (one layer) on the host cores"},
-            "cpu_baseline": {"value": value, "unit": "GB/s", **{k: info[k] for k in ("cores", "kind", "sample")}},
+    ref = ReferenceStep(args.workload, args.layers)
+    for _ in range(max(1, args.warmup)):
+        ref.step()
+    times = []
+    for _ in range(args.steps):
+        times.append(ref.timed(1))
+        if time.perf_counter() - t0 > 150 and len(times) >= 3:   # bounded: the run ends within a few minutes on any host
+            break
+    dt = statistics.median(times)
+    value = ref.bytes / dt / 1e9
+    line = {"impl": "reference", "metric": METRIC[ref.wtype], "value": value, "unit": "GB/s", "n_gpus": args.gpus, "steps": len(times),
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "int8 block dot products, fp32 accumulate", "data": "synthetic", "config": workload_config(args.workload, args.layers),
+            "cpu_baseline": {"value": value, "unit": "GB/s", "cores": ref.nth if ref.kind == "reference" else (os.cpu_count() or 1),
+                             "kind": ref.kind, "sample": ref.describe(len(times))},
             "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
-            "wall_s": time.perf_counter() - t0}
+            "decode_tokens_per_s": 1.0 / dt, "wall_s": time.perf_counter() - t0}
     print(json.dumps(line), flush=True)
 
 
@@ -171,13 +211,121 @@ def log(msg):
         sys.stderr.flush()
 
 
+def synth_dev(torch, dev, wtype, N, K, seed):
+    """Random quant bytes with realistic fp16 scales, built on the device."""
+    g = torch.Generator(device=dev); g.manual_seed(seed)
+    if wtype == F16:
+        return (torch.randn(N, K, device=dev, generator=g) * 0.02).to(torch.float16).view(torch.uint8).reshape(-1)
+    ts, blck = TS_BLCK[wtype]
+    nb = N * K // blck
+    raw = torch.randint(0, 256, (nb, ts), dtype=torch.uint8, device=dev, generator=g)
+    d = (torch.rand(nb, device=dev, generator=g) + 0.5) * 2e-3
+    raw[:, 0:2] = d.to(torch.float16).view(torch.uint8).reshape(nb, 2)
+    if wtype == Q4_K:
+        raw[:, 2:4] = (d * 2).to(torch.float16).view(torch.uint8).reshape(nb, 2)
+    if wtype == Q6_K:   # block_q6_K keeps d in its last two bytes; the first two are quants
+        raw[:, 0:2] = torch.randint(0, 256, (nb, 2), dtype=torch.uint8, device=dev, generator=g)
+        raw[:, 208:210] = (d * 1e-2).to(torch.float16).view(torch.uint8).reshape(nb, 2)
+    return raw.reshape(-1)
+
+
+def sustained(torch, stream, fn, min_s=1.0, calib=3):
+    """fn() launched back to back for >= min_s (the sustained regime: clocks and power settle); ms per call by CUDA events."""
+    with torch.cuda.stream(stream):
+        for _ in range(calib):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(calib):
+            fn()
+        e1.record(stream)
+        stream.synchronize()
+        per = max(e0.elapsed_time(e1) / calib, 1e-3)
+        n = max(5, int(min_s * 1e3 / per) + 1)
+        e0.record(stream)
+        for _ in range(n):
+            fn()
+        e1.record(stream)
+        stream.synchronize()
+    return e0.elapsed_time(e1) / n, n
+
+
+def prefill_leg(torch, tb, dev, stream, sampler, peaks):
+    """BASELINE config 3: Q8_0 and Q4_0 prefill GEMM on tcgen05, T in {512, 4096}, the three Llama-3-8B shapes. Each point runs
+    tb200_mul_mat (activation quantize + fp16 prep + GEMM) back to back for >= 1 s; weights/outputs rotate over enough
+    distinct copies to exceed L2 where one problem would fit in it."""
+    out = []
+    for wtype, name in ((Q8_0, "q8_0"), (Q4_0, "q4_0")):
+        for (N, K) in PREFILL_SHAPES:
+            for T in (512, 4096):
+                foot = N * K * BPE[wtype] + T * K * 4 + T * N * 4
+                copies = max(1, min(8, int(300e6 // foot) + 1))
+                ws = [tb.Weights(synth_dev(torch, dev, wtype, N, K, seed=c), wtype, N, K) for c in range(copies)]
+                x = torch.randn(T, K, device=dev)
+                outs = [torch.empty(T, N, device=dev) for _ in range(copies)]
+                it = [0]
+
+                def fn():
+                    c = it[0] % copies
+                    it[0] += 1
+                    tb.mul_mat(ws[c], x, T, outs[c])
+                sampler.mark(f"pf{len(out)}a")
+                ms, n = sustained(torch, stream, fn, min_s=1.0)
+                sampler.mark(f"pf{len(out)}b")
+                tf = 2.0 * T * N * K / (ms * 1e-3) / 1e12
+                clk = sampler.summary(sampler.marks[f"pf{len(out)}a"], sampler.marks[f"pf{len(out)}b"])
+                out.append({"type": name, "N": N, "K": K, "T": T, "ms": ms, "calls": n, "TFLOPS": tf, "frac_of_measured_sustained": tf / peaks["tf_sustained"][0],
+                            "frac_of_spec_2250": tf / SPEC_BF16_TFLOPS, "distinct_copies": copies, "sm_mhz": clk["sm_mhz"], "power_w_max": clk["power_w_max"],
+                            "reasons": clk["reasons"]})
+                log(f"prefill {name} N={N} K={K} T={T}: {tf:.0f} TFLOPS")
+                for w in ws:
+                    w.free()
+                del outs, x
+    return out
+
+
+def mixmul_leg(torch, tb, dev, stream):
+    """BASELINE config 4: Mixtral-8x7B ffn_gate_exps (8 experts x 14336 x 4096, Q4_0), top-2, through tb200_mixmul_dev
+    (activation quantize + device-side expert grouping + grouped kernel); 264 MB of experts exceed L2."""
+    rows, cols, experts, top = 14336, 4096, 8, 2
+    w = tb.Weights(synth_dev(torch, dev, Q4_0, rows * experts, cols, seed=5), Q4_0, rows * experts, cols)
+    g = torch.Generator(device=dev); g.manual_seed(1)
+    res = []
+    for tokens in (1, 512):
+        x = torch.randn(tokens, 1, cols, device=dev, generator=g)
+        plan = torch.stack([torch.randperm(experts, device=dev, generator=g)[:top] for _ in range(tokens)]).to(torch.int32).contiguous()
+        outb = torch.empty(tokens, top, rows, device=dev)
+        touched = int(torch.unique(plan).numel())
+        ms, n = sustained(torch, stream, lambda: tb.mixmul(w, experts, x, 1, plan, top, tokens, outb), min_s=0.5)
+        byts = touched * rows * cols * BPE[Q4_0] + tokens * cols * 4 + tokens * top * rows * 4
+        res.append({"op": "mul_mat_id", "type": "q4_0", "rows": rows, "cols": cols, "experts": experts, "top": top, "tokens": tokens,
+                    "experts_touched": touched, "ms": ms, "calls": n, "GBps": byts / (ms * 1e-3) / 1e9, "TFLOPS": 2.0 * tokens * top * rows * cols / (ms * 1e-3) / 1e12})
+    w.free()
+    return res
+
+
+def quantizer_leg(torch, tb, dev, stream, peak_hbm):
+    """BASELINE.md §3 last row: T x K fp32 -> Q8_0 blocks, T=512, K=4096, rotating over 32 distinct inputs (268 MB > L2)."""
+    T, K, copies = 512, 4096, 32
+    xs = [torch.randn(T, K, device=dev) for _ in range(copies)]
+    y = torch.empty(T * K // 32 * 34, dtype=torch.uint8, device=dev)
+    it = [0]
+
+    def fn():
+        tb.quantize_q8_0(xs[it[0] % copies], T, K, y)
+        it[0] += 1
+    ms, n = sustained(torch, stream, fn, min_s=0.3)
+    byts = T * K * 4 + T * K // 32 * 34
+    return {"op": "quantize_row_q8_0", "rows": T, "k": K, "ms": ms, "calls": n, "GBps": byts / (ms * 1e-3) / 1e9, "frac": byts / (ms * 1e-3) / 1e9 / peak_hbm}
+
+
 def run_b200_arm(args):
     import torch
     import torch.distributed as dist
 
     log("start")
-    # stdout carries ONE JSON line: native libraries (NCCL's version banner, whatever NCCL_DEBUG says) write to fd 1 directly,
-    # so fd 1 is pointed at stderr for the whole run and the line goes out through a saved copy of the real stdout
+    # stdout carries ONE JSON line: native libraries (NCCL's banner, whatever the caller's NCCL_DEBUG asks for) write to fd 1
+    # directly, so fd 1 is pointed at stderr for the whole run and the line goes out through a saved copy of the real stdout
     sys.stdout.flush()
     real_stdout = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
@@ -185,7 +333,6 @@ def run_b200_arm(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = os.environ.get("TB200_NCCL_DEBUG", "WARN")   # keep NCCL's version banner off stdout: ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from llamafile_b200.build import build
     build()
@@ -196,66 +343,46 @@ def run_b200_arm(args):
     dev = torch.device("cuda", local)
     stream = torch.cuda.Stream(device=dev)
     tb.set_stream(stream.cuda_stream)
+    peaks = measured_peaks()
 
     wtype, layers, layer, tail = WORKLOADS[args.workload]
     if args.layers:
         layers = args.layers
-    ts, blck = {Q4_0: (18, 32), Q4_K: (144, 256), Q6_K: (210, 256)}[wtype]
+    use_plan = args.decode == "plan" and wtype == Q4_0 and world == 1
 
-    # ---- synthetic resident weights: random quant bytes, realistic fp16 scales; each rank builds its row shard
-    def synth(N, K, seed):
-        g = torch.Generator(device=dev); g.manual_seed(seed)
-        nb = N * K // blck
-        raw = torch.randint(0, 256, (nb, ts), dtype=torch.uint8, device=dev, generator=g)
-        d = (torch.rand(nb, device=dev, generator=g) + 0.5) * 2e-3
-        raw[:, 0:2] = d.to(torch.float16).view(torch.uint8).reshape(nb, 2)
-        if wtype == Q4_K:
-            raw[:, 2:4] = (d * 2).to(torch.float16).view(torch.uint8).reshape(nb, 2)
-        if wtype == Q6_K:   # block_q6_K keeps d in its last two bytes; the first two are quants
-            raw[:, 0:2] = torch.randint(0, 256, (nb, 2), dtype=torch.uint8, device=dev, generator=g)
-            raw[:, 208:210] = (d * 1e-2).to(torch.float16).view(torch.uint8).reshape(nb, 2)
-        return raw.reshape(-1)
-
-    mats = []   # (name, N_full, lo, hi, K, group, Weights, raw or None)
     specs = [(f"l{li}.{n}", N, K, f"l{li}.{g}") for li in range(layers) for (n, N, K, g) in layer] + [(n, N, K, g) for (n, N, K, g) in tail]
     # north_star: "weight matrices of layers large enough to split are sharded by output rows". A launch group (the matrices
-    # sharing one input) is split when its weights exceed --split-min-mb; smaller groups are computed in full on every rank, which
-    # needs no exchange at all (an 8B attention group is 14 MB = ~2 us of HBM time, less than one cross-GPU barrier; measured on 2 GPUs, 8B step: everything
-    # split 1.55 ms, groups >= 16 MB split 1.26 ms, one GPU 1.14 ms).
+    # sharing one input) is split when its weights exceed --split-min-mb; smaller groups are computed in full on every rank.
     grp_bytes = {}
     for (name, N, K, grp) in specs:
         grp_bytes[grp] = grp_bytes.get(grp, 0) + N * K * BPE[wtype]
     split_grp = {g: world > 1 and b >= args.split_min_mb * 1e6 for g, b in grp_bytes.items()}
-    keep_raw = args.e2e
-    host_raw = []
+    mats, host_raw = [], []   # (name, N_full, lo, hi, K, group, Weights)
+
+    def shard_seed(i, r, grp):
+        return 1000 * i + (r if split_grp[grp] else 0)   # replicated groups hold the same weights on every rank
     with torch.cuda.stream(stream):
         for i, (name, N, K, grp) in enumerate(specs):
             lo, hi = shard_rows(N, rank, world) if split_grp[grp] else (0, N)
-            raw = synth(hi - lo, K, seed=1000 * i + (rank if split_grp[grp] else 0))   # replicated groups hold the same weights on every rank
+            raw = synth_dev(torch, dev, wtype, hi - lo, K, seed=shard_seed(i, rank, grp))
             w = tb.Weights(raw, wtype, hi - lo, K)
-            if keep_raw:
+            if args.e2e:
                 host_raw.append(raw.cpu().numpy())
             del raw
             mats.append((name, N, lo, hi, K, grp, w))
     torch.cuda.synchronize()
 
-    # one activation tensor per distinct input (attn / o / ffn / down per layer, + output)
-    groups = {}
-    for name, N, lo, hi, K, grp, w in mats:
-        if grp not in groups:
-            x = torch.randn(1, K, device=dev, dtype=torch.float32)
-            groups[grp] = (x, tb.Acts(wtype, K, 1))
-    # launch schedule of one step: matrices that consume the same activations go out in ONE launch
-    # (tb200_mul_mat_acts_multi: wq/wk/wv, gate/up).
-    schedule = []
+    # one fp32 input per launch group (attn / o / ffn / down per layer, + output); matrices that consume the same input
+    # go out together (tb200_mul_mat_acts_multi / one plan group: wq/wk/wv, gate/up)
+    groups, schedule = {}, []
     for i, m in enumerate(mats):
+        if m[5] not in groups:
+            groups[m[5]] = (torch.randn(1, m[4], device=dev, dtype=torch.float32), None if use_plan else tb.Acts(wtype, m[4], 1))
         if schedule and schedule[-1][0] == m[5] and len(schedule[-1][1]) < 4 and wtype in (Q4_0, Q4_K, Q6_K):
             schedule[-1][1].append(i)
         else:
             schedule.append((m[5], [i]))
-    # outputs: each rank writes its row slices of a launch group into ONE staging row (every slice padded to the widest
-    # shard so uneven splits, e.g. vocab 128256 = 1002 tiles, line up), which is all-gathered with one collective per group
-    from llamafile_b200.shard import max_shard
+    # outputs: each rank writes its row slices of a launch group into ONE staging row (every slice padded to the widest shard)
     outs, staging, gathered = [None] * len(mats), [], []
     for grp, idx in schedule:
         widths = [max_shard(mats[i][1], world) if split_grp[grp] else mats[i][1] for i in idx]
@@ -265,10 +392,8 @@ def run_b200_arm(args):
             outs[i] = st[:, off: off + (mats[i][3] - mats[i][2])]
             off += wd
         staging.append(st)
-        gathered.append(torch.empty(world, st.shape[1], device=dev, dtype=torch.float32) if world > 1 else None)
+        gathered.append(torch.empty(world, st.shape[1], device=dev, dtype=torch.float32) if world > 1 and args.gather == "nccl" else None)
 
-    # multi-GPU exchange: "p2p" = the decode kernels store their rows into every rank's symmetric buffer over NVLink
-    # (fused all-gather, one flag barrier per launch group); "nccl" = ncclAllGather of the staging rows per launch group
     pg, p2p_off = None, None
     if world > 1 and args.gather == "p2p":
         from llamafile_b200.peer import PeerGroup
@@ -278,7 +403,14 @@ def run_b200_arm(args):
             off += N * 4
         pg = PeerGroup(world, rank, off)
 
+    plan = None
+    if use_plan:
+        plan = tb.Plan([{"w": [mats[i][6] for i in idx], "out": [outs[i] for i in idx], "x": groups[grp][0]} for grp, idx in schedule])
+
     def step(with_gather=True, with_quant=True):
+        if plan is not None:
+            plan.run()
+            return
         for gi, (grp, idx) in enumerate(schedule):
             x, acts = groups[grp]
             if with_quant:
@@ -296,6 +428,7 @@ def run_b200_arm(args):
 
     step_bytes = sum(algorithmic_bytes(wtype, hi - lo, K) for (_, N, lo, hi, K, g, w) in mats)
     total_step_bytes = sum(algorithmic_bytes(wtype, N, K) for (_, N, lo, hi, K, g, w) in mats)
+    graphs = []
 
     def capture(fn):
         """CUDA graph of one step on our stream (falls back to eager launches if capture is refused)."""
@@ -308,6 +441,7 @@ def run_b200_arm(args):
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g, stream=stream):
                     fn()
+                graphs.append(g)
                 return g.replay, True
             except Exception as e:   # noqa: BLE001
                 sys.stderr.write(f"bench: graph capture unavailable ({e}); timing eager launches\n")
@@ -340,72 +474,137 @@ def run_b200_arm(args):
     l0 = tb.launch_count()
     with torch.cuda.stream(stream):
         step()
+    stream.synchronize()
     launches_per_step = tb.launch_count() - l0
+    if plan is not None and plan.status() != 0:
+        raise SystemExit("bench: the decode plan kernel gave up waiting (status != 0)")
+
+    # ---- N > 1: the exchanged outputs must be the unsharded product. Rank 0 regenerates every rank's shard of a few split
+    # matrices from their seeds, multiplies them unsharded on its own GPU and compares sampled rows with its copy of the
+    # symmetric buffer (fused path) / the gathered rows (NCCL path).
+    parity_checked = None
+    if world > 1:
+        ok, checked = True, 0
+        split_idx = [i for i, m in enumerate(mats) if split_grp[m[5]]]
+        for i in ([split_idx[0], split_idx[len(split_idx) // 2], split_idx[-1]] if split_idx else []):
+            name, N, lo, hi, K, grp, w = mats[i]
+            if rank == 0:
+                x = groups[grp][0]
+                parts = []
+                for r in range(world):
+                    rlo, rhi = shard_rows(N, r, world)
+                    if rhi > rlo:
+                        raw = synth_dev(torch, dev, wtype, rhi - rlo, K, seed=shard_seed(i, r, grp))
+                        wr = tb.Weights(raw, wtype, rhi - rlo, K)
+                        o = torch.empty(1, rhi - rlo, device=dev)
+                        with torch.cuda.stream(stream):
+                            tb.mul_mat(wr, x, 1, o)
+                        stream.synchronize()
+                        parts.append(o.cpu().numpy()[0])
+                        wr.free()
+                full = np.concatenate(parts)
+                if pg is not None:
+                    got = pg.read(p2p_off[i], N)
+                else:
+                    gi = next(k for k, (_, idx) in enumerate(schedule) if i in idx)
+                    col = sum(max_shard(mats[j][1], world) for j in schedule[gi][1] if j < i)
+                    gg = gathered[gi].cpu().numpy()
+                    got = np.concatenate([gg[r, col: col + (shard_rows(N, r, world)[1] - shard_rows(N, r, world)[0])] for r in range(world)])
+                den = float(np.abs(full).max()) or 1.0
+                good = (not np.isnan(got).any()) and float(np.abs(got - full).max()) / den <= 1e-3
+                ok, checked = ok and good, checked + 1
+                if not good:
+                    sys.stderr.write(f"bench: PARITY MISMATCH on gathered output of {name}\n")
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.broadcast(flag, 0)
+        if int(flag.item()) != 1:
+            raise SystemExit("bench: gathered outputs differ from the unsharded product")
+        parity_checked = {"matrices": 3 if split_idx else 0, "rows": "all", "tolerance": 1e-3, "against": "the same matrices multiplied unsharded on rank 0"}
+
     log('capturing full step')
     run_full, graphed = capture(step)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     log('timing full step')
+    sampler.mark("step_a")
     ms_total = timed(run_full, args.steps, args.warmup)
     ms_per_step = ms_total / args.steps
     value = total_step_bytes / (ms_per_step * 1e-3) / 1e9
 
     log('roofline pass')
-    # ---- roofline: the decode GEMV kernel alone (no quantizers, no collectives)
-    run_gemv, _ = capture(lambda: step(with_gather=False, with_quant=False))
-    ms_gemv = timed(run_gemv, args.steps, args.warmup) / args.steps
-    n_gemv = len(schedule)
-    peak, peak_src = measured_peak()
-    achieved = step_bytes / (ms_gemv * 1e-3) / 1e9
-    # DRAM traffic per launch: ratio (dram read + write) / algorithmic bytes of the same kernel from the committed ncu --set full
-    # capture (profiles/r01_gemv_traffic.json), applied to this run's per-launch algorithmic bytes
+    peak, peak_src = peaks["hbm"]
+    if plan is not None:
+        # the plan kernel IS the step: one launch, quantization inside
+        ms_kernel, n_launch, kname = ms_per_step, 1, "plan_q4_0_kernel"
+    else:
+        run_gemv, _ = capture(lambda: step(with_gather=False, with_quant=False))
+        ms_kernel = timed(run_gemv, args.steps, args.warmup) / args.steps
+        n_launch, kname = len(schedule), {Q4_0: "gemv_q4_0_kernel", Q4_K: "gemv_q4_K_kernel", Q6_K: "gemv_q6_K_kernel"}[wtype]
+    sampler.mark("step_b")
+    achieved = step_bytes / (ms_kernel * 1e-3) / 1e9
+    # DRAM traffic per launch: (dram read + write) / algorithmic bytes of the same kernel from the committed ncu --set full capture,
+    # applied to this run's algorithmic bytes — derived, not measured in this run
     traffic, traffic_src = None, None
     try:
-        tj = json.loads((ROOT / "profiles" / "r01_gemv_traffic.json").read_text())
+        tj = json.loads((ROOT / "profiles" / ("r02_plan_traffic.json" if plan is not None else "r01_gemv_traffic.json")).read_text())
         if wtype == Q4_0:
-            traffic, traffic_src = tj["traffic_over_algorithmic"] * step_bytes / n_gemv, tj["source"]
+            traffic, traffic_src = tj["traffic_over_algorithmic"] * step_bytes / n_launch, tj["source"]
     except Exception:   # noqa: BLE001
         pass
-    roofline = {"bound": "hbm", "kernel": {Q4_0: "gemv_q4_0_kernel", Q4_K: "gemv_q4_K_kernel", Q6_K: "gemv_q6_K_kernel"}[wtype], "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": traffic, "traffic_source": traffic_src,
-                "launches_timed": n_gemv, "avg_launch_us": ms_gemv * 1e3 / n_gemv, "algorithmic_bytes_per_launch": step_bytes / n_gemv,
-                "frac_of_spec_8TBs": achieved / 8000.0}
+    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                "traffic": traffic, "traffic_derived": True, "traffic_source": traffic_src, "launches_timed": n_launch,
+                "avg_launch_us": ms_kernel * 1e3 / n_launch, "algorithmic_bytes_per_launch": step_bytes / n_launch,
+                "frac_of_spec_8TBs": achieved / SPEC_HBM_GBS}
     log('per-shape pass')
-    # per-shape view of the same kernel (BASELINE configs[1] names N=4096/14336/128256 at K=4096)
+    # per-shape view (BASELINE configs[1] names N=4096/14336/128256 at K=4096): every matrix of one shape, each its own dependent group
     per_shape = {}
     for shape in sorted({(hi - lo, K) for (_, N, lo, hi, K, g, w) in mats}):
         idx = [i for i, m in enumerate(mats) if (m[3] - m[2], m[4]) == shape]
-
-        def only(idx=idx):
-            for i in idx:
-                tb.mul_mat_acts(mats[i][6], groups[mats[i][5]][1], outs[i])
-        run_s, _ = capture(only)
+        if plan is not None:
+            sub = tb.Plan([{"w": [mats[i][6]], "out": [outs[i]], "x": groups[mats[i][5]][0]} for i in idx])
+            run_s = sub.run
+        else:
+            def only(idx=idx):
+                for i in idx:
+                    tb.mul_mat_acts(mats[i][6], groups[mats[i][5]][1], outs[i])
+            run_s, _ = capture(only)
         ms = timed(run_s, max(3, args.steps // 2), 2) / max(3, args.steps // 2)
         b = algorithmic_bytes(wtype, shape[0], shape[1]) * len(idx)
-        per_shape[f"N={shape[0]},K={shape[1]}"] = {"launches": len(idx), "us_per_launch": ms * 1e3 / len(idx), "GBps": b / (ms * 1e-3) / 1e9,
-                                                  "distinct_MB": b / 1e6}
+        per_shape[f"N={shape[0]},K={shape[1]}"] = {"matrices": len(idx), "us_per_matrix": ms * 1e3 / len(idx), "GBps": b / (ms * 1e-3) / 1e9,
+                                                  "frac": b / (ms * 1e-3) / 1e9 / peak, "distinct_MB": b / 1e6}
+        if plan is not None:
+            sub.free()
+    roofline["per_shape"] = per_shape
+
+    extra_clock_marks = {}
+    if world == 1 and rank == 0 and not args.no_extra:
+        log('prefill leg')
+        roofline["prefill"] = prefill_leg(torch, tb, dev, stream, sampler, peaks)
+        roofline["prefill_peak"] = {"bf16_tflops_sustained": peaks["tf_sustained"][0], "bf16_tflops_burst": peaks["tf_burst"][0], "spec": SPEC_BF16_TFLOPS,
+                                    "source": peaks["tf_sustained"][1], "includes": "activation quantize + fp16 prep + tcgen05 GEMM, back to back >= 1 s per point"}
+        log('mixmul leg')
+        roofline["mixmul"] = mixmul_leg(torch, tb, dev, stream)
+        roofline["quantizer"] = quantizer_leg(torch, tb, dev, stream, peak)
 
     log('e2e pass')
-    # ---- e2e: llamafile_sgemm() with HOST buffers (pinned), weights resident after the first call
+    # ---- e2e: llamafile_sgemm() with HOST buffers, weights registered as the immutable mmap'd range and resident after first use
     e2e = None
     if args.e2e:
-        try:
-            from oracle import binding as OB   # only used to pre-quantize the host activations once (checker-side prep)
-        except Exception:
-            OB = None
         vdt, vts = (Q8_0, 34) if wtype == Q4_0 else (15, 292)   # Q8_K activations for the k-quants
+        blck = TS_BLCK[wtype][1]
         hB, hC = [], []
         for i, (name, N, lo, hi, K, grp, w) in enumerate(mats):
             x = groups[grp][0].cpu().numpy()
             q = tb.quantize_row_q8_0(x[0]) if wtype == Q4_0 else tb.quantize_row_q8_K(x[0])
-            b = torch.from_numpy(q).pin_memory()
-            c = torch.empty(hi - lo, dtype=torch.float32).pin_memory()
+            b = torch.from_numpy(q)
+            c = torch.empty(hi - lo, dtype=torch.float32)
+            if args.e2e_pinned:
+                b, c = b.pin_memory(), c.pin_memory()
             hB.append(b); hC.append(c)
+        for raw in host_raw:
+            tb.register_weights(raw)
         kb = lambda K: K // blck   # noqa: E731
-
-        # the call a user makes is the C entry point itself: resolve the (fixed) pointers once so the timed loop is one
-        # foreign call per matmul, not numpy attribute look-ups
         from llamafile_b200.lib import lib as _lib
         sgemm = _lib().llamafile_sgemm
         calls = [(hi - lo, 1, kb(K), host_raw[i].ctypes.data, kb(K), hB[i].data_ptr(), kb(K), hC[i].data_ptr(), hi - lo, 0, 1, wtype, vdt, F32)
@@ -415,7 +614,7 @@ def run_b200_arm(args):
             for a in calls:
                 if not sgemm(*a):
                     raise SystemExit("bench: llamafile_sgemm returned false")
-        for _ in range(max(1, args.warmup)):
+        for _ in range(max(2, args.warmup)):
             host_step()
         if world > 1:
             dist.barrier()
@@ -430,47 +629,69 @@ def run_b200_arm(args):
             t = torch.tensor([dt], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX); dt = float(t.item())
         e2e = {"value": total_step_bytes / dt / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(sum(kb(m[4]) * vts for m in mats)),
                "d2h_bytes_per_step": int(sum((m[3] - m[2]) * 4 for m in mats)), "ms_per_step": dt * 1e3,
-               "api": "llamafile_sgemm(host A cached on device, pinned host B Q8_0, pinned host C), one blocking call per matmul"}
+               "api": "llamafile_sgemm(host A registered as immutable and resident on the device, host B Q8_0, host C; "
+                      + ("pinned" if args.e2e_pinned else "pageable, as stock ggml buffers are") + "), one blocking call per matmul"}
+        for raw in host_raw:
+            tb.unregister_weights(raw)
 
     log('done; assembling line')
     clocks = None
     if rank == 0:
         sampler.stop_flag = True
         sampler.join(timeout=2)
-        clocks = sampler.summary()
+        clocks = sampler.summary(sampler.marks.get("step_a", 0), sampler.marks.get("step_b"))
+        clocks["whole_run"] = sampler.summary()
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            v, info = reference_sample(args.workload, budget_s=10.0)
-            cpu_baseline = {"value": v, "unit": "GB/s", "cores": info["cores"], "kind": info["kind"], "sample": info["sample"]}
+            ref = ReferenceStep(args.workload, args.layers)
+            ref.step()
+            reps, t0 = 0, time.perf_counter()
+            while reps < 2 or time.perf_counter() - t0 < 10.0:
+                ref.step()
+                reps += 1
+            dt = (time.perf_counter() - t0) / reps
+            cpu_baseline = {"value": ref.bytes / dt / 1e9, "unit": "GB/s", "cores": ref.nth if ref.kind == "reference" else (os.cpu_count() or 1),
+                            "kind": ref.kind, "sample": ref.describe(reps)}
+            del ref
         except Exception as e:   # noqa: BLE001
             cpu_baseline = {"value": None, "unit": "GB/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
 
-    if rank == 0:
-        line = {"metric": {Q4_0: "Q4_0 decode GEMV GB/s (Llama-3-8B shapes)", Q4_K: "Q4_K decode GEMV GB/s (Llama-3-70B shapes)",
-                           Q6_K: "Q6_K decode GEMV GB/s (Llama-3-8B shapes)"}[wtype],
-                "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
-                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int8 dp4a block dots, fp32 accumulate",
-                "data": "synthetic",
-                "config": {"workload": args.workload, "tokens": 1, "layers": layers, "matmuls_per_step": len(mats), "launches_per_step": len(schedule),
-                           "weight_GB_per_step": total_step_bytes / 1e9, "l2": "distinct weights per step exceed L2 (126 MB) 30x; no flush needed",
-                           "cuda_graph": graphed, "split_groups": sum(1 for g2, _ in schedule if split_grp[g2]), "replicated_groups": sum(1 for g2, _ in schedule if not split_grp[g2]),
-                           "split_min_mb": args.split_min_mb,
-                           "parallelism": (f"row-shard x{world} (launch groups >= {args.split_min_mb} MB; smaller ones replicated) + " + ("fused all-gather (peer stores over NVLink + flag barrier per launch group)" if pg is not None else "NCCL all-gather per launch group")) if world > 1 else "single GPU",
-                           "decode_tokens_per_s": 1e3 / ms_per_step},
-                "roofline": roofline, "per_shape": per_shape, "cpu_baseline": cpu_baseline, "e2e": e2e,
-                "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks}
+    timed_out = pg is not None and pg.timed_out()
+    if plan is not None and plan.status() != 0:
+        timed_out = True
+    if rank == 0 and not timed_out:
+        cfg = workload_config(args.workload, args.layers)
+        cfg.update({"launch_groups_per_step": len(schedule), "launches_per_step": int(launches_per_step),
+                    "decode": ("plan: one persistent kernel per step (per-warp TMA rings, in-kernel Q8_0 quantization, grid barrier between groups)" if plan is not None
+                               else "oneshot: one quantizer + one GEMV launch per group, CUDA graph"),
+                    "cuda_graph": graphed, "split_groups": sum(1 for g2, _ in schedule if split_grp[g2]),
+                    "replicated_groups": sum(1 for g2, _ in schedule if not split_grp[g2]), "split_min_mb": args.split_min_mb,
+                    "parallelism": (f"row-shard x{world} (launch groups >= {args.split_min_mb} MB; smaller ones replicated) + " + ("fused all-gather (peer stores over NVLink + flag barrier per launch group); data plane is not NCCL" if pg is not None else "NCCL all-gather per launch group")) if world > 1 else "single GPU",
+                    "decode_tokens_per_s": 1e3 / ms_per_step})
+        line = {"metric": METRIC[wtype], "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "int8 dp4a block dots, fp32 accumulate", "data": "synthetic", "config": cfg,
+                "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
+                "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks, "parity_checked": parity_checked}
         real_stdout.write(json.dumps(line) + "\n")
         real_stdout.flush()
-    if pg is not None and pg.timed_out():
-        sys.stderr.write("bench: WARNING peer barrier timed out\n")
     log("line printed; leaving")
+    # orderly exit (the driver's exit hook records which native libraries this process loaded): graphs first, then the
+    # plan / peer group, then the process group
+    graphs.clear()
+    del run_full
+    if plan is not None:
+        plan.free()
+    torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
+        dist.destroy_process_group()
     sys.stdout.flush()
     sys.stderr.flush()
-    os._exit(0)   # skip interpreter teardown: CUDA graphs holding NCCL nodes + process-group destruction can stall at exit
+    if timed_out:
+        raise SystemExit("bench: a cross-GPU / grid barrier timed out; no result line printed")
 
 
 def main():
@@ -480,12 +701,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="llama3-8b-q4_0-decode", choices=sorted(WORKLOADS))
+    ap.add_argument("--decode", default="plan", choices=["plan", "oneshot"], help="plan = one persistent kernel per step (Q4_0, one GPU); oneshot = a launch per group")
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (debug)")
     ap.add_argument("--no-e2e", dest="e2e", action="store_false")
+    ap.add_argument("--e2e-pinned", action="store_true", help="e2e with pinned host B/C (default: pageable, as stock ggml allocates)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the prefill / mixmul / quantizer legs (roofline.prefill etc.)")
     ap.add_argument("--split-min-mb", type=float, default=80.0,
-                    help="N>1: launch groups with fewer weight MB are computed on every rank instead of sharded. Break-even: splitting g ways saves "
-                         "bytes*(1-1/g)/6.5 TB/s and costs one kernel->barrier->kernel chain (~6 us measured): 78 MB at g=2, 45 MB at g=8")
+                    help="N>1: launch groups with fewer weight MB are computed on every rank instead of sharded")
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="multi-GPU output exchange")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay (debug)")
     args = ap.parse_args()

@@ -93,8 +93,13 @@ typedef struct {
  * Anything else returns false before touching C ("not handled, caller falls back"), never an error.
  * Threading contract: ggml calls this from all nth worker threads. Thread 0 does the whole job
  * on the GPU and returns after C is complete; threads ith != 0 return true immediately and rely on
- * the caller's barrier after the op (ggml.c.patch:2316), as the CPU kernels do for their own tiles.
- * A (the mmap'd weights) is uploaded once and cached by (A, m, k, lda, Atype). */
+ * the caller's barrier after the op (ggml.c.patch:2316), as the CPU kernels do for their own tiles. Because the other
+ * threads have answered before thread 0 touches the GPU, the true/false answer is a pure function of the arguments plus a
+ * sticky "module disabled" flag: a runtime failure on thread 0 is fatal for the call in flight (logged, abort() unless
+ * TB200_ABORT_ON_ERROR=0 or nth == 1) and every later call returns false on every thread.
+ * A is uploaded once and kept ONLY when it lies inside a range registered with tb200_register_weights() (the mmap'd
+ * GGUF file, immutable); any other A (KV cache, scratch) is uploaded on every call and dropped after it.
+ * One host-pointer call runs at a time per device (internal lock); callers on different devices run concurrently. */
 TB200_API bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void *B, long ldb,
                                void *C, long ldc, int ith, int nth, int Atype, int Btype, int Ctype);
 
@@ -116,6 +121,15 @@ TB200_API size_t llamafile_mixmul_needs(const struct ggml_tensor *weights, const
 TB200_API bool llamafile_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, const void *A,
                                     const void *B, float *C, long nb1, long nb2, const void *vrow_mapping,
                                     int ith, int nth);
+
+/* Declares host range [base, base+bytes) immutable until tb200_unregister_weights(base): weight matrices inside it are
+ * uploaded (and repacked) once, keyed by (A, m, k, lda, Atype), and stay resident. llamafile would call this right after
+ * mmap()ing the GGUF file (llama.cpp/src/llama.cpp llama_mmap) and unregister before munmap. Unregistering frees the
+ * resident copies made from the range. */
+TB200_API int tb200_register_weights(const void *base, size_t bytes);
+TB200_API int tb200_unregister_weights(const void *base);
+TB200_API void tb200_weights_cache_clear(void);      /* drops every resident copy (ranges stay registered) */
+TB200_API size_t tb200_weights_cache_bytes(void);    /* HBM bytes held by resident copies */
 
 /* from_float of the vec_dot types (ggml.c type_traits: quantize_row_q8_0 ggml-quants.c:866/940-990,
  * quantize_row_q8_K :3593-3645, ggml_fp32_to_fp16_row). Host in, host out, bit-exact. */
@@ -192,6 +206,36 @@ TB200_API int tb200_acts_quantize(tb200_acts *a, const float *x, long ldx, long 
 TB200_API int tb200_mul_mat_acts(const tb200_weights *w, const tb200_acts *a, float *out, long ldo);
 TB200_API int tb200_mul_mat_acts_multi(int n, const tb200_weights *const *w, const tb200_acts *a, float *const *out, const long *ldo);
 TB200_API void tb200_acts_free(tb200_acts *a);
+
+/* Decode plan: a whole sequence of one-token matmul groups (a decode step: wq/wk/wv, wo, gate/up, down per layer, then the
+ * vocabulary matrix) as ONE persistent kernel, one CTA per SM, the weight stream kept in flight across group boundaries by
+ * per-warp TMA rings in shared memory (tb200_plan.cu). Group g starts when group g-1 is complete on every SM (stream-order
+ * semantics: its input may be any function of earlier outputs). Each group first turns its fp32 input into the Q8_0
+ * activations the reference's from_float would produce (ggml.c:12345-12373), optionally through one of the matmul's
+ * neighbours in the reference graph (llama.cpp/src/llama.cpp:8099-8225 llm_build_norm / llm_build_ffn):
+ *   TB200_PLAN_QUANT    x                                         -> quantize_row_q8_0 (bit-exact)
+ *   TB200_PLAN_RMSNORM  x * 1/sqrt(mean(x^2) + eps) * norm_weight -> quantize   (ggml_rms_norm + ggml_mul)
+ *   TB200_PLAN_SWIGLU   silu(x) * x2                              -> quantize   (ggml_silu + ggml_mul; x = gate, x2 = up)
+ * and every matrix may add a residual on the way out (out = W.x + residual, ggml_add). All matrices Q4_0, K % 256 == 0,
+ * one token. Buffers must stay valid while the plan exists; weights, inputs and outputs may be shared between groups. */
+enum { TB200_PLAN_QUANT = 0, TB200_PLAN_RMSNORM = 1, TB200_PLAN_SWIGLU = 2 };
+typedef struct {
+    int n;                                             /* matrices that share the input, <= TB200_GEMV_MAX_MATS */
+    int prologue;                                      /* TB200_PLAN_* */
+    const tb200_weights *w[TB200_GEMV_MAX_MATS];
+    float *out[TB200_GEMV_MAX_MATS];                   /* fp32 [rows] */
+    const float *residual[TB200_GEMV_MAX_MATS];        /* optional fp32 [rows] */
+    const float *x;                                    /* fp32 [k], 16-byte aligned */
+    const float *x2;                                   /* SWIGLU: fp32 [k] */
+    const float *norm_weight;                          /* RMSNORM: fp32 [k] */
+    float eps;                                         /* RMSNORM */
+} tb200_plan_group;
+typedef struct tb200_plan tb200_plan;
+TB200_API tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups);
+TB200_API int tb200_plan_run(tb200_plan *p, int first, int count);   /* enqueue groups [first, first+count) as one launch */
+TB200_API int tb200_plan_status(tb200_plan *p);   /* 0, or non-zero when a launch gave up waiting (its results are undefined; tb200_plan_reset) */
+TB200_API int tb200_plan_reset(tb200_plan *p);
+TB200_API void tb200_plan_free(tb200_plan *p);
 
 /* Multi-GPU, one process per GPU: weights row-sharded (each rank uploads its row slice), the all-gather of the output
  * slices fused into the kernels as peer stores over NVLink (decode: the GEMV epilogue, one 64-byte segment per CTA and

@@ -9,9 +9,13 @@
 #include <string.h>
 #include <time.h>
 
+#include <pthread.h>
+
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <tuple>
+#include <vector>
 
 #include "tb200_common.cuh"
 
@@ -24,6 +28,35 @@ namespace {
 
 std::mutex g_cache_mu;
 std::map<std::tuple<const void *, long, long, size_t, int>, tb200_weights *> g_cache;
+// Host ranges the caller has declared immutable for the lifetime of the registration (the mmap'd GGUF file,
+// tb200_register_weights): only matrices lying inside one are uploaded once and kept. Any other A — the F16 or quantized
+// KV cache that ggml also sends through llamafile_sgemm (llama.cpp/src/llama.cpp:8387/8430), scratch tensors — is
+// uploaded on every call and dropped after it, because its bytes may change between calls at the same address.
+std::vector<std::pair<const char *, size_t>> g_ranges;
+
+// Sticky failure state. The reference's true/false answer depends only on the arguments, so every ggml worker gets the
+// same one; here threads ith != 0 return true before thread 0 has touched the GPU. A runtime failure on thread 0
+// (allocation, launch, CUDA error) therefore cannot be turned into "false" for everybody after the fact: it is fatal for
+// the call in flight, like the reference's asserts (tinyblas_cpu_sgemm.inc:277-284) — logged and abort()ed unless
+// TB200_ABORT_ON_ERROR=0 — and the module answers false on EVERY thread from then on.
+std::atomic<bool> g_disabled{false};
+bool runtime_failure(const char *where, int nth) {
+    g_disabled.store(true, std::memory_order_release);
+    fprintf(stderr, "tinyblas_b200: runtime failure in %s: %s — module disabled, later calls return false on every thread\n", where, tb200_last_error());
+    static const bool hard = [] { const char *v = getenv("TB200_ABORT_ON_ERROR"); return !(v && *v == '0'); }();
+    if (hard && nth > 1) abort();   // with one caller thread nobody has answered true yet: "false" is still a consistent answer
+    return false;
+}
+
+// One host-pointer call at a time per device: the lane (stream, staging pages, graphs), the io buffer and the context's
+// stream swap below are per-device state. The lock is only taken by the thread that does the work (ith == 0); ggml
+// workers may be pthread_cancel()led, so cancellation is held off while the lock is owned.
+std::mutex g_dev_mu[16];
+struct DeviceLock {
+    std::mutex &mu; int old_state = 0;
+    explicit DeviceLock(int device) : mu(g_dev_mu[device & 15]) { pthread_setcancelstate(PTHREAD_CANCEL_DISABLE, &old_state); mu.lock(); }
+    ~DeviceLock() { mu.unlock(); pthread_setcancelstate(old_state, nullptr); }
+};
 
 // device staging for host-pointer calls, separate from the kernels' scratch arena
 struct Io { void *p = nullptr; size_t cap = 0; };
@@ -235,8 +268,16 @@ int lane_issue(tb200_ctx *c, HostLane &L, const LaneKey &k, size_t b_bytes) {
     return TB200_OK;
 }
 
-tb200_weights *cached_weights(const void *A, int type, long rows, long k, size_t row_stride) {
+// Resident copy of A. *transient is set when A lies outside every registered range: the caller frees the copy after the call.
+tb200_weights *cached_weights(const void *A, int type, long rows, long k, size_t row_stride, bool *transient) {
     std::lock_guard<std::mutex> lk(g_cache_mu);
+    const size_t rb = tb200_gguf_row_bytes(type, k);
+    const size_t span = rows ? (size_t)(rows - 1) * (row_stride ? row_stride : rb) + rb : 0;
+    bool inside = false;
+    for (const auto &r : g_ranges)
+        if ((const char *)A >= r.first && (const char *)A + span <= r.first + r.second) { inside = true; break; }
+    *transient = !inside;
+    if (!inside) return tb200_weights_upload(A, type, rows, k, row_stride);
     const auto key = std::make_tuple(A, rows, k, row_stride, type);
     auto it = g_cache.find(key);
     if (it != g_cache.end()) return it->second;
@@ -244,6 +285,10 @@ tb200_weights *cached_weights(const void *A, int type, long rows, long k, size_t
     if (w) g_cache[key] = w;
     return w;
 }
+struct WeightsRef {   // frees a transient copy when the call ends
+    tb200_weights *w = nullptr; bool transient = false;
+    ~WeightsRef() { if (w && transient) tb200_weights_free(w); }
+};
 
 int blck(int type) { return (tb200_is_kquant(type) || type == TB200_TYPE_Q8_K) ? QK_K : (type == TB200_TYPE_Q4_0 || type == TB200_TYPE_Q8_0) ? QK : 1; }
 size_t tsize(int type) { return tb200_gguf_row_bytes(type, blck(type)); }
@@ -252,14 +297,47 @@ size_t tsize(int type) { return tb200_gguf_row_bytes(type, blck(type)); }
 
 extern "C" {
 
-TB200_API void tb200_weights_cache_clear(void) {
-    std::lock_guard<std::mutex> lk(g_cache_mu);
+static void drop_cached_locked(const char *lo, const char *hi) {   // g_cache_mu held; nullptr range = everything
     for (HostLane &L : g_lane) {   // captured graphs hold weight pointers
         if (L.stream) cudaStreamSynchronize(L.stream);
         lane_drop_graphs(L);
     }
-    for (auto &kv : g_cache) tb200_weights_free(kv.second);
-    g_cache.clear();
+    for (auto it = g_cache.begin(); it != g_cache.end();) {
+        const char *a = (const char *)std::get<0>(it->first);
+        if (!lo || (a >= lo && a < hi)) { tb200_weights_free(it->second); it = g_cache.erase(it); }
+        else ++it;
+    }
+}
+
+void tb200_weights_cache_clear(void) {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    drop_cached_locked(nullptr, nullptr);
+}
+
+int tb200_register_weights(const void *base, size_t bytes) {
+    if (!base || !bytes) { tb200_set_error("register_weights: empty range"); return TB200_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    g_ranges.emplace_back((const char *)base, bytes);
+    return TB200_OK;
+}
+
+int tb200_unregister_weights(const void *base) {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    for (size_t i = 0; i < g_ranges.size(); ++i)
+        if (g_ranges[i].first == (const char *)base) {
+            drop_cached_locked(g_ranges[i].first, g_ranges[i].first + g_ranges[i].second);
+            g_ranges.erase(g_ranges.begin() + i);
+            return TB200_OK;
+        }
+    tb200_set_error("unregister_weights: range not registered");
+    return TB200_ERR_INVALID;
+}
+
+size_t tb200_weights_cache_bytes(void) {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    size_t total = 0;
+    for (auto &kv : g_cache) total += kv.second->bytes;
+    return total;
 }
 
 bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void *B, long ldb, void *C, long ldc, int ith, int nth,
@@ -267,27 +345,31 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
     // the reference asserts these (tinyblas_cpu_sgemm.inc:277-284); a violated precondition is "not handled"
     if (m < 0 || n < 0 || k < 0 || lda < k || ldb < k || ldc < m || nth <= 0 || ith < 0 || ith >= nth) return false;
     if (!tb200_serviced(Atype, Btype, Ctype, n)) return false;
+    if (g_disabled.load(std::memory_order_acquire)) return false;   // same answer on every thread (see g_disabled)
     tb200_ctx *c = tb200_get_ctx();
     if (!c) return false;
     if (ith != 0) return true;   // thread 0 owns the whole job; see the threading contract in the header
     if (m == 0 || n == 0) return true;
+    DeviceLock lock(c->device);
     const long ke = k * blck(Atype);
     // iqk (Q4_0, Q4_K) takes rows ggml_row_size apart and ignores lda/ldb (iqk_mul_mat.inc:191-199); tinyBLAS honours them
     const bool iqk = Atype == TB200_TYPE_Q4_0 || tb200_is_kquant(Atype);
     const size_t a_stride = iqk ? tb200_gguf_row_bytes(Atype, ke) : (size_t)lda * tsize(Atype);
     const long ldb_eff = iqk ? k : ldb;
-    tb200_weights *w = cached_weights(A, Atype, m, ke, a_stride);
-    if (!w) return false;
+    WeightsRef wr;
+    wr.w = cached_weights(A, Atype, m, ke, a_stride, &wr.transient);
+    tb200_weights *w = wr.w;
+    if (!w) return runtime_failure("llamafile_sgemm (weight upload)", nth);
     const size_t b_bytes = ((size_t)(n - 1) * ldb_eff + k) * tsize(Btype), c_bytes = (size_t)n * m * 4;
     if (n <= TB200_GEMV_MAX_TOKENS && lane_enabled()) {
         // decode lane (see HostLane)
         const bool tr = trace_enabled();
         const double t0 = tr ? now_us() : 0;
         HostLane &L = g_lane[c->device];
-        if (!lane_init(L)) return false;
+        if (!lane_init(L)) return runtime_failure("llamafile_sgemm (lane init)", nth);
         LaneKey key = {w, n, Btype, pinned_alias(B), nullptr, ldb_eff, ldc, nullptr};
         if (!key.dB || (Atype == TB200_TYPE_F16 && ((uintptr_t)key.dB & 15))) {   // the fp16/f32 stage copy moves 16-byte words
-            if (!lane_reserve_host(L, &L.in, &L.in_cap, b_bytes)) return false;
+            if (!lane_reserve_host(L, &L.in, &L.in_cap, b_bytes)) return runtime_failure("llamafile_sgemm (staging)", nth);
             memcpy(L.in, B, b_bytes);
             key.dB = L.in;
         }
@@ -295,32 +377,33 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
         if (c_bytes <= lane_direct_bytes()) {   // kernels store C over PCIe
             key.dC = pinC;
             if (!key.dC) {
-                if (!lane_reserve_host(L, &L.out, &L.out_cap, c_bytes)) return false;
+                if (!lane_reserve_host(L, &L.out, &L.out_cap, c_bytes)) return runtime_failure("llamafile_sgemm (staging)", nth);
                 key.dC = L.out, key.ldo = m;
             }
         } else {                             // HBM, then one D2H transfer into pinned memory
-            if (!lane_reserve_dev(L, &L.dout, &L.dout_cap, c_bytes)) return false;
+            if (!lane_reserve_dev(L, &L.dout, &L.dout_cap, c_bytes)) return runtime_failure("llamafile_sgemm (staging)", nth);
             key.dC = L.dout, key.ldo = m;
             key.h_dst = (pinC && (ldc == m || n == 1)) ? (void *)C : nullptr;
             if (!key.h_dst) {
-                if (!lane_reserve_host(L, &L.out, &L.out_cap, c_bytes)) return false;
+                if (!lane_reserve_host(L, &L.out, &L.out_cap, c_bytes)) return runtime_failure("llamafile_sgemm (staging)", nth);
                 key.h_dst = L.out;
             }
         }
         const size_t act_bytes = Atype == TB200_TYPE_F16 ? up256(b_bytes) : up256((size_t)n * ke) + up256((size_t)n * (ke / QK) * 8);
-        if (!lane_reserve_dev(L, &L.dact, &L.dact_cap, act_bytes)) return false;
+        if (!lane_reserve_dev(L, &L.dact, &L.dact_cap, act_bytes)) return runtime_failure("llamafile_sgemm (staging)", nth);
         const double t1 = tr ? now_us() : 0;
 
         const uint32_t seq = ++L.seq;
         bool ok = true;
-        auto it = lane_graphs_enabled() ? L.graphs.find(key) : L.graphs.end();
+        const bool graphs = lane_graphs_enabled() && !wr.transient;   // a transient copy is gone after this call: nothing to replay
+        auto it = graphs ? L.graphs.find(key) : L.graphs.end();
         if (it != L.graphs.end() && it->second) {
             ok = cudaGraphLaunch(it->second, L.stream) == cudaSuccess;
             if (tr) ++g_trace.replays;
         } else {
             cudaStream_t user = c->stream;
             c->stream = L.stream;
-            const bool capture = lane_graphs_enabled() && it != L.graphs.end();   // second sighting: kernel attributes are set, buffers sized
+            const bool capture = graphs && it != L.graphs.end();   // second sighting: kernel attributes are set, buffers sized
             if (capture) ok = cudaStreamBeginCapture(L.stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
             if (ok) ok = lane_issue(c, L, key, b_bytes) == TB200_OK;
             if (capture) {
@@ -330,7 +413,7 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
                 ok = ok && ended && cudaGraphInstantiate(&ex, g, 0) == cudaSuccess;
                 if (g) cudaGraphDestroy(g);
                 if (ok) { it->second = ex; ok = cudaGraphLaunch(ex, L.stream) == cudaSuccess; }
-            } else if (ok && lane_graphs_enabled()) L.graphs[key] = nullptr;
+            } else if (ok && graphs) L.graphs[key] = nullptr;
             c->stream = user;
         }
         if (!ok) {
@@ -338,10 +421,10 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
             cudaStreamSynchronize(L.stream);
             // resynchronise the host mirror with the device counter so later calls keep working
             cudaMemcpy(&L.seq, L.dcount, 4, cudaMemcpyDeviceToHost);
-            return false;
+            return runtime_failure("llamafile_sgemm (lane launch)", nth);
         }
         const double t2 = tr ? now_us() : 0;
-        if (!lane_wait(L, seq)) return false;
+        if (!lane_wait(L, seq)) return runtime_failure("llamafile_sgemm (lane wait)", nth);
         const double t3 = tr ? now_us() : 0;
         const float *src = key.h_dst ? (const float *)key.h_dst : (const float *)key.dC;
         if ((const void *)src == (const void *)L.out)
@@ -356,12 +439,14 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
         return true;
     }
     uint8_t *io = (uint8_t *)io_buffer(c, up256(b_bytes) + c_bytes);
-    if (!io) return false;
+    if (!io) return runtime_failure("llamafile_sgemm (io buffer)", nth);
     float *dC = (float *)(io + up256(b_bytes));
-    if (cudaMemcpyAsync(io, B, b_bytes, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) { cudaGetLastError(); return false; }
-    if (tb200_sgemm_dev(w, n, io, ldb_eff, Btype, dC, m) != TB200_OK) return false;   // ldb: elements for F16/F32, blocks for quants
-    if (cudaMemcpy2DAsync(C, (size_t)ldc * 4, dC, (size_t)m * 4, (size_t)m * 4, (size_t)n, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) { cudaGetLastError(); return false; }
-    return cudaStreamSynchronize(c->stream) == cudaSuccess;
+    bool ok = cudaMemcpyAsync(io, B, b_bytes, cudaMemcpyHostToDevice, c->stream) == cudaSuccess;
+    ok = ok && tb200_sgemm_dev(w, n, io, ldb_eff, Btype, dC, m) == TB200_OK;   // ldb: elements for F16/F32, blocks for quants
+    ok = ok && cudaMemcpy2DAsync(C, (size_t)ldc * 4, dC, (size_t)m * 4, (size_t)m * 4, (size_t)n, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+    ok = cudaStreamSynchronize(c->stream) == cudaSuccess && ok;
+    if (!ok) { cudaGetLastError(); return runtime_failure("llamafile_sgemm", nth); }
+    return true;
 }
 
 // llamafile/tinyblas_cpu_mixmul.inc:97-111 + tinyblas_cpu_mixmul_amd_avx.cpp:8-18 (arena arithmetic only)
@@ -381,6 +466,22 @@ size_t llamafile_mixmul_needs(const struct ggml_tensor *weights_, const struct g
         !alloc(8, 8 * experts))
         return 0;
     return (wdata_aligned - wdata) + allocated;
+}
+
+// A strided host tensor [inner bytes] x [d1 rows, nb1 apart] x [d2 slabs, nb2 apart] <-> a dense device block, with as few
+// transfers as the strides allow: ONE 2-D copy when the slabs continue the row pitch (nb2 == d1*nb1, the layout ggml
+// gives contiguous and row-padded tensors), else one 2-D copy per slab.
+static bool copy_3d(void *dev, const void *host, size_t inner, long d1, size_t nb1, long d2, size_t nb2, bool to_device, cudaStream_t st) {
+    const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+    auto copy2d = [&](char *d, const char *h, long rows) {
+        return (to_device ? cudaMemcpy2DAsync(d, inner, h, nb1, inner, (size_t)rows, kind, st)
+                          : cudaMemcpy2DAsync((void *)h, nb1, d, inner, inner, (size_t)rows, kind, st)) == cudaSuccess;
+    };
+    if (d1 == 1 && d2 > 1) return copy_3d(dev, host, inner, d2, nb2, 1, 0, to_device, st);
+    if (d2 <= 1 || nb2 == (size_t)d1 * nb1) return copy2d((char *)dev, (const char *)host, d1 * (d2 > 0 ? d2 : 0));
+    for (long s = 0; s < d2; ++s)
+        if (!copy2d((char *)dev + (size_t)s * d1 * inner, (const char *)host + (size_t)s * nb2, d1)) return false;
+    return true;
 }
 
 bool llamafile_mixmul(const struct ggml_compute_params *params_, const struct ggml_tensor *weights_, const struct ggml_tensor *thought_,
@@ -409,45 +510,40 @@ bool llamafile_mixmul(const struct ggml_compute_params *params_, const struct gg
     if (x->type != TB200_TYPE_F32) return false;   // pre-converted thought (Q8_0/F16) is never produced by ggml for this op
     if (cols % (w->type == TB200_TYPE_F16 ? 16 : 32)) return false;                        // :273
     if (w->nb[2] != (size_t)rows * w->nb[1]) return false;                                 // experts must be stacked
+    if (pl->nb[0] != 4) return false;
+    if (g_disabled.load(std::memory_order_acquire)) return false;
     tb200_ctx *c = tb200_get_ctx();
     if (!c) return false;
     if (params->ith != 0) return true;
     if (tokens == 0 || rows == 0) return true;
-    tb200_weights *dw = cached_weights(w->data, w->type, rows * experts, cols, w->nb[1]);
-    if (!dw) return false;
+    const int nth = params->nth;
+    DeviceLock lock(c->device);
+    WeightsRef wr;
+    wr.w = cached_weights(w->data, w->type, rows * experts, cols, w->nb[1], &wr.transient);
+    tb200_weights *dw = wr.w;
+    if (!dw) return runtime_failure("llamafile_mixmul (weight upload)", nth);
     const size_t x_bytes = (size_t)tokens * tasks * cols * 4, p_bytes = (size_t)tokens * thinkers * 4, o_bytes = (size_t)tokens * thinkers * rows * 4;
     uint8_t *io = (uint8_t *)io_buffer(c, up256(x_bytes) + up256(p_bytes) + o_bytes);
-    if (!io) return false;
+    if (!io) return runtime_failure("llamafile_mixmul (io buffer)", nth);
     float *dx = (float *)io;
     int32_t *dp = (int32_t *)(io + up256(x_bytes));
     float *dout = (float *)(io + up256(x_bytes) + up256(p_bytes));
-    bool ok = true;
-    // gather the (possibly strided) host tensors into contiguous device buffers
-    for (long t = 0; t < tokens && ok; ++t)
-        ok = cudaMemcpy2DAsync(dx + (size_t)t * tasks * cols, (size_t)cols * 4, (const char *)x->data + t * x->nb[2], x->nb[1], (size_t)cols * 4,
-                               (size_t)tasks, cudaMemcpyHostToDevice, c->stream) == cudaSuccess;
+    // the (possibly strided) host tensors <-> dense device blocks: one transfer each when the strides allow (copy_3d)
+    bool ok = copy_3d(dx, x->data, (size_t)cols * 4, tasks, x->nb[1], tokens, x->nb[2], true, c->stream);
+    ok = ok && copy_3d(dp, pl->data, (size_t)thinkers * 4, tokens, pl->nb[1], 1, 0, true, c->stream);
     bool all_valid = true;
-    if (ok) {
-        if (pl->nb[0] == 4) {
-            ok = cudaMemcpy2DAsync(dp, (size_t)thinkers * 4, pl->data, pl->nb[1], (size_t)thinkers * 4, (size_t)tokens, cudaMemcpyHostToDevice, c->stream) == cudaSuccess;
-        } else ok = false;
-        for (long t = 0; t < tokens; ++t)
-            for (long th = 0; th < thinkers; ++th) {
-                const int32_t e = *(const int32_t *)((const char *)pl->data + t * pl->nb[1] + th * pl->nb[0]);
-                if (e < 0 || e >= experts) all_valid = false;
-            }
-    }
+    for (long t = 0; t < tokens && all_valid; ++t)
+        for (long th = 0; th < thinkers; ++th) {
+            const int32_t e = *(const int32_t *)((const char *)pl->data + t * pl->nb[1] + th * pl->nb[0]);
+            if (e < 0 || e >= experts) { all_valid = false; break; }
+        }
     // rows naming no expert stay untouched in the reference: carry the caller's bytes through the device copy
-    if (ok && !all_valid)
-        for (long t = 0; t < tokens && ok; ++t)
-            ok = cudaMemcpy2DAsync(dout + (size_t)t * thinkers * rows, (size_t)rows * 4, (const char *)out->data + t * out->nb[2], out->nb[1],
-                                   (size_t)rows * 4, (size_t)thinkers, cudaMemcpyHostToDevice, c->stream) == cudaSuccess;
+    if (ok && !all_valid) ok = copy_3d(dout, out->data, (size_t)rows * 4, thinkers, out->nb[1], tokens, out->nb[2], true, c->stream);
     if (ok) ok = tb200_mixmul_dev(dw, (int)experts, dx, (int)tasks, dp, (int)thinkers, tokens, dout) == TB200_OK;
-    for (long t = 0; t < tokens && ok; ++t)
-        ok = cudaMemcpy2DAsync((char *)out->data + t * out->nb[2], out->nb[1], dout + (size_t)t * thinkers * rows, (size_t)rows * 4,
-                               (size_t)rows * 4, (size_t)thinkers, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
-    if (!ok) cudaGetLastError();
-    return cudaStreamSynchronize(c->stream) == cudaSuccess && ok;
+    ok = ok && copy_3d(dout, out->data, (size_t)rows * 4, thinkers, out->nb[1], tokens, out->nb[2], false, c->stream);
+    ok = cudaStreamSynchronize(c->stream) == cudaSuccess && ok;
+    if (!ok) { cudaGetLastError(); return runtime_failure("llamafile_mixmul", nth); }
+    return true;
 }
 
 // iqk_mul_mat_moe (llamafile/iqk_mul_mat.inc:204-221): A = one expert's Nx rows, B = all quantized rows
@@ -456,37 +552,48 @@ bool llamafile_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, cons
                           const void *vrow_mapping, int ith, int nth) {
     if (!tb200_is_kquant(typeA) && typeA != TB200_TYPE_Q4_0) return false;   // the other iqk types are outside this module
     if (!vrow_mapping || Nx < 0 || Ny < 0 || ne11 <= 0 || nth <= 0 || ith < 0 || ith >= nth || ne00 % blck(typeA)) return false;
+    if (g_disabled.load(std::memory_order_acquire)) return false;
     tb200_ctx *c = tb200_get_ctx();
     if (!c) return false;
     if (ith != 0) return true;
     if (Nx == 0 || Ny == 0) return true;
+    DeviceLock lock(c->device);
     const int Btype = tb200_is_kquant(typeA) ? TB200_TYPE_Q8_K : TB200_TYPE_Q8_0;
-    tb200_weights *w = cached_weights(A, typeA, Nx, ne00, 0);
-    if (!w) return false;
+    WeightsRef wr;
+    wr.w = cached_weights(A, typeA, Nx, ne00, 0, &wr.transient);
+    tb200_weights *w = wr.w;
+    if (!w) return runtime_failure("llamafile_mixmul_iqk (weight upload)", nth);
     const int32_t *rm = (const int32_t *)vrow_mapping;
-    const size_t row_b = tb200_gguf_row_bytes(Btype, ne00);
-    // gather the Ny mapped B rows into a contiguous staging block, run one dense sgemm, scatter rows of C back
-    uint8_t *io = (uint8_t *)io_buffer(c, up256(row_b * Ny) + (size_t)Ny * Nx * 4);
-    if (!io) return false;
-    float *dC = (float *)(io + up256(row_b * Ny));
-    bool ok = true;
-    for (long y = 0; y < Ny && ok; ++y) {
+    const size_t row_b = tb200_gguf_row_bytes(Btype, ne00), in_b = up256(row_b * Ny), out_b = (size_t)Ny * Nx * 4;
+    // The mapped B rows are gathered on the host into ONE pinned staging block (plain memcpy, no driver call per row), go
+    // to the device in one transfer, one dense sgemm runs, and the result comes back in one transfer and is scattered to
+    // the caller's rows the same way. (The first version issued a pageable cudaMemcpyAsync per row each way: > 1000 driver
+    // calls around a 300 us kernel at Ny = 512.)
+    HostLane &L = g_lane[c->device];
+    if (!lane_reserve_host(L, &L.in, &L.in_cap, in_b) || !lane_reserve_host(L, &L.out, &L.out_cap, out_b))
+        return runtime_failure("llamafile_mixmul_iqk (staging)", nth);
+    uint8_t *io = (uint8_t *)io_buffer(c, in_b + out_b);
+    if (!io) return runtime_failure("llamafile_mixmul_iqk (io buffer)", nth);
+    float *dC = (float *)(io + in_b);
+    for (long y = 0; y < Ny; ++y) {
         const long brow = (long)(rm[2 * y] % ne11) + (long)rm[2 * y + 1] * ne11;
-        ok = cudaMemcpyAsync(io + y * row_b, (const char *)B + brow * row_b, row_b, cudaMemcpyHostToDevice, c->stream) == cudaSuccess;
+        memcpy(L.in + y * row_b, (const char *)B + brow * row_b, row_b);
     }
-    if (ok) ok = tb200_sgemm_dev(w, Ny, io, ne00 / blck(typeA), Btype, dC, Nx) == TB200_OK;
-    for (long y = 0; y < Ny && ok; ++y) {
-        float *dst = C + (long)rm[2 * y] * (nb1 / 4) + (long)rm[2 * y + 1] * (nb2 / 4);
-        ok = cudaMemcpyAsync(dst, dC + y * Nx, (size_t)Nx * 4, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
-    }
-    if (!ok) cudaGetLastError();
-    return cudaStreamSynchronize(c->stream) == cudaSuccess && ok;
+    bool ok = cudaMemcpyAsync(io, L.in, row_b * Ny, cudaMemcpyHostToDevice, c->stream) == cudaSuccess;
+    ok = ok && tb200_sgemm_dev(w, Ny, io, ne00 / blck(typeA), Btype, dC, Nx) == TB200_OK;
+    ok = ok && cudaMemcpyAsync(L.out, dC, out_b, cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+    ok = cudaStreamSynchronize(c->stream) == cudaSuccess && ok;
+    if (!ok) { cudaGetLastError(); return runtime_failure("llamafile_mixmul_iqk", nth); }
+    for (long y = 0; y < Ny; ++y)
+        memcpy(C + (long)rm[2 * y] * (nb1 / 4) + (long)rm[2 * y + 1] * (nb2 / 4), (const float *)L.out + y * Nx, (size_t)Nx * 4);
+    return true;
 }
 
 static bool quantize_row_host(const float *x, void *y, int64_t k, int type) {
     tb200_ctx *c = tb200_get_ctx();
     if (!c || k < 0) return false;
     if (k == 0) return true;
+    DeviceLock lock(c->device);
     const size_t out_b = type == TB200_TYPE_F16 ? (size_t)k * 2 : tb200_gguf_row_bytes(type, k);
     if (!out_b) return false;
     uint8_t *io = (uint8_t *)io_buffer(c, up256((size_t)k * 4) + out_b);

@@ -56,6 +56,9 @@ def lib() -> C.CDLL:
         "llamafile_mixmul_iqk": (C.c_bool, [l, l, l, i, i, vp, vp, vp, l, l, vp, i, i]),
         "tb200_quantize_row_q8_0": (C.c_bool, [vp, vp, C.c_int64]), "tb200_quantize_row_q8_K": (C.c_bool, [vp, vp, C.c_int64]),
         "tb200_fp32_to_fp16_row": (C.c_bool, [vp, vp, C.c_int64]), "tb200_weights_cache_clear": (None, []),
+        "tb200_register_weights": (i, [vp, sz]), "tb200_unregister_weights": (i, [vp]), "tb200_weights_cache_bytes": (sz, []),
+        "tb200_plan_create": (vp, [i, vp]), "tb200_plan_run": (i, [vp, i, i]), "tb200_plan_status": (i, [vp]), "tb200_plan_reset": (i, [vp]),
+        "tb200_plan_free": (None, [vp]),
         "tb200_gguf_open": (vp, [C.c_char_p]), "tb200_gguf_close": (None, [vp]), "tb200_gguf_tensor_count": (l, [vp]),
         "tb200_gguf_tensor_name": (C.c_char_p, [vp, l]), "tb200_gguf_find": (i, [vp, C.c_char_p, vp, vp, vp, vp]),
         "tb200_gguf_upload": (vp, [vp, C.c_char_p, l, l]),
@@ -211,6 +214,54 @@ def mixmul(w: Weights, experts: int, thought, tasks: int, plan, thinkers: int, t
         return False
     _check(rc, "mixmul")
     return True
+
+
+PLAN_QUANT, PLAN_RMSNORM, PLAN_SWIGLU = 0, 1, 2
+
+
+class PlanGroupC(C.Structure):
+    """tb200_plan_group (include/tinyblas_b200.h)."""
+    _fields_ = [("n", C.c_int), ("prologue", C.c_int), ("w", C.c_void_p * 4), ("out", C.c_void_p * 4), ("residual", C.c_void_p * 4),
+                ("x", C.c_void_p), ("x2", C.c_void_p), ("norm_weight", C.c_void_p), ("eps", C.c_float)]
+
+
+class Plan:
+    """Decode plan (tb200_plan): a sequence of one-token matmul groups run as ONE persistent kernel. `groups` is a list of dicts:
+    {"w": [Weights...], "out": [buffers...], "x": buffer, optional "prologue", "x2", "norm_weight", "eps", "residual": [buffers or None]}."""
+
+    def __init__(self, groups):
+        _require_device()
+        arr = (PlanGroupC * len(groups))()
+        self._keep = groups
+        for g, d in zip(arr, groups):
+            g.n, g.prologue = len(d["w"]), d.get("prologue", PLAN_QUANT)
+            for m, w in enumerate(d["w"]):
+                g.w[m], g.out[m] = w.handle, _ptr(d["out"][m])
+                res = d.get("residual")
+                g.residual[m] = _ptr(res[m]) if res and res[m] is not None else None
+            g.x, g.x2, g.norm_weight = _ptr(d["x"]), _ptr(d.get("x2")) or None, _ptr(d.get("norm_weight")) or None
+            g.eps = d.get("eps", 0.0)
+        self.n = len(groups)
+        self.handle = lib().tb200_plan_create(self.n, arr)
+        if not self.handle:
+            raise TB200Error("plan: " + lib().tb200_last_error().decode(errors="replace"))
+
+    def run(self, first: int = 0, count: int | None = None):
+        _check(lib().tb200_plan_run(self.handle, first, self.n - first if count is None else count), "plan_run")
+
+    def status(self) -> int: return int(lib().tb200_plan_status(self.handle))
+    def reset(self): _check(lib().tb200_plan_reset(self.handle), "plan_reset")
+
+    def free(self):
+        if getattr(self, "handle", None):
+            lib().tb200_plan_free(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
 
 class GgufFile:

@@ -75,5 +75,29 @@ def quantize_row_q8_K(x: np.ndarray) -> np.ndarray:
     return y
 
 
+def fp32_to_fp16_row(x: np.ndarray) -> np.ndarray:
+    """ggml_fp32_to_fp16_row on the device (f32_to_f16_kernel); returns the IEEE half bits as uint16."""
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.zeros(x.size, np.uint16)
+    if not lib().tb200_fp32_to_fp16_row(_p(x), _p(y), x.size):
+        raise TB200Error("fp32_to_fp16_row: " + lib().tb200_last_error().decode(errors="replace"))
+    return y
+
+
 def weights_cache_clear():
     lib().tb200_weights_cache_clear()
+
+
+def register_weights(arr: np.ndarray):
+    """Declare a host array immutable (the mmap'd GGUF range): llamafile_sgemm keeps resident copies of matrices inside it."""
+    if lib().tb200_register_weights(_p(arr), arr.nbytes) != 0:
+        raise TB200Error("register_weights: " + lib().tb200_last_error().decode(errors="replace"))
+
+
+def unregister_weights(arr: np.ndarray):
+    if lib().tb200_unregister_weights(_p(arr)) != 0:
+        raise TB200Error("unregister_weights: " + lib().tb200_last_error().decode(errors="replace"))
+
+
+def weights_cache_bytes() -> int:
+    return int(lib().tb200_weights_cache_bytes())

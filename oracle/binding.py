@@ -159,6 +159,18 @@ class Oracle(_Common):
     def _sgemm(self, m, n, k, A, lda, B, ldb, Cm, ldc, Atype, Btype, Ctype, nth):
         return self.lib.oracle_sgemm(m, n, k, _p(A), lda, _p(B), ldb, _p(Cm), ldc, 0, 1, Atype, Btype, Ctype)
 
+    def rms_norm_mul(self, x, w, eps):
+        x, w = _f32(x), _f32(w); y = np.empty_like(x)
+        self.lib.oracle_rms_norm_mul.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_int64, C.c_void_p]
+        self.lib.oracle_rms_norm_mul(_p(x), _p(w), eps, x.size, _p(y))
+        return y
+
+    def silu_mul(self, gate, up):
+        gate, up = _f32(gate), _f32(up); y = np.empty_like(gate)
+        self.lib.oracle_silu_mul.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        self.lib.oracle_silu_mul(_p(gate), _p(up), gate.size, _p(y))
+        return y
+
     def mixmul_needs(self, w: Tensor, x: Tensor, plan: Tensor) -> int:
         return int(self.lib.oracle_mixmul_needs(C.byref(w), C.byref(x), C.byref(plan)))
 
@@ -229,6 +241,24 @@ class Reference(_Common):
 
     def _sgemm(self, m, n, k, A, lda, B, ldb, Cm, ldc, Atype, Btype, Ctype, nth):
         return self.lib.ref_sgemm(m, n, k, _p(A), lda, _p(B), ldb, _p(Cm), ldc, nth, Atype, Btype, Ctype)
+
+    def rms_norm_mul(self, x, w, eps):
+        x, w = _f32(x), _f32(w); y = np.empty_like(x)
+        self.lib.ref_rms_norm_mul.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_long, C.c_void_p]
+        self.lib.ref_rms_norm_mul(_p(x), _p(w), eps, x.size, _p(y))
+        return y
+
+    def silu_mul(self, gate, up):
+        gate, up = _f32(gate), _f32(up); y = np.empty_like(gate)
+        self.lib.ref_silu_mul.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p]
+        self.lib.ref_silu_mul(_p(gate), _p(up), gate.size, _p(y))
+        return y
+
+    def add(self, a, b):
+        a, b = _f32(a), _f32(b); y = np.empty_like(a)
+        self.lib.ref_add.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p]
+        self.lib.ref_add(_p(a), _p(b), a.size, _p(y))
+        return y
 
     def mixmul_needs(self, w, x, plan) -> int:
         return int(self.lib.ref_mixmul_needs(C.byref(w), C.byref(x), C.byref(plan)))

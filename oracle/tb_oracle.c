@@ -480,3 +480,34 @@ int oracle_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, const vo
     }
     return 1;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * The matmul's neighbours in the reference graph: llm_build_norm = ggml_rms_norm
+ * then ggml_mul by the norm weight; llm_build_ffn (LLM_FFN_SILU, LLM_FFN_PAR) = ggml_silu(gate)
+ * then ggml_mul by up (llama.cpp/src/llama.cpp:8099-8225).
+ * --------------------------------------------------------------------------------------------- */
+
+/* ggml_compute_forward_rms_norm_f32, llama.cpp/ggml/src/ggml.c:11850-11896: sum of x*x (float product) in
+ * ggml_float = double, mean as float, scale = 1/sqrtf(mean + eps), y = x*scale (ggml_vec_scale_f32);
+ * then ggml_mul: y[i] * w[i]. */
+void oracle_rms_norm_mul(const float *x, const float *w, float eps, int64_t n, float *y) {
+    double sum = 0.0;
+    for (int64_t i = 0; i < n; ++i) sum += (double)(x[i] * x[i]);
+    const float mean = (float)(sum / (double)n);
+    const float scale = 1.0f / sqrtf(mean + eps);
+    for (int64_t i = 0; i < n; ++i) {
+        const float v = x[i] * scale;
+        y[i] = v * w[i];
+    }
+}
+
+/* ggml_silu_f32, ggml.c:2393-2395: x/(1.0f + expf(-x)) — the scalar definition; the reference's SIMD
+ * ggml_v_silu (ggml.c:2432-2594) evaluates expf by a polynomial and differs from it by a few ulp, so this
+ * function is pinned to the reference with a tolerance (tests/test_oracle_vs_reference.py), not bit for bit.
+ * Then ggml_mul by up. */
+void oracle_silu_mul(const float *gate, const float *up, int64_t n, float *y) {
+    for (int64_t i = 0; i < n; ++i) {
+        const float s = gate[i] / (1.0f + expf(-gate[i]));
+        y[i] = s * up[i];
+    }
+}

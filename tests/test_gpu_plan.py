@@ -1,0 +1,190 @@
+"""GPU (B200): the decode plan (tb200_plan.cu) — a whole sequence of one-token matmul groups as ONE persistent kernel with
+per-warp TMA rings, in-kernel Q8_0 quantization and the fused graph neighbours (RMSNorm*weight, silu(gate)*up, residual
+add) — against the oracle, the reference-generated fixtures and the one-shot kernels."""
+import sys
+import zlib
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import helpers as H
+from oracle import binding as B
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def q4_bytes(N, K, seed, exact=False):
+    rng = np.random.default_rng(seed)
+    b = rng.integers(0, 256, (N * K // 32, 18), dtype=np.uint8)
+    d = np.full(len(b), 2.0 ** -6, np.float16) if exact else (rng.uniform(0.5, 1.5, len(b)) * 2e-3).astype(np.float16)
+    b[:, :2] = d.view(np.uint8).reshape(-1, 2)
+    return b.reshape(-1)
+
+
+def run_plan(tb, groups_np, repeats=1, ranges=None):
+    """groups_np: list of (list of (W bytes, N), K, x) -> outputs per group/matrix after running the plan."""
+    keep, groups = [], []
+    for mats, K, x in groups_np:
+        ws = [tb.Weights(W, H.Q4_0, N, K) for W, N in mats]
+        outs = [torch.full((N,), float("nan"), device="cuda") for _, N in mats]
+        groups.append({"w": ws, "out": outs, "x": dev(x)})
+        keep.append((ws, outs))
+    plan = tb.Plan(groups)
+    for _ in range(repeats):
+        for o in (o for _, outs in keep for o in outs):
+            o.fill_(float("nan"))
+        if ranges:
+            for first, count in ranges:
+                plan.run(first, count)
+        else:
+            plan.run()
+        tb.synchronize()
+        assert plan.status() == 0, "a plan wait timed out"
+    res = [[o.cpu().numpy() for o in outs] for _, outs in keep]
+    plan.free()
+    for ws, _ in keep:
+        for w in ws:
+            w.free()
+    return res
+
+
+@pytest.mark.parametrize("K", [256, 1024, 4096, 14336])
+def test_plan_single_group_vs_oracle(tb, oracle, K):
+    """One group, several matrices with odd row counts (row-pair tails), K from one partial ring stage to 3.5 stages per row."""
+    shapes = [301, 64, 1]
+    mats = [(q4_bytes(n, K, seed=n + K), n) for n in shapes]
+    x = H.make_acts(1, K, seed=K)[0]
+    res = run_plan(tb, [(mats, K, x)])
+    for (W, n), got in zip(mats, res[0]):
+        H.assert_close(got[None], oracle.mul_mat(W, H.Q4_0, x[None]), f"K={K} n={n}")
+
+
+def test_plan_exact_integer_arithmetic(tb, oracle):
+    """Inputs on which every fp32 operation is exact (power-of-two scales, activations that quantize to themselves): the
+    in-kernel quantizer, the -8 fold and the in-place high nibbles of the plan kernel must reproduce the oracle bit for bit."""
+    K = 2048
+    rng = np.random.default_rng(5)
+    groups, refs = [], []
+    for gi, shapes in enumerate(([777, 130], [2049], [64, 64, 64, 66])):
+        x = rng.integers(-12, 13, K).astype(np.float32)
+        x[::32] = 127.0
+        mats = [(q4_bytes(n, K, seed=gi * 10 + i, exact=True), n) for i, n in enumerate(shapes)]
+        groups.append((mats, K, x))
+        refs.append([oracle.mul_mat(W, H.Q4_0, x[None])[0] for W, _ in mats])
+    res = run_plan(tb, groups, repeats=3)
+    for got_g, ref_g in zip(res, refs):
+        for got, ref in zip(got_g, ref_g):
+            assert np.array_equal(got, ref), float(np.abs(got - ref).max())
+
+
+def test_plan_many_groups_repeated_and_subranges(tb, oracle):
+    """40 groups of mixed shapes (more groups than ring stages, warps with no rows in some groups), replayed several times
+    (the arrival counters must come back to zero) and as sub-range launches."""
+    rng = np.random.default_rng(9)
+    groups, refs = [], []
+    for gi in range(40):
+        K = int(rng.choice([256, 512, 1024, 3072]))
+        shapes = [int(n) for n in rng.integers(1, 700, int(rng.integers(1, 5)))]
+        x = H.make_acts(1, K, seed=gi)[0] * float(rng.uniform(0.01, 30))
+        mats = [(q4_bytes(n, K, seed=gi * 7 + i), n) for i, n in enumerate(shapes)]
+        groups.append((mats, K, x))
+        refs.append([oracle.mul_mat(W, H.Q4_0, x[None])[0] for W, _ in mats])
+    for ranges in (None, [(0, 1), (1, 2), (3, 17), (20, 20)]):
+        res = run_plan(tb, groups, repeats=3, ranges=ranges)
+        for gi, (got_g, ref_g) in enumerate(zip(res, refs)):
+            for got, ref in zip(got_g, ref_g):
+                H.assert_close(got[None], ref[None], f"group {gi} ranges={ranges}")
+
+
+def test_plan_equals_one_shot_quantizer(tb):
+    """The in-kernel activation quantizer is the same arithmetic as quantize_q8_0_kernel: on adversarial rows the plan's result
+    equals what the one-shot path computes from the separately quantized activations, within accumulation order."""
+    K = 256
+    W = q4_bytes(96, K, seed=1)
+    w = tb.Weights(W, H.Q4_0, 96, K)
+    for row in H.adversarial_rows(K)[:13]:
+        if not np.isfinite(row).all() or np.abs(row).max() > 1e30:
+            continue
+        out_p = torch.full((96,), float("nan"), device="cuda")
+        plan = tb.Plan([{"w": [w], "out": [out_p], "x": dev(row)}])
+        plan.run()
+        out_1 = torch.full((1, 96), float("nan"), device="cuda")
+        tb.mul_mat(w, dev(row[None]), 1, out_1)
+        tb.synchronize()
+        a, b = out_p.cpu().numpy(), out_1.cpu().numpy()[0]
+        assert not np.isnan(a).any()
+        den = max(float(np.abs(b).max()), 1e-30)
+        assert float(np.abs(a - b).max()) / den < 1e-5
+        plan.free()
+    w.free()
+
+
+def test_plan_rejects_unsupported(tb):
+    K = 1024
+    w8 = tb.Weights(H.make_weights(H.Q8_0, 64, K), H.Q8_0, 64, K)
+    out = torch.zeros(64, device="cuda")
+    x = torch.zeros(K, device="cuda")
+    with pytest.raises(tb.TB200Error):
+        tb.Plan([{"w": [w8], "out": [out], "x": x}])          # Q8_0: per-matrix API only
+    w4 = tb.Weights(q4_bytes(64, 288, 1), H.Q4_0, 64, 288)
+    with pytest.raises(tb.TB200Error):
+        tb.Plan([{"w": [w4], "out": [out], "x": x}])          # K % 256 != 0
+    w8.free(); w4.free()
+
+
+# ------------------------------------------------------------------ fused neighbours against the reference's own graph ops
+def test_plan_fused_layer_vs_reference_golden(tb, oracle):
+    """One transformer layer's decode matmuls with RMSNorm*weight -> qkv, wo + residual, RMSNorm*weight -> gate/up,
+    silu(gate)*up -> down + residual, as ONE launch, against fixtures produced by ggml's CPU ops + llamafile_sgemm
+    (tests/golden/make_golden_fused.py)."""
+    sys.path.insert(0, str(ROOT / "tests" / "golden"))
+    import make_golden_fused as M
+    g = np.load(ROOT / "tests" / "golden" / "fused_golden.npz")
+    Wb = M.layer_weights(oracle.quantize_q4_0)
+    assert [zlib.crc32(Wb[k].tobytes()) for k in M.SHAPES] == list(g["crc"])
+    W = {k: tb.Weights(Wb[k], H.Q4_0, *M.SHAPES[k]) for k in M.SHAPES}
+    x, attn, n1, n2 = (dev(g[f"in_{k}"]) for k in ("x", "attn", "norm1", "norm2"))
+    o = {k: torch.full((M.SHAPES[k][0],), float("nan"), device="cuda") for k in ("wq", "wk", "wv", "gate", "up")}
+    x2 = torch.full((M.HID,), float("nan"), device="cuda")
+    x3 = torch.full((M.HID,), float("nan"), device="cuda")
+    plan = tb.Plan([
+        {"w": [W["wq"], W["wk"], W["wv"]], "out": [o["wq"], o["wk"], o["wv"]], "x": x, "prologue": tb.PLAN_RMSNORM, "norm_weight": n1, "eps": M.EPS},
+        {"w": [W["wo"]], "out": [x2], "x": attn, "residual": [x]},
+        {"w": [W["gate"], W["up"]], "out": [o["gate"], o["up"]], "x": x2, "prologue": tb.PLAN_RMSNORM, "norm_weight": n2, "eps": M.EPS},
+        {"w": [W["down"]], "out": [x3], "x": o["gate"], "x2": o["up"], "prologue": tb.PLAN_SWIGLU, "residual": [x2]},
+    ])
+    for rep in range(3):
+        plan.run()
+        tb.synchronize()
+        assert plan.status() == 0
+        for k in ("wq", "wk", "wv", "gate", "up"):
+            H.assert_close(o[k].cpu().numpy()[None], g[f"out_{k}"][None], f"{k} rep {rep}")
+        H.assert_close(x2.cpu().numpy()[None], g["out_x2"][None], "x2 = wo.attn + x")
+        H.assert_close(x3.cpu().numpy()[None], g["out_x3"][None], "x3 = down.act + x2")
+    plan.free()
+
+
+def test_plan_llama3_8b_layer_shapes_sampled(tb, oracle):
+    """BASELINE config 2 shapes in one plan (K=4096: 4096+1024+1024, 4096, 14336+14336; K=14336: 4096; vocabulary 128256):
+    sampled rows against the oracle, every output written."""
+    rng = np.random.default_rng(3)
+    spec = [([4096, 1024, 1024], 4096), ([4096], 4096), ([14336, 14336], 4096), ([4096], 14336), ([128256], 4096)]
+    groups = []
+    for gi, (shapes, K) in enumerate(spec):
+        x = H.make_acts(1, K, seed=gi)[0]
+        groups.append(([(q4_bytes(n, K, seed=gi * 5 + i), n) for i, n in enumerate(shapes)], K, x))
+    res = run_plan(tb, groups, repeats=2)
+    for (mats, K, x), got_g in zip(groups, res):
+        rb = K // 32 * 18
+        for (W, n), got in zip(mats, got_g):
+            assert not np.isnan(got).any()
+            for lo in (0, n // 2 - 7, n - 16):
+                ref = oracle.mul_mat(W[lo * rb:(lo + 16) * rb], H.Q4_0, x[None])
+                H.assert_close(got[lo:lo + 16][None], ref, f"K={K} n={n} rows {lo}")

@@ -1,11 +1,15 @@
 """CPU: the oracle (oracle/tb_oracle.c) against the committed fixtures that were produced by running the
 reference's own compiled hot path (tests/golden/make_golden.py). Bit-exact for the quantizers, scaled
 error for fp32 outputs."""
+from pathlib import Path
+
 import numpy as np
 import pytest
 
 import helpers as H
 from oracle import binding as B
+
+ROOT = Path(__file__).resolve().parent.parent
 
 
 def test_quantizers_bit_exact(oracle, golden):
@@ -70,3 +74,20 @@ def test_block_dots_match_vec_dot(oracle):
             for s, a, b in zip(sums, wd, yd):
                 acc = np.float32(acc + np.float32(np.float32(np.float32(s) * a) * b))
             assert acc == np.float32(oracle.vec_dot(wt, K, W, Y))
+
+
+def test_fused_layer_golden(oracle):
+    """The oracle reproduces the reference's one-layer decode chain (matmuls + rms_norm / silu / mul / add neighbours),
+    weights regenerated from the generator's seeds with the oracle's quantizer (CRC proves they are the reference's bytes)."""
+    import sys
+    import zlib
+    sys.path.insert(0, str(ROOT / "tests" / "golden"))
+    import make_golden_fused as M
+    g = np.load(ROOT / "tests" / "golden" / "fused_golden.npz")
+    W = M.layer_weights(oracle.quantize_q4_0)
+    assert [zlib.crc32(W[k].tobytes()) for k in M.SHAPES] == list(g["crc"])
+    I = {k: g[f"in_{k}"] for k in ("x", "attn", "norm1", "norm2")}
+    got = M.run_layer(oracle, W, I)
+    assert np.array_equal(got["h1"], g["out_h1"])            # rms_norm * weight: bit-exact
+    for k, v in got.items():
+        H.assert_close(v[None], g[f"out_{k}"][None], k)

@@ -127,3 +127,16 @@ def test_mixmul_iqk(oracle, reference, typeA):
     assert np.array_equal(np.isnan(outs[0]), np.isnan(outs[1]))
     m = ~np.isnan(outs[1])
     H.assert_close(outs[0][m], outs[1][m])
+
+
+# ------------------------------------------------------------------ the matmul's graph neighbours
+@pytest.mark.parametrize("n", [256, 4096, 14336])
+def test_rms_norm_mul_bit_exact_and_silu_mul_close(oracle, reference, n):
+    rng = np.random.default_rng(n)
+    x = (rng.standard_normal(n) * 3).astype(np.float32)
+    w = (1 + 0.1 * rng.standard_normal(n)).astype(np.float32)
+    assert np.array_equal(oracle.rms_norm_mul(x, w, 1e-5), reference.rms_norm_mul(x, w, 1e-5))
+    g, u = (rng.standard_normal(n) * 2).astype(np.float32), rng.standard_normal(n).astype(np.float32)
+    a, b = oracle.silu_mul(g, u), reference.silu_mul(g, u)
+    # ggml's SIMD silu evaluates expf by a polynomial (ggml.c:2432-2594): a few ulp from the scalar definition
+    assert float(np.abs(a - b).max() / np.abs(b).max()) < 1e-6
