@@ -21,12 +21,17 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std
          "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 
 
+def _flags():
+    """FLAGS + optional -D overrides for experiments (TB200_NVCC_DEFS="-DTB200_PLAN_WARPS=16 -DTB200_PLAN_STAGES=2")."""
+    return FLAGS + os.environ.get("TB200_NVCC_DEFS", "").split()
+
+
 def _sig(paths) -> str:
     h = hashlib.sha1()
     for p in sorted(paths):
         h.update(p.name.encode())
         h.update(p.read_bytes())
-    h.update(" ".join(FLAGS).encode())
+    h.update(" ".join(_flags()).encode())
     return h.hexdigest()
 
 
@@ -45,7 +50,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     def cc(src: Path):
         obj = OBJ / (src.stem + ".o")
-        cmd = [NVCC, *FLAGS, "-c", str(src), "-o", str(obj)]
+        cmd = [NVCC, *_flags(), "-c", str(src), "-o", str(obj)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -28,21 +28,33 @@
 
 namespace {
 
-constexpr int kPW = 16;                                   // warps per CTA, every one a consumer with its own ring
-constexpr int kPS = 2;                                    // ring stages per warp
+#ifndef TB200_PLAN_WARPS
+#define TB200_PLAN_WARPS 15
+#endif
+#ifndef TB200_PLAN_STAGES
+#define TB200_PLAN_STAGES 2
+#endif
+#ifndef TB200_PLAN_ROWS
+#define TB200_PLAN_ROWS 2
+#endif
+constexpr int kPW = TB200_PLAN_WARPS;                     // consumer warps per CTA, each with its own ring
+constexpr int kTW = kPW + 1;                              // + the sync warp, which runs the grid-barrier protocol (and helps staging the activations)
+constexpr int kPS = TB200_PLAN_STAGES;                    // ring stages per warp
+constexpr int kR = TB200_PLAN_ROWS;                       // weight rows per work unit (they share every activation read)
 constexpr int kSegBlocks = 128;                           // 32-element blocks of K per stage and row (4096 elements)
 constexpr int kRowQ = kSegBlocks * 16, kRowS = kSegBlocks * 2;
-constexpr int kStageBytes = 2 * (kRowQ + kRowS);          // a row PAIR: 4608 B
+constexpr int kStageBytes = kR * (kRowQ + kRowS);         // kR rows x (2 KB of nibbles + 256 B of fp16 scales): 8 x 2 x 9 KB = 147 KB in flight per SM
 constexpr int kPlanMats = TB200_GEMV_MAX_MATS;
+constexpr bool kActCache = kTW * 32 <= 384;               // activations of K <= 4096 groups in registers (needs > 128 registers per thread)
 
-struct PlanGroup {
+struct alignas(16) PlanGroup {
     const float *x, *x2, *nw;          // prologue inputs (see tb200_plan_group)
     float eps;
     int prologue;
-    int nb, nseg;                      // 32-blocks per row; ring stages per row pair
-    int npairs, rot;                   // row pairs of all matrices; rotation of the warp -> pair assignment
+    int nb, nseg;                      // 32-blocks per row; ring stages per unit
+    int nunits, rot;                   // units (kR consecutive rows of one matrix) of all matrices; rotation of the warp -> unit assignment
     int nmat;
-    int pair_begin[kPlanMats + 1];
+    int unit_begin[kPlanMats + 1];
     int rows[kPlanMats];
     const uint4 *qs[kPlanMats];
     const __half *sc[kPlanMats];
@@ -50,12 +62,18 @@ struct PlanGroup {
     const float *res[kPlanMats];
 };
 
+static_assert(sizeof(PlanGroup) % 16 == 0, "descriptors are copied to shared memory in 16-byte words");
+constexpr size_t kPlanSmemMax = 224 * 1024;               // dynamic shared memory the kernel may be given (227 KB - its static part)
+
 struct PlanParams {
     const PlanGroup *groups;
     int first, end;                    // groups [first, end) run in this launch
     unsigned *cnt;                     // [n_groups] arrival counters, all zero between launches
     int *err;                          // set when a wait gave up (the results of that launch are then undefined)
     int nb_max;
+    int ahead;                         // the sync warp prefetches group g+ahead into L2 while g is computed (0 = off)
+    int flags;                         // experiments (TB200_PLAN_FLAGS): 1 = no release fence, 2 = stage activations only for the first group, 4 = no grid barrier
+    long long *trace;                  // optional (tb200_plan_trace): [group][CTA][8] SM-clock stamps of the group's phases
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -77,6 +95,9 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ uint64_t policy_evict_first() {
     uint64_t p;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
@@ -87,6 +108,19 @@ __device__ __forceinline__ unsigned ld_acquire(const unsigned *p) {
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ unsigned ld_relaxed(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }   // __threadfence() is fence.sc: dearer
+__device__ __forceinline__ unsigned atom_add_relaxed(unsigned *p, unsigned v) {
+    unsigned old;
+    asm volatile("atom.relaxed.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 constexpr long long kSpinLimit = 4000000000LL;            // ~2 s of SM clocks: a wedged wait gives up and raises *err
 
 // _mm256_cvtps_epi32 + packs (ggml-quants.c:962-977), as in tb200_quantize.cu
@@ -98,15 +132,30 @@ __device__ __forceinline__ int plan_cvt_rne_sat8(float v) {
 // The group's activations: fp32 from global (L2; written by other SMs earlier in this very launch, hence ld.global.cg)
 // -> optional RMSNorm*weight or silu(gate)*up -> quantize_row_q8_0 (ggml-quants.c:940-990, bit-exact: tb200_quantize.cu)
 // -> the decode kernels' planar staging form: s_lo[b] = quants 0..15, s_hi[b] = quants 16..31, s_ds[b] = {d, sum q}.
+// A 4-lane group owns a 32-block (8 elements per lane: two float4 loads, two shuffle steps per reduction); all loads of a
+// chunk (kActR rounds of kTW*8 blocks = 16384 elements with 16 warps) are issued before the first is consumed, so a
+// 14336-wide row costs one L2 round trip. Every CTA does this redundantly: 16..57 KB from L2 per SM and group.
+constexpr int kActR = 4;
+__device__ __forceinline__ float silu_mul(float g, float u) { return __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), u); }   // ggml_silu_f32 (ggml.c:2393) then ggml_mul
 __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, double *s_red, float *s_scale) {
     const int nb = G.nb, K = nb * QK;
+    const int group = threadIdx.x >> 2, j = threadIdx.x & 3;
+    const int prologue = G.prologue;
+    const float4 *x4 = reinterpret_cast<const float4 *>(G.x), *u4 = reinterpret_cast<const float4 *>(G.x2), *w4 = reinterpret_cast<const float4 *>(G.nw);
     float scale = 1.f;
-    if (G.prologue == TB200_PLAN_RMSNORM) {
-        // ggml_compute_forward_rms_norm_f32 (llama.cpp/ggml/src/ggml.c): sum of x*x in double, mean as float, 1/sqrtf(mean + eps)
+    if (prologue == TB200_PLAN_RMSNORM) {
+        // ggml_compute_forward_rms_norm_f32 (llama.cpp/ggml/src/ggml.c:11850-11896): sum of x*x in double, mean as float, 1/sqrtf(mean + eps)
         double s = 0.0;
-        for (int i = threadIdx.x; i < K / 4; i += kPW * 32) {
-            const float4 v = __ldcg(reinterpret_cast<const float4 *>(G.x) + i);
-            s += (double)__fmul_rn(v.x, v.x) + (double)__fmul_rn(v.y, v.y) + (double)__fmul_rn(v.z, v.z) + (double)__fmul_rn(v.w, v.w);
+        for (int i0 = 0; i0 < K / 4; i0 += kTW * 32 * 2 * kActR) {
+            float4 v[2 * kActR];
+#pragma unroll
+            for (int u = 0; u < 2 * kActR; ++u) {
+                const int i = i0 + u * kTW * 32 + (int)threadIdx.x;
+                v[u] = i < K / 4 ? __ldcg(x4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 2 * kActR; ++u)
+                s += (double)__fmul_rn(v[u].x, v[u].x) + (double)__fmul_rn(v[u].y, v[u].y) + (double)__fmul_rn(v[u].z, v[u].z) + (double)__fmul_rn(v[u].w, v[u].w);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -114,133 +163,314 @@ __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_l
         __syncthreads();
         if (threadIdx.x == 0) {
             double t = 0.0;
-            for (int w = 0; w < kPW; ++w) t += s_red[w];
+            for (int w = 0; w < kTW; ++w) t += s_red[w];
             const float mean = (float)(t / (double)K);
             *s_scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, G.eps)));
         }
         __syncthreads();
         scale = *s_scale;
     }
-    const int group = threadIdx.x >> 3, g8 = threadIdx.x & 7;
-    for (int b0 = 0; b0 < nb; b0 += kPW * 4) {
-        const int b = b0 + group;
-        const bool live = b < nb;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (live) {
-            const int i4 = b * 8 + g8;
-            v = __ldcg(reinterpret_cast<const float4 *>(G.x) + i4);
-            if (G.prologue == TB200_PLAN_RMSNORM) {   // y = x*scale (ggml_vec_scale_f32), then ggml_mul by the norm weight
-                const float4 w = __ldg(reinterpret_cast<const float4 *>(G.nw) + i4);
-                v.x = __fmul_rn(__fmul_rn(v.x, scale), w.x), v.y = __fmul_rn(__fmul_rn(v.y, scale), w.y);
-                v.z = __fmul_rn(__fmul_rn(v.z, scale), w.z), v.w = __fmul_rn(__fmul_rn(v.w, scale), w.w);
-            } else if (G.prologue == TB200_PLAN_SWIGLU) {   // ggml_silu(gate) then ggml_mul(., up): x/(1+exp(-x)) * up
-                const float4 u = __ldcg(reinterpret_cast<const float4 *>(G.x2) + i4);
-                v.x = __fmul_rn(__fdiv_rn(v.x, __fadd_rn(1.0f, expf(-v.x))), u.x), v.y = __fmul_rn(__fdiv_rn(v.y, __fadd_rn(1.0f, expf(-v.y))), u.y);
-                v.z = __fmul_rn(__fdiv_rn(v.z, __fadd_rn(1.0f, expf(-v.z))), u.z), v.w = __fmul_rn(__fdiv_rn(v.w, __fadd_rn(1.0f, expf(-v.w))), u.w);
+    for (int b0 = 0; b0 < nb; b0 += kTW * 8 * kActR) {
+        float4 va[kActR], vb[kActR], ta[kActR], tb[kActR];
+#pragma unroll
+        for (int r = 0; r < kActR; ++r) {
+            const int b = b0 + r * kTW * 8 + group;
+            va[r] = vb[r] = ta[r] = tb[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (b < nb) {
+                const int i = b * 8 + 2 * j;
+                va[r] = __ldcg(x4 + i), vb[r] = __ldcg(x4 + i + 1);
+                if (prologue == TB200_PLAN_RMSNORM) ta[r] = __ldg(w4 + i), tb[r] = __ldg(w4 + i + 1);
+                else if (prologue == TB200_PLAN_SWIGLU) ta[r] = __ldcg(u4 + i), tb[r] = __ldcg(u4 + i + 1);
             }
         }
-        float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
 #pragma unroll
-        for (int o = 4; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-        const float d = __fdiv_rn(amax, 127.f);
-        const float id = (amax != 0.0f) ? __fdiv_rn(127.f, amax) : 0.0f;
-        const int q0 = plan_cvt_rne_sat8(__fmul_rn(v.x, id)), q1 = plan_cvt_rne_sat8(__fmul_rn(v.y, id));
-        const int q2 = plan_cvt_rne_sat8(__fmul_rn(v.z, id)), q3 = plan_cvt_rne_sat8(__fmul_rn(v.w, id));
-        const uint32_t packed = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
-        int sum = q0 + q1 + q2 + q3;
+        for (int r = 0; r < kActR; ++r) {
+            if (b0 + r * kTW * 8 >= nb) break;               // CTA-uniform: the whole round is past the row
+            const int b = b0 + r * kTW * 8 + group;
+            float y[8] = {va[r].x, va[r].y, va[r].z, va[r].w, vb[r].x, vb[r].y, vb[r].z, vb[r].w};
+            const float t[8] = {ta[r].x, ta[r].y, ta[r].z, ta[r].w, tb[r].x, tb[r].y, tb[r].z, tb[r].w};
+            if (prologue == TB200_PLAN_RMSNORM) {            // y = x*scale (ggml_vec_scale_f32), then ggml_mul by the norm weight
 #pragma unroll
-        for (int o = 4; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        if (live) {
-            reinterpret_cast<uint32_t *>(g8 < 4 ? s_lo + b : s_hi + b)[g8 & 3] = packed;
-            if (g8 == 0) s_ds[b] = make_int2(__float_as_int(__half2float(__float2half_rn(d))), sum);
+                for (int e = 0; e < 8; ++e) y[e] = __fmul_rn(__fmul_rn(y[e], scale), t[e]);
+            } else if (prologue == TB200_PLAN_SWIGLU) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) y[e] = silu_mul(y[e], t[e]);
+            }
+            float amax = 0.f;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(y[e]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            const float d = __fdiv_rn(amax, 127.f);
+            const float id = (amax != 0.0f) ? __fdiv_rn(127.f, amax) : 0.0f;
+            int q[8];
+            if (amax >= 1e-30f && amax <= 3e38f) {           // |x*id| <= 127*(1+2^-23): plain round-to-nearest-even, no saturation corner
+#pragma unroll
+                for (int e = 0; e < 8; ++e) q[e] = __float2int_rn(__fmul_rn(y[e], id));
+            } else {                                         // id overflowed or inputs are not finite: the reference's cvtps/packs saturation
+#pragma unroll
+                for (int e = 0; e < 8; ++e) q[e] = plan_cvt_rne_sat8(__fmul_rn(y[e], id));
+            }
+            int sum = ((q[0] + q[1]) + (q[2] + q[3])) + ((q[4] + q[5]) + (q[6] + q[7]));
+            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+            if (b < nb) {
+                uint2 pk;
+                pk.x = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)q[3] << 24);
+                pk.y = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)q[7] << 24);
+                reinterpret_cast<uint2 *>(j < 2 ? s_lo + b : s_hi + b)[j & 1] = pk;
+                if (j == 0) s_ds[b] = make_int2(__float_as_int(__half2float(__float2half_rn(d))), sum);
+            }
         }
     }
 }
 
-__global__ void __launch_bounds__(kPW * 32, 1) plan_q4_0_kernel(const __grid_constant__ PlanParams P) {
+// Block dots of one ring stage (kR rows x `segb` blocks of K) against the group's activations. kCached: the row has one
+// stage (K <= 4096), so a lane meets the same four blocks in every unit and keeps their activations in registers for the
+// whole group; shared memory then only carries the weights (2.3 KB per row instead of 2.3 + 5/kR).
+struct ActCache { uint4 al[kSegBlocks / 32], ah[kSegBlocks / 32]; int2 ds[kSegBlocks / 32]; };
+template <bool kCached, bool kFull>
+__device__ __forceinline__ void stage_dots(const uint8_t *stage, const ActCache &C, const uint4 *s_lo, const uint4 *s_hi, const int2 *s_ds, int kb0, int segb,
+                                           int lane, float (&acc)[kR]) {
+#pragma unroll
+    for (int u = 0; u < kSegBlocks / 32; ++u) {
+        const int b = lane + 32 * u;
+        if (kFull || b < segb) {
+            uint4 al, ah;
+            int2 ds;
+            if (kCached) al = C.al[u], ah = C.ah[u], ds = C.ds[u];
+            else al = s_lo[kb0 + b], ah = s_hi[kb0 + b], ds = s_ds[kb0 + b];
+            const float dy = __int_as_float(ds.x);
+            const int bias = -8 * ds.y;                      // sum (q-8)*y = sum q*y - 8*sum y (exact in int32)
+#pragma unroll
+            for (int r = 0; r < kR; ++r) {
+                const uint4 w = reinterpret_cast<const uint4 *>(stage + r * kRowQ)[b];
+                const float dw = __half2float(reinterpret_cast<const __half *>(stage + kR * kRowQ + r * kRowS)[b]);
+                int l = dp4a_us(w.x & 0x0f0f0f0fu, (int)al.x, bias);
+                l = dp4a_us(w.y & 0x0f0f0f0fu, (int)al.y, l);
+                l = dp4a_us(w.z & 0x0f0f0f0fu, (int)al.z, l);
+                l = dp4a_us(w.w & 0x0f0f0f0fu, (int)al.w, l);
+                // high nibbles stay in place (= 16*q as unsigned bytes); their sum is an exact multiple of 16
+                int h = dp4a_us(w.x & 0xf0f0f0f0u, (int)ah.x, 0);
+                h = dp4a_us(w.y & 0xf0f0f0f0u, (int)ah.y, h);
+                h = dp4a_us(w.z & 0xf0f0f0f0u, (int)ah.z, h);
+                h = dp4a_us(w.w & 0xf0f0f0f0u, (int)ah.w, h);
+                acc[r] = fmaf(dw * dy, (float)(l + (h >> 4)), acc[r]);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_constant__ PlanParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *ring = smem;                                                          // [kPW][kPS][kStageBytes]
     uint4 *s_lo = reinterpret_cast<uint4 *>(smem + kPW * kPS * kStageBytes);       // [nb_max]
     uint4 *s_hi = s_lo + P.nb_max;
     int2 *s_ds = reinterpret_cast<int2 *>(s_hi + P.nb_max);
+    // the descriptors of this launch's groups: every warp walks them (twice: as consumer and, a few groups ahead, as its own
+    // TMA producer), and a gpu-scope fence invalidates L1, so from global memory each look-up was an L2 round trip
+    const PlanGroup *tab = reinterpret_cast<const PlanGroup *>(s_ds + P.nb_max) - P.first;   // tab[g], g in [first, end)
     __shared__ uint64_t s_full[kPW][kPS];
-    __shared__ double s_red[kPW];
+    __shared__ double s_red[kTW];
     __shared__ float s_scale;
+    constexpr int kThreads = kTW * 32;
+    constexpr int kBarArrived = 1, kBarRelease = 2;         // named barriers (0 is __syncthreads)
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int GW = (int)gridDim.x * kPW, gw = (int)blockIdx.x * kPW + warp;
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(P.groups + P.first);
+        uint4 *dst = reinterpret_cast<uint4 *>(s_ds + P.nb_max);
+        const int n16 = (P.end - P.first) * (int)(sizeof(PlanGroup) / 16);
+        for (int i = threadIdx.x; i < n16; i += kThreads) dst[i] = __ldg(src + i);
+    }
     if (threadIdx.x == 0) {
         for (int i = 0; i < kPW * kPS; ++i) mbar_init(&s_full[0][0] + i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+
+    // ================================================================================================ the sync warp
+    // Between two groups stands a grid-wide barrier (group g's input is a function of group g-1's output). Its protocol - wait
+    // until this CTA's consumers have stored their results, release fence, arrival on the group's counter in L2, poll until
+    // all CTAs have arrived, let the consumers go - runs in a warp of its own, so no consumer ever waits for a fence or an
+    // atomic round trip: consumers only ARRIVE (bar.arrive, non-blocking) and use the wait for the work that is not urgent
+    // (refilling the ring stage they just emptied with a row of the group after next).
+    if (warp == kPW) {
+        for (int g = P.first; g < P.end; ++g) {
+            const PlanGroup &G = tab[g];
+            long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * 16 : nullptr;
+            if (g > P.first && !(P.flags & 4)) {
+                bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
+                if (tr) tr[1] = clock64();
+                if (lane == 0) {
+                    if (!(P.flags & 1)) fence_acq_rel_gpu();   // release: those stores (ordered before by the CTA barrier) precede the arrival
+                    const unsigned old = atom_add_relaxed(P.cnt + (g - 1), 1u);
+                    if (tr) tr[2] = clock64();
+                    if (old == gridDim.x - 1 && g - 1 > P.first) P.cnt[g - 2] = 0;   // everybody has left barrier g-2: re-arm it for the next launch
+                    const long long t0 = clock64();
+                    // Acquire side: a relaxed (L2) poll, no fence and no L1 invalidation per iteration. What an acquire would add is
+                    // there by construction: every value another SM wrote is read with ld.global.cg / from L2 (no stale L1 copy can
+                    // be hit), and those loads are issued only after the CTA barrier below, which this thread joins after the poll
+                    // has seen the last arrival - whose release fence made the arriving CTA's stores visible at L2 first.
+                    while (ld_relaxed(P.cnt + (g - 1)) < gridDim.x)
+                        if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
+                    if (tr) tr[3] = clock64();
+                }
+                __syncwarp();
+            } else if (g > P.first) bar_sync(kBarArrived, kThreads);
+            bar_sync(kBarRelease, kThreads);                // consumers may stage and compute group g
+            if (!(P.flags & 2) || g == P.first) stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale);
+            __syncthreads();
+            // Experiment, OFF by default (TB200_PLAN_AHEAD=n): while the consumers work, pull this CTA's rows of group g+n from HBM
+            // into L2 with one bulk prefetch per unit and plane, so that HBM keeps streaming during the barrier chains of the small
+            // groups. Measured on the 8B step: 1.27 ms with n = 1..3 against 1.07 ms without - the prefetched lines do not survive
+            // until the ring asks for them (the demand stream is evict-first, the prefetches are not) and the bytes cross HBM twice.
+            const int gp = g + P.ahead;
+            if (P.ahead > 0 && gp < P.end) {
+                const PlanGroup &Gp = tab[gp];
+                const int per_warp = (Gp.nunits + GW - 1) / GW;
+                for (int i = lane; i < kPW * per_warp; i += 32) {
+                    const int w = i % kPW, j = i / kPW;
+                    int u = (int)blockIdx.x * kPW + w - Gp.rot;
+                    if (u < 0) u += GW;
+                    u += j * GW;
+                    if (u < Gp.nunits) {
+                        int m = 0;
+#pragma unroll
+                        for (int mm = 1; mm < kPlanMats; ++mm)
+                            if (u >= Gp.unit_begin[mm]) m = mm;
+                        const long r0 = (long)kR * (u - Gp.unit_begin[m]);
+                        const int nr = min(kR, Gp.rows[m] - (int)r0);
+                        bulk_prefetch_l2(Gp.qs[m] + r0 * Gp.nb, (uint32_t)(nr * Gp.nb * 16));
+                        bulk_prefetch_l2(Gp.sc[m] + r0 * Gp.nb, (uint32_t)(nr * Gp.nb * 2));
+                    }
+                }
+            }
+        }
+        // the last group: count this CTA in, and the last CTA leaves every counter at zero for the next launch
+        bar_sync(kBarArrived, kThreads);
+        if (lane == 0 && P.end - P.first > 1) {
+            const int last = P.end - 1;
+            fence_acq_rel_gpu();
+            const unsigned old = atom_add_relaxed(P.cnt + last, 1u);
+            if (old == gridDim.x - 1) {
+                if (last - 1 >= P.first) P.cnt[last - 1] = 0;
+                P.cnt[last] = 0;
+            }
+        }
+        return;
+    }
+
+    // ================================================================================================ consumer warps
     const uint64_t policy = policy_evict_first();
     uint8_t *my_ring = ring + (size_t)warp * kPS * kStageBytes;
 
-    // ---- producer side of this warp: the item (group, pair, segment) to be copied next
-    int ig = P.first, ipair = 0, iseg = 0, i_nseg = 1, i_npairs = 0;
-    auto first_pair = [&](const PlanGroup &G) { int p = gw - G.rot % GW; return p < 0 ? p + GW : p; };
-    auto iseek = [&]() {   // first group from ig on in which this warp owns a pair
-        while (ig < P.end) {
-            const PlanGroup &G = P.groups[ig];
-            ipair = first_pair(G), iseg = 0, i_nseg = G.nseg, i_npairs = G.npairs;
-            if (ipair < i_npairs) return;
-            ++ig;
-        }
-    };
-    auto issue = [&](int st) {   // lane 0: four bulk copies (two rows x {nibbles, scales}) into stage st
-        const PlanGroup &G = P.groups[ig];
+    // ---- producer side of this warp: the item (group, unit, segment) to be copied next. Lanes 0..2*kR-1 stand for (plane,
+    // row): lane % kR the row of the unit, lanes < kR the nibble plane, the others the scale plane. When the unit's rows are
+    // one contiguous run in memory (K = 4096, no clamped tail row) the first lane of each plane copies all kR rows at once:
+    // two bulk copies per stage. What a lane needs per item lives in registers, is computed right after the iterator moves
+    // (off the refill path) and is refreshed from the descriptor only when the iterator crosses into another matrix or group.
+    int ig = P.first, iunit = 0, iseg = 0, i_nseg = 1, i_nunits = 0, i_nb = 0, i_ub = 0, i_ue = 0, i_rows = 1;
+    const char *i_base = nullptr;
+    const int prow = lane % kR, plane = (lane / kR) & 1;
+    const int bunit = plane ? 2 : 16;                       // bytes per block in this lane's plane
+    const int dst_off = plane ? kR * kRowQ + prow * kRowS : prow * kRowQ;
+    auto first_unit = [&](const PlanGroup &G) { int p = gw - G.rot; return p < 0 ? p + GW : p; };
+    auto iload_mat = [&]() {
+        const PlanGroup &G = tab[ig];
         int m = 0;
 #pragma unroll
         for (int mm = 1; mm < kPlanMats; ++mm)
-            if (mm < G.nmat && ipair >= G.pair_begin[mm]) m = mm;
-        const int lp = ipair - G.pair_begin[m];
-        const long r0 = 2L * lp, r1 = min(2L * lp + 1, (long)G.rows[m] - 1);   // odd tail: the last row twice, stored once
-        const int b0 = iseg * kSegBlocks, segb = min(kSegBlocks, G.nb - b0);
-        uint8_t *stage = my_ring + st * kStageBytes;
-        uint64_t *bar = &s_full[warp][st];
-        mbar_expect_tx(bar, (uint32_t)segb * 36u);
-        bulk_g2s(stage, G.qs[m] + (r0 * G.nb + b0), segb * 16, bar, policy);
-        bulk_g2s(stage + kRowQ, G.qs[m] + (r1 * G.nb + b0), segb * 16, bar, policy);
-        bulk_g2s(stage + 2 * kRowQ, G.sc[m] + (r0 * G.nb + b0), segb * 2, bar, policy);
-        bulk_g2s(stage + 2 * kRowQ + kRowS, G.sc[m] + (r1 * G.nb + b0), segb * 2, bar, policy);
+            if (iunit >= G.unit_begin[mm]) m = mm;            // unit_begin[] of unused matrices = nunits
+        i_ub = G.unit_begin[m], i_ue = G.unit_begin[m + 1], i_rows = G.rows[m];
+        i_base = plane ? reinterpret_cast<const char *>(G.sc[m]) : reinterpret_cast<const char *>(G.qs[m]);
+    };
+    auto iseek = [&]() {   // first group from ig on in which this warp owns a unit
+        while (ig < P.end) {
+            const PlanGroup &G = tab[ig];
+            iunit = first_unit(G), iseg = 0, i_nseg = G.nseg, i_nunits = G.nunits, i_nb = G.nb;
+            if (iunit < i_nunits) { iload_mat(); return; }
+            ++ig;
+        }
+    };
+    const char *nx_src = nullptr;
+    uint32_t nx_bytes = 0, nx_tx = 0;
+    bool nx_on = false;
+    auto iprepare = [&]() {
+        const long r_first = (long)kR * (iunit - i_ub);
+        const bool contig = i_nb == kSegBlocks && r_first + kR <= i_rows;          // warp-uniform
+        const long row = min(r_first + prow, (long)i_rows - 1);                    // tail: the last row again, stored once
+        const int b0 = iseg * kSegBlocks, segb = min(kSegBlocks, i_nb - b0);
+        nx_tx = (uint32_t)segb * 18u * kR;
+        nx_src = i_base + (row * i_nb + b0) * bunit;
+        nx_bytes = (uint32_t)(segb * bunit) * (contig ? kR : 1);
+        nx_on = lane < 2 * kR && (!contig || prow == 0) && ig < P.end;
     };
     auto iadvance = [&]() {
         if (++iseg < i_nseg) return;
-        iseg = 0, ipair += GW;
-        if (ipair < i_npairs) return;
+        iseg = 0, iunit += GW;
+        if (iunit < i_ue) return;
+        if (iunit < i_nunits) { iload_mat(); return; }
         ++ig;
         iseek();
     };
-    iseek();
-#pragma unroll
-    for (int st = 0; st < kPS; ++st)
-        if (ig < P.end) {
-            if (lane == 0) issue(st);
-            iadvance();
+    auto refill = [&](int st) {   // stage st is empty: copy the iterator's item into it and move on
+        if (ig >= P.end) return;
+        if (lane < 2 * kR) {
+            uint64_t *bar = &s_full[warp][st];
+            if (lane == 0) mbar_expect_tx(bar, nx_tx);
+            __syncwarp((1u << (2 * kR)) - 1);               // the expected byte count is posted before any copy can complete
+            if (nx_on) bulk_g2s(my_ring + st * kStageBytes + dst_off, nx_src, nx_bytes, bar, policy);
         }
+        iadvance();
+        iprepare();
+    };
+    iseek();
+    iprepare();
+#pragma unroll
+    for (int st = 0; st < kPS; ++st) refill(st);
 
     unsigned seq = 0;                                       // items consumed by this warp
     for (int g = P.first; g < P.end; ++g) {
-        const PlanGroup &G = P.groups[g];
-        // ---- the previous group is complete on every SM (its outputs are this group's inputs)
-        __syncthreads();                                    // this CTA's warps are done with group g-1 and its staged activations
-        if (g > P.first && threadIdx.x == 0) {
-            __threadfence();
-            const unsigned old = atomicAdd(P.cnt + (g - 1), 1u);
-            if (old == gridDim.x - 1 && g - 1 > P.first) P.cnt[g - 2] = 0;   // everybody has left barrier g-2: re-arm it for the next launch
-            const long long t0 = clock64();
-            while (ld_acquire(P.cnt + (g - 1)) < gridDim.x)
-                if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
-        }
+        const PlanGroup &G = tab[g];
+        long long *tr = P.trace && threadIdx.x == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * 16 : nullptr;
+        if (tr) tr[0] = clock64(), tr[8] = tr[11] = 0;
+        bar_sync(kBarRelease, kThreads);                    // group g-1 is complete on every SM
+        if (tr) tr[4] = clock64();
+        if (!(P.flags & 2) || g == P.first) stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale);
+        if (tr) tr[7] = clock64();
         __syncthreads();
-        stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale);
-        __syncthreads();
+        if (tr) tr[5] = clock64();
 
-        // ---- this warp's row pairs of the group
-        const int nb = G.nb, nseg = G.nseg, npairs = G.npairs;
-        for (int pair = first_pair(G); pair < npairs; pair += GW) {
-            float acc0 = 0.f, acc1 = 0.f;
+        // ---- this warp's units of the group
+        const int nb = G.nb, nseg = G.nseg, nunits = G.nunits;
+        const bool cached = kActCache && nseg == 1;
+        ActCache C;
+        if (cached) {
+#pragma unroll
+            for (int u = 0; u < kSegBlocks / 32; ++u) {
+                const int b = min(lane + 32 * u, nb - 1);
+                C.al[u] = s_lo[b], C.ah[u] = s_hi[b], C.ds[u] = s_ds[b];
+            }
+        }
+        bool first_item = tr != nullptr;
+        int deferred = -1;                                  // the stage emptied by the warp's last item of the group: refilled after the arrival
+        for (int unit = first_unit(G); unit < nunits; unit += GW) {
+            float acc[kR];
+#pragma unroll
+            for (int r = 0; r < kR; ++r) acc[r] = 0.f;
+            // where the unit's results go (looked up while the stage is still on its way): row r of the unit ends up in lane r*(32/kR)
+            int m = 0;
+#pragma unroll
+            for (int mm = 1; mm < kPlanMats; ++mm)
+                if (unit >= G.unit_begin[mm]) m = mm;
+            const int my_r = lane / (32 / kR);
+            const int o_row = kR * (unit - G.unit_begin[m]) + my_r;
+            const bool o_on = lane % (32 / kR) == 0 && o_row < G.rows[m];
+            float *o_ptr = G.out[m] + o_row;
+            const float *o_res = G.res[m] ? G.res[m] + o_row : nullptr;
+            const bool last_unit = unit + GW >= nunits;
             for (int seg = 0; seg < nseg; ++seg, ++seq) {
                 const int st = seq % kPS;
                 {
@@ -252,63 +482,45 @@ __global__ void __launch_bounds__(kPW * 32, 1) plan_q4_0_kernel(const __grid_con
                             if (clock64() - t0 > kSpinLimit) { *P.err = 2; break; }
                     }
                 }
+                if (first_item) tr[8] = clock64();
                 const uint8_t *stage = my_ring + st * kStageBytes;
-                const uint4 *q0 = reinterpret_cast<const uint4 *>(stage), *q1 = reinterpret_cast<const uint4 *>(stage + kRowQ);
-                const __half *d0 = reinterpret_cast<const __half *>(stage + 2 * kRowQ), *d1 = reinterpret_cast<const __half *>(stage + 2 * kRowQ + kRowS);
                 const int kb0 = seg * kSegBlocks, segb = min(kSegBlocks, nb - kb0);
-#pragma unroll
-                for (int u = 0; u < kSegBlocks / 32; ++u) {
-                    const int b = lane + 32 * u;
-                    if (b < segb) {
-                        const uint4 w0 = q0[b], w1 = q1[b];
-                        const float dw0 = __half2float(d0[b]), dw1 = __half2float(d1[b]);
-                        const uint4 al = s_lo[kb0 + b], ah = s_hi[kb0 + b];
-                        const int2 ds = s_ds[kb0 + b];
-                        const float dy = __int_as_float(ds.x);
-                        const int bias = -8 * ds.y;                      // sum (q-8)*y = sum q*y - 8*sum y (exact in int32)
-                        int l0 = dp4a_us(w0.x & 0x0f0f0f0fu, (int)al.x, bias), l1 = dp4a_us(w1.x & 0x0f0f0f0fu, (int)al.x, bias);
-                        l0 = dp4a_us(w0.y & 0x0f0f0f0fu, (int)al.y, l0), l1 = dp4a_us(w1.y & 0x0f0f0f0fu, (int)al.y, l1);
-                        l0 = dp4a_us(w0.z & 0x0f0f0f0fu, (int)al.z, l0), l1 = dp4a_us(w1.z & 0x0f0f0f0fu, (int)al.z, l1);
-                        l0 = dp4a_us(w0.w & 0x0f0f0f0fu, (int)al.w, l0), l1 = dp4a_us(w1.w & 0x0f0f0f0fu, (int)al.w, l1);
-                        // high nibbles stay in place (= 16*q as unsigned bytes); their sum is an exact multiple of 16
-                        int h0 = dp4a_us(w0.x & 0xf0f0f0f0u, (int)ah.x, 0), h1 = dp4a_us(w1.x & 0xf0f0f0f0u, (int)ah.x, 0);
-                        h0 = dp4a_us(w0.y & 0xf0f0f0f0u, (int)ah.y, h0), h1 = dp4a_us(w1.y & 0xf0f0f0f0u, (int)ah.y, h1);
-                        h0 = dp4a_us(w0.z & 0xf0f0f0f0u, (int)ah.z, h0), h1 = dp4a_us(w1.z & 0xf0f0f0f0u, (int)ah.z, h1);
-                        h0 = dp4a_us(w0.w & 0xf0f0f0f0u, (int)ah.w, h0), h1 = dp4a_us(w1.w & 0xf0f0f0f0u, (int)ah.w, h1);
-                        acc0 = fmaf(dw0 * dy, (float)(l0 + (h0 >> 4)), acc0);
-                        acc1 = fmaf(dw1 * dy, (float)(l1 + (h1 >> 4)), acc1);
-                    }
+                if (cached) {
+                    if (segb == kSegBlocks) stage_dots<true, true>(stage, C, s_lo, s_hi, s_ds, kb0, segb, lane, acc);
+                    else stage_dots<true, false>(stage, C, s_lo, s_hi, s_ds, kb0, segb, lane, acc);
+                } else {
+                    if (segb == kSegBlocks) stage_dots<false, true>(stage, C, s_lo, s_hi, s_ds, kb0, segb, lane, acc);
+                    else stage_dots<false, false>(stage, C, s_lo, s_hi, s_ds, kb0, segb, lane, acc);
                 }
                 __syncwarp();                               // every lane has read the stage: it can be refilled
-                if (ig < P.end) {
-                    if (lane == 0) issue(st);
-                    iadvance();
-                }
+                if (first_item) tr[9] = clock64();
+                if (last_unit && seg == nseg - 1) deferred = st;   // not urgent (it is for a later group): after the arrival
+                else refill(st);
+                if (first_item) tr[10] = clock64(), first_item = false;
             }
-            const float v0 = warp_sum(acc0), v1 = warp_sum(acc1);
-            if (lane == 0) {
-                int m = 0;
+            // kR sums with one transposing butterfly: each step halves the values a lane carries (the lane keeps the rows of its own
+            // half and hands the others over), then plain steps finish the sum inside a 32/kR-lane segment: 5 or 6 shuffles, not 5*kR
+            float v;
+            if (kR == 2) {
+                const bool up = lane & 16;
+                v = (up ? acc[1] : acc[0]) + __shfl_xor_sync(0xffffffffu, up ? acc[0] : acc[1], 16);
+            } else {
+                const bool up = lane & 16, up2 = lane & 8;
+                const float a = (up ? acc[2] : acc[0]) + __shfl_xor_sync(0xffffffffu, up ? acc[0] : acc[2], 16);
+                const float b = (up ? acc[3] : acc[1]) + __shfl_xor_sync(0xffffffffu, up ? acc[1] : acc[3], 16);
+                v = (up2 ? b : a) + __shfl_xor_sync(0xffffffffu, up2 ? a : b, 8);
+            }
 #pragma unroll
-                for (int mm = 1; mm < kPlanMats; ++mm)
-                    if (mm < G.nmat && pair >= G.pair_begin[mm]) m = mm;
-                const int r0 = 2 * (pair - G.pair_begin[m]);
-                float *out = G.out[m];
-                const float *res = G.res[m];
-                out[r0] = res ? __fadd_rn(v0, __ldcg(res + r0)) : v0;
-                if (r0 + 1 < G.rows[m]) out[r0 + 1] = res ? __fadd_rn(v1, __ldcg(res + r0 + 1)) : v1;
+            for (int o = 16 / kR; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (o_on) {
+                *o_ptr = o_res ? __fadd_rn(v, __ldcg(o_res)) : v;
+                if (tr && tr[11] == 0) tr[11] = clock64();
             }
         }
-    }
-    // ---- leave every counter at zero for the next launch
-    __syncthreads();
-    if (threadIdx.x == 0 && P.end - P.first > 1) {
-        const int last = P.end - 1;
-        __threadfence();
-        const unsigned old = atomicAdd(P.cnt + last, 1u);
-        if (old == gridDim.x - 1) {
-            if (last - 1 >= P.first) P.cnt[last - 1] = 0;
-            P.cnt[last] = 0;
-        }
+        if (tr) tr[6] = clock64();
+        __syncwarp();
+        bar_arrive(kBarArrived, kThreads);                  // this warp's results of group g are stored; never blocks
+        if (deferred >= 0) refill(deferred);
     }
 }
 
@@ -320,6 +532,8 @@ struct tb200_plan {
     PlanGroup *d_groups;
     unsigned *d_cnt;
     int *d_err;
+    long long *d_trace;
+    int grid;
     size_t smem;
 };
 
@@ -343,7 +557,7 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
         else if (s.prologue == TB200_PLAN_RMSNORM && !s.norm_weight) bad = "RMSNORM needs norm_weight";
         else if (s.prologue == TB200_PLAN_SWIGLU && !s.x2) bad = "SWIGLU needs x2";
         else if (((uintptr_t)s.x | (uintptr_t)s.x2 | (uintptr_t)s.norm_weight) & 15) bad = "inputs must be 16-byte aligned";
-        long pairs = 0;
+        long units = 0;
         for (int m = 0; m < s.n && !bad; ++m) {
             const tb200_weights *w = s.w[m];
             if (!w || w->type != TB200_TYPE_Q4_0) bad = "only Q4_0 weights (use the per-matrix API for the other types)";
@@ -351,23 +565,23 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
             else if (w->rows < 1 || !s.out[m]) bad = "empty matrix or missing output";
             else if (w->device != c->device) bad = "weights live on another device";
             if (bad) break;
-            G.pair_begin[m] = (int)pairs;
-            pairs += (w->rows + 1) / 2;
+            G.unit_begin[m] = (int)units;
+            units += (w->rows + kR - 1) / kR;
             G.rows[m] = (int)w->rows, G.qs[m] = (const uint4 *)w->qs, G.sc[m] = (const __half *)w->sc, G.out[m] = s.out[m], G.res[m] = s.residual[m];
         }
         if (bad) { tb200_set_error("plan_create: group %d: %s", g, bad); free(h); return nullptr; }
-        for (int m = s.n; m <= kPlanMats; ++m) G.pair_begin[m] = (int)pairs;
+        for (int m = s.n; m <= kPlanMats; ++m) G.unit_begin[m] = (int)units;
         G.x = s.x, G.x2 = s.x2, G.nw = s.norm_weight, G.eps = s.eps, G.prologue = s.prologue;
         G.nmat = s.n, G.nb = (int)(s.w[0]->k / QK), G.nseg = (G.nb + kSegBlocks - 1) / kSegBlocks;
-        G.npairs = (int)pairs, G.rot = (int)(rot % GW);
-        rot += pairs;                                       // the pairs left over by one group go to the warps after them in the next
+        G.nunits = (int)units, G.rot = (int)(rot % GW);
+        rot += units;                                       // the units left over by one group go to the warps after them in the next
         nb_max = G.nb > nb_max ? G.nb : nb_max;
     }
     tb200_plan *p = new tb200_plan();
     memset(p, 0, sizeof(*p));
     p->n_groups = n_groups, p->nb_max = nb_max, p->device = c->device;
-    p->smem = (size_t)kPW * kPS * kStageBytes + (size_t)nb_max * 40;
-    bool ok = p->smem <= 220 * 1024;
+    p->smem = (size_t)kPW * kPS * kStageBytes + (size_t)nb_max * 40;   // + the launch's descriptor table (tb200_plan_run)
+    bool ok = p->smem + 16 * sizeof(PlanGroup) <= kPlanSmemMax;
     if (!ok) tb200_set_error("plan_create: K = %d does not fit the activation staging", nb_max * QK);
     ok = ok && cudaMalloc((void **)&p->d_groups, (size_t)n_groups * sizeof(PlanGroup)) == cudaSuccess;
     ok = ok && cudaMalloc((void **)&p->d_cnt, (size_t)(n_groups + 1) * 4 + 16) == cudaSuccess;
@@ -375,7 +589,7 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
         p->d_err = (int *)(p->d_cnt + n_groups + 1);
         ok = cudaMemcpy(p->d_groups, h, (size_t)n_groups * sizeof(PlanGroup), cudaMemcpyHostToDevice) == cudaSuccess &&
              cudaMemset(p->d_cnt, 0, (size_t)(n_groups + 1) * 4 + 16) == cudaSuccess &&
-             cudaFuncSetAttribute(plan_q4_0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem) == cudaSuccess;
+             cudaFuncSetAttribute(plan_q4_0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess;
         if (!ok) tb200_set_error("plan_create: %s", cudaGetErrorString(cudaGetLastError()));
     } else cudaGetLastError();
     free(h);
@@ -387,14 +601,24 @@ int tb200_plan_run(tb200_plan *p, int first, int count) {
     tb200_ctx *c = tb200_get_ctx();
     if (!c) return TB200_ERR_NO_DEVICE;
     if (!p || first < 0 || count < 0 || first + count > p->n_groups || p->device != c->device) { tb200_set_error("plan_run: bad arguments"); return TB200_ERR_INVALID; }
-    if (count == 0) return TB200_OK;
-    PlanParams P;
-    P.groups = p->d_groups, P.first = first, P.end = first + count, P.cnt = p->d_cnt, P.err = p->d_err, P.nb_max = p->nb_max;
-    // one CTA per SM, all co-resident (the groups synchronise through arrival counters); plain stream order, no PDL: the
-    // kernel owns the whole GPU for the step
-    plan_q4_0_kernel<<<dim3((unsigned)c->sm_count), dim3(kPW * 32), p->smem, c->stream>>>(P);
-    tb200_count_launch();
-    TB_CUDA(cudaGetLastError());
+    // the descriptors of a launch live in shared memory: longer sequences go out as several launches
+    const int per_launch = (int)((kPlanSmemMax - p->smem) / sizeof(PlanGroup));
+    for (int g0 = first; g0 < first + count; g0 += per_launch) {
+        const int n = first + count - g0 < per_launch ? first + count - g0 : per_launch;
+        PlanParams P;
+        P.groups = p->d_groups, P.first = g0, P.end = g0 + n, P.cnt = p->d_cnt, P.err = p->d_err, P.nb_max = p->nb_max;
+        P.trace = p->d_trace;
+        static const int flags = [] { const char *v = getenv("TB200_PLAN_FLAGS"); return v && *v ? atoi(v) : 0; }();
+        P.flags = flags;
+        static const int ahead = [] { const char *v = getenv("TB200_PLAN_AHEAD"); return v && *v ? atoi(v) : 0; }();
+        P.ahead = ahead;
+        p->grid = c->sm_count;
+        // one CTA per SM, all co-resident (the groups synchronise through arrival counters); plain stream order, no PDL: the
+        // kernel owns the whole GPU for the step
+        plan_q4_0_kernel<<<dim3((unsigned)c->sm_count), dim3(kTW * 32), p->smem + (size_t)n * sizeof(PlanGroup), c->stream>>>(P);
+        tb200_count_launch();
+        TB_CUDA(cudaGetLastError());
+    }
     return TB200_OK;
 }
 
@@ -411,8 +635,24 @@ int tb200_plan_reset(tb200_plan *p) {
     return TB200_OK;
 }
 
+// Debug aid: per group and CTA, the SM clock at {loop top, CTA done with g-1, arrived, barrier complete, CTA released,
+// activations staged, warp 0 done}. Call once before tb200_plan_run to switch it on; copies out after a run. out: [n_groups][grid][16].
+long tb200_plan_trace(tb200_plan *p, long long *out, long capacity) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!p || !c) return -1;
+    const long n = (long)p->n_groups * c->sm_count * 16;
+    if (!p->d_trace) {
+        if (cudaMalloc((void **)&p->d_trace, (size_t)n * 8) != cudaSuccess || cudaMemset(p->d_trace, 0, (size_t)n * 8) != cudaSuccess) { cudaGetLastError(); p->d_trace = nullptr; return -1; }
+        return 0;
+    }
+    if (!out || capacity < n) return n;
+    if (cudaMemcpy(out, p->d_trace, (size_t)n * 8, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); return -1; }
+    return n;
+}
+
 void tb200_plan_free(tb200_plan *p) {
     if (!p) return;
+    if (p->d_trace) cudaFree(p->d_trace);
     if (p->d_groups) cudaFree(p->d_groups);
     if (p->d_cnt) cudaFree(p->d_cnt);
     delete p;

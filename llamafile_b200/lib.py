@@ -57,7 +57,7 @@ def lib() -> C.CDLL:
         "tb200_quantize_row_q8_0": (C.c_bool, [vp, vp, C.c_int64]), "tb200_quantize_row_q8_K": (C.c_bool, [vp, vp, C.c_int64]),
         "tb200_fp32_to_fp16_row": (C.c_bool, [vp, vp, C.c_int64]), "tb200_weights_cache_clear": (None, []),
         "tb200_register_weights": (i, [vp, sz]), "tb200_unregister_weights": (i, [vp]), "tb200_weights_cache_bytes": (sz, []),
-        "tb200_plan_create": (vp, [i, vp]), "tb200_plan_run": (i, [vp, i, i]), "tb200_plan_status": (i, [vp]), "tb200_plan_reset": (i, [vp]),
+        "tb200_plan_create": (vp, [i, vp]), "tb200_plan_run": (i, [vp, i, i]), "tb200_plan_status": (i, [vp]), "tb200_plan_reset": (i, [vp]), "tb200_plan_trace": (l, [vp, vp, l]),
         "tb200_plan_free": (None, [vp]),
         "tb200_gguf_open": (vp, [C.c_char_p]), "tb200_gguf_close": (None, [vp]), "tb200_gguf_tensor_count": (l, [vp]),
         "tb200_gguf_tensor_name": (C.c_char_p, [vp, l]), "tb200_gguf_find": (i, [vp, C.c_char_p, vp, vp, vp, vp]),
@@ -250,6 +250,16 @@ class Plan:
         _check(lib().tb200_plan_run(self.handle, first, self.n - first if count is None else count), "plan_run")
 
     def status(self) -> int: return int(lib().tb200_plan_status(self.handle))
+
+    def trace(self):
+        """First call: switch phase stamps on. Later calls: numpy [n_groups, SMs, 8] int64 of SM-clock stamps (debug aid)."""
+        import numpy as np
+        n = lib().tb200_plan_trace(self.handle, None, 0)
+        if n <= 0:
+            return None
+        out = np.zeros(n, np.int64)
+        lib().tb200_plan_trace(self.handle, out.ctypes.data, n)
+        return out.reshape(self.n, -1, 16)
     def reset(self): _check(lib().tb200_plan_reset(self.handle), "plan_reset")
 
     def free(self):

@@ -110,7 +110,7 @@ def test_plan_equals_one_shot_quantizer(tb):
     W = q4_bytes(96, K, seed=1)
     w = tb.Weights(W, H.Q4_0, 96, K)
     for row in H.adversarial_rows(K)[:13]:
-        if not np.isfinite(row).all() or np.abs(row).max() > 1e30:
+        if not np.isfinite(row).all() or np.abs(row).max() / 127 > 65504:   # fp16 block scale would overflow to inf on either path
             continue
         out_p = torch.full((96,), float("nan"), device="cuda")
         plan = tb.Plan([{"w": [w], "out": [out_p], "x": dev(row)}])
