@@ -59,6 +59,12 @@ def lib() -> C.CDLL:
         "tb200_register_weights": (i, [vp, sz]), "tb200_unregister_weights": (i, [vp]), "tb200_weights_cache_bytes": (sz, []),
         "tb200_plan_create": (vp, [i, vp]), "tb200_plan_run": (i, [vp, i, i]), "tb200_plan_status": (i, [vp]), "tb200_plan_reset": (i, [vp]), "tb200_plan_trace": (l, [vp, vp, l]),
         "tb200_plan_free": (None, [vp]),
+        "tb200_backend_link": (C.c_bool, [vp]), "tb200_backend_init": (vp, [i]), "tb200_backend_is_tb200": (C.c_bool, [vp]),
+        "tb200_backend_buffer_type": (vp, [i]), "tb200_backend_host_buffer_type": (vp, []), "tb200_backend_split_buffer_type": (vp, [vp]),
+        "tb200_backend_reg_devices": (i, []), "tb200_backend_get_device_count": (i, []), "tb200_backend_get_device_memory": (None, [i, vp, vp]),
+        "tb200_backend_get_device_description": (None, [i, C.c_char_p, sz]), "tb200_backend_get_device_properties": (None, [i, vp]),
+        "tb200_backend_register_host_buffer": (C.c_bool, [vp, sz]), "tb200_backend_unregister_host_buffer": (None, [vp]),
+        "tb200_backend_last_graph_stats": (None, [vp, vp, vp]),
         "tb200_gguf_open": (vp, [C.c_char_p]), "tb200_gguf_close": (None, [vp]), "tb200_gguf_tensor_count": (l, [vp]),
         "tb200_gguf_tensor_name": (C.c_char_p, [vp, l]), "tb200_gguf_find": (i, [vp, C.c_char_p, vp, vp, vp, vp]),
         "tb200_gguf_upload": (vp, [vp, C.c_char_p, l, l]),
@@ -319,3 +325,22 @@ class GgufFile:
             self.close()
         except Exception:
             pass
+
+
+# ---- ggml backend (include/tb200_ggml_backend.h)
+def backend_link(api_table: int | None = None) -> bool:
+    """tb200_backend_link: api_table = address of the host's ggml_backend_api table, or None for the stand-alone host."""
+    return bool(lib().tb200_backend_link(api_table))
+
+
+def backend_init(device: int = 0) -> int:
+    h = lib().tb200_backend_init(device)
+    if not h:
+        raise TB200Error("backend_init: " + lib().tb200_last_error().decode(errors="replace"))
+    return h
+
+
+def backend_last_graph_stats(backend: int):
+    a, b = C.c_int(), C.c_int()
+    lib().tb200_backend_last_graph_stats(backend, C.byref(a), C.byref(b))
+    return a.value, b.value

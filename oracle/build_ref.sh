@@ -24,7 +24,7 @@ if [ ! -d "$REF/llamafile" ]; then
 fi
 mkdir -p "$OUT"
 STAMP="$OUT/.stamp"
-SIG="$(cat "$HERE/ref_wrap.cpp" "$HERE/ref_ops.c" "$HERE/build_ref.sh" | sha1sum | cut -d' ' -f1)"
+SIG="$(cat "$HERE/ref_wrap.cpp" "$HERE/ref_ops.c" "$HERE/build_ref.sh" "$HERE/../include/tb200_ggml_backend.h" | sha1sum | cut -d' ' -f1)"
 if [ -f "$OUT/libtb200_ref.so" ] && [ -f "$STAMP" ] && [ "$(cat "$STAMP")" = "$SIG" ]; then
   exit 0
 fi
@@ -83,12 +83,14 @@ GG="$REF/llama.cpp/ggml"
 ( cd "$S" && gcc -O2 -fPIC -fvisibility=hidden -mavx -mavx2 -mfma -mf16c -ffp-contract=off -DNDEBUG -w \
       -I. -Ishim -c llama.cpp/ggml-quants-amd-avx2.c -o obj/lf_quants_avx2.o ) & pids+=($!)
 for f in ggml ggml-quants ggml-aarch64 ggml-alloc ggml-backend; do
-  ( gcc -O2 -fPIC -fvisibility=hidden -mavx -mavx2 -mfma -mf16c -ffp-contract=off -D_GNU_SOURCE \
+  # default visibility: tests drive ggml's own graph / backend machinery (ggml_init, ggml_mul_mat, ggml_backend_graph_compute ...)
+  # through ctypes to run the SAME graph on ggml's CPU backend and on the TB200 backend (tests/test_gpu_backend.py)
+  ( gcc -O2 -fPIC -fvisibility=default -mavx -mavx2 -mfma -mf16c -ffp-contract=off -D_GNU_SOURCE \
         -DNDEBUG -w -Dquantize_row_q8_0=upstream_quantize_row_q8_0 -I"$GG/include" -I"$GG/src" -c "$GG/src/$f.c" -o "$S/obj/up_$f.o" ) & pids+=($!)
 done
 ( g++ $CXXF $AVX2 -fopenmp -c "$HERE/ref_wrap.cpp" -o "$S/obj/ref_wrap.o" ) & pids+=($!)
 # the matmul's neighbours (rms_norm, silu, mul, add) through the pristine ggml's own graph compute
-( gcc -O2 -fPIC -fvisibility=hidden -w -I"$GG/include" -c "$HERE/ref_ops.c" -o "$S/obj/ref_ops.o" ) & pids+=($!)
+( gcc -O2 -fPIC -fvisibility=hidden -w -I"$GG/include" -I"$GG/src" -I"$HERE/../include" -c "$HERE/ref_ops.c" -o "$S/obj/ref_ops.o" ) & pids+=($!)
 for p in "${pids[@]}"; do wait "$p"; done
 
 g++ -shared -fopenmp -o "$OUT/libtb200_ref.so" "$S"/obj/*.o -lm -lpthread

@@ -5,9 +5,14 @@
  * llama.cpp/src/llama.cpp:8099-8225) and ggml_silu + ggml_mul (llm_build_ffn, LLM_FFN_SILU + LLM_FFN_PAR). Nothing here
  * computes: each function builds a two-node ggml graph and runs ggml_graph_compute_with_ctx on it. Compiled against the
  * pristine ggml.h so the struct layouts agree with the ggml.c objects it is linked with. */
+#include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include "ggml.h"
+#include "ggml-backend.h"
+#include "ggml-backend-impl.h"
+#include "tb200_ggml_backend.h"   /* the product's mirror of llamafile's ggml_backend_api table, filled below with the reference's functions */
 
 #define EXPORT __attribute__((visibility("default")))
 
@@ -51,4 +56,76 @@ EXPORT void ref_add(const float *x, const float *r, long n, float *y) {
     memcpy(b->data, r, (size_t)n * 4);
     compute(ctx, ggml_add(ctx, a, b), y, n);
     ggml_free(ctx);
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * The host side of llamafile's DSO handshake for tests: llamafile passes `ggml_backend_api()`
+ * (llama.cpp.patches/patches/ggml-backend.c.patch) to ggml_cuda_link(); here the same table is filled with the pristine
+ * ggml's functions and handed to tb200_backend_link(), so the TB200 backend is driven by the reference's own
+ * ggml-backend.c / ggml-alloc.c machinery (ggml_backend_alloc_ctx_tensors, ggml_backend_tensor_set, ggml_backend_graph_compute).
+ * It also proves the mirrored struct layouts at run time: ggml's code dereferences the backend's objects directly.
+ * --------------------------------------------------------------------------------------------- */
+static bool g_log_disable = false;
+static long host_write(int fd, const void *p, long n) { return write(fd, p, (size_t)n); }
+
+EXPORT const struct tb200_ggml_backend_api *ref_backend_api(void) {
+    static struct tb200_ggml_backend_api api;
+    memset(&api, 0, sizeof api);
+    api.FLAG_log_disable = &g_log_disable;
+    api.exit = exit, api.free = free, api.malloc = malloc, api.getenv = getenv, api.write = host_write;
+    api.ggml_backend_register = (void *)ggml_backend_register;
+    api.ggml_backend_buffer_init = (void *)ggml_backend_buffer_init;
+    api.ggml_backend_cpu_buffer_from_ptr = (void *)ggml_backend_cpu_buffer_from_ptr;
+    api.ggml_backend_cpu_buffer_type = (void *)ggml_backend_cpu_buffer_type;
+    api.ggml_backend_buft_get_alloc_size = (void *)ggml_backend_buft_get_alloc_size;
+    api.ggml_backend_buft_alloc_buffer = (void *)ggml_backend_buft_alloc_buffer;
+    api.ggml_backend_is_cpu = (void *)ggml_backend_is_cpu;
+    api.ggml_backend_tensor_get = (void *)ggml_backend_tensor_get;
+    api.ggml_backend_tensor_set = (void *)ggml_backend_tensor_set;
+    api.ggml_is_quantized = (void *)ggml_is_quantized;
+    api.ggml_type_size = (void *)ggml_type_size;
+    api.ggml_blck_size = (void *)ggml_blck_size;
+    api.ggml_is_transposed = (void *)ggml_is_transposed;
+    api.ggml_nbytes = (void *)ggml_nbytes;
+    api.ggml_get_unary_op = (void *)ggml_get_unary_op;
+    api.ggml_nelements = (void *)ggml_nelements;
+    api.ggml_nrows = (void *)ggml_nrows;
+    api.ggml_is_permuted = (void *)ggml_is_permuted;
+    api.ggml_is_contiguous = (void *)ggml_is_contiguous;
+    api.ggml_op_name = (void *)ggml_op_name;
+    api.ggml_type_name = (void *)ggml_type_name;
+    api.ggml_element_size = (void *)ggml_element_size;
+    api.ggml_row_size = (void *)ggml_row_size;
+    api.ggml_rope_yarn_corr_dims = (void *)ggml_rope_yarn_corr_dims;
+    api.ggml_op_desc = (void *)ggml_op_desc;
+    api.ggml_backend_buffer_is_host = (void *)ggml_backend_buffer_is_host;
+    api.ggml_guid_matches = (void *)ggml_guid_matches;
+    api.ggml_is_empty = (void *)ggml_is_empty;
+    api.ggml_backend_buffer_get_usage = (void *)ggml_backend_buffer_get_usage;
+    api.ggml_are_same_shape = (void *)ggml_are_same_shape;
+    api.ggml_is_contiguous_1 = (void *)ggml_is_contiguous_1;
+    api.ggml_is_contiguous_2 = (void *)ggml_is_contiguous_2;
+    return &api;
+}
+
+/* struct layouts and enum values of the reference, for tests/test_abi.py to compare with include/tb200_ggml_backend.h */
+EXPORT int ref_backend_abi(long *out, int cap) {
+    const long v[] = {
+        GGML_OP_NONE, GGML_OP_MUL_MAT, GGML_OP_MUL_MAT_ID, GGML_OP_RESHAPE, GGML_OP_VIEW, GGML_OP_PERMUTE, GGML_OP_TRANSPOSE,
+        GGML_STATUS_ALLOC_FAILED, GGML_STATUS_FAILED, GGML_STATUS_SUCCESS, GGML_STATUS_ABORTED,
+        GGML_BACKEND_BUFFER_USAGE_ANY, GGML_BACKEND_BUFFER_USAGE_WEIGHTS, GGML_BACKEND_BUFFER_USAGE_COMPUTE,
+        offsetof(struct ggml_tensor, type), offsetof(struct ggml_tensor, buffer), offsetof(struct ggml_tensor, ne), offsetof(struct ggml_tensor, nb),
+        offsetof(struct ggml_tensor, op), offsetof(struct ggml_tensor, op_params), offsetof(struct ggml_tensor, flags), offsetof(struct ggml_tensor, src),
+        offsetof(struct ggml_tensor, view_src), offsetof(struct ggml_tensor, view_offs), offsetof(struct ggml_tensor, data),
+        offsetof(struct ggml_cgraph, n_nodes), offsetof(struct ggml_cgraph, nodes),
+        sizeof(struct ggml_backend_buffer_type_i), sizeof(struct ggml_backend_buffer_type), offsetof(struct ggml_backend_buffer_type, context),
+        sizeof(struct ggml_backend_buffer_i), sizeof(struct ggml_backend_buffer), offsetof(struct ggml_backend_buffer, buft),
+        offsetof(struct ggml_backend_buffer, context), offsetof(struct ggml_backend_buffer, size), offsetof(struct ggml_backend_buffer, usage),
+        sizeof(struct ggml_backend_i), offsetof(struct ggml_backend_i, graph_compute), offsetof(struct ggml_backend_i, supports_op),
+        offsetof(struct ggml_backend_i, supports_buft), offsetof(struct ggml_backend_i, event_synchronize),
+        sizeof(struct ggml_backend), offsetof(struct ggml_backend, iface), offsetof(struct ggml_backend, context),
+    };
+    const int n = (int)(sizeof v / sizeof v[0]);
+    for (int i = 0; i < n && i < cap; ++i) out[i] = v[i];
+    return n;
 }

@@ -22,7 +22,7 @@ def tbmod():
 
 
 def declared_symbols():
-    text = (ROOT / "include" / "tinyblas_b200.h").read_text()
+    text = (ROOT / "include" / "tinyblas_b200.h").read_text() + (ROOT / "include" / "tb200_ggml_backend.h").read_text()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     return sorted(set(re.findall(r"TB200_API\s+[\w\s\*]+?\b(\w+)\s*\(", text)))
 
@@ -30,7 +30,8 @@ def declared_symbols():
 def test_header_symbols_exported(tbmod):
     names = declared_symbols()
     assert {"llamafile_sgemm", "llamafile_mixmul", "llamafile_mixmul_needs", "llamafile_mixmul_iqk", "tb200_link",
-            "tb200_mul_mat", "tb200_mixmul_dev", "tb200_quantize_q8_0_dev", "tb200_quantize_q8_K_dev"} <= set(names)
+            "tb200_mul_mat", "tb200_mixmul_dev", "tb200_quantize_q8_0_dev", "tb200_quantize_q8_K_dev", "tb200_plan_create",
+            "tb200_backend_link", "tb200_backend_init", "tb200_backend_buffer_type", "tb200_register_weights"} <= set(names)
     raw = C.CDLL(str(tbmod.lib()._name))
     missing = [n for n in names if not hasattr(raw, n)]
     assert not missing, missing
@@ -84,3 +85,46 @@ def test_c_loader_handshake(tbmod):
     ready = L.tb200_loader_init(str(tbmod.lib()._name).encode())
     assert ready == (1 if tbmod.device_count() > 0 else 0)
     assert L.tb200_loader_ready() == ready
+
+
+def test_backend_struct_layouts_match_reference(tmp_path):
+    """include/tb200_ggml_backend.h mirrors ggml's backend interface structs and enum values; a probe compiled against OUR header must
+    print the numbers the reference's own headers give (oracle/ref_ops.c ref_backend_abi, compiled against llama.cpp/ggml)."""
+    import ctypes as C
+    import subprocess
+    from oracle import binding as B
+    r = B.reference()
+    if r is None:
+        pytest.skip("oracle/_ref not built")
+    src = tmp_path / "probe.c"
+    src.write_text(r"""
+#include <stdio.h>
+#include <stddef.h>
+#include "tb200_ggml_backend.h"
+int main(void) {
+    const long v[] = {
+        TB200_GGML_OP_NONE, TB200_GGML_OP_MUL_MAT, TB200_GGML_OP_MUL_MAT_ID, TB200_GGML_OP_RESHAPE, TB200_GGML_OP_VIEW, TB200_GGML_OP_PERMUTE, TB200_GGML_OP_TRANSPOSE,
+        TB200_GGML_STATUS_ALLOC_FAILED, TB200_GGML_STATUS_FAILED, TB200_GGML_STATUS_SUCCESS, TB200_GGML_STATUS_ABORTED,
+        TB200_GGML_BUFFER_USAGE_ANY, TB200_GGML_BUFFER_USAGE_WEIGHTS, TB200_GGML_BUFFER_USAGE_COMPUTE,
+        offsetof(tb200_ggml_tensor_view, type), offsetof(tb200_ggml_tensor_view, buffer_), offsetof(tb200_ggml_tensor_view, ne), offsetof(tb200_ggml_tensor_view, nb),
+        offsetof(tb200_ggml_tensor_view, op_), offsetof(tb200_ggml_tensor_view, op_params_), offsetof(tb200_ggml_tensor_view, flags_), offsetof(tb200_ggml_tensor_view, src_),
+        offsetof(tb200_ggml_tensor_view, view_src_), offsetof(tb200_ggml_tensor_view, view_offs_), offsetof(tb200_ggml_tensor_view, data),
+        offsetof(tb200_ggml_cgraph_view, n_nodes), offsetof(tb200_ggml_cgraph_view, nodes),
+        sizeof(struct tb200_ggml_backend_buffer_type_i), sizeof(struct tb200_ggml_backend_buffer_type), offsetof(struct tb200_ggml_backend_buffer_type, context),
+        sizeof(struct tb200_ggml_backend_buffer_i), sizeof(struct tb200_ggml_backend_buffer), offsetof(struct tb200_ggml_backend_buffer, buft),
+        offsetof(struct tb200_ggml_backend_buffer, context), offsetof(struct tb200_ggml_backend_buffer, size), offsetof(struct tb200_ggml_backend_buffer, usage),
+        sizeof(struct tb200_ggml_backend_i), offsetof(struct tb200_ggml_backend_i, graph_compute), offsetof(struct tb200_ggml_backend_i, supports_op),
+        offsetof(struct tb200_ggml_backend_i, supports_buft), offsetof(struct tb200_ggml_backend_i, event_synchronize),
+        sizeof(struct tb200_ggml_backend), offsetof(struct tb200_ggml_backend, iface), offsetof(struct tb200_ggml_backend, context),
+    };
+    for (unsigned i = 0; i < sizeof v / sizeof v[0]; ++i) printf("%ld\n", v[i]);
+    return 0;
+}
+""")
+    exe = tmp_path / "probe"
+    subprocess.check_call(["gcc", "-I", str(ROOT / "include"), str(src), "-o", str(exe)])
+    ours = [int(x) for x in subprocess.check_output([str(exe)], text=True).split()]
+    buf = (C.c_long * 128)()
+    r.lib.ref_backend_abi.argtypes = [C.c_void_p, C.c_int]
+    n = r.lib.ref_backend_abi(buf, 128)
+    assert ours == list(buf[:n])
