@@ -74,38 +74,61 @@ from llamafile_b200.shard import max_shard, shard_rows  # noqa: E402  (row split
 
 
 class ClockSampler(threading.Thread):
+    """SM clock, power and throttle reasons of one GPU, sampled through NVML every ~2 ms (a decode step lasts ~1 ms: nvidia-smi's
+    ~100 ms per query would never land inside the timed region). Falls back to polling nvidia-smi when pynvml is unusable."""
+
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag, self.marks = index, [], False, {}
+        self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it is a plain index list
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = pynvml
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:   # noqa: BLE001
+            self.nv = None
 
     def run(self):
-        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw"
+        if self.nv is not None:
+            nv = self.nv
+            R = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+            while not self.stop_flag:
+                try:
+                    sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                    pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                    self.rows.append((sm, self.sm_max, pw, tuple(k for k, bit in R.items() if mask & bit)))
+                except Exception:   # noqa: BLE001
+                    pass
+                time.sleep(0.002)
+            return
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
-            except Exception:
+                c = [v.strip() for v in out.split(",")]
+                self.rows.append((float(c[0]), float(c[1]), float(c[2]), tuple(n for n, v in zip(names, c[3:7]) if v.lower().startswith("active"))))
+            except Exception:   # noqa: BLE001
                 pass
-            time.sleep(0.1)
+            time.sleep(0.05)
 
     def mark(self, name):
         self.marks[name] = len(self.rows)
 
     def summary(self, lo=0, hi=None):
         rows = self.rows[lo:hi]
-        num = lambda s: s.replace(".", "", 1).isdigit()   # noqa: E731
-        sm = [float(r[0]) for r in rows if r and num(r[0])]
-        mx = [float(r[1]) for r in rows if len(r) > 1 and num(r[1])]
-        pw = [float(r[7]) for r in rows if len(r) > 7 and num(r[7])]
-        reasons = set()
-        for r in rows:
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm), "power_w_max": max(pw) if pw else None}
+        reasons = sorted({r for row in rows for r in row[3]})
+        return {"sm_mhz": statistics.median([r[0] for r in rows]) if rows else None, "sm_max_mhz": max(r[1] for r in rows) if rows else None,
+                "reasons": reasons, "samples": len(rows), "power_w_max": max(r[2] for r in rows) if rows else None,
+                "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
 def measured_peaks():

@@ -36,10 +36,15 @@ enum tb200_type {
     TB200_TYPE_F32 = 0,
     TB200_TYPE_F16 = 1,
     TB200_TYPE_Q4_0 = 2,
+    TB200_TYPE_Q4_1 = 3,    /* the remaining types iqk serves on the same entry points */
+    TB200_TYPE_Q5_0 = 6,
     TB200_TYPE_Q8_0 = 8,
+    TB200_TYPE_Q8_1 = 9,    /* activations of Q4_1 (vec_dot_type) */
     TB200_TYPE_Q4_K = 12,
+    TB200_TYPE_Q5_K = 13,
     TB200_TYPE_Q6_K = 14,   /* the type Q4_K_M files keep output / ffn_down / attn_v in */
     TB200_TYPE_Q8_K = 15,
+    TB200_TYPE_IQ4_XS = 23,
     TB200_TYPE_I32 = 26,
 };
 
@@ -51,6 +56,11 @@ typedef struct { uint16_t d; int8_t qs[32]; } tb200_block_q8_0;
 typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qs[128]; } tb200_block_q4_K;
 typedef struct { float d; int16_t bsums[16]; int8_t qs[256]; } tb200_block_q8_K;
 typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d; } tb200_block_q6_K;   /* ggml-common.h:299-307 */
+typedef struct { uint16_t d, m; uint8_t qs[16]; } tb200_block_q4_1;                                     /* ggml-common.h:151-161 */
+typedef struct { uint16_t d; uint8_t qh[4]; uint8_t qs[16]; } tb200_block_q5_0;                          /* ggml-common.h:164-169 */
+typedef struct { uint16_t d, s; int8_t qs[32]; } tb200_block_q8_1;                                       /* ggml-common.h:193-203 */
+typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qh[32]; uint8_t qs[128]; } tb200_block_q5_K;   /* ggml-common.h:280-295 */
+typedef struct { uint16_t d; uint16_t scales_h; uint8_t scales_l[4]; uint8_t qs[128]; } tb200_block_iq4_xs;   /* ggml-common.h:393-398 */
 #pragma pack(pop)
 
 /* Layout-compatible prefix views of the two ggml structs llamafile_mixmul reads
@@ -88,7 +98,8 @@ typedef struct {
 /* llamafile/sgemm.h:23-24, llamafile/sgemm.cpp:128-131. C[ldc*j + i] = sum_l A[lda*i + l] * B[ldb*j + l],
  * m = weight rows, n = tokens, k/lda/ldb counted in BLOCKS of Atype/Btype, ldc in floats.
  * Serviced (returns true, C written) for the combinations the reference's x86 build services:
- *   Q4_0 x Q8_0, Q8_0 x Q8_0, Q4_K x Q8_K, Q6_K x Q8_K, F16 x F16, F16 x F32 (n <= 2); Ctype F32. (F32 and BF16
+ *   Q4_0 x Q8_0, Q8_0 x Q8_0, Q4_K x Q8_K, Q6_K x Q8_K, Q5_K x Q8_K, IQ4_XS x Q8_K, Q5_0 x Q8_0, Q4_1 x Q8_1,
+ *   F16 x F16, F16 x F32 (n <= 2); Ctype F32. (F32 and BF16
  *   weights, which the reference also serves, are outside north_star's list and are handed back.)
  * Anything else returns false before touching C ("not handled, caller falls back"), never an error.
  * Threading contract: ggml calls this from all nth worker threads. Thread 0 does the whole job
@@ -238,6 +249,18 @@ TB200_API int tb200_plan_reset(tb200_plan *p);
 /* debug: first call switches per-group phase stamps on (returns 0); later calls copy [n_groups][SMs][8] SM-clock stamps out */
 TB200_API long tb200_plan_trace(tb200_plan *p, long long *out, long capacity);
 TB200_API void tb200_plan_free(tb200_plan *p);
+
+/* The matmul's neighbours for any token count (the decode plan fuses the same operations into its kernel):
+ * fp32 device tensors, row-major with leading dimensions in floats. Same IEEE operations in the same order as ggml's CPU ops:
+ *   tb200_rms_norm_mul_dev   y = x * 1/sqrtf(mean(x^2) + eps) * norm_weight     ggml_rms_norm (ggml.c:11850-11896) + ggml_mul
+ *   tb200_silu_mul_dev       y = gate/(1 + expf(-gate)) * up                    ggml_silu (ggml.c:2393) + ggml_mul
+ *   tb200_moe_combine_dev    out[t] = sum_j expert_out[t][j] * weights[t][j]    ggml_mul + ggml_add in expert order (llama.cpp:8303-8318)
+ * and the first two straight into resident activations (transform, then the bit-exact from_float of the vec_dot type). */
+TB200_API int tb200_rms_norm_mul_dev(const float *x, long ldx, const float *norm_weight, float eps, long tokens, long k, float *y, long ldy);
+TB200_API int tb200_silu_mul_dev(const float *gate, const float *up, long ld, long tokens, long k, float *y, long ldy);
+TB200_API int tb200_moe_combine_dev(const float *expert_out, const float *weights, long tokens, int used, long rows, float *out, long ldo);
+TB200_API int tb200_acts_quantize_rmsnorm(tb200_acts *a, const float *x, long ldx, long tokens, const float *norm_weight, float eps, long k);
+TB200_API int tb200_acts_quantize_swiglu(tb200_acts *a, const float *gate, const float *up, long ld, long tokens, long k);
 
 /* Multi-GPU, one process per GPU: weights row-sharded (each rank uploads its row slice), the all-gather of the output
  * slices fused into the kernels as peer stores over NVLink (decode: the GEMV epilogue, one 64-byte segment per CTA and

@@ -91,6 +91,17 @@ void *tb200_scratch(tb200_ctx *c, size_t bytes) {
     return c->scratch;
 }
 
+void *tb200_scratch2(tb200_ctx *c, size_t bytes) {
+    if (bytes <= c->scratch2_bytes) return c->scratch2;
+    cudaStreamSynchronize(c->stream);
+    if (c->scratch2) cudaFree(c->scratch2);
+    c->scratch2 = nullptr, c->scratch2_bytes = 0;
+    const size_t want = round_up(bytes + bytes / 2, 1 << 20);
+    if (cudaMalloc(&c->scratch2, want) != cudaSuccess) { tb200_set_error("scratch2: cudaMalloc(%zu) failed", want); cudaGetLastError(); return nullptr; }
+    c->scratch2_bytes = want;
+    return c->scratch2;
+}
+
 // ------------------------------------------------------------------------------------------------
 extern "C" {
 
@@ -132,6 +143,8 @@ static bool weight_geometry(int type, long rows, long k, tb200_weights *w) {
     case TB200_TYPE_Q4_K: if (k % QK_K) return false; w->qs_row_bytes = (size_t)k / 2, w->sc_row_bytes = (size_t)k / QK_K * 16; break;
     case TB200_TYPE_Q6_K: if (k % QK_K) return false; w->qs_row_bytes = (size_t)k / QK_K * 192, w->sc_row_bytes = (size_t)k / QK_K * 16, w->d_row_bytes = (size_t)k / QK_K * 2; break;
     case TB200_TYPE_F16: w->qs_row_bytes = (size_t)k * 2, w->sc_row_bytes = 0; break;
+    case TB200_TYPE_Q4_1: case TB200_TYPE_Q5_0: if (k % QK) return false; w->qs_row_bytes = (size_t)k, w->sc_row_bytes = (size_t)k / QK * 4; break;
+    case TB200_TYPE_Q5_K: case TB200_TYPE_IQ4_XS: if (k % QK_K) return false; w->qs_row_bytes = (size_t)k, w->sc_row_bytes = (size_t)k / QK * 4; break;
     default: return false;
     }
     return true;
@@ -144,6 +157,11 @@ static size_t gguf_row_bytes(int type, long k) {
     case TB200_TYPE_Q4_K: return (size_t)k / QK_K * 144;
     case TB200_TYPE_Q6_K: return (size_t)k / QK_K * 210;
     case TB200_TYPE_Q8_K: return (size_t)k / QK_K * 292;
+    case TB200_TYPE_Q4_1: return (size_t)k / QK * 20;
+    case TB200_TYPE_Q5_0: return (size_t)k / QK * 22;
+    case TB200_TYPE_Q8_1: return (size_t)k / QK * 36;
+    case TB200_TYPE_Q5_K: return (size_t)k / QK_K * 176;
+    case TB200_TYPE_IQ4_XS: return (size_t)k / QK_K * 136;
     case TB200_TYPE_F16: return (size_t)k * 2;
     case TB200_TYPE_F32: return (size_t)k * 4;
     default: return 0;
@@ -446,8 +464,9 @@ void tb200_acts_free(tb200_acts *a) {
 static bool serviced(int Atype, int Btype, int Ctype, long n) {
     if (Ctype != TB200_TYPE_F32) return false;
     switch (Atype) {
-    case TB200_TYPE_Q4_0: case TB200_TYPE_Q8_0: return Btype == TB200_TYPE_Q8_0;
-    case TB200_TYPE_Q4_K: case TB200_TYPE_Q6_K: return Btype == TB200_TYPE_Q8_K;
+    case TB200_TYPE_Q4_0: case TB200_TYPE_Q8_0: case TB200_TYPE_Q5_0: return Btype == TB200_TYPE_Q8_0;
+    case TB200_TYPE_Q4_1: return Btype == TB200_TYPE_Q8_1;   // iqk mul_mat_qX_1_q8_1_T<Q4_1_Unpacker> (iqk_mul_mat.inc:1442)
+    case TB200_TYPE_Q4_K: case TB200_TYPE_Q6_K: case TB200_TYPE_Q5_K: case TB200_TYPE_IQ4_XS: return Btype == TB200_TYPE_Q8_K;
     case TB200_TYPE_F16: return Btype == TB200_TYPE_F16 || (Btype == TB200_TYPE_F32 && n <= 2);
     default: return false;
     }
@@ -468,7 +487,8 @@ int tb200_sgemm_dev(const tb200_weights *w, long n, const void *B, long ldb, int
     Planar p = carve(c, w->type, n, w->k, 0, nullptr);
     if (!p.q) return TB200_ERR_CUDA;
     int rc = tb200_is_kquant(w->type) ? tb200_launch_unpack_q8_K(c, B, ldb, n, w->k, p.q, p.ds)
-                                       : tb200_launch_unpack_q8_0(c, B, ldb, n, w->k, p.q, p.ds);
+             : Btype == TB200_TYPE_Q8_1 ? tb200_launch_unpack_q8_1(c, B, ldb, n, w->k, p.q, p.ds)
+                                        : tb200_launch_unpack_q8_0(c, B, ldb, n, w->k, p.q, p.ds);
     if (rc) return rc;
     return run_matmul(c, w, 0, w->rows, p.q, p.ds, nullptr, 0, w->k, n, C, ldc);
 }

@@ -37,7 +37,7 @@ void backend_log(const char *msg) {
 }
 
 bool weight_type_ok(int type) {
-    return type == TB200_TYPE_F16 || type == TB200_TYPE_Q4_0 || type == TB200_TYPE_Q8_0 || type == TB200_TYPE_Q4_K || type == TB200_TYPE_Q6_K;
+    return type == TB200_TYPE_F16 || type == TB200_TYPE_Q4_0 || type == TB200_TYPE_Q8_0 || type == TB200_TYPE_Q4_K || type == TB200_TYPE_Q6_K || tb200_is_g8(type);
 }
 long type_blck(int type) { return type == TB200_TYPE_F16 ? 1 : (tb200_is_kquant(type) ? QK_K : QK); }
 
@@ -305,7 +305,13 @@ int backend_graph_compute(tb200_backend_t bk, struct ggml_cgraph *cg_) {
     BackendCtx *c = (BackendCtx *)bk->context;
     const tb200_ggml_cgraph_view *cg = (const tb200_ggml_cgraph_view *)cg_;
     DeviceGuard g(c->device);
-    if (tb200_set_stream(c->stream) != TB200_OK) return TB200_GGML_STATUS_FAILED;
+    tb200_ctx *mc = tb200_get_ctx();
+    if (!mc) return TB200_GGML_STATUS_FAILED;
+    struct StreamSwap {   // the module's device-level calls run on the context's current stream: point it at this backend's for the graph
+        tb200_ctx *mc; cudaStream_t old;
+        StreamSwap(tb200_ctx *m, cudaStream_t s) : mc(m), old(m->stream) { m->stream = s; }
+        ~StreamSwap() { mc->stream = old; }
+    } swap(mc, c->stream);
     const uint64_t l0 = tb200_launch_count();
     c->last_plan_nodes = 0;
     int rc = TB200_OK;

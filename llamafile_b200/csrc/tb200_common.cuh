@@ -21,9 +21,14 @@ static_assert(sizeof(tb200_block_q8_0) == 34, "block_q8_0");
 static_assert(sizeof(tb200_block_q4_K) == 144, "block_q4_K");
 static_assert(sizeof(tb200_block_q8_K) == 292, "block_q8_K");
 static_assert(sizeof(tb200_block_q6_K) == 210, "block_q6_K");
+static_assert(sizeof(tb200_block_q4_1) == 20 && sizeof(tb200_block_q5_0) == 22 && sizeof(tb200_block_q8_1) == 36, "block_q4_1 / q5_0 / q8_1");
+static_assert(sizeof(tb200_block_q5_K) == 176 && sizeof(tb200_block_iq4_xs) == 136, "block_q5_K / iq4_xs");
 
 // weight types whose activations are Q8_K (256-element super-blocks)
-static inline bool tb200_is_kquant(int type) { return type == TB200_TYPE_Q4_K || type == TB200_TYPE_Q6_K; }
+static inline bool tb200_is_kquant(int type) { return type == TB200_TYPE_Q4_K || type == TB200_TYPE_Q6_K || type == TB200_TYPE_Q5_K || type == TB200_TYPE_IQ4_XS; }
+// weight types held in the generic resident form G8 (below): the remaining types iqk serves (llamafile/iqk_mul_mat.inc:1408-1463)
+static inline bool tb200_is_g8(int type) { return type == TB200_TYPE_Q4_1 || type == TB200_TYPE_Q5_0 || type == TB200_TYPE_Q5_K || type == TB200_TYPE_IQ4_XS; }
+#define TB200_TYPE_G8 1000   // kernel-template tag of that form (never a ggml type code)
 
 // ---------------------------------------------------------------------------------------------
 // Resident weight matrix: the GGUF rows split into 16-byte-aligned planes (one-time repack at
@@ -36,6 +41,11 @@ static inline bool tb200_is_kquant(int type) { return type == TB200_TYPE_Q4_K ||
 //              128*half + 16*(l/16) + 32*j + [0,16), j = 0..3: one 64-wide K stage of the prefill path, one lane of the decode
 //              path); piece j < 3, byte e = q_j[e] << 2 | two bits of q_3[e] (bits 5:4, 3:2, 1:0 for j = 0, 1, 2)
 //         sc  [rows][k/256] x 16 B int8 scales, byte 4u + j ; d [rows][k/256] fp16
+//   G8  : (Q4_1, Q5_0, Q5_K, IQ4_XS) every 32-block as int8 quants q and an fp16 pair {a, b}: value = a*q + b, exactly what the
+//         block decodes to - Q4_1: q = nibble, a = d, b = m; Q5_0: q = q5 - 16, a = d; Q5_K: q = q5, a = fp16(d*sc), b = fp16(-dmin*m);
+//         IQ4_XS: q = kvalues_iq4nl[nibble], a = fp16(d*(ls - 32)). qs [rows][k] int8 ; sc [rows][k/32] x {fp16 a, fp16 b}.
+//         1.125 B/element in HBM instead of 0.53..0.69: these types are served (decode and prefill, bit-for-bit integer block
+//         dots), at about half the bandwidth efficiency of a native nibble kernel.
 //   F16 : qs  [rows][k] fp16 ; sc = nullptr
 // ---------------------------------------------------------------------------------------------
 struct tb200_weights {
@@ -73,10 +83,13 @@ struct tb200_ctx {
     size_t scratch_bytes;
     void *pinned;           // host staging for the host-pointer entry points
     size_t pinned_bytes;
+    void *scratch2;         // second arena: fp32 intermediates of the fused neighbours (tb200_fused.cu), alive across a matmul that uses `scratch`
+    size_t scratch2_bytes;
 };
 
 tb200_ctx *tb200_get_ctx();                       // nullptr when no device
 void *tb200_scratch(tb200_ctx *c, size_t bytes);  // grows on demand (stream-ordered)
+void *tb200_scratch2(tb200_ctx *c, size_t bytes);
 void tb200_set_error(const char *fmt, ...);
 void tb200_count_launch(int n = 1);
 
@@ -97,6 +110,7 @@ int tb200_launch_f32_to_f16(tb200_ctx *c, const float *x, long ldx, long rows, l
 // raw GGUF activation blocks -> planar
 int tb200_launch_unpack_q8_0(tb200_ctx *c, const void *raw, long ldb_blocks, long rows, long k, int8_t *q, int2 *ds);
 int tb200_launch_unpack_q8_K(tb200_ctx *c, const void *raw, long ldb_blocks, long rows, long k, int8_t *q, int2 *ds);
+int tb200_launch_unpack_q8_1(tb200_ctx *c, const void *raw, long ldb_blocks, long rows, long k, int8_t *q, int2 *ds);
 // repack
 int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long k, size_t row_stride, void *qs, void *sc, void *d);
 // decode path. out[t*ldo + i]. rowmap: optional per-token (weight-row offset, output pointer) for mixmul.

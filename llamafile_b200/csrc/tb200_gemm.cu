@@ -37,7 +37,7 @@ constexpr int kDequantWarps = 16;
 constexpr int kGroups = kDequantWarps / 4;   // dequant groups of four warps (one per 32 TMEM lanes); group g takes the stages i = g (mod kGroups)
 // packed quant bytes of one weight row in one 64-wide K stage (0: F16 weights are not dequantised)
 __host__ __device__ constexpr int packed_row_bytes(int type) {
-    return type == TB200_TYPE_Q8_0 ? 64 : (type == TB200_TYPE_Q6_K ? 48 : (type == TB200_TYPE_F16 ? 0 : 32));
+    return (type == TB200_TYPE_Q8_0 || type == TB200_TYPE_G8) ? 64 : (type == TB200_TYPE_Q6_K ? 48 : (type == TB200_TYPE_F16 ? 0 : 32));
 }
 constexpr int kThreads = (4 + kDequantWarps) * 32;
 
@@ -217,6 +217,17 @@ __device__ __forceinline__ uint2 dequant_q8_word(uint32_t w, __half2 d2) {
     return o;
 }
 
+// G8 word (4 int8 of the generic form, tb200_common.cuh): value = a*q + b with the block's fp16 pair; q comes out exactly as for Q8_0.
+__device__ __forceinline__ uint2 dequant_g8_word(uint32_t w, __half2 a2, __half2 b2) {
+    const __half2 k1152 = __floats2half2_rn(1152.f, 1152.f);
+    const uint32_t x = w ^ 0x80808080u;
+    auto q = [&](uint32_t v) { const __half2 r = __hsub2(*reinterpret_cast<const __half2 *>(&v), k1152); return *reinterpret_cast<const uint32_t *>(&r); };
+    uint2 o;
+    o.x = h2_fma(q(__byte_perm(x, 0x64646464u, 0x4140)), a2, b2);
+    o.y = h2_fma(q(__byte_perm(x, 0x64646464u, 0x4342)), a2, b2);
+    return o;
+}
+
 __device__ __forceinline__ void q4k_scale_min(const uint4 hdr, int j, int &sc, int &m) {   // get_scale_min_k4, ggml-quants.c:1891-1899
     const uint32_t s0 = hdr.y, s1 = hdr.z, s2 = hdr.w;
     auto byte = [&](int i) -> uint32_t { const uint32_t wv = i < 4 ? s0 : (i < 8 ? s1 : s2); return (wv >> (8 * (i & 3))) & 0xff; };
@@ -293,12 +304,13 @@ struct RowDequant {
     int row;
 
     __device__ __forceinline__ void fetch(int stage, __half2 &d, uint4 &h) const {
-        if (kType == TB200_TYPE_Q4_K) h = __ldg(hdp + (stage >> 2));
+        if (kType == TB200_TYPE_G8) { const uint2 ab = __ldg(reinterpret_cast<const uint2 *>(scp) + stage); h.x = ab.x, h.y = ab.y; }   // {a, b} of the stage's two blocks
+        else if (kType == TB200_TYPE_Q4_K) h = __ldg(hdp + (stage >> 2));
         else if (kType == TB200_TYPE_Q6_K) h.x = __ldg(reinterpret_cast<const uint32_t *>(hdp) + stage), d = __half2half2(d6p[stage >> 2]);
         else d = *reinterpret_cast<const __half2 *>(scp + 2 * stage);
     }
     __device__ __forceinline__ RowDequant(const GemmParams &p, long grow, int row_, int first_stage, int kt) : row(row_) {
-        scp = reinterpret_cast<const __half *>(p.sc) + grow * p.sc_row_stride;
+        scp = reinterpret_cast<const __half *>(p.sc) + grow * p.sc_row_stride * (kType == TB200_TYPE_G8 ? 2 : 1);   // G8: 4 bytes per block
         hdp = reinterpret_cast<const uint4 *>(p.sc) + grow * p.sc_row_stride;
         d6p = reinterpret_cast<const __half *>(p.d6) + grow * p.sc_row_stride;
 #pragma unroll
@@ -341,6 +353,24 @@ struct RowDequant {
             a = dequant_q8_word(w1.y, d2), r[10] = a.x, r[11] = a.y;
             a = dequant_q8_word(w1.z, d2), r[12] = a.x, r[13] = a.y;
             a = dequant_q8_word(w1.w, d2), r[14] = a.x, r[15] = a.y;
+        } else if (kType == TB200_TYPE_G8) {
+            // same tile as Q8_0 (64-byte rows, SWIZZLE_64B); value = a*q + b with the fp16 pair of block 2i + chalf
+            const uint8_t *rp = tile + row * 64;
+            const int sw = (row >> 1) & 3;
+            const uint4 w0 = *reinterpret_cast<const uint4 *>(rp + (((chalf * 2) ^ sw) << 4));
+            const uint4 w1 = *reinterpret_cast<const uint4 *>(rp + (((chalf * 2 + 1) ^ sw) << 4));
+            const uint32_t ab = chalf ? hdr.y : hdr.x;
+            const __half2 abh = *reinterpret_cast<const __half2 *>(&ab);
+            const __half2 a2 = __low2half2(abh), b2 = __high2half2(abh);
+            uint2 a;
+            a = dequant_g8_word(w0.x, a2, b2), r[0] = a.x, r[1] = a.y;
+            a = dequant_g8_word(w0.y, a2, b2), r[2] = a.x, r[3] = a.y;
+            a = dequant_g8_word(w0.z, a2, b2), r[4] = a.x, r[5] = a.y;
+            a = dequant_g8_word(w0.w, a2, b2), r[6] = a.x, r[7] = a.y;
+            a = dequant_g8_word(w1.x, a2, b2), r[8] = a.x, r[9] = a.y;
+            a = dequant_g8_word(w1.y, a2, b2), r[10] = a.x, r[11] = a.y;
+            a = dequant_g8_word(w1.z, a2, b2), r[12] = a.x, r[13] = a.y;
+            a = dequant_g8_word(w1.w, a2, b2), r[14] = a.x, r[15] = a.y;
         } else if (kType == TB200_TYPE_Q6_K) {
             // stage i is unit u = i & 3 of super-block i >> 2: 48 bytes = pieces j = 0,1,2 (byte = q_j << 2 | two bits of q_3,
             // tb200_repack.cu); half `chalf` of the stage is j = 2*chalf, 2*chalf+1 (16 elements each, scale byte j of hdr.x):
@@ -830,7 +860,7 @@ CUtensorMap *weight_map(const tb200_weights *w) {
         CUtensorMap *m = new CUtensorMap();
         bool ok;
         if (w->type == TB200_TYPE_F16) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k * 2, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
-        else if (w->type == TB200_TYPE_Q8_0) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k, BK, BM, CU_TENSOR_MAP_SWIZZLE_64B);
+        else if (w->type == TB200_TYPE_Q8_0 || tb200_is_g8(w->type)) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k, (uint64_t)w->rows, (uint64_t)w->k, BK, BM, CU_TENSOR_MAP_SWIZZLE_64B);
         else if (w->type == TB200_TYPE_Q6_K) ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / QK_K * 192, (uint64_t)w->rows, (uint64_t)w->k / QK_K * 192, 48, BM, CU_TENSOR_MAP_SWIZZLE_NONE);
         else ok = make_map_2d(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, w->qs, (uint64_t)w->k / 2, (uint64_t)w->rows, (uint64_t)w->k / 2, BK / 2, BM, CU_TENSOR_MAP_SWIZZLE_32B);
         if (!ok) { delete m; return nullptr; }
@@ -894,7 +924,7 @@ int launch_type(tb200_ctx *c, const tb200_weights *w, CUtensorMap &mw, long toke
         return launch_cfg_pair<kType, 128, 8>(c, mw, mb, p);
     }
     switch (bn) {
-    case 256: return launch_cfg<kType, 256, f16 ? 4 : ((kType == TB200_TYPE_Q8_0 || kType == TB200_TYPE_Q6_K) ? 5 : 6)>(c, mw, mb, p);
+    case 256: return launch_cfg<kType, 256, f16 ? 4 : ((kType == TB200_TYPE_Q8_0 || kType == TB200_TYPE_Q6_K || kType == TB200_TYPE_G8) ? 5 : 6)>(c, mw, mb, p);
     // small token tiles are weight-streaming-bound: the ring is as deep as tensor memory (accumulator + 32 columns of A' per
     // stage <= 512) and shared memory allow, since bytes in flight per SM are what sets the HBM rate there
     case 128: return launch_cfg<kType, 128, deep_stages(kType, 128)>(c, mw, mb, p);
@@ -1035,7 +1065,7 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
         b_src = af;
         TB_CUDA(tb200_launch(fill_ones_kernel, dim3((unsigned)((tokens + 255) / 256)), dim3(256), 0, c->stream, colscale, tokens));
     } else {
-        const int perm = w->type == TB200_TYPE_Q8_0 ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : (w->type == TB200_TYPE_Q6_K ? 3 : 2));
+        const int perm = (w->type == TB200_TYPE_Q8_0 || tb200_is_g8(w->type)) ? 0 : (w->type == TB200_TYPE_Q4_0 ? 1 : (w->type == TB200_TYPE_Q6_K ? 3 : 2));
         TB_CUDA(tb200_launch(prep_acts_kernel, dim3((unsigned)tokens), dim3(256), 0, c->stream, aq, ads, a_stride, w->k, perm, bp, colscale, (const int *)nullptr, 1, 1));
     }
     // weight tensor map (whole matrix), cached on the weights object
@@ -1044,7 +1074,7 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
     CUtensorMap &mw = *mwp;
     GemmParams p;
     p.sc = w->sc;
-    p.sc_row_stride = tb200_is_kquant(w->type) ? w->k / QK_K : w->k / QK;
+    p.sc_row_stride = (tb200_is_kquant(w->type) && !tb200_is_g8(w->type)) ? w->k / QK_K : w->k / QK;
     p.d6 = w->d;
     p.row0 = row0, p.nrows = nrows, p.k = w->k, p.tokens = tokens, p.colscale = colscale, p.out = out, p.ldo = ldo;
     p.tiles = nullptr, p.rowmap = nullptr, p.n_tiles = 0;
@@ -1060,6 +1090,7 @@ int tb200_launch_gemm(tb200_ctx *c, const tb200_weights *w, long row0, long nrow
     case TB200_TYPE_Q4_K: return launch_type<TB200_TYPE_Q4_K>(c, w, mw, tokens, (void *)b_src, p);
     case TB200_TYPE_Q6_K: return launch_type<TB200_TYPE_Q6_K>(c, w, mw, tokens, (void *)b_src, p);
     case TB200_TYPE_F16: return launch_type<TB200_TYPE_F16>(c, w, mw, tokens, (void *)b_src, p);
+    case TB200_TYPE_Q4_1: case TB200_TYPE_Q5_0: case TB200_TYPE_Q5_K: case TB200_TYPE_IQ4_XS: return launch_type<TB200_TYPE_G8>(c, w, mw, tokens, (void *)b_src, p);
     default: return TB200_ERR_UNSUPPORTED;
     }
 }

@@ -963,6 +963,86 @@ __global__ void __launch_bounds__(kWarps * 32) gemv_q8_0_kernel(const uint4 *__r
         }
 }
 
+// ---- G8: the generic resident form of Q4_1 / Q5_0 / Q5_K / IQ4_XS (tb200_common.cuh) -------------------------------------
+// int8 quants + fp16 {a, b} per 32-block, value = a*q + b, so a block contributes a*d_y*sum(q*q_y) + b*d_y*sum(q_y): the
+// integer block dot of the reference's kernels (ggml_vec_dot_q5_0_q8_0 ggml-quants.c:4498, _q4_1_q8_1 :4211 with its
+// m*s term, _q5_K_q8_K :7400, _iq4_xs_q8_K :11799) with the sub-block scale folded into a. Same walk as the Q8_0 kernel.
+template <int T, int R>
+__global__ void __launch_bounds__(kWarps * 32) gemv_g8_kernel(const uint4 *__restrict__ qs, const uint32_t *__restrict__ sc,
+                                                              long nb, long nbc, long row0, long nrows,
+                                                              const int8_t *__restrict__ aq, const int2 *__restrict__ ads,
+                                                              long a_stride, float *__restrict__ out, long ldo) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint4 *s_q = reinterpret_cast<uint4 *>(smem);             // [T][2*nbc]
+    int2 *s_ds = reinterpret_cast<int2 *>(s_q + T * nbc * 2);  // [T][nbc]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long r_base = ((long)blockIdx.x * kWarps + warp) * R;
+    const bool active = r_base < nrows;
+    pdl_launch_dependents();
+    pdl_wait();
+    float acc[R][T];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+    const uint4 *wrow[R];
+    const uint32_t *srow[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const long row = row0 + min(r_base + r, nrows - 1);
+        wrow[r] = qs + row * nb * 2;
+        srow[r] = sc + row * nb;
+    }
+    for (long b0 = 0; b0 < nb; b0 += nbc) {
+        const long cnt = min(nbc, nb - b0);
+        if (b0) __syncthreads();
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const uint4 *src = reinterpret_cast<const uint4 *>(aq + (long)t * a_stride + b0 * 32);
+            const int2 *dsrc = ads + (long)t * (a_stride / QK) + b0;
+            for (int g = threadIdx.x; g < (int)cnt * 2; g += kWarps * 32) s_q[t * (int)nbc * 2 + g] = src[g];
+            for (int g = threadIdx.x; g < (int)cnt; g += kWarps * 32) s_ds[t * (int)nbc + g] = dsrc[g];
+        }
+        __syncthreads();
+        if (!active) continue;
+        for (long g = lane; g < cnt * 2; g += 32) {
+            uint4 w[R];
+            float a[R], b[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) w[r] = ldg_stream(wrow[r] + b0 * 2 + g);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const uint32_t ab = __ldg(srow[r] + b0 + (g >> 1));
+                a[r] = __half2float(__ushort_as_half((unsigned short)(ab & 0xffffu)));
+                b[r] = (g & 1) ? 0.f : __half2float(__ushort_as_half((unsigned short)(ab >> 16)));   // the b*sum(q_y) term once per block
+            }
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const uint4 y = s_q[t * nbc * 2 + g];
+                const int2 ds = s_ds[t * nbc + (g >> 1)];
+                const float dy = __int_as_float(ds.x);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    int s = dp4a_ss((int)w[r].x, (int)y.x, 0);
+                    s = dp4a_ss((int)w[r].y, (int)y.y, s);
+                    s = dp4a_ss((int)w[r].z, (int)y.z, s);
+                    s = dp4a_ss((int)w[r].w, (int)y.w, s);
+                    acc[r][t] = fmaf(a[r] * dy, (float)s, acc[r][t]);
+                    acc[r][t] = fmaf(b[r] * dy, (float)ds.y, acc[r][t]);
+                }
+            }
+        }
+    }
+    if (!active) return;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const float v = warp_sum(acc[r][t]);
+            if (lane == 0 && r_base + r < nrows) out[(long)t * ldo + r_base + r] = v;
+        }
+}
+
 // ---- Q4_K ---------------------------------------------------------------------------------------
 // Super-block = 128 B of nibbles = 8 pieces of 16 B; piece p = 2c+h holds, for 64-element chunk c,
 // low nibbles = elements 64c+16h+[0,16) (sub-block 2c) and high nibbles = 64c+32+16h+[0,16) (sub-block 2c+1)
@@ -1503,6 +1583,17 @@ int launch_TR(tb200_ctx *c, const tb200_gemv_args &a) {
         const dim3 g2((unsigned)ctas, grid.y);
         if ((rc = set_smem(gemv_q6_K_kernel<T, R>, smem))) return rc;
         TB_CUDA(tb200_launch(gemv_q6_K_kernel<T, R>, g2, dim3(kWarps * 32), smem, c->stream, ka));
+        break;
+    }
+    case TB200_TYPE_Q4_1: case TB200_TYPE_Q5_0: case TB200_TYPE_Q5_K: case TB200_TYPE_IQ4_XS: {
+        if (a.items) { tb200_set_error("gemv: grouped mode is not available for type %d", w->type); return TB200_ERR_UNSUPPORTED; }
+        const long nb = w->k / QK;
+        long nbc = (long)(kSmemBudget / ((size_t)T * 40)) / 32 * 32;
+        if (nbc >= nb) nbc = nb;
+        const size_t smem = (size_t)T * nbc * 40;
+        if ((rc = set_smem(gemv_g8_kernel<T, R>, smem))) return rc;
+        TB_CUDA(tb200_launch(gemv_g8_kernel<T, R>, grid, dim3(kWarps * 32), smem, c->stream, (const uint4 *)w->qs, (const uint32_t *)w->sc, nb, nbc, a.row0, a.nrows,
+                             a.aq, a.ads, a.a_stride, a.out, a.ldo));
         break;
     }
     case TB200_TYPE_F16: {

@@ -196,7 +196,7 @@ tb200_weights *tb200_gguf_upload(const tb200_gguf *g, const char *name, long row
     const void *data = nullptr;
     size_t bytes = 0;
     if (tb200_gguf_find(g, name, &type, ne, &data, &bytes) != TB200_OK) return nullptr;
-    if (type != TB200_TYPE_F16 && type != TB200_TYPE_Q4_0 && type != TB200_TYPE_Q8_0 && !tb200_is_kquant(type)) {
+    if (type != TB200_TYPE_F16 && type != TB200_TYPE_Q4_0 && type != TB200_TYPE_Q8_0 && !tb200_is_kquant(type) && !tb200_is_g8(type)) {
         tb200_set_error("gguf: tensor %s has type %d, which this module does not hold", name, type);
         return nullptr;
     }

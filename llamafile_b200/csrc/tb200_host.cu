@@ -246,7 +246,9 @@ int lane_issue(tb200_ctx *c, HostLane &L, const LaneKey &k, size_t b_bytes) {
     } else {
         int8_t *q = (int8_t *)L.dact;
         int2 *ds = (int2 *)(L.dact + up256((size_t)k.n * w->k));
-        rc = tb200_is_kquant(w->type) ? tb200_launch_unpack_q8_K(c, k.dB, k.ldb, k.n, w->k, q, ds) : tb200_launch_unpack_q8_0(c, k.dB, k.ldb, k.n, w->k, q, ds);
+        rc = tb200_is_kquant(w->type) ? tb200_launch_unpack_q8_K(c, k.dB, k.ldb, k.n, w->k, q, ds)
+             : k.btype == TB200_TYPE_Q8_1 ? tb200_launch_unpack_q8_1(c, k.dB, k.ldb, k.n, w->k, q, ds)
+                                          : tb200_launch_unpack_q8_0(c, k.dB, k.ldb, k.n, w->k, q, ds);
         if (rc) return rc;
         rc = tb200_run_matmul(c, w, 0, w->rows, q, ds, nullptr, 0, w->k, k.n, (float *)k.dC, k.ldo);
     }
@@ -290,7 +292,10 @@ struct WeightsRef {   // frees a transient copy when the call ends
     ~WeightsRef() { if (w && transient) tb200_weights_free(w); }
 };
 
-int blck(int type) { return (tb200_is_kquant(type) || type == TB200_TYPE_Q8_K) ? QK_K : (type == TB200_TYPE_Q4_0 || type == TB200_TYPE_Q8_0) ? QK : 1; }
+int blck(int type) {
+    if (tb200_is_kquant(type) || type == TB200_TYPE_Q8_K) return QK_K;
+    return (type == TB200_TYPE_Q4_0 || type == TB200_TYPE_Q8_0 || type == TB200_TYPE_Q4_1 || type == TB200_TYPE_Q5_0 || type == TB200_TYPE_Q8_1) ? QK : 1;
+}
 size_t tsize(int type) { return tb200_gguf_row_bytes(type, blck(type)); }
 
 }  // namespace
@@ -353,7 +358,7 @@ bool llamafile_sgemm(long m, long n, long k, const void *A, long lda, const void
     DeviceLock lock(c->device);
     const long ke = k * blck(Atype);
     // iqk (Q4_0, Q4_K) takes rows ggml_row_size apart and ignores lda/ldb (iqk_mul_mat.inc:191-199); tinyBLAS honours them
-    const bool iqk = Atype == TB200_TYPE_Q4_0 || tb200_is_kquant(Atype);
+    const bool iqk = Atype == TB200_TYPE_Q4_0 || Atype == TB200_TYPE_Q5_0 || Atype == TB200_TYPE_Q4_1 || tb200_is_kquant(Atype);
     const size_t a_stride = iqk ? tb200_gguf_row_bytes(Atype, ke) : (size_t)lda * tsize(Atype);
     const long ldb_eff = iqk ? k : ldb;
     WeightsRef wr;
@@ -550,7 +555,7 @@ bool llamafile_mixmul(const struct ggml_compute_params *params_, const struct gg
 // [ne12][ne11], C row for mapping y = C + i1*nb1 + i2*nb2, B row = (i1 % ne11) + i2*ne11.
 bool llamafile_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, const void *A, const void *B, float *C, long nb1, long nb2,
                           const void *vrow_mapping, int ith, int nth) {
-    if (!tb200_is_kquant(typeA) && typeA != TB200_TYPE_Q4_0) return false;   // the other iqk types are outside this module
+    if (!tb200_is_kquant(typeA) && typeA != TB200_TYPE_Q4_0 && typeA != TB200_TYPE_Q5_0 && typeA != TB200_TYPE_Q4_1) return false;   // the i-quants below 4 bits and Q5_1 / IQ4_NL are outside this module
     if (!vrow_mapping || Nx < 0 || Ny < 0 || ne11 <= 0 || nth <= 0 || ith < 0 || ith >= nth || ne00 % blck(typeA)) return false;
     if (g_disabled.load(std::memory_order_acquire)) return false;
     tb200_ctx *c = tb200_get_ctx();
@@ -558,7 +563,7 @@ bool llamafile_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, cons
     if (ith != 0) return true;
     if (Nx == 0 || Ny == 0) return true;
     DeviceLock lock(c->device);
-    const int Btype = tb200_is_kquant(typeA) ? TB200_TYPE_Q8_K : TB200_TYPE_Q8_0;
+    const int Btype = tb200_is_kquant(typeA) ? TB200_TYPE_Q8_K : (typeA == TB200_TYPE_Q4_1 ? TB200_TYPE_Q8_1 : TB200_TYPE_Q8_0);
     WeightsRef wr;
     wr.w = cached_weights(A, typeA, Nx, ne00, 0, &wr.transient);
     tb200_weights *w = wr.w;

@@ -173,6 +173,23 @@ __global__ void unpack_q8_0_kernel(const uint8_t *__restrict__ raw, long ldb, lo
     if (g8 == 0) ds[blk] = make_int2(__float_as_int(__half2float(__ushort_as_half(*reinterpret_cast<const uint16_t *>(src)))), sum);
 }
 
+// block_q8_1 {fp16 d; fp16 s; int8 qs[32]} (ggml-common.h:193-203): the quants and d are quantize_row_q8_0's; s = fp16(d*sum q) is
+// re-formed by the consumer from {d, sum q}
+__global__ void unpack_q8_1_kernel(const uint8_t *__restrict__ raw, long ldb, long rows, long nb, int8_t *__restrict__ q, int2 *__restrict__ ds) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;   // one thread per 4 quants
+    const bool live = i < rows * nb * 8;
+    const long blk = live ? i >> 3 : 0, row = blk / nb, b = blk % nb;
+    const int g8 = i & 7;
+    const uint8_t *src = raw + (row * ldb + b) * sizeof(tb200_block_q8_1);
+    const uint32_t packed = *reinterpret_cast<const uint32_t *>(src + 4 + 4 * g8);   // 36-byte blocks: 4-byte aligned
+    int sum = __dp4a((int)packed, 0x01010101, 0);
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (!live) return;
+    *reinterpret_cast<uint32_t *>(q + blk * QK + 4 * g8) = packed;
+    if (g8 == 0) ds[blk] = make_int2(__float_as_int(__half2float(__ushort_as_half(*reinterpret_cast<const uint16_t *>(src)))), sum);
+}
+
 __global__ void unpack_q8_K_kernel(const uint8_t *__restrict__ raw, long ldb, long rows, long nb, int8_t *__restrict__ q,
                                    int2 *__restrict__ ds) {
     const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;   // one thread per 4 quants
@@ -231,6 +248,15 @@ int tb200_launch_unpack_q8_K(tb200_ctx *c, const void *raw, long ldb, long rows,
     const long nb = k / QK_K, n = rows * nb * 64;
     if (n == 0) return TB200_OK;
     unpack_q8_K_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>((const uint8_t *)raw, ldb, rows, nb, q, ds);
+    tb200_count_launch();
+    TB_CUDA(cudaGetLastError());
+    return TB200_OK;
+}
+
+int tb200_launch_unpack_q8_1(tb200_ctx *c, const void *raw, long ldb, long rows, long k, int8_t *q, int2 *ds) {
+    const long nb = k / QK, n = rows * nb * 8;
+    if (n == 0) return TB200_OK;
+    unpack_q8_1_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>((const uint8_t *)raw, ldb, rows, nb, q, ds);
     tb200_count_launch();
     TB_CUDA(cudaGetLastError());
     return TB200_OK;

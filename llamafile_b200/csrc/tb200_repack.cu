@@ -87,6 +87,67 @@ __global__ void repack_q6_K_kernel(const uint8_t *__restrict__ raw, size_t row_s
     }
 }
 
+// ---- the generic form G8 (tb200_common.cuh): every 32-block as int8 quants + fp16 {a, b}, value = a*q + b. One thread per 32-block.
+//   block_q4_1  (ggml-common.h:151-161, dequantize_row_q4_1 ggml-quants.c:1535-1554): x = d*q + m
+//   block_q5_0  (ggml-common.h:164-169, dequantize_row_q5_0 :1556-1580):              x = d*(q5 - 16), 5th bits in qh
+//   block_q5_K  (ggml-common.h:280-295, dequantize_row_q5_K :2756-2781):              x = (d*sc)*q5 - dmin*m per 32-sub-block
+//   block_iq4_xs (ggml-common.h:393-398, dequantize_row_iq4_xs :3568-3590):           x = d*(ls - 32) * kvalues_iq4nl[q4]
+__device__ __constant__ int8_t kvalues_iq4nl_dev[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};   // ggml-quants.c:3548
+
+__device__ __forceinline__ void g8_store(int8_t *qs, uint32_t *sc, long blk, const int (&q)[32], float a, float b) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        w[i] = (uint32_t)(q[4 * i] & 0xff) | ((uint32_t)(q[4 * i + 1] & 0xff) << 8) | ((uint32_t)(q[4 * i + 2] & 0xff) << 16) | ((uint32_t)(q[4 * i + 3] & 0xff) << 24);
+    uint4 *dst = reinterpret_cast<uint4 *>(qs + blk * 32);
+    dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    sc[blk] = (uint32_t)__half_as_ushort(__float2half_rn(a)) | ((uint32_t)__half_as_ushort(__float2half_rn(b)) << 16);
+}
+__device__ __forceinline__ float h16(const uint8_t *p) { return __half2float(__ushort_as_half((unsigned short)(p[0] | (p[1] << 8)))); }
+
+__global__ void repack_g8_kernel(int type, const uint8_t *__restrict__ raw, size_t row_stride, long rows, long nb32, int8_t *__restrict__ qs, uint32_t *__restrict__ sc) {
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;   // 32-block index
+    if (i >= rows * nb32) return;
+    const long row = i / nb32, b = i % nb32;
+    const uint8_t *r = raw + row * row_stride;
+    int q[32];
+    float a, bb = 0.f;
+    if (type == TB200_TYPE_Q4_1) {
+        const uint8_t *x = r + b * sizeof(tb200_block_q4_1);
+        a = h16(x), bb = h16(x + 2);
+        for (int j = 0; j < 16; ++j) q[j] = x[4 + j] & 0xF, q[j + 16] = x[4 + j] >> 4;
+    } else if (type == TB200_TYPE_Q5_0) {
+        const uint8_t *x = r + b * sizeof(tb200_block_q5_0);
+        a = h16(x);
+        const uint32_t qh = (uint32_t)x[2] | ((uint32_t)x[3] << 8) | ((uint32_t)x[4] << 16) | ((uint32_t)x[5] << 24);
+        for (int j = 0; j < 16; ++j) {
+            q[j] = (int)((x[6 + j] & 0x0F) | (((qh >> j) << 4) & 0x10)) - 16;
+            q[j + 16] = (int)((x[6 + j] >> 4) | ((qh >> (j + 12)) & 0x10)) - 16;
+        }
+    } else if (type == TB200_TYPE_Q5_K) {
+        const long sb = b >> 3;
+        const int s = (int)(b & 7);
+        const uint8_t *x = r + sb * sizeof(tb200_block_q5_K);
+        const uint8_t *scales = x + 4, *qh = x + 16, *ql = x + 48 + 32 * (s >> 1);
+        int scv, mv;   // get_scale_min_k4, ggml-quants.c:1891-1899
+        if (s < 4) scv = scales[s] & 63, mv = scales[s + 4] & 63;
+        else scv = (scales[s + 4] & 0xF) | ((scales[s - 4] >> 6) << 4), mv = (scales[s + 4] >> 4) | ((scales[s] >> 6) << 4);
+        a = h16(x) * (float)scv, bb = -(h16(x + 2) * (float)mv);
+        for (int l = 0; l < 32; ++l) q[l] = (int)((s & 1) ? (ql[l] >> 4) : (ql[l] & 0xF)) + (((qh[l] >> s) & 1) ? 16 : 0);
+    } else {   // IQ4_XS
+        const long sb = b >> 3;
+        const int ib = (int)(b & 7);
+        const uint8_t *x = r + sb * sizeof(tb200_block_iq4_xs);
+        const uint32_t scales_h = (uint32_t)x[2] | ((uint32_t)x[3] << 8);
+        const int ls = ((x[4 + ib / 2] >> (4 * (ib % 2))) & 0xf) | (((scales_h >> (2 * ib)) & 3) << 4);
+        a = h16(x) * (float)(ls - 32);
+        const uint8_t *qsrc = x + 8 + 16 * ib;
+        for (int j = 0; j < 16; ++j) q[j] = kvalues_iq4nl_dev[qsrc[j] & 0xf], q[j + 16] = kvalues_iq4nl_dev[qsrc[j] >> 4];
+    }
+    g8_store(qs, sc, i, q, a, bb);
+}
+
 }  // namespace
 
 int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long k, size_t row_stride, void *qs, void *sc, void *d) {
@@ -111,6 +172,11 @@ int tb200_launch_repack(tb200_ctx *c, const void *raw, int type, long rows, long
     case TB200_TYPE_Q6_K: {
         const long nb = k / QK_K, n = rows * nb * 13;
         repack_q6_K_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(r, row_stride, rows, nb, (uint8_t *)qs, (uint8_t *)sc, (uint16_t *)d);
+        break;
+    }
+    case TB200_TYPE_Q4_1: case TB200_TYPE_Q5_0: case TB200_TYPE_Q5_K: case TB200_TYPE_IQ4_XS: {
+        const long nb32 = k / QK, n = rows * nb32;
+        repack_g8_kernel<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(type, r, row_stride, rows, nb32, (int8_t *)qs, (uint32_t *)sc);
         break;
     }
     case TB200_TYPE_F16:

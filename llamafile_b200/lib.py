@@ -12,8 +12,9 @@ PKG = Path(__file__).resolve().parent
 LIB_PATH = PKG / "libtinyblas_b200.so"
 
 F32, F16, Q4_0, Q8_0, Q4_K, Q6_K, Q8_K, I32 = 0, 1, 2, 8, 12, 14, 15, 26
-TYPE_SIZE = {F32: 4, F16: 2, Q4_0: 18, Q8_0: 34, Q4_K: 144, Q6_K: 210, Q8_K: 292, I32: 4}
-BLCK = {F32: 1, F16: 1, Q4_0: 32, Q8_0: 32, Q4_K: 256, Q6_K: 256, Q8_K: 256, I32: 1}
+Q4_1, Q5_0, Q8_1, Q5_K, IQ4_XS = 3, 6, 9, 13, 23
+TYPE_SIZE = {F32: 4, F16: 2, Q4_0: 18, Q8_0: 34, Q4_K: 144, Q6_K: 210, Q8_K: 292, I32: 4, Q4_1: 20, Q5_0: 22, Q8_1: 36, Q5_K: 176, IQ4_XS: 136}
+BLCK = {F32: 1, F16: 1, Q4_0: 32, Q8_0: 32, Q4_K: 256, Q6_K: 256, Q8_K: 256, I32: 1, Q4_1: 32, Q5_0: 32, Q8_1: 32, Q5_K: 256, IQ4_XS: 256}
 OK, ERR_NO_DEVICE, ERR_UNSUPPORTED, ERR_INVALID, ERR_CUDA = range(5)
 
 
@@ -57,6 +58,9 @@ def lib() -> C.CDLL:
         "tb200_quantize_row_q8_0": (C.c_bool, [vp, vp, C.c_int64]), "tb200_quantize_row_q8_K": (C.c_bool, [vp, vp, C.c_int64]),
         "tb200_fp32_to_fp16_row": (C.c_bool, [vp, vp, C.c_int64]), "tb200_weights_cache_clear": (None, []),
         "tb200_register_weights": (i, [vp, sz]), "tb200_unregister_weights": (i, [vp]), "tb200_weights_cache_bytes": (sz, []),
+        "tb200_rms_norm_mul_dev": (i, [vp, l, vp, C.c_float, l, l, vp, l]), "tb200_silu_mul_dev": (i, [vp, vp, l, l, l, vp, l]),
+        "tb200_moe_combine_dev": (i, [vp, vp, l, i, l, vp, l]), "tb200_acts_quantize_rmsnorm": (i, [vp, vp, l, l, vp, C.c_float, l]),
+        "tb200_acts_quantize_swiglu": (i, [vp, vp, vp, l, l, l]),
         "tb200_plan_create": (vp, [i, vp]), "tb200_plan_run": (i, [vp, i, i]), "tb200_plan_status": (i, [vp]), "tb200_plan_reset": (i, [vp]), "tb200_plan_trace": (l, [vp, vp, l]),
         "tb200_plan_free": (None, [vp]),
         "tb200_backend_link": (C.c_bool, [vp]), "tb200_backend_init": (vp, [i]), "tb200_backend_is_tb200": (C.c_bool, [vp]),
@@ -171,6 +175,26 @@ class Acts:
             self.free()
         except Exception:
             pass
+
+
+def rms_norm_mul(x, norm_weight, eps: float, tokens: int, k: int, y):
+    _check(lib().tb200_rms_norm_mul_dev(_ptr(x), k, _ptr(norm_weight), eps, tokens, k, _ptr(y), k), "rms_norm_mul")
+
+
+def silu_mul(gate, up, tokens: int, k: int, y):
+    _check(lib().tb200_silu_mul_dev(_ptr(gate), _ptr(up), k, tokens, k, _ptr(y), k), "silu_mul")
+
+
+def moe_combine(expert_out, weights, tokens: int, used: int, rows: int, out):
+    _check(lib().tb200_moe_combine_dev(_ptr(expert_out), _ptr(weights), tokens, used, rows, _ptr(out), rows), "moe_combine")
+
+
+def acts_quantize_rmsnorm(a: Acts, x, tokens: int, norm_weight, eps: float):
+    _check(lib().tb200_acts_quantize_rmsnorm(a.handle, _ptr(x), a.k, tokens, _ptr(norm_weight), eps, a.k), "acts_quantize_rmsnorm")
+
+
+def acts_quantize_swiglu(a: Acts, gate, up, tokens: int):
+    _check(lib().tb200_acts_quantize_swiglu(a.handle, _ptr(gate), _ptr(up), a.k, tokens, a.k), "acts_quantize_swiglu")
 
 
 def mul_mat_acts(w: Weights, a: Acts, out, ldo: int | None = None):

@@ -18,9 +18,10 @@ ORACLE_SO = HERE / "_build" / "liboracle.so"
 REF_SO = HERE / "_ref" / "libtb200_ref.so"
 
 F32, F16, Q4_0, Q8_0, Q4_K, Q6_K, Q8_K, I32 = 0, 1, 2, 8, 12, 14, 15, 26
-TYPE_SIZE = {F32: 4, F16: 2, Q4_0: 18, Q8_0: 34, Q4_K: 144, Q6_K: 210, Q8_K: 292, I32: 4}
-BLCK = {F32: 1, F16: 1, Q4_0: 32, Q8_0: 32, Q4_K: 256, Q6_K: 256, Q8_K: 256, I32: 1}
-VEC_DOT_TYPE = {Q4_0: Q8_0, Q8_0: Q8_0, Q4_K: Q8_K, Q6_K: Q8_K, F16: F16}   # ggml.c type_traits.vec_dot_type
+Q4_1, Q5_0, Q8_1, Q5_K, IQ4_XS = 3, 6, 9, 13, 23
+TYPE_SIZE = {F32: 4, F16: 2, Q4_0: 18, Q8_0: 34, Q4_K: 144, Q6_K: 210, Q8_K: 292, I32: 4, Q4_1: 20, Q5_0: 22, Q8_1: 36, Q5_K: 176, IQ4_XS: 136}
+BLCK = {F32: 1, F16: 1, Q4_0: 32, Q8_0: 32, Q4_K: 256, Q6_K: 256, Q8_K: 256, I32: 1, Q4_1: 32, Q5_0: 32, Q8_1: 32, Q5_K: 256, IQ4_XS: 256}
+VEC_DOT_TYPE = {Q4_0: Q8_0, Q8_0: Q8_0, Q4_K: Q8_K, Q6_K: Q8_K, F16: F16, Q4_1: Q8_1, Q5_0: Q8_0, Q5_K: Q8_K, IQ4_XS: Q8_K}   # ggml.c type_traits.vec_dot_type
 
 
 def row_bytes(t: int, k: int) -> int:
@@ -102,6 +103,8 @@ class _Common:
             return self.quantize_q8_K(X)
         if vdt == F16:
             return self.fp32_to_fp16(X)
+        if vdt == Q8_1:
+            return self.quantize_q8_1(X)
         raise ValueError(vdt)
 
 
@@ -135,6 +138,10 @@ class Oracle(_Common):
     def quantize_q8_0_ref(self, X): return self._rows(self.lib.oracle_quantize_row_q8_0_ref, X, Q8_0)
     def quantize_q8_K(self, X): return self._rows(self.lib.oracle_quantize_row_q8_K, X, Q8_K)
     def quantize_q4_0(self, X): return self._rows(self.lib.oracle_quantize_row_q4_0_ref, X, Q4_0)
+
+    def quantize_q8_1(self, X):
+        self.lib.oracle_quantize_row_q8_1.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        return self._rows(self.lib.oracle_quantize_row_q8_1, X, Q8_1)
 
     def fp32_to_fp16(self, X):
         X = _f32(X); out = np.zeros(X.size, np.uint16)
@@ -170,6 +177,14 @@ class Oracle(_Common):
         self.lib.oracle_silu_mul.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         self.lib.oracle_silu_mul(_p(gate), _p(up), gate.size, _p(y))
         return y
+
+    def moe_combine(self, experts, weights):
+        """llama.cpp/src/llama.cpp:8303-8318 restated: rounded products, added in expert order (plain IEEE fp32)."""
+        experts, weights = _f32(experts), _f32(weights)
+        acc = experts[:, 0, :] * weights[:, 0:1]
+        for j in range(1, experts.shape[1]):
+            acc = acc + experts[:, j, :] * weights[:, j:j + 1]
+        return acc.astype(np.float32)
 
     def mixmul_needs(self, w: Tensor, x: Tensor, plan: Tensor) -> int:
         return int(self.lib.oracle_mixmul_needs(C.byref(w), C.byref(x), C.byref(plan)))
@@ -223,6 +238,19 @@ class Reference(_Common):
     def quantize_q4_K(self, X): return self._rows(self.lib.ref_quantize_q4_K_ref, X, Q4_K)
     def quantize_q6_K(self, X): return self._rows(self.lib.ref_quantize_q6_K_ref, X, Q6_K)
 
+    def quantize_type(self, type_, X):
+        """quantize_row_<type>_ref for the §8 f3 types (Q4_1, Q5_0, Q5_K, IQ4_XS)."""
+        X = _f32(X)
+        rows, k = X.reshape(-1, X.shape[-1]).shape
+        out = np.zeros(rows * row_bytes(type_, k), np.uint8)
+        self.lib.ref_quantize_type_ref.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_long, C.c_long]
+        assert self.lib.ref_quantize_type_ref(type_, _p(X), _p(out), rows, k)
+        return out
+
+    def quantize_q8_1(self, X, nth=1):
+        self.lib.ref_quantize_q8_1.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_long, C.c_int]
+        return self._rows(self.lib.ref_quantize_q8_1, X, Q8_1, nth)
+
     def fp32_to_fp16(self, X):
         X = _f32(X); out = np.zeros(X.size, np.uint16)
         self.lib.ref_fp32_to_fp16_row(_p(X), _p(out), X.size)
@@ -230,6 +258,10 @@ class Reference(_Common):
 
     def dequantize(self, type_, data, n):
         out = np.zeros(n, np.float32)
+        if type_ in (Q4_1, Q5_0, Q5_K, IQ4_XS):
+            self.lib.ref_dequantize_type.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_long]
+            assert self.lib.ref_dequantize_type(type_, _p(data), _p(out), n)
+            return out
         {Q4_0: self.lib.ref_dequantize_q4_0, Q8_0: self.lib.ref_dequantize_q8_0, Q4_K: self.lib.ref_dequantize_q4_K, Q6_K: self.lib.ref_dequantize_q6_K,
          F16: self.lib.ref_fp16_to_fp32_row}[type_](_p(data), _p(out), n)
         return out
@@ -252,6 +284,15 @@ class Reference(_Common):
         gate, up = _f32(gate), _f32(up); y = np.empty_like(gate)
         self.lib.ref_silu_mul.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_void_p]
         self.lib.ref_silu_mul(_p(gate), _p(up), gate.size, _p(y))
+        return y
+
+    def moe_combine(self, experts, weights):
+        """experts [tokens, used, rows], weights [tokens, used] -> [tokens, rows] through ggml_mul + ggml_add."""
+        experts, weights = _f32(experts), _f32(weights)
+        tokens, used, rows = experts.shape
+        y = np.empty((tokens, rows), np.float32)
+        self.lib.ref_moe_combine.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_long, C.c_long, C.c_void_p]
+        self.lib.ref_moe_combine(_p(experts), _p(weights), rows, used, tokens, _p(y))
         return y
 
     def add(self, a, b):

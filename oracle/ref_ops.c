@@ -129,3 +129,20 @@ EXPORT int ref_backend_abi(long *out, int cap) {
     for (int i = 0; i < n && i < cap; ++i) out[i] = v[i];
     return n;
 }
+
+/* MoE tail (llama.cpp/src/llama.cpp:8303-8318): experts [rows, used, tokens] * weights [1, used, tokens], then the used experts'
+ * slices added in order. out [rows, tokens]. */
+EXPORT void ref_moe_combine(const float *experts, const float *weights, long rows, long used, long tokens, float *out) {
+    struct ggml_context *ctx = ctx_for(rows * used * tokens);
+    struct ggml_tensor *e = ggml_new_tensor_3d(ctx, GGML_TYPE_F32, rows, used, tokens), *w = ggml_new_tensor_3d(ctx, GGML_TYPE_F32, 1, used, tokens);
+    memcpy(e->data, experts, (size_t)rows * used * tokens * 4);
+    memcpy(w->data, weights, (size_t)used * tokens * 4);
+    struct ggml_tensor *m = ggml_mul(ctx, e, w), *acc = NULL;
+    for (long i = 0; i < used; ++i) {
+        struct ggml_tensor *cur = ggml_view_2d(ctx, m, rows, tokens, m->nb[2], i * m->nb[1]);
+        acc = i == 0 ? cur : ggml_add(ctx, acc, cur);
+    }
+    if (used == 1) acc = ggml_cont(ctx, acc);
+    compute(ctx, acc, out, rows * tokens);
+    ggml_free(ctx);
+}

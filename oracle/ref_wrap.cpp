@@ -11,6 +11,7 @@
 #include <omp.h>
 #include <stddef.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "llama.cpp/ggml.h"            // PATCHED header (scratch tree): ggml_tensor / ggml_compute_params layout
@@ -37,6 +38,15 @@ void Q(quantize_row_q8_K)(const float *x, void *y, int64_t k);
 void Q(quantize_row_q4_0_ref)(const float *x, void *y, int64_t k);
 void Q(quantize_row_q4_K_ref)(const float *x, void *y, int64_t k);
 void Q(quantize_row_q6_K_ref)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q4_1_ref)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q5_0_ref)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q5_K_ref)(const float *x, void *y, int64_t k);
+void Q(quantize_row_iq4_xs_ref)(const float *x, void *y, int64_t k);
+void Q(quantize_row_q8_1)(const float *x, void *y, int64_t k);
+void Q(dequantize_row_q4_1)(const void *x, float *y, int64_t k);
+void Q(dequantize_row_q5_0)(const void *x, float *y, int64_t k);
+void Q(dequantize_row_q5_K)(const void *x, float *y, int64_t k);
+void Q(dequantize_row_iq4_xs)(const void *x, float *y, int64_t k);
 void Q(dequantize_row_q4_0)(const void *x, float *y, int64_t k);
 void Q(dequantize_row_q8_0)(const void *x, float *y, int64_t k);
 void Q(dequantize_row_q4_K)(const void *x, float *y, int64_t k);
@@ -64,13 +74,15 @@ struct Funcs {
     moe_fn *iqk_mixmul;
     Funcs() {
         __builtin_cpu_init();
+        const char *force = getenv("TB200_REF_VARIANT");   // diagnosis only: "avx2" / "avx512f" force a lower ISA variant than the CPU's
+        const bool no512 = force && !strcmp(force, "avx2"), nozen4 = no512 || (force && !strcmp(force, "avx512f"));
         // llamafile/sgemm.cpp:32-60
-        if (__builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512vl") &&
+        if (!nozen4 && __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512vl") &&
             __builtin_cpu_supports("avx512bw") && __builtin_cpu_supports("avx512dq") &&
             __builtin_cpu_supports("avx512vnni") && __builtin_cpu_supports("avx512bf16")) {
             variant = 0, name = "amd_zen4";
             sgemm = llamafile_sgemm_amd_zen4, mixmul = llamafile_mixmul_amd_zen4, iqk_mixmul = iqk_mul_mat_moe_zen4;
-        } else if (__builtin_cpu_supports("avx512f")) {
+        } else if (!no512 && __builtin_cpu_supports("avx512f")) {
             variant = 1, name = "amd_avx512f";
             sgemm = llamafile_sgemm_amd_avx512f, mixmul = llamafile_mixmul_amd_avx512f, iqk_mixmul = iqk_mul_mat_moe;
         } else {
@@ -195,6 +207,36 @@ EXPORT void ref_quantize_q6_K_ref(const float *x, void *y, long rows, long k) {
     funcs();
 #pragma omp parallel for
     for (long r = 0; r < rows; ++r) Q(quantize_row_q6_K_ref)(x + r * k, (char *)y + r * (k / 256) * 210, k);
+}
+// SURVEY.md §8 f3 types: `type` is the ggml type code; row bytes from the block sizes
+EXPORT int ref_quantize_type_ref(int type, const float *x, void *y, long rows, long k) {
+    funcs();
+    long rb; void (*fn)(const float *, void *, int64_t);
+    switch (type) {
+    case 3: rb = k / 32 * 20, fn = Q(quantize_row_q4_1_ref); break;
+    case 6: rb = k / 32 * 22, fn = Q(quantize_row_q5_0_ref); break;
+    case 13: rb = k / 256 * 176, fn = Q(quantize_row_q5_K_ref); break;
+    case 23: rb = k / 256 * 136, fn = Q(quantize_row_iq4_xs_ref); break;
+    default: return 0;
+    }
+#pragma omp parallel for
+    for (long r = 0; r < rows; ++r) fn(x + r * k, (char *)y + r * rb, k);
+    return 1;
+}
+EXPORT void ref_quantize_q8_1(const float *x, void *y, long rows, long k, int nth) {
+    funcs();
+#pragma omp parallel for num_threads(clamp_threads(nth))
+    for (long r = 0; r < rows; ++r) Q(quantize_row_q8_1)(x + r * k, (char *)y + r * (k / 32) * 36, k);
+}
+EXPORT int ref_dequantize_type(int type, const void *x, float *y, long n) {
+    funcs();
+    switch (type) {
+    case 3: Q(dequantize_row_q4_1)(x, y, n); return 1;
+    case 6: Q(dequantize_row_q5_0)(x, y, n); return 1;
+    case 13: Q(dequantize_row_q5_K)(x, y, n); return 1;
+    case 23: Q(dequantize_row_iq4_xs)(x, y, n); return 1;
+    default: return 0;
+    }
 }
 EXPORT void ref_fp32_to_fp16_row(const float *x, uint16_t *y, long n) { funcs(); ggml_fp32_to_fp16_row(x, y, n); }
 EXPORT void ref_fp16_to_fp32_row(const uint16_t *x, float *y, long n) { funcs(); ggml_fp16_to_fp32_row(x, y, n); }

@@ -18,6 +18,13 @@ typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qs[128]; } blk_q4
 typedef struct { float d; int16_t bsums[16]; int8_t qs[256]; } blk_q8_K;       /* 292 B */
 /* llama.cpp/ggml/src/ggml-common.h:299-307 */
 typedef struct { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; uint16_t d; } blk_q6_K; /* 210 B */
+/* the remaining types iqk serves on the same entry points (ggml-common.h:151-169, 193-203, 280-295, 393-398) */
+typedef struct { uint16_t d, m; uint8_t qs[16]; } blk_q4_1;                                   /* 20 B */
+typedef struct { uint16_t d; uint8_t qh[4]; uint8_t qs[16]; } blk_q5_0;                        /* 22 B */
+typedef struct { uint16_t d, s; int8_t qs[32]; } blk_q8_1;                                     /* 36 B */
+typedef struct { uint16_t d, dmin; uint8_t scales[12]; uint8_t qh[32]; uint8_t qs[128]; } blk_q5_K;   /* 176 B */
+typedef struct { uint16_t d; uint16_t scales_h; uint8_t scales_l[4]; uint8_t qs[128]; } blk_iq4_xs;   /* 136 B */
+static const int8_t kvalues_iq4nl[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};   /* ggml-quants.c:3548 */
 #pragma pack(pop)
 _Static_assert(sizeof(blk_q6_K) == 210, "q6_K");
 _Static_assert(sizeof(blk_q4_0) == 18, "q4_0");
@@ -33,13 +40,14 @@ static inline uint16_t f2h(float f) { _Float16 v = (_Float16)f; uint16_t h; memc
 size_t oracle_type_size(int type) {
     switch (type) {
     case OR_F32: return 4; case OR_F16: return 2; case OR_Q4_0: return 18; case OR_Q8_0: return 34;
-    case OR_Q4_K: return 144; case OR_Q6_K: return 210; case OR_Q8_K: return 292; case OR_I32: return 4; default: return 0;
+    case OR_Q4_K: return 144; case OR_Q6_K: return 210; case OR_Q8_K: return 292; case OR_I32: return 4;
+    case OR_Q4_1: return 20; case OR_Q5_0: return 22; case OR_Q8_1: return 36; case OR_Q5_K: return 176; case OR_IQ4_XS: return 136; default: return 0;
     }
 }
 int oracle_blck_size(int type) {
     switch (type) {
-    case OR_F32: case OR_F16: case OR_I32: return 1; case OR_Q4_0: case OR_Q8_0: return 32;
-    case OR_Q4_K: case OR_Q6_K: case OR_Q8_K: return 256; default: return 0;
+    case OR_F32: case OR_F16: case OR_I32: return 1; case OR_Q4_0: case OR_Q8_0: case OR_Q4_1: case OR_Q5_0: case OR_Q8_1: return 32;
+    case OR_Q4_K: case OR_Q6_K: case OR_Q8_K: case OR_Q5_K: case OR_IQ4_XS: return 256; default: return 0;
     }
 }
 
@@ -65,6 +73,22 @@ void oracle_quantize_row_q8_0(const float *x, void *vy, int64_t k) {
         const float id = (amax != 0.0f) ? 127.f / amax : 0.0f;
         y[i].d = f2h(d);
         for (int j = 0; j < QK; ++j) y[i].qs[j] = cvt_rne_sat8(x[j] * id);
+    }
+}
+
+/* quantize_row_q8_1, x86 runtime body (ggml-quants.c:1276-1321): quantize_row_q8_0's d and quants, plus s = fp16(d * sum q)
+ * with the UNROUNDED d. */
+void oracle_quantize_row_q8_1(const float *x, void *vy, int64_t k) {
+    blk_q8_1 *y = (blk_q8_1 *)vy;
+    for (int64_t i = 0; i < k / QK; ++i, x += QK) {
+        float amax = 0.0f;
+        for (int j = 0; j < QK; ++j) { float a = fabsf(x[j]); if (a > amax) amax = a; }
+        const float d = amax / 127.f;
+        const float id = (amax != 0.0f) ? 127.f / amax : 0.0f;
+        y[i].d = f2h(d);
+        int sum = 0;
+        for (int j = 0; j < QK; ++j) { y[i].qs[j] = cvt_rne_sat8(x[j] * id); sum += y[i].qs[j]; }
+        y[i].s = f2h(d * sum);
     }
 }
 
@@ -184,6 +208,49 @@ void oracle_dequantize_row(int type, const void *vx, float *y, int64_t k) {
                 y += 128; ql += 64; qh += 32; sc += 8;
             }
         }
+    } else if (type == OR_Q4_1) {   /* ggml-quants.c:1535-1554 */
+        const blk_q4_1 *x = (const blk_q4_1 *)vx;
+        for (int64_t i = 0; i < k / QK; ++i) {
+            const float d = h2f(x[i].d), m = h2f(x[i].m);
+            for (int j = 0; j < 16; ++j) { y[i * QK + j] = (x[i].qs[j] & 0x0F) * d + m; y[i * QK + j + 16] = (x[i].qs[j] >> 4) * d + m; }
+        }
+    } else if (type == OR_Q5_0) {   /* ggml-quants.c:1556-1580 */
+        const blk_q5_0 *x = (const blk_q5_0 *)vx;
+        for (int64_t i = 0; i < k / QK; ++i) {
+            const float d = h2f(x[i].d);
+            uint32_t qh; memcpy(&qh, x[i].qh, 4);
+            for (int j = 0; j < 16; ++j) {
+                const uint8_t xh_0 = ((qh >> (j + 0)) << 4) & 0x10, xh_1 = ((qh >> (j + 12))) & 0x10;
+                y[i * QK + j] = (((x[i].qs[j] & 0x0F) | xh_0) - 16) * d;
+                y[i * QK + j + 16] = (((x[i].qs[j] >> 4) | xh_1) - 16) * d;
+            }
+        }
+    } else if (type == OR_Q5_K) {   /* ggml-quants.c:2756-2781 */
+        const blk_q5_K *x = (const blk_q5_K *)vx;
+        for (int64_t i = 0; i < k / QK_K; ++i) {
+            const uint8_t *ql = x[i].qs, *qh = x[i].qh;
+            const float d = h2f(x[i].d), min = h2f(x[i].dmin);
+            int is = 0; uint8_t sc, m, u1 = 1, u2 = 2;
+            for (int j = 0; j < QK_K; j += 64) {
+                get_scale_min_k4(is + 0, x[i].scales, &sc, &m); const float d1 = d * sc, m1 = min * m;
+                get_scale_min_k4(is + 1, x[i].scales, &sc, &m); const float d2 = d * sc, m2 = min * m;
+                for (int l = 0; l < 32; ++l) *y++ = d1 * ((ql[l] & 0xF) + (qh[l] & u1 ? 16 : 0)) - m1;
+                for (int l = 0; l < 32; ++l) *y++ = d2 * ((ql[l] >> 4) + (qh[l] & u2 ? 16 : 0)) - m2;
+                ql += 32; is += 2; u1 <<= 2; u2 <<= 2;
+            }
+        }
+    } else if (type == OR_IQ4_XS) {   /* ggml-quants.c:3568-3590 */
+        const blk_iq4_xs *x = (const blk_iq4_xs *)vx;
+        for (int64_t i = 0; i < k / QK_K; ++i) {
+            const uint8_t *qs = x[i].qs;
+            const float d = h2f(x[i].d);
+            for (int ib = 0; ib < QK_K / 32; ++ib) {
+                const int ls = ((x[i].scales_l[ib / 2] >> 4 * (ib % 2)) & 0xf) | (((x[i].scales_h >> 2 * ib) & 3) << 4);
+                const float dl = d * (ls - 32);
+                for (int j = 0; j < 16; ++j) { y[j] = dl * kvalues_iq4nl[qs[j] & 0xf]; y[j + 16] = dl * kvalues_iq4nl[qs[j] >> 4]; }
+                y += 32; qs += 16;
+            }
+        }
     } else if (type == OR_F16) {
         oracle_fp16_to_fp32_row((const uint16_t *)vx, y, k);
     } else if (type == OR_F32) {
@@ -298,6 +365,68 @@ float oracle_vec_dot(int xtype, int64_t n, const void *vx, const void *vy) {
         }
         return sumf;
     }
+    if (xtype == OR_Q5_0) {   /* ggml_vec_dot_q5_0_q8_0 generic branch, ggml-quants.c:4828-4848: sumf += (d_x*d_y) * sumi */
+        const int64_t nb = n / QK; float sumf = 0;
+        const blk_q5_0 *x = (const blk_q5_0 *)vx; const blk_q8_0 *y = (const blk_q8_0 *)vy;
+        for (int64_t ib = 0; ib < nb; ++ib) {
+            uint32_t qh; memcpy(&qh, x[ib].qh, 4);
+            int sumi = 0;
+            for (int j = 0; j < 16; ++j) {
+                const uint8_t xh_0 = ((qh & (1u << (j + 0))) >> (j + 0)) << 4, xh_1 = ((qh & (1u << (j + 16))) >> (j + 12));
+                const int x0 = ((x[ib].qs[j] & 0x0F) | xh_0) - 16, x1 = ((x[ib].qs[j] >> 4) | xh_1) - 16;
+                sumi += x0 * y[ib].qs[j] + x1 * y[ib].qs[j + 16];
+            }
+            sumf += (h2f(x[ib].d) * h2f(y[ib].d)) * sumi;
+        }
+        return sumf;
+    }
+    if (xtype == OR_Q4_1) {   /* ggml_vec_dot_q4_1_q8_1 scalar, ggml-quants.c:4476-4492: sumf += (d_x*d_y)*sumi + m_x*s_y */
+        const int64_t nb = n / QK; float sumf = 0;
+        const blk_q4_1 *x = (const blk_q4_1 *)vx; const blk_q8_1 *y = (const blk_q8_1 *)vy;
+        for (int64_t ib = 0; ib < nb; ++ib) {
+            int sumi = 0;
+            for (int j = 0; j < 16; ++j) sumi += (x[ib].qs[j] & 0x0F) * y[ib].qs[j] + (x[ib].qs[j] >> 4) * y[ib].qs[j + 16];
+            sumf += (h2f(x[ib].d) * h2f(y[ib].d)) * sumi + h2f(x[ib].m) * h2f(y[ib].s);
+        }
+        return sumf;
+    }
+    if (xtype == OR_Q5_K) {   /* ggml_vec_dot_q5_K_q8_K generic branch, ggml-quants.c:7985-8032: per super-block d*sum_s sc_s*dot_s - dmin*sum_j m*bsums */
+        const int64_t nb = n / QK_K; float sumq = 0, sumf = 0;
+        const blk_q5_K *x = (const blk_q5_K *)vx; const blk_q8_K *y = (const blk_q8_K *)vy;
+        for (int64_t i = 0; i < nb; ++i) {
+            int32_t sq = 0, sm = 0;
+            for (int s8 = 0; s8 < 8; ++s8) {
+                uint8_t sc, m; get_scale_min_k4(s8, x[i].scales, &sc, &m);
+                const uint8_t *ql = x[i].qs + 32 * (s8 / 2);
+                int dot = 0;
+                for (int l = 0; l < 32; ++l) {
+                    const int q = ((s8 & 1) ? (ql[l] >> 4) : (ql[l] & 0xF)) + (((x[i].qh[l] >> s8) & 1) ? 16 : 0);
+                    dot += q * y[i].qs[32 * s8 + l];
+                }
+                sq += sc * dot;
+                sm += m * (y[i].bsums[2 * s8] + y[i].bsums[2 * s8 + 1]);
+            }
+            sumq += h2f(x[i].d) * y[i].d * sq;
+            sumf -= h2f(x[i].dmin) * y[i].d * sm;
+        }
+        return sumf + sumq;
+    }
+    if (xtype == OR_IQ4_XS) {   /* ggml_vec_dot_iq4_xs_q8_K generic branch, ggml-quants.c:12100-12130: d4d8 * (ls - 32) * dot per 32-sub-block (integer sub-block sums here, one fp32 scale per super-block) */
+        const int64_t nb = n / QK_K; float sumf = 0;
+        const blk_iq4_xs *x = (const blk_iq4_xs *)vx; const blk_q8_K *y = (const blk_q8_K *)vy;
+        for (int64_t i = 0; i < nb; ++i) {
+            int32_t si = 0;
+            for (int ib = 0; ib < 8; ++ib) {
+                const int ls = ((x[i].scales_l[ib / 2] >> 4 * (ib % 2)) & 0xf) | (((x[i].scales_h >> 2 * ib) & 3) << 4);
+                const uint8_t *qs = x[i].qs + 16 * ib;
+                int dot = 0;
+                for (int j = 0; j < 16; ++j) dot += kvalues_iq4nl[qs[j] & 0xf] * y[i].qs[32 * ib + j] + kvalues_iq4nl[qs[j] >> 4] * y[i].qs[32 * ib + 16 + j];
+                si += (ls - 32) * dot;
+            }
+            sumf += h2f(x[i].d) * y[i].d * si;
+        }
+        return sumf;
+    }
     return NAN;
 }
 
@@ -323,8 +452,8 @@ int oracle_sgemm(long m, long n, long k, const void *A, long lda, const void *B,
     if (Ctype != OR_F32) return 0;
     float *c = (float *)C;
     if (Btype == OR_Q8_K) {
-        if (Atype != OR_Q4_K && Atype != OR_Q6_K) return 0;   /* iqk_mul_mat.inc:1408-1463: the k-quants this build holds */
-        const long rowa = Atype == OR_Q4_K ? 144 : 210;
+        if (Atype != OR_Q4_K && Atype != OR_Q6_K && Atype != OR_Q5_K && Atype != OR_IQ4_XS) return 0;   /* iqk_mul_mat.inc:1408-1463: the k-quants this build holds */
+        const long rowa = (long)oracle_type_size(Atype);
         /* iqk ignores lda/ldb: rows are ggml_row_size apart (iqk_mul_mat.inc:191-199) */
         _Pragma("omp parallel for collapse(2)")
         for (long j = 0; j < n; ++j) for (long i = 0; i < m; ++i)
@@ -335,6 +464,13 @@ int oracle_sgemm(long m, long n, long k, const void *A, long lda, const void *B,
         _Pragma("omp parallel for collapse(2)")
         for (long j = 0; j < n; ++j) for (long i = 0; i < m; ++i)
             c[ldc * j + i] = oracle_vec_dot(OR_Q4_0, k * QK, (const char *)A + i * k * 18, (const char *)B + j * k * 34);
+        return 1;
+    }
+    if ((Atype == OR_Q5_0 && Btype == OR_Q8_0) || (Atype == OR_Q4_1 && Btype == OR_Q8_1)) {   /* iqk_mul_mat.inc:1442-1451 */
+        const long rowa = (long)oracle_type_size(Atype), rowb = (long)oracle_type_size(Btype);
+        _Pragma("omp parallel for collapse(2)")
+        for (long j = 0; j < n; ++j) for (long i = 0; i < m; ++i)
+            c[ldc * j + i] = oracle_vec_dot(Atype, k * QK, (const char *)A + i * k * rowa, (const char *)B + j * k * rowb);
         return 1;
     }
     if (Atype == OR_Q8_0 && Btype == OR_Q8_0) {
@@ -467,6 +603,10 @@ int oracle_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, const vo
     if (typeA == OR_Q4_K) { btype = OR_Q8_K; bs_a = 144; bs_b = 292; blk = 256; }
     else if (typeA == OR_Q6_K) { btype = OR_Q8_K; bs_a = 210; bs_b = 292; blk = 256; }
     else if (typeA == OR_Q4_0) { btype = OR_Q8_0; bs_a = 18; bs_b = 34; blk = 32; }
+    else if (typeA == OR_Q5_K) { btype = OR_Q8_K; bs_a = 176; bs_b = 292; blk = 256; }
+    else if (typeA == OR_IQ4_XS) { btype = OR_Q8_K; bs_a = 136; bs_b = 292; blk = 256; }
+    else if (typeA == OR_Q5_0) { btype = OR_Q8_0; bs_a = 22; bs_b = 34; blk = 32; }
+    else if (typeA == OR_Q4_1) { btype = OR_Q8_1; bs_a = 20; bs_b = 36; blk = 32; }
     else return 0;   /* other iqk types (:1408-1463) are outside the build's scope */
     (void)btype;
     if (ne00 % blk) return 0;

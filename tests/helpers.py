@@ -6,8 +6,11 @@ import numpy as np
 from oracle import binding as B
 
 F32, F16, Q4_0, Q8_0, Q4_K, Q6_K, Q8_K, I32 = B.F32, B.F16, B.Q4_0, B.Q8_0, B.Q4_K, B.Q6_K, B.Q8_K, B.I32
+Q4_1, Q5_0, Q8_1, Q5_K, IQ4_XS = B.Q4_1, B.Q5_0, B.Q8_1, B.Q5_K, B.IQ4_XS
 WEIGHT_TYPES = [Q4_0, Q8_0, Q4_K, Q6_K, F16]
-TYPE_NAME = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K", Q8_K: "q8_K"}
+G8_TYPES = [Q4_1, Q5_0, Q5_K, IQ4_XS]   # served through the generic resident form
+TYPE_NAME = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K", Q8_K: "q8_K", Q4_1: "q4_1", Q5_0: "q5_0", Q8_1: "q8_1",
+             Q5_K: "q5_K", IQ4_XS: "iq4_xs"}
 
 # fp32 output gate (north_star): max|c-r| / max|r| <= 1e-3, plus the reference's own backend gate NMSE <= 5e-4
 # (llama.cpp/tests/test-backend-ops.cpp:966-968)
@@ -56,6 +59,22 @@ def synth_q6_K(rows: int, k: int, seed: int) -> np.ndarray:
     return blk.reshape(-1)
 
 
+def synth_g8(wtype: int, rows: int, k: int, seed: int) -> np.ndarray:
+    """Random but well-formed blocks of the §8 f3 types (any byte pattern is valid; the fp16 scales kept finite and small)."""
+    rng = np.random.default_rng(seed)
+    ts, blck = B.TYPE_SIZE[wtype], B.BLCK[wtype]
+    nb = rows * k // blck
+    blk = rng.integers(0, 256, (nb, ts), dtype=np.uint8)
+    d = (rng.uniform(0.5, 2.0, nb) * {Q4_1: 2e-3, Q5_0: 1e-3, Q5_K: 4e-5, IQ4_XS: 1e-5}[wtype]).astype(np.float16)
+    blk[:, 0:2] = d.view(np.uint8).reshape(nb, 2)
+    if wtype in (Q4_1, Q5_K):
+        m = (rng.uniform(-1.0, 1.0, nb) * (2e-2 if wtype == Q4_1 else 2e-4)).astype(np.float16)
+        if wtype == Q5_K:
+            m = np.abs(m)
+        blk[:, 2:4] = m.view(np.uint8).reshape(nb, 2)
+    return blk.reshape(-1)
+
+
 def make_weights(wtype: int, rows: int, k: int, seed: int = 1, realistic_q4k: bool = True) -> np.ndarray:
     """fp32 N(0, 0.02^2) quantized with the reference's *_ref quantizers (oracle restatements). Q4_K uses the
     reference library when present (quantize_row_q4_K_ref is weight-prep, outside the hot path), else
@@ -72,6 +91,11 @@ def make_weights(wtype: int, rows: int, k: int, seed: int = 1, realistic_q4k: bo
         if r is None:
             return synth_q6_K(rows, k, seed)
         return r.quantize_q6_K((rng.standard_normal((rows, k)) * 0.02).astype(np.float32))
+    if wtype in G8_TYPES:
+        r = B.reference() if realistic_q4k else None
+        if r is None:
+            return synth_g8(wtype, rows, k, seed)
+        return r.quantize_type(wtype, (rng.standard_normal((rows, k)) * 0.02).astype(np.float32))
     w = (rng.standard_normal((rows, k)) * 0.02).astype(np.float32)
     if wtype == Q4_0:
         return o.quantize_q4_0(w)

@@ -188,3 +188,60 @@ def test_plan_llama3_8b_layer_shapes_sampled(tb, oracle):
             for lo in (0, n // 2 - 7, n - 16):
                 ref = oracle.mul_mat(W[lo * rb:(lo + 16) * rb], H.Q4_0, x[None])
                 H.assert_close(got[lo:lo + 16][None], ref, f"K={K} n={n} rows {lo}")
+
+
+# ------------------------------------------------------------------ the neighbours for any token count (tb200_fused.cu)
+@pytest.mark.parametrize("tokens,k", [(1, 4096), (5, 512), (33, 14336)])
+def test_rms_norm_mul_and_silu_mul_device(tb, oracle, tokens, k):
+    rng = np.random.default_rng(tokens + k)
+    x = (rng.standard_normal((tokens, k)) * 3).astype(np.float32)
+    w = (1 + 0.1 * rng.standard_normal(k)).astype(np.float32)
+    y = torch.empty(tokens, k, device="cuda")
+    tb.rms_norm_mul(dev(x), dev(w), 1e-5, tokens, k, y)
+    tb.synchronize()
+    ref = np.stack([oracle.rms_norm_mul(r, w, 1e-5) for r in x])
+    got = y.cpu().numpy()
+    # bit-exact up to the last bit of the double-precision sum of squares (a tree here, sequential in ggml): allow a 1-ulp scale slip
+    assert float(np.abs(got - ref).max() / np.abs(ref).max()) < 2e-7
+    assert float((got != ref).mean()) < 0.5
+    g, u = (rng.standard_normal((tokens, k)) * 2).astype(np.float32), rng.standard_normal((tokens, k)).astype(np.float32)
+    tb.silu_mul(dev(g), dev(u), tokens, k, y)
+    tb.synchronize()
+    ref = np.stack([oracle.silu_mul(a, b) for a, b in zip(g, u)])
+    assert float(np.abs(y.cpu().numpy() - ref).max() / np.abs(ref).max()) < 1e-6
+
+
+@pytest.mark.parametrize("tokens,used,rows", [(1, 2, 4096), (9, 2, 1000), (4, 1, 64), (3, 4, 300)])
+def test_moe_combine_bit_exact(tb, oracle, tokens, used, rows):
+    rng = np.random.default_rng(rows)
+    e = rng.standard_normal((tokens, used, rows)).astype(np.float32)
+    w = rng.uniform(0, 1, (tokens, used)).astype(np.float32)
+    out = torch.full((tokens, rows), float("nan"), device="cuda")
+    tb.moe_combine(dev(e), dev(w), tokens, used, rows, out)
+    tb.synchronize()
+    assert np.array_equal(out.cpu().numpy(), oracle.moe_combine(e, w))
+
+
+@pytest.mark.parametrize("wt", [H.Q4_0, H.Q4_K])
+def test_fused_acts_feed_prefill_matmuls(tb, oracle, wt):
+    """RMSNorm*weight -> from_float -> matmul and silu(gate)*up -> from_float -> matmul at a prefill token count."""
+    T, K, N = 40, 1024, 200
+    rng = np.random.default_rng(8)
+    x = (rng.standard_normal((T, K)) * 2).astype(np.float32)
+    nw = (1 + 0.1 * rng.standard_normal(K)).astype(np.float32)
+    W = H.make_weights(wt, N, K, seed=5, realistic_q4k=False)
+    w = tb.Weights(W, wt, N, K)
+    acts = tb.Acts(wt, K, T)
+    out = torch.full((T, N), float("nan"), device="cuda")
+    tb.acts_quantize_rmsnorm(acts, dev(x), T, dev(nw), 1e-5)
+    tb.mul_mat_acts(w, acts, out)
+    tb.synchronize()
+    ref = oracle.mul_mat(W, wt, np.stack([oracle.rms_norm_mul(r, nw, 1e-5) for r in x]))
+    H.assert_close(out.cpu().numpy(), ref, "rmsnorm -> matmul")
+    g, u = (rng.standard_normal((T, K)) * 2).astype(np.float32), rng.standard_normal((T, K)).astype(np.float32)
+    tb.acts_quantize_swiglu(acts, dev(g), dev(u), T)
+    tb.mul_mat_acts(w, acts, out)
+    tb.synchronize()
+    ref = oracle.mul_mat(W, wt, np.stack([oracle.silu_mul(a, b) for a, b in zip(g, u)]))
+    H.assert_close(out.cpu().numpy(), ref, "swiglu -> matmul")
+    w.free(); acts.free()

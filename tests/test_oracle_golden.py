@@ -91,3 +91,14 @@ def test_fused_layer_golden(oracle):
     assert np.array_equal(got["h1"], g["out_h1"])            # rms_norm * weight: bit-exact
     for k, v in got.items():
         H.assert_close(v[None], g[f"out_{k}"][None], k)
+
+
+@pytest.mark.parametrize("wt", H.G8_TYPES)
+def test_g8_types_golden(oracle, wt):
+    """SURVEY.md §8 f3 types: the oracle's dequantizers are bit-equal to the reference's, its products agree with llamafile_sgemm."""
+    g = np.load(ROOT / "tests" / "golden" / "g8_golden.npz")
+    W = g[f"w_{wt}"]
+    assert np.array_equal(oracle.dequantize(wt, W, 40 * 512), g[f"deq_{wt}"])
+    for T in (1, 3, 8, 33):
+        H.assert_close(oracle.mul_mat(W, wt, g[f"x_{wt}_{T}"]), g[f"mm_{wt}_{T}"], f"{H.TYPE_NAME[wt]} T={T}")
+    assert np.array_equal(oracle.quantize_q8_1(g["q81_x"]), g["q81_y"])

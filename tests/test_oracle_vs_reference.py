@@ -140,3 +140,28 @@ def test_rms_norm_mul_bit_exact_and_silu_mul_close(oracle, reference, n):
     a, b = oracle.silu_mul(g, u), reference.silu_mul(g, u)
     # ggml's SIMD silu evaluates expf by a polynomial (ggml.c:2432-2594): a few ulp from the scalar definition
     assert float(np.abs(a - b).max() / np.abs(b).max()) < 1e-6
+
+
+@pytest.mark.parametrize("tokens,used,rows", [(1, 2, 4096), (7, 2, 512), (5, 1, 64), (3, 4, 1000)])
+def test_moe_combine_bit_exact(oracle, reference, tokens, used, rows):
+    rng = np.random.default_rng(tokens + rows)
+    e = rng.standard_normal((tokens, used, rows)).astype(np.float32)
+    w = rng.uniform(0, 1, (tokens, used)).astype(np.float32)
+    assert np.array_equal(oracle.moe_combine(e, w), reference.moe_combine(e, w))
+
+
+@pytest.mark.parametrize("wt", H.G8_TYPES)
+def test_g8_types_oracle_vs_reference(oracle, reference, wt):
+    """Q4_1 / Q5_0 / Q5_K / IQ4_XS on fresh inputs. IQ4_XS: inside the reference kernels' exact domain (see
+    tests/golden/make_golden_g8.py: they saturate int16 lanes on large activation quants)."""
+    N, K = 33, 1024
+    W = H.make_weights(wt, N, K, seed=wt)
+    assert np.array_equal(oracle.dequantize(wt, W, N * K), reference.dequantize(wt, W, N * K))
+    for T in (1, 5):
+        X = H.make_acts(T, K, seed=T)
+        if wt == H.IQ4_XS:
+            X[:, ::256] = 60.0
+        a, b = oracle.mul_mat(W, wt, X), reference.mul_mat(W, wt, X, nth=2)
+        assert H.scaled_err(a, b) < 5e-6
+    x = (np.random.default_rng(3).standard_normal((7, 512)) * 2).astype(np.float32)
+    assert np.array_equal(oracle.quantize_q8_1(x), reference.quantize_q8_1(x))
