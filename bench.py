@@ -371,7 +371,7 @@ def run_b200_arm(args):
     wtype, layers, layer, tail = WORKLOADS[args.workload]
     if args.layers:
         layers = args.layers
-    use_plan = args.decode == "plan" and wtype == Q4_0 and world == 1
+    use_plan = args.decode == "plan" and wtype == Q4_0   # N > 1: the replicated groups run as plan launches, the sharded ones through the fused all-gather
 
     specs = [(f"l{li}.{n}", N, K, f"l{li}.{g}") for li in range(layers) for (n, N, K, g) in layer] + [(n, N, K, g) for (n, N, K, g) in tail]
     # north_star: "weight matrices of layers large enough to split are sharded by output rows". A launch group (the matrices
@@ -400,7 +400,9 @@ def run_b200_arm(args):
     groups, schedule = {}, []
     for i, m in enumerate(mats):
         if m[5] not in groups:
-            groups[m[5]] = (torch.randn(1, m[4], device=dev, dtype=torch.float32), None if use_plan else tb.Acts(wtype, m[4], 1))
+            gx = torch.Generator(device=dev); gx.manual_seed(77000 + len(groups))   # the activations are replicated: same values on every rank
+            groups[m[5]] = (torch.randn(1, m[4], device=dev, dtype=torch.float32, generator=gx),
+                            None if (use_plan and not split_grp[m[5]]) else tb.Acts(wtype, m[4], 1))
         if schedule and schedule[-1][0] == m[5] and len(schedule[-1][1]) < 4 and wtype in (Q4_0, Q4_K, Q6_K):
             schedule[-1][1].append(i)
         else:
@@ -426,15 +428,34 @@ def run_b200_arm(args):
             off += N * 4
         pg = PeerGroup(world, rank, off)
 
-    plan = None
+    plan, plan_index, segments = None, {}, []
     if use_plan:
-        plan = tb.Plan([{"w": [mats[i][6] for i in idx], "out": [outs[i] for i in idx], "x": groups[grp][0]} for grp, idx in schedule])
+        planned = [gi for gi, (grp, idx) in enumerate(schedule) if not split_grp[grp]]
+        plan = tb.Plan([{"w": [mats[i][6] for i in schedule[gi][1]], "out": [outs[i] for i in schedule[gi][1]], "x": groups[schedule[gi][0]][0]} for gi in planned])
+        plan_index = {gi: pi for pi, gi in enumerate(planned)}
+        # the step as segments: maximal runs of consecutive replicated groups (one plan launch each) and single sharded groups
+        for gi in range(len(schedule)):
+            if gi in plan_index and segments and segments[-1][0] == "plan" and segments[-1][2] == gi:
+                segments[-1][2] = gi + 1
+            elif gi in plan_index:
+                segments.append(["plan", gi, gi + 1])
+            else:
+                segments.append(["split", gi, gi + 1])
 
     def step(with_gather=True, with_quant=True):
-        if plan is not None:
+        if plan is not None and len(segments) == 1:
             plan.run()
             return
-        for gi, (grp, idx) in enumerate(schedule):
+        todo = segments if plan is not None else [["split", 0, len(schedule)]]
+        for kind, g0, g1 in todo:
+            if kind == "plan":
+                plan.run(plan_index[g0], g1 - g0)
+                continue
+            run_groups(range(g0, g1), with_gather, with_quant)
+
+    def run_groups(gis, with_gather, with_quant):
+        for gi in gis:
+            grp, idx = schedule[gi]
             x, acts = groups[grp]
             if with_quant:
                 acts.quantize(x, 1)
@@ -537,7 +558,9 @@ def run_b200_arm(args):
                 good = (not np.isnan(got).any()) and float(np.abs(got - full).max()) / den <= 1e-3
                 ok, checked = ok and good, checked + 1
                 if not good:
-                    sys.stderr.write(f"bench: PARITY MISMATCH on gathered output of {name}\n")
+                    bad = np.nonzero(~(np.abs(got - full) <= 1e-3 * den))[0]
+                    sys.stderr.write(f"bench: PARITY MISMATCH on gathered output of {name}: {bad.size} of {N} rows differ, first {bad[:8].tolist()}, last {bad[-4:].tolist()}, "
+                                     f"nan {int(np.isnan(got).sum())}, got {got[bad[:4]].tolist()} want {full[bad[:4]].tolist()}\n")
         flag = torch.tensor([1 if ok else 0], device=dev)
         dist.broadcast(flag, 0)
         if int(flag.item()) != 1:
@@ -557,9 +580,14 @@ def run_b200_arm(args):
 
     log('roofline pass')
     peak, peak_src = peaks["hbm"]
-    if plan is not None:
+    if plan is not None and len(segments) == 1:
         # the plan kernel IS the step: one launch, quantization inside
         ms_kernel, n_launch, kname = ms_per_step, 1, "plan_q4_0_kernel"
+    elif plan is not None:
+        # N > 1: the plan launches of the replicated groups + the sharded groups' GEMVs, no exchange and no quantizer launches
+        run_gemv, _ = capture(lambda: step(with_gather=False, with_quant=False))
+        ms_kernel = timed(run_gemv, args.steps, args.warmup) / args.steps
+        n_launch, kname = len(segments), "plan_q4_0_kernel + gemv_q4_0_kernel (sharded groups)"
     else:
         run_gemv, _ = capture(lambda: step(with_gather=False, with_quant=False))
         ms_kernel = timed(run_gemv, args.steps, args.warmup) / args.steps
@@ -584,7 +612,8 @@ def run_b200_arm(args):
     per_shape = {}
     for shape in sorted({(hi - lo, K) for (_, N, lo, hi, K, g, w) in mats}):
         idx = [i for i, m in enumerate(mats) if (m[3] - m[2], m[4]) == shape]
-        if plan is not None:
+        sub = None
+        if plan is not None and not split_grp[mats[idx[0]][5]]:
             sub = tb.Plan([{"w": [mats[i][6]], "out": [outs[i]], "x": groups[mats[i][5]][0]} for i in idx])
             run_s = sub.run
         else:
@@ -596,7 +625,7 @@ def run_b200_arm(args):
         b = algorithmic_bytes(wtype, shape[0], shape[1]) * len(idx)
         per_shape[f"N={shape[0]},K={shape[1]}"] = {"matrices": len(idx), "us_per_matrix": ms * 1e3 / len(idx), "GBps": b / (ms * 1e-3) / 1e9,
                                                   "frac": b / (ms * 1e-3) / 1e9 / peak, "distinct_MB": b / 1e6}
-        if plan is not None:
+        if sub is not None:
             sub.free()
     roofline["per_shape"] = per_shape
 
@@ -768,7 +797,8 @@ def run_b200_arm(args):
     if rank == 0 and not timed_out:
         cfg = workload_config(args.workload, args.layers)
         cfg.update({"launch_groups_per_step": len(schedule), "launches_per_step": int(launches_per_step),
-                    "decode": ("plan: one persistent kernel per step (per-warp TMA rings, in-kernel Q8_0 quantization, grid barrier between groups)" if plan is not None
+                    "decode": (("plan: one persistent kernel per step (per-warp TMA rings, in-kernel Q8_0 quantization, grid barrier between groups)" if len(segments) == 1 else
+                                f"plan launches for the replicated groups ({sum(1 for sg in segments if sg[0] == 'plan')} launches) + fused-all-gather GEMVs for the sharded ones") if plan is not None
                                else "oneshot: one quantizer + one GEMV launch per group, CUDA graph"),
                     "cuda_graph": graphed, "split_groups": sum(1 for g2, _ in schedule if split_grp[g2]),
                     "replicated_groups": sum(1 for g2, _ in schedule if not split_grp[g2]), "split_min_mb": args.split_min_mb,

@@ -269,7 +269,12 @@ TB200_API int tb200_acts_quantize_swiglu(tb200_acts *a, const float *gate, const
  * IPC handles (both from tb200_malloc). Matrix m's rows are this rank's slice starting at row row_lo[m] of a full output
  * with leading dimension ldo[m] stored at byte offset out_offset[m] of the symmetric buffer; every rank holds every
  * slice once tb200_peers_barrier() has passed. The reference moves such slices with cudaMemcpyPeerAsync + events per
- * device (llama.cpp/ggml/src/ggml-cuda.cu:1600-1676). */
+ * device (llama.cpp/ggml/src/ggml-cuda.cu:1600-1676).
+ * SLOT REUSE RULE: the barrier orders "all ranks have WRITTEN" before "any rank reads", not "all ranks have READ" before the
+ * next write. A region of the symmetric buffer may therefore be written again only after a LATER barrier that every rank
+ * enqueued after its last read of the region (e.g. give every matrix of a step its own offset, as bench.py does: a slot is
+ * rewritten one step, i.e. >= 1 barrier, after its consumers ran; or alternate two offsets). A barrier that gives up waiting
+ * (~2 s, a peer died) sets a sticky flag, tb200_peers_timed_out(): treat it as fatal, the epochs of the ranks no longer agree. */
 typedef struct tb200_peers tb200_peers;
 TB200_API int tb200_ipc_get_handle(const void *dev_ptr, void *handle64);
 TB200_API void *tb200_ipc_open_handle(const void *handle64);

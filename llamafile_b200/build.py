@@ -40,6 +40,19 @@ def sources():
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
+    """Idempotent and safe to call from several processes at once (one rank per GPU under torchrun): an exclusive file lock
+    serialises them, and whoever comes second finds the stamp up to date."""
+    import fcntl
+    OBJ.mkdir(exist_ok=True)
+    with open(OBJ / ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            return _build_locked(force, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(force: bool, verbose: bool) -> Path:
     srcs = sources()
     deps = srcs + sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.c")) + [PKG.parent / "include" / "tinyblas_b200.h"]
     sig = _sig(deps)

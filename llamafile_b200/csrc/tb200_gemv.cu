@@ -78,7 +78,8 @@ __device__ __forceinline__ void store_rows(const GemvQ4Args &A, int mat, float (
     }
     constexpr int kRowsPerCta = kWarps * R;
     __shared__ float s_out[T * kRowsPerCta];
-    const int warp = threadIdx.x >> 5;
+    __shared__ int s_live[kWarps];                    // a warp without work this round (resident grids: the last round) must not store:
+    const int warp = threadIdx.x >> 5;                // its r_base is the previous round's, and its sums are zero
 #pragma unroll
     for (int r = 0; r < R; ++r)
 #pragma unroll
@@ -86,10 +87,11 @@ __device__ __forceinline__ void store_rows(const GemvQ4Args &A, int mat, float (
             const float v = warp_sum(acc[r][t]);
             if (lane == 0) s_out[t * kRowsPerCta + warp * R + r] = v;
         }
+    if (lane == 0) s_live[warp] = active;
     __syncthreads();
     const long cta_base = r_base - (long)warp * R;   // first row of this CTA (relative to row0)
     const int j = threadIdx.x;                        // thread j < kRowsPerCta owns row j of the CTA: lanes write consecutive floats
-    if (j < kRowsPerCta && cta_base + j < nrows) {
+    if (j < kRowsPerCta && s_live[j / R] && cta_base + j < nrows) {
 #pragma unroll
         for (int t = 0; t < T; ++t)
             if (t < ntok) {
@@ -98,6 +100,7 @@ __device__ __forceinline__ void store_rows(const GemvQ4Args &A, int mat, float (
                 for (int pr = 0; pr < A.world; ++pr) *reinterpret_cast<float *>(A.peer_base[pr] + off) = v;
             }
     }
+    __syncthreads();                                  // resident grids call this once per round: s_out / s_live are rewritten next round
 }
 
 // (Unlike the K-quant kernels, this one loses with a shallower batch and four CTAs per SM: 3347 vs 3704 GB/s on the 8B step.)
@@ -1732,8 +1735,11 @@ int launch_T(tb200_ctx *c, const tb200_gemv_args &a) {
         if (a.w->type == TB200_TYPE_Q4_0 && a.items && a.n_live && a.nmat <= 1 && a.world <= 1 && grouped_q4_0_smem(T, a.w->k) <= 110 * 1024)
             return launch_grouped_q4_0<T>(c, a);
     if (total < (long)c->sm_count * kWarps * 4) return launch_TR<T, 1>(c, a);
+    // with peers the resident kernel's epilogue collects a CTA's 16 rows under ONE matrix: every matrix must then be whole CTAs
+    bool cta_aligned = a.nrows % (kWarps * 2) == 0;
+    for (int m = 1; m < a.nmat; ++m) cta_aligned = cta_aligned && a.w_more[m - 1]->rows % (kWarps * 2) == 0;
     if (a.w->type == TB200_TYPE_Q4_0 && !a.items && T <= 2 && resident_enabled() && total / 2 > 4 * 3L * c->sm_count * kWarps &&   // >= 4 rounds of the resident grid
-        (size_t)T * (a.w->k / QK) * 40 * 3 <= 200 * 1024)
+        (size_t)T * (a.w->k / QK) * 40 * 3 <= 200 * 1024 && (a.world <= 1 || cta_aligned))
         return launch_resident_q4_0<T>(c, a);
     return launch_TR<T, 2>(c, a);
 }

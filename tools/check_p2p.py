@@ -28,7 +28,8 @@ def main():
     o = B.oracle()
     ok_all = True
     # (weight type, K, matrix row counts, token counts); T > 8 goes through the tcgen05 GEMM whose epilogue does the peer stores
-    cases = ((H.Q4_0, 1024, [1000, 384, 130], (1, 4)), (H.Q4_K, 1024, [520, 256], (1, 4)), (H.Q4_0, 512, [128256 // 8], (1, 4)),
+    # 61440 rows / rank at K = 256 take the RESIDENT decode kernel (3 CTAs per SM walking row pairs; its last round is part empty)
+    cases = ((H.Q4_0, 256, [61440 * world + 256], (1, 2)), (H.Q4_0, 1024, [1000, 384, 130], (1, 4)), (H.Q4_K, 1024, [520, 256], (1, 4)), (H.Q4_0, 512, [128256 // 8], (1, 4)),
              (H.Q4_0, 1024, [1000, 384], (40, 300)), (H.Q8_0, 512, [700], (129,)), (H.Q4_K, 1024, [520], (64,)), (H.F16, 512, [300], (33,)))
     for wt, K, shapes, toks in cases:
         for T in toks:
