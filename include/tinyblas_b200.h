@@ -204,6 +204,21 @@ TB200_API int tb200_quantize_q8_K_dev(const float *x, long ldx, void *y, long ro
 #define TB200_MAX_PEERS 8
 TB200_API int tb200_mul_mat(const tb200_weights *w, const float *x, long ldx, long tokens, float *out, long ldo);
 
+/* tb200_mul_mat for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same arguments, same kernels and
+ * bit-identical results as tb200_mul_mat, but the quantized activations go into a fixed device array inside the library
+ * (TB200_NOALLOC_SCRATCH_BYTES of HBM per GPU that loads the library, held until exit) instead of the context's growable
+ * cudaMalloc arena, and the call path contains no cudaMalloc / cudaFree / allocating library routine.
+ * Limits: tokens <= TB200_GEMV_MAX_TOKENS (decode-size calls) and tokens * k * 1.25 bytes (quantized weight types; tokens * k * 2
+ * for F16 weights with 3..8 tokens), rounded up to 256, <= TB200_NOALLOC_SCRATCH_BYTES - e.g. 8 tokens at k = 32768; anything
+ * larger returns TB200_ERR_INVALID with tb200_last_error() naming the limit, before any launch.
+ * The array is shared by every call on the GPU and keeps the last call's contents (nothing in it needs to start at zero: the
+ * quantizer rewrites all the decode kernel reads): calls that OVERLAP on the GPU - two streams, two graph branches - race on
+ * it; calls in one stream are ordered. The first call per device resolves the array's address (cudaGetSymbolAddress, no
+ * allocation); make that first call outside a stream capture. */
+#define TB200_NOALLOC_SCRATCH_BYTES (320 * 1024)
+TB200_API int tb200_mul_mat_noalloc(const tb200_weights *w, const float *x, long ldx, long tokens, float *out, long ldo);
+
 /* Decode only (tokens <= TB200_GEMV_MAX_TOKENS): n <= TB200_GEMV_MAX_MATS weight matrices of the same type and K that
  * consume the SAME activations (wq/wk/wv, gate/up) in one launch; out[m][t*ldo[m] + i]. */
 TB200_API int tb200_mul_mat_multi(int n, const tb200_weights *const *w, const float *x, long ldx, long tokens, float *const *out,

@@ -41,7 +41,8 @@ def lib() -> C.CDLL:
         "tb200_weights_upload": (vp, [vp, i, l, l, sz]), "tb200_weights_from_device": (vp, [vp, i, l, l, sz]),
         "tb200_weights_free": (None, [vp]), "tb200_weights_bytes": (sz, [vp]),
         "tb200_quantize_q8_0_dev": (i, [vp, l, vp, l, l]), "tb200_quantize_q8_K_dev": (i, [vp, l, vp, l, l]),
-        "tb200_mul_mat": (i, [vp, vp, l, l, vp, l]), "tb200_sgemm_dev": (i, [vp, l, vp, l, i, vp, l]),
+        "tb200_mul_mat": (i, [vp, vp, l, l, vp, l]), "tb200_mul_mat_noalloc": (i, [vp, vp, l, l, vp, l]),
+        "tb200_sgemm_dev": (i, [vp, l, vp, l, i, vp, l]),
         "tb200_mul_mat_multi": (i, [i, vp, vp, l, l, vp, vp]),
         "tb200_acts_create": (vp, [i, l, l]), "tb200_acts_quantize": (i, [vp, vp, l, l]),
         "tb200_mul_mat_acts": (i, [vp, vp, vp, l]), "tb200_mul_mat_acts_multi": (i, [i, vp, vp, vp, vp]), "tb200_acts_free": (None, [vp]),
@@ -150,6 +151,11 @@ class Weights:
 def mul_mat(w: Weights, x, tokens: int, out, ldx: int | None = None, ldo: int | None = None):
     """out[t, :] = W . vec_dot_type(x[t]) — ggml_compute_forward_mul_mat on device buffers (f32 in/out)."""
     _check(lib().tb200_mul_mat(w.handle, _ptr(x), ldx or w.k, tokens, _ptr(out), ldo or w.rows), "mul_mat")
+
+
+def mul_mat_noalloc(w: Weights, x, tokens: int, out, ldx: int | None = None, ldo: int | None = None):
+    """mul_mat for callers that may not allocate: activation scratch in a fixed device array of the library (header: limits)."""
+    _check(lib().tb200_mul_mat_noalloc(w.handle, _ptr(x), ldx or w.k, tokens, _ptr(out), ldo or w.rows), "mul_mat_noalloc")
 
 
 class Acts:
