@@ -72,7 +72,8 @@ struct PlanParams {
     int *err;                          // set when a wait gave up (the results of that launch are then undefined)
     int nb_max;
     int ahead;                         // the sync warp prefetches group g+ahead into L2 while g is computed (0 = off)
-    int flags;                         // experiments (TB200_PLAN_FLAGS): 1 = no release fence, 2 = stage activations only for the first group, 4 = no grid barrier
+    int flags;                         // experiments (TB200_PLAN_FLAGS): 2 = stage activations only for the first group, 4 = no grid barrier (both wrong results),
+                                       // 8 = plain result stores + release fence instead of confirmed exchanges (1 with 8: no fence, unsafe)
     long long *trace;                  // optional (tb200_plan_trace): [group][CTA][8] SM-clock stamps of the group's phases
 };
 
@@ -119,6 +120,11 @@ __device__ __forceinline__ unsigned atom_add_relaxed(unsigned *p, unsigned v) {
     asm volatile("atom.relaxed.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
     return old;
 }
+__device__ __forceinline__ unsigned atom_exch_relaxed(float *p, float v) {
+    unsigned old;
+    asm volatile("atom.relaxed.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(__float_as_uint(v)) : "memory");
+    return old;
+}
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 constexpr long long kSpinLimit = 4000000000LL;            // ~2 s of SM clocks: a wedged wait gives up and raises *err
@@ -137,7 +143,7 @@ __device__ __forceinline__ int plan_cvt_rne_sat8(float v) {
 // 14336-wide row costs one L2 round trip. Every CTA does this redundantly: 16..57 KB from L2 per SM and group.
 constexpr int kActR = 4;
 __device__ __forceinline__ float silu_mul(float g, float u) { return __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), u); }   // ggml_silu_f32 (ggml.c:2393) then ggml_mul
-__device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, double *s_red, float *s_scale) {
+__device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, double *s_red, float *s_scale, long long *tr = nullptr) {
     const int nb = G.nb, K = nb * QK;
     const int group = threadIdx.x >> 2, j = threadIdx.x & 3;
     const int prologue = G.prologue;
@@ -183,6 +189,10 @@ __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_l
                 else if (prologue == TB200_PLAN_SWIGLU) ta[r] = __ldcg(u4 + i), tb[r] = __ldcg(u4 + i + 1);
             }
         }
+        if (tr && b0 == 0) {                                 // trace: the first round's loads have landed
+            asm volatile("" ::"f"(va[0].x), "f"(vb[0].x));
+            tr[12] = clock64();
+        }
 #pragma unroll
         for (int r = 0; r < kActR; ++r) {
             if (b0 + r * kTW * 8 >= nb) break;               // CTA-uniform: the whole round is past the row
@@ -203,21 +213,26 @@ __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_l
             amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
             const float d = __fdiv_rn(amax, 127.f);
             const float id = (amax != 0.0f) ? __fdiv_rn(127.f, amax) : 0.0f;
-            int q[8];
-            if (amax >= 1e-30f && amax <= 3e38f) {           // |x*id| <= 127*(1+2^-23): plain round-to-nearest-even, no saturation corner
+            uint2 pk;
+            if (amax >= 1e-30f && amax <= 3e38f) {           // |x*id| <= 127*(1+2^-23): plain round-to-nearest-even, no saturation corner.
+                // v + 1.5*2^23 rounds v to an integer exactly like cvt.rni (the sum's ulp is 1) and leaves it, two's complement, in
+                // the low mantissa bits: byte 0 is the int8 quant. Full-rate FADD + PRMT instead of quarter-rate F2I + mask/shift/or.
+                uint32_t m[8];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) q[e] = __float2int_rn(__fmul_rn(y[e], id));
+                for (int e = 0; e < 8; ++e) m[e] = __float_as_uint(__fadd_rn(__fmul_rn(y[e], id), 12582912.f));
+                pk.x = __byte_perm(__byte_perm(m[0], m[1], 0x0040), __byte_perm(m[2], m[3], 0x0040), 0x5410);
+                pk.y = __byte_perm(__byte_perm(m[4], m[5], 0x0040), __byte_perm(m[6], m[7], 0x0040), 0x5410);
             } else {                                         // id overflowed or inputs are not finite: the reference's cvtps/packs saturation
+                int q[8];
 #pragma unroll
                 for (int e = 0; e < 8; ++e) q[e] = plan_cvt_rne_sat8(__fmul_rn(y[e], id));
+                pk.x = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)q[3] << 24);
+                pk.y = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)q[7] << 24);
             }
-            int sum = ((q[0] + q[1]) + (q[2] + q[3])) + ((q[4] + q[5]) + (q[6] + q[7]));
+            int sum = __dp4a((int)pk.x, 0x01010101, __dp4a((int)pk.y, 0x01010101, 0));
             sum += __shfl_xor_sync(0xffffffffu, sum, 1);
             sum += __shfl_xor_sync(0xffffffffu, sum, 2);
             if (b < nb) {
-                uint2 pk;
-                pk.x = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)q[3] << 24);
-                pk.y = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)q[7] << 24);
                 reinterpret_cast<uint2 *>(j < 2 ? s_lo + b : s_hi + b)[j & 1] = pk;
                 if (j == 0) s_ds[b] = make_int2(__float_as_int(__half2float(__float2half_rn(d))), sum);
             }
@@ -304,7 +319,8 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
                 bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
                 if (tr) tr[1] = clock64();
                 if (lane == 0) {
-                    if (!(P.flags & 1)) fence_acq_rel_gpu();   // release: those stores (ordered before by the CTA barrier) precede the arrival
+                    if ((P.flags & 9) == 8) fence_acq_rel_gpu();   // (old protocol, flag 8: plain stores + a release fence here, ~1 us per group)
+                    if (tr) tr[13] = clock64();
                     const unsigned old = atom_add_relaxed(P.cnt + (g - 1), 1u);
                     if (tr) tr[2] = clock64();
                     if (old == gridDim.x - 1 && g - 1 > P.first) P.cnt[g - 2] = 0;   // everybody has left barrier g-2: re-arm it for the next launch
@@ -438,7 +454,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
         if (tr) tr[0] = clock64(), tr[8] = tr[11] = 0;
         bar_sync(kBarRelease, kThreads);                    // group g-1 is complete on every SM
         if (tr) tr[4] = clock64();
-        if (!(P.flags & 2) || g == P.first) stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale);
+        if (!(P.flags & 2) || g == P.first) stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale, tr);
         if (tr) tr[7] = clock64();
         __syncthreads();
         if (tr) tr[5] = clock64();
@@ -455,6 +471,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
             }
         }
         bool first_item = tr != nullptr;
+        unsigned sink = 0;
         int deferred = -1;                                  // the stage emptied by the warp's last item of the group: refilled after the arrival
         for (int unit = first_unit(G); unit < nunits; unit += GW) {
             float acc[kR];
@@ -513,10 +530,18 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
 #pragma unroll
             for (int o = 16 / kR; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
             if (o_on) {
-                *o_ptr = o_res ? __fadd_rn(v, __ldcg(o_res)) : v;
+                const float val = o_res ? __fadd_rn(v, __ldcg(o_res)) : v;
+                // The result is written with an exchange, not a store: when the old value comes back the write has been performed
+                // at L2, the point of coherence of every SM. Once all of a warp's exchanges have returned it arrives; the CTA's
+                // arrival on the group counter (one relaxed atomic by the sync warp, after the CTA barrier) then needs no release
+                // fence - a fence.acq_rel.gpu there cost ~1 us per group, it waits for the SM's whole memory pipe including the
+                // ring's bulk copies in flight. The round trips overlap the following units' block dots; only the last is exposed.
+                if (!(P.flags & 8)) sink ^= atom_exch_relaxed(o_ptr, val);
+                else *o_ptr = val;
                 if (tr && tr[11] == 0) tr[11] = clock64();
             }
         }
+        if (!(P.flags & 8)) asm volatile("" ::"r"(sink) : "memory");   // every exchange of this lane has returned
         if (tr) tr[6] = clock64();
         __syncwarp();
         bar_arrive(kBarArrived, kThreads);                  // this warp's results of group g are stored; never blocks

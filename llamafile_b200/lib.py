@@ -8,8 +8,11 @@ from __future__ import annotations
 import ctypes as C
 from pathlib import Path
 
+import os
+
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libtinyblas_b200.so"
+# TB200_LIB: an experimental build of the same library (tools/build_variant.sh), for A/B measurements only
+LIB_PATH = Path(os.environ["TB200_LIB"]).resolve() if os.environ.get("TB200_LIB") else PKG / "libtinyblas_b200.so"
 
 F32, F16, Q4_0, Q8_0, Q4_K, Q6_K, Q8_K, I32 = 0, 1, 2, 8, 12, 14, 15, 26
 Q4_1, Q5_0, Q8_1, Q5_K, IQ4_XS = 3, 6, 9, 13, 23

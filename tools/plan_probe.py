@@ -69,6 +69,11 @@ def main():
     def rep(nm, a):
         a = a[has]
         print(f"  {nm:34s} mean {a.mean():8.0f}  median {np.median(a):8.0f}  p95 {np.percentile(a, 95):8.0f}")
+    rep("sync warp: release fence", t[:, :, 13] - t[:, :, 1])
+    rep("sync warp: atomic add round trip", t[:, :, 2] - t[:, :, 13])
+    rep("release -> x loads landed", t[:, :, 12] - t[:, :, 4])
+    rep("x landed -> quantized (warp 0)", t[:, :, 7] - t[:, :, 12])
+    rep("quantized -> CTA barrier passed", t[:, :, 5] - t[:, :, 7])
     rep("staged -> first item landed", t[:, :, 8] - t[:, :, 5])
     rep("first item: block dots", t[:, :, 9] - t[:, :, 8])
     rep("first item: refill + advance", t[:, :, 10] - t[:, :, 9])
