@@ -63,7 +63,7 @@ struct alignas(16) PlanGroup {
 };
 
 static_assert(sizeof(PlanGroup) % 16 == 0, "descriptors are copied to shared memory in 16-byte words");
-constexpr size_t kPlanSmemMax = 224 * 1024;               // dynamic shared memory the kernel may be given (227 KB - its static part)
+constexpr size_t kPlanSmemMax = 227 * 1024 - 512;         // dynamic shared memory the kernel may be given (227 KB per CTA minus its static part, < 400 B)
 
 struct PlanParams {
     const PlanGroup *groups;
@@ -127,6 +127,7 @@ __device__ __forceinline__ unsigned atom_exch_relaxed(float *p, float v) {
 }
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+constexpr int kTraceSlots = 24;                            // tb200_plan_trace: stamps 0..15, per-group sums of warp 0 in 16..21
 constexpr long long kSpinLimit = 4000000000LL;            // ~2 s of SM clocks: a wedged wait gives up and raises *err
 
 // _mm256_cvtps_epi32 + packs (ggml-quants.c:962-977), as in tb200_quantize.cu
@@ -314,7 +315,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
     if (warp == kPW) {
         for (int g = P.first; g < P.end; ++g) {
             const PlanGroup &G = tab[g];
-            long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * 16 : nullptr;
+            long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
             if (g > P.first && !(P.flags & 4)) {
                 bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
                 if (tr) tr[1] = clock64();
@@ -410,37 +411,56 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
             ++ig;
         }
     };
-    const char *nx_src = nullptr;
+    const char *nx_src = nullptr, *nx_unit = nullptr;       // this lane's source of the next item; of segment 0 of that item's unit
+    long nx_ustride = 0;                                    // bytes from a unit to this warp's next unit of the same matrix (GW units on)
     uint32_t nx_bytes = 0, nx_tx = 0;
     bool nx_on = false;
-    auto iprepare = [&]() {
+    auto iprepare = [&]() {                                 // everything from the iterator (after it moved into another matrix or group)
         const long r_first = (long)kR * (iunit - i_ub);
         const bool contig = i_nb == kSegBlocks && r_first + kR <= i_rows;          // warp-uniform
         const long row = min(r_first + prow, (long)i_rows - 1);                    // tail: the last row again, stored once
         const int b0 = iseg * kSegBlocks, segb = min(kSegBlocks, i_nb - b0);
         nx_tx = (uint32_t)segb * 18u * kR;
-        nx_src = i_base + (row * i_nb + b0) * bunit;
+        nx_unit = i_base + row * i_nb * bunit;
+        nx_ustride = (long)kR * GW * i_nb * bunit;
+        nx_src = nx_unit + b0 * bunit;
         nx_bytes = (uint32_t)(segb * bunit) * (contig ? kR : 1);
         nx_on = lane < 2 * kR && (!contig || prow == 0) && ig < P.end;
     };
-    auto iadvance = [&]() {
-        if (++iseg < i_nseg) return;
+    auto iadvance = [&]() {                                 // moves the iterator and prepares the item; the common steps only add to pointers
+        if (++iseg < i_nseg) {                              // next K segment of the same unit (never contiguous: rows are longer than a stage)
+            const int segb = min(kSegBlocks, i_nb - iseg * kSegBlocks);
+            nx_src += kSegBlocks * bunit;
+            nx_tx = (uint32_t)segb * 18u * kR, nx_bytes = (uint32_t)(segb * bunit);
+            return;
+        }
         iseg = 0, iunit += GW;
-        if (iunit < i_ue) return;
-        if (iunit < i_nunits) { iload_mat(); return; }
+        if (iunit < i_ue && kR * (iunit - i_ub) + kR <= i_rows) {   // a whole unit of the same matrix
+            nx_unit += nx_ustride, nx_src = nx_unit;
+            if (i_nseg > 1) nx_tx = (uint32_t)kSegBlocks * 18u * kR, nx_bytes = (uint32_t)(kSegBlocks * bunit);
+            return;
+        }
+        if (iunit < i_ue) { iprepare(); return; }           // the matrix's clamped tail unit
+        if (iunit < i_nunits) { iload_mat(); iprepare(); return; }
         ++ig;
         iseek();
+        iprepare();
     };
-    auto refill = [&](int st) {   // stage st is empty: copy the iterator's item into it and move on
+    auto refill = [&](int st, long long *trp = nullptr) {   // stage st is empty: copy the iterator's item into it and move on
         if (ig >= P.end) return;
         if (lane < 2 * kR) {
             uint64_t *bar = &s_full[warp][st];
             if (lane == 0) mbar_expect_tx(bar, nx_tx);
             __syncwarp((1u << (2 * kR)) - 1);               // the expected byte count is posted before any copy can complete
+#ifdef TB200_PLAN_TRACE_ITEMS
+            if (trp) trp[14] = clock64();
+#endif
             if (nx_on) bulk_g2s(my_ring + st * kStageBytes + dst_off, nx_src, nx_bytes, bar, policy);
+#ifdef TB200_PLAN_TRACE_ITEMS
+            if (trp) trp[15] = clock64();
+#endif
         }
         iadvance();
-        iprepare();
     };
     iseek();
     iprepare();
@@ -450,7 +470,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
     unsigned seq = 0;                                       // items consumed by this warp
     for (int g = P.first; g < P.end; ++g) {
         const PlanGroup &G = tab[g];
-        long long *tr = P.trace && threadIdx.x == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * 16 : nullptr;
+        long long *tr = P.trace && threadIdx.x == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
         if (tr) tr[0] = clock64(), tr[8] = tr[11] = 0;
         bar_sync(kBarRelease, kThreads);                    // group g-1 is complete on every SM
         if (tr) tr[4] = clock64();
@@ -471,7 +491,13 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
             }
         }
         bool first_item = tr != nullptr;
-        unsigned sink = 0;
+#ifdef TB200_PLAN_TRACE_ITEMS   // per-item sums cost 2.6 % of the step even when tracing is off: a probe build only (tools/build_variant.sh)
+        long long *const tra = tr;
+#else
+        long long *const tra = nullptr;
+#endif
+        long long a_wait = 0, a_dots = 0, a_refill = 0, a_tail = 0, a_items = 0, t_prev = tra ? clock64() : 0;   // trace: where warp 0's time goes
+        unsigned sink = 0, pend = 0;
         int deferred = -1;                                  // the stage emptied by the warp's last item of the group: refilled after the arrival
         for (int unit = first_unit(G); unit < nunits; unit += GW) {
             float acc[kR];
@@ -500,6 +526,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
                     }
                 }
                 if (first_item) tr[8] = clock64();
+                if (tra) { const long long t = clock64(); a_wait += t - t_prev, t_prev = t; }
                 const uint8_t *stage = my_ring + st * kStageBytes;
                 const int kb0 = seg * kSegBlocks, segb = min(kSegBlocks, nb - kb0);
                 if (cached) {
@@ -511,9 +538,11 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
                 }
                 __syncwarp();                               // every lane has read the stage: it can be refilled
                 if (first_item) tr[9] = clock64();
+                if (tra) { const long long t = clock64(); a_dots += t - t_prev, t_prev = t, ++a_items; }
                 if (last_unit && seg == nseg - 1) deferred = st;   // not urgent (it is for a later group): after the arrival
-                else refill(st);
+                else refill(st, first_item ? tr : nullptr);
                 if (first_item) tr[10] = clock64(), first_item = false;
+                if (tra) { const long long t = clock64(); a_refill += t - t_prev, t_prev = t; }
             }
             // kR sums with one transposing butterfly: each step halves the values a lane carries (the lane keeps the rows of its own
             // half and hands the others over), then plain steps finish the sum inside a 32/kR-lane segment: 5 or 6 shuffles, not 5*kR
@@ -536,12 +565,16 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
                 // arrival on the group counter (one relaxed atomic by the sync warp, after the CTA barrier) then needs no release
                 // fence - a fence.acq_rel.gpu there cost ~1 us per group, it waits for the SM's whole memory pipe including the
                 // ring's bulk copies in flight. The round trips overlap the following units' block dots; only the last is exposed.
-                if (!(P.flags & 8)) sink ^= atom_exch_relaxed(o_ptr, val);
+                // (A warp executes in order: consuming the old value right away would park the warp for the whole round trip,
+                // ~600 cycles per unit. It is folded in one unit later, when it has long since returned.)
+                if (!(P.flags & 8)) sink ^= pend, pend = atom_exch_relaxed(o_ptr, val);
                 else *o_ptr = val;
                 if (tr && tr[11] == 0) tr[11] = clock64();
             }
+            if (tra) { const long long t = clock64(); a_tail += t - t_prev, t_prev = t; }
         }
-        if (!(P.flags & 8)) asm volatile("" ::"r"(sink) : "memory");   // every exchange of this lane has returned
+        if (tra) tr[16] = a_wait, tr[17] = a_dots, tr[18] = a_refill, tr[19] = a_tail, tr[20] = a_items;
+        if (!(P.flags & 8)) { sink ^= pend; asm volatile("" ::"r"(sink) : "memory"); }   // every exchange of this lane has returned
         if (tr) tr[6] = clock64();
         __syncwarp();
         bar_arrive(kBarArrived, kThreads);                  // this warp's results of group g are stored; never blocks
@@ -661,11 +694,11 @@ int tb200_plan_reset(tb200_plan *p) {
 }
 
 // Debug aid: per group and CTA, the SM clock at {loop top, CTA done with g-1, arrived, barrier complete, CTA released,
-// activations staged, warp 0 done}. Call once before tb200_plan_run to switch it on; copies out after a run. out: [n_groups][grid][16].
+// activations staged, warp 0 done}. Call once before tb200_plan_run to switch it on; copies out after a run. out: [n_groups][grid][24].
 long tb200_plan_trace(tb200_plan *p, long long *out, long capacity) {
     tb200_ctx *c = tb200_get_ctx();
     if (!p || !c) return -1;
-    const long n = (long)p->n_groups * c->sm_count * 16;
+    const long n = (long)p->n_groups * c->sm_count * kTraceSlots;
     if (!p->d_trace) {
         if (cudaMalloc((void **)&p->d_trace, (size_t)n * 8) != cudaSuccess || cudaMemset(p->d_trace, 0, (size_t)n * 8) != cudaSuccess) { cudaGetLastError(); p->d_trace = nullptr; return -1; }
         return 0;

@@ -298,7 +298,7 @@ class Plan:
             return None
         out = np.zeros(n, np.int64)
         lib().tb200_plan_trace(self.handle, out.ctypes.data, n)
-        return out.reshape(self.n, -1, 16)
+        return out.reshape(self.n, -1, 24)
     def reset(self): _check(lib().tb200_plan_reset(self.handle), "plan_reset")
 
     def free(self):

@@ -77,7 +77,13 @@ def main():
     rep("staged -> first item landed", t[:, :, 8] - t[:, :, 5])
     rep("first item: block dots", t[:, :, 9] - t[:, :, 8])
     rep("first item: refill + advance", t[:, :, 10] - t[:, :, 9])
+    rep("   expect_tx + syncwarp", t[:, :, 14] - t[:, :, 9])
+    rep("   bulk copy issue", t[:, :, 15] - t[:, :, 14])
+    rep("   advance + prepare", t[:, :, 10] - t[:, :, 15])
     rep("first pair: rest + reduce + store", t[:, :, 11] - t[:, :, 10])
+    items = np.maximum(t[:, :, 20], 1)
+    print(f"  warp 0, all its items of a group: {t[:, :, 20][has].mean():.2f} items; per item: wait {(t[:, :, 16] / items)[has].mean():.0f}  dots {(t[:, :, 17] / items)[has].mean():.0f}"
+          f"  refill {(t[:, :, 18] / items)[has].mean():.0f}  reduce+store (per unit) {(t[:, :, 19] / items)[has].mean():.0f} cycles")
     per_group = t[1:, :, 0] - t[:-1, :, 0]
     print(f"  loop-top to loop-top        mean {per_group.mean():8.0f} cycles")
     # arrival skew: spread of the arrival stamps (tr[2]) across CTAs of one group is not comparable across SMs (per-SM clocks),
