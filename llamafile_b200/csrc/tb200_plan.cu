@@ -144,6 +144,95 @@ __device__ __forceinline__ int plan_cvt_rne_sat8(float v) {
 // 14336-wide row costs one L2 round trip. Every CTA does this redundantly: 16..57 KB from L2 per SM and group.
 constexpr int kActR = 4;
 __device__ __forceinline__ float silu_mul(float g, float u) { return __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), u); }   // ggml_silu_f32 (ggml.c:2393) then ggml_mul
+template <int R>
+__device__ __forceinline__ void stage_rounds(const PlanGroup &G, int b0, int group, int j, float scale, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, long long *tr) {
+    const int nb = G.nb, prologue = G.prologue;
+    const float4 *x4 = reinterpret_cast<const float4 *>(G.x), *u4 = reinterpret_cast<const float4 *>(G.x2), *w4 = reinterpret_cast<const float4 *>(G.nw);
+    float y[R][8], t[R][8];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int b = b0 + r * kTW * 8 + group;
+        float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va, ta = va, tb = va;
+        if (b < nb) {
+            const int i = b * 8 + 2 * j;
+            va = __ldcg(x4 + i), vb = __ldcg(x4 + i + 1);
+            if (prologue == TB200_PLAN_RMSNORM) ta = __ldg(w4 + i), tb = __ldg(w4 + i + 1);
+            else if (prologue == TB200_PLAN_SWIGLU) ta = __ldcg(u4 + i), tb = __ldcg(u4 + i + 1);
+        }
+        y[r][0] = va.x, y[r][1] = va.y, y[r][2] = va.z, y[r][3] = va.w, y[r][4] = vb.x, y[r][5] = vb.y, y[r][6] = vb.z, y[r][7] = vb.w;
+        t[r][0] = ta.x, t[r][1] = ta.y, t[r][2] = ta.z, t[r][3] = ta.w, t[r][4] = tb.x, t[r][5] = tb.y, t[r][6] = tb.z, t[r][7] = tb.w;
+    }
+    if (tr && b0 == 0) {                                     // trace: the first round's loads have landed
+        asm volatile("" ::"f"(y[0][0]), "f"(y[0][4]));
+        tr[12] = clock64();
+    }
+    if (prologue == TB200_PLAN_RMSNORM) {                    // y = x*scale (ggml_vec_scale_f32), then ggml_mul by the norm weight
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) y[r][e] = __fmul_rn(__fmul_rn(y[r][e], scale), t[r][e]);
+    } else if (prologue == TB200_PLAN_SWIGLU) {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) y[r][e] = silu_mul(y[r][e], t[r][e]);
+    }
+    float amax[R], d[R], id[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        float a = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) a = fmaxf(a, fabsf(y[r][e]));
+        amax[r] = a;
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) amax[r] = fmaxf(amax[r], __shfl_xor_sync(0xffffffffu, amax[r], 1));
+#pragma unroll
+    for (int r = 0; r < R; ++r) amax[r] = fmaxf(amax[r], __shfl_xor_sync(0xffffffffu, amax[r], 2));
+    // d = amax/127 is only needed by the lane that stores it (j == 0), id = 127/amax by all four: lane 0 of the group divides
+    // amax by 127, the others 127 by amax - ONE IEEE division per thread instead of two - and lane 1's quotient is broadcast
+#pragma unroll
+    for (int r = 0; r < R; ++r) d[r] = __fdiv_rn(j == 0 ? amax[r] : 127.f, j == 0 ? 127.f : amax[r]);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const float q = __shfl_sync(0xffffffffu, d[r], ((int)threadIdx.x & 28) | 1);
+        id[r] = (amax[r] != 0.0f) ? q : 0.0f;
+    }
+    uint2 pk[R];
+    int sum[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        if (amax[r] >= 1e-30f && amax[r] <= 3e38f) {         // |x*id| <= 127*(1+2^-23): plain round-to-nearest-even, no saturation corner.
+            // v + 1.5*2^23 rounds v to an integer exactly like cvt.rni (the sum's ulp is 1) and leaves it, two's complement, in
+            // the low mantissa bits: byte 0 is the int8 quant. Full-rate FADD + PRMT instead of quarter-rate F2I + mask/shift/or.
+            uint32_t m[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) m[e] = __float_as_uint(__fadd_rn(__fmul_rn(y[r][e], id[r]), 12582912.f));
+            pk[r].x = __byte_perm(__byte_perm(m[0], m[1], 0x0040), __byte_perm(m[2], m[3], 0x0040), 0x5410);
+            pk[r].y = __byte_perm(__byte_perm(m[4], m[5], 0x0040), __byte_perm(m[6], m[7], 0x0040), 0x5410);
+        } else {                                             // id overflowed or inputs are not finite: the reference's cvtps/packs saturation
+            int q[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) q[e] = plan_cvt_rne_sat8(__fmul_rn(y[r][e], id[r]));
+            pk[r].x = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)q[3] << 24);
+            pk[r].y = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)q[7] << 24);
+        }
+        sum[r] = __dp4a((int)pk[r].x, 0x01010101, __dp4a((int)pk[r].y, 0x01010101, 0));
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) sum[r] += __shfl_xor_sync(0xffffffffu, sum[r], 1);
+#pragma unroll
+    for (int r = 0; r < R; ++r) sum[r] += __shfl_xor_sync(0xffffffffu, sum[r], 2);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int b = b0 + r * kTW * 8 + group;
+        if (b < nb) {
+            reinterpret_cast<uint2 *>(j < 2 ? s_lo + b : s_hi + b)[j & 1] = pk[r];
+            if (j == 0) s_ds[b] = make_int2(__float_as_int(__half2float(__float2half_rn(d[r]))), sum[r]);
+        }
+    }
+}
+
 __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, double *s_red, float *s_scale, long long *tr = nullptr) {
     const int nb = G.nb, K = nb * QK;
     const int group = threadIdx.x >> 2, j = threadIdx.x & 3;
@@ -177,67 +266,17 @@ __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_l
         __syncthreads();
         scale = *s_scale;
     }
-    for (int b0 = 0; b0 < nb; b0 += kTW * 8 * kActR) {
-        float4 va[kActR], vb[kActR], ta[kActR], tb[kActR];
-#pragma unroll
-        for (int r = 0; r < kActR; ++r) {
-            const int b = b0 + r * kTW * 8 + group;
-            va[r] = vb[r] = ta[r] = tb[r] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (b < nb) {
-                const int i = b * 8 + 2 * j;
-                va[r] = __ldcg(x4 + i), vb[r] = __ldcg(x4 + i + 1);
-                if (prologue == TB200_PLAN_RMSNORM) ta[r] = __ldg(w4 + i), tb[r] = __ldg(w4 + i + 1);
-                else if (prologue == TB200_PLAN_SWIGLU) ta[r] = __ldcg(u4 + i), tb[r] = __ldcg(u4 + i + 1);
-            }
-        }
-        if (tr && b0 == 0) {                                 // trace: the first round's loads have landed
-            asm volatile("" ::"f"(va[0].x), "f"(vb[0].x));
-            tr[12] = clock64();
-        }
-#pragma unroll
-        for (int r = 0; r < kActR; ++r) {
-            if (b0 + r * kTW * 8 >= nb) break;               // CTA-uniform: the whole round is past the row
-            const int b = b0 + r * kTW * 8 + group;
-            float y[8] = {va[r].x, va[r].y, va[r].z, va[r].w, vb[r].x, vb[r].y, vb[r].z, vb[r].w};
-            const float t[8] = {ta[r].x, ta[r].y, ta[r].z, ta[r].w, tb[r].x, tb[r].y, tb[r].z, tb[r].w};
-            if (prologue == TB200_PLAN_RMSNORM) {            // y = x*scale (ggml_vec_scale_f32), then ggml_mul by the norm weight
-#pragma unroll
-                for (int e = 0; e < 8; ++e) y[e] = __fmul_rn(__fmul_rn(y[e], scale), t[e]);
-            } else if (prologue == TB200_PLAN_SWIGLU) {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) y[e] = silu_mul(y[e], t[e]);
-            }
-            float amax = 0.f;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(y[e]));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-            const float d = __fdiv_rn(amax, 127.f);
-            const float id = (amax != 0.0f) ? __fdiv_rn(127.f, amax) : 0.0f;
-            uint2 pk;
-            if (amax >= 1e-30f && amax <= 3e38f) {           // |x*id| <= 127*(1+2^-23): plain round-to-nearest-even, no saturation corner.
-                // v + 1.5*2^23 rounds v to an integer exactly like cvt.rni (the sum's ulp is 1) and leaves it, two's complement, in
-                // the low mantissa bits: byte 0 is the int8 quant. Full-rate FADD + PRMT instead of quarter-rate F2I + mask/shift/or.
-                uint32_t m[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) m[e] = __float_as_uint(__fadd_rn(__fmul_rn(y[e], id), 12582912.f));
-                pk.x = __byte_perm(__byte_perm(m[0], m[1], 0x0040), __byte_perm(m[2], m[3], 0x0040), 0x5410);
-                pk.y = __byte_perm(__byte_perm(m[4], m[5], 0x0040), __byte_perm(m[6], m[7], 0x0040), 0x5410);
-            } else {                                         // id overflowed or inputs are not finite: the reference's cvtps/packs saturation
-                int q[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) q[e] = plan_cvt_rne_sat8(__fmul_rn(y[e], id));
-                pk.x = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)q[3] << 24);
-                pk.y = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)q[7] << 24);
-            }
-            int sum = __dp4a((int)pk.x, 0x01010101, __dp4a((int)pk.y, 0x01010101, 0));
-            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-            if (b < nb) {
-                reinterpret_cast<uint2 *>(j < 2 ? s_lo + b : s_hi + b)[j & 1] = pk;
-                if (j == 0) s_ds[b] = make_int2(__float_as_int(__half2float(__float2half_rn(d))), sum);
-            }
-        }
+    // K in chunks of up to kActR rounds (a round = kTW*8 blocks, one per 4-lane group). The rounds of a chunk are independent
+    // dependency chains (loads -> amax -> two divisions -> round -> pack -> sum), so they are written phase by phase across
+    // the rounds: the scheduler interleaves them and a 14336-wide row costs little more than one round's latency instead of
+    // 3.5 of them (3400 -> see DESIGN 5.2c). Chunks are sized to the rounds that remain, so K = 4096 still runs one round.
+    for (int b0 = 0; b0 < nb;) {
+        const int rounds = (nb - b0 + kTW * 8 - 1) / (kTW * 8);
+        if (rounds >= 4) stage_rounds<4>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
+        else if (rounds == 3) stage_rounds<3>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
+        else if (rounds == 2) stage_rounds<2>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
+        else stage_rounds<1>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
+        b0 += (rounds >= 4 ? 4 : rounds) * kTW * 8;
     }
 }
 
@@ -330,8 +369,14 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
                     // there by construction: every value another SM wrote is read with ld.global.cg / from L2 (no stale L1 copy can
                     // be hit), and those loads are issued only after the CTA barrier below, which this thread joins after the poll
                     // has seen the last arrival - whose release fence made the arriving CTA's stores visible at L2 first.
-                    while (ld_relaxed(P.cnt + (g - 1)) < gridDim.x)
+                    // (Four polls in flight a quarter of a round trip apart were measured SLOWER, 0.999 vs 0.972 ms per step: 148 pollers
+                    // on the line the arrivals' atomics target already compete with them.)
+                    while (ld_relaxed(P.cnt + (g - 1)) < gridDim.x) {
+#ifdef TB200_PLAN_POLL_SLEEP
+                        __nanosleep(TB200_PLAN_POLL_SLEEP);
+#endif
                         if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
+                    }
                     if (tr) tr[3] = clock64();
                 }
                 __syncwarp();
