@@ -371,7 +371,7 @@ def run_b200_arm(args):
     wtype, layers, layer, tail = WORKLOADS[args.workload]
     if args.layers:
         layers = args.layers
-    use_plan = args.decode == "plan" and wtype == Q4_0   # N > 1: the replicated groups run as plan launches, the sharded ones through the fused all-gather
+    use_plan = args.decode == "plan" and wtype in (Q4_0, Q4_K)   # N > 1: the replicated groups run as plan launches, the sharded ones through the fused all-gather
 
     specs = [(f"l{li}.{n}", N, K, f"l{li}.{g}") for li in range(layers) for (n, N, K, g) in layer] + [(n, N, K, g) for (n, N, K, g) in tail]
     # north_star: "weight matrices of layers large enough to split are sharded by output rows". A launch group (the matrices
@@ -582,12 +582,12 @@ def run_b200_arm(args):
     peak, peak_src = peaks["hbm"]
     if plan is not None and len(segments) == 1:
         # the plan kernel IS the step: one launch, quantization inside
-        ms_kernel, n_launch, kname = ms_per_step, 1, "plan_q4_0_kernel"
+        ms_kernel, n_launch, kname = ms_per_step, 1, "plan_kernel<%s>" % {Q4_0: "Q4_0", Q4_K: "Q4_K"}[wtype]
     elif plan is not None:
         # N > 1: the plan launches of the replicated groups + the sharded groups' GEMVs, no exchange and no quantizer launches
         run_gemv, _ = capture(lambda: step(with_gather=False, with_quant=False))
         ms_kernel = timed(run_gemv, args.steps, args.warmup) / args.steps
-        n_launch, kname = len(segments), "plan_q4_0_kernel + gemv_q4_0_kernel (sharded groups)"
+        n_launch, kname = len(segments), "plan_kernel + gemv kernel (sharded groups)"
     else:
         run_gemv, _ = capture(lambda: step(with_gather=False, with_quant=False))
         ms_kernel = timed(run_gemv, args.steps, args.warmup) / args.steps

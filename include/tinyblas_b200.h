@@ -242,8 +242,8 @@ TB200_API void tb200_acts_free(tb200_acts *a);
  *   TB200_PLAN_QUANT    x                                         -> quantize_row_q8_0 (bit-exact)
  *   TB200_PLAN_RMSNORM  x * 1/sqrt(mean(x^2) + eps) * norm_weight -> quantize   (ggml_rms_norm + ggml_mul)
  *   TB200_PLAN_SWIGLU   silu(x) * x2                              -> quantize   (ggml_silu + ggml_mul; x = gate, x2 = up)
- * and every matrix may add a residual on the way out (out = W.x + residual, ggml_add). All matrices Q4_0, K % 256 == 0,
- * one token. Buffers must stay valid while the plan exists; weights, inputs and outputs may be shared between groups. */
+ * and every matrix may add a residual on the way out (out = W.x + residual, ggml_add). All matrices of a plan Q4_0 (Q8_0
+ * activations) or all Q4_K (the prologue then ends in quantize_row_q8_K, bit-exact likewise), K % 256 == 0, one token. Buffers must stay valid while the plan exists; weights, inputs and outputs may be shared between groups. */
 enum { TB200_PLAN_QUANT = 0, TB200_PLAN_RMSNORM = 1, TB200_PLAN_SWIGLU = 2 };
 typedef struct {
     int n;                                             /* matrices that share the input, <= TB200_GEMV_MAX_MATS */

@@ -263,11 +263,13 @@ bool backend_supports_buft(tb200_backend_t b, tb200_buft_t t) {
 }
 bool backend_offload_op(tb200_backend_t, const struct ggml_tensor *) { return false; }
 
-// a node the decode plan can take: one token, Q4_0 weights, K a multiple of 256, dense vectors
-bool plan_node(const T *op) {
-    if (op->op_ != TB200_GGML_OP_MUL_MAT || !mul_mat_supported(op)) return false;
+// a node the decode plan can take: one token, Q4_0 or Q4_K weights, K a multiple of 256, dense vectors. Returns the weight type
+// (a plan holds one type: a run of plannable nodes ends where the type changes), 0 when the node cannot be planned.
+int plan_node(const T *op) {
+    if (op->op_ != TB200_GGML_OP_MUL_MAT || !mul_mat_supported(op)) return 0;
     const T *a = tv((const struct ggml_tensor *)op->src_[0]), *b = tv((const struct ggml_tensor *)op->src_[1]);
-    return a->type == TB200_TYPE_Q4_0 && b->ne[1] == 1 && a->ne[0] % 256 == 0 && ((uintptr_t)b->data & 15) == 0;
+    const bool ok = (a->type == TB200_TYPE_Q4_0 || a->type == TB200_TYPE_Q4_K) && b->ne[1] == 1 && a->ne[0] % 256 == 0 && ((uintptr_t)b->data & 15) == 0;
+    return ok ? a->type : 0;
 }
 
 int run_mul_mat(BackendCtx *, const T *op) {
@@ -320,7 +322,8 @@ int backend_graph_compute(tb200_backend_t bk, struct ggml_cgraph *cg_) {
         if (is_view_op(op->op_)) { ++i; continue; }
         // a run of consecutive one-token Q4_0 matmuls: ONE persistent kernel for the whole run (nodes sharing their input form a group)
         int j = i;
-        while (j < cg->n_nodes && (is_view_op(tv(cg->nodes[j])->op_) || plan_node(tv(cg->nodes[j])))) ++j;
+        const int run_type = plan_node(op);
+        while (run_type && j < cg->n_nodes && (is_view_op(tv(cg->nodes[j])->op_) || plan_node(tv(cg->nodes[j])) == run_type)) ++j;
         int n_plan = 0;
         for (int q = i; q < j; ++q) n_plan += !is_view_op(tv(cg->nodes[q])->op_);
         if (n_plan >= 2) {

@@ -144,6 +144,37 @@ __device__ __forceinline__ int plan_cvt_rne_sat8(float v) {
 // 14336-wide row costs one L2 round trip. Every CTA does this redundantly: 16..57 KB from L2 per SM and group.
 constexpr int kActR = 4;
 __device__ __forceinline__ float silu_mul(float g, float u) { return __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), u); }   // ggml_silu_f32 (ggml.c:2393) then ggml_mul
+// RMSNorm scale of the group's input row, by the whole CTA: ggml_compute_forward_rms_norm_f32 (llama.cpp/ggml/src/ggml.c:11850-11896):
+// sum of x*x in double, mean as float, 1/sqrtf(mean + eps)
+__device__ __forceinline__ float plan_rms_scale(const PlanGroup &G, double *s_red, float *s_scale) {
+    const int K = G.nb * QK;
+    const float4 *x4 = reinterpret_cast<const float4 *>(G.x);
+    double s = 0.0;
+    for (int i0 = 0; i0 < K / 4; i0 += kTW * 32 * 2 * kActR) {
+        float4 v[2 * kActR];
+#pragma unroll
+        for (int u = 0; u < 2 * kActR; ++u) {
+            const int i = i0 + u * kTW * 32 + (int)threadIdx.x;
+            v[u] = i < K / 4 ? __ldcg(x4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 2 * kActR; ++u)
+            s += (double)__fmul_rn(v[u].x, v[u].x) + (double)__fmul_rn(v[u].y, v[u].y) + (double)__fmul_rn(v[u].z, v[u].z) + (double)__fmul_rn(v[u].w, v[u].w);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < kTW; ++w) t += s_red[w];
+        const float mean = (float)(t / (double)K);
+        *s_scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, G.eps)));
+    }
+    __syncthreads();
+    return *s_scale;
+}
+
 template <int R>
 __device__ __forceinline__ void stage_rounds(const PlanGroup &G, int b0, int group, int j, float scale, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, long long *tr) {
     const int nb = G.nb, prologue = G.prologue;
@@ -234,38 +265,10 @@ __device__ __forceinline__ void stage_rounds(const PlanGroup &G, int b0, int gro
 }
 
 __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, double *s_red, float *s_scale, long long *tr = nullptr) {
-    const int nb = G.nb, K = nb * QK;
+    const int nb = G.nb;
     const int group = threadIdx.x >> 2, j = threadIdx.x & 3;
     const int prologue = G.prologue;
-    const float4 *x4 = reinterpret_cast<const float4 *>(G.x), *u4 = reinterpret_cast<const float4 *>(G.x2), *w4 = reinterpret_cast<const float4 *>(G.nw);
-    float scale = 1.f;
-    if (prologue == TB200_PLAN_RMSNORM) {
-        // ggml_compute_forward_rms_norm_f32 (llama.cpp/ggml/src/ggml.c:11850-11896): sum of x*x in double, mean as float, 1/sqrtf(mean + eps)
-        double s = 0.0;
-        for (int i0 = 0; i0 < K / 4; i0 += kTW * 32 * 2 * kActR) {
-            float4 v[2 * kActR];
-#pragma unroll
-            for (int u = 0; u < 2 * kActR; ++u) {
-                const int i = i0 + u * kTW * 32 + (int)threadIdx.x;
-                v[u] = i < K / 4 ? __ldcg(x4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int u = 0; u < 2 * kActR; ++u)
-                s += (double)__fmul_rn(v[u].x, v[u].x) + (double)__fmul_rn(v[u].y, v[u].y) + (double)__fmul_rn(v[u].z, v[u].z) + (double)__fmul_rn(v[u].w, v[u].w);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = s;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            double t = 0.0;
-            for (int w = 0; w < kTW; ++w) t += s_red[w];
-            const float mean = (float)(t / (double)K);
-            *s_scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, G.eps)));
-        }
-        __syncthreads();
-        scale = *s_scale;
-    }
+    const float scale = prologue == TB200_PLAN_RMSNORM ? plan_rms_scale(G, s_red, s_scale) : 1.f;
     // K in chunks of up to kActR rounds (a round = kTW*8 blocks, one per 4-lane group). The rounds of a chunk are independent
     // dependency chains (loads -> amax -> two divisions -> round -> pack -> sum), so they are written phase by phase across
     // the rounds: the scheduler interleaves them and a 14336-wide row costs little more than one round's latency instead of
@@ -316,12 +319,133 @@ __device__ __forceinline__ void stage_dots(const uint8_t *stage, const ActCache 
     }
 }
 
-__global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_constant__ PlanParams P) {
+// ---- Q4_K plans: Q8_K activations -----------------------------------------------------------------------------------
+// nearest_int (ggml-quants.c:1632-1637) with the x86 result for a non-finite argument, as in tb200_quantize.cu
+__device__ __forceinline__ int plan_nearest_int(float fval) {
+    if (!(fabsf(fval) <= 3.4028234664e38f)) return 0;
+    return (__float_as_int(__fadd_rn(fval, 12582912.f)) & 0x007fffff) - 0x00400000;
+}
+// quantize_row_q8_K (ggml-quants.c:3593-3645; bit-exact, same arithmetic as quantize_q8_K_kernel in tb200_quantize.cu) of the
+// group's input after its prologue, one warp per 256-element super-block (lane l: elements 4l..4l+3 and 128+4l..128+4l+3),
+// into the Q4_K decode kernel's staging form: s_q[sb][chunk c][5 x 16 B] = the 64 quants of chunk c (+ 16 B of padding: an
+// 80-byte lane stride is bank-conflict free, 64 is not), s_ds[sb*8 + k] = {d, sum of the 32 quants of sub-block k}.
+__device__ __forceinline__ void stage_activations_q8k(const PlanGroup &G, uint4 *s_q, int2 *s_ds, double *s_red, float *s_scale) {
+    const int nsb = G.nb / 8, prologue = G.prologue;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float scale = prologue == TB200_PLAN_RMSNORM ? plan_rms_scale(G, s_red, s_scale) : 1.f;
+    for (int sb = warp; sb < nsb; sb += kTW) {               // warp-uniform
+        const float4 *x4 = reinterpret_cast<const float4 *>(G.x) + sb * 64;
+        const float4 a = __ldcg(x4 + lane), c = __ldcg(x4 + 32 + lane);
+        float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+        if (prologue == TB200_PLAN_RMSNORM) {
+            const float4 *w4 = reinterpret_cast<const float4 *>(G.nw) + sb * 64;
+            const float4 ta = __ldg(w4 + lane), tc = __ldg(w4 + 32 + lane);
+            const float t[8] = {ta.x, ta.y, ta.z, ta.w, tc.x, tc.y, tc.z, tc.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __fmul_rn(__fmul_rn(v[e], scale), t[e]);
+        } else if (prologue == TB200_PLAN_SWIGLU) {
+            const float4 *u4 = reinterpret_cast<const float4 *>(G.x2) + sb * 64;
+            const float4 ta = __ldcg(u4 + lane), tc = __ldcg(u4 + 32 + lane);
+            const float t[8] = {ta.x, ta.y, ta.z, ta.w, tc.x, tc.y, tc.z, tc.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = silu_mul(v[e], t[e]);
+        }
+        // first arg-max |x| (strict >), carrying the signed value
+        float amax = 0.f, vmax = 0.f;
+        int imax = QK_K;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float ax = fabsf(v[i]);
+            const int idx = (i < 4) ? 4 * lane + i : 128 + 4 * lane + (i - 4);
+            if (ax > amax) amax = ax, vmax = v[i], imax = idx;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float oa = __shfl_xor_sync(0xffffffffu, amax, o), ov = __shfl_xor_sync(0xffffffffu, vmax, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, imax, o);
+            if (oa > amax || (oa == amax && oi < imax)) amax = oa, vmax = ov, imax = oi;
+        }
+        int qv[8];
+        float d = 0.f;
+        if (amax != 0.f) {
+            const float iscale = __fdiv_rn(-127.f, vmax);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) qv[i] = min(127, plan_nearest_int(__fmul_rn(iscale, v[i])));
+            d = __fdiv_rn(1.f, iscale);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) qv[i] = 0;
+        }
+        const uint32_t lo = (uint32_t)(qv[0] & 0xff) | ((uint32_t)(qv[1] & 0xff) << 8) | ((uint32_t)(qv[2] & 0xff) << 16) | ((uint32_t)(qv[3] & 0xff) << 24);
+        const uint32_t hi = (uint32_t)(qv[4] & 0xff) | ((uint32_t)(qv[5] & 0xff) << 8) | ((uint32_t)(qv[6] & 0xff) << 16) | ((uint32_t)(qv[7] & 0xff) << 24);
+        int s_lo = qv[0] + qv[1] + qv[2] + qv[3], s_hi = qv[4] + qv[5] + qv[6] + qv[7];
+#pragma unroll
+        for (int o = 1; o <= 4; o <<= 1) s_lo += __shfl_xor_sync(0xffffffffu, s_lo, o), s_hi += __shfl_xor_sync(0xffffffffu, s_hi, o);   // 32-element sums
+        // word `lane` of the block's 64 (elements 4*lane..): chunk lane/16, piece (lane%16)/4, word lane%4; `hi` two chunks on
+        uint32_t *qw = reinterpret_cast<uint32_t *>(s_q + (size_t)sb * 20);
+        const int off = ((lane >> 4) * 5 + ((lane & 15) >> 2)) * 4 + (lane & 3);
+        qw[off] = lo, qw[off + 2 * 20] = hi;
+        if ((lane & 7) == 0) {
+            s_ds[sb * 8 + (lane >> 3)] = make_int2(__float_as_int(d), s_lo);
+            s_ds[sb * 8 + 4 + (lane >> 3)] = make_int2(__float_as_int(d), s_hi);
+        }
+    }
+}
+
+// Block dots of one ring stage of Q4_K rows: kR rows x up to 16 super-blocks. A lane owns 64-element chunk c = lane % 4 of
+// super-block lane / 4 (+ 8): 32 contiguous bytes of nibbles per row, the arithmetic of gemv_q4_K_kernel (tb200_gemv.cu):
+// ggml_vec_dot_q4_K_q8_K (ggml-quants.c:7341-7397) - integer sub-block sums scaled by the 6-bit scales, minus dmin * sum m_j * bsum_j.
+template <bool kFull>
+__device__ __forceinline__ void stage_dots_q4k(const uint8_t *stage, const uint4 *s_q, const int2 *s_ds, int kb0, int segb, int lane, float (&acc)[kR]) {
+    const int c = lane & 3, grp = lane >> 2, shift = 16 * (c & 1);
+    const int sb0 = kb0 >> 3, nsbseg = segb >> 3;
+#pragma unroll
+    for (int u = 0; u < kSegBlocks / 64; ++u) {
+        const int sb = grp + 8 * u;
+        if (kFull || sb < nsbseg) {
+            const uint4 *ap = s_q + ((size_t)(sb0 + sb) * 4 + c) * 5;
+            const uint4 y0 = ap[0], y1 = ap[1], y2 = ap[2], y3 = ap[3];
+            const int4 dsv = *reinterpret_cast<const int4 *>(s_ds + (sb0 + sb) * 8 + 2 * c);   // {d, sum} of sub-blocks 2c, 2c+1
+            const float dy = __int_as_float(dsv.x);
+#pragma unroll
+            for (int r = 0; r < kR; ++r) {
+                const uint4 *qrow = reinterpret_cast<const uint4 *>(stage + r * kRowQ) + sb * 8 + 2 * c;
+                const uint4 a = qrow[0], b = qrow[1];
+                const uint4 h = reinterpret_cast<const uint4 *>(stage + kR * kRowQ + r * kRowS)[sb];   // {d, dmin, scales[12]}
+                const __half2 dd = *reinterpret_cast<const __half2 *>(&h.x);
+                const float d = __low2float(dd), dmin = __high2float(dd);
+                // get_scale_min_k4 (ggml-quants.c:1891-1899) four bytes at a time; the lane takes its two pairs by a fixed shift
+                const uint32_t scw = c < 2 ? (h.y & 0x3f3f3f3fu) : ((h.w & 0x0f0f0f0fu) | ((h.y >> 2) & 0x30303030u));
+                const uint32_t mw = c < 2 ? (h.z & 0x3f3f3f3fu) : (((h.w >> 4) & 0x0f0f0f0fu) | ((h.z >> 2) & 0x30303030u));
+                const int sc_lo = (scw >> shift) & 0xff, sc_hi = (scw >> (shift + 8)) & 0xff;
+                const int m_lo = (mw >> shift) & 0xff, m_hi = (mw >> (shift + 8)) & 0xff;
+                int sl = dp4a_us(a.x & 0x0f0f0f0fu, (int)y0.x, 0);
+                sl = dp4a_us(a.y & 0x0f0f0f0fu, (int)y0.y, sl), sl = dp4a_us(a.z & 0x0f0f0f0fu, (int)y0.z, sl), sl = dp4a_us(a.w & 0x0f0f0f0fu, (int)y0.w, sl);
+                sl = dp4a_us(b.x & 0x0f0f0f0fu, (int)y1.x, sl), sl = dp4a_us(b.y & 0x0f0f0f0fu, (int)y1.y, sl);
+                sl = dp4a_us(b.z & 0x0f0f0f0fu, (int)y1.z, sl), sl = dp4a_us(b.w & 0x0f0f0f0fu, (int)y1.w, sl);
+                int sh = dp4a_us(a.x & 0xf0f0f0f0u, (int)y2.x, 0);                 // high nibbles in place = 16*q
+                sh = dp4a_us(a.y & 0xf0f0f0f0u, (int)y2.y, sh), sh = dp4a_us(a.z & 0xf0f0f0f0u, (int)y2.z, sh), sh = dp4a_us(a.w & 0xf0f0f0f0u, (int)y2.w, sh);
+                sh = dp4a_us(b.x & 0xf0f0f0f0u, (int)y3.x, sh), sh = dp4a_us(b.y & 0xf0f0f0f0u, (int)y3.y, sh);
+                sh = dp4a_us(b.z & 0xf0f0f0f0u, (int)y3.z, sh), sh = dp4a_us(b.w & 0xf0f0f0f0u, (int)y3.w, sh);
+                const int isum = sc_lo * sl + sc_hi * (sh >> 4);
+                const int msum = m_lo * dsv.y + m_hi * dsv.w;
+                acc[r] = fmaf(d * dy, (float)isum, acc[r]);
+                acc[r] = fmaf(-(dmin * dy), (float)msum, acc[r]);
+            }
+        }
+    }
+}
+
+template <int kType>
+__global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant__ PlanParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *ring = smem;                                                          // [kPW][kPS][kStageBytes]
-    uint4 *s_lo = reinterpret_cast<uint4 *>(smem + kPW * kPS * kStageBytes);       // [nb_max]
+    constexpr bool kQ4K = kType == TB200_TYPE_Q4_K;
+    // staged activations. Q4_0: s_lo / s_hi [nb_max] x 16 B + s_ds [nb_max] x 8 B (40 B per 32-block); Q4_K: s_lo = the Q8_K
+    // quants in the decode kernel's chunked form, [nb_max / 8] x 20 x 16 B, + s_ds [nb_max] x 8 B (48 B per 32-block)
+    uint4 *s_lo = reinterpret_cast<uint4 *>(smem + kPW * kPS * kStageBytes);
     uint4 *s_hi = s_lo + P.nb_max;
-    int2 *s_ds = reinterpret_cast<int2 *>(s_hi + P.nb_max);
+    int2 *s_ds = reinterpret_cast<int2 *>(s_lo + (kQ4K ? P.nb_max / 8 * 20 : 2 * P.nb_max));
     // the descriptors of this launch's groups: every warp walks them (twice: as consumer and, a few groups ahead, as its own
     // TMA producer), and a gpu-scope fence invalidates L1, so from global memory each look-up was an L2 round trip
     const PlanGroup *tab = reinterpret_cast<const PlanGroup *>(s_ds + P.nb_max) - P.first;   // tab[g], g in [first, end)
@@ -382,7 +506,10 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
                 __syncwarp();
             } else if (g > P.first) bar_sync(kBarArrived, kThreads);
             bar_sync(kBarRelease, kThreads);                // consumers may stage and compute group g
-            if (!(P.flags & 2) || g == P.first) stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale);
+            if (!(P.flags & 2) || g == P.first) {
+                if (kQ4K) stage_activations_q8k(G, s_lo, s_ds, s_red, &s_scale);
+                else stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale);
+            }
             __syncthreads();
             // Experiment, OFF by default (TB200_PLAN_AHEAD=n): while the consumers work, pull this CTA's rows of group g+n from HBM
             // into L2 with one bulk prefetch per unit and plane, so that HBM keeps streaming during the barrier chains of the small
@@ -519,14 +646,17 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
         if (tr) tr[0] = clock64(), tr[8] = tr[11] = 0;
         bar_sync(kBarRelease, kThreads);                    // group g-1 is complete on every SM
         if (tr) tr[4] = clock64();
-        if (!(P.flags & 2) || g == P.first) stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale, tr);
+        if (!(P.flags & 2) || g == P.first) {
+            if (kQ4K) stage_activations_q8k(G, s_lo, s_ds, s_red, &s_scale);
+            else stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale, tr);
+        }
         if (tr) tr[7] = clock64();
         __syncthreads();
         if (tr) tr[5] = clock64();
 
         // ---- this warp's units of the group
         const int nb = G.nb, nseg = G.nseg, nunits = G.nunits;
-        const bool cached = kActCache && nseg == 1;
+        const bool cached = kActCache && !kQ4K && nseg == 1;
         ActCache C;
         if (cached) {
 #pragma unroll
@@ -574,7 +704,10 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
                 if (tra) { const long long t = clock64(); a_wait += t - t_prev, t_prev = t; }
                 const uint8_t *stage = my_ring + st * kStageBytes;
                 const int kb0 = seg * kSegBlocks, segb = min(kSegBlocks, nb - kb0);
-                if (cached) {
+                if (kQ4K) {
+                    if (segb == kSegBlocks) stage_dots_q4k<true>(stage, s_lo, s_ds, kb0, segb, lane, acc);
+                    else stage_dots_q4k<false>(stage, s_lo, s_ds, kb0, segb, lane, acc);
+                } else if (cached) {
                     if (segb == kSegBlocks) stage_dots<true, true>(stage, C, s_lo, s_hi, s_ds, kb0, segb, lane, acc);
                     else stage_dots<true, false>(stage, C, s_lo, s_hi, s_ds, kb0, segb, lane, acc);
                 } else {
@@ -631,7 +764,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_q4_0_kernel(const __grid_con
 
 // ------------------------------------------------------------------------------------------------ host side
 struct tb200_plan {
-    int n_groups, nb_max, device;
+    int n_groups, nb_max, device, type;
     PlanGroup *d_groups;
     unsigned *d_cnt;
     int *d_err;
@@ -663,7 +796,8 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
         long units = 0;
         for (int m = 0; m < s.n && !bad; ++m) {
             const tb200_weights *w = s.w[m];
-            if (!w || w->type != TB200_TYPE_Q4_0) bad = "only Q4_0 weights (use the per-matrix API for the other types)";
+            if (!w || (w->type != TB200_TYPE_Q4_0 && w->type != TB200_TYPE_Q4_K)) bad = "only Q4_0 or Q4_K weights (use the per-matrix API for the other types)";
+            else if (w->type != groups[0].w[0]->type) bad = "all matrices of a plan have one weight type";
             else if (w->k != s.w[0]->k || w->k % 256) bad = "matrices of a group share K, a multiple of 256";
             else if (w->rows < 1 || !s.out[m]) bad = "empty matrix or missing output";
             else if (w->device != c->device) bad = "weights live on another device";
@@ -682,8 +816,8 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
     }
     tb200_plan *p = new tb200_plan();
     memset(p, 0, sizeof(*p));
-    p->n_groups = n_groups, p->nb_max = nb_max, p->device = c->device;
-    p->smem = (size_t)kPW * kPS * kStageBytes + (size_t)nb_max * 40;   // + the launch's descriptor table (tb200_plan_run)
+    p->n_groups = n_groups, p->nb_max = nb_max, p->device = c->device, p->type = groups[0].w[0]->type;
+    p->smem = (size_t)kPW * kPS * kStageBytes + (size_t)nb_max * (p->type == TB200_TYPE_Q4_K ? 48 : 40);   // + the launch's descriptor table (tb200_plan_run)
     bool ok = p->smem + 16 * sizeof(PlanGroup) <= kPlanSmemMax;
     if (!ok) tb200_set_error("plan_create: K = %d does not fit the activation staging", nb_max * QK);
     ok = ok && cudaMalloc((void **)&p->d_groups, (size_t)n_groups * sizeof(PlanGroup)) == cudaSuccess;
@@ -692,7 +826,8 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
         p->d_err = (int *)(p->d_cnt + n_groups + 1);
         ok = cudaMemcpy(p->d_groups, h, (size_t)n_groups * sizeof(PlanGroup), cudaMemcpyHostToDevice) == cudaSuccess &&
              cudaMemset(p->d_cnt, 0, (size_t)(n_groups + 1) * 4 + 16) == cudaSuccess &&
-             cudaFuncSetAttribute(plan_q4_0_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess;
+             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
+             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess;
         if (!ok) tb200_set_error("plan_create: %s", cudaGetErrorString(cudaGetLastError()));
     } else cudaGetLastError();
     free(h);
@@ -718,7 +853,9 @@ int tb200_plan_run(tb200_plan *p, int first, int count) {
         p->grid = c->sm_count;
         // one CTA per SM, all co-resident (the groups synchronise through arrival counters); plain stream order, no PDL: the
         // kernel owns the whole GPU for the step
-        plan_q4_0_kernel<<<dim3((unsigned)c->sm_count), dim3(kTW * 32), p->smem + (size_t)n * sizeof(PlanGroup), c->stream>>>(P);
+        const size_t smem = p->smem + (size_t)n * sizeof(PlanGroup);
+        if (p->type == TB200_TYPE_Q4_K) plan_kernel<TB200_TYPE_Q4_K><<<dim3((unsigned)c->sm_count), dim3(kTW * 32), smem, c->stream>>>(P);
+        else plan_kernel<TB200_TYPE_Q4_0><<<dim3((unsigned)c->sm_count), dim3(kTW * 32), smem, c->stream>>>(P);
         tb200_count_launch();
         TB_CUDA(cudaGetLastError());
     }

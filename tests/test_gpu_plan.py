@@ -28,11 +28,11 @@ def q4_bytes(N, K, seed, exact=False):
     return b.reshape(-1)
 
 
-def run_plan(tb, groups_np, repeats=1, ranges=None):
+def run_plan(tb, groups_np, repeats=1, ranges=None, wtype=H.Q4_0):
     """groups_np: list of (list of (W bytes, N), K, x) -> outputs per group/matrix after running the plan."""
     keep, groups = [], []
     for mats, K, x in groups_np:
-        ws = [tb.Weights(W, H.Q4_0, N, K) for W, N in mats]
+        ws = [tb.Weights(W, wtype, N, K) for W, N in mats]
         outs = [torch.full((N,), float("nan"), device="cuda") for _, N in mats]
         groups.append({"w": ws, "out": outs, "x": dev(x)})
         keep.append((ws, outs))
@@ -245,3 +245,97 @@ def test_fused_acts_feed_prefill_matmuls(tb, oracle, wt):
     ref = oracle.mul_mat(W, wt, np.stack([oracle.silu_mul(a, b) for a, b in zip(g, u)]))
     H.assert_close(out.cpu().numpy(), ref, "swiglu -> matmul")
     w.free(); acts.free()
+
+
+# ------------------------------------------------------------------ Q4_K plans (Q8_K activations quantized in the kernel)
+def q4k_bytes(N, K, seed, exact=False):
+    if not exact:
+        return H.synth_q4_K(N, K, seed)
+    rng = np.random.default_rng(seed)
+    nb = N * K // 256
+    b = rng.integers(0, 256, (nb, 144), dtype=np.uint8)
+    b[:, 0:2] = np.full(nb, 2.0 ** -8, np.float16).view(np.uint8).reshape(-1, 2)    # d
+    b[:, 2:4] = np.full(nb, 2.0 ** -7, np.float16).view(np.uint8).reshape(-1, 2)    # dmin
+    return b.reshape(-1)
+
+
+@pytest.mark.parametrize("K", [256, 1024, 4096, 8192, 14336, 28672])
+def test_plan_q4_K_single_group_vs_oracle(tb, oracle, K):
+    """Q4_K weights: one group, odd row counts, K from one super-block to 7 ring stages per row (the 70B down projection)."""
+    shapes = [301, 64, 1] if K <= 8192 else [130, 3]
+    mats = [(q4k_bytes(n, K, seed=n + K), n) for n in shapes]
+    x = H.make_acts(1, K, seed=K)[0]
+    res = run_plan(tb, [(mats, K, x)], wtype=H.Q4_K)
+    for (W, n), got in zip(mats, res[0]):
+        H.assert_close(got[None], oracle.mul_mat(W, H.Q4_K, x[None]), f"q4_K K={K} n={n}")
+
+
+def test_plan_q4_K_exact_integer_arithmetic(tb, oracle):
+    """Power-of-two d / dmin and activations that Q8_K-quantize to themselves (max |x| = 127 with iscale = -1 exactly... the
+    row's maximum is -127, so iscale = 1): every fp32 product is exact up to the final sums, which the oracle forms in the same
+    order per super-block; the gate is the usual one, tightened to 1e-6 scaled error."""
+    K = 2048
+    rng = np.random.default_rng(6)
+    groups, refs = [], []
+    for gi, shapes in enumerate(([777, 130], [2049], [64, 64, 66])):
+        x = rng.integers(-12, 13, K).astype(np.float32)
+        x[::256] = -127.0
+        mats = [(q4k_bytes(n, K, seed=gi * 10 + i, exact=True), n) for i, n in enumerate(shapes)]
+        groups.append((mats, K, x))
+        refs.append([oracle.mul_mat(W, H.Q4_K, x[None])[0] for W, _ in mats])
+    res = run_plan(tb, groups, repeats=3, wtype=H.Q4_K)
+    for got_g, ref_g in zip(res, refs):
+        for got, ref in zip(got_g, ref_g):
+            assert H.scaled_err(got, ref) <= 1e-6, H.scaled_err(got, ref)
+
+
+def test_plan_q4_K_equals_one_shot_path(tb):
+    """Same arithmetic as the one-shot Q4_K decode kernel fed by quantize_q8_K_kernel: equal within accumulation order, on rows
+    with the quantizer's corner cases (all-zero super-block, ties for the maximum, tiny and huge magnitudes)."""
+    K, N = 1024, 96
+    W = q4k_bytes(N, K, seed=3)
+    rng = np.random.default_rng(2)
+    x = rng.standard_normal(K).astype(np.float32)
+    x[0:256] = 0.0
+    x[256] = 3.0; x[300] = -3.0
+    x[512:768] *= 1e-20
+    x[768:1024] *= 1e18
+    w = tb.Weights(W, H.Q4_K, N, K)
+    xd = dev(x[None])
+    ref = torch.full((1, N), float("nan"), device="cuda")
+    tb.mul_mat(w, xd, 1, ref)
+    out = torch.full((N,), float("nan"), device="cuda")
+    plan = tb.Plan([{"w": [w], "out": [out], "x": xd[0]}])
+    plan.run()
+    tb.synchronize()
+    assert plan.status() == 0
+    H.assert_close(out.cpu().numpy()[None], ref.cpu().numpy(), "plan vs one-shot q4_K")
+    assert H.scaled_err(out.cpu().numpy(), ref.cpu().numpy()[0]) <= 1e-5
+    plan.free(); w.free()
+
+
+def test_plan_q4_K_chain_with_prologues(tb, oracle):
+    """A layer-shaped chain of Q4_K groups with the fused neighbours: RMSNorm -> (a, b) ; SwiGLU(a, b) -> c + residual; repeated
+    launches. Checked against the oracle's fp32 neighbours + reference quantizer + mul_mat."""
+    K, F = 1024, 2048
+    rng = np.random.default_rng(11)
+    h = (rng.standard_normal(K) * 0.7).astype(np.float32)
+    nw = rng.uniform(0.5, 1.5, K).astype(np.float32)
+    Wa, Wb, Wc = q4k_bytes(F, K, 21), q4k_bytes(F, K, 22), q4k_bytes(K, F, 23)
+    wa, wb, wc = tb.Weights(Wa, H.Q4_K, F, K), tb.Weights(Wb, H.Q4_K, F, K), tb.Weights(Wc, H.Q4_K, K, F)
+    hd, nwd = dev(h), dev(nw)
+    a = torch.zeros(F, device="cuda"); b = torch.zeros(F, device="cuda"); c = torch.zeros(K, device="cuda")
+    plan = tb.Plan([{"w": [wa, wb], "out": [a, b], "x": hd, "prologue": tb.PLAN_RMSNORM, "norm_weight": nwd, "eps": 1e-5},
+                    {"w": [wc], "out": [c], "x": a, "x2": b, "prologue": tb.PLAN_SWIGLU, "residual": [hd]}])
+    for _ in range(3):
+        plan.run()
+        tb.synchronize()
+        assert plan.status() == 0
+    xn = oracle.rms_norm_mul(h[None], nw, 1e-5)
+    ra, rb = oracle.mul_mat(Wa, H.Q4_K, xn)[0], oracle.mul_mat(Wb, H.Q4_K, xn)[0]
+    H.assert_close(a.cpu().numpy()[None], ra[None], "q4_K rmsnorm group a")
+    H.assert_close(b.cpu().numpy()[None], rb[None], "q4_K rmsnorm group b")
+    act = oracle.silu_mul(a.cpu().numpy()[None], b.cpu().numpy()[None])      # from the GPU's own a, b: isolates the second group
+    rc = oracle.mul_mat(Wc, H.Q4_K, act)[0] + h
+    H.assert_close(c.cpu().numpy()[None], rc[None], "q4_K swiglu + residual group")
+    plan.free(); wa.free(); wb.free(); wc.free()
