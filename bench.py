@@ -538,10 +538,10 @@ def run_b200_arm(args):
                 for r in range(world):
                     rlo, rhi = shard_rows(N, r, world)
                     if rhi > rlo:
-                        raw = synth_dev(torch, dev, wtype, rhi - rlo, K, seed=shard_seed(i, r, grp))
-                        wr = tb.Weights(raw, wtype, rhi - rlo, K)
-                        o = torch.empty(1, rhi - rlo, device=dev)
-                        with torch.cuda.stream(stream):
+                        with torch.cuda.stream(stream):   # the module's launches go to `stream`: generate the bytes there too (the 300 MB vocabulary shard was repacked before torch's default stream had written it)
+                            raw = synth_dev(torch, dev, wtype, rhi - rlo, K, seed=shard_seed(i, r, grp))
+                            wr = tb.Weights(raw, wtype, rhi - rlo, K)
+                            o = torch.empty(1, rhi - rlo, device=dev)
                             tb.mul_mat(wr, x, 1, o)
                         stream.synchronize()
                         parts.append(o.cpu().numpy()[0])
