@@ -264,6 +264,7 @@ TB200_API int tb200_plan_reset(tb200_plan *p);
 /* debug: first call switches per-group phase stamps on (returns 0); later calls copy [n_groups][SMs][8] SM-clock stamps out */
 TB200_API long tb200_plan_trace(tb200_plan *p, long long *out, long capacity);
 TB200_API void tb200_plan_free(tb200_plan *p);
+/* Multi-GPU decode plan, one process per GPU (declared after tb200_peers below): tb200_plan_create_peers. */
 
 /* The matmul's neighbours for any token count (the decode plan fuses the same operations into its kernel):
  * fp32 device tensors, row-major with leading dimensions in floats. Same IEEE operations in the same order as ggml's CPU ops:
@@ -300,6 +301,15 @@ TB200_API int tb200_mul_mat_acts_multi_gather(tb200_peers *g, int n, const tb200
                                               const size_t *out_offset, const long *ldo, const long *row_lo);
 TB200_API int tb200_peers_barrier(tb200_peers *g);   /* enqueue: all ranks' slices of everything launched so far are visible after it */
 TB200_API int tb200_peers_timed_out(tb200_peers *g);
+/* The decode plan on row-sharded weights (north_star "sharded by output rows ... all-gather"): every rank creates
+ * the SAME sequence of groups over its own row slices and runs it the same number of times. A matrix whose `out` pointer lies
+ * inside this rank's symmetric buffer [out_bases[rank], + symmetric_bytes) is a row slice: the kernel stores every result at the
+ * same offset of every rank's buffer (NVLink peer stores from the epilogue) and the barrier after such a group is grid-wide AND
+ * cross-GPU - a sequence number published in the peers' flag buffers, words 8.. - so the next group, on every rank, reads the
+ * full vector from its local buffer; the launch itself ends only after the last group's slices of all ranks have arrived. Groups
+ * whose outputs are private (replicated weights) synchronise locally only. No collective call, no extra launch: the all-gather of
+ * ggml-cuda.cu:1600-1676 is stores + two words. The SLOT REUSE RULE above applies to the offsets. */
+TB200_API tb200_plan *tb200_plan_create_peers(tb200_peers *g, size_t symmetric_bytes, int n_groups, const tb200_plan_group *groups);
 TB200_API int tb200_memset(void *dst, int value, size_t bytes);
 
 /* GGUF tensor loader: tensors of a GGUF file (v2/v3) straight from an mmap to resident weights.

@@ -54,6 +54,7 @@ struct alignas(16) PlanGroup {
     int nb, nseg;                      // 32-blocks per row; ring stages per unit
     int nunits, rot;                   // units (kR consecutive rows of one matrix) of all matrices; rotation of the warp -> unit assignment
     int nmat;
+    int shared_mask, sh_before;        // multi-GPU plans: bit m = matrix m's rows are stored into every rank's symmetric buffer; shared groups before this one
     int unit_begin[kPlanMats + 1];
     int rows[kPlanMats];
     const uint4 *qs[kPlanMats];
@@ -71,11 +72,17 @@ struct PlanParams {
     unsigned *cnt;                     // [n_groups] arrival counters, all zero between launches
     int *err;                          // set when a wait gave up (the results of that launch are then undefined)
     int nb_max;
-    int ahead;                         // the sync warp prefetches group g+ahead into L2 while g is computed (0 = off)
     int flags;                         // experiments (TB200_PLAN_FLAGS): 2 = stage activations only for the first group, 4 = no grid barrier (both wrong results),
                                        // 8 = plain result stores + release fence instead of confirmed exchanges (1 with 8: no fence, unsafe)
     long long *trace;                  // optional (tb200_plan_trace): [group][CTA][8] SM-clock stamps of the group's phases
+    // multi-GPU plans (tb200_plan_create_peers): one process per GPU runs the same group sequence on its row shards
+    int world, rank, n_shared;         // n_shared: shared groups of the whole plan
+    const char *local_base;            // this rank's symmetric buffer; a shared result at local_base + off also goes to peer_base[p] + off
+    char *peer_base[TB200_MAX_PEERS];
+    unsigned *peer_flag[TB200_MAX_PEERS];   // rank p's flag words: [kPeerFlag0 + r] = the last shared-group sequence number rank r has completed
+    unsigned *epoch, *done;            // launches of this plan so far (device side: survives CUDA-graph replay); CTAs that left the launch
 };
+constexpr int kPeerFlag0 = 8;           // words 0..7 of a rank's flag buffer belong to tb200_peers_barrier
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
@@ -96,8 +103,11 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
-__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+__device__ __forceinline__ void st_relaxed_sys(unsigned *p, unsigned v) { asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
 }
 __device__ __forceinline__ uint64_t policy_evict_first() {
     uint64_t p;
@@ -436,6 +446,27 @@ __device__ __forceinline__ void stage_dots_q4k(const uint8_t *stage, const uint4
     }
 }
 
+// ---- multi-GPU plans: the cross-GPU half of a group barrier (sync warp, lane 0) --------------------------------------
+// After a SHARED group every rank has stored its row slice into every rank's symmetric buffer (plain remote stores over NVLink
+// from the consumer warps). A CTA makes those stores visible system-wide before it arrives on the local counter
+// (fence.acq_rel.sys; the CTA barrier before it orders the consumer warps' stores first); the rank's LAST arriving CTA then
+// publishes the group's sequence number in every peer's flag buffer, and everybody waits until all peers' numbers have arrived
+// in the local flag buffer. Sequence numbers only grow (epoch * shared groups of the plan + index), so one word per peer does.
+__device__ __forceinline__ void peers_signal(const PlanParams &P, unsigned seq) {
+    __threadfence_system();                                  // acquire the other CTAs' arrivals (and with them their fenced remote stores), release ours
+#pragma unroll
+    for (int p = 0; p < TB200_MAX_PEERS; ++p)
+        if (p < P.world && p != P.rank) st_relaxed_sys(P.peer_flag[p] + kPeerFlag0 + P.rank, seq);
+}
+__device__ __forceinline__ void peers_wait(const PlanParams &P, unsigned seq) {
+    const long long t0 = clock64();
+#pragma unroll
+    for (int p = 0; p < TB200_MAX_PEERS; ++p)
+        if (p < P.world && p != P.rank)
+            while ((int)(ld_relaxed_sys(P.peer_flag[P.rank] + kPeerFlag0 + p) - seq) < 0)
+                if (clock64() - t0 > kSpinLimit) { *P.err = 3; break; }
+}
+
 template <int kType>
 __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant__ PlanParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -476,6 +507,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
     // atomic round trip: consumers only ARRIVE (bar.arrive, non-blocking) and use the wait for the work that is not urgent
     // (refilling the ring stage they just emptied with a row of the group after next).
     if (warp == kPW) {
+        const unsigned ep = P.world > 1 ? ld_relaxed(P.epoch) : 0u, ep_base = ep * (unsigned)P.n_shared;
         for (int g = P.first; g < P.end; ++g) {
             const PlanGroup &G = tab[g];
             long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
@@ -483,11 +515,17 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
                 if (tr) tr[1] = clock64();
                 if (lane == 0) {
+                    const bool shared = P.world > 1 && tab[g - 1].shared_mask != 0;
+                    const unsigned seq = ep_base + (unsigned)tab[g - 1].sh_before + 1u;
                     if ((P.flags & 9) == 8) fence_acq_rel_gpu();   // (old protocol, flag 8: plain stores + a release fence here, ~1 us per group)
+                    if (shared) __threadfence_system();            // this CTA's remote stores before its arrival
                     if (tr) tr[13] = clock64();
                     const unsigned old = atom_add_relaxed(P.cnt + (g - 1), 1u);
                     if (tr) tr[2] = clock64();
-                    if (old == gridDim.x - 1 && g - 1 > P.first) P.cnt[g - 2] = 0;   // everybody has left barrier g-2: re-arm it for the next launch
+                    if (old == gridDim.x - 1) {
+                        if (g - 1 > P.first) P.cnt[g - 2] = 0;     // everybody has left barrier g-2: re-arm it for the next launch
+                        if (shared) peers_signal(P, seq);
+                    }
                     const long long t0 = clock64();
                     // Acquire side: a relaxed (L2) poll, no fence and no L1 invalidation per iteration. What an acquire would add is
                     // there by construction: every value another SM wrote is read with ld.global.cg / from L2 (no stale L1 copy can
@@ -501,6 +539,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
 #endif
                         if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
                     }
+                    if (shared) peers_wait(P, seq);
                     if (tr) tr[3] = clock64();
                 }
                 __syncwarp();
@@ -511,35 +550,34 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 else stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale);
             }
             __syncthreads();
-            // Experiment, OFF by default (TB200_PLAN_AHEAD=n): while the consumers work, pull this CTA's rows of group g+n from HBM
-            // into L2 with one bulk prefetch per unit and plane, so that HBM keeps streaming during the barrier chains of the small
-            // groups. Measured on the 8B step: 1.27 ms with n = 1..3 against 1.07 ms without - the prefetched lines do not survive
-            // until the ring asks for them (the demand stream is evict-first, the prefetches are not) and the bytes cross HBM twice.
-            const int gp = g + P.ahead;
-            if (P.ahead > 0 && gp < P.end) {
-                const PlanGroup &Gp = tab[gp];
-                const int per_warp = (Gp.nunits + GW - 1) / GW;
-                for (int i = lane; i < kPW * per_warp; i += 32) {
-                    const int w = i % kPW, j = i / kPW;
-                    int u = (int)blockIdx.x * kPW + w - Gp.rot;
-                    if (u < 0) u += GW;
-                    u += j * GW;
-                    if (u < Gp.nunits) {
-                        int m = 0;
-#pragma unroll
-                        for (int mm = 1; mm < kPlanMats; ++mm)
-                            if (u >= Gp.unit_begin[mm]) m = mm;
-                        const long r0 = (long)kR * (u - Gp.unit_begin[m]);
-                        const int nr = min(kR, Gp.rows[m] - (int)r0);
-                        bulk_prefetch_l2(Gp.qs[m] + r0 * Gp.nb, (uint32_t)(nr * Gp.nb * 16));
-                        bulk_prefetch_l2(Gp.sc[m] + r0 * Gp.nb, (uint32_t)(nr * Gp.nb * 2));
-                    }
-                }
-            }
         }
         // the last group: count this CTA in, and the last CTA leaves every counter at zero for the next launch
         bar_sync(kBarArrived, kThreads);
-        if (lane == 0 && P.end - P.first > 1) {
+        if (lane == 0 && P.world > 1) {
+            // multi-GPU plan: the launch may only end when the last group's slices of every rank have arrived here (whoever runs
+            // next in the stream reads them), so the tail is a full barrier; the CTA that leaves last re-arms the counters and
+            // advances the plan's epoch
+            const int last = P.end - 1;
+            const bool shared = tab[last].shared_mask != 0;
+            const unsigned seq = ep_base + (unsigned)tab[last].sh_before + 1u;
+            if (shared) __threadfence_system();
+            const unsigned old = atom_add_relaxed(P.cnt + last, 1u);
+            if (old == gridDim.x - 1) {
+                if (last - 1 >= P.first) P.cnt[last - 1] = 0;
+                if (shared) peers_signal(P, seq);
+            }
+            if (shared) {
+                const long long t0 = clock64();
+                while (ld_relaxed(P.cnt + last) < gridDim.x)
+                    if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
+                peers_wait(P, seq);
+            }
+            if (atom_add_relaxed(P.done, 1u) == gridDim.x - 1) {   // every CTA is past its polls of cnt[last]
+                P.cnt[last] = 0;
+                *P.done = 0;
+                *P.epoch = ep + 1u;
+            }
+        } else if (lane == 0 && P.end - P.first > 1) {
             const int last = P.end - 1;
             fence_acq_rel_gpu();
             const unsigned old = atom_add_relaxed(P.cnt + last, 1u);
@@ -747,6 +785,12 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 // ~600 cycles per unit. It is folded in one unit later, when it has long since returned.)
                 if (!(P.flags & 8)) sink ^= pend, pend = atom_exch_relaxed(o_ptr, val);
                 else *o_ptr = val;
+                if (P.world > 1 && ((G.shared_mask >> m) & 1)) {   // row-sharded matrix: the same row of every rank's symmetric buffer (plain stores over NVLink; the sync warp fences)
+                    const long off = reinterpret_cast<const char *>(o_ptr) - P.local_base;
+#pragma unroll
+                    for (int p = 0; p < TB200_MAX_PEERS; ++p)
+                        if (p < P.world && p != P.rank) *reinterpret_cast<float *>(P.peer_base[p] + off) = val;
+                }
                 if (tr && tr[11] == 0) tr[11] = clock64();
             }
             if (tra) { const long long t = clock64(); a_tail += t - t_prev, t_prev = t; }
@@ -765,6 +809,11 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
 // ------------------------------------------------------------------------------------------------ host side
 struct tb200_plan {
     int n_groups, nb_max, device, type;
+    int world, rank, n_shared;
+    const char *local_base;
+    char *peer_base[TB200_MAX_PEERS];
+    unsigned *peer_flag[TB200_MAX_PEERS];
+    unsigned *d_epoch;                 // {epoch, done}
     PlanGroup *d_groups;
     unsigned *d_cnt;
     int *d_err;
@@ -775,7 +824,7 @@ struct tb200_plan {
 
 extern "C" {
 
-tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
+static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int n_groups, const tb200_plan_group *groups) {
     tb200_ctx *c = tb200_get_ctx();
     if (!c) return nullptr;
     if (n_groups < 1 || !groups) { tb200_set_error("plan_create: bad arguments"); return nullptr; }
@@ -783,7 +832,8 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
     if (!h) return nullptr;
     const long GW = (long)c->sm_count * kPW;
     long rot = 0;
-    int nb_max = 0;
+    int nb_max = 0, n_shared = 0;
+    const char *sym_lo = pg ? (const char *)pg->out_base[pg->rank] : nullptr, *sym_hi = sym_lo + sym_bytes;
     for (int g = 0; g < n_groups; ++g) {
         const tb200_plan_group &s = groups[g];
         PlanGroup &G = h[g];
@@ -805,11 +855,19 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
             G.unit_begin[m] = (int)units;
             units += (w->rows + kR - 1) / kR;
             G.rows[m] = (int)w->rows, G.qs[m] = (const uint4 *)w->qs, G.sc[m] = (const __half *)w->sc, G.out[m] = s.out[m], G.res[m] = s.residual[m];
+            // multi-GPU plan: an output inside this rank's symmetric buffer is a row slice that every rank must receive
+            const char *o = (const char *)s.out[m];
+            if (pg && pg->world > 1 && o >= sym_lo && o < sym_hi) {
+                if (o + w->rows * 4 > sym_hi) bad = "output slice runs past the symmetric buffer";
+                G.shared_mask |= 1 << m;
+            }
         }
         if (bad) { tb200_set_error("plan_create: group %d: %s", g, bad); free(h); return nullptr; }
         for (int m = s.n; m <= kPlanMats; ++m) G.unit_begin[m] = (int)units;
         G.x = s.x, G.x2 = s.x2, G.nw = s.norm_weight, G.eps = s.eps, G.prologue = s.prologue;
         G.nmat = s.n, G.nb = (int)(s.w[0]->k / QK), G.nseg = (G.nb + kSegBlocks - 1) / kSegBlocks;
+        G.sh_before = n_shared;
+        n_shared += G.shared_mask != 0;
         G.nunits = (int)units, G.rot = (int)(rot % GW);
         rot += units;                                       // the units left over by one group go to the warps after them in the next
         nb_max = G.nb > nb_max ? G.nb : nb_max;
@@ -818,12 +876,15 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
     memset(p, 0, sizeof(*p));
     p->n_groups = n_groups, p->nb_max = nb_max, p->device = c->device, p->type = groups[0].w[0]->type;
     p->smem = (size_t)kPW * kPS * kStageBytes + (size_t)nb_max * (p->type == TB200_TYPE_Q4_K ? 48 : 40);   // + the launch's descriptor table (tb200_plan_run)
+    p->world = pg ? pg->world : 1, p->rank = pg ? pg->rank : 0, p->n_shared = n_shared, p->local_base = sym_lo;
+    for (int q = 0; pg && q < pg->world; ++q) p->peer_base[q] = (char *)pg->out_base[q], p->peer_flag[q] = pg->flags[q];
     bool ok = p->smem + 16 * sizeof(PlanGroup) <= kPlanSmemMax;
     if (!ok) tb200_set_error("plan_create: K = %d does not fit the activation staging", nb_max * QK);
     ok = ok && cudaMalloc((void **)&p->d_groups, (size_t)n_groups * sizeof(PlanGroup)) == cudaSuccess;
     ok = ok && cudaMalloc((void **)&p->d_cnt, (size_t)(n_groups + 1) * 4 + 16) == cudaSuccess;
     if (ok) {
-        p->d_err = (int *)(p->d_cnt + n_groups + 1);
+        p->d_err = (int *)(p->d_cnt + n_groups + 1);   // then {done, epoch}
+        p->d_epoch = p->d_cnt + n_groups + 3;
         ok = cudaMemcpy(p->d_groups, h, (size_t)n_groups * sizeof(PlanGroup), cudaMemcpyHostToDevice) == cudaSuccess &&
              cudaMemset(p->d_cnt, 0, (size_t)(n_groups + 1) * 4 + 16) == cudaSuccess &&
              cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
@@ -833,6 +894,13 @@ tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) {
     free(h);
     if (!ok) { tb200_plan_free(p); return nullptr; }
     return p;
+}
+
+tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups) { return plan_create_impl(nullptr, 0, n_groups, groups); }
+
+tb200_plan *tb200_plan_create_peers(tb200_peers *g, size_t symmetric_bytes, int n_groups, const tb200_plan_group *groups) {
+    if (!g || !symmetric_bytes) { tb200_set_error("plan_create_peers: bad arguments"); return nullptr; }
+    return plan_create_impl(g, symmetric_bytes, n_groups, groups);
 }
 
 int tb200_plan_run(tb200_plan *p, int first, int count) {
@@ -846,10 +914,11 @@ int tb200_plan_run(tb200_plan *p, int first, int count) {
         PlanParams P;
         P.groups = p->d_groups, P.first = g0, P.end = g0 + n, P.cnt = p->d_cnt, P.err = p->d_err, P.nb_max = p->nb_max;
         P.trace = p->d_trace;
+        P.world = p->world, P.rank = p->rank, P.n_shared = p->n_shared, P.local_base = p->local_base;
+        for (int q = 0; q < TB200_MAX_PEERS; ++q) P.peer_base[q] = p->peer_base[q], P.peer_flag[q] = p->peer_flag[q];
+        P.done = p->d_cnt + p->n_groups + 2, P.epoch = p->d_epoch;
         static const int flags = [] { const char *v = getenv("TB200_PLAN_FLAGS"); return v && *v ? atoi(v) : 0; }();
         P.flags = flags;
-        static const int ahead = [] { const char *v = getenv("TB200_PLAN_AHEAD"); return v && *v ? atoi(v) : 0; }();
-        P.ahead = ahead;
         p->grid = c->sm_count;
         // one CTA per SM, all co-resident (the groups synchronise through arrival counters); plain stream order, no PDL: the
         // kernel owns the whole GPU for the step
@@ -871,7 +940,7 @@ int tb200_plan_status(tb200_plan *p) {
 
 int tb200_plan_reset(tb200_plan *p) {
     if (!p) return TB200_ERR_INVALID;
-    TB_CUDA(cudaMemset(p->d_cnt, 0, (size_t)(p->n_groups + 1) * 4 + 16));
+    TB_CUDA(cudaMemset(p->d_cnt, 0, (size_t)(p->n_groups + 1) * 4 + 8));   // counters, the error word and `done`; the epoch of a multi-GPU plan keeps counting (the peers' flags do)
     return TB200_OK;
 }
 

@@ -65,7 +65,7 @@ def lib() -> C.CDLL:
         "tb200_rms_norm_mul_dev": (i, [vp, l, vp, C.c_float, l, l, vp, l]), "tb200_silu_mul_dev": (i, [vp, vp, l, l, l, vp, l]),
         "tb200_moe_combine_dev": (i, [vp, vp, l, i, l, vp, l]), "tb200_acts_quantize_rmsnorm": (i, [vp, vp, l, l, vp, C.c_float, l]),
         "tb200_acts_quantize_swiglu": (i, [vp, vp, vp, l, l, l]),
-        "tb200_plan_create": (vp, [i, vp]), "tb200_plan_run": (i, [vp, i, i]), "tb200_plan_status": (i, [vp]), "tb200_plan_reset": (i, [vp]), "tb200_plan_trace": (l, [vp, vp, l]),
+        "tb200_plan_create": (vp, [i, vp]), "tb200_plan_create_peers": (vp, [vp, sz, i, vp]), "tb200_plan_run": (i, [vp, i, i]), "tb200_plan_status": (i, [vp]), "tb200_plan_reset": (i, [vp]), "tb200_plan_trace": (l, [vp, vp, l]),
         "tb200_plan_free": (None, [vp]),
         "tb200_backend_link": (C.c_bool, [vp]), "tb200_backend_init": (vp, [i]), "tb200_backend_is_tb200": (C.c_bool, [vp]),
         "tb200_backend_buffer_type": (vp, [i]), "tb200_backend_host_buffer_type": (vp, []), "tb200_backend_split_buffer_type": (vp, [vp]),
@@ -266,9 +266,10 @@ class PlanGroupC(C.Structure):
 
 class Plan:
     """Decode plan (tb200_plan): a sequence of one-token matmul groups run as ONE persistent kernel. `groups` is a list of dicts:
-    {"w": [Weights...], "out": [buffers...], "x": buffer, optional "prologue", "x2", "norm_weight", "eps", "residual": [buffers or None]}."""
+    {"w": [Weights...], "out": [buffers...], "x": buffer, optional "prologue", "x2", "norm_weight", "eps", "residual": [buffers or None]}.
+    peers: a PeerGroup (one process per GPU) - outputs that point into its symmetric buffer are row slices every rank receives."""
 
-    def __init__(self, groups):
+    def __init__(self, groups, peers=None):
         _require_device()
         arr = (PlanGroupC * len(groups))()
         self._keep = groups
@@ -281,7 +282,8 @@ class Plan:
             g.x, g.x2, g.norm_weight = _ptr(d["x"]), _ptr(d.get("x2")) or None, _ptr(d.get("norm_weight")) or None
             g.eps = d.get("eps", 0.0)
         self.n = len(groups)
-        self.handle = lib().tb200_plan_create(self.n, arr)
+        self.handle = (lib().tb200_plan_create_peers(peers.handle, peers.out_bytes, self.n, arr) if peers is not None
+                       else lib().tb200_plan_create(self.n, arr))
         if not self.handle:
             raise TB200Error("plan: " + lib().tb200_last_error().decode(errors="replace"))
 
