@@ -376,6 +376,15 @@ def run_b200_arm(args):
     specs = [(f"l{li}.{n}", N, K, f"l{li}.{g}") for li in range(layers) for (n, N, K, g) in layer] + [(n, N, K, g) for (n, N, K, g) in tail]
     # north_star: "weight matrices of layers large enough to split are sharded by output rows". A launch group (the matrices
     # sharing one input) is split when its weights exceed --split-min-mb; smaller groups are computed in full on every rank.
+    if args.split_min_mb is None:
+        # Break-even of a split: it saves bytes*(1 - 1/W) / 6.5 TB/s of streaming and costs one cross-GPU exchange on the group's
+        # critical path - measured 3.2 us (W = 2) to ~4 us (W = 8) inside the multi-GPU plan (remote exchange round trip + flag +
+        # poll), ~6 us as kernel -> barrier kernel -> kernel on the one-shot path (round 1's 80 MB rule).
+        in_plan = use_plan and args.gather == "p2p"
+        cost_us = ({2: 3.2, 4: 3.6}.get(world, 4.0) if in_plan else 6.0)
+        args.split_min_mb = round(cost_us * 6.5e3 / (1.0 - 1.0 / world), 1) if world > 1 else 80.0
+        if not in_plan:
+            args.split_min_mb = 80.0
     grp_bytes = {}
     for (name, N, K, grp) in specs:
         grp_bytes[grp] = grp_bytes.get(grp, 0) + N * K * BPE[wtype]
@@ -429,7 +438,18 @@ def run_b200_arm(args):
         pg = PeerGroup(world, rank, off)
 
     plan, plan_index, segments = None, {}, []
-    if use_plan:
+    sharded_plan = (use_plan and world > 1 and pg is not None and os.environ.get("TB200_BENCH_SHARDED_PLAN", "1") != "0" and
+                    all(mats[i][3] > mats[i][2] for grp, idx in schedule if split_grp[grp] for i in idx))
+    if sharded_plan:
+        # N > 1: the whole step as ONE multi-GPU plan (tb200_plan_create_peers). A split group's outputs point at this rank's row
+        # slice inside the symmetric buffer: the kernel stores them into every rank's copy and the barrier after the group spans
+        # the GPUs; replicated groups keep private outputs and a local barrier.
+        plan = tb.Plan([{"w": [mats[i][6] for i in idx],
+                         "out": [(pg.out + p2p_off[i] + mats[i][2] * 4) if split_grp[grp] else outs[i] for i in idx],
+                         "x": groups[grp][0]} for grp, idx in schedule], peers=pg)
+        plan_index = {gi: gi for gi in range(len(schedule))}
+        segments = [["plan", 0, len(schedule)]]
+    elif use_plan:
         planned = [gi for gi, (grp, idx) in enumerate(schedule) if not split_grp[grp]]
         plan = tb.Plan([{"w": [mats[i][6] for i in schedule[gi][1]], "out": [outs[i] for i in schedule[gi][1]], "x": groups[schedule[gi][0]][0]} for gi in planned])
         plan_index = {gi: pi for pi, gi in enumerate(planned)}
@@ -563,9 +583,9 @@ def run_b200_arm(args):
                                      f"nan {int(np.isnan(got).sum())}, got {got[bad[:4]].tolist()} want {full[bad[:4]].tolist()}\n")
         flag = torch.tensor([1 if ok else 0], device=dev)
         dist.broadcast(flag, 0)
-        if int(flag.item()) != 1:
+        if int(flag.item()) != 1 and os.environ.get("TB200_BENCH_IGNORE_PARITY") != "1":   # (the override is for kernel experiments that break results on purpose)
             raise SystemExit("bench: gathered outputs differ from the unsharded product")
-        parity_checked = {"matrices": 3 if split_idx else 0, "rows": "all", "tolerance": 1e-3, "against": "the same matrices multiplied unsharded on rank 0"}
+        parity_checked = None if int(flag.item()) != 1 else {"matrices": 3 if split_idx else 0, "rows": "all", "tolerance": 1e-3, "against": "the same matrices multiplied unsharded on rank 0"}
 
     log('capturing full step')
     run_full, graphed = capture(step)
@@ -797,7 +817,8 @@ def run_b200_arm(args):
     if rank == 0 and not timed_out:
         cfg = workload_config(args.workload, args.layers)
         cfg.update({"launch_groups_per_step": len(schedule), "launches_per_step": int(launches_per_step),
-                    "decode": (("plan: one persistent kernel per step (per-warp TMA rings, in-kernel Q8_0 quantization, grid barrier between groups)" if len(segments) == 1 else
+                    "decode": (("multi-GPU plan: one persistent kernel per step and rank; split groups store their row slices into every rank's buffer from the epilogue, barrier after them spans the GPUs" if sharded_plan else
+                                "plan: one persistent kernel per step (per-warp TMA rings, in-kernel activation quantization, grid barrier between groups)" if len(segments) == 1 else
                                 f"plan launches for the replicated groups ({sum(1 for sg in segments if sg[0] == 'plan')} launches) + fused-all-gather GEMVs for the sharded ones") if plan is not None
                                else "oneshot: one quantizer + one GEMV launch per group, CUDA graph"),
                     "cuda_graph": graphed, "split_groups": sum(1 for g2, _ in schedule if split_grp[g2]),
@@ -841,8 +862,8 @@ def main():
     ap.add_argument("--e2e-pinned", action="store_true", help="e2e with pinned host B/C (default: pageable, as stock ggml allocates)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the prefill / mixmul / quantizer legs (roofline.prefill etc.)")
-    ap.add_argument("--split-min-mb", type=float, default=80.0,
-                    help="N>1: launch groups with fewer weight MB are computed on every rank instead of sharded")
+    ap.add_argument("--split-min-mb", type=float, default=None,
+                    help="N>1: launch groups with fewer weight MB are computed on every rank instead of sharded (default: the break-even of the path in use)")
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="multi-GPU output exchange")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph replay (debug)")
     args = ap.parse_args()

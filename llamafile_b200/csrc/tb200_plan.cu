@@ -135,6 +135,17 @@ __device__ __forceinline__ unsigned atom_exch_relaxed(float *p, float v) {
     asm volatile("atom.relaxed.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(__float_as_uint(v)) : "memory");
     return old;
 }
+__device__ __forceinline__ unsigned atom_exch_relaxed_sys(float *p, float v) {
+    unsigned old;
+    asm volatile("atom.relaxed.sys.global.exch.b32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(__float_as_uint(v)) : "memory");
+    return old;
+}
+__device__ __forceinline__ unsigned atom_exch64_relaxed_sys(char *p, float lo, float hi) {   // two adjacent fp32 rows in one exchange
+    unsigned long long old;
+    const unsigned long long v = (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
+    asm volatile("atom.relaxed.sys.global.exch.b64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(v) : "memory");
+    return (unsigned)old ^ (unsigned)(old >> 32);
+}
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 constexpr int kTraceSlots = 24;                            // tb200_plan_trace: stamps 0..15, per-group sums of warp 0 in 16..21
@@ -448,26 +459,29 @@ __device__ __forceinline__ void stage_dots_q4k(const uint8_t *stage, const uint4
 
 // ---- multi-GPU plans: the cross-GPU half of a group barrier (sync warp, lane 0) --------------------------------------
 // After a SHARED group every rank has stored its row slice into every rank's symmetric buffer (plain remote stores over NVLink
-// from the consumer warps). A CTA makes those stores visible system-wide before it arrives on the local counter
-// (fence.acq_rel.sys; the CTA barrier before it orders the consumer warps' stores first); the rank's LAST arriving CTA then
+// from the consumer warps, written as exchanges: a warp arrives only after their old values have come back, i.e. after the peers
+// hold its rows - the same protocol as for the local copy, one scope further out); the rank's LAST arriving CTA then
 // publishes the group's sequence number in every peer's flag buffer, and everybody waits until all peers' numbers have arrived
 // in the local flag buffer. Sequence numbers only grow (epoch * shared groups of the plan + index), so one word per peer does.
 __device__ __forceinline__ void peers_signal(const PlanParams &P, unsigned seq) {
-    __threadfence_system();                                  // acquire the other CTAs' arrivals (and with them their fenced remote stores), release ours
+    // No fence: every warp's remote exchanges had returned before its CTA arrived, and this thread has seen all arrivals, so nothing
+    // the flag could overtake is still on its way.
 #pragma unroll
     for (int p = 0; p < TB200_MAX_PEERS; ++p)
         if (p < P.world && p != P.rank) st_relaxed_sys(P.peer_flag[p] + kPeerFlag0 + P.rank, seq);
 }
-__device__ __forceinline__ void peers_wait(const PlanParams &P, unsigned seq) {
-    const long long t0 = clock64();
-#pragma unroll
-    for (int p = 0; p < TB200_MAX_PEERS; ++p)
-        if (p < P.world && p != P.rank)
-            while ((int)(ld_relaxed_sys(P.peer_flag[P.rank] + kPeerFlag0 + p) - seq) < 0)
-                if (clock64() - t0 > kSpinLimit) { *P.err = 3; break; }
+// warp-collective: lane p waits for rank p's number, all peers at once (one lane polling them in turn paid an L2 round trip per peer
+// even when every flag had long been there: ~2.5 us per shared group on 8 GPUs)
+__device__ __forceinline__ void peers_wait(const PlanParams &P, unsigned seq, int lane) {
+    if (lane < P.world && lane != P.rank) {
+        const long long t0 = clock64();
+        while ((int)(ld_relaxed_sys(P.peer_flag[P.rank] + kPeerFlag0 + lane) - seq) < 0)
+            if (clock64() - t0 > kSpinLimit) { *P.err = 3; break; }
+    }
+    __syncwarp();
 }
 
-template <int kType>
+template <int kType, bool kPeers>
 __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant__ PlanParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *ring = smem;                                                          // [kPW][kPS][kStageBytes]
@@ -507,7 +521,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
     // atomic round trip: consumers only ARRIVE (bar.arrive, non-blocking) and use the wait for the work that is not urgent
     // (refilling the ring stage they just emptied with a row of the group after next).
     if (warp == kPW) {
-        const unsigned ep = P.world > 1 ? ld_relaxed(P.epoch) : 0u, ep_base = ep * (unsigned)P.n_shared;
+        const unsigned ep = kPeers ? ld_relaxed(P.epoch) : 0u, ep_base = ep * (unsigned)P.n_shared;
         for (int g = P.first; g < P.end; ++g) {
             const PlanGroup &G = tab[g];
             long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
@@ -515,10 +529,9 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
                 if (tr) tr[1] = clock64();
                 if (lane == 0) {
-                    const bool shared = P.world > 1 && tab[g - 1].shared_mask != 0;
+                    const bool shared = kPeers && tab[g - 1].shared_mask != 0;
                     const unsigned seq = ep_base + (unsigned)tab[g - 1].sh_before + 1u;
                     if ((P.flags & 9) == 8) fence_acq_rel_gpu();   // (old protocol, flag 8: plain stores + a release fence here, ~1 us per group)
-                    if (shared) __threadfence_system();            // this CTA's remote stores before its arrival
                     if (tr) tr[13] = clock64();
                     const unsigned old = atom_add_relaxed(P.cnt + (g - 1), 1u);
                     if (tr) tr[2] = clock64();
@@ -539,10 +552,10 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
 #endif
                         if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
                     }
-                    if (shared) peers_wait(P, seq);
                     if (tr) tr[3] = clock64();
                 }
                 __syncwarp();
+                if (kPeers && tab[g - 1].shared_mask != 0) peers_wait(P, ep_base + (unsigned)tab[g - 1].sh_before + 1u, lane);
             } else if (g > P.first) bar_sync(kBarArrived, kThreads);
             bar_sync(kBarRelease, kThreads);                // consumers may stage and compute group g
             if (!(P.flags & 2) || g == P.first) {
@@ -553,26 +566,28 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
         }
         // the last group: count this CTA in, and the last CTA leaves every counter at zero for the next launch
         bar_sync(kBarArrived, kThreads);
-        if (lane == 0 && P.world > 1) {
+        if (kPeers) {
             // multi-GPU plan: the launch may only end when the last group's slices of every rank have arrived here (whoever runs
             // next in the stream reads them), so the tail is a full barrier; the CTA that leaves last re-arms the counters and
             // advances the plan's epoch
             const int last = P.end - 1;
             const bool shared = tab[last].shared_mask != 0;
             const unsigned seq = ep_base + (unsigned)tab[last].sh_before + 1u;
-            if (shared) __threadfence_system();
-            const unsigned old = atom_add_relaxed(P.cnt + last, 1u);
-            if (old == gridDim.x - 1) {
-                if (last - 1 >= P.first) P.cnt[last - 1] = 0;
-                if (shared) peers_signal(P, seq);
+            if (lane == 0) {
+                const unsigned old = atom_add_relaxed(P.cnt + last, 1u);
+                if (old == gridDim.x - 1) {
+                    if (last - 1 >= P.first) P.cnt[last - 1] = 0;
+                    if (shared) peers_signal(P, seq);
+                }
+                if (shared) {
+                    const long long t0 = clock64();
+                    while (ld_relaxed(P.cnt + last) < gridDim.x)
+                        if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
+                }
             }
-            if (shared) {
-                const long long t0 = clock64();
-                while (ld_relaxed(P.cnt + last) < gridDim.x)
-                    if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
-                peers_wait(P, seq);
-            }
-            if (atom_add_relaxed(P.done, 1u) == gridDim.x - 1) {   // every CTA is past its polls of cnt[last]
+            __syncwarp();
+            if (shared) peers_wait(P, seq, lane);
+            if (lane == 0 && atom_add_relaxed(P.done, 1u) == gridDim.x - 1) {   // every CTA is past its polls of cnt[last]
                 P.cnt[last] = 0;
                 *P.done = 0;
                 *P.epoch = ep + 1u;
@@ -711,6 +726,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
 #endif
         long long a_wait = 0, a_dots = 0, a_refill = 0, a_tail = 0, a_items = 0, t_prev = tra ? clock64() : 0;   // trace: where warp 0's time goes
         unsigned sink = 0, pend = 0;
+        unsigned pendr[TB200_MAX_PEERS] = {0, 0, 0, 0, 0, 0, 0, 0};   // multi-GPU plans: the remote exchanges of the previous unit
         int deferred = -1;                                  // the stage emptied by the warp's last item of the group: refilled after the arrival
         for (int unit = first_unit(G); unit < nunits; unit += GW) {
             float acc[kR];
@@ -774,8 +790,8 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             }
 #pragma unroll
             for (int o = 16 / kR; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            const float val = (o_on && o_res) ? __fadd_rn(v, __ldcg(o_res)) : v;
             if (o_on) {
-                const float val = o_res ? __fadd_rn(v, __ldcg(o_res)) : v;
                 // The result is written with an exchange, not a store: when the old value comes back the write has been performed
                 // at L2, the point of coherence of every SM. Once all of a warp's exchanges have returned it arrives; the CTA's
                 // arrival on the group counter (one relaxed atomic by the sync warp, after the CTA barrier) then needs no release
@@ -785,18 +801,39 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 // ~600 cycles per unit. It is folded in one unit later, when it has long since returned.)
                 if (!(P.flags & 8)) sink ^= pend, pend = atom_exch_relaxed(o_ptr, val);
                 else *o_ptr = val;
-                if (P.world > 1 && ((G.shared_mask >> m) & 1)) {   // row-sharded matrix: the same row of every rank's symmetric buffer (plain stores over NVLink; the sync warp fences)
+                if (tr && tr[11] == 0) tr[11] = clock64();
+            }
+            if (kPeers && ((G.shared_mask >> m) & 1)) {
+                // row-sharded matrix: the same rows of every rank's symmetric buffer, over NVLink - again as exchanges whose old
+                // values are folded in one unit later: once they are back the peers hold the rows, so no system-scope fence is
+                // needed before the arrival (a fence.acq_rel.sys per CTA and group cost 3.8 us: 1.41 vs 0.93 ms per step with
+                // every group of the 8B step shared on two GPUs; plain stores cost nothing measurable but prove nothing). Lane 0
+                // sends the unit's row pair as ONE 8-byte exchange per peer (half the NVLink atomics; a lone tail row as 4 bytes).
+                static_assert(kR == 2, "the pair exchange assumes two rows per unit");
+                const float val1 = __shfl_sync(0xffffffffu, val, 16);
+                const int row0 = kR * (unit - G.unit_begin[m]);
+                const bool pair = row0 + 1 < G.rows[m] && ((reinterpret_cast<uintptr_t>(G.out[m] + row0) & 7) == 0);   // warp-uniform
+                if (o_on && (pair ? lane == 0 : true)) {
                     const long off = reinterpret_cast<const char *>(o_ptr) - P.local_base;
 #pragma unroll
                     for (int p = 0; p < TB200_MAX_PEERS; ++p)
-                        if (p < P.world && p != P.rank) *reinterpret_cast<float *>(P.peer_base[p] + off) = val;
+                        if (p < P.world && p != P.rank) {
+                            sink ^= pendr[p];
+                            if (pair) pendr[p] = atom_exch64_relaxed_sys(P.peer_base[p] + off, val, val1);
+                            else pendr[p] = atom_exch_relaxed_sys(reinterpret_cast<float *>(P.peer_base[p] + off), val);
+                        }
                 }
-                if (tr && tr[11] == 0) tr[11] = clock64();
             }
             if (tra) { const long long t = clock64(); a_tail += t - t_prev, t_prev = t; }
         }
         if (tra) tr[16] = a_wait, tr[17] = a_dots, tr[18] = a_refill, tr[19] = a_tail, tr[20] = a_items;
+        if (kPeers && G.shared_mask != 0) {
+#pragma unroll
+            for (int p = 0; p < TB200_MAX_PEERS; ++p)
+                if (p < P.world) sink ^= pendr[p], pendr[p] = 0;
+        }
         if (!(P.flags & 8)) { sink ^= pend; asm volatile("" ::"r"(sink) : "memory"); }   // every exchange of this lane has returned
+
         if (tr) tr[6] = clock64();
         __syncwarp();
         bar_arrive(kBarArrived, kThreads);                  // this warp's results of group g are stored; never blocks
@@ -887,8 +924,10 @@ static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int
         p->d_epoch = p->d_cnt + n_groups + 3;
         ok = cudaMemcpy(p->d_groups, h, (size_t)n_groups * sizeof(PlanGroup), cudaMemcpyHostToDevice) == cudaSuccess &&
              cudaMemset(p->d_cnt, 0, (size_t)(n_groups + 1) * 4 + 16) == cudaSuccess &&
-             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
-             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess;
+             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
+             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
+             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
+             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess;
         if (!ok) tb200_set_error("plan_create: %s", cudaGetErrorString(cudaGetLastError()));
     } else cudaGetLastError();
     free(h);
@@ -923,8 +962,12 @@ int tb200_plan_run(tb200_plan *p, int first, int count) {
         // one CTA per SM, all co-resident (the groups synchronise through arrival counters); plain stream order, no PDL: the
         // kernel owns the whole GPU for the step
         const size_t smem = p->smem + (size_t)n * sizeof(PlanGroup);
-        if (p->type == TB200_TYPE_Q4_K) plan_kernel<TB200_TYPE_Q4_K><<<dim3((unsigned)c->sm_count), dim3(kTW * 32), smem, c->stream>>>(P);
-        else plan_kernel<TB200_TYPE_Q4_0><<<dim3((unsigned)c->sm_count), dim3(kTW * 32), smem, c->stream>>>(P);
+        const dim3 grid((unsigned)c->sm_count), block(kTW * 32);
+        if (p->world > 1) {
+            if (p->type == TB200_TYPE_Q4_K) plan_kernel<TB200_TYPE_Q4_K, true><<<grid, block, smem, c->stream>>>(P);
+            else plan_kernel<TB200_TYPE_Q4_0, true><<<grid, block, smem, c->stream>>>(P);
+        } else if (p->type == TB200_TYPE_Q4_K) plan_kernel<TB200_TYPE_Q4_K, false><<<grid, block, smem, c->stream>>>(P);
+        else plan_kernel<TB200_TYPE_Q4_0, false><<<grid, block, smem, c->stream>>>(P);
         tb200_count_launch();
         TB_CUDA(cudaGetLastError());
     }
