@@ -232,7 +232,7 @@ def test_multi_gpu_fused_gather_parity(world):
     port = 29600 + os.getpid() % 300 + world
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
                         "--master-port", str(port), str(ROOT / "tools" / "check_p2p.py")], capture_output=True, text=True, timeout=1500)
-    assert r.returncode == 0 and "P2P_GATHER_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.returncode == 0 and "P2P_GATHER_OK" in r.stdout and "P2P_PLAN_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
 # ------------------------------------------------------------------ host entry point: what may be kept resident
