@@ -378,11 +378,13 @@ def run_b200_arm(args):
     # sharing one input) is split when its weights exceed --split-min-mb; smaller groups are computed in full on every rank.
     if args.split_min_mb is None:
         # Break-even of a split: it saves bytes*(1 - 1/W) / 6.5 TB/s of streaming and costs one cross-GPU exchange on the group's
-        # critical path - measured 3.2 us (W = 2) to ~4 us (W = 8) inside the multi-GPU plan (remote exchange round trip + flag +
-        # poll), ~6 us as kernel -> barrier kernel -> kernel on the one-shot path (round 1's 80 MB rule).
+        # critical path - ~3.2..4 us inside the multi-GPU plan (remote exchange round trip + flag + poll), ~6 us as
+        # kernel -> barrier kernel -> kernel on the one-shot path (round 1's 80 MB rule). On 2 GPUs a 66 MB group (gate + up) measured
+        # as a net loss (1.040 vs 0.993 ms per 8B step) although the formula says +2 us: its halves are chain-bound, not
+        # bandwidth-bound, so W = 2 only splits what is far above the break-even (the vocabulary matrix).
         in_plan = use_plan and args.gather == "p2p"
-        cost_us = ({2: 3.2, 4: 3.6}.get(world, 4.0) if in_plan else 6.0)
-        args.split_min_mb = round(cost_us * 6.5e3 / (1.0 - 1.0 / world), 1) if world > 1 else 80.0
+        cost_us = ({2: 8.0, 4: 3.6}.get(world, 4.0) if in_plan else 6.0)
+        args.split_min_mb = round(cost_us * 6.5 / (1.0 - 1.0 / world), 1) if world > 1 else 80.0   # us x 6.5 TB/s = MB
         if not in_plan:
             args.split_min_mb = 80.0
     grp_bytes = {}
