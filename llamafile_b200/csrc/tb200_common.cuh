@@ -72,6 +72,7 @@ struct tb200_peers {
     uint32_t *flags[TB200_MAX_PEERS];   // [world] arrival epochs on every rank
     uint32_t *epoch;                    // local launch counter (device memory, so graph replays advance it)
     int *timeout_flag;                  // set when a barrier gave up waiting
+    uint32_t *plan_seq;                 // shared groups completed by ALL multi-GPU plan launches on this peer group (device memory; the plans' flag values)
 };
 
 // per-device context (tb200_api.cu)

@@ -78,8 +78,9 @@ tb200_peers *tb200_peers_create(int world, int rank, void *const *out_bases, voi
     memset(g, 0, sizeof(*g));
     g->world = world, g->rank = rank;
     for (int p = 0; p < world; ++p) g->out_base[p] = out_bases[p], g->flags[p] = (uint32_t *)flag_bases[p];
-    if (cudaMalloc(&g->epoch, 8) != cudaSuccess || cudaMemsetAsync(g->epoch, 0, 8, c->stream) != cudaSuccess) { cudaGetLastError(); delete g; return nullptr; }
+    if (cudaMalloc(&g->epoch, 16) != cudaSuccess || cudaMemsetAsync(g->epoch, 0, 16, c->stream) != cudaSuccess) { cudaGetLastError(); delete g; return nullptr; }
     g->timeout_flag = (int *)(g->epoch + 1);
+    g->plan_seq = g->epoch + 2;
     return g;
 }
 

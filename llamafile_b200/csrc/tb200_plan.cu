@@ -80,7 +80,7 @@ struct PlanParams {
     const char *local_base;            // this rank's symmetric buffer; a shared result at local_base + off also goes to peer_base[p] + off
     char *peer_base[TB200_MAX_PEERS];
     unsigned *peer_flag[TB200_MAX_PEERS];   // rank p's flag words: [kPeerFlag0 + r] = the last shared-group sequence number rank r has completed
-    unsigned *epoch, *done;            // launches of this plan so far (device side: survives CUDA-graph replay); CTAs that left the launch
+    unsigned *epoch, *done;            // the peer group's count of completed shared groups (tb200_peers::plan_seq); CTAs that left the launch
 };
 constexpr int kPeerFlag0 = 8;           // words 0..7 of a rank's flag buffer belong to tb200_peers_barrier
 
@@ -148,6 +148,10 @@ __device__ __forceinline__ unsigned atom_exch64_relaxed_sys(char *p, float lo, f
 }
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+#ifndef TB200_PLAN_CNT_STRIDE
+#define TB200_PLAN_CNT_STRIDE 1
+#endif
+constexpr int kCS = TB200_PLAN_CNT_STRIDE;                   // words between the arrival counters of consecutive groups
 constexpr int kTraceSlots = 24;                            // tb200_plan_trace: stamps 0..15, per-group sums of warp 0 in 16..21
 constexpr long long kSpinLimit = 4000000000LL;            // ~2 s of SM clocks: a wedged wait gives up and raises *err
 
@@ -521,7 +525,9 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
     // atomic round trip: consumers only ARRIVE (bar.arrive, non-blocking) and use the wait for the work that is not urgent
     // (refilling the ring stage they just emptied with a row of the group after next).
     if (warp == kPW) {
-        const unsigned ep = kPeers ? ld_relaxed(P.epoch) : 0u, ep_base = ep * (unsigned)P.n_shared;
+        // sequence numbers of this launch's shared groups continue where the last multi-GPU plan launch on this peer group stopped
+        // (one counter per peer group, in device memory: CUDA-graph replays and different plans sharing the buffers stay monotonic)
+        const unsigned ep_base = kPeers ? ld_relaxed(P.epoch) - (unsigned)tab[P.first].sh_before : 0u;
         for (int g = P.first; g < P.end; ++g) {
             const PlanGroup &G = tab[g];
             long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
@@ -533,10 +539,10 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                     const unsigned seq = ep_base + (unsigned)tab[g - 1].sh_before + 1u;
                     if ((P.flags & 9) == 8) fence_acq_rel_gpu();   // (old protocol, flag 8: plain stores + a release fence here, ~1 us per group)
                     if (tr) tr[13] = clock64();
-                    const unsigned old = atom_add_relaxed(P.cnt + (g - 1), 1u);
+                    const unsigned old = atom_add_relaxed(P.cnt + (g - 1) * kCS, 1u);
                     if (tr) tr[2] = clock64();
                     if (old == gridDim.x - 1) {
-                        if (g - 1 > P.first) P.cnt[g - 2] = 0;     // everybody has left barrier g-2: re-arm it for the next launch
+                        if (g - 1 > P.first) P.cnt[(g - 2) * kCS] = 0;     // everybody has left barrier g-2: re-arm it for the next launch
                         if (shared) peers_signal(P, seq);
                     }
                     const long long t0 = clock64();
@@ -546,7 +552,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                     // has seen the last arrival - whose release fence made the arriving CTA's stores visible at L2 first.
                     // (Four polls in flight a quarter of a round trip apart were measured SLOWER, 0.999 vs 0.972 ms per step: 148 pollers
                     // on the line the arrivals' atomics target already compete with them.)
-                    while (ld_relaxed(P.cnt + (g - 1)) < gridDim.x) {
+                    while (ld_relaxed(P.cnt + (g - 1) * kCS) < gridDim.x) {
 #ifdef TB200_PLAN_POLL_SLEEP
                         __nanosleep(TB200_PLAN_POLL_SLEEP);
 #endif
@@ -574,31 +580,31 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             const bool shared = tab[last].shared_mask != 0;
             const unsigned seq = ep_base + (unsigned)tab[last].sh_before + 1u;
             if (lane == 0) {
-                const unsigned old = atom_add_relaxed(P.cnt + last, 1u);
+                const unsigned old = atom_add_relaxed(P.cnt + last * kCS, 1u);
                 if (old == gridDim.x - 1) {
-                    if (last - 1 >= P.first) P.cnt[last - 1] = 0;
+                    if (last - 1 >= P.first) P.cnt[(last - 1) * kCS] = 0;
                     if (shared) peers_signal(P, seq);
                 }
                 if (shared) {
                     const long long t0 = clock64();
-                    while (ld_relaxed(P.cnt + last) < gridDim.x)
+                    while (ld_relaxed(P.cnt + last * kCS) < gridDim.x)
                         if (clock64() - t0 > kSpinLimit) { *P.err = 1; break; }
                 }
             }
             __syncwarp();
             if (shared) peers_wait(P, seq, lane);
             if (lane == 0 && atom_add_relaxed(P.done, 1u) == gridDim.x - 1) {   // every CTA is past its polls of cnt[last]
-                P.cnt[last] = 0;
+                P.cnt[last * kCS] = 0;
                 *P.done = 0;
-                *P.epoch = ep + 1u;
+                *P.epoch = seq - (shared ? 0u : 1u);   // = the number of the launch's last shared group
             }
         } else if (lane == 0 && P.end - P.first > 1) {
             const int last = P.end - 1;
             fence_acq_rel_gpu();
-            const unsigned old = atom_add_relaxed(P.cnt + last, 1u);
+            const unsigned old = atom_add_relaxed(P.cnt + last * kCS, 1u);
             if (old == gridDim.x - 1) {
-                if (last - 1 >= P.first) P.cnt[last - 1] = 0;
-                P.cnt[last] = 0;
+                if (last - 1 >= P.first) P.cnt[(last - 1) * kCS] = 0;
+                P.cnt[last * kCS] = 0;
             }
         }
         return;
@@ -850,7 +856,7 @@ struct tb200_plan {
     const char *local_base;
     char *peer_base[TB200_MAX_PEERS];
     unsigned *peer_flag[TB200_MAX_PEERS];
-    unsigned *d_epoch;                 // {epoch, done}
+    unsigned *d_epoch;                 // multi-GPU plans: the peer group's sequence counter
     PlanGroup *d_groups;
     unsigned *d_cnt;
     int *d_err;
@@ -918,12 +924,12 @@ static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int
     bool ok = p->smem + 16 * sizeof(PlanGroup) <= kPlanSmemMax;
     if (!ok) tb200_set_error("plan_create: K = %d does not fit the activation staging", nb_max * QK);
     ok = ok && cudaMalloc((void **)&p->d_groups, (size_t)n_groups * sizeof(PlanGroup)) == cudaSuccess;
-    ok = ok && cudaMalloc((void **)&p->d_cnt, (size_t)(n_groups + 1) * 4 + 16) == cudaSuccess;
+    ok = ok && cudaMalloc((void **)&p->d_cnt, (size_t)(n_groups + 1) * kCS * 4 + 16) == cudaSuccess;
     if (ok) {
-        p->d_err = (int *)(p->d_cnt + n_groups + 1);   // then {done, epoch}
-        p->d_epoch = p->d_cnt + n_groups + 3;
+        p->d_err = (int *)(p->d_cnt + (size_t)(n_groups + 1) * kCS);   // then {-, done, epoch}
+        p->d_epoch = pg ? pg->plan_seq : p->d_cnt + (size_t)(n_groups + 1) * kCS + 3;
         ok = cudaMemcpy(p->d_groups, h, (size_t)n_groups * sizeof(PlanGroup), cudaMemcpyHostToDevice) == cudaSuccess &&
-             cudaMemset(p->d_cnt, 0, (size_t)(n_groups + 1) * 4 + 16) == cudaSuccess &&
+             cudaMemset(p->d_cnt, 0, (size_t)(n_groups + 1) * kCS * 4 + 16) == cudaSuccess &&
              cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
              cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
              cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
@@ -955,7 +961,7 @@ int tb200_plan_run(tb200_plan *p, int first, int count) {
         P.trace = p->d_trace;
         P.world = p->world, P.rank = p->rank, P.n_shared = p->n_shared, P.local_base = p->local_base;
         for (int q = 0; q < TB200_MAX_PEERS; ++q) P.peer_base[q] = p->peer_base[q], P.peer_flag[q] = p->peer_flag[q];
-        P.done = p->d_cnt + p->n_groups + 2, P.epoch = p->d_epoch;
+        P.done = p->d_cnt + (size_t)(p->n_groups + 1) * kCS + 2, P.epoch = p->d_epoch;
         static const int flags = [] { const char *v = getenv("TB200_PLAN_FLAGS"); return v && *v ? atoi(v) : 0; }();
         P.flags = flags;
         p->grid = c->sm_count;
@@ -983,7 +989,7 @@ int tb200_plan_status(tb200_plan *p) {
 
 int tb200_plan_reset(tb200_plan *p) {
     if (!p) return TB200_ERR_INVALID;
-    TB_CUDA(cudaMemset(p->d_cnt, 0, (size_t)(p->n_groups + 1) * 4 + 8));   // counters, the error word and `done`; the epoch of a multi-GPU plan keeps counting (the peers' flags do)
+    TB_CUDA(cudaMemset(p->d_cnt, 0, (size_t)(p->n_groups + 1) * kCS * 4 + 12));   // counters, the error word and `done`; the epoch of a multi-GPU plan keeps counting (the peers' flags do)
     return TB200_OK;
 }
 

@@ -45,10 +45,15 @@ def check_plan(torch, dist, tb, H, o, B, PeerGroup, shard_rows, rank, world):
                         {"w": [w1a, w1b], "out": [sym("y1a", l1), sym("y1b", l1)], "x": pg.out + offs["y0"]},
                         {"w": [w2], "out": [y2], "x": pg.out + offs["y1a"]},
                         {"w": [w3], "out": [sym("y3", l3)], "x": pg.out + offs["y1b"]}], peers=pg)
+        # a second plan on the same peer group (the first two groups only): its launches share the peers' flag words with the first
+        plan_b = tb.Plan([{"w": [w0], "out": [sym("y0", l0)], "x": x0d},
+                          {"w": [w1a, w1b], "out": [sym("y1a", l1), sym("y1b", l1)], "x": pg.out + offs["y0"]}], peers=pg)
         for rep in range(4):
             plan.run()
             if rep == 1:
                 plan.run(0, 2); plan.run(2, 2)   # the same as two launches (the second starts from gathered data of the first)
+            if rep == 2:
+                plan_b.run()
         tb.synchronize()
         assert plan.status() == 0, f"plan wait timed out (status {plan.status()})"
         y0 = pg.read(offs["y0"], N0); y1a = pg.read(offs["y1a"], N1); y1b = pg.read(offs["y1b"], N1); y3 = pg.read(offs["y3"], N3)
@@ -60,7 +65,7 @@ def check_plan(torch, dist, tb, H, o, B, PeerGroup, shard_rows, rank, world):
             if not good:
                 print(f"rank {rank}: PLAN MISMATCH {H.TYPE_NAME[wt]} {name} err={H.scaled_err(got, ref):.3e} nan={int(np.isnan(got).sum())}", flush=True)
         dist.barrier()
-        plan.free()
+        plan.free(); plan_b.free()
     if rank == 0:
         print("P2P_PLAN_OK" if ok else "P2P_PLAN_FAILED", flush=True)
     return ok
