@@ -531,12 +531,13 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
         for (int g = P.first; g < P.end; ++g) {
             const PlanGroup &G = tab[g];
             long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
+            // (descriptor look-ups of the boundary before the wait, off the critical path)
+            const bool shared = kPeers && g > P.first && tab[g - 1].shared_mask != 0;
+            const unsigned seq = (kPeers && g > P.first) ? ep_base + (unsigned)tab[g - 1].sh_before + 1u : 0u;
             if (g > P.first && !(P.flags & 4)) {
                 bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
                 if (tr) tr[1] = clock64();
                 if (lane == 0) {
-                    const bool shared = kPeers && tab[g - 1].shared_mask != 0;
-                    const unsigned seq = ep_base + (unsigned)tab[g - 1].sh_before + 1u;
                     if ((P.flags & 9) == 8) fence_acq_rel_gpu();   // (old protocol, flag 8: plain stores + a release fence here, ~1 us per group)
                     if (tr) tr[13] = clock64();
                     const unsigned old = atom_add_relaxed(P.cnt + (g - 1) * kCS, 1u);
@@ -561,7 +562,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                     if (tr) tr[3] = clock64();
                 }
                 __syncwarp();
-                if (kPeers && tab[g - 1].shared_mask != 0) peers_wait(P, ep_base + (unsigned)tab[g - 1].sh_before + 1u, lane);
+                if (shared) peers_wait(P, seq, lane);
             } else if (g > P.first) bar_sync(kBarArrived, kThreads);
             bar_sync(kBarRelease, kThreads);                // consumers may stage and compute group g
             if (!(P.flags & 2) || g == P.first) {
@@ -715,6 +716,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
 
         // ---- this warp's units of the group
         const int nb = G.nb, nseg = G.nseg, nunits = G.nunits;
+        const int shmask = kPeers ? G.shared_mask : 0;     // once per group: the descriptor lives in shared memory
         const bool cached = kActCache && !kQ4K && nseg == 1;
         ActCache C;
         if (cached) {
@@ -809,7 +811,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 else *o_ptr = val;
                 if (tr && tr[11] == 0) tr[11] = clock64();
             }
-            if (kPeers && ((G.shared_mask >> m) & 1)) {
+            if (kPeers && ((shmask >> m) & 1)) {
                 // row-sharded matrix: the same rows of every rank's symmetric buffer, over NVLink - again as exchanges whose old
                 // values are folded in one unit later: once they are back the peers hold the rows, so no system-scope fence is
                 // needed before the arrival (a fence.acq_rel.sys per CTA and group cost 3.8 us: 1.41 vs 0.93 ms per step with
@@ -833,7 +835,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             if (tra) { const long long t = clock64(); a_tail += t - t_prev, t_prev = t; }
         }
         if (tra) tr[16] = a_wait, tr[17] = a_dots, tr[18] = a_refill, tr[19] = a_tail, tr[20] = a_items;
-        if (kPeers && G.shared_mask != 0) {
+        if (kPeers && shmask != 0) {
 #pragma unroll
             for (int p = 0; p < TB200_MAX_PEERS; ++p)
                 if (p < P.world) sink ^= pendr[p], pendr[p] = 0;
@@ -969,7 +971,8 @@ int tb200_plan_run(tb200_plan *p, int first, int count) {
         // kernel owns the whole GPU for the step
         const size_t smem = p->smem + (size_t)n * sizeof(PlanGroup);
         const dim3 grid((unsigned)c->sm_count), block(kTW * 32);
-        if (p->world > 1) {
+        static const bool force_peers = [] { const char *v = getenv("TB200_PLAN_FORCE_PEERS"); return v && *v == '1'; }();   // A/B: the multi-GPU instantiation on one GPU
+        if (p->world > 1 || force_peers) {
             if (p->type == TB200_TYPE_Q4_K) plan_kernel<TB200_TYPE_Q4_K, true><<<grid, block, smem, c->stream>>>(P);
             else plan_kernel<TB200_TYPE_Q4_0, true><<<grid, block, smem, c->stream>>>(P);
         } else if (p->type == TB200_TYPE_Q4_K) plan_kernel<TB200_TYPE_Q4_K, false><<<grid, block, smem, c->stream>>>(P);
