@@ -354,66 +354,100 @@ __device__ __forceinline__ int plan_nearest_int(float fval) {
 // group's input after its prologue, one warp per 256-element super-block (lane l: elements 4l..4l+3 and 128+4l..128+4l+3),
 // into the Q4_K decode kernel's staging form: s_q[sb][chunk c][5 x 16 B] = the 64 quants of chunk c (+ 16 B of padding: an
 // 80-byte lane stride is bank-conflict free, 64 is not), s_ds[sb*8 + k] = {d, sum of the 32 quants of sub-block k}.
-__device__ __forceinline__ void stage_activations_q8k(const PlanGroup &G, uint4 *s_q, int2 *s_ds, double *s_red, float *s_scale) {
+// R super-blocks per warp at a time (sb, sb + kTW, ...), phase by phase so that their dependency chains - loads, a five-step arg-max
+// butterfly, two divisions, rounding, sums - interleave: the 70B down projection (K = 28672, 7 super-blocks per warp) would
+// otherwise pay seven such chains back to back on every group boundary.
+template <int R>
+__device__ __forceinline__ void stage_q8k_rounds(const PlanGroup &G, int sb0, float scale, uint4 *s_q, int2 *s_ds) {
     const int nsb = G.nb / 8, prologue = G.prologue;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const float scale = prologue == TB200_PLAN_RMSNORM ? plan_rms_scale(G, s_red, s_scale) : 1.f;
-    for (int sb = warp; sb < nsb; sb += kTW) {               // warp-uniform
+    const int lane = threadIdx.x & 31;
+    float v[R][8];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int sb = min(sb0 + r * kTW, nsb - 1);          // (clamped: a round past the row recomputes the last block and does not store)
         const float4 *x4 = reinterpret_cast<const float4 *>(G.x) + sb * 64;
         const float4 a = __ldcg(x4 + lane), c = __ldcg(x4 + 32 + lane);
-        float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+        v[r][0] = a.x, v[r][1] = a.y, v[r][2] = a.z, v[r][3] = a.w, v[r][4] = c.x, v[r][5] = c.y, v[r][6] = c.z, v[r][7] = c.w;
         if (prologue == TB200_PLAN_RMSNORM) {
             const float4 *w4 = reinterpret_cast<const float4 *>(G.nw) + sb * 64;
             const float4 ta = __ldg(w4 + lane), tc = __ldg(w4 + 32 + lane);
             const float t[8] = {ta.x, ta.y, ta.z, ta.w, tc.x, tc.y, tc.z, tc.w};
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = __fmul_rn(__fmul_rn(v[e], scale), t[e]);
+            for (int e = 0; e < 8; ++e) v[r][e] = __fmul_rn(__fmul_rn(v[r][e], scale), t[e]);
         } else if (prologue == TB200_PLAN_SWIGLU) {
             const float4 *u4 = reinterpret_cast<const float4 *>(G.x2) + sb * 64;
             const float4 ta = __ldcg(u4 + lane), tc = __ldcg(u4 + 32 + lane);
             const float t[8] = {ta.x, ta.y, ta.z, ta.w, tc.x, tc.y, tc.z, tc.w};
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = silu_mul(v[e], t[e]);
+            for (int e = 0; e < 8; ++e) v[r][e] = silu_mul(v[r][e], t[e]);
         }
-        // first arg-max |x| (strict >), carrying the signed value
-        float amax = 0.f, vmax = 0.f;
-        int imax = QK_K;
+    }
+    // first arg-max |x| (strict >), carrying the signed value
+    float amax[R], vmax[R];
+    int imax[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        amax[r] = 0.f, vmax[r] = 0.f, imax[r] = QK_K;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const float ax = fabsf(v[i]);
+            const float ax = fabsf(v[r][i]);
             const int idx = (i < 4) ? 4 * lane + i : 128 + 4 * lane + (i - 4);
-            if (ax > amax) amax = ax, vmax = v[i], imax = idx;
+            if (ax > amax[r]) amax[r] = ax, vmax[r] = v[r][i], imax[r] = idx;
         }
+    }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float oa = __shfl_xor_sync(0xffffffffu, amax, o), ov = __shfl_xor_sync(0xffffffffu, vmax, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, imax, o);
-            if (oa > amax || (oa == amax && oi < imax)) amax = oa, vmax = ov, imax = oi;
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float oa = __shfl_xor_sync(0xffffffffu, amax[r], o), ov = __shfl_xor_sync(0xffffffffu, vmax[r], o);
+            const int oi = __shfl_xor_sync(0xffffffffu, imax[r], o);
+            if (oa > amax[r] || (oa == amax[r] && oi < imax[r])) amax[r] = oa, vmax[r] = ov, imax[r] = oi;
         }
+    }
+    float d[R], iscale[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) iscale[r] = amax[r] != 0.f ? __fdiv_rn(-127.f, vmax[r]) : 0.f;
+#pragma unroll
+    for (int r = 0; r < R; ++r) d[r] = amax[r] != 0.f ? __fdiv_rn(1.f, iscale[r]) : 0.f;
+    uint32_t lo[R], hi[R];
+    int s_lo[R], s_hi[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
         int qv[8];
-        float d = 0.f;
-        if (amax != 0.f) {
-            const float iscale = __fdiv_rn(-127.f, vmax);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) qv[i] = min(127, plan_nearest_int(__fmul_rn(iscale, v[i])));
-            d = __fdiv_rn(1.f, iscale);
-        } else {
+        for (int i = 0; i < 8; ++i) qv[i] = amax[r] != 0.f ? min(127, plan_nearest_int(__fmul_rn(iscale[r], v[r][i]))) : 0;
+        lo[r] = (uint32_t)(qv[0] & 0xff) | ((uint32_t)(qv[1] & 0xff) << 8) | ((uint32_t)(qv[2] & 0xff) << 16) | ((uint32_t)(qv[3] & 0xff) << 24);
+        hi[r] = (uint32_t)(qv[4] & 0xff) | ((uint32_t)(qv[5] & 0xff) << 8) | ((uint32_t)(qv[6] & 0xff) << 16) | ((uint32_t)(qv[7] & 0xff) << 24);
+        s_lo[r] = qv[0] + qv[1] + qv[2] + qv[3], s_hi[r] = qv[4] + qv[5] + qv[6] + qv[7];
+    }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) qv[i] = 0;
+    for (int o = 1; o <= 4; o <<= 1)
+#pragma unroll
+        for (int r = 0; r < R; ++r) s_lo[r] += __shfl_xor_sync(0xffffffffu, s_lo[r], o), s_hi[r] += __shfl_xor_sync(0xffffffffu, s_hi[r], o);   // 32-element sums
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int sb = sb0 + r * kTW;
+        if (sb < nsb) {                                      // warp-uniform
+            // word `lane` of the block's 64 (elements 4*lane..): chunk lane/16, piece (lane%16)/4, word lane%4; `hi` two chunks on
+            uint32_t *qw = reinterpret_cast<uint32_t *>(s_q + (size_t)sb * 20);
+            const int off = ((lane >> 4) * 5 + ((lane & 15) >> 2)) * 4 + (lane & 3);
+            qw[off] = lo[r], qw[off + 2 * 20] = hi[r];
+            if ((lane & 7) == 0) {
+                s_ds[sb * 8 + (lane >> 3)] = make_int2(__float_as_int(d[r]), s_lo[r]);
+                s_ds[sb * 8 + 4 + (lane >> 3)] = make_int2(__float_as_int(d[r]), s_hi[r]);
+            }
         }
-        const uint32_t lo = (uint32_t)(qv[0] & 0xff) | ((uint32_t)(qv[1] & 0xff) << 8) | ((uint32_t)(qv[2] & 0xff) << 16) | ((uint32_t)(qv[3] & 0xff) << 24);
-        const uint32_t hi = (uint32_t)(qv[4] & 0xff) | ((uint32_t)(qv[5] & 0xff) << 8) | ((uint32_t)(qv[6] & 0xff) << 16) | ((uint32_t)(qv[7] & 0xff) << 24);
-        int s_lo = qv[0] + qv[1] + qv[2] + qv[3], s_hi = qv[4] + qv[5] + qv[6] + qv[7];
-#pragma unroll
-        for (int o = 1; o <= 4; o <<= 1) s_lo += __shfl_xor_sync(0xffffffffu, s_lo, o), s_hi += __shfl_xor_sync(0xffffffffu, s_hi, o);   // 32-element sums
-        // word `lane` of the block's 64 (elements 4*lane..): chunk lane/16, piece (lane%16)/4, word lane%4; `hi` two chunks on
-        uint32_t *qw = reinterpret_cast<uint32_t *>(s_q + (size_t)sb * 20);
-        const int off = ((lane >> 4) * 5 + ((lane & 15) >> 2)) * 4 + (lane & 3);
-        qw[off] = lo, qw[off + 2 * 20] = hi;
-        if ((lane & 7) == 0) {
-            s_ds[sb * 8 + (lane >> 3)] = make_int2(__float_as_int(d), s_lo);
-            s_ds[sb * 8 + 4 + (lane >> 3)] = make_int2(__float_as_int(d), s_hi);
-        }
+    }
+}
+__device__ __forceinline__ void stage_activations_q8k(const PlanGroup &G, uint4 *s_q, int2 *s_ds, double *s_red, float *s_scale) {
+    const int nsb = G.nb / 8;
+    const int warp = threadIdx.x >> 5;
+    const float scale = G.prologue == TB200_PLAN_RMSNORM ? plan_rms_scale(G, s_red, s_scale) : 1.f;
+    for (int sb0 = warp; sb0 < nsb;) {                       // warp-uniform
+        const int rounds = (nsb - sb0 + kTW - 1) / kTW;
+        if (rounds >= 4) { stage_q8k_rounds<4>(G, sb0, scale, s_q, s_ds); sb0 += 4 * kTW; }
+        else if (rounds >= 2) { stage_q8k_rounds<2>(G, sb0, scale, s_q, s_ds); sb0 += 2 * kTW; }
+        else { stage_q8k_rounds<1>(G, sb0, scale, s_q, s_ds); sb0 += kTW; }
     }
 }
 
