@@ -714,6 +714,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
     };
     auto refill = [&](int st, long long *trp = nullptr) {   // stage st is empty: copy the iterator's item into it and move on
         if (ig >= P.end) return;
+        // (Lane 0 issuing all copies of an item one after the other instead of one lane per copy: 1.023 vs 0.973 ms per step.)
         if (lane < 2 * kR) {
             uint64_t *bar = &s_full[warp][st];
             if (lane == 0) mbar_expect_tx(bar, nx_tx);
