@@ -383,8 +383,12 @@ def run_b200_arm(args):
         # as a net loss (1.040 vs 0.993 ms per 8B step) although the formula says +2 us: its halves are chain-bound, not
         # bandwidth-bound, so W = 2 only splits what is far above the break-even (the vocabulary matrix).
         in_plan = use_plan and args.gather == "p2p"
-        cost_us = ({2: 8.0, 4: 3.6}.get(world, 4.0) if in_plan else 6.0)
+        cost_us = ({4: 3.6}.get(world, 4.0) if in_plan else 6.0)
         args.split_min_mb = round(cost_us * 6.5 / (1.0 - 1.0 / world), 1) if world > 1 else 80.0   # us x 6.5 TB/s = MB
+        if in_plan and world == 2 and wtype == Q4_0:
+            # measured on 2 GPUs (8B step): everything replicated with the single-GPU kernel 0.971 ms; only the vocabulary matrix
+            # split 0.999 ms; gate/up split as well 1.040 ms. Two ranks do not pay for an exchange at T = 1: nothing is split.
+            args.split_min_mb = 1e6
         if not in_plan:
             args.split_min_mb = 80.0
     grp_bytes = {}
@@ -440,7 +444,7 @@ def run_b200_arm(args):
         pg = PeerGroup(world, rank, off)
 
     plan, plan_index, segments = None, {}, []
-    sharded_plan = (use_plan and world > 1 and pg is not None and os.environ.get("TB200_BENCH_SHARDED_PLAN", "1") != "0" and
+    sharded_plan = (use_plan and world > 1 and pg is not None and os.environ.get("TB200_BENCH_SHARDED_PLAN", "1") != "0" and any(split_grp.values()) and
                     all(mats[i][3] > mats[i][2] for grp, idx in schedule if split_grp[grp] for i in idx))
     if sharded_plan:
         # N > 1: the whole step as ONE multi-GPU plan (tb200_plan_create_peers). A split group's outputs point at this rank's row
@@ -825,7 +829,7 @@ def run_b200_arm(args):
                                else "oneshot: one quantizer + one GEMV launch per group, CUDA graph"),
                     "cuda_graph": graphed, "split_groups": sum(1 for g2, _ in schedule if split_grp[g2]),
                     "replicated_groups": sum(1 for g2, _ in schedule if not split_grp[g2]), "split_min_mb": args.split_min_mb,
-                    "parallelism": (f"row-shard x{world} (launch groups >= {args.split_min_mb} MB; smaller ones replicated) + " + ("fused all-gather (peer stores over NVLink + flag barrier per launch group); data plane is not NCCL" if pg is not None else "NCCL all-gather per launch group")) if world > 1 else "single GPU",
+                    "parallelism": (f"{world} replicas of the single-GPU step (no launch group is worth an exchange at this size and rank count: DESIGN 6.1)" if not any(split_grp.values()) else f"row-shard x{world} (launch groups >= {args.split_min_mb} MB; smaller ones replicated) + " + ("fused all-gather (peer stores over NVLink + flag barrier per launch group); data plane is not NCCL" if pg is not None else "NCCL all-gather per launch group")) if world > 1 else "single GPU",
                     "decode_tokens_per_s": 1e3 / ms_per_step})
         line = {"metric": METRIC[wtype], "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
