@@ -75,12 +75,13 @@ def test_supports_op_matrix(host):
     g.free()
 
 
-def decode_chain(K, F, V):
+def decode_chain(K, F, V, types=None):
     """One transformer layer's matmuls + the output projection as a dependent chain of one-token MUL_MAT nodes."""
     shapes = {"wq": (K, K), "wk": (K // 4, K), "wv": (K // 4, K), "wo": (K, K), "gate": (F, K), "up": (F, K), "down": (K, F), "out": (V, K)}
+    types = types or {}
 
     def build(g):
-        t = {n: g.tensor(H.Q4_0, k, rows) for n, (rows, k) in shapes.items()}
+        t = {n: g.tensor(types.get(n, H.Q4_0), k, rows) for n, (rows, k) in shapes.items()}
         t["x"] = g.tensor(H.F32, K, 1)
         q, kk, v = g.mul_mat(t["wq"], t["x"]), g.mul_mat(t["wk"], t["x"]), g.mul_mat(t["wv"], t["x"])
         o = g.mul_mat(t["wo"], q)
@@ -133,6 +134,37 @@ def test_decode_chain_is_one_persistent_launch(tb, host):
     assert g.compute() == 0
     H.assert_close(g.get(outs[0][0], outs[0][1]), B.oracle().mul_mat(Wn, H.Q4_0, x2), "wq after new weights")
     g.free()
+
+
+def test_decode_chain_q4_K_and_mixed_types(tb, host):
+    """A Q4_K chain runs as one persistent launch too; in a Q4_K_M-like mix (ffn_down and the output matrix Q6_K) the runs of
+    plannable nodes end where the type changes: two plan launches + two one-shot matmuls (each = quantizer + kernel), values
+    equal to ggml's CPU backend either way."""
+    G, backend, cpu = host
+    K, F, V = 512, 1280, 3000
+    rng = np.random.default_rng(8)
+    for types, want_plan_nodes in (({n: H.Q4_K for n in ("wq", "wk", "wv", "wo", "gate", "up", "down", "out")}, 8),
+                                   ({**{n: H.Q4_K for n in ("wq", "wk", "wv", "wo", "gate", "up")}, "down": H.Q6_K, "out": H.Q6_K}, 6)):
+        shapes, build = decode_chain(K, F, V, types)
+        inputs = {}
+        for i, (n, (rows, k)) in enumerate(shapes.items()):
+            w = rng.standard_normal((rows, k)).astype(np.float32) * (1.6 / np.sqrt(k))    # keeps the hidden state's magnitude through the chain
+            r = B.reference()
+            inputs[n] = (r.quantize_q4_K(w) if types[n] == H.Q4_K else r.quantize_q6_K(w)) if r is not None else H.make_weights(types[n], rows, k, seed=i)
+        inputs["x"] = rng.standard_normal((1, K)).astype(np.float32)
+        pairs = run_both(host, build, inputs)
+        for i, (got, ref) in enumerate(pairs):
+            H.assert_close(got, ref, f"chain output {i} ({len(set(types.values()))} types)")
+        g = Graph(backend)
+        tensors, outs = build(g)
+        g.build([t for t, _ in outs], weights_usage=True)
+        for name, arr in inputs.items():
+            g.set(tensors[name], arr)
+        assert g.compute() == 0 and g.compute() == 0
+        launches, plan_nodes = tb.backend_last_graph_stats(backend)
+        assert plan_nodes == want_plan_nodes, (launches, plan_nodes)
+        assert launches == (1 if want_plan_nodes == 8 else 1 + 2 * 2), (launches, plan_nodes)
+        g.free()
 
 
 @pytest.mark.parametrize("wt", [H.Q4_0, H.Q8_0, H.F16])
