@@ -99,6 +99,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
 }
 // 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier; the weights are read exactly once, so the
 // lines are marked evict-first in L2 and leave the activations / outputs of the step resident there
+// the same three on precomputed 32-bit shared-memory addresses (the ring's refill path runs once per 4.6 KB item)
+__device__ __forceinline__ void mbar_expect_tx_a(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s_a(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
+}
 __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar, uint64_t policy) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
@@ -712,17 +726,18 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
         iseek();
         iprepare();
     };
+    const uint32_t bar_u32 = smem_u32(&s_full[warp][0]), ring_u32 = smem_u32(my_ring) + (uint32_t)dst_off;
     auto refill = [&](int st, long long *trp = nullptr) {   // stage st is empty: copy the iterator's item into it and move on
         if (ig >= P.end) return;
         // (Lane 0 issuing all copies of an item one after the other instead of one lane per copy: 1.023 vs 0.973 ms per step.)
         if (lane < 2 * kR) {
-            uint64_t *bar = &s_full[warp][st];
-            if (lane == 0) mbar_expect_tx(bar, nx_tx);
+            const uint32_t bar = bar_u32 + (uint32_t)st * 8u;
+            if (lane == 0) mbar_expect_tx_a(bar, nx_tx);
             __syncwarp((1u << (2 * kR)) - 1);               // the expected byte count is posted before any copy can complete
 #ifdef TB200_PLAN_TRACE_ITEMS
             if (trp) trp[14] = clock64();
 #endif
-            if (nx_on) bulk_g2s(my_ring + st * kStageBytes + dst_off, nx_src, nx_bytes, bar, policy);
+            if (nx_on) bulk_g2s_a(ring_u32 + (uint32_t)st * kStageBytes, nx_src, nx_bytes, bar, policy);
 #ifdef TB200_PLAN_TRACE_ITEMS
             if (trp) trp[15] = clock64();
 #endif
@@ -789,11 +804,11 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             for (int seg = 0; seg < nseg; ++seg, ++seq) {
                 const int st = seq % kPS;
                 {
-                    uint64_t *bar = &s_full[warp][st];
+                    const uint32_t bar = bar_u32 + (uint32_t)st * 8u;
                     const uint32_t parity = (seq / kPS) & 1;
-                    if (!mbar_try_wait(bar, parity)) {
+                    if (!mbar_try_wait_a(bar, parity)) {
                         const long long t0 = clock64();
-                        while (!mbar_try_wait(bar, parity))
+                        while (!mbar_try_wait_a(bar, parity))
                             if (clock64() - t0 > kSpinLimit) { *P.err = 2; break; }
                     }
                 }
