@@ -259,7 +259,9 @@ typedef struct {
 typedef struct tb200_plan tb200_plan;
 TB200_API tb200_plan *tb200_plan_create(int n_groups, const tb200_plan_group *groups);
 TB200_API int tb200_plan_run(tb200_plan *p, int first, int count);   /* enqueue groups [first, first+count) as one launch */
-TB200_API int tb200_plan_status(tb200_plan *p);   /* 0, or non-zero when a launch gave up waiting (its results are undefined; tb200_plan_reset) */
+TB200_API int tb200_plan_status(tb200_plan *p);   /* 0, or non-zero when a launch gave up waiting: 1 = grid barrier, 2 = a ring stage never landed, 3 = a peer's
+                                                   * sequence number (multi-GPU). Sticky: from then on launches stop waiting (they drain at once, results undefined)
+                                                   * until tb200_plan_reset */
 TB200_API int tb200_plan_reset(tb200_plan *p);
 /* debug: first call switches per-group phase stamps on (returns 0); later calls copy [n_groups][SMs][8] SM-clock stamps out */
 TB200_API long tb200_plan_trace(tb200_plan *p, long long *out, long capacity);

@@ -580,7 +580,10 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             const PlanGroup &G = tab[g];
             long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
             // (descriptor look-ups of the boundary before the wait, off the critical path)
-            const bool shared = kPeers && g > P.first && tab[g - 1].shared_mask != 0;
+            // once any wait of this launch has given up (a peer died, the ranks' plans disagree) nobody waits any more: the launch
+            // drains in microseconds instead of a spin limit per group, and tb200_plan_status() reports it
+            const bool dead = g > P.first && ld_relaxed(reinterpret_cast<const unsigned *>(P.err)) != 0;
+            const bool shared = kPeers && g > P.first && tab[g - 1].shared_mask != 0;   // (a dead launch still signals its peers, it only stops waiting)
             const unsigned seq = (kPeers && g > P.first) ? ep_base + (unsigned)tab[g - 1].sh_before + 1u : 0u;
             if (g > P.first && !(P.flags & 4)) {
                 bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
@@ -601,7 +604,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                     // has seen the last arrival - whose release fence made the arriving CTA's stores visible at L2 first.
                     // (Four polls in flight a quarter of a round trip apart were measured SLOWER, 0.999 vs 0.972 ms per step: 148 pollers
                     // on the line the arrivals' atomics target already compete with them.)
-                    while (ld_relaxed(P.cnt + (g - 1) * kCS) < gridDim.x) {
+                    while (!dead && ld_relaxed(P.cnt + (g - 1) * kCS) < gridDim.x) {
 #ifdef TB200_PLAN_POLL_SLEEP
                         __nanosleep(TB200_PLAN_POLL_SLEEP);
 #endif
@@ -610,7 +613,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                     if (tr) tr[3] = clock64();
                 }
                 __syncwarp();
-                if (shared) peers_wait(P, seq, lane);
+                if (shared && !dead) peers_wait(P, seq, lane);
             } else if (g > P.first) bar_sync(kBarArrived, kThreads);
             bar_sync(kBarRelease, kThreads);                // consumers may stage and compute group g
             if (!(P.flags & 2) || g == P.first) {
