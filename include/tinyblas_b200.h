@@ -128,7 +128,8 @@ TB200_API size_t llamafile_mixmul_needs(const struct ggml_tensor *weights, const
                                         const struct ggml_tensor *plan);
 
 /* llamafile/sgemm.h:76-77, llamafile/iqk_mul_mat.inc:204-221: one expert's rows with an
- * mmid_row_mapping {int32 i1, int32 i2}[Ny]; typeA Q4_K (B rows Q8_K) or Q4_0 (B rows Q8_0). */
+ * mmid_row_mapping {int32 i1, int32 i2}[Ny]; typeA one of the k-quants held here (Q4_K, Q5_K, Q6_K, IQ4_XS; B rows Q8_K), Q4_0 or Q5_0
+ * (B rows Q8_0) or Q4_1 (B rows Q8_1); false for anything else. */
 TB200_API bool llamafile_mixmul_iqk(long Nx, long Ny, long ne00, int ne11, int typeA, const void *A,
                                     const void *B, float *C, long nb1, long nb2, const void *vrow_mapping,
                                     int ith, int nth);
@@ -317,8 +318,8 @@ TB200_API int tb200_memset(void *dst, int value, size_t bytes);
 /* GGUF tensor loader: tensors of a GGUF file (v2/v3) straight from an mmap to resident weights.
  * Mirrors the reader in llama.cpp/ggml/src/ggml.c:20896-21160 (gguf_init_from_file) for the parts this path needs:
  * header, metadata skipped except general.alignment, tensor infos, aligned data section. `data` pointers returned by
- * tb200_gguf_find() point into the mapping and stay valid until tb200_gguf_close(). tb200_gguf_upload() accepts F16, Q4_0,
- * Q8_0 and Q4_K tensors of rank 2 (a weight matrix; rows [row_lo, row_hi) when row_hi > row_lo = a rank's shard) or
+ * tb200_gguf_find() point into the mapping and stay valid until tb200_gguf_close(). tb200_gguf_upload() accepts tensors of every weight type above
+ * (tb200_weights_upload's list) of rank 2 (a weight matrix; rows [row_lo, row_hi) when row_hi > row_lo = a rank's shard) or
  * rank 3 (ne[2] stacked expert matrices, the form tb200_mixmul_dev takes). */
 typedef struct tb200_gguf tb200_gguf;
 TB200_API tb200_gguf *tb200_gguf_open(const char *path);
