@@ -653,7 +653,16 @@ def run_b200_arm(args):
                                                   "frac": b / (ms * 1e-3) / 1e9 / peak, "distinct_MB": b / 1e6}
         if sub is not None:
             sub.free()
+            # the same matrices as INDEPENDENT groups (TB200_PLAN_INDEPENDENT: every matrix has its own weights, input and output,
+            # nothing depends on anything): the GEMV path's streaming rate for this shape without a dependency chain between matrices
+            sub = tb.Plan([{"w": [mats[i][6]], "out": [outs[i]], "x": groups[mats[i][5]][0], "prologue": tb.PLAN_QUANT | tb.PLAN_INDEPENDENT} for i in idx])
+            ms_i = timed(sub.run, max(3, args.steps // 2), 2) / max(3, args.steps // 2)
+            per_shape[f"N={shape[0]},K={shape[1]}"].update({"independent_us_per_matrix": ms_i * 1e3 / len(idx), "independent_GBps": b / (ms_i * 1e-3) / 1e9,
+                                                            "independent_frac": b / (ms_i * 1e-3) / 1e9 / peak})
+            sub.free()
     roofline["per_shape"] = per_shape
+    roofline["per_shape_note"] = ("us_per_matrix / GBps / frac: every matrix of the shape as its own group of ONE launch, each group waiting for the one "
+                                  "before it (a decode step's dependency chain); independent_*: the same launch with the groups declared independent")
 
     extra_clock_marks = {}
     if world == 1 and rank == 0 and not args.no_extra:

@@ -245,7 +245,11 @@ TB200_API void tb200_acts_free(tb200_acts *a);
  *   TB200_PLAN_SWIGLU   silu(x) * x2                              -> quantize   (ggml_silu + ggml_mul; x = gate, x2 = up)
  * and every matrix may add a residual on the way out (out = W.x + residual, ggml_add). All matrices of a plan Q4_0 (Q8_0
  * activations) or all Q4_K (the prologue then ends in quantize_row_q8_K, bit-exact likewise), K % 256 == 0, one token. Buffers must stay valid while the plan exists; weights, inputs and outputs may be shared between groups. */
-enum { TB200_PLAN_QUANT = 0, TB200_PLAN_RMSNORM = 1, TB200_PLAN_SWIGLU = 2 };
+enum { TB200_PLAN_QUANT = 0, TB200_PLAN_RMSNORM = 1, TB200_PLAN_SWIGLU = 2,
+       /* OR-ed into `prologue`: the caller declares that this group reads nothing an earlier group of the same launch writes and
+        * overwrites nothing one of them reads (independent matmuls: experts, branches, a micro-benchmark of one shape): it starts
+        * without the grid barrier, so the weight stream of consecutive independent groups never stops */
+       TB200_PLAN_INDEPENDENT = 0x100 };
 typedef struct {
     int n;                                             /* matrices that share the input, <= TB200_GEMV_MAX_MATS */
     int prologue;                                      /* TB200_PLAN_* */

@@ -54,6 +54,8 @@ struct alignas(16) PlanGroup {
     int nb, nseg;                      // 32-blocks per row; ring stages per unit
     int nunits, rot;                   // units (kR consecutive rows of one matrix) of all matrices; rotation of the warp -> unit assignment
     int nmat;
+    int nodep;                         // the caller declared the group independent of earlier groups of the launch (TB200_PLAN_INDEPENDENT): no grid barrier before it
+    int pad_;
     int shared_mask, sh_before;        // multi-GPU plans: bit m = matrix m's rows are stored into every rank's symmetric buffer; shared groups before this one
     int unit_begin[kPlanMats + 1];
     int rows[kPlanMats];
@@ -558,6 +560,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
         // sequence numbers of this launch's shared groups continue where the last multi-GPU plan launch on this peer group stopped
         // (one counter per peer group, in device memory: CUDA-graph replays and different plans sharing the buffers stay monotonic)
         const unsigned ep_base = kPeers ? ld_relaxed(P.epoch) - (unsigned)tab[P.first].sh_before : 0u;
+        int prev_real = -1;                                 // counter of the last boundary that was a real grid barrier (to be re-armed by the next one)
         for (int g = P.first; g < P.end; ++g) {
             const PlanGroup &G = tab[g];
             long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
@@ -567,7 +570,10 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             const bool dead = g > P.first && ld_relaxed(reinterpret_cast<const unsigned *>(P.err)) != 0;
             const bool shared = kPeers && g > P.first && tab[g - 1].shared_mask != 0;   // (a dead launch still signals its peers, it only stops waiting)
             const unsigned seq = (kPeers && g > P.first) ? ep_base + (unsigned)tab[g - 1].sh_before + 1u : 0u;
-            if (g > P.first && !(P.flags & 4)) {
+            // a group declared independent starts without the grid barrier (only the CTA's own warps meet, the staging buffers are
+            // reused) - unless the group before it exchanged rows with the peers, whose arrival some barrier has to cover
+            const bool skip = g > P.first && G.nodep && !shared;
+            if (g > P.first && !(P.flags & 4) && !skip) {
                 bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
                 if (tr) tr[1] = clock64();
                 if (lane == 0) {
@@ -576,9 +582,10 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                     const unsigned old = atom_add_relaxed(P.cnt + (g - 1) * kCS, 1u);
                     if (tr) tr[2] = clock64();
                     if (old == gridDim.x - 1) {
-                        if (g - 1 > P.first) P.cnt[(g - 2) * kCS] = 0;     // everybody has left barrier g-2: re-arm it for the next launch
+                        if (prev_real >= 0) P.cnt[prev_real * kCS] = 0;    // everybody has left the previous barrier: re-arm it for the next launch
                         if (shared) peers_signal(P, seq);
                     }
+                    prev_real = g - 1;
                     const long long t0 = clock64();
                     // Acquire side: a relaxed (L2) poll, no fence and no L1 invalidation per iteration. What an acquire would add is
                     // there by construction: every value another SM wrote is read with ld.global.cg / from L2 (no stale L1 copy can
@@ -616,7 +623,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             if (lane == 0) {
                 const unsigned old = atom_add_relaxed(P.cnt + last * kCS, 1u);
                 if (old == gridDim.x - 1) {
-                    if (last - 1 >= P.first) P.cnt[(last - 1) * kCS] = 0;
+                    if (prev_real >= 0) P.cnt[prev_real * kCS] = 0;
                     if (shared) peers_signal(P, seq);
                 }
                 if (shared) {
@@ -632,12 +639,12 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 *P.done = 0;
                 *P.epoch = seq - (shared ? 0u : 1u);   // = the number of the launch's last shared group
             }
-        } else if (lane == 0 && P.end - P.first > 1) {
+        } else if (lane == 0 && prev_real >= 0) {           // (a launch without a grid barrier used no counter)
             const int last = P.end - 1;
             fence_acq_rel_gpu();
             const unsigned old = atom_add_relaxed(P.cnt + last * kCS, 1u);
             if (old == gridDim.x - 1) {
-                if (last - 1 >= P.first) P.cnt[(last - 1) * kCS] = 0;
+                P.cnt[prev_real * kCS] = 0;
                 P.cnt[last * kCS] = 0;
             }
         }
@@ -919,9 +926,9 @@ static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int
         PlanGroup &G = h[g];
         const char *bad = nullptr;
         if (s.n < 1 || s.n > kPlanMats || !s.x) bad = "1..4 matrices and an input are required";
-        else if (s.prologue < TB200_PLAN_QUANT || s.prologue > TB200_PLAN_SWIGLU) bad = "unknown prologue";
-        else if (s.prologue == TB200_PLAN_RMSNORM && !s.norm_weight) bad = "RMSNORM needs norm_weight";
-        else if (s.prologue == TB200_PLAN_SWIGLU && !s.x2) bad = "SWIGLU needs x2";
+        else if ((s.prologue & ~TB200_PLAN_INDEPENDENT) < TB200_PLAN_QUANT || (s.prologue & ~TB200_PLAN_INDEPENDENT) > TB200_PLAN_SWIGLU) bad = "unknown prologue";
+        else if ((s.prologue & 0xff) == TB200_PLAN_RMSNORM && !s.norm_weight) bad = "RMSNORM needs norm_weight";
+        else if ((s.prologue & 0xff) == TB200_PLAN_SWIGLU && !s.x2) bad = "SWIGLU needs x2";
         else if (((uintptr_t)s.x | (uintptr_t)s.x2 | (uintptr_t)s.norm_weight) & 15) bad = "inputs must be 16-byte aligned";
         long units = 0;
         for (int m = 0; m < s.n && !bad; ++m) {
@@ -944,7 +951,7 @@ static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int
         }
         if (bad) { tb200_set_error("plan_create: group %d: %s", g, bad); free(h); return nullptr; }
         for (int m = s.n; m <= kPlanMats; ++m) G.unit_begin[m] = (int)units;
-        G.x = s.x, G.x2 = s.x2, G.nw = s.norm_weight, G.eps = s.eps, G.prologue = s.prologue;
+        G.x = s.x, G.x2 = s.x2, G.nw = s.norm_weight, G.eps = s.eps, G.prologue = s.prologue & 0xff, G.nodep = (s.prologue & TB200_PLAN_INDEPENDENT) != 0;
         G.nmat = s.n, G.nb = (int)(s.w[0]->k / QK), G.nseg = (G.nb + kSegBlocks - 1) / kSegBlocks;
         G.sh_before = n_shared;
         n_shared += G.shared_mask != 0;

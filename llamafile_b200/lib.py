@@ -256,6 +256,7 @@ def mixmul(w: Weights, experts: int, thought, tasks: int, plan, thinkers: int, t
 
 
 PLAN_QUANT, PLAN_RMSNORM, PLAN_SWIGLU = 0, 1, 2
+PLAN_INDEPENDENT = 0x100
 
 
 class PlanGroupC(C.Structure):

@@ -339,3 +339,37 @@ def test_plan_q4_K_chain_with_prologues(tb, oracle):
     rc = oracle.mul_mat(Wc, H.Q4_K, act)[0] + h
     H.assert_close(c.cpu().numpy()[None], rc[None], "q4_K swiglu + residual group")
     plan.free(); wa.free(); wb.free(); wc.free()
+
+
+def test_plan_independent_groups(tb, oracle):
+    """TB200_PLAN_INDEPENDENT: groups declared independent start without the grid barrier; mixed with dependent groups (one reads
+    an independent group's output, so the barrier before IT must still hold) and replayed, for both weight types."""
+    for wt, mk in ((H.Q4_0, q4_bytes), (H.Q4_K, q4k_bytes)):
+        K, N = 1024, 1024
+        rng = np.random.default_rng(17)
+        xs = [H.make_acts(1, K, seed=40 + i)[0] for i in range(6)]
+        Ws = [mk(N, K, seed=50 + i) for i in range(8)]
+        ws = [tb.Weights(W, wt, N, K) for W in Ws]
+        outs = [torch.full((N,), float("nan"), device="cuda") for _ in range(8)]
+        xd = [dev(x) for x in xs]
+        ind = tb.PLAN_QUANT | tb.PLAN_INDEPENDENT
+        groups = [{"w": [ws[0]], "out": [outs[0]], "x": xd[0]},
+                  {"w": [ws[1]], "out": [outs[1]], "x": xd[1], "prologue": ind},
+                  {"w": [ws[2]], "out": [outs[2]], "x": xd[2], "prologue": ind},
+                  {"w": [ws[3]], "out": [outs[3]], "x": outs[2]},                       # depends on an independent group's output
+                  {"w": [ws[4], ws[5]], "out": [outs[4], outs[5]], "x": xd[3], "prologue": ind},
+                  {"w": [ws[6]], "out": [outs[6]], "x": outs[3]},                       # depends across an independent group
+                  {"w": [ws[7]], "out": [outs[7]], "x": xd[4], "prologue": ind}]
+        plan = tb.Plan(groups)
+        for _ in range(4):
+            plan.run()
+        plan.run(1, 3); plan.run(4, 3)
+        tb.synchronize()
+        assert plan.status() == 0
+        got = [o.cpu().numpy() for o in outs]
+        ref_in = [xs[0], xs[1], xs[2], got[2], xs[3], xs[3], got[3], xs[4]]
+        for i in range(8):
+            H.assert_close(got[i][None], oracle.mul_mat(Ws[i], wt, ref_in[i][None]), f"{H.TYPE_NAME[wt]} independent-groups plan, matrix {i}")
+        plan.free()
+        for w in ws:
+            w.free()

@@ -8,7 +8,8 @@ print(f"{j['metric']}: {j['value']:.0f} {j['unit']}  {j['ms_per_step']:.4f} ms/s
 r = j["roofline"]
 print(f"roofline: {r['kernel']} achieved {r['achieved']:.0f} / {r['peak']:.0f} = {r['frac']:.3f} (of 8 TB/s: {r['frac_of_spec_8TBs']:.3f}) traffic={r.get('traffic')}")
 for k, v in r.get("per_shape", {}).items():
-    print(f"   {k:18s} {v['us_per_matrix']:7.2f} us  {v['GBps']:6.0f} GB/s  frac {v['frac']:.3f}")
+    ind = f"   | independent groups: {v['independent_us_per_matrix']:6.2f} us {v['independent_GBps']:6.0f} GB/s frac {v['independent_frac']:.3f}" if "independent_frac" in v else ""
+    print(f"   {k:18s} {v['us_per_matrix']:7.2f} us  {v['GBps']:6.0f} GB/s  frac {v['frac']:.3f}{ind}")
 for p in r.get("prefill", []):
     print(f"   prefill {p['type']} N={p['N']:6d} K={p['K']:6d} T={p['T']:5d}: {p['TFLOPS']:6.0f} TFLOPS  {p['frac_of_measured_sustained']:.2f} of sustained  {p['frac_of_spec_2250']:.2f} of 2.25PF  {p['sm_mhz']} MHz {p['power_w_max']} W {p['reasons']}")
 for m in r.get("mixmul", []):
