@@ -41,6 +41,11 @@ extern "C" {
 enum {
     TB200_GGML_OP_NONE = 0, TB200_GGML_OP_MUL_MAT = 23, TB200_GGML_OP_MUL_MAT_ID = 24,
     TB200_GGML_OP_RESHAPE = 30, TB200_GGML_OP_VIEW = 31, TB200_GGML_OP_PERMUTE = 32, TB200_GGML_OP_TRANSPOSE = 33,
+    /* the matmul's neighbours in llm_build_norm / llm_build_ffn: taken so that activations stay on the device, and
+     * fused into the decode plan where the graph allows */
+    TB200_GGML_OP_ADD = 2, TB200_GGML_OP_MUL = 6, TB200_GGML_OP_RMS_NORM = 20, TB200_GGML_OP_UNARY = 63,
+    TB200_GGML_UNARY_OP_SILU = 10,          /* enum ggml_unary_op, kept in op_params[0] of a GGML_OP_UNARY node */
+    TB200_GGML_TENSOR_FLAG_OUTPUT = 2,      /* enum ggml_tensor_flag */
 };
 enum { TB200_GGML_STATUS_ALLOC_FAILED = -2, TB200_GGML_STATUS_FAILED = -1, TB200_GGML_STATUS_SUCCESS = 0, TB200_GGML_STATUS_ABORTED = 1 };
 enum { TB200_GGML_BUFFER_USAGE_ANY = 0, TB200_GGML_BUFFER_USAGE_WEIGHTS = 1, TB200_GGML_BUFFER_USAGE_COMPUTE = 2 };

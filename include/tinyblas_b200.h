@@ -282,6 +282,14 @@ TB200_API void tb200_plan_free(tb200_plan *p);
 TB200_API int tb200_rms_norm_mul_dev(const float *x, long ldx, const float *norm_weight, float eps, long tokens, long k, float *y, long ldy);
 TB200_API int tb200_silu_mul_dev(const float *gate, const float *up, long ld, long tokens, long k, float *y, long ldy);
 TB200_API int tb200_moe_combine_dev(const float *expert_out, const float *weights, long tokens, int used, long rows, float *out, long ldo);
+/* the same graph ops one by one (what the ggml backend runs when a neighbour cannot be fused into a matmul: more than one token, or
+ * an intermediate that something else reads): ggml_rms_norm, ggml_mul / ggml_add (ldb = 0: b is one row broadcast over the tokens,
+ * ggml's broadcasting of a norm weight), ggml_silu. fp32, row-major, leading dimensions in floats; bit-for-bit ggml's CPU arithmetic
+ * except expf in silu (see tb200_silu_mul_dev). */
+TB200_API int tb200_rms_norm_dev(const float *x, long ldx, float eps, long tokens, long k, float *y, long ldy);
+TB200_API int tb200_mul_dev(const float *a, long lda, const float *b, long ldb, long tokens, long k, float *y, long ldy);
+TB200_API int tb200_add_dev(const float *a, long lda, const float *b, long ldb, long tokens, long k, float *y, long ldy);
+TB200_API int tb200_silu_dev(const float *x, long ldx, long tokens, long k, float *y, long ldy);
 TB200_API int tb200_acts_quantize_rmsnorm(tb200_acts *a, const float *x, long ldx, long tokens, const float *norm_weight, float eps, long k);
 TB200_API int tb200_acts_quantize_swiglu(tb200_acts *a, const float *gate, const float *up, long ld, long tokens, long k);
 

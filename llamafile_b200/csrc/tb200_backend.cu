@@ -11,6 +11,7 @@
 
 #include <atomic>
 #include <map>
+#include <unordered_map>
 #include <mutex>
 #include <vector>
 
@@ -168,7 +169,7 @@ struct PlanKey {
 struct BackendCtx {
     int device;
     cudaStream_t stream;
-    struct PlanEntry { tb200_plan *plan; int groups; uint64_t epoch; };
+    struct PlanEntry { tb200_plan *plan; int groups; uint64_t epoch; int end, matmuls; };   // end: first node after the run the plan covers
     std::map<PlanKey, PlanEntry> plans;
     void *ids_scratch = nullptr; size_t ids_cap = 0;
     int last_launches = 0, last_plan_nodes = 0;
@@ -251,11 +252,26 @@ bool mul_mat_id_supported(const T *op) {
 bool is_view_op(int op) {
     return op == TB200_GGML_OP_NONE || op == TB200_GGML_OP_RESHAPE || op == TB200_GGML_OP_VIEW || op == TB200_GGML_OP_PERMUTE || op == TB200_GGML_OP_TRANSPOSE;
 }
+// the matmul's neighbours (llm_build_norm, llm_build_ffn: llama.cpp/src/llama.cpp:8099-8225): fp32 matrices [ne0 x ne1] with dense rows;
+// MUL / ADD take a second operand of the same shape or one row broadcast over the tokens (the norm weight)
+bool f32_rows(const T *t) { return t && t->type == TB200_TYPE_F32 && t->ne[2] == 1 && t->ne[3] == 1 && t->nb[0] == 4 && t->nb[1] % 4 == 0 && t->nb[1] >= (size_t)t->ne[0] * 4; }
+bool ew_supported(const T *op) {
+    const T *a = tv((const struct ggml_tensor *)op->src_[0]), *b = tv((const struct ggml_tensor *)op->src_[1]);
+    if (!f32_rows(op) || !f32_rows(a) || a->ne[0] != op->ne[0] || a->ne[1] != op->ne[1]) return false;
+    switch (op->op_) {
+    case TB200_GGML_OP_RMS_NORM: return true;
+    case TB200_GGML_OP_UNARY: return op->op_params_[0] == TB200_GGML_UNARY_OP_SILU;
+    case TB200_GGML_OP_MUL: case TB200_GGML_OP_ADD: return f32_rows(b) && b->ne[0] == a->ne[0] && (b->ne[1] == a->ne[1] || b->ne[1] == 1);
+    default: return false;
+    }
+}
+bool is_ew_op(int op) { return op == TB200_GGML_OP_RMS_NORM || op == TB200_GGML_OP_UNARY || op == TB200_GGML_OP_MUL || op == TB200_GGML_OP_ADD; }
 bool backend_supports_op(tb200_backend_t, const struct ggml_tensor *op_) {
     const T *op = tv(op_);
     if (is_view_op(op->op_)) return true;
     if (op->op_ == TB200_GGML_OP_MUL_MAT) return mul_mat_supported(op);
     if (op->op_ == TB200_GGML_OP_MUL_MAT_ID) return mul_mat_id_supported(op);
+    if (is_ew_op(op->op_)) return ew_supported(op);
     return false;
 }
 bool backend_supports_buft(tb200_backend_t b, tb200_buft_t t) {
@@ -303,6 +319,110 @@ int run_mul_mat_id(BackendCtx *c, const T *op) {
     return tb200_mixmul_dev(w, (int)experts, (const float *)b->data, (int)tasks, plan, (int)thinkers, tokens, (float *)op->data);
 }
 
+int run_ew(const T *op) {
+    const T *a = tv((const struct ggml_tensor *)op->src_[0]), *b = tv((const struct ggml_tensor *)op->src_[1]);
+    const long k = op->ne[0], tokens = op->ne[1], lda = (long)(a->nb[1] / 4), ldy = (long)(op->nb[1] / 4);
+    float *y = (float *)op->data;
+    switch (op->op_) {
+    case TB200_GGML_OP_RMS_NORM: { float eps; memcpy(&eps, op->op_params_, 4); return tb200_rms_norm_dev((const float *)a->data, lda, eps, tokens, k, y, ldy); }
+    case TB200_GGML_OP_UNARY: return tb200_silu_dev((const float *)a->data, lda, tokens, k, y, ldy);
+    case TB200_GGML_OP_MUL: return tb200_mul_dev((const float *)a->data, lda, (const float *)b->data, b->ne[1] == 1 && tokens > 1 ? 0 : (long)(b->nb[1] / 4), tokens, k, y, ldy);
+    default: return tb200_add_dev((const float *)a->data, lda, (const float *)b->data, b->ne[1] == 1 && tokens > 1 ? 0 : (long)(b->nb[1] / 4), tokens, k, y, ldy);
+    }
+}
+
+// ---- a run of plannable nodes starting at node i, with the matmul's neighbours folded into the decode plan --------------------------
+// One-token RMS_NORM -> MUL(norm weight) feeding matmuls becomes the TB200_PLAN_RMSNORM prologue of their group, UNARY(SILU) ->
+// MUL(up) the TB200_PLAN_SWIGLU prologue, an ADD of a matmul's result with another tensor its residual epilogue. The intermediates
+// are then never written, so a pattern is only folded when NOTHING else reads them (every consumer in the graph is the folding node,
+// and they are not graph outputs); otherwise the run ends before the pattern and those nodes run as kernels of their own.
+struct FusedRun {
+    std::vector<tb200_plan_group> groups;
+    int end = 0, matmuls = 0, folded = 0;
+};
+typedef std::unordered_map<const void *, std::vector<int>> UseMap;   // tensor -> indices of the nodes that read it
+
+bool build_fused_run(const tb200_ggml_cgraph_view *cg, int i, int limit, const UseMap &uses, FusedRun &R, int &cut) {
+    struct Virt { int kind; const float *x, *y; float eps; int start, fused_uses; };   // kind: 1 NORM, 2 NORM*weight, 3 SILU, 4 SILU*up
+    std::unordered_map<const void *, Virt> virt;
+    std::unordered_map<const void *, std::pair<int, int>> slot;   // matmul (or its ADD) node -> (group, matrix)
+    std::vector<const void *> group_in;                            // identity of each group's input (tensor), for joining
+    R.groups.clear(), R.matmuls = R.folded = 0;
+    int run_type = 0, j = i;
+    auto n_uses = [&](const void *t) { auto it = uses.find(t); return it == uses.end() ? 0 : (int)it->second.size(); };
+    auto is_output = [&](const T *t) { return (t->flags_ & TB200_GGML_TENSOR_FLAG_OUTPUT) != 0; };
+    for (; j < limit; ++j) {
+        const struct ggml_tensor *nt = cg->nodes[j];
+        const T *n = tv(nt);
+        if (is_view_op(n->op_)) {
+            if (n->src_[0] && virt.count(n->src_[0])) break;      // a view of something we would not write
+            continue;
+        }
+        const T *a = tv((const struct ggml_tensor *)n->src_[0]), *b = tv((const struct ggml_tensor *)n->src_[1]);
+        if (n->op_ == TB200_GGML_OP_MUL_MAT) {
+            const int t = plan_node(n);
+            if (!t || (run_type && t != run_type)) break;
+            tb200_plan_group pg;
+            memset(&pg, 0, sizeof pg);
+            auto v = virt.find(n->src_[1]);
+            if (v != virt.end()) {
+                if (v->second.kind == 2) pg.prologue = TB200_PLAN_RMSNORM, pg.x = v->second.x, pg.norm_weight = v->second.y, pg.eps = v->second.eps;
+                else if (v->second.kind == 4) pg.prologue = TB200_PLAN_SWIGLU, pg.x = v->second.x, pg.x2 = v->second.y;
+                else { cut = v->second.start; return false; }
+                if (((uintptr_t)pg.x | (uintptr_t)pg.x2 | (uintptr_t)pg.norm_weight) & 15) { cut = v->second.start; return false; }
+                v->second.fused_uses++;
+            } else pg.x = (const float *)b->data, pg.prologue = TB200_PLAN_QUANT;
+            tb200_weights *w = resident_weights(a, a->ne[1]);
+            if (!w) { cut = j; return false; }
+            run_type = t;
+            // joins the previous group when it reads the same input (and therefore none of that group's outputs)
+            const bool join = !R.groups.empty() && group_in.back() == n->src_[1] && R.groups.back().n < TB200_GEMV_MAX_MATS && R.groups.back().w[0]->k == w->k;
+            if (!join) R.groups.push_back(pg), group_in.push_back(n->src_[1]);
+            tb200_plan_group &G = R.groups.back();
+            G.w[G.n] = w, G.out[G.n] = (float *)n->data;
+            slot[nt] = std::make_pair((int)R.groups.size() - 1, G.n);
+            G.n++, R.matmuls++;
+            continue;
+        }
+        if (!is_ew_op(n->op_) || !ew_supported(n) || n->ne[1] != 1) break;
+        if (n->op_ == TB200_GGML_OP_RMS_NORM || n->op_ == TB200_GGML_OP_UNARY) {
+            if (virt.count(n->src_[0])) break;
+            Virt v = {n->op_ == TB200_GGML_OP_RMS_NORM ? 1 : 3, (const float *)a->data, nullptr, 0.f, j, 0};
+            if (v.kind == 1) memcpy(&v.eps, n->op_params_, 4);
+            virt[nt] = v;
+            continue;
+        }
+        if (n->op_ == TB200_GGML_OP_MUL) {
+            auto va = virt.find(n->src_[0]);
+            if (va == virt.end() || virt.count(n->src_[1]) || (va->second.kind != 1 && va->second.kind != 3)) { if (va != virt.end()) { cut = va->second.start; return false; } break; }
+            if (va->second.kind == 3 && b->ne[1] != 1) break;
+            va->second.fused_uses++;
+            virt[nt] = Virt{va->second.kind + 1, va->second.x, (const float *)b->data, va->second.eps, va->second.start, 0};
+            continue;
+        }
+        // ADD: residual epilogue of a matmul of this run whose result nothing else reads
+        if (virt.count(n->src_[0]) || virt.count(n->src_[1])) break;
+        const struct ggml_tensor *mm = slot.count(n->src_[0]) ? (const struct ggml_tensor *)n->src_[0] : (slot.count(n->src_[1]) ? (const struct ggml_tensor *)n->src_[1] : nullptr);
+        if (!mm) break;
+        const T *other = mm == n->src_[0] ? b : a;
+        const std::pair<int, int> gm = slot[mm];
+        tb200_plan_group &G = R.groups[gm.first];
+        if (n_uses(mm) != 1 || is_output(tv(mm)) || G.residual[gm.second] || other->ne[1] != 1 || tv(mm)->op_ != TB200_GGML_OP_MUL_MAT) break;
+        G.out[gm.second] = (float *)n->data, G.residual[gm.second] = (const float *)other->data;
+        R.folded++;
+    }
+    // every folded intermediate must be read by its folding nodes only
+    for (auto &kv : virt) {
+        const Virt &v = kv.second;
+        if (v.fused_uses != n_uses(kv.first) || v.fused_uses == 0 || is_output(tv((const struct ggml_tensor *)kv.first))) {
+            if (v.start < cut) cut = v.start;
+        } else R.folded++;
+    }
+    if (cut < limit) return false;
+    R.end = j;
+    return true;
+}
+
 int backend_graph_compute(tb200_backend_t bk, struct ggml_cgraph *cg_) {
     BackendCtx *c = (BackendCtx *)bk->context;
     const tb200_ggml_cgraph_view *cg = (const tb200_ggml_cgraph_view *)cg_;
@@ -317,69 +437,71 @@ int backend_graph_compute(tb200_backend_t bk, struct ggml_cgraph *cg_) {
     const uint64_t l0 = tb200_launch_count();
     c->last_plan_nodes = 0;
     int rc = TB200_OK;
+    bool has_ew = false;
+    for (int q = 0; q < cg->n_nodes && !has_ew; ++q) has_ew = is_ew_op(tv(cg->nodes[q])->op_);
+    UseMap uses;   // filled on the first plan that has to be built for a graph with elementwise nodes
     for (int i = 0; i < cg->n_nodes && rc == TB200_OK;) {
         const T *op = tv(cg->nodes[i]);
         if (is_view_op(op->op_)) { ++i; continue; }
-        // a run of consecutive one-token Q4_0 matmuls: ONE persistent kernel for the whole run (nodes sharing their input form a group)
-        int j = i;
-        const int run_type = plan_node(op);
-        while (run_type && j < cg->n_nodes && (is_view_op(tv(cg->nodes[j])->op_) || plan_node(tv(cg->nodes[j])) == run_type)) ++j;
-        int n_plan = 0;
-        for (int q = i; q < j; ++q) n_plan += !is_view_op(tv(cg->nodes[q])->op_);
-        if (n_plan >= 2) {
+        // a run of consecutive one-token Q4_0 (or Q4_K) matmuls and their foldable neighbours: ONE persistent kernel for the whole run
+        // (matmuls sharing their input form a group)
+        const bool starts_run = plan_node(op) != 0 || (has_ew && is_ew_op(op->op_) && ew_supported(op) && op->ne[1] == 1 &&
+                                                      (op->op_ == TB200_GGML_OP_RMS_NORM || op->op_ == TB200_GGML_OP_UNARY));
+        if (starts_run) {
+            // cheap extent of what COULD be one run (no folding rules yet): the plan cache is keyed by these nodes' pointers
+            int jmax = i;
             PlanKey key;
-            for (int q = i; q < j; ++q) {
-                const T *n = tv(cg->nodes[q]);
+            const int type0 = plan_node(op);
+            for (; jmax < cg->n_nodes; ++jmax) {
+                const T *n = tv(cg->nodes[jmax]);
                 if (is_view_op(n->op_)) continue;
-                key.ptrs.push_back(tv((const struct ggml_tensor *)n->src_[0])->data);
-                key.ptrs.push_back(tv((const struct ggml_tensor *)n->src_[1])->data);
+                const int t = plan_node(n);
+                if (!(t != 0 || (has_ew && is_ew_op(n->op_) && ew_supported(n) && n->ne[1] == 1))) break;
+                if (t && type0 && t != type0) break;
                 key.ptrs.push_back(n->data);
+                key.ptrs.push_back(n->src_[0] ? tv((const struct ggml_tensor *)n->src_[0])->data : nullptr);
+                key.ptrs.push_back(n->src_[1] ? tv((const struct ggml_tensor *)n->src_[1])->data : nullptr);
+                key.ptrs.push_back((const void *)(uintptr_t)n->op_);
             }
             auto it = c->plans.find(key);
             if (it != c->plans.end() && it->second.epoch != g_resident_epoch.load()) {   // some resident weights were freed since: the plan may hold one
                 cudaStreamSynchronize(c->stream);
-                tb200_plan_free(it->second.plan);
+                if (it->second.plan) tb200_plan_free(it->second.plan);
                 c->plans.erase(it);
                 it = c->plans.end();
             }
             if (it == c->plans.end()) {
-                std::vector<tb200_plan_group> groups;
-                bool ok = true;
-                for (int q = i; q < j && ok; ++q) {
-                    const T *n = tv(cg->nodes[q]);
-                    if (is_view_op(n->op_)) continue;
-                    const T *a = tv((const struct ggml_tensor *)n->src_[0]), *b = tv((const struct ggml_tensor *)n->src_[1]);
-                    tb200_weights *w = resident_weights(a, a->ne[1]);
-                    if (!w) { ok = false; break; }
-                    // joins the previous group when it reads the same input and none of that group's outputs (then it depends on it)
-                    bool join = !groups.empty() && groups.back().x == (const float *)b->data && groups.back().n < TB200_GEMV_MAX_MATS &&
-                                groups.back().w[0]->k == w->k;
-                    if (groups.empty() || !join) {
-                        tb200_plan_group pg;
-                        memset(&pg, 0, sizeof pg);
-                        pg.x = (const float *)b->data, pg.prologue = TB200_PLAN_QUANT;
-                        groups.push_back(pg);
-                    }
-                    tb200_plan_group &pg = groups.back();
-                    pg.w[pg.n] = w, pg.out[pg.n] = (float *)n->data, pg.n++;
+                if (has_ew && uses.empty())
+                    for (int q = 0; q < cg->n_nodes; ++q)
+                        for (int sidx = 0; sidx < 10; ++sidx)
+                            if (tv(cg->nodes[q])->src_[sidx]) uses[tv(cg->nodes[q])->src_[sidx]].push_back(q);
+                FusedRun R;
+                int limit = jmax;
+                bool ok = false;
+                while (limit > i) {
+                    int cut = limit;
+                    if (build_fused_run(cg, i, limit, uses, R, cut)) { ok = true; break; }
+                    limit = cut < limit ? cut : limit - 1;
                 }
-                tb200_plan *p = ok ? tb200_plan_create((int)groups.size(), groups.data()) : nullptr;
+                ok = ok && R.end > i && (R.matmuls >= 2 || (R.matmuls >= 1 && R.folded > 0));
+                tb200_plan *p = ok ? tb200_plan_create((int)R.groups.size(), R.groups.data()) : nullptr;
                 if (c->plans.size() >= 16) {   // graphs that keep changing: do not hoard plans
                     cudaStreamSynchronize(c->stream);
-                    for (auto &kv : c->plans) tb200_plan_free(kv.second.plan);
+                    for (auto &kv : c->plans) if (kv.second.plan) tb200_plan_free(kv.second.plan);
                     c->plans.clear();
                 }
-                it = c->plans.emplace(key, BackendCtx::PlanEntry{p, (int)groups.size(), g_resident_epoch.load()}).first;   // plan == nullptr: "cannot be planned", node by node below
+                it = c->plans.emplace(key, BackendCtx::PlanEntry{p, p ? (int)R.groups.size() : 0, g_resident_epoch.load(), p ? R.end : i, p ? R.matmuls : 0}).first;   // plan == nullptr: "cannot be planned", node by node below
             }
             if (it->second.plan) {
                 rc = tb200_plan_run(it->second.plan, 0, it->second.groups);
-                i = j;
-                c->last_plan_nodes += n_plan;
+                i = it->second.end;
+                c->last_plan_nodes += it->second.matmuls;
                 continue;
             }
         }
         if (op->op_ == TB200_GGML_OP_MUL_MAT && mul_mat_supported(op)) rc = run_mul_mat(c, op);
         else if (op->op_ == TB200_GGML_OP_MUL_MAT_ID && mul_mat_id_supported(op)) rc = run_mul_mat_id(c, op);
+        else if (is_ew_op(op->op_) && ew_supported(op)) rc = run_ew(op);
         else {
             char msg[128];
             snprintf(msg, sizeof msg, "tb200_backend: node %d (op %d) is not supported by this backend\n", i, op->op_);

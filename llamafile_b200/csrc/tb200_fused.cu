@@ -37,7 +37,8 @@ __global__ void __launch_bounds__(256) rmsnorm_mul_kernel(const float *__restric
     }
     __syncthreads();
     const float scale = s_scale;
-    for (long i = threadIdx.x; i < k; i += blockDim.x) out[i] = __fmul_rn(__fmul_rn(row[i], scale), w[i]);
+    if (w) for (long i = threadIdx.x; i < k; i += blockDim.x) out[i] = __fmul_rn(__fmul_rn(row[i], scale), w[i]);
+    else for (long i = threadIdx.x; i < k; i += blockDim.x) out[i] = __fmul_rn(row[i], scale);   // ggml_rms_norm alone (ggml_vec_scale_f32)
 }
 
 __global__ void __launch_bounds__(256) swiglu_kernel(const float *__restrict__ gate, const float *__restrict__ up, long ld, long rows, long k,
@@ -65,9 +66,53 @@ __global__ void __launch_bounds__(256) moe_combine_kernel(const float *__restric
     out[t * ldo + r] = acc;
 }
 
+// the graph's plain elementwise ops, for a ggml backend that keeps the matmul's neighbours on the device when they cannot be fused
+// (more than one token, or an intermediate somebody else reads): y = a (op) b with b either a full [tokens][k] tensor or one row
+// broadcast over the tokens (ggml_mul by a norm weight), y = silu(x)
+enum { kOpMul = 0, kOpAdd = 1, kOpSilu = 2 };
+template <int kOp>
+__global__ void __launch_bounds__(256) elementwise_kernel(const float *__restrict__ a, long lda, const float *__restrict__ b, long ldb, long tokens, long k,
+                                                          float *__restrict__ y, long ldy) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i >= tokens * k) return;
+    const long r = i / k, c = i % k;
+    const float av = a[r * lda + c];
+    float out;
+    if (kOp == kOpSilu) out = __fdiv_rn(av, __fadd_rn(1.0f, expf(-av)));
+    else if (kOp == kOpMul) out = __fmul_rn(av, b[r * ldb + c]);
+    else out = __fadd_rn(av, b[r * ldb + c]);
+    y[r * ldy + c] = out;
+}
+
 }  // namespace
 
 extern "C" {
+
+int tb200_rms_norm_dev(const float *x, long ldx, float eps, long tokens, long k, float *y, long ldy) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!c) return TB200_ERR_NO_DEVICE;
+    if (!x || !y || tokens < 0 || k <= 0 || ldx < k || ldy < k) { tb200_set_error("rms_norm: bad arguments"); return TB200_ERR_INVALID; }
+    if (tokens == 0) return TB200_OK;
+    TB_CUDA(tb200_launch(rmsnorm_mul_kernel, dim3((unsigned)tokens), dim3(256), 0, c->stream, x, ldx, (const float *)nullptr, eps, k, y, ldy));
+    return TB200_OK;
+}
+
+static int elementwise(int op, const float *a, long lda, const float *b, long ldb, long tokens, long k, float *y, long ldy) {
+    tb200_ctx *c = tb200_get_ctx();
+    if (!c) return TB200_ERR_NO_DEVICE;
+    if (!a || !y || (op != kOpSilu && !b) || tokens < 0 || k <= 0 || lda < k || ldy < k || (ldb != 0 && ldb < k)) { tb200_set_error("elementwise: bad arguments"); return TB200_ERR_INVALID; }
+    if (tokens == 0) return TB200_OK;
+    const dim3 grid((unsigned)((tokens * k + 255) / 256));
+    if (op == kOpMul) TB_CUDA(tb200_launch(elementwise_kernel<kOpMul>, grid, dim3(256), 0, c->stream, a, lda, b, ldb, tokens, k, y, ldy));
+    else if (op == kOpAdd) TB_CUDA(tb200_launch(elementwise_kernel<kOpAdd>, grid, dim3(256), 0, c->stream, a, lda, b, ldb, tokens, k, y, ldy));
+    else TB_CUDA(tb200_launch(elementwise_kernel<kOpSilu>, grid, dim3(256), 0, c->stream, a, lda, b, ldb, tokens, k, y, ldy));
+    return TB200_OK;
+}
+int tb200_mul_dev(const float *a, long lda, const float *b, long ldb, long tokens, long k, float *y, long ldy) { return elementwise(kOpMul, a, lda, b, ldb, tokens, k, y, ldy); }
+int tb200_add_dev(const float *a, long lda, const float *b, long ldb, long tokens, long k, float *y, long ldy) { return elementwise(kOpAdd, a, lda, b, ldb, tokens, k, y, ldy); }
+int tb200_silu_dev(const float *x, long ldx, long tokens, long k, float *y, long ldy) { return elementwise(kOpSilu, x, ldx, nullptr, 0, tokens, k, y, ldy); }
 
 int tb200_rms_norm_mul_dev(const float *x, long ldx, const float *norm_weight, float eps, long tokens, long k, float *y, long ldy) {
     tb200_ctx *c = tb200_get_ctx();

@@ -112,6 +112,7 @@ EXPORT const struct tb200_ggml_backend_api *ref_backend_api(void) {
 EXPORT int ref_backend_abi(long *out, int cap) {
     const long v[] = {
         GGML_OP_NONE, GGML_OP_MUL_MAT, GGML_OP_MUL_MAT_ID, GGML_OP_RESHAPE, GGML_OP_VIEW, GGML_OP_PERMUTE, GGML_OP_TRANSPOSE,
+        GGML_OP_ADD, GGML_OP_MUL, GGML_OP_RMS_NORM, GGML_OP_UNARY, GGML_UNARY_OP_SILU, GGML_TENSOR_FLAG_OUTPUT,
         GGML_STATUS_ALLOC_FAILED, GGML_STATUS_FAILED, GGML_STATUS_SUCCESS, GGML_STATUS_ABORTED,
         GGML_BACKEND_BUFFER_USAGE_ANY, GGML_BACKEND_BUFFER_USAGE_WEIGHTS, GGML_BACKEND_BUFFER_USAGE_COMPUTE,
         offsetof(struct ggml_tensor, type), offsetof(struct ggml_tensor, buffer), offsetof(struct ggml_tensor, ne), offsetof(struct ggml_tensor, nb),

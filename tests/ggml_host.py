@@ -32,6 +32,7 @@ def ggml():
         "ggml_new_tensor_1d": (vp, [vp, C.c_int, i64]), "ggml_new_tensor_2d": (vp, [vp, C.c_int, i64, i64]), "ggml_new_tensor_3d": (vp, [vp, C.c_int, i64, i64, i64]),
         "ggml_view_2d": (vp, [vp, vp, i64, i64, sz, sz]),
         "ggml_mul_mat": (vp, [vp, vp, vp]), "ggml_mul_mat_id": (vp, [vp, vp, vp, vp]), "ggml_add": (vp, [vp, vp, vp]),
+        "ggml_mul": (vp, [vp, vp, vp]), "ggml_rms_norm": (vp, [vp, vp, C.c_float]), "ggml_silu": (vp, [vp, vp]),
         "ggml_new_graph": (vp, [vp]), "ggml_build_forward_expand": (None, [vp, vp]), "ggml_nbytes": (sz, [vp]),
         "ggml_backend_cpu_init": (vp, []), "ggml_backend_cpu_set_n_threads": (None, [vp, C.c_int]), "ggml_backend_free": (None, [vp]),
         "ggml_backend_alloc_ctx_tensors": (vp, [vp, vp]), "ggml_backend_buffer_free": (None, [vp]), "ggml_backend_buffer_set_usage": (None, [vp, C.c_int]),
@@ -62,6 +63,10 @@ class Graph:
 
     def mul_mat(self, a, b): return self.G.ggml_mul_mat(self.ctx, a, b)
     def mul_mat_id(self, as_, b, ids): return self.G.ggml_mul_mat_id(self.ctx, as_, b, ids)
+    def add(self, a, b): return self.G.ggml_add(self.ctx, a, b)
+    def mul(self, a, b): return self.G.ggml_mul(self.ctx, a, b)
+    def rms_norm(self, a, eps): return self.G.ggml_rms_norm(self.ctx, a, eps)
+    def silu(self, a): return self.G.ggml_silu(self.ctx, a)
 
     def build(self, outputs, weights_usage=False):
         self.gf = self.G.ggml_new_graph(self.ctx)

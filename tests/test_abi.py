@@ -104,6 +104,7 @@ def test_backend_struct_layouts_match_reference(tmp_path):
 int main(void) {
     const long v[] = {
         TB200_GGML_OP_NONE, TB200_GGML_OP_MUL_MAT, TB200_GGML_OP_MUL_MAT_ID, TB200_GGML_OP_RESHAPE, TB200_GGML_OP_VIEW, TB200_GGML_OP_PERMUTE, TB200_GGML_OP_TRANSPOSE,
+        TB200_GGML_OP_ADD, TB200_GGML_OP_MUL, TB200_GGML_OP_RMS_NORM, TB200_GGML_OP_UNARY, TB200_GGML_UNARY_OP_SILU, TB200_GGML_TENSOR_FLAG_OUTPUT,
         TB200_GGML_STATUS_ALLOC_FAILED, TB200_GGML_STATUS_FAILED, TB200_GGML_STATUS_SUCCESS, TB200_GGML_STATUS_ABORTED,
         TB200_GGML_BUFFER_USAGE_ANY, TB200_GGML_BUFFER_USAGE_WEIGHTS, TB200_GGML_BUFFER_USAGE_COMPUTE,
         offsetof(tb200_ggml_tensor_view, type), offsetof(tb200_ggml_tensor_view, buffer_), offsetof(tb200_ggml_tensor_view, ne), offsetof(tb200_ggml_tensor_view, nb),

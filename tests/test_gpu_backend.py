@@ -70,7 +70,13 @@ def test_supports_op_matrix(host):
     assert not G.ggml_backend_supports_op(backend, g.mul_mat(af32, b))       # F32 weights: handed back, as llamafile_sgemm does here
     assert not G.ggml_backend_supports_op(backend, g.mul_mat(a4, bh))        # activations must be F32
     assert not G.ggml_backend_supports_op(backend, g.mul_mat(a3, b3))        # batched matmuls (attention) stay on another backend
-    assert not G.ggml_backend_supports_op(backend, G.ggml_add(g.ctx, b, b))  # everything that is not the matmul path
+    # the matmul's neighbours (fp32 matrices): taken; anything else is not
+    nw = g.tensor(H.F32, 256)
+    assert G.ggml_backend_supports_op(backend, g.add(b, b)) and G.ggml_backend_supports_op(backend, g.mul(b, nw))
+    assert G.ggml_backend_supports_op(backend, g.rms_norm(b, 1e-5)) and G.ggml_backend_supports_op(backend, g.silu(b))
+    assert not G.ggml_backend_supports_op(backend, g.add(b3, b3))            # batched tensors
+    assert not G.ggml_backend_supports_op(backend, g.add(bh, bh))            # not fp32
+    assert not G.ggml_backend_supports_op(backend, G.ggml_rms_norm(g.ctx, b3, 1e-5))
     assert G.ggml_backend_name(backend).startswith(b"TB200")
     g.free()
 
@@ -165,6 +171,66 @@ def test_decode_chain_q4_K_and_mixed_types(tb, host):
         assert plan_nodes == want_plan_nodes, (launches, plan_nodes)
         assert launches == (1 if want_plan_nodes == 8 else 1 + 2 * 2), (launches, plan_nodes)
         g.free()
+
+
+def ffn_block(K, F, wt, tokens, extra_reader=False):
+    """llm_build_norm + llm_build_ffn (LLM_FFN_SILU, LLM_FFN_PAR) + the residual add of a llama layer's second half, preceded by the
+    attention output projection with ITS residual (llama.cpp/src/llama.cpp:8099-8225): x -> wo x + h -> rms_norm * w -> gate, up ->
+    silu(gate) * up -> down + (wo x + h)."""
+    shapes = {"wo": (K, K), "gate": (F, K), "up": (F, K), "down": (K, F)}
+
+    def build(g):
+        t = {n: g.tensor(wt, k, rows) for n, (rows, k) in shapes.items()}
+        t["x"], t["h"], t["nw"] = g.tensor(H.F32, K, tokens), g.tensor(H.F32, K, tokens), g.tensor(H.F32, K)
+        o = g.mul_mat(t["wo"], t["x"])
+        ffn_inp = g.add(o, t["h"])
+        cur = g.mul(g.rms_norm(ffn_inp, 1e-5), t["nw"])
+        ga, up = g.mul_mat(t["gate"], cur), g.mul_mat(t["up"], cur)
+        act = g.mul(g.silu(ga), up)
+        d = g.mul_mat(t["down"], act)
+        out = g.add(d, ffn_inp)
+        outs = [(ffn_inp, (tokens, K)), (out, (tokens, K))]
+        if extra_reader:   # something else reads the normalised activations: that pattern must then NOT be folded away
+            outs.append((g.add(cur, t["h"]), (tokens, K)))
+        return t, outs
+    return shapes, build
+
+
+@pytest.mark.parametrize("wt", [H.Q4_0, H.Q4_K])
+@pytest.mark.parametrize("tokens,extra_reader", [(1, False), (1, True), (5, False)])
+def test_ffn_block_neighbours_folded_into_the_plan(tb, host, wt, tokens, extra_reader):
+    """The matmul's graph neighbours on this backend (SURVEY.md §8 f4 through f1): at one token the whole block - 4 matmuls, RMSNorm,
+    the norm weight, SiLU, the gate*up product and both residual adds, 10 nodes - is ONE persistent kernel launch with no fp32
+    intermediate in memory; with a second reader of an intermediate, or more tokens, the same nodes run as kernels of their own.
+    Values against ggml's CPU backend either way (SiLU's expf differs by a few ulp: the usual fp32 gate)."""
+    G, backend, cpu = host
+    K, F = 512, 1280
+    shapes, build = ffn_block(K, F, wt, tokens, extra_reader)
+    rng = np.random.default_rng(21)
+    inputs = {}
+    for i, (n, (rows, k)) in enumerate(shapes.items()):
+        w = rng.standard_normal((rows, k)).astype(np.float32) * (1.2 / np.sqrt(k))
+        inputs[n] = B.oracle().quantize_q4_0(w) if wt == H.Q4_0 else (B.reference().quantize_q4_K(w) if B.reference() is not None else H.make_weights(wt, rows, k, seed=i))
+    inputs["x"] = rng.standard_normal((tokens, K)).astype(np.float32)
+    inputs["h"] = rng.standard_normal((tokens, K)).astype(np.float32)
+    inputs["nw"] = rng.uniform(0.5, 1.5, K).astype(np.float32)
+    pairs = run_both(host, build, inputs)
+    for i, (got, ref) in enumerate(pairs):
+        H.assert_close(got, ref, f"ffn block output {i} tokens={tokens} extra_reader={extra_reader}")
+    g = Graph(backend)
+    tensors, outs = build(g)
+    g.build([t for t, _ in outs], weights_usage=True)
+    for name, arr in inputs.items():
+        g.set(tensors[name], arr)
+    assert g.compute() == 0 and g.compute() == 0
+    launches, plan_nodes = tb.backend_last_graph_stats(backend)
+    if tokens == 1 and not extra_reader:
+        assert (launches, plan_nodes) == (1, 4), (launches, plan_nodes)
+    elif tokens == 1:
+        assert plan_nodes >= 2 and launches > 1, (launches, plan_nodes)      # the norm pattern runs unfused, the rest still plans
+    else:
+        assert plan_nodes == 0, (launches, plan_nodes)
+    g.free()
 
 
 @pytest.mark.parametrize("wt", [H.Q4_0, H.Q8_0, H.F16])
