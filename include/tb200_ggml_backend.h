@@ -23,9 +23,12 @@
  *   ggml_backend_cuda_register_host_buffer   -> tb200_backend_register_host_buffer
  *   ggml_backend_cuda_unregister_host_buffer -> tb200_backend_unregister_host_buffer
  *
- * What the backend computes: GGML_OP_MUL_MAT and GGML_OP_MUL_MAT_ID for the weight types of include/tinyblas_b200.h (and the
- * view ops, which are no-ops); supports_op() answers false for everything else, so ggml's scheduler keeps those nodes on
- * another backend. Weights are repacked once, on the device, the first time a graph uses them; a run of consecutive
+ * What the backend computes: GGML_OP_MUL_MAT and GGML_OP_MUL_MAT_ID for the weight types of include/tinyblas_b200.h, the view ops
+ * (no-ops) and the matmul's neighbours in llm_build_norm / llm_build_ffn on fp32 matrices - RMS_NORM, MUL (same shape or a row
+ * broadcast: the norm weight), ADD, UNARY(SILU) - so that a transformer block's activations stay on the device; supports_op()
+ * answers false for everything else (rope, soft_max, the batched attention matmuls, ...), which ggml's scheduler keeps on another
+ * backend. At one token those neighbours are folded into the decode plan when nothing else reads the intermediates: RMSNorm * weight
+ * and silu(gate) * up become a matmul group's prologue, a residual add its epilogue. Weights are repacked once, on the device, the first time a graph uses them; a run of consecutive
  * one-token Q4_0 MUL_MAT nodes is executed as ONE persistent kernel (the decode plan, tb200_plan.cu), cached per graph the
  * way ggml-cuda caches its CUDA graph (ggml-cuda.cu:2467-2700). */
 #ifndef TB200_GGML_BACKEND_H
