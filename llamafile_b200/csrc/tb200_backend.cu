@@ -485,7 +485,7 @@ int backend_graph_compute(tb200_backend_t bk, struct ggml_cgraph *cg_) {
                 }
                 ok = ok && R.end > i && (R.matmuls >= 2 || (R.matmuls >= 1 && R.folded > 0));
                 tb200_plan *p = ok ? tb200_plan_create((int)R.groups.size(), R.groups.data()) : nullptr;
-                if (c->plans.size() >= 16) {   // graphs that keep changing: do not hoard plans
+                if (c->plans.size() >= 512) {   // graphs that keep changing: do not hoard plans (a 80-layer model is ~160 runs per graph)
                     cudaStreamSynchronize(c->stream);
                     for (auto &kv : c->plans) if (kv.second.plan) tb200_plan_free(kv.second.plan);
                     c->plans.clear();
