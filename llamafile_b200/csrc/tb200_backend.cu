@@ -407,7 +407,9 @@ bool build_fused_run(const tb200_ggml_cgraph_view *cg, int i, int limit, const U
         const T *other = mm == n->src_[0] ? b : a;
         const std::pair<int, int> gm = slot[mm];
         tb200_plan_group &G = R.groups[gm.first];
-        if (n_uses(mm) != 1 || is_output(tv(mm)) || G.residual[gm.second] || other->ne[1] != 1 || tv(mm)->op_ != TB200_GGML_OP_MUL_MAT) break;
+        const struct ggml_tensor *other_t = mm == n->src_[0] ? (const struct ggml_tensor *)n->src_[1] : (const struct ggml_tensor *)n->src_[0];
+        const bool same_group = slot.count(other_t) && slot[other_t].first == gm.first;   // a sum of two matmuls of ONE group: no barrier stands between them
+        if (n_uses(mm) != 1 || is_output(tv(mm)) || G.residual[gm.second] || other->ne[1] != 1 || tv(mm)->op_ != TB200_GGML_OP_MUL_MAT || same_group) break;
         G.out[gm.second] = (float *)n->data, G.residual[gm.second] = (const float *)other->data;
         R.folded++;
     }

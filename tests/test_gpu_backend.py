@@ -233,6 +233,27 @@ def test_ffn_block_neighbours_folded_into_the_plan(tb, host, wt, tokens, extra_r
     g.free()
 
 
+def test_sum_of_two_matmuls_of_one_group_is_not_folded(tb, host):
+    """a.x + b.x: both matmuls share their input, i.e. one plan group without a barrier between them, so the add cannot become the
+    residual epilogue of either (it would read the other's rows while they are being written); and a chain a.x -> + r -> b -> + (a.x + r)."""
+    G, backend, cpu = host
+    K = 512
+    rng = np.random.default_rng(33)
+    Wa, Wb = (B.oracle().quantize_q4_0(rng.standard_normal((K, K)).astype(np.float32) / np.sqrt(K)) for _ in range(2))
+
+    def build(g):
+        t = {"a": g.tensor(H.Q4_0, K, K), "b": g.tensor(H.Q4_0, K, K), "x": g.tensor(H.F32, K, 1), "r": g.tensor(H.F32, K, 1)}
+        ya, yb = g.mul_mat(t["a"], t["x"]), g.mul_mat(t["b"], t["x"])
+        s1 = g.add(ya, yb)
+        s2 = g.add(s1, t["r"])
+        yc = g.mul_mat(t["b"], s2)
+        return t, [(s1, (1, K)), (g.add(yc, s2), (1, K))]
+    inputs = {"a": Wa, "b": Wb, "x": rng.standard_normal((1, K)).astype(np.float32), "r": rng.standard_normal((1, K)).astype(np.float32)}
+    for _ in range(3):
+        for i, (got, ref) in enumerate(run_both(host, build, inputs)):
+            H.assert_close(got, ref, f"output {i}")
+
+
 @pytest.mark.parametrize("wt", [H.Q4_0, H.Q8_0, H.F16])
 @pytest.mark.parametrize("tokens,strided_ids", [(1, False), (5, False), (19, True), (64, True), (300, False)])
 def test_mul_mat_id_vs_cpu_backend(host, wt, tokens, strided_ids):
