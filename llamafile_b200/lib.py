@@ -62,7 +62,9 @@ def lib() -> C.CDLL:
         "tb200_quantize_row_q8_0": (C.c_bool, [vp, vp, C.c_int64]), "tb200_quantize_row_q8_K": (C.c_bool, [vp, vp, C.c_int64]),
         "tb200_fp32_to_fp16_row": (C.c_bool, [vp, vp, C.c_int64]), "tb200_weights_cache_clear": (None, []),
         "tb200_register_weights": (i, [vp, sz]), "tb200_unregister_weights": (i, [vp]), "tb200_weights_cache_bytes": (sz, []),
-        "tb200_rms_norm_mul_dev": (i, [vp, l, vp, C.c_float, l, l, vp, l]), "tb200_silu_mul_dev": (i, [vp, vp, l, l, l, vp, l]),
+        "tb200_rms_norm_mul_dev": (i, [vp, l, vp, C.c_float, l, l, vp, l]),
+        "tb200_rms_norm_dev": (i, [vp, l, C.c_float, l, l, vp, l]), "tb200_mul_dev": (i, [vp, l, vp, l, l, l, vp, l]), "tb200_add_dev": (i, [vp, l, vp, l, l, l, vp, l]),
+        "tb200_silu_dev": (i, [vp, l, l, l, vp, l]), "tb200_silu_mul_dev": (i, [vp, vp, l, l, l, vp, l]),
         "tb200_moe_combine_dev": (i, [vp, vp, l, i, l, vp, l]), "tb200_acts_quantize_rmsnorm": (i, [vp, vp, l, l, vp, C.c_float, l]),
         "tb200_acts_quantize_swiglu": (i, [vp, vp, vp, l, l, l]),
         "tb200_plan_create": (vp, [i, vp]), "tb200_plan_create_peers": (vp, [vp, sz, i, vp]), "tb200_plan_run": (i, [vp, i, i]), "tb200_plan_status": (i, [vp]), "tb200_plan_reset": (i, [vp]), "tb200_plan_trace": (l, [vp, vp, l]),
@@ -192,6 +194,22 @@ def rms_norm_mul(x, norm_weight, eps: float, tokens: int, k: int, y):
 
 def silu_mul(gate, up, tokens: int, k: int, y):
     _check(lib().tb200_silu_mul_dev(_ptr(gate), _ptr(up), k, tokens, k, _ptr(y), k), "silu_mul")
+
+
+def rms_norm(x, eps: float, tokens: int, k: int, y):
+    _check(lib().tb200_rms_norm_dev(_ptr(x), k, eps, tokens, k, _ptr(y), k), "rms_norm")
+
+
+def mul(a, b, tokens: int, k: int, y, broadcast_b: bool = False):
+    _check(lib().tb200_mul_dev(_ptr(a), k, _ptr(b), 0 if broadcast_b else k, tokens, k, _ptr(y), k), "mul")
+
+
+def add(a, b, tokens: int, k: int, y, broadcast_b: bool = False):
+    _check(lib().tb200_add_dev(_ptr(a), k, _ptr(b), 0 if broadcast_b else k, tokens, k, _ptr(y), k), "add")
+
+
+def silu(x, tokens: int, k: int, y):
+    _check(lib().tb200_silu_dev(_ptr(x), k, tokens, k, _ptr(y), k), "silu")
 
 
 def moe_combine(expert_out, weights, tokens: int, used: int, rows: int, out):

@@ -211,6 +211,30 @@ def test_rms_norm_mul_and_silu_mul_device(tb, oracle, tokens, k):
     assert float(np.abs(y.cpu().numpy() - ref).max() / np.abs(ref).max()) < 1e-6
 
 
+@pytest.mark.parametrize("tokens,k", [(1, 4096), (5, 1000), (33, 64)])
+def test_plain_neighbour_ops_device(tb, oracle, tokens, k):
+    """ggml_rms_norm, ggml_mul (same shape and a broadcast row), ggml_add, ggml_silu one by one (what the backend runs unfused):
+    mul and add are single IEEE operations, hence bit-exact; rms_norm as above; silu within expf's few ulp."""
+    rng = np.random.default_rng(7 * tokens + k)
+    a = (rng.standard_normal((tokens, k)) * 3).astype(np.float32)
+    b = rng.standard_normal((tokens, k)).astype(np.float32)
+    row = rng.uniform(0.5, 1.5, k).astype(np.float32)
+    y = torch.empty(tokens, k, device="cuda")
+    da, db, drow = dev(a), dev(b), dev(row)
+    tb.mul(da, db, tokens, k, y); tb.synchronize()
+    assert np.array_equal(y.cpu().numpy(), a * b)
+    tb.mul(da, drow, tokens, k, y, broadcast_b=True); tb.synchronize()
+    assert np.array_equal(y.cpu().numpy(), a * row[None])
+    tb.add(da, db, tokens, k, y); tb.synchronize()
+    assert np.array_equal(y.cpu().numpy(), a + b)
+    tb.rms_norm(da, 1e-6, tokens, k, y); tb.synchronize()
+    ref = np.stack([oracle.rms_norm_mul(r, np.ones(k, np.float32), 1e-6) for r in a])
+    assert float(np.abs(y.cpu().numpy() - ref).max() / np.abs(ref).max()) < 2e-7
+    tb.silu(da, tokens, k, y); tb.synchronize()
+    ref = np.stack([oracle.silu_mul(r, np.ones(k, np.float32)) for r in a])
+    assert float(np.abs(y.cpu().numpy() - ref).max() / np.abs(ref).max()) < 1e-6
+
+
 @pytest.mark.parametrize("tokens,used,rows", [(1, 2, 4096), (9, 2, 1000), (4, 1, 64), (3, 4, 300)])
 def test_moe_combine_bit_exact(tb, oracle, tokens, used, rows):
     rng = np.random.default_rng(rows)
