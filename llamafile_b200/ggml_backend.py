@@ -12,6 +12,7 @@ from .sgemm import GgmlTensor
 
 vp, sz = C.c_void_p, C.c_size_t
 OP_MUL_MAT, OP_MUL_MAT_ID = 23, 24
+OP_ADD, OP_MUL, OP_RMS_NORM, OP_UNARY, UNARY_SILU = 2, 6, 20, 63, 10   # include/tb200_ggml_backend.h
 
 
 class BuftIface(C.Structure):
@@ -94,6 +95,19 @@ class StandaloneHost:
     def mul_mat(self, a, b):
         """ggml_mul_mat(a, b): a [K, N] weights, b [K, T] f32 -> [N, T] f32."""
         return self.tensor(F32, a.ne[1], b.ne[1], OP_MUL_MAT, (a, b))
+
+    def add(self, a, b): return self.tensor(F32, a.ne[0], a.ne[1], OP_ADD, (a, b))
+    def mul(self, a, b): return self.tensor(F32, a.ne[0], a.ne[1], OP_MUL, (a, b))
+
+    def rms_norm(self, a, eps: float):
+        t = self.tensor(F32, a.ne[0], a.ne[1], OP_RMS_NORM, (a,))
+        t.op_params_[0] = C.c_int32.from_buffer_copy(C.c_float(eps)).value
+        return t
+
+    def silu(self, a):
+        t = self.tensor(F32, a.ne[0], a.ne[1], OP_UNARY, (a,))
+        t.op_params_[0] = UNARY_SILU
+        return t
 
     def set(self, t, ptr: int, nbytes: int):
         self.buffer.iface.set_tensor(self.buffer_p, C.addressof(t), ptr, 0, nbytes)

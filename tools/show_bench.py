@@ -20,6 +20,9 @@ if r.get("quantizer"):
 e = j.get("e2e")
 if e:
     print(f"e2e: {e['value']:.0f} {e['unit']} {e['ms_per_step']:.3f} ms/step  h2d {e['h2d_bytes_per_step']} d2h {e['d2h_bytes_per_step']}  {e.get('kernel_launches_per_step')} launches, {e.get('nodes_in_decode_plan')} plan nodes; {e['api'][:90]}")
+    wn = e.get("with_neighbours")
+    if wn:
+        print("   graph with the matmuls' neighbours:", {k: (round(v, 4) if isinstance(v, float) else v) for k, v in wn.items() if k != "graph"})
     s = e.get("llamafile_sgemm_shim")
     if s:
         print(f"   llamafile_sgemm shim: {s['value']:.0f} GB/s {s['ms_per_step']:.3f} ms/step")
