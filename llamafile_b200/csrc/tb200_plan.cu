@@ -198,9 +198,12 @@ __device__ __forceinline__ float plan_rms_scale(const PlanGroup &G, double *s_re
     return *s_scale;
 }
 
-template <int R>
-__device__ __forceinline__ void stage_rounds(const PlanGroup &G, int b0, int group, int j, float scale, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, long long *tr) {
-    const int nb = G.nb, prologue = G.prologue;
+// kNormHere: the chunk is the whole row and the prologue is RMSNorm - the sum of squares is formed from the values just loaded
+// (CTA-wide, two barriers) instead of a separate pass over the row, which cost a second L2 round trip per group.
+template <bool kFused, int R, bool kNormHere = false>
+__device__ __forceinline__ void stage_rounds(const PlanGroup &G, int b0, int group, int j, float scale, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, long long *tr,
+                                             double *s_red = nullptr, float *s_scale = nullptr) {
+    const int nb = G.nb, prologue = kFused ? G.prologue : TB200_PLAN_QUANT;   // !kFused: a plan without neighbours, the prologue branches fold away
     const float4 *x4 = reinterpret_cast<const float4 *>(G.x), *u4 = reinterpret_cast<const float4 *>(G.x2), *w4 = reinterpret_cast<const float4 *>(G.nw);
     float y[R][8], t[R][8];
 #pragma unroll
@@ -219,6 +222,26 @@ __device__ __forceinline__ void stage_rounds(const PlanGroup &G, int b0, int gro
     if (tr && b0 == 0) {                                     // trace: the first round's loads have landed
         asm volatile("" ::"f"(y[0][0]), "f"(y[0][4]));
         tr[12] = clock64();
+    }
+    if (kNormHere) {
+        // ggml_compute_forward_rms_norm_f32 (ggml.c:11850-11896): sum of x*x in double (blocks past the row were loaded as zeros), mean as float
+        double sq = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) sq += (double)__fmul_rn(y[r][e], y[r][e]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = sq;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double tot = 0.0;
+            for (int w = 0; w < kTW; ++w) tot += s_red[w];
+            const float mean = (float)(tot / (double)(nb * QK));
+            *s_scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, G.eps)));
+        }
+        __syncthreads();
+        scale = *s_scale;
     }
     if (prologue == TB200_PLAN_RMSNORM) {                    // y = x*scale (ggml_vec_scale_f32), then ggml_mul by the norm weight
 #pragma unroll
@@ -287,10 +310,17 @@ __device__ __forceinline__ void stage_rounds(const PlanGroup &G, int b0, int gro
     }
 }
 
+template <bool kFused>
 __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_lo, uint4 *s_hi, int2 *s_ds, double *s_red, float *s_scale, long long *tr = nullptr) {
     const int nb = G.nb;
     const int group = threadIdx.x >> 2, j = threadIdx.x & 3;
-    const int prologue = G.prologue;
+    const int prologue = kFused ? G.prologue : TB200_PLAN_QUANT;
+    const int all_rounds = (nb + kTW * 8 - 1) / (kTW * 8);
+    if (prologue == TB200_PLAN_RMSNORM && all_rounds <= 2) {   // the row (K <= 8192) is one chunk: norm scale from the same registers
+        if (all_rounds == 2) stage_rounds<kFused, 2, true>(G, 0, group, j, 1.f, s_lo, s_hi, s_ds, tr, s_red, s_scale);
+        else stage_rounds<kFused, 1, true>(G, 0, group, j, 1.f, s_lo, s_hi, s_ds, tr, s_red, s_scale);
+        return;
+    }
     const float scale = prologue == TB200_PLAN_RMSNORM ? plan_rms_scale(G, s_red, s_scale) : 1.f;
     // K in chunks of up to kActR rounds (a round = kTW*8 blocks, one per 4-lane group). The rounds of a chunk are independent
     // dependency chains (loads -> amax -> two divisions -> round -> pack -> sum), so they are written phase by phase across
@@ -298,10 +328,10 @@ __device__ __forceinline__ void stage_activations(const PlanGroup &G, uint4 *s_l
     // 3.5 of them (3400 -> see DESIGN 5.2c). Chunks are sized to the rounds that remain, so K = 4096 still runs one round.
     for (int b0 = 0; b0 < nb;) {
         const int rounds = (nb - b0 + kTW * 8 - 1) / (kTW * 8);
-        if (rounds >= 4) stage_rounds<4>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
-        else if (rounds == 3) stage_rounds<3>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
-        else if (rounds == 2) stage_rounds<2>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
-        else stage_rounds<1>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
+        if (rounds >= 4) stage_rounds<kFused, 4>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
+        else if (rounds == 3) stage_rounds<kFused, 3>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
+        else if (rounds == 2) stage_rounds<kFused, 2>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
+        else stage_rounds<kFused, 1>(G, b0, group, j, scale, s_lo, s_hi, s_ds, tr);
         b0 += (rounds >= 4 ? 4 : rounds) * kTW * 8;
     }
 }
@@ -355,9 +385,9 @@ __device__ __forceinline__ int plan_nearest_int(float fval) {
 // R super-blocks per warp at a time (sb, sb + kTW, ...), phase by phase so that their dependency chains - loads, a five-step arg-max
 // butterfly, two divisions, rounding, sums - interleave: the 70B down projection (K = 28672, 7 super-blocks per warp) would
 // otherwise pay seven such chains back to back on every group boundary.
-template <int R>
+template <bool kFused, int R>
 __device__ __forceinline__ void stage_q8k_rounds(const PlanGroup &G, int sb0, float scale, uint4 *s_q, int2 *s_ds) {
-    const int nsb = G.nb / 8, prologue = G.prologue;
+    const int nsb = G.nb / 8, prologue = kFused ? G.prologue : TB200_PLAN_QUANT;
     const int lane = threadIdx.x & 31;
     float v[R][8];
 #pragma unroll
@@ -437,15 +467,16 @@ __device__ __forceinline__ void stage_q8k_rounds(const PlanGroup &G, int sb0, fl
         }
     }
 }
+template <bool kFused>
 __device__ __forceinline__ void stage_activations_q8k(const PlanGroup &G, uint4 *s_q, int2 *s_ds, double *s_red, float *s_scale) {
     const int nsb = G.nb / 8;
     const int warp = threadIdx.x >> 5;
-    const float scale = G.prologue == TB200_PLAN_RMSNORM ? plan_rms_scale(G, s_red, s_scale) : 1.f;
+    const float scale = (kFused && G.prologue == TB200_PLAN_RMSNORM) ? plan_rms_scale(G, s_red, s_scale) : 1.f;
     for (int sb0 = warp; sb0 < nsb;) {                       // warp-uniform
         const int rounds = (nsb - sb0 + kTW - 1) / kTW;
-        if (rounds >= 4) { stage_q8k_rounds<4>(G, sb0, scale, s_q, s_ds); sb0 += 4 * kTW; }
-        else if (rounds >= 2) { stage_q8k_rounds<2>(G, sb0, scale, s_q, s_ds); sb0 += 2 * kTW; }
-        else { stage_q8k_rounds<1>(G, sb0, scale, s_q, s_ds); sb0 += kTW; }
+        if (rounds >= 4) { stage_q8k_rounds<kFused, 4>(G, sb0, scale, s_q, s_ds); sb0 += 4 * kTW; }
+        else if (rounds >= 2) { stage_q8k_rounds<kFused, 2>(G, sb0, scale, s_q, s_ds); sb0 += 2 * kTW; }
+        else { stage_q8k_rounds<kFused, 1>(G, sb0, scale, s_q, s_ds); sb0 += kTW; }
     }
 }
 
@@ -517,7 +548,9 @@ __device__ __forceinline__ void peers_wait(const PlanParams &P, unsigned seq, in
     __syncwarp();
 }
 
-template <int kType, bool kPeers>
+// kFused: some group of the plan has a neighbour folded in (RMSNorm / SwiGLU prologue, residual epilogue). Plans without any - a bare
+// chain of matmuls - run the instantiation in which all of that is compiled out: the extra live registers cost the bare chain 1.8 %.
+template <int kType, bool kPeers, bool kFused>
 __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant__ PlanParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *ring = smem;                                                          // [kPW][kPS][kStageBytes]
@@ -606,8 +639,8 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             } else if (g > P.first) bar_sync(kBarArrived, kThreads);
             bar_sync(kBarRelease, kThreads);                // consumers may stage and compute group g
             if (!(P.flags & 2) || g == P.first) {
-                if (kQ4K) stage_activations_q8k(G, s_lo, s_ds, s_red, &s_scale);
-                else stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale);
+                if (kQ4K) stage_activations_q8k<kFused>(G, s_lo, s_ds, s_red, &s_scale);
+                else stage_activations<kFused>(G, s_lo, s_hi, s_ds, s_red, &s_scale);
             }
             __syncthreads();
         }
@@ -749,8 +782,8 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
         bar_sync(kBarRelease, kThreads);                    // group g-1 is complete on every SM
         if (tr) tr[4] = clock64();
         if (!(P.flags & 2) || g == P.first) {
-            if (kQ4K) stage_activations_q8k(G, s_lo, s_ds, s_red, &s_scale);
-            else stage_activations(G, s_lo, s_hi, s_ds, s_red, &s_scale, tr);
+            if (kQ4K) stage_activations_q8k<kFused>(G, s_lo, s_ds, s_red, &s_scale);
+            else stage_activations<kFused>(G, s_lo, s_hi, s_ds, s_red, &s_scale, tr);
         }
         if (tr) tr[7] = clock64();
         __syncthreads();
@@ -791,7 +824,8 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             const int o_row = kR * (unit - G.unit_begin[m]) + my_r;
             const bool o_on = lane % (32 / kR) == 0 && o_row < G.rows[m];
             float *o_ptr = G.out[m] + o_row;
-            const float *o_res = G.res[m] ? G.res[m] + o_row : nullptr;
+            const float *o_res = (kFused && G.res[m]) ? G.res[m] + o_row : nullptr;
+            const float resv = (kFused && o_on && o_res) ? __ldcg(o_res) : 0.f;   // fetched now, used after the unit's block dots: an in-order warp would otherwise park on this L2 round trip at every unit's tail
             const bool last_unit = unit + GW >= nunits;
             for (int seg = 0; seg < nseg; ++seg, ++seq) {
                 const int st = seq % kPS;
@@ -840,7 +874,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             }
 #pragma unroll
             for (int o = 16 / kR; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            const float val = (o_on && o_res) ? __fadd_rn(v, __ldcg(o_res)) : v;
+            const float val = (kFused && o_on && o_res) ? __fadd_rn(v, resv) : v;
             if (o_on) {
                 // The result is written with an exchange, not a store: when the old value comes back the write has been performed
                 // at L2, the point of coherence of every SM. Once all of a warp's exchanges have returned it arrives; the CTA's
@@ -894,9 +928,27 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ host side
+typedef void (*PlanKernelFn)(const PlanParams);
+static PlanKernelFn plan_kernel_for(int type, bool peers, bool fused) {
+    const bool k = type == TB200_TYPE_Q4_K;
+    if (fused) return k ? (peers ? plan_kernel<TB200_TYPE_Q4_K, true, true> : plan_kernel<TB200_TYPE_Q4_K, false, true>)
+                        : (peers ? plan_kernel<TB200_TYPE_Q4_0, true, true> : plan_kernel<TB200_TYPE_Q4_0, false, true>);
+    return k ? (peers ? plan_kernel<TB200_TYPE_Q4_K, true, false> : plan_kernel<TB200_TYPE_Q4_K, false, false>)
+             : (peers ? plan_kernel<TB200_TYPE_Q4_0, true, false> : plan_kernel<TB200_TYPE_Q4_0, false, false>);
+}
+static bool plan_kernels_set_smem() {
+    bool ok = true;
+    for (int t = 0; t < 2; ++t)
+        for (int pe = 0; pe < 2; ++pe)
+            for (int f = 0; f < 2; ++f)
+                ok = ok && cudaFuncSetAttribute(plan_kernel_for(t ? TB200_TYPE_Q4_K : TB200_TYPE_Q4_0, pe != 0, f != 0), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess;
+    return ok;
+}
+
 struct tb200_plan {
     int n_groups, nb_max, device, type;
     int world, rank, n_shared;
+    bool fused;                        // some group has a prologue other than QUANT or a residual
     const char *local_base;
     char *peer_base[TB200_MAX_PEERS];
     unsigned *peer_flag[TB200_MAX_PEERS];
@@ -920,6 +972,7 @@ static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int
     const long GW = (long)c->sm_count * kPW;
     long rot = 0;
     int nb_max = 0, n_shared = 0;
+    bool any_fused = false;
     const char *sym_lo = pg ? (const char *)pg->out_base[pg->rank] : nullptr, *sym_hi = sym_lo + sym_bytes;
     for (int g = 0; g < n_groups; ++g) {
         const tb200_plan_group &s = groups[g];
@@ -954,6 +1007,8 @@ static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int
         G.x = s.x, G.x2 = s.x2, G.nw = s.norm_weight, G.eps = s.eps, G.prologue = s.prologue & 0xff, G.nodep = (s.prologue & TB200_PLAN_INDEPENDENT) != 0;
         G.nmat = s.n, G.nb = (int)(s.w[0]->k / QK), G.nseg = (G.nb + kSegBlocks - 1) / kSegBlocks;
         G.sh_before = n_shared;
+        if ((s.prologue & 0xff) != TB200_PLAN_QUANT) any_fused = true;
+        for (int m = 0; m < s.n; ++m) any_fused = any_fused || s.residual[m] != nullptr;
         n_shared += G.shared_mask != 0;
         G.nunits = (int)units, G.rot = (int)(rot % GW);
         rot += units;                                       // the units left over by one group go to the warps after them in the next
@@ -963,6 +1018,7 @@ static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int
     memset(p, 0, sizeof(*p));
     p->n_groups = n_groups, p->nb_max = nb_max, p->device = c->device, p->type = groups[0].w[0]->type;
     p->smem = (size_t)kPW * kPS * kStageBytes + (size_t)nb_max * (p->type == TB200_TYPE_Q4_K ? 48 : 40);   // + the launch's descriptor table (tb200_plan_run)
+    p->fused = any_fused;
     p->world = pg ? pg->world : 1, p->rank = pg ? pg->rank : 0, p->n_shared = n_shared, p->local_base = sym_lo;
     for (int q = 0; pg && q < pg->world; ++q) p->peer_base[q] = (char *)pg->out_base[q], p->peer_flag[q] = pg->flags[q];
     bool ok = p->smem + 16 * sizeof(PlanGroup) <= kPlanSmemMax;
@@ -974,10 +1030,7 @@ static tb200_plan *plan_create_impl(const tb200_peers *pg, size_t sym_bytes, int
         p->d_epoch = pg ? pg->plan_seq : p->d_cnt + (size_t)(n_groups + 1) * kCS + 3;
         ok = cudaMemcpy(p->d_groups, h, (size_t)n_groups * sizeof(PlanGroup), cudaMemcpyHostToDevice) == cudaSuccess &&
              cudaMemset(p->d_cnt, 0, (size_t)(n_groups + 1) * kCS * 4 + 16) == cudaSuccess &&
-             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
-             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
-             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess &&
-             cudaFuncSetAttribute(plan_kernel<TB200_TYPE_Q4_K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPlanSmemMax) == cudaSuccess;
+             plan_kernels_set_smem();
         if (!ok) tb200_set_error("plan_create: %s", cudaGetErrorString(cudaGetLastError()));
     } else cudaGetLastError();
     free(h);
@@ -1014,11 +1067,7 @@ int tb200_plan_run(tb200_plan *p, int first, int count) {
         const size_t smem = p->smem + (size_t)n * sizeof(PlanGroup);
         const dim3 grid((unsigned)c->sm_count), block(kTW * 32);
         static const bool force_peers = [] { const char *v = getenv("TB200_PLAN_FORCE_PEERS"); return v && *v == '1'; }();   // A/B: the multi-GPU instantiation on one GPU
-        if (p->world > 1 || force_peers) {
-            if (p->type == TB200_TYPE_Q4_K) plan_kernel<TB200_TYPE_Q4_K, true><<<grid, block, smem, c->stream>>>(P);
-            else plan_kernel<TB200_TYPE_Q4_0, true><<<grid, block, smem, c->stream>>>(P);
-        } else if (p->type == TB200_TYPE_Q4_K) plan_kernel<TB200_TYPE_Q4_K, false><<<grid, block, smem, c->stream>>>(P);
-        else plan_kernel<TB200_TYPE_Q4_0, false><<<grid, block, smem, c->stream>>>(P);
+        plan_kernel_for(p->type, p->world > 1 || force_peers, p->fused)<<<grid, block, smem, c->stream>>>(P);
         tb200_count_launch();
         TB_CUDA(cudaGetLastError());
     }
