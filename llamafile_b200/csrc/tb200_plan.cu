@@ -149,6 +149,11 @@ __device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.ar
 #ifndef TB200_PLAN_CNT_STRIDE
 #define TB200_PLAN_CNT_STRIDE 1
 #endif
+#ifndef TB200_PLAN_DEBUG
+#define TB200_PLAN_DEBUG 0
+#endif
+constexpr bool kDbg = TB200_PLAN_DEBUG != 0;             // phase stamps (tb200_plan_trace) and the TB200_PLAN_FLAGS experiments: a probe build only
+                                                          // (tools/build_variant.sh ... -DTB200_PLAN_DEBUG=1); their branches and live registers cost the step ~1-2 %
 constexpr int kCS = TB200_PLAN_CNT_STRIDE;                   // words between the arrival counters of consecutive groups
 constexpr int kTraceSlots = 24;                            // tb200_plan_trace: stamps 0..15, per-group sums of warp 0 in 16..21
 constexpr long long kSpinLimit = 4000000000LL;            // ~2 s of SM clocks: a wedged wait gives up and raises *err
@@ -571,6 +576,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int GW = (int)gridDim.x * kPW, gw = (int)blockIdx.x * kPW + warp;
+    const int xflags = kDbg ? P.flags : 0;              // experiment switches (probe builds only)
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(P.groups + P.first);
         uint4 *dst = reinterpret_cast<uint4 *>(s_ds + P.nb_max);
@@ -596,7 +602,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
         int prev_real = -1;                                 // counter of the last boundary that was a real grid barrier (to be re-armed by the next one)
         for (int g = P.first; g < P.end; ++g) {
             const PlanGroup &G = tab[g];
-            long long *tr = P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
+            long long *tr = kDbg && P.trace && lane == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
             // (descriptor look-ups of the boundary before the wait, off the critical path)
             // once any wait of this launch has given up (a peer died, the ranks' plans disagree) nobody waits any more: the launch
             // drains in microseconds instead of a spin limit per group, and tb200_plan_status() reports it
@@ -606,11 +612,11 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             // a group declared independent starts without the grid barrier (only the CTA's own warps meet, the staging buffers are
             // reused) - unless the group before it exchanged rows with the peers, whose arrival some barrier has to cover
             const bool skip = g > P.first && G.nodep && !shared;
-            if (g > P.first && !(P.flags & 4) && !skip) {
+            if (g > P.first && !(xflags & 4) && !skip) {
                 bar_sync(kBarArrived, kThreads);            // every consumer warp of this CTA has stored its results of group g-1
                 if (tr) tr[1] = clock64();
                 if (lane == 0) {
-                    if ((P.flags & 9) == 8) fence_acq_rel_gpu();   // (old protocol, flag 8: plain stores + a release fence here, ~1 us per group)
+                    if ((xflags & 9) == 8) fence_acq_rel_gpu();   // (old protocol, flag 8: plain stores + a release fence here, ~1 us per group)
                     if (tr) tr[13] = clock64();
                     const unsigned old = atom_add_relaxed(P.cnt + (g - 1) * kCS, 1u);
                     if (tr) tr[2] = clock64();
@@ -638,7 +644,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 if (shared && !dead) peers_wait(P, seq, lane);
             } else if (g > P.first) bar_sync(kBarArrived, kThreads);
             bar_sync(kBarRelease, kThreads);                // consumers may stage and compute group g
-            if (!(P.flags & 2) || g == P.first) {
+            if (!(xflags & 2) || g == P.first) {
                 if (kQ4K) stage_activations_q8k<kFused>(G, s_lo, s_ds, s_red, &s_scale);
                 else stage_activations<kFused>(G, s_lo, s_hi, s_ds, s_red, &s_scale);
             }
@@ -777,11 +783,11 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
     unsigned seq = 0;                                       // items consumed by this warp
     for (int g = P.first; g < P.end; ++g) {
         const PlanGroup &G = tab[g];
-        long long *tr = P.trace && threadIdx.x == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
+        long long *tr = kDbg && P.trace && threadIdx.x == 0 ? P.trace + ((long)g * gridDim.x + blockIdx.x) * kTraceSlots : nullptr;
         if (tr) tr[0] = clock64(), tr[8] = tr[11] = 0;
         bar_sync(kBarRelease, kThreads);                    // group g-1 is complete on every SM
         if (tr) tr[4] = clock64();
-        if (!(P.flags & 2) || g == P.first) {
+        if (!(xflags & 2) || g == P.first) {
             if (kQ4K) stage_activations_q8k<kFused>(G, s_lo, s_ds, s_red, &s_scale);
             else stage_activations<kFused>(G, s_lo, s_hi, s_ds, s_red, &s_scale, tr);
         }
@@ -883,7 +889,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
                 // ring's bulk copies in flight. The round trips overlap the following units' block dots; only the last is exposed.
                 // (A warp executes in order: consuming the old value right away would park the warp for the whole round trip,
                 // ~600 cycles per unit. It is folded in one unit later, when it has long since returned.)
-                if (!(P.flags & 8)) sink ^= pend, pend = atom_exch_relaxed(o_ptr, val);
+                if (!(xflags & 8)) sink ^= pend, pend = atom_exch_relaxed(o_ptr, val);
                 else *o_ptr = val;
                 if (tr && tr[11] == 0) tr[11] = clock64();
             }
@@ -916,7 +922,7 @@ __global__ void __launch_bounds__(kTW * 32, 1) plan_kernel(const __grid_constant
             for (int p = 0; p < TB200_MAX_PEERS; ++p)
                 if (p < P.world) sink ^= pendr[p], pendr[p] = 0;
         }
-        if (!(P.flags & 8)) { sink ^= pend; asm volatile("" ::"r"(sink) : "memory"); }   // every exchange of this lane has returned
+        if (!(xflags & 8)) { sink ^= pend; asm volatile("" ::"r"(sink) : "memory"); }   // every exchange of this lane has returned
 
         if (tr) tr[6] = clock64();
         __syncwarp();
@@ -1092,6 +1098,7 @@ int tb200_plan_reset(tb200_plan *p) {
 long tb200_plan_trace(tb200_plan *p, long long *out, long capacity) {
     tb200_ctx *c = tb200_get_ctx();
     if (!p || !c) return -1;
+    if (!kDbg) { tb200_set_error("plan_trace: this build has no phase stamps (compile tb200_plan.cu with -DTB200_PLAN_DEBUG=1)"); return -2; }
     const long n = (long)p->n_groups * c->sm_count * kTraceSlots;
     if (!p->d_trace) {
         if (cudaMalloc((void **)&p->d_trace, (size_t)n * 8) != cudaSuccess || cudaMemset(p->d_trace, 0, (size_t)n * 8) != cudaSuccess) { cudaGetLastError(); p->d_trace = nullptr; return -1; }

@@ -1,7 +1,10 @@
 #!/usr/bin/env python
 """Where does a decode-plan group spend its time? Runs a plan of identical groups and prints per-phase SM-clock deltas
 (tb200_plan_trace) averaged over groups, for a few CTAs, plus the CUDA-event time per group.
-    python tools/plan_probe.py [--n 4096 --k 4096 --groups 32]"""
+    python tools/plan_probe.py [--n 4096 --k 4096 --groups 32]
+The stamps exist only in a probe build of the library:
+    tools/build_variant.sh plan_dbg tb200_plan.cu -DTB200_PLAN_DEBUG=1 [-DTB200_PLAN_TRACE_ITEMS]
+    TB200_LIB=tools/_variants/plan_dbg.so python tools/plan_probe.py ..."""
 import argparse
 import sys
 from pathlib import Path
@@ -10,6 +13,11 @@ import numpy as np
 
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
+
+
+def lib_has_no_trace(plan):
+    from llamafile_b200.lib import lib
+    return lib().tb200_plan_trace(plan.handle, None, 0) == -2
 
 
 def main():
@@ -53,7 +61,9 @@ def main():
     us = e0.elapsed_time(e1) * 1e3 / 10 / a.groups
     byts = a.mats * a.n * a.k * 18 / 32
     print(f"N={a.n} K={a.k} mats={a.mats}: {us:.2f} us per group, {byts / us / 1e3:.0f} GB/s, status {plan.status()}")
-    plan.trace()
+    if plan.trace() is None and lib_has_no_trace(plan):
+        print('  (no phase stamps in this build: see the docstring)')
+        return
     with torch.cuda.stream(stream):
         plan.run()
         stream.synchronize()
