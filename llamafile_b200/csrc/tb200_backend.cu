@@ -163,7 +163,7 @@ bool host_buft_is_host(tb200_buft_t) { return true; }
 
 // ------------------------------------------------------------------------------------------------ backend
 struct PlanKey {
-    std::vector<const void *> ptrs;   // (weights data, input data, output data) per node
+    std::vector<const void *> ptrs;   // (output data, weights data, input data, op | first parameter word, row length) per node
     bool operator<(const PlanKey &o) const { return ptrs < o.ptrs; }
 };
 struct BackendCtx {
@@ -463,7 +463,10 @@ int backend_graph_compute(tb200_backend_t bk, struct ggml_cgraph *cg_) {
                 key.ptrs.push_back(n->data);
                 key.ptrs.push_back(n->src_[0] ? tv((const struct ggml_tensor *)n->src_[0])->data : nullptr);
                 key.ptrs.push_back(n->src_[1] ? tv((const struct ggml_tensor *)n->src_[1])->data : nullptr);
-                key.ptrs.push_back((const void *)(uintptr_t)n->op_);
+                // op, its first parameter word (rms_norm's eps, the unary function) and the row length: an allocator may hand the same
+                // addresses to a different graph
+                key.ptrs.push_back((const void *)((uintptr_t)(uint32_t)n->op_ | ((uintptr_t)(uint32_t)n->op_params_[0] << 32)));
+                key.ptrs.push_back((const void *)(uintptr_t)n->ne[0]);
             }
             auto it = c->plans.find(key);
             if (it != c->plans.end() && it->second.epoch != g_resident_epoch.load()) {   // some resident weights were freed since: the plan may hold one

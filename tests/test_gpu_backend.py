@@ -233,6 +233,46 @@ def test_ffn_block_neighbours_folded_into_the_plan(tb, host, wt, tokens, extra_r
     g.free()
 
 
+def test_cached_plan_follows_a_changed_node_parameter(tb, host):
+    """The plan cache is keyed by the run's nodes: addresses, op, first parameter word, row length. The same tensors at the same
+    addresses with another rms_norm eps (here: the node's op_params rewritten in place between two computes, what a second graph
+    from a reusing allocator looks like to the backend) must not replay the plan that folded the old eps."""
+    import ctypes as C
+    from llamafile_b200.sgemm import GgmlTensor
+    G, backend, cpu = host
+    K, F, wt = 512, 1280, H.Q4_0
+    shapes = {"gate": (F, K), "up": (F, K)}
+    rng = np.random.default_rng(44)
+    inputs = {n: B.oracle().quantize_q4_0(rng.standard_normal((rows, k)).astype(np.float32) / np.sqrt(k)) for n, (rows, k) in shapes.items()}
+    inputs["x"] = (rng.standard_normal((1, K)) * 1e-2).astype(np.float32)     # small values: eps matters (mean square 1e-4)
+    inputs["nw"] = rng.uniform(0.5, 1.5, K).astype(np.float32)
+    res = {}
+    for bk, name in ((backend, "tb200"), (cpu, "cpu")):
+        g = Graph(bk)
+        t = {n: g.tensor(wt, k, rows) for n, (rows, k) in shapes.items()}
+        t["x"], t["nw"] = g.tensor(H.F32, K, 1), g.tensor(H.F32, K)
+        norm = g.rms_norm(t["x"], 1e-5)
+        cur = g.mul(norm, t["nw"])
+        ga, up = g.mul_mat(t["gate"], cur), g.mul_mat(t["up"], cur)
+        g.build([ga, up], weights_usage=True)
+        for n, arr in inputs.items():
+            g.set(t[n], arr)
+        outs = []
+        for eps in (1e-5, 1e-3, 1e-5):
+            C.cast(norm, C.POINTER(GgmlTensor)).contents.op_params_[0] = C.c_int32.from_buffer_copy(C.c_float(eps)).value
+            assert g.compute() == 0 and g.compute() == 0
+            if name == "tb200":
+                launches, plan_nodes = tb.backend_last_graph_stats(backend)
+                assert plan_nodes == 2, (launches, plan_nodes)      # both matmuls ran inside a plan (the norm + its weight as the group's prologue)
+            outs.append(g.get(ga, (1, F)))
+        res[name] = outs
+        g.free()
+    for i, (got, ref) in enumerate(zip(res["tb200"], res["cpu"])):
+        H.assert_close(got, ref, f"eps case {i}")
+    assert np.array_equal(res["tb200"][0], res["tb200"][2])
+    assert np.abs(res["cpu"][0] - res["cpu"][1]).max() > 0.05 * np.abs(res["cpu"][0]).max(), "the test's eps values must change the result"
+
+
 def test_sum_of_two_matmuls_of_one_group_is_not_folded(tb, host):
     """a.x + b.x: both matmuls share their input, i.e. one plan group without a barrier between them, so the add cannot become the
     residual epilogue of either (it would read the other's rows while they are being written); and a chain a.x -> + r -> b -> + (a.x + r)."""
