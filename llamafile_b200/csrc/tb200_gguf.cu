@@ -132,13 +132,21 @@ tb200_gguf *tb200_gguf_open(const char *path) {
         if (!skip_value(c, type, is_align ? &v : nullptr)) return fail("truncated or unknown metadata value");
         if (is_align && type == 4 && v && (v & (v - 1)) == 0) g->alignment = (size_t)v;
     }
+    // a tensor info is at least 8 (name length) + 4 (rank) + 8 (one extent) + 4 (type) + 8 (offset) bytes: a header that announces
+    // more of them than the rest of the file can hold is refused before anything is allocated for it
+    if (n_tensors > (uint64_t)(c.end - c.p) / 32) return fail("more tensor infos announced than the file can hold");
     g->tensors.resize((size_t)n_tensors);
     for (auto &t : g->tensors) {
         if (!c.str(&t.name)) return fail("truncated tensor name");
         t.n_dims = (int)c.get<uint32_t>();
         if (!c.ok || t.n_dims < 1 || t.n_dims > 4) return fail("tensor rank outside 1..4");
         for (int d = 0; d < 4; ++d) t.ne[d] = 1;
-        for (int d = 0; d < t.n_dims; ++d) t.ne[d] = (int64_t)c.get<uint64_t>();
+        uint64_t elems = 1;
+        for (int d = 0; d < t.n_dims; ++d) {
+            const uint64_t e = c.get<uint64_t>();
+            if (e > (uint64_t)INT64_MAX || __builtin_mul_overflow(elems, e, &elems) || elems > (uint64_t)INT64_MAX) return fail("tensor extents overflow");
+            t.ne[d] = (int64_t)e;
+        }
         t.type = (int)c.get<uint32_t>();
         t.offset = c.get<uint64_t>();
         if (!c.ok) return fail("truncated tensor info");
@@ -170,18 +178,22 @@ int tb200_gguf_find(const tb200_gguf *g, const char *name, int *type, int64_t ne
         if (t.name != name) continue;
         if (type) *type = t.type;
         if (ne) memcpy(ne, t.ne, sizeof(t.ne));
-        size_t row = 0;
+        uint64_t row = 0;
+        bool wraps = false;
         switch (t.type) {
-        case TB200_TYPE_F32: case TB200_TYPE_I32: row = (size_t)t.ne[0] * 4; break;
+        case TB200_TYPE_F32: case TB200_TYPE_I32: wraps = __builtin_mul_overflow((uint64_t)t.ne[0], (uint64_t)4, &row); break;
         default: row = tb200_gguf_row_bytes(t.type, (long)t.ne[0]); break;
         }
-        const size_t total = row * (size_t)t.ne[1] * (size_t)t.ne[2] * (size_t)t.ne[3];
-        if (g->data_start + t.offset > g->size || (total && g->data_start + t.offset + total > g->size)) {
+        // offset and extents come from the file: compare without letting either sum or product wrap
+        const uint64_t avail = (uint64_t)(g->size - g->data_start);
+        uint64_t total = row;
+        for (int d = 1; d < 4; ++d) wraps |= __builtin_mul_overflow(total, (uint64_t)t.ne[d], &total);
+        if (wraps || t.offset > avail || total > avail - t.offset) {
             tb200_set_error("gguf: tensor %s lies outside the file", name);
             return TB200_ERR_INVALID;
         }
         if (data) *data = g->map + g->data_start + t.offset;
-        if (bytes) *bytes = total;
+        if (bytes) *bytes = (size_t)total;
         return TB200_OK;
     }
     tb200_set_error("gguf: no tensor named %s", name);

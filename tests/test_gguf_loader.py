@@ -97,6 +97,110 @@ def test_loader_rejects_garbage(tbmod, tmp_path):
     f.close()
 
 
+def raw_gguf(tensors, kvs=b"", n_kv=0, version=3, n_tensors=None, data=b"", pad_to=32):
+    """A GGUF file written by hand (ggml.c:20896-21160): tensors = [(name, [ne...], ggml type, offset)]."""
+    import struct
+    def s(b): return struct.pack("<Q", len(b)) + b
+    out = b"GGUF" + struct.pack("<IQQ", version, len(tensors) if n_tensors is None else n_tensors, n_kv) + kvs
+    for name, ne, ty, off in tensors:
+        out += s(name.encode()) + struct.pack("<I", len(ne)) + b"".join(struct.pack("<Q", e & (2**64 - 1)) for e in ne) + struct.pack("<IQ", ty, off & (2**64 - 1))
+    out += bytes(-len(out) % pad_to)
+    return out + data
+
+
+def test_loader_refuses_hostile_headers(tbmod, tmp_path):
+    """Extents, offsets and counts come from the file: nothing may wrap, be allocated for, or be read past the mapping."""
+    import struct
+    p = tmp_path / "h.gguf"
+    data = bytes(range(256)) * 16                      # 4096 bytes of tensor data
+
+    def opens(blob):
+        p.write_bytes(blob)
+        return tbmod.GgufFile(p)
+
+    def refused_at_open(blob):
+        p.write_bytes(blob)
+        with pytest.raises(tbmod.TB200Error):
+            tbmod.GgufFile(p)
+
+    # the well-formed twin first: one F32 vector of 1024 elements = the whole data section
+    f = opens(raw_gguf([("v", [1024], H.F32, 0)], data=data))
+    assert f.info("v")[3] == 4096 and np.array_equal(f.raw("v"), np.frombuffer(data, np.uint8))
+    f.close()
+    # offsets: just past the end, far past, and 2^64 - 32 (data_start + offset wraps to a small number)
+    for off in (32, 1 << 40, -32, -4096 + 32):
+        f = opens(raw_gguf([("v", [1024], H.F32, off)], data=data))
+        with pytest.raises(tbmod.TB200Error, match="outside the file"):
+            f.info("v")
+        f.close()
+    # extents whose byte size wraps: 2^62 floats x 4 = 2^64 = 0 bytes; rows x row bytes wrapping; 2^63 as a "negative" extent
+    for ne in ([1 << 62], [1024, 1 << 52], [32, 1 << 29, 1 << 28], [1 << 61, 3]):
+        f = opens(raw_gguf([("v", ne, H.F32, 0)], data=data))
+        with pytest.raises(tbmod.TB200Error, match="outside the file"):
+            f.info("v")
+        f.close()
+    refused_at_open(raw_gguf([("v", [1 << 63], H.F32, 0)], data=data))
+    refused_at_open(raw_gguf([("v", [1024, 1 << 54], H.F32, 0)], data=data))
+    refused_at_open(raw_gguf([("v", [32, 1 << 31, 1 << 31], H.F32, 0)], data=data))
+    refused_at_open(raw_gguf([("v", [1 << 32, 1 << 32], H.F32, 0)], data=data))      # element count does not fit int64
+    refused_at_open(raw_gguf([("v", [4, 4, 4, 4, 4], H.F32, 0)], data=data))          # rank 5
+    refused_at_open(raw_gguf([("v", [], H.F32, 0)], data=data))                       # rank 0
+    # counts: a header announcing 16M tensors / kvs in a 4 KB file, an array of 2^60 u64s, a string of 2^63 bytes
+    refused_at_open(raw_gguf([], n_tensors=1 << 24, data=data))
+    refused_at_open(raw_gguf([], n_tensors=1 << 60, data=data))
+    refused_at_open(raw_gguf([], n_kv=1 << 24, data=data))
+    key = struct.pack("<Q", 1) + b"k"
+    refused_at_open(raw_gguf([], kvs=key + struct.pack("<IIQ", 9, 10, 1 << 60), n_kv=1, data=data))
+    refused_at_open(raw_gguf([], kvs=key + struct.pack("<IQ", 8, 1 << 63), n_kv=1, data=data))
+    refused_at_open(raw_gguf([], kvs=key + struct.pack("<I", 13), n_kv=1, data=data))             # unknown value type
+    refused_at_open(raw_gguf([], kvs=key + struct.pack("<IIQ", 9, 9, 1), n_kv=1, data=data))      # array of arrays: not in the format
+    refused_at_open(raw_gguf([("v", [1024], H.F32, 0)], version=1, data=data))
+    refused_at_open(raw_gguf([("v", [1024], H.F32, 0)], version=4, data=data))
+    # every metadata value type the format has, skipped correctly (the tensor after them is found where it is)
+    kvs, n = b"", 0
+    for ty, payload in ((0, b"\x01"), (1, b"\xff"), (2, b"\x01\x02"), (3, b"\x01\x02"), (4, bytes(4)), (5, bytes(4)), (6, bytes(4)), (7, b"\x01"),
+                        (8, struct.pack("<Q", 3) + b"abc"), (10, bytes(8)), (11, bytes(8)), (12, bytes(8)),
+                        (9, struct.pack("<IQ", 6, 3) + bytes(12)), (9, struct.pack("<IQ", 8, 2) + struct.pack("<Q", 1) + b"x" + struct.pack("<Q", 0)),
+                        (9, struct.pack("<IQ", 12, 0))):
+        k = f"key.{n}".encode()
+        kvs += struct.pack("<Q", len(k)) + k + struct.pack("<I", ty) + payload
+        n += 1
+    k = b"general.alignment"
+    kvs += struct.pack("<Q", len(k)) + k + struct.pack("<II", 4, 128)
+    f = opens(raw_gguf([("v", [1024], H.F32, 0)], kvs=kvs, n_kv=n + 1, data=data, pad_to=128))
+    assert np.array_equal(f.raw("v"), np.frombuffer(data, np.uint8))
+    f.close()
+
+
+def test_loader_survives_every_truncation(tbmod, tmp_path):
+    """The first n bytes of a real file, for every n in the header and a sample beyond: open() either refuses or returns a file
+    whose tensors are each readable in full or refused - never a crash, never a read past the mapping."""
+    good = tmp_path / "m.gguf"
+    tensors = model_tensors()
+    write_model(good, tensors)
+    blob = good.read_bytes()
+    f = tbmod.GgufFile(good)
+    f.close()
+    p = tmp_path / "t.gguf"
+    header_end = blob.index(b"blk.0.w0.weight") + 600
+    opened = 0
+    for n in list(range(0, min(header_end, len(blob)))) + list(range(header_end, len(blob), 997)):
+        p.write_bytes(blob[:n])
+        try:
+            f = tbmod.GgufFile(p)
+        except tbmod.TB200Error:
+            continue
+        opened += 1
+        for name in f.names():
+            try:
+                raw = f.raw(name)
+            except tbmod.TB200Error:
+                continue
+            assert np.array_equal(raw, tensors[name][2]), (n, name)
+        f.close()
+    assert opened > 0
+
+
 @pytest.mark.gpu
 def test_gguf_weights_multiply_like_direct_upload(tmp_path):
     import torch
